@@ -1,0 +1,239 @@
+/* vulcan_b200.h — C ABI of the B200-native TSDF-fusion hot path.
+ *
+ * This is the drop-in boundary underneath the reference's public C++ classes
+ * (vulcan::Volume, *Integrator, Tracer, Frame).  Every entry point cites the
+ * reference interface it replaces (paths relative to /root/reference).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++ or torch types.
+ *   - return value: 0 = ok, >0 = cudaError_t, <0 = VK_E_* below.  Nothing throws.
+ *   - all work is stream-ordered on the `stream` argument (a cudaStream_t passed
+ *     as void*; NULL = legacy default stream, which is what the reference uses for
+ *     all of its launches, include/vulcan/device.h:40-52).
+ *   - no process-global device state (the reference keeps its allocator counters
+ *     in translation-unit __device__ globals, src/volume.cu:17-21; here they are
+ *     per volume).
+ *   - struct layouts below that mirror reference value types are byte images of
+ *     those types so that the C++ wrappers can pass `&member` without repacking.
+ */
+#ifndef VULCAN_B200_H_
+#define VULCAN_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VK_E_INVALID   (-1)  /* bad argument                                        */
+#define VK_E_NODEVICE  (-2)  /* no CUDA device / kernels not built for this device  */
+#define VK_E_OVERFLOW  (-3)  /* voxel pool or excess list exhausted (non fatal;     */
+                             /* the reference drops such requests silently,         */
+                             /* src/volume.cu:338-356)                              */
+
+#define VK_BLOCK_RES     8      /* Block::resolution, include/vulcan/block.h:13    */
+#define VK_BLOCK_VOXELS  512    /* Block::voxel_count, include/vulcan/block.h:15   */
+#define VK_BOUNDS_W      80     /* hard coded in src/tracer.cpp:56                 */
+#define VK_BOUNDS_H      60     /* hard coded in src/tracer.cpp:57                 */
+
+/* byte image of vulcan::Voxel (include/vulcan/voxel.h:41-49), 20 bytes */
+typedef struct vkVoxel {
+  float   distance;
+  float   color[3];
+  int16_t distance_weight;
+  int16_t color_weight;
+} vkVoxel;
+
+/* byte image of vulcan::HashEntry (include/vulcan/hash.h:49-55), 16 bytes */
+typedef struct vkHashEntry {
+  int16_t block[3];
+  int16_t pad;
+  int32_t data;   /* voxel-block id, -1 = not allocated */
+  int32_t next;   /* entry index of next chain element, -1 = end */
+} vkHashEntry;
+
+/* byte image of vulcan::Patch (include/vulcan/tracer.h:13-22), 16 bytes */
+typedef struct vkPatch {
+  int16_t origin[2];
+  int16_t size[2];
+  float   bounds[2];
+} vkPatch;
+
+/* byte image of vulcan::Transform (include/vulcan/transform.h:166-170):
+ * column-major 4x4 matrix followed by its (cached) inverse, 128 bytes */
+typedef struct vkTransform {
+  float m[16];
+  float inv[16];
+} vkTransform;
+
+/* byte image of vulcan::Projection (include/vulcan/projection.h:109-113) */
+typedef struct vkProjection {
+  float fx, fy, cx, cy;
+} vkProjection;
+
+/* byte image of vulcan::Light (include/vulcan/light.h:62-66) */
+typedef struct vkLight {
+  float intensity;
+  float position[3];
+} vkLight;
+
+/* vulcan::Visibility (include/vulcan/types.h:6-11) */
+enum { VK_VIS_UNKNOWN = 0, VK_VIS_FALSE = 1, VK_VIS_TRUE = 2 };
+
+/* device-resident counters of one volume (ints) */
+enum {
+  VK_CNT_VISIBLE0   = 0,  /* visible count, slot 0                                  */
+  VK_CNT_VISIBLE1   = 1,  /* visible count, slot 1                                  */
+  VK_CNT_VOXEL_PTR  = 2,  /* top of free voxel-block stack (voxel_pointer)          */
+  VK_CNT_EXCESS_PTR = 3,  /* next excess entry (excess_pointer)                     */
+  VK_CNT_OVERFLOW   = 4,  /* number of dropped allocations                          */
+  VK_CNT_NEW_BLOCKS = 5,  /* blocks allocated by the last vk_set_view               */
+  VK_CNT_ALLOCATED  = 6,  /* blocks allocated in total                              */
+  VK_CNT_PATCHES    = 7,  /* patch count of the last vk_compute_patches             */
+  VK_CNT_COUNT      = 16
+};
+
+/* One voxel-hash volume.  Replaces the data members of vulcan::Volume
+ * (include/vulcan/volume.h:86-116).  All pointers are device pointers owned by
+ * the library between vk_volume_create and vk_volume_destroy. */
+typedef struct vkVolume {
+  vkVoxel*     voxels;        /* [(M+E)*512], 256-byte aligned                      */
+  vkHashEntry* entries;       /* [M+E]: [0,M) bucket heads, [M,M+E) excess          */
+  int32_t*     free_list;     /* [M+E] free voxel-block ids (stack)                 */
+  uint8_t*     visibility;    /* [M+E] vulcan::Visibility per entry                 */
+  int32_t*     visible[2];    /* [M+E] each; visible[visible_slot] is current       */
+  int32_t*     stamps;        /* [M+E] id of the last SetView that touched an entry */
+  int32_t*     locks;         /* [M]   per-bucket insertion locks                   */
+  int32_t*     counters;      /* [VK_CNT_COUNT] device                              */
+  int32_t*     host_counters; /* [VK_CNT_COUNT] pinned host mirror                  */
+  int32_t      main_blocks;   /* M (also the hash modulus K)                        */
+  int32_t      excess_blocks; /* E                                                  */
+  float        voxel_length;
+  float        trunc_length;
+  float        min_depth;     /* Volume::depth_range_ (gates allocation only)       */
+  float        max_depth;
+  int32_t      shard_rank;    /* 0 when unsharded                                   */
+  int32_t      shard_count;   /* 1 when unsharded                                   */
+  int32_t      shard_shift;   /* log2 of the brick edge in blocks                   */
+  int32_t      visible_slot;  /* which of visible[] / VK_CNT_VISIBLE* is current    */
+  int32_t      view_id;       /* number of vk_set_view calls so far                 */
+  int32_t      reserved;
+} vkVolume;
+
+/* One RGB-D frame on the device.  Replaces vulcan::Frame
+ * (include/vulcan/frame.h:11-32); images are row-major, colour/normal images are
+ * packed 3 x float per pixel like vulcan::ColorImage (include/vulcan/image.h:268-272). */
+typedef struct vkFrame {
+  const float* depth;         /* [depth_w*depth_h] metric z depth, 0 = invalid      */
+  const float* color;         /* [color_w*color_h*3] or NULL                        */
+  const float* normal;        /* [depth_w*depth_h*3] or NULL (LightIntegrator)      */
+  int32_t      depth_w, depth_h;
+  int32_t      color_w, color_h;
+  vkProjection depth_proj;
+  vkProjection color_proj;
+  vkTransform  depth_to_world;
+  vkTransform  depth_to_color;
+} vkFrame;
+
+/* ---- volume lifetime --------------------------------------------------------- */
+
+/* Volume::Volume + Volume::Initialize (src/volume.cu:370-380,552-627).  Allocates
+ * every pool with cudaMalloc and fills it like the reference: voxels = Voxel::Empty(),
+ * entries invalid, free list = 0..B-1, voxel pointer B-1, excess pointer M,
+ * visibility FALSE.  Defaults: trunc 0.04, voxel 0.008, depth range (0.1, 5). */
+int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks, void* stream);
+
+/* Re-runs the fills of vk_volume_create on the existing pools. */
+int vk_volume_reset(vkVolume* v, void* stream);
+
+/* ~Buffer<T> of each member (include/vulcan/buffer.h:28-31). */
+int vk_volume_destroy(vkVolume* v);
+
+/* ---- Volume::SetView (src/volume.cu:430-437) --------------------------------- */
+
+/* ResetBlockVisibility + CreateAllocationRequests + HandleAllocationRequests +
+ * UpdateBlockVisibility, iterated to the fixed point the reference reaches by
+ * calling SetView repeatedly (apps/vulcan/vulcan.cu:316-318,
+ * tests/tracer_test.cu:298-303) — in one call, with no host synchronisation.
+ * The visible count stays on the device (counters[VK_CNT_VISIBLE0 + visible_slot]). */
+int vk_set_view(vkVolume* v, const vkFrame* f, void* stream);
+
+/* Copies the counters to host_counters and synchronises the stream.  Returns the
+ * current visible-block count in *visible (Volume::GetBufferSize, src/volume.cu:537-543);
+ * returns VK_E_OVERFLOW if any allocation has been dropped. */
+int vk_volume_sync_counters(vkVolume* v, int* visible, void* stream);
+
+/* ---- Integrators ------------------------------------------------------------- */
+
+/* DepthIntegrator::Integrate (src/depth_integrator.cu:17-115). */
+int vk_integrate_depth(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
+                       float max_distance_weight, void* stream);
+
+/* ColorIntegrator::Integrate (src/color_integrator.cu:17-204): depth update followed
+ * by the colour update of the same voxel, in one pass over the voxel tiles. */
+int vk_integrate_color(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
+                       float max_distance_weight, float max_color_weight, void* stream);
+
+/* LightIntegrator::ComputeFrameMask (src/light_integrator.cu:17-103,277-293). */
+int vk_compute_frame_mask(const vkFrame* f, float depth_threshold, float* mask, void* stream);
+
+/* LightIntegrator::Integrate (src/light_integrator.cu:270-354); `mask` is scratch of
+ * depth_w*depth_h floats (LightIntegrator::frame_mask_). */
+int vk_integrate_light(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
+                       float max_distance_weight, float max_color_weight,
+                       const vkLight* light, float depth_threshold, float* mask, void* stream);
+
+/* ---- Tracer ------------------------------------------------------------------ */
+
+/* Tracer::Trace (src/tracer.cpp:41-47): ray bounds from the current visible list,
+ * per-pixel ray march, normals.  `bounds` is scratch of VK_BOUNDS_W*VK_BOUNDS_H*2 floats
+ * (Tracer::bounds_).  out_depth/out_color/out_normal are the traced frame's images
+ * (out_normal may be NULL).  `view` supplies pose, intrinsics and image size only. */
+int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth,
+             float* bounds, float* out_depth, float* out_color, float* out_normal,
+             void* stream);
+
+/* Same, but additionally writes per-pixel merge keys (depth_bits << 32 | rgb8 << 8 | rank)
+ * for the sharded nearest-hit merge; a pixel without an owned hit gets the key of +inf. */
+int vk_trace_keys(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth,
+                  float* bounds, unsigned long long* out_keys, void* stream);
+
+/* Decode merged keys into depth + colour images and compute normals from the merged depth. */
+int vk_resolve_keys(const unsigned long long* keys, const vkFrame* view, float* out_depth,
+                    float* out_color, float* out_normal, void* stream);
+
+/* Step-wise entry points with the reference's free-function signatures
+ * (include/vulcan/tracer.cuh:14-32; used directly by tests/tracer_test.cu). */
+int vk_compute_patches(const int* indices, const vkHashEntry* entries, const vkTransform* Tcw,
+                       const vkProjection* proj, float block_length, float min_depth,
+                       float max_depth, int block_count, int image_w, int image_h,
+                       int bounds_w, int bounds_h, vkPatch* patches, int* patch_count,
+                       void* stream);
+int vk_compute_bounds(const vkPatch* patches, float* bounds, int bounds_w, int patch_count,
+                      void* stream);
+int vk_reset_bounds(float* bounds, int count, void* stream);
+int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxels, const float* bounds,
+                      int block_count, float block_length, float voxel_length,
+                      float trunc_length, const vkTransform* Twc, const vkProjection* proj,
+                      float* depths, float* colors, int image_w, int image_h,
+                      int bounds_w, int bounds_h, void* stream);
+
+/* Frame::ComputeNormals / vulcan::ComputeNormals (src/frame.cu:7-122,183-192). */
+int vk_compute_normals(const float* depths, const vkProjection* proj, float* normals,
+                       int image_w, int image_h, void* stream);
+
+/* Frame::FilterDepths / vulcan::FilterDepths (src/frame.cu:124-181,194-203). */
+int vk_filter_depths(int image_w, int image_h, const float* src, float* dst, void* stream);
+
+/* ---- misc -------------------------------------------------------------------- */
+
+/* Library version and the number of kernels launched by this library since load
+ * (used by bench.py's gpu_launches). */
+int vk_version(void);
+unsigned long long vk_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* VULCAN_B200_H_ */

@@ -1,0 +1,470 @@
+// vk_alloc.cu — Volume::SetView rebuilt for sm_100a.
+//
+// Reference (src/volume.cu:430-437) = thrust::replace over all B visibility bytes
+// + per-pixel request kernel (one surviving request per bucket per pass, racy)
+// + per-bucket handler + a 20-barrier scan over all B entries + two blocking
+// symbol memcpys, and the caller has to repeat the whole thing until allocation
+// converges.  Here one call reaches that fixed point with two launches and no host
+// synchronisation:
+//
+//   vk_alloc_kernel    one warp per 8x4 pixel tile walks the truncation band of its
+//                      32 rays in lock step; identical block coordinates inside the
+//                      warp are merged with __match_any_sync so one lane per distinct
+//                      block does a find-or-insert in the hash (per-bucket lock only
+//                      on the insert path).  The first lane to touch an entry in
+//                      this view (atomicExch on a per-entry view stamp) marks it
+//                      VISIBILITY_TRUE and appends it to the new visible list.
+//   vk_carry_kernel    walks the *previous* visible list only (the UNKNOWN entries of
+//                      the reference are exactly that list): entries not touched in
+//                      this view get the 8-corner frustum test (Q6) and are carried
+//                      over (stay UNKNOWN, Q5) or dropped (FALSE).  O(V) instead of
+//                      O(M+E).
+#include "vk_math.cuh"
+#include "vk_launch.h"
+
+namespace vk {
+
+struct AllocParams {
+  vkHashEntry* entries;
+  uint8_t* visibility;
+  int32_t* stamps;
+  int32_t* locks;
+  const int32_t* free_list;
+  int32_t* counters;
+  int32_t* visible_out;
+  int cnt_slot;
+  const float* depth;
+  int w, h;
+  vkProjection proj;
+  float Twd[12];  // rows 0..2 of depth_to_world, row-major 3x4
+  uint32_t K;
+  int B;
+  float block_length, trunc, min_depth, max_depth;
+  int view_id;
+  int shard_rank, shard_count, shard_shift;
+};
+
+// chain walk; returns entry index of block `key` or -1.  `tail` receives the last
+// entry visited, `head_empty` whether the bucket head is unallocated.
+__device__ __forceinline__ int find_block(const vkHashEntry* entries, uint32_t h,
+                                          unsigned long long key, int& tail, bool& head_empty) {
+  int idx = (int)h;
+  int4 e = ld_entry_cg(entries + idx);
+  head_empty = (e.z == -1);
+  if (head_empty) { tail = idx; return -1; }
+  while (true) {
+    if (entry_block(e) == key && e.z != -1) return idx;
+    if (e.w == -1) { tail = idx; return -1; }
+    idx = e.w;
+    e = ld_entry_cg(entries + idx);
+  }
+}
+
+__device__ __forceinline__ void touch_entry(const AllocParams& p, int idx) {
+  if (__ldcg(p.stamps + idx) != p.view_id) {
+    const int old = atomicExch(p.stamps + idx, p.view_id);
+    if (old != p.view_id) {
+      p.visibility[idx] = VK_VIS_TRUE;
+      const int pos = atomicAdd(p.counters + p.cnt_slot, 1);
+      p.visible_out[pos] = idx;
+    }
+  }
+}
+
+__device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int bx, int by, int bz,
+                                         unsigned long long key) {
+  int result = -1;
+  bool done = false;
+  while (!done) {
+    if (atomicCAS(p.locks + h, 0, 1) == 0) {
+      __threadfence();
+      int tail;
+      bool head_empty;
+      int idx = find_block(p.entries, h, key, tail, head_empty);
+      if (idx < 0) {
+        // HandleAllocationRequestsKernel (src/volume.cu:303-368): MAIN request writes the
+        // bucket head, EXCESS request bump-allocates an entry and links it to the tail.
+        int slot = tail;
+        if (!head_empty) slot = atomicAdd(p.counters + VK_CNT_EXCESS_PTR, 1);
+        const int vtop = atomicSub(p.counters + VK_CNT_VOXEL_PTR, 1);
+        if (slot < p.B && vtop >= 0) {
+          const int data = p.free_list[vtop];
+          int4 ne;
+          ne.x = (int)((uint32_t)(uint16_t)(int16_t)bx | ((uint32_t)(uint16_t)(int16_t)by << 16));
+          ne.y = (int)(uint32_t)(uint16_t)(int16_t)bz;
+          ne.w = -1;
+          if (head_empty) {
+            // publish coordinates first, then the data id that makes the head "allocated"
+            int2* dst = reinterpret_cast<int2*>(p.entries + slot);
+            __stcg(dst, make_int2(ne.x, ne.y));
+            __threadfence();
+            __stcg(reinterpret_cast<int*>(p.entries + slot) + 2, data);
+          } else {
+            ne.z = data;
+            __stcg(reinterpret_cast<int4*>(p.entries + slot), ne);
+            __threadfence();
+            __stcg(reinterpret_cast<int*>(p.entries + tail) + 3, slot);
+          }
+          atomicAdd(p.counters + VK_CNT_ALLOCATED, 1);
+          idx = slot;
+        } else {
+          atomicAdd(p.counters + VK_CNT_OVERFLOW, 1);
+          idx = -1;
+        }
+      }
+      result = idx;
+      __threadfence();
+      atomicExch(p.locks + h, 0);
+      done = true;
+    } else {
+      // another lane is inserting into this bucket: it may be inserting our block
+      int tail;
+      bool head_empty;
+      const int idx = find_block(p.entries, h, key, tail, head_empty);
+      if (idx >= 0) { result = idx; done = true; }
+    }
+  }
+  return result;
+}
+
+// CreateAllocationRequestsKernel (src/volume.cu:86-301) + HandleAllocationRequestsKernel
+// (src/volume.cu:303-368) to their common fixed point.
+__global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  // CTA tile 32x8 pixels, warp tile 8x4
+  const int x = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
+  const int y = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
+
+  bool active = (x < p.w && y < p.h);
+  int bx = 0, by = 0, bz = 0, ex = 0, ey = 0, ez = 0, sx = 1, sy = 1, sz = 1;
+  float tmx = 0, tmy = 0, tmz = 0, tdx = 0, tdy = 0, tdz = 0;
+
+  if (active) {
+    const float depth = __ldg(p.depth + y * p.w + x);
+    if (depth < p.min_depth || depth > p.max_depth) active = false;
+    if (active) {
+      const float u = (float)x + 0.5f, v = (float)y + 0.5f;
+      const Vec3 d0 = unproject(p.proj, u, v);
+      // direction = Twd * (d, 0)
+      Vec3 dir;
+      dir.x = add(add(add(mul(p.Twd[0], d0.x), mul(p.Twd[1], d0.y)), mul(p.Twd[2], d0.z)), mul(p.Twd[3], 0.0f));
+      dir.y = add(add(add(mul(p.Twd[4], d0.x), mul(p.Twd[5], d0.y)), mul(p.Twd[6], d0.z)), mul(p.Twd[7], 0.0f));
+      dir.z = add(add(add(mul(p.Twd[8], d0.x), mul(p.Twd[9], d0.y)), mul(p.Twd[10], d0.z)), mul(p.Twd[11], 0.0f));
+      const float Xx = add(p.Twd[3], mul(dir.x, depth));
+      const float Xy = add(p.Twd[7], mul(dir.y, depth));
+      const float Xz = add(p.Twd[11], mul(dir.z, depth));
+      dir = normalized(dir);
+      const float bgx = sub(Xx, mul(dir.x, p.trunc)), bgy = sub(Xy, mul(dir.y, p.trunc)),
+                  bgz = sub(Xz, mul(dir.z, p.trunc));
+      const float enx = add(Xx, mul(dir.x, p.trunc)), eny = add(Xy, mul(dir.y, p.trunc)),
+                  enz = add(Xz, mul(dir.z, p.trunc));
+      sx = (dir.x < 0) ? -1 : 1;
+      sy = (dir.y < 0) ? -1 : 1;
+      sz = (dir.z < 0) ? -1 : 1;
+      const float inv = fdiv(1.0f, p.block_length);
+      bx = (int)floorf(mul(bgx, inv));
+      by = (int)floorf(mul(bgy, inv));
+      bz = (int)floorf(mul(bgz, inv));
+      ex = (int)floorf(mul(enx, inv));
+      ey = (int)floorf(mul(eny, inv));
+      ez = (int)floorf(mul(enz, inv));
+      const float ox = sub(mul(p.block_length, (float)(bx + max(0, sx))), bgx);
+      const float oy = sub(mul(p.block_length, (float)(by + max(0, sy))), bgy);
+      const float oz = sub(mul(p.block_length, (float)(bz + max(0, sz))), bgz);
+      tmx = fdiv(ox, dir.x);
+      tmy = fdiv(oy, dir.y);
+      tmz = fdiv(oz, dir.z);
+      if (dir.x == 0) tmx = 1E20f;
+      if (dir.y == 0) tmy = 1E20f;
+      if (dir.z == 0) tmz = 1E20f;
+      tdx = fdiv(mul((float)sx, p.block_length), dir.x);
+      tdy = fdiv(mul((float)sy, p.block_length), dir.y);
+      tdz = fdiv(mul((float)sz, p.block_length), dir.z);
+    }
+  }
+
+  unsigned long long last_key = ~0ull;  // block this lane handled last as leader
+  while (__any_sync(0xffffffffu, active)) {
+    const unsigned long long key = active ? pack_block(bx, by, bz) : ~0ull;
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const bool leader = active && (lane == (__ffs(peers) - 1)) && key != last_key;
+    if (leader) {
+      last_key = key;
+      const uint32_t h = block_hash(bx, by, bz, p.K);
+      int tail;
+      bool head_empty;
+      int idx = find_block(p.entries, h, key, tail, head_empty);
+      if (idx < 0 && shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank))
+        idx = insert_block(p, h, bx, by, bz, key);
+      if (idx >= 0) touch_entry(p, idx);
+    }
+    if (active) {
+      // Amanatides-Woo step with the reference's comparison tree (src/volume.cu:241-295)
+      if (tmx < tmy) {
+        if (tmx < tmz) { bx += sx; if (bx == ex + sx) active = false; tmx = add(tmx, tdx); }
+        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
+      } else {
+        if (tmy < tmz) { by += sy; if (by == ey + sy) active = false; tmy = add(tmy, tdy); }
+        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
+      }
+    }
+  }
+}
+
+struct CarryParams {
+  const vkHashEntry* entries;
+  uint8_t* visibility;
+  const int32_t* stamps;
+  int32_t* counters;
+  int32_t* host_counters;
+  const int32_t* prev_list;
+  int32_t* visible_out;
+  int prev_slot, cnt_slot;
+  int w, h;
+  vkProjection proj;
+  float Tdw[12];
+  float block_length;
+  int view_id;
+  int* ticket;
+};
+
+// UpdateBlockVisibilityKernel (src/volume.cu:23-84) restricted to the entries that can
+// be VISIBILITY_UNKNOWN, i.e. the previous visible list.
+__global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
+  const int n_prev = p.counters[p.prev_slot];
+  const int lane = threadIdx.x & 31;
+  for (int base = blockIdx.x * blockDim.x; base < n_prev; base += gridDim.x * blockDim.x) {
+    const int i = base + threadIdx.x;
+    bool keep = false;
+    int e = -1;
+    if (i < n_prev) {
+      e = p.prev_list[i];
+      if (p.stamps[e] != p.view_id) {
+        const int4 ent = ld_entry(p.entries + e);
+        const int ox = (int)(int16_t)(ent.x & 0xffff);
+        const int oy = (int)(int16_t)((uint32_t)ent.x >> 16);
+        const int oz = (int)(int16_t)(ent.y & 0xffff);
+        Mat34 M;
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) M.r[r][c] = p.Tdw[r * 4 + c];
+        for (int c = 0; c < 8; ++c) {
+          const float X = mul(p.block_length, (float)(ox + ((c & 1) >> 0)));
+          const float Y = mul(p.block_length, (float)(oy + ((c & 2) >> 1)));
+          const float Z = mul(p.block_length, (float)(oz + ((c & 4) >> 2)));
+          const Vec3 Xd = xform(M, X, Y, Z, 1.0f);
+          if (Xd.z < 0) continue;
+          float u, v;
+          project(p.proj, Xd, u, v);
+          if (u >= 0 && u <= (float)p.w && v >= 0 && v <= (float)p.h) { keep = true; break; }
+        }
+        p.visibility[e] = keep ? VK_VIS_UNKNOWN : VK_VIS_FALSE;
+      }
+    }
+    // warp-aggregated append
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (m) {
+      int pos = 0;
+      if (lane == 0) pos = atomicAdd(p.counters + p.cnt_slot, __popc(m));
+      pos = __shfl_sync(0xffffffffu, pos, 0);
+      if (keep) p.visible_out[pos + __popc(m & ((1u << lane) - 1))] = e;
+    }
+  }
+  // last CTA out: retire the previous list and mirror the counters to the host
+  __shared__ bool last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = (atomicAdd(p.ticket, 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (last) {
+    __threadfence();
+    if (threadIdx.x == 0) {
+      p.counters[p.prev_slot] = 0;
+      *p.ticket = 0;
+    }
+    if (threadIdx.x < VK_CNT_COUNT && p.host_counters) {
+      int val = __ldcg(p.counters + threadIdx.x);
+      if (threadIdx.x == p.prev_slot) val = 0;
+      p.host_counters[threadIdx.x] = val;
+    }
+  }
+}
+
+// pool fills of Volume::Initialize (src/volume.cu:552-627)
+__global__ void vk_fill_pools_kernel(uint4* voxels16, size_t n16, vkHashEntry* entries, int32_t* free_list,
+                                     uint8_t* visibility, int32_t* stamps, int32_t* locks, int B, int M) {
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  // Voxel::Empty() = {1.0f, 0,0,0, 0,0}: 5 words; a 16-byte chunk q starts at word 4q.
+  for (size_t q = tid; q < n16; q += stride) {
+    const uint32_t r = (uint32_t)((q * 4) % 5);
+    uint4 val;
+    val.x = (r == 0) ? 0x3f800000u : 0u;
+    val.y = (r == 4) ? 0x3f800000u : 0u;
+    val.z = (r == 3) ? 0x3f800000u : 0u;
+    val.w = (r == 2) ? 0x3f800000u : 0u;
+    voxels16[q] = val;
+  }
+  for (size_t i = tid; i < (size_t)B; i += stride) {
+    reinterpret_cast<int4*>(entries)[i] = make_int4(0, 0, -1, -1);
+    free_list[i] = (int)i;
+    visibility[i] = VK_VIS_FALSE;
+    stamps[i] = 0;
+    if (i < (size_t)M) locks[i] = 0;
+  }
+}
+
+}  // namespace vk
+
+using namespace vk;
+
+static void rows34(const float* colmajor, float* out12) {
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 4; ++c) out12[r * 4 + c] = colmajor[c * 4 + r];
+}
+
+extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
+  if (!v || !v->voxels) return VK_E_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int B = v->main_blocks + v->excess_blocks;
+  const size_t n16 = (size_t)B * VK_BLOCK_VOXELS * sizeof(vkVoxel) / 16;
+  vk_fill_pools_kernel<<<148 * 8, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), n16, v->entries,
+                                               v->free_list, v->visibility, v->stamps, v->locks, B,
+                                               v->main_blocks);
+  VK_COUNT_LAUNCH();
+  int32_t init[VK_CNT_COUNT] = {0};
+  init[VK_CNT_VOXEL_PTR] = B - 1;               // src/volume.cu:595-601
+  init[VK_CNT_EXCESS_PTR] = v->main_blocks;     // src/volume.cu:579-584
+  for (int i = 0; i < VK_CNT_COUNT; ++i) v->host_counters[i] = init[i];
+  cudaError_t err = cudaMemcpyAsync(v->counters, v->host_counters, sizeof(init), cudaMemcpyHostToDevice, s);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaMemsetAsync(v->counters + VK_CNT_COUNT, 0, sizeof(int), s);  // ticket
+  if (err != cudaSuccess) return (int)err;
+  err = cudaStreamSynchronize(s);  // host_counters is reused by kernels afterwards
+  v->visible_slot = 0;
+  v->view_id = 0;
+  return (int)err;
+}
+
+extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks, void* stream) {
+  if (!v || main_blocks <= 0 || excess_blocks < 0) return VK_E_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return VK_E_NODEVICE; }
+  // Q20: voxel indices are 32-bit ints in the reference (B <= 4194303); ours are 64-bit
+  // byte offsets, the limit here is only that ids fit an int.
+  const size_t B = (size_t)main_blocks + (size_t)excess_blocks;
+  memset(v, 0, sizeof(*v));
+  v->main_blocks = main_blocks;
+  v->excess_blocks = excess_blocks;
+  v->voxel_length = 0.008f;   // src/volume.cu:374-376
+  v->trunc_length = 0.04f;
+  v->min_depth = 0.1f;
+  v->max_depth = 5.0f;
+  v->shard_rank = 0;
+  v->shard_count = 1;
+  v->shard_shift = 3;
+  cudaError_t err;
+#define VK_TRY(x) if ((err = (x)) != cudaSuccess) { vk_volume_destroy(v); return (int)err; }
+  VK_TRY(cudaMalloc((void**)&v->voxels, B * VK_BLOCK_VOXELS * sizeof(vkVoxel)));
+  VK_TRY(cudaMalloc((void**)&v->entries, B * sizeof(vkHashEntry)));
+  VK_TRY(cudaMalloc((void**)&v->free_list, B * sizeof(int32_t)));
+  VK_TRY(cudaMalloc((void**)&v->visibility, B));
+  VK_TRY(cudaMalloc((void**)&v->visible[0], B * sizeof(int32_t)));
+  VK_TRY(cudaMalloc((void**)&v->visible[1], B * sizeof(int32_t)));
+  VK_TRY(cudaMalloc((void**)&v->stamps, B * sizeof(int32_t)));
+  VK_TRY(cudaMalloc((void**)&v->locks, (size_t)main_blocks * sizeof(int32_t)));
+  VK_TRY(cudaMalloc((void**)&v->counters, (VK_CNT_COUNT + 4) * sizeof(int32_t)));
+  VK_TRY(cudaHostAlloc((void**)&v->host_counters, VK_CNT_COUNT * sizeof(int32_t), cudaHostAllocMapped));
+#undef VK_TRY
+  return vk_volume_reset(v, stream);
+}
+
+extern "C" int vk_volume_destroy(vkVolume* v) {
+  if (!v) return VK_E_INVALID;
+  cudaFree(v->voxels);
+  cudaFree(v->entries);
+  cudaFree(v->free_list);
+  cudaFree(v->visibility);
+  cudaFree(v->visible[0]);
+  cudaFree(v->visible[1]);
+  cudaFree(v->stamps);
+  cudaFree(v->locks);
+  cudaFree(v->counters);
+  if (v->host_counters) cudaFreeHost(v->host_counters);
+  const int m = v->main_blocks, e = v->excess_blocks;
+  memset(v, 0, sizeof(*v));
+  v->main_blocks = m;
+  v->excess_blocks = e;
+  return 0;
+}
+
+extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
+  if (!v || !f || !v->voxels || !f->depth || f->depth_w <= 0 || f->depth_h <= 0) return VK_E_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int prev = v->visible_slot, cur = prev ^ 1;
+  v->view_id += 1;
+
+  AllocParams a;
+  a.entries = v->entries;
+  a.visibility = v->visibility;
+  a.stamps = v->stamps;
+  a.locks = v->locks;
+  a.free_list = v->free_list;
+  a.counters = v->counters;
+  a.visible_out = v->visible[cur];
+  a.cnt_slot = VK_CNT_VISIBLE0 + cur;
+  a.depth = f->depth;
+  a.w = f->depth_w;
+  a.h = f->depth_h;
+  a.proj = f->depth_proj;
+  rows34(f->depth_to_world.m, a.Twd);
+  a.K = (uint32_t)v->main_blocks;
+  a.B = v->main_blocks + v->excess_blocks;
+  a.block_length = VK_BLOCK_RES * v->voxel_length;
+  a.trunc = v->trunc_length;
+  a.min_depth = v->min_depth;
+  a.max_depth = v->max_depth;
+  a.view_id = v->view_id;
+  a.shard_rank = v->shard_rank;
+  a.shard_count = v->shard_count;
+  a.shard_shift = v->shard_shift;
+  dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
+  vk_alloc_kernel<<<grid, 256, 0, s>>>(a);
+  VK_COUNT_LAUNCH();
+
+  CarryParams c;
+  c.entries = v->entries;
+  c.visibility = v->visibility;
+  c.stamps = v->stamps;
+  c.counters = v->counters;
+  c.host_counters = v->host_counters;
+  c.prev_list = v->visible[prev];
+  c.visible_out = v->visible[cur];
+  c.prev_slot = VK_CNT_VISIBLE0 + prev;
+  c.cnt_slot = VK_CNT_VISIBLE0 + cur;
+  c.w = f->depth_w;
+  c.h = f->depth_h;
+  c.proj = f->depth_proj;
+  rows34(f->depth_to_world.inv, c.Tdw);
+  c.block_length = a.block_length;
+  c.view_id = v->view_id;
+  c.ticket = v->counters + VK_CNT_COUNT;
+  vk_carry_kernel<<<148, 256, 0, s>>>(c);
+  VK_COUNT_LAUNCH();
+  v->visible_slot = cur;
+  return (int)cudaGetLastError();
+}
+
+extern "C" int vk_volume_sync_counters(vkVolume* v, int* visible, void* stream) {
+  if (!v || !v->counters) return VK_E_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t err = cudaMemcpyAsync(v->host_counters, v->counters, VK_CNT_COUNT * sizeof(int32_t),
+                                    cudaMemcpyDeviceToHost, s);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return (int)err;
+  if (visible) *visible = v->host_counters[VK_CNT_VISIBLE0 + v->visible_slot];
+  return v->host_counters[VK_CNT_OVERFLOW] ? VK_E_OVERFLOW : 0;
+}

@@ -1,0 +1,326 @@
+// vk_integrate.cu — DepthIntegrator / ColorIntegrator / LightIntegrator for sm_100a.
+//
+// Reference: one CUDA block (8,8,8) per visible voxel block, one thread per voxel,
+// scalar 4-byte accesses at a 20-byte stride, and a second full pass over the same
+// voxel tiles for colour (src/depth_integrator.cu:17-80, src/color_integrator.cu:82-135,
+// src/light_integrator.cu:170-250).
+//
+// Here: persistent CTAs of 128 threads grid-stride over the device-resident visible
+// list (no host read-back of the count).  A thread owns 4 consecutive voxels of a row
+// (80 bytes = 5 aligned 16-byte chunks of the AoS tile), decides from the projection
+// and the depth image alone whether any of them can change, and only then moves the
+// 80 bytes with 128-bit loads; depth and colour updates happen on the registers in
+// one pass, and only the 16-byte chunks that changed are written back.
+#include "vk_math.cuh"
+#include "vk_launch.h"
+#include <cfloat>
+
+namespace vk {
+
+enum { MODE_DEPTH = 0, MODE_COLOR = 1, MODE_LIGHT = 2 };
+
+struct IntegrateParams {
+  const int32_t* visible;
+  const int32_t* count;
+  const vkHashEntry* entries;
+  vkVoxel* voxels;
+  const float* depth;
+  const float* color;
+  const float* normal;
+  const float* mask;
+  int dw, dh, cw, ch;
+  vkProjection dproj, cproj;
+  float Tdw[12], Tcw[12], Tcd[12];
+  float voxel_length, block_length, trunc;
+  float min_depth, max_depth, max_dw, max_cw;
+  vkLight light;
+};
+
+__device__ __forceinline__ void load_rows(Mat34& M, const float* rows) {
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) M.r[r][c] = rows[r * 4 + c];
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams p) {
+  const int n = *p.count;
+  const int t = threadIdx.x;
+  const int vz = t >> 4, vy = (t >> 1) & 7, vx0 = (t & 1) * 4;
+  Mat34 Tdw, Tcw;
+  load_rows(Tdw, p.Tdw);
+  if (MODE != MODE_DEPTH) load_rows(Tcw, p.Tcw);
+
+  for (int bi = blockIdx.x; bi < n; bi += gridDim.x) {
+    const int e = __ldg(p.visible + bi);
+    const int4 ent = ld_entry(p.entries + e);
+    const float ox = (float)(int)(int16_t)(ent.x & 0xffff);
+    const float oy = (float)(int)(int16_t)((uint32_t)ent.x >> 16);
+    const float oz = (float)(int)(int16_t)(ent.y & 0xffff);
+    // Xwp = block_length * origin + voxel_length * (xyz + 0.5)   (src/depth_integrator.cu:36-39)
+    const float Xy = add(mul(oy, p.block_length), mul(add((float)vy, 0.5f), p.voxel_length));
+    const float Xz = add(mul(oz, p.block_length), mul(add((float)vz, 0.5f), p.voxel_length));
+    const float bxl = mul(ox, p.block_length);
+
+    bool dpass[4];          // depth update applies
+    float dcur[4];          // depth - Xd.z
+    bool cin[4];            // colour-side geometric test passes
+    int cidx[4];            // colour pixel
+    int didx[4];            // depth pixel (light mode)
+    Vec3 Xc[4];
+    bool need = false;
+
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float Xx = add(bxl, mul(add((float)(vx0 + k), 0.5f), p.voxel_length));
+      const Vec3 Xd = xform(Tdw, Xx, Xy, Xz, 1.0f);
+      float u, v;
+      project(p.dproj, Xd, u, v);
+      const bool din = (u >= 0 && u < (float)p.dw && v >= 0 && v < (float)p.dh);
+      dpass[k] = false;
+      dcur[k] = 0.f;
+      int di = 0;
+      if (din) {
+        di = (int)v * p.dw + (int)u;
+        const float d = __ldg(p.depth + di);
+        if (!(d < p.min_depth || d > p.max_depth)) {
+          const float s = sub(d, Xd.z);
+          if (s > -p.trunc) { dpass[k] = true; dcur[k] = s; }
+        }
+      }
+      need |= dpass[k];
+      if (MODE == MODE_COLOR) {
+        Xc[k] = xform(Tcw, Xx, Xy, Xz, 1.0f);
+        float cu, cv;
+        project(p.cproj, Xc[k], cu, cv);
+        cin[k] = (cu >= 0 && cu < (float)p.cw && cv >= 0 && cv < (float)p.ch);
+        cidx[k] = cin[k] ? (int)cv * p.cw + (int)cu : 0;
+        need |= cin[k];
+      } else if (MODE == MODE_LIGHT) {
+        // both projections are tested against the depth image size (src/light_integrator.cu:207-215,335-336)
+        Xc[k] = xform(Tcw, Xx, Xy, Xz, 1.0f);
+        float cu, cv;
+        project(p.cproj, Xc[k], cu, cv);
+        bool ok = din && (cu >= 0 && cu < (float)p.dw && cv >= 0 && cv < (float)p.dh);
+        didx[k] = di;
+        cidx[k] = ok ? (int)cv * p.dw + (int)cu : 0;
+        if (ok) ok = __ldg(p.mask + di) > 0.5f;
+        cin[k] = ok;
+        need |= ok;
+      }
+    }
+    if (!need) continue;
+
+    uint4* tile = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) +
+                                           (size_t)ent.z * (VK_BLOCK_VOXELS * sizeof(vkVoxel)) + (size_t)t * 80);
+    uint32_t w[20];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      const uint4 q = tile[c];
+      w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
+    }
+    uint32_t dirty = 0;  // bit per word
+
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float D = __uint_as_float(w[5 * k]);
+      int dwt = (int)(int16_t)(w[5 * k + 4] & 0xffff);
+      int cwt = (int)(int16_t)(w[5 * k + 4] >> 16);
+      if (dpass[k]) {
+        // src/depth_integrator.cu:68-76
+        const float prev = mul((float)dwt, D);
+        const float cur = vmin(1.0f, fdiv(dcur[k], p.trunc));
+        const float wn = add((float)dwt, 1.0f);
+        dwt = (int)(short)vmin(p.max_dw, wn);
+        D = fdiv(add(prev, cur), wn);
+        w[5 * k] = __float_as_uint(D);
+        dirty |= (1u << (5 * k)) | (1u << (5 * k + 4));
+      }
+      if (MODE != MODE_DEPTH) {
+        if (cin[k] && fabsf(D) < 1.0f) {
+          float cr = __ldg(p.color + 3 * (size_t)cidx[k] + 0);
+          float cg = __ldg(p.color + 3 * (size_t)cidx[k] + 1);
+          float cb = __ldg(p.color + 3 * (size_t)cidx[k] + 2);
+          bool ok = true;
+          if (MODE == MODE_LIGHT) {
+            // src/light_integrator.cu:229-237, include/vulcan/light.h:52-60
+            const float nx = __ldg(p.normal + 3 * (size_t)didx[k] + 0);
+            const float ny = __ldg(p.normal + 3 * (size_t)didx[k] + 1);
+            const float nz = __ldg(p.normal + 3 * (size_t)didx[k] + 2);
+            Mat34 Tcd;
+            load_rows(Tcd, p.Tcd);
+            const Vec3 Xcn = xform(Tcd, nx, ny, nz, 0.0f);
+            Vec3 delta = {sub(p.light.position[0], Xc[k].x), sub(p.light.position[1], Xc[k].y),
+                          sub(p.light.position[2], Xc[k].z)};
+            const Vec3 dirn = normalized(delta);
+            const float dist2 = dot3(delta, delta);
+            const float cos_theta = dot3(Xcn, dirn);
+            const float shading = fdiv(mul(p.light.intensity, cos_theta), dist2);
+            ok = shading > 0.05f;
+            if (ok) {
+              const float inv = fdiv(1.0f, shading);
+              cr = mul(cr, inv); cg = mul(cg, inv); cb = mul(cb, inv);
+            }
+          }
+          if (ok) {
+            // src/color_integrator.cu:121-126
+            const float fw = (float)cwt;
+            const float wn = add(fw, 1.0f);
+            const float inv = fdiv(1.0f, wn);
+            const float r0 = __uint_as_float(w[5 * k + 1]);
+            const float g0 = __uint_as_float(w[5 * k + 2]);
+            const float b0 = __uint_as_float(w[5 * k + 3]);
+            w[5 * k + 1] = __float_as_uint(mul(add(mul(r0, fw), cr), inv));
+            w[5 * k + 2] = __float_as_uint(mul(add(mul(g0, fw), cg), inv));
+            w[5 * k + 3] = __float_as_uint(mul(add(mul(b0, fw), cb), inv));
+            cwt = (int)(short)vmin(p.max_cw, wn);
+            dirty |= (0xeu << (5 * k)) | (1u << (5 * k + 4));
+          }
+        }
+      }
+      w[5 * k + 4] = ((uint32_t)(uint16_t)(int16_t)dwt) | ((uint32_t)(uint16_t)(int16_t)cwt << 16);
+    }
+
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+      if ((dirty >> (4 * c)) & 0xfu) tile[c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+    }
+  }
+}
+
+// ComputeFrameMaskKernel<16,3> (src/light_integrator.cu:17-103) including Q14: the
+// shared tile is filled from image offset -1 (not -KERNEL_SIZE) while the window is read
+// at [-3,+3] around (t + 3), so the window covers image offsets [-1,+5] of the pixel.
+__global__ void __launch_bounds__(256) vk_frame_mask_kernel(int width, int height, const float* depths,
+                                                            const float* colors, float threshold, float* mask) {
+  constexpr int BD = 16, KS = 3, DIM = BD + 2 * KS;
+  __shared__ float buf[DIM * DIM];
+  const int x = blockIdx.x * BD + threadIdx.x;
+  const int y = blockIdx.y * BD + threadIdx.y;
+  for (int s = threadIdx.y * BD + threadIdx.x; s < DIM * DIM; s += BD * BD) {
+    const int vx = blockIdx.x * BD - 1 + (s % DIM);
+    const int vy = blockIdx.y * BD - 1 + (s / DIM);
+    float d = 0;
+    if (vx >= 0 && vx < width && vy >= 0 && vy < height) d = __ldg(depths + vy * width + vx);
+    buf[s] = d;
+  }
+  __syncthreads();
+  if (x < width && y < height) {
+    const int index = y * width + x;
+    const float r = colors[3 * (size_t)index], g = colors[3 * (size_t)index + 1], b = colors[3 * (size_t)index + 2];
+    if (r < 0.02f || r > 0.98f || g < 0.02f || g > 0.98f || b < 0.02f || b > 0.98f) {
+      mask[index] = 0.0f;
+      return;
+    }
+    float dmin = +FLT_MAX, dmax = -FLT_MAX;
+    const int cx = threadIdx.x + KS, cy = threadIdx.y + KS;
+    for (int i = -KS; i <= KS; ++i)
+      for (int j = -KS; j <= KS; ++j) {
+        const float d = buf[(cy + i) * DIM + (cx + j)];
+        dmin = fminf(d, dmin);
+        dmax = fmaxf(d, dmax);
+      }
+    mask[index] = (sub(dmax, dmin) <= threshold) ? 1.0f : 0.0f;
+  }
+}
+
+}  // namespace vk
+
+using namespace vk;
+
+static void rows34(const float* colmajor, float* out12) {
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 4; ++c) out12[r * 4 + c] = colmajor[c * 4 + r];
+}
+
+// Matrix::operator* (include/vulcan/matrix.h:296-316), evaluated on the host like the
+// reference does for Tcw = Tcd * Tdw (src/color_integrator.cu:191-193).
+static void matmul4(const float* A, const float* Bm, float* C) {
+  for (int p = 0; p < 4; ++p)
+    for (int m = 0; m < 4; ++m) {
+      volatile float acc = 0;
+      for (int n = 0; n < 4; ++n) {
+        volatile float prod = A[n * 4 + m] * Bm[p * 4 + n];
+        acc = acc + prod;
+      }
+      C[p * 4 + m] = acc;
+    }
+}
+
+static int fill_params(IntegrateParams& p, vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
+                       float max_dw, float max_cw) {
+  if (!v || !f || !v->voxels || !f->depth) return VK_E_INVALID;
+  p.visible = v->visible[v->visible_slot];
+  p.count = v->counters + VK_CNT_VISIBLE0 + v->visible_slot;
+  p.entries = v->entries;
+  p.voxels = v->voxels;
+  p.depth = f->depth;
+  p.color = f->color;
+  p.normal = f->normal;
+  p.mask = nullptr;
+  p.dw = f->depth_w; p.dh = f->depth_h; p.cw = f->color_w; p.ch = f->color_h;
+  p.dproj = f->depth_proj;
+  p.cproj = f->color_proj;
+  rows34(f->depth_to_world.inv, p.Tdw);
+  float Tcw[16];
+  matmul4(f->depth_to_color.m, f->depth_to_world.inv, Tcw);
+  rows34(Tcw, p.Tcw);
+  rows34(f->depth_to_color.m, p.Tcd);
+  p.voxel_length = v->voxel_length;
+  p.block_length = VK_BLOCK_RES * v->voxel_length;
+  p.trunc = v->trunc_length;
+  p.min_depth = min_depth; p.max_depth = max_depth;
+  p.max_dw = max_dw; p.max_cw = max_cw;
+  p.light.intensity = 1.0f;
+  p.light.position[0] = p.light.position[1] = p.light.position[2] = 0.f;
+  return 0;
+}
+
+static const int kIntegrateGrid = 148 * 12;
+
+extern "C" int vk_integrate_depth(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
+                                  float max_distance_weight, void* stream) {
+  IntegrateParams p;
+  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, 16.f);
+  if (rc) return rc;
+  vk_integrate_kernel<MODE_DEPTH><<<kIntegrateGrid, 128, 0, (cudaStream_t)stream>>>(p);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
+
+extern "C" int vk_integrate_color(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
+                                  float max_distance_weight, float max_color_weight, void* stream) {
+  IntegrateParams p;
+  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, max_color_weight);
+  if (rc) return rc;
+  if (!f->color || f->color_w <= 0 || f->color_h <= 0) return VK_E_INVALID;
+  vk_integrate_kernel<MODE_COLOR><<<kIntegrateGrid, 128, 0, (cudaStream_t)stream>>>(p);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
+
+extern "C" int vk_compute_frame_mask(const vkFrame* f, float depth_threshold, float* mask, void* stream) {
+  if (!f || !f->depth || !f->color || !mask) return VK_E_INVALID;
+  dim3 grid((f->depth_w + 15) / 16, (f->depth_h + 15) / 16), block(16, 16);
+  vk_frame_mask_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(f->depth_w, f->depth_h, f->depth, f->color,
+                                                                 depth_threshold, mask);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
+
+extern "C" int vk_integrate_light(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
+                                  float max_distance_weight, float max_color_weight, const vkLight* light,
+                                  float depth_threshold, float* mask, void* stream) {
+  IntegrateParams p;
+  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, max_color_weight);
+  if (rc) return rc;
+  if (!f->color || !f->normal || !mask || !light) return VK_E_INVALID;
+  rc = vk_compute_frame_mask(f, depth_threshold, mask, stream);
+  if (rc) return rc;
+  p.mask = mask;
+  p.light = *light;
+  vk_integrate_kernel<MODE_LIGHT><<<kIntegrateGrid, 128, 0, (cudaStream_t)stream>>>(p);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
