@@ -1,0 +1,468 @@
+#!/usr/bin/env python
+"""bench.py — the reference's headline workload on B200.
+
+Workload (BASELINE.json configs[1], "c2_orbit"): 640x480 synthetic sphere-on-plane depth,
+4 mm voxels, Volume(262144, 65536), ground-truth poses on a 1.2 deg/frame orbit.  One step =
+one frame of the hot path: Volume::SetView (to its fixed point) + DepthIntegrator::Integrate
++ Tracer::Trace.  `value` = voxel updates (visible blocks x 512) per second over the whole
+step with inputs resident in HBM; `e2e` = the same with the depth image coming from pinned
+host memory and the traced depth/colour/normal images read back, every step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+--impl reference runs the reference's own CUDA sources (oracle/_ref, built unmodified from
+/root/reference by oracle/build_ref.sh) through its own classes on the same frames; the
+reference has no CPU implementation of this path, so the CPU number reported beside both
+arms (`cpu_baseline`) is the oracle port timed on the host cores.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+W, H = 640, 480
+VOXEL = 0.004
+TRUNC = 5 * VOXEL
+MAIN, EXCESS = 262144, 65536
+METRIC = "voxel-updates/s (visible blocks x 512 per frame / SetView+Integrate+Trace time), 640x480, 4 mm"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
+            while not self._stop_evt.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.05)
+        except Exception as e:  # NVML missing: report that instead of inventing numbers
+            self.reasons.add("nvml_unavailable:%s" % type(e).__name__)
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def make_frames(n, start=0):
+    import harness as Hh
+    frames = []
+    K = Hh.synth.intrinsics(W, H)
+    for k in range(start, start + n):
+        R, t = Hh.synth.orbit_pose(k)
+        frames.append((Hh.synth.render_sphere_plane(W, H, K, R, t), Hh.raw32(R, t)))
+    return np.array(K, dtype=np.float32), frames
+
+
+def shard_owner_torch(entries, shift, count):
+    """torch restatement of vk::shard_owner for counting owned blocks (outside timed regions)."""
+    import torch
+    e0 = entries[:, 0].long()
+    e1 = entries[:, 1].long()
+    def s16(v):
+        v = v & 0xFFFF
+        return torch.where(v >= 0x8000, v - 0x10000, v)
+    bx, by, bz = s16(e0), s16(e0 >> 16), s16(e1)
+    m = 0xFFFFFFFF
+    h = (((bx >> shift) & m) * 0x9E3779B1 & m) ^ (((by >> shift) & m) * 0x85EBCA77 & m) ^ (((bz >> shift) & m) * 0xC2B2AE3D & m)
+    h ^= h >> 16
+    h = h * 0x7FEB352D & m
+    h ^= h >> 15
+    h = h * 0x846CA68B & m
+    h ^= h >> 16
+    return h % count
+
+
+def algorithmic_bytes_integrate(updated_voxels, visible_blocks):
+    """40 B per updated voxel + 20 B per visible block + 4*W*H."""
+    return 40.0 * updated_voxels + 20.0 * visible_blocks + 4.0 * W * H
+
+
+def run_ours(args, rank, world):
+    import torch
+    import torch.distributed as dist
+    import vulcan_b200 as vb
+
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
+    torch.cuda.set_device(dev)
+    K, frames = make_frames(args.warmup + args.steps)
+    nfr = len(frames)
+
+    def new_volume():
+        vol = vb.Volume(MAIN, EXCESS)
+        vol.SetVoxelLength(VOXEL)
+        vol.SetTruncationLength(TRUNC)
+        if world > 1:
+            vol.SetSharding(rank, world, 3)
+        return vol
+
+    def transform(raw):
+        return vb.Transform(raw[:16].reshape(4, 4).T.copy(), raw[16:].reshape(4, 4).T.copy())
+
+    poses = [transform(T) for _, T in frames]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    keys = torch.empty((H, W), dtype=torch.int64, device=dev) if world > 1 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    import ctypes as C
+    lib = vb.lib
+    bounds = torch.empty((60, 80, 2), dtype=torch.float32, device=dev)
+
+    def cframe(k, depth_t):
+        f = vb.Frame()
+        f.depth_projection = vb.Projection(*K)
+        f.depth_to_world_transform = poses[k]
+        f.depth_image = depth_t
+        return f.to_c()
+
+    def step(vol, cin, cout, outs, ev=None):
+        """One frame through the C ABI (include/vulcan_b200.h) with prebuilt descriptors."""
+        s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        v = C.byref(vol._v)
+        if ev: ev[0].record()
+        vb.api.check(lib.vk_set_view(v, C.byref(cin), s), "vk_set_view")
+        if ev: ev[1].record()
+        vb.api.check(lib.vk_integrate_depth(v, C.byref(cin), 0.1, 5.0, 16.0, s), "vk_integrate_depth")
+        if ev: ev[2].record()
+        if world > 1:
+            vb.api.check(lib.vk_trace_keys(v, C.byref(cout), 0.1, 5.0, bounds.data_ptr(), keys.data_ptr(), s), "vk_trace_keys")
+            dist.all_reduce(keys, op=dist.ReduceOp.MIN)
+            vb.api.check(lib.vk_resolve_keys(keys.data_ptr(), C.byref(cout), outs[0].data_ptr(), outs[1].data_ptr(),
+                                             outs[2].data_ptr(), s), "vk_resolve_keys")
+        else:
+            vb.api.check(lib.vk_trace(v, C.byref(cout), 0.1, 5.0, bounds.data_ptr(), outs[0].data_ptr(),
+                                      outs[1].data_ptr(), outs[2].data_ptr(), s), "vk_trace")
+        if ev: ev[3].record()
+
+    def frame_for(k, depth_t):
+        f = vb.Frame()
+        f.depth_projection = vb.Projection(*K)
+        f.depth_to_world_transform = poses[k]
+        f.depth_image = depth_t
+        return f
+
+    # ---------------- device-resident leg -------------------------------------------------
+    vol = new_volume()
+    dev_depth = [torch.from_numpy(d).to(dev) for d, _ in frames]
+    outs = (torch.zeros((H, W), dtype=torch.float32, device=dev),
+            torch.zeros((H, W, 3), dtype=torch.float32, device=dev),
+            torch.zeros((H, W, 3), dtype=torch.float32, device=dev))
+    cin = [cframe(k, dev_depth[k]) for k in range(nfr)]
+    cout = [cframe(k, outs[0]) for k in range(nfr)]
+    sampler = ClockSampler(dev.index)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(nfr)]
+    count_log = torch.zeros(nfr, dtype=torch.int32, device=dev)
+    counters = vb.api.device_view(vol._v.counters, (16,), "<i4")
+    launches0 = 0
+    barrier()
+    for k in range(nfr):
+        if k == args.warmup:
+            barrier()
+            sampler.start()
+            launches0 = lib.vk_launch_count()
+            updated0 = int(counters[8:10].cpu().view(torch.int64).item())
+            t_wall0 = time.perf_counter()
+        flush.zero_()  # L2 flush between steps, outside the per-step events
+        step(vol, cin[k], cout[k], outs, evs[k])
+        if world > 1:
+            torch.cuda.current_stream().synchronize()
+            ent = vol.GetHashEntries()[vol.GetVisibleBlocks().long()]
+            count_log[k] = (shard_owner_torch(ent, 3, world) == rank).sum()
+        else:
+            count_log[k:k + 1].copy_(counters[vol._v.visible_slot:vol._v.visible_slot + 1])
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = lib.vk_launch_count() - launches0
+    clocks = sampler.finish()
+    counts = count_log[args.warmup:].cpu().tolist()
+    updated_timed = float(int(counters[8:10].cpu().view(torch.int64).item()) - updated0)
+    assert vol.SyncCounters()[1][4] == 0, "voxel/excess pool overflow"
+    timed = range(args.warmup, nfr)
+    t_step = np.array([evs[k][0].elapsed_time(evs[k][3]) for k in timed])
+    t_set = np.array([evs[k][0].elapsed_time(evs[k][1]) for k in timed])
+    t_int = np.array([evs[k][1].elapsed_time(evs[k][2]) for k in timed])
+    t_trc = np.array([evs[k][2].elapsed_time(evs[k][3]) for k in timed])
+    tot = torch.tensor([t_step.sum(), t_int.sum(), t_trc.sum(), t_set.sum()], dtype=torch.float64, device=dev)
+    units = torch.tensor([float(sum(counts)) * 512.0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        dist.all_reduce(units, op=dist.ReduceOp.SUM)
+    tot_ms, int_ms, trc_ms, set_ms = (float(x) for x in tot.tolist())
+    total_units = float(units.item())
+
+    # roofline of the dominant streaming kernel (integration), live over the timed region:
+    # algorithmic bytes from the kernel's own count of voxels written / the
+    # CUDA-event time of the Integrate phase summed over the same steps
+    roof = None
+    if world == 1:
+        peaks, which = load_peaks()
+        vis_total = float(sum(counts))
+        ab = 40.0 * updated_timed + 20.0 * vis_total + 4.0 * W * H * args.steps
+        gbs = ab / (int_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "vk_integrate_kernel<MODE_DEPTH>", "achieved": gbs,
+                "peak": peaks["hbm_gbs"], "peak_source": which, "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                "traffic": None, "algorithmic_bytes_per_launch": ab / args.steps,
+                "updated_voxels_per_launch": updated_timed / args.steps,
+                "launch_ms": int_ms / args.steps}
+
+    # ---------------- end-to-end leg (host buffers, copies inside the timed region) ---------
+    del vol
+    torch.cuda.empty_cache()
+    vol = new_volume()
+    pinned_in = [torch.from_numpy(d).pin_memory() for d, _ in frames]
+    d_in = torch.empty((H, W), dtype=torch.float32, device=dev)
+    cin = [cframe(k, d_in) for k in range(nfr)]
+    h_depth = torch.empty((H, W), dtype=torch.float32).pin_memory()
+    h_color = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    h_normal = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    barrier()
+    t_e2e = 0.0
+    for k in range(nfr):
+        if k == args.warmup:
+            barrier()
+            t0 = time.perf_counter()
+        d_in.copy_(pinned_in[k], non_blocking=True)
+        step(vol, cin[k], cout[k], outs)
+        h_depth.copy_(outs[0], non_blocking=True)
+        h_color.copy_(outs[1], non_blocking=True)
+        h_normal.copy_(outs[2], non_blocking=True)
+        torch.cuda.current_stream().synchronize()   # the caller reads the result every step
+    barrier()
+    t_e2e = time.perf_counter() - t0
+    t_e2e_t = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_e2e_t, op=dist.ReduceOp.MAX)
+    t_e2e = float(t_e2e_t.item())
+    h2d = W * H * 4
+    d2h = W * H * 4 * 7
+
+    line = {
+        "metric": METRIC, "value": total_units / (tot_ms * 1e-3), "unit": "voxel-updates/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "c2_orbit: 640x480 sphere-on-plane depth, 4 mm voxels, Volume(262144,65536), "
+                               "1.2 deg/frame orbit, GT poses; step = SetView(fixed point)+DepthIntegrate+Trace",
+                   "l2": "256 MiB device memset between steps, outside the per-step CUDA events",
+                   "sharding": "none" if world == 1 else "blocks by brick hash (8^3-block bricks, 1-block halo), "
+                                                         "ray hits merged with NCCL all_reduce(MIN) on 64-bit keys"},
+        "phases": {"setview_ms": set_ms / args.steps, "integrate_ms": int_ms / args.steps,
+                   "trace_ms": trc_ms / args.steps,
+                   "integrate_voxel_updates_per_s": total_units / (int_ms * 1e-3),
+                   "trace_rays_per_s": W * H * args.steps / (trc_ms * 1e-3)},
+        "visible_blocks_per_frame": float(np.mean(counts)),
+        "clocks": clocks,
+        "e2e": {"value": total_units / t_e2e, "unit": "voxel-updates/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": t_e2e * 1e3 / args.steps,
+                "what": "pinned host depth -> device, SetView+Integrate+Trace, traced depth+colour+normal -> pinned host, sync every step"},
+        "gpu_launches": int(launches),
+        "wall_s_timed_region": t_wall,
+    }
+    if roof:
+        line["roofline"] = roof
+    return line
+
+
+def run_reference(args):
+    """The reference's own CUDA sources through its own classes (oracle/_ref), same frames."""
+    import torch
+    import harness as Hh
+    if not Hh.have_ref():
+        return {"impl": "reference", "unavailable": "oracle/_ref/libvulcan_ref.so not built (needs /root/reference at build time)"}
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    K, frames = make_frames(args.warmup + args.steps)
+    nfr = len(frames)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def new_ref():
+        rv = Hh.RefVolume(MAIN, EXCESS, VOXEL, TRUNC)
+        rv.set_ranges()
+        return rv
+
+    # device-resident leg
+    rv = new_ref()
+    dev_depth = [torch.from_numpy(d).to(dev) for d, _ in frames]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(nfr)]
+    counts, passes = [], []
+    sampler = ClockSampler(0)
+    torch.cuda.synchronize()
+    for k in range(nfr):
+        if k == args.warmup:
+            torch.cuda.synchronize()
+            sampler.start()
+        flush.zero_()
+        rv.set_frame_device(dev_depth[k].data_ptr(), W, H, K, frames[k][1])
+        ev = evs[k]
+        ev[0].record()
+        p = rv.set_view_converged()
+        ev[1].record()
+        rv.integrate(0)
+        ev[2].record()
+        rv.trace(W, H, K, frames[k][1])
+        ev[3].record()
+        if k >= args.warmup:
+            counts.append(rv.visible_count())
+            passes.append(p)
+    torch.cuda.synchronize()
+    clocks = sampler.finish()
+    timed = range(args.warmup, nfr)
+    tot_ms = sum(evs[k][0].elapsed_time(evs[k][3]) for k in timed)
+    set_ms = sum(evs[k][0].elapsed_time(evs[k][1]) for k in timed)
+    int_ms = sum(evs[k][1].elapsed_time(evs[k][2]) for k in timed)
+    trc_ms = sum(evs[k][2].elapsed_time(evs[k][3]) for k in timed)
+    units = float(sum(counts)) * 512.0
+    rv.close()
+
+    # end-to-end leg: Image upload from host, SetView..Trace, download of the traced images
+    rv = new_ref()
+    pinned_in = [torch.from_numpy(d).pin_memory() for d, _ in frames]
+    h_depth = torch.empty((H, W), dtype=torch.float32).pin_memory()
+    h_color = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    h_normal = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    torch.cuda.synchronize()
+    for k in range(nfr):
+        if k == args.warmup:
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+        rv.set_frame(pinned_in[k].numpy(), K, frames[k][1])
+        rv.set_view_converged()
+        rv.integrate(0)
+        rv.trace(W, H, K, frames[k][1])
+        rv.lib.ref_download(h_depth.data_ptr(), rv.ptr(4), W * H * 4)
+        rv.lib.ref_download(h_color.data_ptr(), rv.ptr(5), W * H * 12)
+        rv.lib.ref_download(h_normal.data_ptr(), rv.ptr(6), W * H * 12)
+    torch.cuda.synchronize()
+    t_e2e = time.perf_counter() - t0
+    rv.close()
+    return {
+        "impl": "reference", "device": "cuda (the reference is CUDA-only; built unmodified for sm_100a, -O3 -DNDEBUG)",
+        "metric": METRIC, "value": units / (tot_ms * 1e-3), "unit": "voxel-updates/s", "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "c2_orbit: 640x480 sphere-on-plane depth, 4 mm voxels, Volume(262144,65536), "
+                               "1.2 deg/frame orbit, GT poses; step = SetView (repeated until the visible count is "
+                               "stable)+DepthIntegrate+Trace",
+                   "l2": "256 MiB device memset between steps, outside the per-step CUDA events"},
+        "phases": {"setview_ms": set_ms / args.steps, "integrate_ms": int_ms / args.steps,
+                   "trace_ms": trc_ms / args.steps, "setview_passes_mean": float(np.mean(passes)),
+                   "integrate_voxel_updates_per_s": units / (int_ms * 1e-3),
+                   "trace_rays_per_s": W * H * args.steps / (trc_ms * 1e-3)},
+        "visible_blocks_per_frame": float(np.mean(counts)),
+        "clocks": clocks,
+        "e2e": {"value": units / t_e2e, "unit": "voxel-updates/s", "h2d_bytes_per_step": W * H * 4,
+                "d2h_bytes_per_step": W * H * 28, "ms_per_step": t_e2e * 1e3 / args.steps},
+    }
+
+
+def cpu_baseline(sample_frames=6):
+    """The oracle port on the host cores: a bounded sample (first frames of the same orbit)."""
+    import harness as Hh
+    K, frames = make_frames(sample_frames)
+    threads = os.cpu_count() or 1
+    ov = Hh.OracleVolume(MAIN, EXCESS, VOXEL, TRUNC)
+    units = 0
+    t_int = t_trc = t_set = 0.0
+    for depth, T in frames:
+        t0 = time.perf_counter()
+        ov.set_view_converged(depth, K, T)
+        t1 = time.perf_counter()
+        ov.integrate_depth(depth, K, T)
+        t2 = time.perf_counter()
+        ov.trace(W, H, K, T)
+        t3 = time.perf_counter()
+        units += len(ov.visible()) * 512
+        t_set += t1 - t0
+        t_int += t2 - t1
+        t_trc += t3 - t2
+    tot = t_set + t_int + t_trc
+    return {"value": units / tot, "unit": "voxel-updates/s", "cores": threads, "kind": "port",
+            "sample": "first %d frames of the same orbit through oracle/vulcan_oracle.cpp (OpenMP, %d threads; "
+                      "allocation sequential)" % (sample_frames, threads),
+            "ms_per_step": tot * 1e3 / sample_frames,
+            "integrate_voxel_updates_per_s": units / t_int, "trace_rays_per_s": W * H * sample_frames / t_trc}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        line = run_reference(args)
+        if "unavailable" not in line and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(line))
+        return
+
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+        dist.init_process_group("nccl")
+    line = run_ours(args, rank, world)
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

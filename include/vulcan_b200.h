@@ -87,9 +87,10 @@ enum {
   VK_CNT_VOXEL_PTR  = 2,  /* top of free voxel-block stack (voxel_pointer)          */
   VK_CNT_EXCESS_PTR = 3,  /* next excess entry (excess_pointer)                     */
   VK_CNT_OVERFLOW   = 4,  /* number of dropped allocations                          */
-  VK_CNT_NEW_BLOCKS = 5,  /* blocks allocated by the last vk_set_view               */
+  VK_CNT_NEW_BLOCKS = 5,  /* reserved                                               */
   VK_CNT_ALLOCATED  = 6,  /* blocks allocated in total                              */
-  VK_CNT_PATCHES    = 7,  /* patch count of the last vk_compute_patches             */
+  VK_CNT_PATCHES    = 7,  /* reserved                                               */
+  VK_CNT_UPDATED    = 8,  /* 64-bit (slots 8,9): voxels written by the integrators  */
   VK_CNT_COUNT      = 16
 };
 

@@ -1,0 +1,896 @@
+// vulcan_oracle.cpp — CPU restatement of Vulcan's TSDF-fusion hot path.
+//
+// TEST INFRASTRUCTURE ONLY.  Nothing in the product (vulcan_b200/, include/) links,
+// imports or calls this file; it is used by tests/, __graft_entry__.smoke() and the
+// cpu_baseline / --impl reference legs of bench.py as the checker and as the timed CPU
+// baseline.
+//
+// Each function restates one reference kernel with plain IEEE float arithmetic (build
+// with -ffp-contract=off: one rounding per source operation, in the reference's source
+// order) and cites the reference lines it follows (paths relative to /root/reference).
+// The reference has no CPU implementation of this path and stores no golden vectors
+// (SURVEY.md 8c); parity of this oracle is pinned by running the reference's own CUDA
+// sources (oracle/_ref, built by oracle/build_ref.sh) on a B200 on identical inputs —
+// see tests/test_parity_gpu.py and tests/golden/ (vectors produced by that build).
+//
+// Build:  g++ -O2 -ffp-contract=off -fopenmp -shared -fPIC -o _build/libvulcan_oracle.so vulcan_oracle.cpp
+#include <cfloat>
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+namespace {
+
+struct Voxel {  // include/vulcan/voxel.h:41-49
+  float distance;
+  float color[3];
+  int16_t distance_weight;
+  int16_t color_weight;
+};
+static_assert(sizeof(Voxel) == 20, "Voxel layout");
+
+struct HashEntry {  // include/vulcan/hash.h:49-55, include/vulcan/block.h:79-85
+  int16_t block[3];
+  int16_t pad;
+  int32_t data;
+  int32_t next;
+};
+static_assert(sizeof(HashEntry) == 16, "HashEntry layout");
+
+struct Patch {  // include/vulcan/tracer.h:13-22
+  int16_t origin[2];
+  int16_t size[2];
+  float bounds[2];
+};
+
+enum { VIS_UNKNOWN = 0, VIS_FALSE = 1, VIS_TRUE = 2 };      // include/vulcan/types.h:6-11
+enum { ALLOC_NONE = 0, ALLOC_MAIN = 1, ALLOC_EXCESS = 2 };  // include/vulcan/types.h:13-18
+
+struct V3 { float x, y, z; };
+
+// column-major 4x4, include/vulcan/matrix.h:320-333
+inline float M(const float* m, int r, int c) { return m[c * 4 + r]; }
+
+// Transform::operator*(Vector4f), include/vulcan/transform.h:43-58
+inline V3 xform(const float* m, float x, float y, float z, float w) {
+  V3 o;
+  o.x = M(m, 0, 0) * x + M(m, 0, 1) * y + M(m, 0, 2) * z + M(m, 0, 3) * w;
+  o.y = M(m, 1, 0) * x + M(m, 1, 1) * y + M(m, 1, 2) * z + M(m, 1, 3) * w;
+  o.z = M(m, 2, 0) * x + M(m, 2, 1) * y + M(m, 2, 2) * z + M(m, 2, 3) * w;
+  return o;
+}
+
+struct Proj { float fx, fy, cx, cy; };
+
+// Projection::Project, include/vulcan/projection.h:63-71
+inline void project(const Proj& P, const V3& X, float& u, float& v) {
+  const float inv_w = 1.0f / X.z;
+  u = inv_w * P.fx * X.x + P.cx;
+  v = inv_w * P.fy * X.y + P.cy;
+}
+
+// Projection::Unproject, include/vulcan/projection.h:80-89
+inline V3 unproject(const Proj& P, float u, float v) {
+  const float ifx = 1.0f / P.fx;
+  const float ify = 1.0f / P.fy;
+  V3 o;
+  o.x = ifx * u - P.cx * ifx;
+  o.y = ify * v - P.cy * ify;
+  o.z = 1;
+  return o;
+}
+
+// Matrix::Dot, include/vulcan/matrix.h:158-171
+inline float dot(const V3& a, const V3& b) {
+  float r = 0;
+  r += a.x * b.x;
+  r += a.y * b.y;
+  r += a.z * b.z;
+  return r;
+}
+
+// Matrix::Normalize, include/vulcan/matrix.h:118-141
+inline V3 normalized(const V3& a) {
+  const float inv_norm = 1.0f / std::sqrt(dot(a, a));
+  V3 o = {a.x * inv_norm, a.y * inv_norm, a.z * inv_norm};
+  return o;
+}
+
+inline V3 scale(const V3& a, float s) { V3 o = {a.x * s, a.y * s, a.z * s}; return o; }
+inline V3 plus(const V3& a, const V3& b) { V3 o = {a.x + b.x, a.y + b.y, a.z + b.z}; return o; }
+inline V3 minus(const V3& a, const V3& b) { V3 o = {a.x - b.x, a.y - b.y, a.z - b.z}; return o; }
+
+template <typename T> inline T vmin(T a, T b) { return (b < a) ? b : a; }   // include/vulcan/math.h:9-14
+template <typename T> inline T vmax(T a, T b) { return (b > a) ? b : a; }   // include/vulcan/math.h:16-21
+template <typename T> inline T vclamp(T v, T lo, T hi) { return vmin(hi, vmax(lo, v)); }  // :23-28
+
+// Q1 hash, src/volume.cu:168-180
+inline uint32_t block_hash(int bx, int by, int bz, uint32_t K) {
+  return (((uint32_t)bx * 73856093u) ^ ((uint32_t)by * 19349669u) ^ ((uint32_t)bz * 83492791u)) % K;
+}
+
+inline bool same_block(const HashEntry& e, int bx, int by, int bz) {
+  return e.block[0] == (int16_t)bx && e.block[1] == (int16_t)by && e.block[2] == (int16_t)bz;
+}
+
+struct Volume {
+  int M_, E_, B_;
+  float voxel_length, trunc_length, min_depth, max_depth;
+  Voxel* voxels;
+  std::vector<HashEntry> entries;
+  std::vector<int32_t> free_list;
+  std::vector<uint8_t> alloc_types;
+  std::vector<HashEntry> alloc_blocks;  // only .block used
+  std::vector<uint8_t> visibility;
+  std::vector<int32_t> visible;
+  int voxel_pointer, excess_pointer;
+  long long dropped;
+  // work counters of the last trace (for algorithmic bytes)
+  long long voxel_fetches, entry_fetches;
+};
+
+}  // namespace
+
+extern "C" {
+
+// Volume::Volume + Initialize, src/volume.cu:370-380,552-627
+void* vo_create(int main_blocks, int excess_blocks) {
+  Volume* v = new Volume();
+  v->M_ = main_blocks;
+  v->E_ = excess_blocks;
+  v->B_ = main_blocks + excess_blocks;
+  v->voxel_length = 0.008f;
+  v->trunc_length = 0.04f;
+  v->min_depth = 0.1f;
+  v->max_depth = 5.0f;
+  const size_t nvox = (size_t)v->B_ * 512;
+  v->voxels = (Voxel*)std::malloc(nvox * sizeof(Voxel));
+  Voxel empty;  // Voxel::Empty(), include/vulcan/voxel.h:29-37
+  empty.distance = 1;
+  empty.color[0] = empty.color[1] = empty.color[2] = 0;
+  empty.distance_weight = 0;
+  empty.color_weight = 0;
+#pragma omp parallel for schedule(static)
+  for (long long i = 0; i < (long long)nvox; ++i) v->voxels[i] = empty;
+  HashEntry he;
+  he.block[0] = he.block[1] = he.block[2] = 0;
+  he.pad = 0;
+  he.data = -1;
+  he.next = -1;
+  v->entries.assign(v->B_, he);
+  v->free_list.resize(v->B_);
+  for (int i = 0; i < v->B_; ++i) v->free_list[i] = i;
+  v->alloc_types.assign(v->M_, ALLOC_NONE);
+  v->alloc_blocks.assign(v->M_, he);
+  v->visibility.assign(v->B_, VIS_FALSE);
+  v->visible.reserve(v->B_);
+  v->voxel_pointer = v->B_ - 1;
+  v->excess_pointer = v->M_;
+  v->dropped = 0;
+  v->voxel_fetches = v->entry_fetches = 0;
+  return v;
+}
+
+void vo_destroy(void* h) {
+  Volume* v = (Volume*)h;
+  if (!v) return;
+  std::free(v->voxels);
+  delete v;
+}
+
+void vo_set_params(void* h, float voxel_length, float trunc_length, float min_depth, float max_depth) {
+  Volume* v = (Volume*)h;
+  v->voxel_length = voxel_length;
+  v->trunc_length = trunc_length;
+  v->min_depth = min_depth;
+  v->max_depth = max_depth;
+}
+
+void* vo_voxels(void* h) { return ((Volume*)h)->voxels; }
+void* vo_entries(void* h) { return ((Volume*)h)->entries.data(); }
+void* vo_visibility(void* h) { return ((Volume*)h)->visibility.data(); }
+void* vo_visible(void* h) { return ((Volume*)h)->visible.data(); }
+int vo_visible_count(void* h) { return (int)((Volume*)h)->visible.size(); }
+int vo_voxel_pointer(void* h) { return ((Volume*)h)->voxel_pointer; }
+int vo_excess_pointer(void* h) { return ((Volume*)h)->excess_pointer; }
+long long vo_dropped(void* h) { return ((Volume*)h)->dropped; }
+long long vo_voxel_fetches(void* h) { return ((Volume*)h)->voxel_fetches; }
+long long vo_entry_fetches(void* h) { return ((Volume*)h)->entry_fetches; }
+
+}  // extern "C"
+
+// ---- Volume::SetView ---------------------------------------------------------------
+
+namespace {
+
+// ResetBlockVisibility, src/volume.cu:465-471
+void reset_visibility(Volume* v) {
+  for (int i = 0; i < v->B_; ++i)
+    if (v->visibility[i] == VIS_TRUE) v->visibility[i] = VIS_UNKNOWN;
+}
+
+// CreateAllocationRequestsKernel, src/volume.cu:86-301.  Pixels are visited in raster
+// order, so the "last writer" of a contended bucket is the last pixel in that order; the
+// reference leaves the winner unspecified (Q3).  Returns the number of requests written.
+long long create_requests(Volume* v, const float* depths, int w, int h, const Proj& P, const float* Twd) {
+  long long requests = 0;
+  const float block_length = 8 * v->voxel_length;
+  const float trunc = v->trunc_length;
+  const uint32_t K = (uint32_t)v->M_;
+  for (int y = 0; y < h; ++y)
+    for (int x = 0; x < w; ++x) {
+      V3 direction = unproject(P, x + 0.5f, y + 0.5f);
+      direction = xform(Twd, direction.x, direction.y, direction.z, 0);
+      const V3 origin = {M(Twd, 0, 3), M(Twd, 1, 3), M(Twd, 2, 3)};
+      const float depth = depths[y * w + x];
+      if (depth < v->min_depth || depth > v->max_depth) continue;
+      const V3 Xwp = plus(origin, scale(direction, depth));
+      direction = normalized(direction);
+      const V3 begin = minus(Xwp, scale(direction, trunc));
+      const V3 end = plus(Xwp, scale(direction, trunc));
+      const int step_x = (direction.x < 0) ? -1 : 1;
+      const int step_y = (direction.y < 0) ? -1 : 1;
+      const int step_z = (direction.z < 0) ? -1 : 1;
+      const float inv_block_length = 1.0f / block_length;
+      int bx = (int)floorf(begin.x * inv_block_length);
+      int by = (int)floorf(begin.y * inv_block_length);
+      int bz = (int)floorf(begin.z * inv_block_length);
+      const int ex = (int)floorf(end.x * inv_block_length);
+      const int ey = (int)floorf(end.y * inv_block_length);
+      const int ez = (int)floorf(end.z * inv_block_length);
+      const float ox = block_length * (bx + vmax(0, step_x)) - begin.x;
+      const float oy = block_length * (by + vmax(0, step_y)) - begin.y;
+      const float oz = block_length * (bz + vmax(0, step_z)) - begin.z;
+      float tmax_x = ox / direction.x;
+      float tmax_y = oy / direction.y;
+      float tmax_z = oz / direction.z;
+      if (direction.x == 0) tmax_x = 1E20f;
+      if (direction.y == 0) tmax_y = 1E20f;
+      if (direction.z == 0) tmax_z = 1E20f;
+      const float tdelta_x = (step_x * block_length) / direction.x;
+      const float tdelta_y = (step_y * block_length) / direction.y;
+      const float tdelta_z = (step_z * block_length) / direction.z;
+      while (true) {
+        const uint32_t hash_code = block_hash(bx, by, bz, K);
+        HashEntry entry = v->entries[hash_code];
+        if (same_block(entry, bx, by, bz)) {
+          v->visibility[hash_code] = VIS_TRUE;  // also Q23 for block (0,0,0) in an empty bucket 0
+        } else if (entry.data == -1) {
+          v->visibility[hash_code] = VIS_TRUE;
+          v->alloc_types[hash_code] = ALLOC_MAIN;
+          v->alloc_blocks[hash_code].block[0] = (int16_t)bx;
+          v->alloc_blocks[hash_code].block[1] = (int16_t)by;
+          v->alloc_blocks[hash_code].block[2] = (int16_t)bz;
+          ++requests;
+        } else {
+          bool found = false;
+          while (entry.next != -1) {
+            const int index = entry.next;
+            entry = v->entries[index];
+            if (same_block(entry, bx, by, bz)) {
+              v->visibility[index] = VIS_TRUE;
+              found = true;
+              break;
+            }
+          }
+          if (!found) {
+            v->alloc_types[hash_code] = ALLOC_EXCESS;
+            v->alloc_blocks[hash_code].block[0] = (int16_t)bx;
+            v->alloc_blocks[hash_code].block[1] = (int16_t)by;
+            v->alloc_blocks[hash_code].block[2] = (int16_t)bz;
+            ++requests;
+          }
+        }
+        if (tmax_x < tmax_y) {
+          if (tmax_x < tmax_z) { bx += step_x; if (bx == ex + step_x) break; tmax_x += tdelta_x; }
+          else                 { bz += step_z; if (bz == ez + step_z) break; tmax_z += tdelta_z; }
+        } else {
+          if (tmax_y < tmax_z) { by += step_y; if (by == ey + step_y) break; tmax_y += tdelta_y; }
+          else                 { bz += step_z; if (bz == ez + step_z) break; tmax_z += tdelta_z; }
+        }
+      }
+    }
+  return requests;
+}
+
+// HandleAllocationRequestsKernel, src/volume.cu:303-368 (buckets visited in index order)
+void handle_requests(Volume* v) {
+  for (int index = 0; index < v->M_; ++index) {
+    const uint8_t type = v->alloc_types[index];
+    if (type == ALLOC_NONE) continue;
+    HashEntry entry;
+    entry.block[0] = v->alloc_blocks[index].block[0];
+    entry.block[1] = v->alloc_blocks[index].block[1];
+    entry.block[2] = v->alloc_blocks[index].block[2];
+    entry.pad = 0;
+    entry.data = -1;
+    entry.next = -1;
+    int entry_index = index;
+    if (type == ALLOC_EXCESS) {
+      int other_index = index;
+      HashEntry other = v->entries[other_index];
+      while (other.next != -1) {
+        other_index = other.next;
+        other = v->entries[other_index];
+      }
+      entry_index = v->excess_pointer++;
+      if (entry_index < v->B_) {
+        v->entries[other_index].next = entry_index;
+        v->visibility[entry_index] = VIS_TRUE;
+      }
+    }
+    const int voxel_index = v->voxel_pointer--;
+    if (entry_index < v->B_ && voxel_index >= 0) {
+      entry.data = v->free_list[voxel_index];
+      v->entries[entry_index] = entry;
+    } else {
+      v->dropped++;
+    }
+    v->alloc_types[index] = ALLOC_NONE;
+  }
+}
+
+// UpdateBlockVisibilityKernel, src/volume.cu:23-84 (entries visited in index order)
+void update_visibility(Volume* v, int w, int h, const Proj& P, const float* Tdw) {
+  const float block_length = 8 * v->voxel_length;
+  v->visible.clear();
+  for (int index = 0; index < v->B_; ++index) {
+    const uint8_t vis = v->visibility[index];
+    bool visible = (vis == VIS_TRUE);
+    if (vis == VIS_UNKNOWN) {
+      const HashEntry& e = v->entries[index];
+      for (int i = 0; i < 8; ++i) {
+        const float X = block_length * (e.block[0] + ((i & 1) >> 0));
+        const float Y = block_length * (e.block[1] + ((i & 2) >> 1));
+        const float Z = block_length * (e.block[2] + ((i & 4) >> 2));
+        const V3 Xdp = xform(Tdw, X, Y, Z, 1);
+        if (Xdp.z < 0) continue;
+        float u, vv;
+        project(P, Xdp, u, vv);
+        if (u >= 0 && u <= w && vv >= 0 && vv <= h) { visible = true; break; }
+      }
+      if (!visible) v->visibility[index] = VIS_FALSE;
+    }
+    if (visible) v->visible.push_back(index);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+// One Volume::SetView pass (src/volume.cu:430-437).  T = 32 floats: column-major
+// depth_to_world matrix followed by its inverse.  Returns the number of allocation
+// requests the pass generated (0 => the pass was at the fixed point).
+long long vo_set_view(void* h, const float* depth, int w, int hgt, const float* proj4, const float* T) {
+  Volume* v = (Volume*)h;
+  const Proj P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  reset_visibility(v);
+  const long long req = create_requests(v, depth, w, hgt, P, T);
+  handle_requests(v);
+  update_visibility(v, w, hgt, P, T + 16);
+  return req;
+}
+
+// SetView repeated until a pass generates no request (apps/vulcan/vulcan.cu:316-318 calls it
+// three times; tests/tracer_test.cu:298-303 loops to the fixed point).  Returns the passes run.
+int vo_set_view_converged(void* h, const float* depth, int w, int hgt, const float* proj4, const float* T,
+                          int max_passes) {
+  int passes = 0;
+  while (passes < max_passes) {
+    ++passes;
+    if (vo_set_view(h, depth, w, hgt, proj4, T) == 0) break;
+  }
+  return passes;
+}
+
+}  // extern "C"
+
+// ---- integrators -------------------------------------------------------------------
+
+namespace {
+
+// Matrix::operator*(Matrix), include/vulcan/matrix.h:296-316 (column-major 4x4)
+void matmul4(const float* A, const float* Bm, float* C) {
+  for (int p = 0; p < 4; ++p)
+    for (int m = 0; m < 4; ++m) {
+      float acc = 0;
+      for (int n = 0; n < 4; ++n) acc += A[n * 4 + m] * Bm[p * 4 + n];
+      C[p * 4 + m] = acc;
+    }
+}
+
+inline V3 voxel_world(const HashEntry& e, float block_length, float voxel_length, int x, int y, int z) {
+  // src/depth_integrator.cu:36-39
+  V3 Xwp;
+  Xwp.x = block_length * (float)e.block[0] + voxel_length * ((float)x + 0.5f);
+  Xwp.y = block_length * (float)e.block[1] + voxel_length * ((float)y + 0.5f);
+  Xwp.z = block_length * (float)e.block[2] + voxel_length * ((float)z + 0.5f);
+  return Xwp;
+}
+
+// IntegrateKernel, src/depth_integrator.cu:17-80 (= IntegrateDepthKernel of the colour and
+// light integrators, src/color_integrator.cu:17-80, src/light_integrator.cu:105-168)
+void integrate_depth(Volume* v, const float* depths, int w, int h, const Proj& P, const float* Tdw,
+                     float min_depth, float max_depth, float max_dist_weight) {
+  const float voxel_length = v->voxel_length;
+  const float block_length = 8 * voxel_length;
+  const float trunc = v->trunc_length;
+  const int n = (int)v->visible.size();
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int b = 0; b < n; ++b) {
+    const HashEntry entry = v->entries[v->visible[b]];
+    for (int z = 0; z < 8; ++z)
+      for (int y = 0; y < 8; ++y)
+        for (int x = 0; x < 8; ++x) {
+          const V3 Xwp = voxel_world(entry, block_length, voxel_length, x, y, z);
+          const V3 Xdp = xform(Tdw, Xwp.x, Xwp.y, Xwp.z, 1);
+          float u, vv;
+          project(P, Xdp, u, vv);
+          if (u >= 0 && u < w && vv >= 0 && vv < h) {  // Q9a: no z > 0 test
+            const float depth = depths[(int)vv * w + (int)u];
+            if (depth < min_depth || depth > max_depth) continue;
+            const float distance = depth - Xdp.z;
+            if (distance > -trunc) {
+              Voxel& voxel = v->voxels[(long long)entry.data * 512 + z * 64 + y * 8 + x];
+              const float prev_dist = voxel.distance_weight * voxel.distance;
+              const float curr_dist = vmin(1.0f, distance / trunc);
+              const float dist_weight = voxel.distance_weight + 1;
+              voxel.distance_weight = (int16_t)vmin(max_dist_weight, dist_weight);
+              voxel.distance = (prev_dist + curr_dist) / dist_weight;  // Q9b
+            }
+          }
+        }
+  }
+}
+
+// IntegrateColorKernel, src/color_integrator.cu:82-135
+void integrate_color(Volume* v, const float* colors, int w, int h, const Proj& P, const float* Tcw,
+                     float max_color_weight) {
+  const float voxel_length = v->voxel_length;
+  const float block_length = 8 * voxel_length;
+  const int n = (int)v->visible.size();
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int b = 0; b < n; ++b) {
+    const HashEntry entry = v->entries[v->visible[b]];
+    for (int z = 0; z < 8; ++z)
+      for (int y = 0; y < 8; ++y)
+        for (int x = 0; x < 8; ++x) {
+          const V3 Xwp = voxel_world(entry, block_length, voxel_length, x, y, z);
+          const V3 Xcp = xform(Tcw, Xwp.x, Xwp.y, Xwp.z, 1);
+          float u, vv;
+          project(P, Xcp, u, vv);
+          if (u >= 0 && u < w && vv >= 0 && vv < h) {
+            Voxel& voxel = v->voxels[(long long)entry.data * 512 + z * 64 + y * 8 + x];
+            if (fabsf(voxel.distance) < 1.0) {  // Q10
+              const float* c = colors + 3 * ((long long)(int)vv * w + (int)u);
+              const float cw = voxel.color_weight;
+              const float color_weight = voxel.color_weight + 1;
+              const float inv = 1.0f / color_weight;  // Matrix::operator/=, include/vulcan/matrix.h:288-295
+              for (int k = 0; k < 3; ++k) voxel.color[k] = (voxel.color[k] * cw + c[k]) * inv;
+              voxel.color_weight = (int16_t)vmin(max_color_weight, color_weight);
+            }
+          }
+        }
+  }
+}
+
+// ComputeFrameMaskKernel<16,3>, src/light_integrator.cu:17-103 (Q14: tile filled from image
+// offset -1, window read at +3 +/- 3 => window = image offsets [-1, +5] around the pixel)
+void frame_mask(int w, int h, const float* depths, const float* colors, float threshold, float* mask) {
+#pragma omp parallel for schedule(static)
+  for (int y = 0; y < h; ++y)
+    for (int x = 0; x < w; ++x) {
+      const int index = y * w + x;
+      const float* c = colors + 3 * (long long)index;
+      if (c[0] < 0.02f || c[0] > 0.98f || c[1] < 0.02f || c[1] > 0.98f || c[2] < 0.02f || c[2] > 0.98f) {
+        mask[index] = 0;
+        continue;
+      }
+      float dmin = +FLT_MAX, dmax = -FLT_MAX;
+      for (int i = -3; i <= 3; ++i)
+        for (int j = -3; j <= 3; ++j) {
+          const int vx = x - 1 + 3 + j, vy = y - 1 + 3 + i;
+          float d = 0;
+          if (vx >= 0 && vx < w && vy >= 0 && vy < h) d = depths[vy * w + vx];
+          dmin = fminf(d, dmin);
+          dmax = fmaxf(d, dmax);
+        }
+      mask[index] = (dmax - dmin <= threshold) ? 1.0f : 0.0f;
+    }
+}
+
+// IntegrateColorKernel of the light integrator, src/light_integrator.cu:170-250 with
+// Light::GetShading, include/vulcan/light.h:52-60
+void integrate_light_color(Volume* v, const float* mask, const float* colors, const float* normals, int w, int h,
+                           const Proj& Pd, const Proj& Pc, const float* Tdw, const float* Tcw, const float* Tcd,
+                           float intensity, const float* lpos, float max_color_weight) {
+  const float voxel_length = v->voxel_length;
+  const float block_length = 8 * voxel_length;
+  const int n = (int)v->visible.size();
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int b = 0; b < n; ++b) {
+    const HashEntry entry = v->entries[v->visible[b]];
+    for (int z = 0; z < 8; ++z)
+      for (int y = 0; y < 8; ++y)
+        for (int x = 0; x < 8; ++x) {
+          const V3 Xwp = voxel_world(entry, block_length, voxel_length, x, y, z);
+          const V3 Xdp = xform(Tdw, Xwp.x, Xwp.y, Xwp.z, 1);
+          const V3 Xcp = xform(Tcw, Xwp.x, Xwp.y, Xwp.z, 1);
+          float du, dv, cu, cv;
+          project(Pd, Xdp, du, dv);
+          project(Pc, Xcp, cu, cv);
+          if (!(du >= 0 && du < w && dv >= 0 && dv < h && cu >= 0 && cu < w && cv >= 0 && cv < h)) continue;
+          const int depth_index = (int)dv * w + (int)du;
+          const int color_index = (int)cv * w + (int)cu;
+          if (!(mask[depth_index] > 0.5f)) continue;
+          Voxel& voxel = v->voxels[(long long)entry.data * 512 + z * 64 + y * 8 + x];
+          if (!(fabsf(voxel.distance) < 1.0)) continue;
+          float cur[3] = {colors[3 * (long long)color_index], colors[3 * (long long)color_index + 1],
+                          colors[3 * (long long)color_index + 2]};
+          const float* nrm = normals + 3 * (long long)depth_index;
+          const V3 Xcn = xform(Tcd, nrm[0], nrm[1], nrm[2], 0);
+          const V3 delta = {lpos[0] - Xcp.x, lpos[1] - Xcp.y, lpos[2] - Xcp.z};
+          const V3 direction = normalized(delta);
+          const float distance_squared = dot(delta, delta);
+          const float cos_theta = dot(Xcn, direction);
+          const float shading = intensity * cos_theta / distance_squared;
+          if (shading > 0.05f) {
+            const float inv_s = 1.0f / shading;
+            for (int k = 0; k < 3; ++k) cur[k] *= inv_s;
+            const float cw = voxel.color_weight;
+            const float color_weight = voxel.color_weight + 1;
+            const float inv = 1.0f / color_weight;
+            for (int k = 0; k < 3; ++k) voxel.color[k] = (voxel.color[k] * cw + cur[k]) * inv;
+            voxel.color_weight = (int16_t)vmin(max_color_weight, color_weight);
+          }
+        }
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+// DepthIntegrator::Integrate, src/depth_integrator.cu:89-115
+void vo_integrate_depth(void* h, const float* depth, int w, int hgt, const float* proj4, const float* T,
+                        float min_depth, float max_depth, float max_dist_weight) {
+  const Proj P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  integrate_depth((Volume*)h, depth, w, hgt, P, T + 16, min_depth, max_depth, max_dist_weight);
+}
+
+// ColorIntegrator::Integrate, src/color_integrator.cu:144-204.  Tcd = 32 floats like T.
+void vo_integrate_color(void* h, const float* depth, int w, int hgt, const float* dproj4, const float* T,
+                        const float* color, int cw, int ch, const float* cproj4, const float* Tcd,
+                        float min_depth, float max_depth, float max_dist_weight, float max_color_weight) {
+  const Proj Pd = {dproj4[0], dproj4[1], dproj4[2], dproj4[3]};
+  const Proj Pc = {cproj4[0], cproj4[1], cproj4[2], cproj4[3]};
+  integrate_depth((Volume*)h, depth, w, hgt, Pd, T + 16, min_depth, max_depth, max_dist_weight);
+  float Tcw[16];
+  matmul4(Tcd, T + 16, Tcw);  // Tcd * Twd.Inverse(), src/color_integrator.cu:191-193
+  integrate_color((Volume*)h, color, cw, ch, Pc, Tcw, max_color_weight);
+}
+
+void vo_frame_mask(int w, int hgt, const float* depth, const float* color, float threshold, float* mask) {
+  frame_mask(w, hgt, depth, color, threshold, mask);
+}
+
+// LightIntegrator::Integrate, src/light_integrator.cu:270-354
+void vo_integrate_light(void* h, const float* depth, int w, int hgt, const float* dproj4, const float* T,
+                        const float* color, const float* normal, const float* cproj4, const float* Tcd,
+                        float min_depth, float max_depth, float max_dist_weight, float max_color_weight,
+                        float intensity, const float* light_pos, float depth_threshold, float* mask) {
+  const Proj Pd = {dproj4[0], dproj4[1], dproj4[2], dproj4[3]};
+  const Proj Pc = {cproj4[0], cproj4[1], cproj4[2], cproj4[3]};
+  frame_mask(w, hgt, depth, color, depth_threshold, mask);
+  integrate_depth((Volume*)h, depth, w, hgt, Pd, T + 16, min_depth, max_depth, max_dist_weight);
+  float Tcw[16];
+  matmul4(Tcd, T + 16, Tcw);
+  integrate_light_color((Volume*)h, mask, color, normal, w, hgt, Pd, Pc, T + 16, Tcw, Tcd, intensity, light_pos,
+                        max_color_weight);
+}
+
+}  // extern "C"
+
+// ---- Tracer --------------------------------------------------------------------------
+
+namespace {
+
+// float -> short like the device conversion the reference relies on (saturating,
+// NaN -> 0); in-range values truncate toward zero exactly like a C cast
+inline int16_t to_short(float f) {
+  if (f != f) return 0;
+  if (f >= 32767.0f) return 32767;
+  if (f <= -32768.0f) return -32768;
+  return (int16_t)f;
+}
+
+// ComputePatchesKernel, src/tracer.cu:13-87, for one block; returns patch count
+int block_patches(const HashEntry& entry, const float* Tcw, const Proj& P, float block_length, float min_depth,
+                  float max_depth, int image_w, int image_h, int bw, int bh, Patch* out) {
+  int16_t bmax[2] = {-1, -1};
+  int16_t bmin[2] = {(int16_t)bw, (int16_t)bh};
+  float db[2] = {+FLT_MAX, -FLT_MAX};
+  for (int z = 0; z <= 1; ++z) {
+    const float Z = block_length * (z + entry.block[2]);
+    for (int y = 0; y <= 1; ++y) {
+      const float Y = block_length * (y + entry.block[1]);
+      for (int x = 0; x <= 1; ++x) {
+        const float X = block_length * (x + entry.block[0]);
+        const V3 Xcp = xform(Tcw, X, Y, Z, 1);
+        float u, v;
+        project(P, Xcp, u, v);
+        u = bw * u / image_w;
+        v = bh * v / image_h;
+        bmin[0] = vclamp<int16_t>(vmin(to_short(floorf(u)), bmin[0]), 0, bw - 1);
+        bmin[1] = vclamp<int16_t>(vmin(to_short(floorf(v)), bmin[1]), 0, bh - 1);
+        bmax[0] = vclamp<int16_t>(vmax(to_short(ceilf(u)), bmax[0]), 0, bw - 1);
+        bmax[1] = vclamp<int16_t>(vmax(to_short(ceilf(v)), bmax[1]), 0, bh - 1);
+        db[0] = vclamp(vmin(Xcp.z, db[0]), min_depth, max_depth);
+        db[1] = vclamp(vmax(Xcp.z, db[1]), min_depth, max_depth);
+      }
+    }
+  }
+  const int rx = bmax[0] - bmin[0];
+  const int ry = bmax[1] - bmin[1];
+  const int gx = (rx + 16 - 1) / 16;  // Q12
+  const int gy = (ry + 16 - 1) / 16;
+  const int count = (db[1] > db[0]) ? gx * gy : 0;
+  if (count == 0) return 0;
+  for (int i = 0; i < gy; ++i)
+    for (int j = 0; j < gx; ++j) {
+      Patch& p = out[i * gx + j];
+      p.origin[0] = (int16_t)(bmin[0] + 16 * j);
+      p.origin[1] = (int16_t)(bmin[1] + 16 * i);
+      p.size[0] = (int16_t)vmin(16, bmax[0] - p.origin[0] + 1);
+      p.size[1] = (int16_t)vmin(16, bmax[1] - p.origin[1] + 1);
+      p.bounds[0] = db[0];
+      p.bounds[1] = db[1];
+    }
+  return count;
+}
+
+struct Tap { float distance; float color[3]; int color_weight; };
+
+struct Fetch { long long voxels, entries; };
+
+// lookup used by ComputePointsKernel (src/tracer.cu:363-371) and GetVoxel (:151-175)
+inline int find_data(const Volume* v, int bx, int by, int bz, Fetch& f) {
+  HashEntry entry = v->entries[block_hash(bx, by, bz, (uint32_t)v->M_)];
+  ++f.entries;
+  while (!same_block(entry, bx, by, bz) && entry.next != -1) {
+    entry = v->entries[entry.next];
+    ++f.entries;
+  }
+  return same_block(entry, bx, by, bz) ? entry.data : -1;
+}
+
+inline Tap tap_at(const Volume* v, int data, int offset, Fetch& f) {
+  const Voxel& vx = v->voxels[(long long)data * 512 + offset];
+  ++f.voxels;
+  Tap t = {vx.distance, {vx.color[0], vx.color[1], vx.color[2]}, vx.color_weight};
+  return t;
+}
+
+// GetVoxel, src/tracer.cu:114-188
+Tap get_voxel(const Volume* v, int bx, int by, int bz, int vx, int vy, int vz, Fetch& f) {
+  if (vx < 0) { --bx; vx = 8 + vx; } else if (vx >= 8) { ++bx; vx = vx - 8; }
+  if (vy < 0) { --by; vy = 8 + vy; } else if (vy >= 8) { ++by; vy = vy - 8; }
+  if (vz < 0) { --bz; vz = 8 + vz; } else if (vz >= 8) { ++bz; vz = vz - 8; }
+  const int data = find_data(v, bx, by, bz, f);
+  if (data != -1) return tap_at(v, data, vz * 64 + vy * 8 + vx, f);
+  Tap t = {1.0f, {0, 0, 0}, 0};  // Voxel::Empty(), Q16
+  return t;
+}
+
+// GetInterpolatedDistance, src/tracer.cu:190-315
+void interpolate(const Volume* v, float block_length, float voxel_length, int bx, int by, int bz, int data,
+                 const V3& p, float& sdf, float* color, Fetch& f) {
+  const float wx = (p.x - bx * block_length) / voxel_length;
+  const float wy = (p.y - by * block_length) / voxel_length;
+  const float wz = (p.z - bz * block_length) / voxel_length;
+  const int i0x = (int)floorf(wx - 0.5f);
+  const int i0y = (int)floorf(wy - 0.5f);
+  const int i0z = (int)floorf(wz - 0.5f);
+  Tap t[8];  // index z*4 + y*2 + x  (v000, v001, v010, v011, v100, ...: last digit = x)
+  if (i0x >= 0 && i0y >= 0 && i0z >= 0 && i0x < 7 && i0y < 7 && i0z < 7) {
+    for (int c = 0; c < 8; ++c)
+      t[c] = tap_at(v, data, (i0z + (c >> 2)) * 64 + (i0y + ((c >> 1) & 1)) * 8 + (i0x + (c & 1)), f);
+  } else {
+    for (int c = 0; c < 8; ++c)
+      t[c] = get_voxel(v, bx, by, bz, i0x + (c & 1), i0y + ((c >> 1) & 1), i0z + (c >> 2), f);
+  }
+  const float w1[3] = {wx - (i0x + 0.5f), wy - (i0y + 0.5f), wz - (i0z + 0.5f)};
+  const float w0[3] = {1.0f - w1[0], 1.0f - w1[1], 1.0f - w1[2]};
+  const float n00 = t[0].distance * w0[0] + t[1].distance * w1[0];
+  const float n01 = t[2].distance * w0[0] + t[3].distance * w1[0];
+  const float n10 = t[4].distance * w0[0] + t[5].distance * w1[0];
+  const float n11 = t[6].distance * w0[0] + t[7].distance * w1[0];
+  const float n0 = n00 * w0[1] + n01 * w1[1];
+  const float n1 = n10 * w0[1] + n11 * w1[1];
+  float total = 0;
+  float col[3] = {0, 0, 0};
+  for (int c = 0; c < 8; ++c) {
+    const float wz_ = (c >> 2) ? w1[2] : w0[2];
+    const float wy_ = ((c >> 1) & 1) ? w1[1] : w0[1];
+    const float wx_ = (c & 1) ? w1[0] : w0[0];
+    // Q15: `wz * wy * wx * (cw > 0) ? 1 : 0`
+    const float weight = (wz_ * wy_ * wx_ * (t[c].color_weight > 0)) ? 1 : 0;
+    total += weight;
+    for (int k = 0; k < 3; ++k) col[k] += t[c].color[k] * weight;
+  }
+  if (total > 0) {
+    const float inv = 1.0f / total;
+    for (int k = 0; k < 3; ++k) col[k] *= inv;
+  }
+  color[0] = col[0]; color[1] = col[1]; color[2] = col[2];
+  sdf = n0 * w0[2] + n1 * w1[2];
+}
+
+// ComputeNormalsKernel<16>, src/frame.cu:7-122
+void normals(const float* depths, const Proj& P, float* out, int w, int h) {
+  auto at = [&](int x, int y) -> float { return (x >= 0 && x < w && y >= 0 && y < h) ? depths[y * w + x] : 0.0f; };
+#pragma omp parallel for schedule(static)
+  for (int y = 0; y < h; ++y)
+    for (int x = 0; x < w; ++x) {
+      float n[3] = {0, 0, 0};
+      const float depth = at(x, y);
+      if (depth > 0) {
+        const V3 z0 = scale(unproject(P, (x + 0) + 0.5f, (y + 0) + 0.5f), depth);
+        const int ox[4] = {-2, +2, 0, 0}, oy[4] = {0, 0, -2, +2};
+        V3 q[4];
+        for (int k = 0; k < 4; ++k) {
+          const float d = at(x + ox[k], y + oy[k]);
+          q[k] = (d == 0) ? z0 : scale(unproject(P, (x + ox[k]) + 0.5f, (y + oy[k]) + 0.5f), d);
+        }
+        const V3 dx = minus(q[0], q[1]);
+        const V3 dy = minus(q[2], q[3]);
+        if (dot(dx, dx) > 0 && dot(dy, dy) > 0) {
+          V3 c;  // dy.Cross(dx), include/vulcan/matrix.h:174-183
+          c.x = (dy.y * dx.z) - (dy.z * dx.y);
+          c.y = (dy.z * dx.x) - (dy.x * dx.z);
+          c.z = (dy.x * dx.y) - (dy.y * dx.x);
+          c = normalized(c);
+          n[0] = c.x; n[1] = c.y; n[2] = c.z;
+        }
+      }
+      float* o = out + 3 * ((long long)y * w + x);
+      o[0] = n[0]; o[1] = n[1]; o[2] = n[2];
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// Tracer::ComputePatches for an explicit index list (tests/tracer_test.cu:22-166 scenario).
+// Tcw = 16 floats column-major.  Returns the patch count.
+int vo_compute_patches(void* h, const int* indices, int count, const float* Tcw, const float* proj4,
+                       float block_length, float min_depth, float max_depth, int image_w, int image_h, int bw,
+                       int bh, void* patches_out) {
+  Volume* v = (Volume*)h;
+  const Proj P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  Patch* out = (Patch*)patches_out;
+  int total = 0;
+  for (int i = 0; i < count; ++i)
+    total += block_patches(v->entries[indices[i]], Tcw, P, block_length, min_depth, max_depth, image_w, image_h, bw,
+                           bh, out + total);
+  return total;
+}
+
+// ComputeBoundsKernel + FillKernel, src/tracer.cu:89-112,494-500
+void vo_compute_bounds(const void* patches_in, int count, float* bounds, int bw, int bh, int reset) {
+  const Patch* patches = (const Patch*)patches_in;
+  if (reset)
+    for (int i = 0; i < bw * bh; ++i) { bounds[2 * i] = +FLT_MAX; bounds[2 * i + 1] = -FLT_MAX; }
+  for (int k = 0; k < count; ++k) {
+    const Patch& p = patches[k];
+    for (int i = 0; i < p.size[1]; ++i)
+      for (int j = 0; j < p.size[0]; ++j) {
+        const int pixel = (p.origin[1] + i) * bw + p.origin[0] + j;
+        bounds[2 * pixel] = vmin(p.bounds[0], bounds[2 * pixel]);
+        bounds[2 * pixel + 1] = vmax(p.bounds[1], bounds[2 * pixel + 1]);
+      }
+  }
+}
+
+void vo_compute_normals(const float* depth, const float* proj4, float* out, int w, int hgt) {
+  const Proj P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  normals(depth, P, out, w, hgt);
+}
+
+// ComputePointsKernel, src/tracer.cu:317-451
+void vo_compute_points(void* h, const float* bounds, const float* T, const float* proj4, float* depths,
+                       float* colors, int w, int hgt, int bw, int bh) {
+  Volume* v = (Volume*)h;
+  const Proj P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  const float* Twc = T;
+  const float* Tcw = T + 16;
+  const float voxel_length = v->voxel_length;
+  const float block_length = 8 * voxel_length;
+  const float trunc = v->trunc_length;
+  long long tot_vox = 0, tot_ent = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : tot_vox, tot_ent)
+  for (int y = 0; y < hgt; ++y)
+    for (int x = 0; x < w; ++x) {
+      Fetch f = {0, 0};
+      const int px = bw * x / w;
+      const int py = bh * y / hgt;
+      const float lo = bounds[2 * (py * bw + px)], hi = bounds[2 * (py * bw + px) + 1];
+      float depth = 0, final_depth = 0;
+      float color[3] = {0, 0, 0};
+      if (lo < hi) {
+        const V3 Xcp = scale(unproject(P, x + 0.5f, y + 0.5f), lo);
+        const V3 Xwp = xform(Twc, Xcp.x, Xcp.y, Xcp.z, 1.0f);
+        const V3 dir = normalized(xform(Twc, Xcp.x, Xcp.y, Xcp.z, 0.0f));
+        V3 p = Xwp;
+        depth = lo;
+        int iters = 0;
+        do {
+          const int bx = (int)floorf(p.x / block_length);
+          const int by = (int)floorf(p.y / block_length);
+          const int bz = (int)floorf(p.z / block_length);
+          const int data = find_data(v, bx, by, bz, f);
+          if (data != -1) {
+            const float wx = (p.x - bx * block_length) / voxel_length;
+            const float wy = (p.y - by * block_length) / voxel_length;
+            const float wz = (p.z - bz * block_length) / voxel_length;
+            const int vx = (int)wx, vy = (int)wy, vz = (int)wz;  // Q22
+            float sdf = v->voxels[(long long)data * 512 + vz * 64 + vy * 8 + vx].distance;
+            ++f.voxels;
+            if (sdf <= 0.1f && sdf >= -0.5f) interpolate(v, block_length, voxel_length, bx, by, bz, data, p, sdf, color, f);
+            if (sdf <= 0.0f) {
+              p = plus(p, scale(dir, trunc * sdf));
+              const int bx2 = (int)floorf(p.x / block_length);
+              const int by2 = (int)floorf(p.y / block_length);
+              const int bz2 = (int)floorf(p.z / block_length);
+              const int data2 = find_data(v, bx2, by2, bz2, f);
+              if (data2 != -1) {
+                interpolate(v, block_length, voxel_length, bx2, by2, bz2, data2, p, sdf, color, f);
+                p = plus(p, scale(dir, trunc * sdf));
+              }
+              final_depth = xform(Tcw, p.x, p.y, p.z, 1.0f).z;
+              break;
+            } else {
+              p = plus(p, scale(dir, vmax(voxel_length, trunc * sdf)));
+            }
+          } else {
+            p = plus(p, scale(dir, block_length));
+          }
+          depth = xform(Tcw, p.x, p.y, p.z, 1.0f).z;
+          if (++iters >= 500) { color[0] = 1; color[1] = 0; color[2] = 0; break; }
+        } while (depth < hi);
+      }
+      const long long pixel = (long long)y * w + x;
+      depths[pixel] = final_depth;
+      colors[3 * pixel] = color[0]; colors[3 * pixel + 1] = color[1]; colors[3 * pixel + 2] = color[2];
+      tot_vox += f.voxels;
+      tot_ent += f.entries;
+    }
+  v->voxel_fetches = tot_vox;
+  v->entry_fetches = tot_ent;
+}
+
+// Tracer::Trace, src/tracer.cpp:41-47, with the hard-coded 80x60 bounds grid
+void vo_trace(void* h, const float* T, const float* proj4, int w, int hgt, float min_depth, float max_depth,
+              float* bounds /* 80*60*2 */, float* out_depth, float* out_color, float* out_normal) {
+  Volume* v = (Volume*)h;
+  const int bw = 80, bh = 60;
+  std::vector<Patch> patches;
+  patches.resize(1);
+  std::vector<Patch> all;
+  const Proj P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  Patch tmp[256 + 64];
+  for (size_t i = 0; i < v->visible.size(); ++i) {
+    const int n = block_patches(v->entries[v->visible[i]], T + 16, P, 8 * v->voxel_length, min_depth, max_depth, w, hgt,
+                                bw, bh, tmp);
+    all.insert(all.end(), tmp, tmp + n);
+  }
+  vo_compute_bounds(all.data(), (int)all.size(), bounds, bw, bh, 1);
+  vo_compute_points(h, bounds, T, proj4, out_depth, out_color, w, hgt, bw, bh);
+  if (out_normal) normals(out_depth, P, out_normal, w, hgt);
+}
+
+}  // extern "C"

@@ -1,0 +1,512 @@
+"""Test infrastructure: ctypes drivers for the CPU oracle (oracle/vulcan_oracle.cpp) and for
+the reference's own CUDA build (oracle/_ref, via oracle/ref_shim.cu), plus helpers that
+compare volumes by block coordinates (entry indices and voxel-block ids are not pinned by
+the reference)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SRC = os.path.join(ROOT, "oracle", "vulcan_oracle.cpp")
+ORACLE_LIB = os.path.join(ROOT, "oracle", "_build", "libvulcan_oracle.so")
+REF_LIB = os.path.join(ROOT, "oracle", "_ref", "libvulcan_ref.so")
+REF_LIB_NOFMAD = os.path.join(ROOT, "oracle", "_ref", "libvulcan_ref_nofmad.so")
+
+_F = C.c_float
+_I = C.c_int
+_P = C.c_void_p
+
+
+def build_oracle(force=False):
+    if force or not os.path.exists(ORACLE_LIB) or os.path.getmtime(ORACLE_LIB) < os.path.getmtime(ORACLE_SRC):
+        os.makedirs(os.path.dirname(ORACLE_LIB), exist_ok=True)
+        subprocess.check_call(["g++", "-O3", "-march=native", "-ffp-contract=off", "-fopenmp", "-shared", "-fPIC",
+                               "-o", ORACLE_LIB, ORACLE_SRC])
+    return ORACLE_LIB
+
+
+_oracle = None
+
+
+def oracle_lib():
+    global _oracle
+    if _oracle is None:
+        lib = C.CDLL(build_oracle())
+        lib.vo_create.restype = _P
+        lib.vo_create.argtypes = [_I, _I]
+        lib.vo_destroy.argtypes = [_P]
+        lib.vo_set_params.argtypes = [_P, _F, _F, _F, _F]
+        for n in ("vo_voxels", "vo_entries", "vo_visibility", "vo_visible"):
+            getattr(lib, n).restype = _P
+            getattr(lib, n).argtypes = [_P]
+        for n in ("vo_visible_count", "vo_voxel_pointer", "vo_excess_pointer"):
+            getattr(lib, n).restype = _I
+            getattr(lib, n).argtypes = [_P]
+        for n in ("vo_dropped", "vo_voxel_fetches", "vo_entry_fetches"):
+            getattr(lib, n).restype = C.c_longlong
+            getattr(lib, n).argtypes = [_P]
+        lib.vo_set_view.restype = C.c_longlong
+        lib.vo_set_view.argtypes = [_P, _P, _I, _I, _P, _P]
+        lib.vo_set_view_converged.restype = _I
+        lib.vo_set_view_converged.argtypes = [_P, _P, _I, _I, _P, _P, _I]
+        lib.vo_integrate_depth.argtypes = [_P, _P, _I, _I, _P, _P, _F, _F, _F]
+        lib.vo_integrate_color.argtypes = [_P, _P, _I, _I, _P, _P, _P, _I, _I, _P, _P, _F, _F, _F, _F]
+        lib.vo_frame_mask.argtypes = [_I, _I, _P, _P, _F, _P]
+        lib.vo_integrate_light.argtypes = [_P, _P, _I, _I, _P, _P, _P, _P, _P, _P, _F, _F, _F, _F, _F, _P, _F, _P]
+        lib.vo_compute_patches.restype = _I
+        lib.vo_compute_patches.argtypes = [_P, _P, _I, _P, _P, _F, _F, _F, _I, _I, _I, _I, _P]
+        lib.vo_compute_bounds.argtypes = [_P, _I, _P, _I, _I, _I]
+        lib.vo_compute_normals.argtypes = [_P, _P, _P, _I, _I]
+        lib.vo_compute_points.argtypes = [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I]
+        lib.vo_trace.argtypes = [_P, _P, _P, _I, _I, _F, _F, _P, _P, _P, _P]
+        _oracle = lib
+    return _oracle
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_P)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+class OracleVolume:
+    """CPU oracle with the reference's call structure (one SetView = one reference pass)."""
+
+    def __init__(self, main_blocks, excess_blocks, voxel_length=0.008, trunc_length=0.04, min_depth=0.1,
+                 max_depth=5.0):
+        self.lib = oracle_lib()
+        self.M, self.E, self.B = main_blocks, excess_blocks, main_blocks + excess_blocks
+        self.h = self.lib.vo_create(main_blocks, excess_blocks)
+        self.lib.vo_set_params(self.h, voxel_length, trunc_length, min_depth, max_depth)
+        self.voxel_length, self.trunc_length = voxel_length, trunc_length
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.lib.vo_destroy(self.h)
+            self.h = None
+
+    def set_view(self, depth, proj4, T32):
+        depth = _f32(depth)
+        return self.lib.vo_set_view(self.h, _ptr(depth), depth.shape[1], depth.shape[0], _ptr(_f32(proj4)),
+                                    _ptr(_f32(T32)))
+
+    def set_view_converged(self, depth, proj4, T32, max_passes=64):
+        depth = _f32(depth)
+        return self.lib.vo_set_view_converged(self.h, _ptr(depth), depth.shape[1], depth.shape[0],
+                                              _ptr(_f32(proj4)), _ptr(_f32(T32)), max_passes)
+
+    def integrate_depth(self, depth, proj4, T32, dmin=0.1, dmax=5.0, max_w=16.0):
+        depth = _f32(depth)
+        self.lib.vo_integrate_depth(self.h, _ptr(depth), depth.shape[1], depth.shape[0], _ptr(_f32(proj4)),
+                                    _ptr(_f32(T32)), dmin, dmax, max_w)
+
+    def integrate_color(self, depth, dproj4, T32, color, cproj4, Tcd32, dmin=0.1, dmax=5.0, max_w=16.0,
+                        max_cw=16.0):
+        depth, color = _f32(depth), _f32(color)
+        self.lib.vo_integrate_color(self.h, _ptr(depth), depth.shape[1], depth.shape[0], _ptr(_f32(dproj4)),
+                                    _ptr(_f32(T32)), _ptr(color), color.shape[1], color.shape[0],
+                                    _ptr(_f32(cproj4)), _ptr(_f32(Tcd32)), dmin, dmax, max_w, max_cw)
+
+    def integrate_light(self, depth, dproj4, T32, color, normal, cproj4, Tcd32, intensity, light_pos,
+                        dmin=0.1, dmax=5.0, max_w=16.0, max_cw=16.0, depth_threshold=0.2):
+        depth, color, normal = _f32(depth), _f32(color), _f32(normal)
+        mask = np.zeros(depth.shape, dtype=np.float32)
+        self.lib.vo_integrate_light(self.h, _ptr(depth), depth.shape[1], depth.shape[0], _ptr(_f32(dproj4)),
+                                    _ptr(_f32(T32)), _ptr(color), _ptr(normal), _ptr(_f32(cproj4)),
+                                    _ptr(_f32(Tcd32)), dmin, dmax, max_w, max_cw, intensity,
+                                    _ptr(_f32(light_pos)), depth_threshold, _ptr(mask))
+        return mask
+
+    def trace(self, w, h, proj4, T32, dmin=0.1, dmax=5.0, normals=True):
+        bounds = np.zeros((60, 80, 2), dtype=np.float32)
+        depth = np.zeros((h, w), dtype=np.float32)
+        color = np.zeros((h, w, 3), dtype=np.float32)
+        normal = np.zeros((h, w, 3), dtype=np.float32) if normals else None
+        self.lib.vo_trace(self.h, _ptr(_f32(T32)), _ptr(_f32(proj4)), w, h, dmin, dmax, _ptr(bounds), _ptr(depth),
+                          _ptr(color), _ptr(normal) if normals else None)
+        return depth, color, normal, bounds
+
+    def fetch_counts(self):
+        return self.lib.vo_voxel_fetches(self.h), self.lib.vo_entry_fetches(self.h)
+
+    # zero-copy numpy views of the oracle's state
+    def entries(self):
+        buf = (C.c_int32 * (self.B * 4)).from_address(self.lib.vo_entries(self.h))
+        return np.frombuffer(buf, dtype=np.int32).reshape(self.B, 4)
+
+    def voxels(self):
+        buf = (C.c_int32 * (self.B * 512 * 5)).from_address(self.lib.vo_voxels(self.h))
+        return np.frombuffer(buf, dtype=np.int32).reshape(self.B * 512, 5)
+
+    def visibility(self):
+        buf = (C.c_uint8 * self.B).from_address(self.lib.vo_visibility(self.h))
+        return np.frombuffer(buf, dtype=np.uint8)
+
+    def visible(self):
+        n = self.lib.vo_visible_count(self.h)
+        if n == 0:
+            return np.zeros((0,), dtype=np.int32)
+        buf = (C.c_int32 * n).from_address(self.lib.vo_visible(self.h))
+        return np.frombuffer(buf, dtype=np.int32).copy()
+
+    def dropped(self):
+        return self.lib.vo_dropped(self.h)
+
+
+def have_ref(nofmad=False):
+    return os.path.exists(REF_LIB_NOFMAD if nofmad else REF_LIB)
+
+
+_ref_libs = {}
+
+
+def ref_lib(nofmad=False):
+    path = REF_LIB_NOFMAD if nofmad else REF_LIB
+    if path not in _ref_libs:
+        lib = C.CDLL(path)
+        lib.ref_create.restype = _P
+        lib.ref_create.argtypes = [_I, _I, _F, _F, _F, _F]
+        lib.ref_destroy.argtypes = [_P]
+        lib.ref_set_ranges.argtypes = [_P, _F, _F, _F, _F, _F, _F]
+        lib.ref_set_light.argtypes = [_P, _F, _F, _F, _F]
+        lib.ref_set_frame.argtypes = [_P, _P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _P]
+        lib.ref_set_frame_device.argtypes = [_P, _P, _I, _I, _P, _P]
+        lib.ref_compute_input_normals.argtypes = [_P]
+        lib.ref_set_view.argtypes = [_P]
+        lib.ref_integrate.argtypes = [_P, _I]
+        lib.ref_trace.argtypes = [_P, _I, _I, _P, _P]
+        lib.ref_device_ptr.restype = _P
+        lib.ref_device_ptr.argtypes = [_P, _I]
+        lib.ref_visible_count.argtypes = [_P]
+        lib.ref_download.argtypes = [_P, _P, C.c_size_t]
+        _ref_libs[path] = lib
+    return _ref_libs[path]
+
+
+class RefVolume:
+    """The reference's own classes (Volume + integrators + Tracer) on the GPU.  Only one
+    instance may be alive per library at a time: the reference keeps its allocator counters
+    in translation-unit __device__ globals (Q8)."""
+
+    def __init__(self, main_blocks, excess_blocks, voxel_length=0.008, trunc_length=0.04, min_depth=0.1,
+                 max_depth=5.0, nofmad=False):
+        self.lib = ref_lib(nofmad)
+        self.M, self.E, self.B = main_blocks, excess_blocks, main_blocks + excess_blocks
+        self.h = self.lib.ref_create(main_blocks, excess_blocks, voxel_length, trunc_length, min_depth, max_depth)
+        if not self.h:
+            raise RuntimeError("ref_create failed")
+        self.w = self.hgt = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ref_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def set_ranges(self, imin=0.1, imax=5.0, max_dw=16.0, max_cw=16.0, tmin=0.1, tmax=5.0):
+        self.lib.ref_set_ranges(self.h, imin, imax, max_dw, max_cw, tmin, tmax)
+
+    def set_light(self, intensity, pos):
+        self.lib.ref_set_light(self.h, intensity, pos[0], pos[1], pos[2])
+
+    def set_frame(self, depth, dproj4, T32, color=None, cproj4=None, Tcd32=None, normal=None):
+        depth = _f32(depth)
+        self.hgt, self.w = depth.shape
+        color = _f32(color) if color is not None else None
+        normal = _f32(normal) if normal is not None else None
+        rc = self.lib.ref_set_frame(self.h, _ptr(depth), self.w, self.hgt,
+                                    _ptr(color) if color is not None else None,
+                                    color.shape[1] if color is not None else 0,
+                                    color.shape[0] if color is not None else 0,
+                                    _ptr(normal) if normal is not None else None, _ptr(_f32(dproj4)),
+                                    _ptr(_f32(cproj4)) if cproj4 is not None else None, _ptr(_f32(T32)),
+                                    _ptr(_f32(Tcd32)) if Tcd32 is not None else None)
+        assert rc == 0, rc
+
+    def set_frame_device(self, depth_ptr, w, h, dproj4, T32):
+        self.w, self.hgt = w, h
+        rc = self.lib.ref_set_frame_device(self.h, depth_ptr, w, h, _ptr(_f32(dproj4)), _ptr(_f32(T32)))
+        assert rc == 0, rc
+
+    def compute_input_normals(self):
+        assert self.lib.ref_compute_input_normals(self.h) == 0
+
+    def set_view(self):
+        n = self.lib.ref_set_view(self.h)
+        assert n >= 0
+        return n
+
+    def set_view_converged(self, max_passes=64):
+        """SetView until the visible count stops changing (tests/tracer_test.cu:298-303), then
+        once more so that the last pass is a pass at the fixed point."""
+        prev = -1
+        passes = 0
+        while passes < max_passes:
+            n = self.set_view()
+            passes += 1
+            if n == prev:
+                break
+            prev = n
+        return passes
+
+    def integrate(self, kind=0):
+        assert self.lib.ref_integrate(self.h, kind) == 0
+
+    def trace(self, w, h, dproj4, T32):
+        assert self.lib.ref_trace(self.h, w, h, _ptr(_f32(dproj4)), _ptr(_f32(T32))) == 0
+
+    def ptr(self, which):
+        return self.lib.ref_device_ptr(self.h, which)
+
+    def visible_count(self):
+        return self.lib.ref_visible_count(self.h)
+
+    def tensor(self, which, shape, typestr):
+        from vulcan_b200.api import device_view
+        return device_view(self.ptr(which), shape, typestr)
+
+    def entries(self):
+        return self.tensor(0, (self.B, 4), "<i4")
+
+    def voxels(self):
+        return self.tensor(1, (self.B * 512, 5), "<i4")
+
+    def visibility(self):
+        return self.tensor(2, (self.B,), "|u1")
+
+    def visible(self):
+        return self.tensor(3, (self.B,), "<i4")[: self.visible_count()]
+
+    def traced(self, w, h):
+        return (self.tensor(4, (h, w), "<f4"), self.tensor(5, (h, w, 3), "<f4"), self.tensor(6, (h, w, 3), "<f4"))
+
+
+# ---- comparisons by block coordinate (numpy or torch tensors alike) ---------------------
+
+def entry_keys(entries):
+    """int64 key per entry from the packed coordinates (x | y<<16, z) of an (N,4) int32 table."""
+    e0 = entries[:, 0].astype(np.int64) & 0xFFFFFFFF
+    e1 = entries[:, 1].astype(np.int64) & 0xFFFF
+    return e0 | (e1 << 32)
+
+
+def allocated_table(entries):
+    """(sorted keys, data ids in the same order) of the allocated entries (numpy)."""
+    entries = np.asarray(entries)
+    mask = entries[:, 2] != -1
+    keys = entry_keys(entries[mask])
+    order = np.argsort(keys, kind="stable")
+    return keys[order], entries[mask][order, 2], np.nonzero(mask)[0][order]
+
+
+def visible_keys(entries, visible):
+    entries = np.asarray(entries)
+    return np.sort(entry_keys(entries[np.asarray(visible)]))
+
+
+def gather_blocks(voxels, data_ids):
+    """(n, 512, 5) int32 voxel words of the given voxel-block ids."""
+    return np.asarray(voxels).reshape(-1, 512, 5)[np.asarray(data_ids)]
+
+
+def split_voxels(words):
+    """(..., 5) int32 words -> distance, rgb, distance_weight, color_weight."""
+    words = np.ascontiguousarray(words)
+    dist = words[..., 0].view(np.float32)
+    rgb = words[..., 1:4].view(np.float32)
+    w = words[..., 4]
+    dw = (w & 0xFFFF).astype(np.int16)
+    cw = ((w >> 16) & 0xFFFF).astype(np.int16)
+    return dist, rgb, dw, cw
+
+
+# ---- scenario runners ------------------------------------------------------------------
+
+def _load_synth():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("vk_synth", os.path.join(ROOT, "vulcan_b200", "synth.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+synth = _load_synth()
+
+
+def raw32(R, t):
+    """Byte image of vulcan::Transform for a rigid pose (float64 R, t rounded once)."""
+    m = np.eye(4)
+    m[:3, :3] = R
+    m[:3, 3] = t
+    i = np.eye(4)
+    i[:3, :3] = np.asarray(R).T
+    i[:3, 3] = -np.asarray(R).T @ np.asarray(t)
+    return np.concatenate([m.T.reshape(-1), i.T.reshape(-1)]).astype(np.float32)
+
+
+def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2):
+    """Sphere-on-plane scenarios.  frames = orbit indices."""
+    cfg = {
+        "tiny": dict(w=64, h=48, voxel=0.016, M=4096, E=1024),
+        "small": dict(w=160, h=120, voxel=0.008, M=32768, E=8192),
+        "c1": dict(w=640, h=480, voxel=0.004, M=262144, E=65536),
+        "c3": dict(w=1280, h=720, voxel=0.004, M=262144, E=65536),
+    }[name]
+    w, h = cfg["w"], cfg["h"]
+    K = synth.intrinsics(w, h)
+    scn = dict(cfg, name=name, mode=mode, K=np.array(K, dtype=np.float32), trunc=5 * cfg["voxel"], frames=[])
+    for k in frames:
+        if k == 0 and step_deg == 1.2:
+            R, t = np.eye(3), np.zeros(3)   # C1: identity pose
+        else:
+            R, t = synth.orbit_pose(k, step_deg=step_deg)
+        if mode == "depth":
+            depth, color = synth.render_sphere_plane(w, h, K, R, t), None
+        else:
+            depth, color = synth.render_sphere_plane(w, h, K, R, t, with_color=True)
+        scn["frames"].append(dict(depth=depth, color=color, T=raw32(R, t)))
+    # depth -> colour camera: 25 mm baseline (App. D, C3)
+    scn["Tcd"] = raw32(np.eye(3), np.array([0.025, 0.0, 0.0]))
+    scn["light"] = (2.0, (0.025, 0.08, 0.0))
+    return scn
+
+
+def _pack_result(entries, voxels, visibility, visible, traced):
+    keys, data, idx = allocated_table(entries)
+    return dict(keys=keys, voxels=gather_blocks(voxels, data), vis_flags=np.asarray(visibility)[idx],
+                visible_keys=visible_keys(entries, visible), depth=traced[0], color=traced[1], normal=traced[2])
+
+
+def run_oracle(scn):
+    ov = OracleVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"])
+    K = scn["K"]
+    for fr in scn["frames"]:
+        ov.set_view_converged(fr["depth"], K, fr["T"])
+        if scn["mode"] == "depth":
+            ov.integrate_depth(fr["depth"], K, fr["T"])
+        elif scn["mode"] == "color":
+            ov.integrate_color(fr["depth"], K, fr["T"], fr["color"], K, scn["Tcd"])
+        else:
+            nrm = np.zeros(fr["depth"].shape + (3,), dtype=np.float32)
+            ov.lib.vo_compute_normals(_ptr(_f32(fr["depth"])), _ptr(_f32(K)), _ptr(nrm), scn["w"], scn["h"])
+            ov.integrate_light(fr["depth"], K, fr["T"], fr["color"], nrm, K, scn["Tcd"], scn["light"][0],
+                               np.array(scn["light"][1], dtype=np.float32))
+    last = scn["frames"][-1]
+    d, c, n, _ = ov.trace(scn["w"], scn["h"], K, last["T"])
+    res = _pack_result(ov.entries(), ov.voxels(), ov.visibility(), ov.visible(), (d, c, n))
+    res["fetches"] = ov.fetch_counts()
+    assert ov.dropped() == 0
+    return res
+
+
+def run_ref(scn, nofmad=False):
+    rv = RefVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"], nofmad=nofmad)
+    try:
+        K = scn["K"]
+        kind = {"depth": 0, "color": 1, "light": 2}[scn["mode"]]
+        rv.set_light(*scn["light"])
+        for fr in scn["frames"]:
+            rv.set_frame(fr["depth"], K, fr["T"], color=fr["color"], cproj4=K, Tcd32=scn["Tcd"])
+            if kind == 2:
+                rv.compute_input_normals()
+            rv.set_view_converged()
+            rv.integrate(kind)
+        last = scn["frames"][-1]
+        rv.trace(scn["w"], scn["h"], K, last["T"])
+        d, c, n = rv.traced(scn["w"], scn["h"])
+        entries = rv.entries().cpu().numpy()
+        keys, data, idx = allocated_table(entries)
+        import torch
+        vox = rv.voxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy()
+        return dict(keys=keys, voxels=vox, vis_flags=rv.visibility().cpu().numpy()[idx],
+                    visible_keys=visible_keys(entries, rv.visible().cpu().numpy()), depth=d.cpu().numpy(),
+                    color=c.cpu().numpy(), normal=n.cpu().numpy())
+    finally:
+        rv.close()
+
+
+def run_ours(scn, shard=None):
+    import torch
+    import vulcan_b200 as vb
+    vol = vb.Volume(scn["M"], scn["E"])
+    vol.SetVoxelLength(scn["voxel"])
+    vol.SetTruncationLength(scn["trunc"])
+    if shard:
+        vol.SetSharding(*shard)
+    integ = {"depth": vb.DepthIntegrator, "color": vb.ColorIntegrator, "light": vb.LightIntegrator}[scn["mode"]](vol)
+    if scn["mode"] == "light":
+        integ.SetLight(*scn["light"])
+    tracer = vb.Tracer(vol)
+    K = scn["K"]
+
+    def transform(raw):
+        return vb.Transform(raw[:16].reshape(4, 4).T.copy(), raw[16:].reshape(4, 4).T.copy())
+
+    frame = vb.Frame()
+    for fr in scn["frames"]:
+        frame = vb.Frame()
+        frame.depth_projection = vb.Projection(*K)
+        frame.color_projection = vb.Projection(*K)
+        frame.depth_to_world_transform = transform(fr["T"])
+        frame.depth_to_color_transform = transform(scn["Tcd"])
+        frame.depth_image = torch.from_numpy(fr["depth"]).cuda()
+        if fr["color"] is not None:
+            frame.color_image = torch.from_numpy(fr["color"]).cuda()
+        if scn["mode"] == "light":
+            frame.ComputeNormals()
+        vol.SetView(frame)
+        integ.Integrate(frame)
+    out = vb.Frame()
+    out.depth_projection = frame.depth_projection
+    out.depth_to_world_transform = frame.depth_to_world_transform
+    out.depth_image = torch.zeros((scn["h"], scn["w"]), dtype=torch.float32, device="cuda")
+    tracer.Trace(out)
+    n_vis, counters = vol.SyncCounters()
+    assert counters[4] == 0, "pool overflow"
+    entries = vol.GetHashEntries().cpu().numpy()
+    keys, data, idx = allocated_table(entries)
+    vox = vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy()
+    res = dict(keys=keys, voxels=vox, vis_flags=vol.GetBlockVisibility().cpu().numpy()[idx],
+               visible_keys=visible_keys(entries, vol.GetVisibleBlocks().cpu().numpy()),
+               depth=out.depth_image.cpu().numpy(), color=out.color_image.cpu().numpy(),
+               normal=out.normal_image.cpu().numpy(), counters=counters)
+    del vol
+    return res
+
+
+def compare(a, b, trunc):
+    """Parity report between two results (dicts of _pack_result)."""
+    rep = {}
+    rep["alloc_equal"] = bool(len(a["keys"]) == len(b["keys"]) and np.array_equal(a["keys"], b["keys"]))
+    rep["alloc_counts"] = (int(len(a["keys"])), int(len(b["keys"])))
+    rep["visible_equal"] = bool(len(a["visible_keys"]) == len(b["visible_keys"]) and
+                                np.array_equal(a["visible_keys"], b["visible_keys"]))
+    rep["visible_counts"] = (int(len(a["visible_keys"])), int(len(b["visible_keys"])))
+    if rep["alloc_equal"]:
+        rep["vis_flags_equal"] = bool(np.array_equal(a["vis_flags"], b["vis_flags"]))
+        da, ca, dwa, cwa = split_voxels(a["voxels"])
+        db, cb, dwb, cwb = split_voxels(b["voxels"])
+        rep["voxels"] = int(da.size)
+        rep["dw_mismatch"] = int((dwa != dwb).sum())
+        rep["cw_mismatch"] = int((cwa != cwb).sum())
+        rep["dist_bits_mismatch"] = int((a["voxels"][..., 0] != b["voxels"][..., 0]).sum())
+        same_w = dwa == dwb
+        rep["dist_max_abs"] = float(np.abs(da - db)[same_w].max()) if same_w.any() else 0.0
+        rep["color_bits_mismatch"] = int((a["voxels"][..., 1:4] != b["voxels"][..., 1:4]).sum())
+        same_c = cwa == cwb
+        rep["color_max_abs"] = float(np.abs(ca - cb)[same_c].max()) if same_c.any() else 0.0
+    ha, hb = a["depth"] > 0, b["depth"] > 0
+    both = ha & hb
+    rep["hit_mismatch_frac"] = float((ha != hb).mean())
+    rep["depth_bits_mismatch"] = int((a["depth"].view(np.int32) != b["depth"].view(np.int32)).sum())
+    rep["depth_max_abs_mm"] = float(np.abs(a["depth"] - b["depth"])[both].max() * 1000) if both.any() else 0.0
+    rep["depth_gt_half_mm_frac"] = float((np.abs(a["depth"] - b["depth"])[both] > 0.0005).mean()) if both.any() else 0.0
+    rep["color_img_max_abs"] = float(np.abs(a["color"] - b["color"]).max())
+    rep["normal_img_max_abs"] = float(np.abs(a["normal"] - b["normal"])[both].max()) if both.any() else 0.0
+    rep["normal_bits_mismatch"] = int((a["normal"].view(np.int32) != b["normal"].view(np.int32)).sum())
+    return rep

@@ -1,0 +1,384 @@
+"""Host-side mirror of the reference's public interface for the TSDF-fusion hot path,
+over the C ABI (include/vulcan_b200.h).  Same class and method names, argument meaning
+and error behaviour as the reference's C++ classes:
+
+  Volume            include/vulcan/volume.h:16-117
+  Integrator etc.   include/vulcan/integrator.h:16-34, depth_/color_/light_integrator.h
+  Tracer            include/vulcan/tracer.h:24-76
+  Frame             include/vulcan/frame.h:11-32
+  Transform         include/vulcan/transform.h:9-171
+  Projection        include/vulcan/projection.h:11-114
+
+The C++ drop-in headers (include/vulcan/*.h) wrap the same C ABI; this module is what the
+parity tests and bench.py use.  torch supplies device memory for images and the stream.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check, VulcanError  # noqa: F401
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _DevView:
+    """Zero-copy torch view of library-owned device memory."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {
+            "shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2, "strides": None}
+
+
+def device_view(ptr, shape, typestr):
+    if int(np.prod(shape)) == 0:
+        dt = {"<i4": torch.int32, "|u1": torch.uint8, "<f4": torch.float32, "<i2": torch.int16}[typestr]
+        return torch.empty(tuple(shape), dtype=dt, device="cuda")
+    return torch.as_tensor(_DevView(ptr, shape, typestr), device="cuda")
+
+
+class Transform:
+    """Column-major 4x4 matrix plus its cached inverse (include/vulcan/transform.h:166-170)."""
+
+    def __init__(self, matrix=None, inv_matrix=None):
+        self.matrix = np.eye(4, dtype=np.float32) if matrix is None else np.asarray(matrix, dtype=np.float32)
+        self.inv_matrix = np.eye(4, dtype=np.float32) if inv_matrix is None else np.asarray(inv_matrix, dtype=np.float32)
+
+    @staticmethod
+    def Translate(x, y, z):
+        m = np.eye(4, dtype=np.float32)
+        m[:3, 3] = (x, y, z)
+        i = np.eye(4, dtype=np.float32)
+        i[:3, 3] = (-np.float32(x), -np.float32(y), -np.float32(z))
+        return Transform(m, i)
+
+    @staticmethod
+    def Rotate(R):
+        m = np.eye(4, dtype=np.float32)
+        m[:3, :3] = np.asarray(R, dtype=np.float32)
+        return Transform(m, m.T.copy())
+
+    @staticmethod
+    def FromRt(R, t):
+        """Rigid transform from float64 R, t; matrix and inverse each rounded once to float32."""
+        R = np.asarray(R, dtype=np.float64)
+        t = np.asarray(t, dtype=np.float64)
+        m = np.eye(4)
+        m[:3, :3] = R
+        m[:3, 3] = t
+        i = np.eye(4)
+        i[:3, :3] = R.T
+        i[:3, 3] = -R.T @ t
+        return Transform(m.astype(np.float32), i.astype(np.float32))
+
+    def Inverse(self):
+        return Transform(self.inv_matrix, self.matrix)
+
+    def __mul__(self, other):
+        # Transform::operator*(Transform) (include/vulcan/transform.h:61-64), float32 accumulate
+        return Transform(_matmul4(self.matrix, other.matrix), _matmul4(other.inv_matrix, self.inv_matrix))
+
+    def raw32(self):
+        """32 floats: column-major matrix then inverse (byte image of vulcan::Transform)."""
+        return np.concatenate([self.matrix.T.reshape(-1), self.inv_matrix.T.reshape(-1)]).astype(np.float32)
+
+    def to_c(self):
+        t = _lib.vkTransform()
+        raw = self.raw32()
+        for k in range(16):
+            t.m[k] = raw[k]
+            t.inv[k] = raw[16 + k]
+        return t
+
+
+def _matmul4(a, b):
+    out = np.zeros((4, 4), dtype=np.float32)
+    for p in range(4):
+        for m in range(4):
+            acc = np.float32(0)
+            for n in range(4):
+                acc = np.float32(acc + np.float32(a[m, n] * b[n, p]))
+            out[m, p] = acc
+    return out
+
+
+class Projection:
+    """Pinhole intrinsics; defaults as include/vulcan/projection.h:16-20."""
+
+    def __init__(self, fx=500.0, fy=500.0, cx=320.0, cy=240.0):
+        self.fx, self.fy, self.cx, self.cy = (float(np.float32(v)) for v in (fx, fy, cx, cy))
+
+    def raw4(self):
+        return np.array([self.fx, self.fy, self.cx, self.cy], dtype=np.float32)
+
+    def to_c(self):
+        return _lib.vkProjection(self.fx, self.fy, self.cx, self.cy)
+
+
+class Frame:
+    """include/vulcan/frame.h:11-32; images are CUDA float32 tensors (H,W) / (H,W,3)."""
+
+    def __init__(self):
+        self.depth_projection = Projection()
+        self.color_projection = Projection()
+        self.depth_to_world_transform = Transform()
+        self.depth_to_color_transform = Transform()
+        self.depth_image = None
+        self.color_image = None
+        self.normal_image = None
+
+    def to_c(self):
+        if self.depth_image is None:
+            raise VulcanError("missing depth image")  # frame.cpp:10,23
+        f = _lib.vkFrame()
+        d = self.depth_image
+        assert d.is_cuda and d.dtype == torch.float32 and d.is_contiguous()
+        f.depth = d.data_ptr()
+        f.depth_h, f.depth_w = d.shape[0], d.shape[1]
+        if self.color_image is not None:
+            c = self.color_image
+            assert c.is_cuda and c.dtype == torch.float32 and c.is_contiguous()
+            f.color = c.data_ptr()
+            f.color_h, f.color_w = c.shape[0], c.shape[1]
+        if self.normal_image is not None:
+            f.normal = self.normal_image.data_ptr()
+        f.depth_proj = self.depth_projection.to_c()
+        f.color_proj = self.color_projection.to_c()
+        f.depth_to_world = self.depth_to_world_transform.to_c()
+        f.depth_to_color = self.depth_to_color_transform.to_c()
+        return f
+
+    def ComputeNormals(self):
+        """Frame::ComputeNormals (src/frame.cpp:21-36)."""
+        if self.depth_image is None:
+            raise VulcanError("missing depth image")
+        h, w = self.depth_image.shape
+        if self.normal_image is None or tuple(self.normal_image.shape) != (h, w, 3):
+            self.normal_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+        p = self.depth_projection.to_c()
+        check(lib.vk_compute_normals(self.depth_image.data_ptr(), C.byref(p), self.normal_image.data_ptr(), w, h,
+                                     _stream()), "ComputeNormals")
+
+    def FilterDepths(self):
+        """Frame::FilterDepths (src/frame.cpp:8-19)."""
+        if self.depth_image is None:
+            raise VulcanError("missing depth image")
+        h, w = self.depth_image.shape
+        tmp = torch.empty_like(self.depth_image)
+        check(lib.vk_filter_depths(w, h, self.depth_image.data_ptr(), tmp.data_ptr(), _stream()), "FilterDepths")
+        self.depth_image.copy_(tmp)
+
+
+class Volume:
+    """vulcan::Volume (include/vulcan/volume.h:16-117, src/volume.cu:370-463)."""
+
+    def __init__(self, main_block_count, excess_block_count):
+        self._v = _lib.vkVolume()
+        check(lib.vk_volume_create(C.byref(self._v), int(main_block_count), int(excess_block_count), _stream()),
+              "Volume")
+        self._alive = True
+
+    def __del__(self):
+        if getattr(self, "_alive", False):
+            lib.vk_volume_destroy(C.byref(self._v))
+            self._alive = False
+
+    def GetMainBlockCount(self):
+        return self._v.main_blocks
+
+    def GetExcessBlockCount(self):
+        return self._v.excess_blocks
+
+    def GetDepthRange(self):
+        return (self._v.min_depth, self._v.max_depth)
+
+    def SetDepthRange(self, dmin, dmax):
+        self._v.min_depth, self._v.max_depth = dmin, dmax
+
+    def GetVoxelLength(self):
+        return self._v.voxel_length
+
+    def SetVoxelLength(self, length):
+        self._v.voxel_length = length
+
+    def GetTruncationLength(self):
+        return self._v.trunc_length
+
+    def SetTruncationLength(self, length):
+        self._v.trunc_length = length
+
+    def SetSharding(self, rank, count, shift=3):
+        self._v.shard_rank, self._v.shard_count, self._v.shard_shift = rank, count, shift
+
+    def Reset(self):
+        check(lib.vk_volume_reset(C.byref(self._v), _stream()), "Volume.Reset")
+
+    def SetView(self, frame):
+        """One call reaches the fixed point of repeated reference SetView calls."""
+        f = frame.to_c()
+        check(lib.vk_set_view(C.byref(self._v), C.byref(f), _stream()), "SetView")
+
+    def SyncCounters(self):
+        n = C.c_int(0)
+        rc = lib.vk_volume_sync_counters(C.byref(self._v), C.byref(n), _stream())
+        if rc != 0 and rc != _lib.VK_E_OVERFLOW:
+            check(rc, "SyncCounters")
+        return n.value, [self._v.host_counters[i] for i in range(_lib.VK_CNT_COUNT)]
+
+    def GetVisibleCount(self):
+        return self.SyncCounters()[0]
+
+    def GetAllocatedBlocks(self):
+        raise VulcanError("not implemented")  # Q21, src/volume.cu:444-448
+
+    @property
+    def _B(self):
+        return self._v.main_blocks + self._v.excess_blocks
+
+    def GetVisibleBlocks(self):
+        n = self.GetVisibleCount()
+        return device_view(self._v.visible[self._v.visible_slot], (self._B,), "<i4")[:n]
+
+    def GetHashEntries(self):
+        """(B, 4) int32 view: [x | y<<16, z | pad<<16, data, next]."""
+        return device_view(self._v.entries, (self._B, 4), "<i4")
+
+    def GetVoxels(self):
+        """(B*512, 5) int32 view of the 20-byte voxels: distance, r, g, b bits, dw | cw<<16."""
+        return device_view(self._v.voxels, (self._B * 512, 5), "<i4")
+
+    def GetBlockVisibility(self):
+        return device_view(self._v.visibility, (self._B,), "|u1")
+
+
+class Integrator:
+    """vulcan::Integrator (include/vulcan/integrator.h:16-45, src/integrator.cu:7-56)."""
+
+    def __init__(self, volume):
+        self.volume_ = volume
+        self.depth_range_ = (0.1, 5.0)
+        self.max_distance_weight_ = 16.0
+        self.max_color_weight_ = 16.0
+
+    def GetVolume(self):
+        return self.volume_
+
+    def GetDepthRange(self):
+        return self.depth_range_
+
+    def SetDepthRange(self, dmin, dmax):
+        self.depth_range_ = (dmin, dmax)
+
+    def GetMaxDistanceWeight(self):
+        return self.max_distance_weight_
+
+    def SetMaxDistanceWeight(self, weight):
+        self.max_distance_weight_ = float(weight)
+
+    def GetMaxColorWeight(self):
+        return self.max_color_weight_
+
+    def SetMaxColorWeight(self, weight):
+        self.max_color_weight_ = float(weight)
+
+    def Integrate(self, frame):
+        raise NotImplementedError
+
+
+class DepthIntegrator(Integrator):
+    def Integrate(self, frame):
+        f = frame.to_c()
+        check(lib.vk_integrate_depth(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0],
+                                     self.depth_range_[1], self.max_distance_weight_, _stream()), "Integrate")
+
+
+class ColorIntegrator(Integrator):
+    def Integrate(self, frame):
+        if frame.color_image is None:
+            raise VulcanError("missing color image")
+        f = frame.to_c()
+        check(lib.vk_integrate_color(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0],
+                                     self.depth_range_[1], self.max_distance_weight_, self.max_color_weight_,
+                                     _stream()), "Integrate")
+
+
+class LightIntegrator(Integrator):
+    def __init__(self, volume):
+        super().__init__(volume)
+        self.light_ = (1.0, (0.0, 0.0, 0.0))  # include/vulcan/light.h:16-20
+        self.depth_threshold_ = 0.2           # src/light_integrator.cu:254-258
+        self.frame_mask_ = None
+
+    def GetLight(self):
+        return self.light_
+
+    def SetLight(self, intensity, position):
+        self.light_ = (float(intensity), tuple(float(p) for p in position))
+
+    def Integrate(self, frame):
+        if frame.color_image is None or frame.normal_image is None:
+            raise VulcanError("missing color or normal image")
+        h, w = frame.depth_image.shape
+        if self.frame_mask_ is None or tuple(self.frame_mask_.shape) != (h, w):
+            self.frame_mask_ = torch.empty((h, w), dtype=torch.float32, device="cuda")
+        light = _lib.vkLight()
+        light.intensity = self.light_[0]
+        for k in range(3):
+            light.position[k] = self.light_[1][k]
+        f = frame.to_c()
+        check(lib.vk_integrate_light(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0],
+                                     self.depth_range_[1], self.max_distance_weight_, self.max_color_weight_,
+                                     C.byref(light), self.depth_threshold_, self.frame_mask_.data_ptr(), _stream()),
+              "Integrate")
+
+
+class Tracer:
+    """vulcan::Tracer (include/vulcan/tracer.h:24-76, src/tracer.cpp:13-147)."""
+
+    def __init__(self, volume):
+        self.volume_ = volume
+        self.depth_range_ = (0.1, 5.0)
+        self.bounds_ = torch.empty((_lib.BOUNDS_H, _lib.BOUNDS_W, 2), dtype=torch.float32, device="cuda")
+
+    def GetVolume(self):
+        return self.volume_
+
+    def GetDepthRange(self):
+        return self.depth_range_
+
+    def SetDepthRange(self, dmin, dmax):
+        self.depth_range_ = (dmin, dmax)
+
+    def Trace(self, frame):
+        """Overwrites frame.depth_image (must be pre-sized, src/tracer.cpp:83-84), resizes
+        color_image and creates normal_image like the reference (tracer.cpp:88, frame.cpp:25-28)."""
+        if frame.depth_image is None:
+            raise VulcanError("missing depth image")
+        h, w = frame.depth_image.shape
+        if frame.color_image is None or tuple(frame.color_image.shape) != (h, w, 3):
+            frame.color_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+        if frame.normal_image is None or tuple(frame.normal_image.shape) != (h, w, 3):
+            frame.normal_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+        f = frame.to_c()
+        check(lib.vk_trace(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0], self.depth_range_[1],
+                           self.bounds_.data_ptr(), frame.depth_image.data_ptr(), frame.color_image.data_ptr(),
+                           frame.normal_image.data_ptr(), _stream()), "Trace")
+
+    def TraceKeys(self, frame, keys):
+        f = frame.to_c()
+        check(lib.vk_trace_keys(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0], self.depth_range_[1],
+                                self.bounds_.data_ptr(), keys.data_ptr(), _stream()), "TraceKeys")
+
+    def ResolveKeys(self, frame, keys):
+        h, w = frame.depth_image.shape
+        if frame.color_image is None or tuple(frame.color_image.shape) != (h, w, 3):
+            frame.color_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+        if frame.normal_image is None or tuple(frame.normal_image.shape) != (h, w, 3):
+            frame.normal_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+        f = frame.to_c()
+        check(lib.vk_resolve_keys(keys.data_ptr(), C.byref(f), frame.depth_image.data_ptr(),
+                                  frame.color_image.data_ptr(), frame.normal_image.data_ptr(), _stream()),
+              "ResolveKeys")

@@ -28,6 +28,7 @@ struct IntegrateParams {
   const float* color;
   const float* normal;
   const float* mask;
+  unsigned long long* updated;  // counters[VK_CNT_UPDATED..+1]: voxels written since reset
   int dw, dh, cw, ch;
   vkProjection dproj, cproj;
   float Tdw[12], Tcw[12], Tcd[12];
@@ -51,6 +52,7 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
   Mat34 Tdw, Tcw;
   load_rows(Tdw, p.Tdw);
   if (MODE != MODE_DEPTH) load_rows(Tcw, p.Tcw);
+  unsigned n_updated = 0;
 
   for (int bi = blockIdx.x; bi < n; bi += gridDim.x) {
     const int e = __ldg(p.visible + bi);
@@ -186,7 +188,11 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
     for (int c = 0; c < 5; ++c) {
       if ((dirty >> (4 * c)) & 0xfu) tile[c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
     }
+    // voxels written = voxels whose weight word is dirty (bit 5k+4)
+    n_updated += __popc(dirty & 0x84210u);
   }
+  n_updated = __reduce_add_sync(0xffffffffu, n_updated);
+  if ((threadIdx.x & 31) == 0 && n_updated) atomicAdd(p.updated, (unsigned long long)n_updated);
 }
 
 // ComputeFrameMaskKernel<16,3> (src/light_integrator.cu:17-103) including Q14: the
@@ -259,6 +265,7 @@ static int fill_params(IntegrateParams& p, vkVolume* v, const vkFrame* f, float 
   p.color = f->color;
   p.normal = f->normal;
   p.mask = nullptr;
+  p.updated = reinterpret_cast<unsigned long long*>(v->counters + VK_CNT_UPDATED);
   p.dw = f->depth_w; p.dh = f->depth_h; p.cw = f->color_w; p.ch = f->color_h;
   p.dproj = f->depth_proj;
   p.cproj = f->color_proj;
