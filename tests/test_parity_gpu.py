@@ -39,9 +39,33 @@ def _assert_exact(rep, what):
     assert rep["color_img_max_abs"] == 0.0, (what, rep)
 
 
+def _ref_extras(rep):
+    """Blocks only the reference allocated (torn request writes, Q24: they differ between two
+    runs of the reference itself) - never more than a handful."""
+    extras = rep["alloc_only_b"] + rep["alloc_dup_b"]
+    assert rep["alloc_only_a"] == 0 and rep["alloc_dup_a"] == 0, rep
+    assert extras <= max(4, rep["alloc_counts"][0] // 500), rep
+    assert rep["visible_only_a"] == 0 and rep["visible_only_b_known"] == 0, rep
+    return extras
+
+
+def _assert_exact_ref(rep, what):
+    """Bit-exact on everything the reference computes deterministically."""
+    extras = _ref_extras(rep)
+    assert rep["vis_flags_equal"], (what, rep)
+    assert rep["dw_mismatch"] == 0 and rep["cw_mismatch"] == 0, (what, rep)
+    assert rep["dist_bits_mismatch"] == 0 and rep["color_bits_mismatch"] == 0, (what, rep)
+    if extras == 0:
+        assert rep["alloc_equal"] and rep["visible_equal"], (what, rep)
+        assert rep["depth_bits_mismatch"] == 0 and rep["normal_bits_mismatch"] == 0, (what, rep)
+        assert rep["color_img_max_abs"] == 0.0, (what, rep)
+    else:  # rays crossing a phantom block of the reference step differently
+        assert rep["hit_mismatch_frac"] <= 1e-3 and rep["depth_gt_half_mm_frac"] <= 1e-3, (what, rep)
+        assert rep["depth_bits_mismatch"] <= 64 * extras + 0.002 * rep["pixels"], (what, rep)
+
+
 def _assert_tolerance(rep, what):
-    assert rep["alloc_equal"], (what, rep)
-    assert rep["visible_equal"], (what, rep)
+    _ref_extras(rep)
     # knife-edge voxels may flip under FMA contraction; weights of all others are equal
     assert rep["dw_mismatch"] <= 1e-4 * rep["voxels"], (what, rep)
     assert rep["dist_max_abs"] <= 1e-4, (what, rep)
@@ -78,7 +102,7 @@ def test_ours_vs_reference_nofmad_exact(name, frames, mode, step):
     ref = H.run_ref(scn, nofmad=True)
     rep = H.compare(ours, ref, scn["trunc"])
     _dump("refnofmad_%s_%s_%d_%g" % (name, mode, len(frames), step), rep)
-    _assert_exact(rep, "ours vs reference (-fmad=false)")
+    _assert_exact_ref(rep, "ours vs reference (-fmad=false)")
 
 
 @pytest.mark.parametrize("name,frames,mode,step", SCENARIOS)
@@ -100,7 +124,7 @@ def test_c1_full_size_vs_reference():
     ref = H.run_ref(scn, nofmad=True)
     rep = H.compare(ours, ref, scn["trunc"])
     _dump("refnofmad_c1", rep)
-    _assert_exact(rep, "c1 ours vs reference (-fmad=false)")
+    _assert_exact_ref(rep, "c1 ours vs reference (-fmad=false)")
     ref2 = H.run_ref(scn)
     rep2 = H.compare(ours, ref2, scn["trunc"])
     _dump("ref_c1", rep2)
