@@ -31,6 +31,12 @@ extern "C" {
                              /* the reference drops such requests silently,         */
                              /* src/volume.cu:338-356)                              */
 
+/* vkVolume::math_mode: where float multiply-adds round.                               */
+#define VK_MATH_REFERENCE 0  /* fused exactly where nvcc's default -fmad=true fuses them  */
+                             /* in the reference's release build (bit-exact with it)      */
+#define VK_MATH_STRICT    1  /* one rounding per source operation (reference built with   */
+                             /* -fmad=false; the CPU oracle's strict mode)                */
+
 #define VK_BLOCK_RES     8      /* Block::resolution, include/vulcan/block.h:13    */
 #define VK_BLOCK_VOXELS  512    /* Block::voxel_count, include/vulcan/block.h:15   */
 #define VK_BOUNDS_W      80     /* hard coded in src/tracer.cpp:56                 */
@@ -118,7 +124,7 @@ typedef struct vkVolume {
   int32_t      shard_shift;   /* log2 of the brick edge in blocks                   */
   int32_t      visible_slot;  /* which of visible[] / VK_CNT_VISIBLE* is current    */
   int32_t      view_id;       /* number of vk_set_view calls so far                 */
-  int32_t      reserved;
+  int32_t      math_mode;     /* VK_MATH_REFERENCE (default) or VK_MATH_STRICT       */
 } vkVolume;
 
 /* One RGB-D frame on the device.  Replaces vulcan::Frame
@@ -232,6 +238,19 @@ int vk_filter_depths(int image_w, int image_h, const float* src, float* dst, voi
  * (used by bench.py's gpu_launches). */
 int vk_version(void);
 unsigned long long vk_launch_count(void);
+
+/* Math mode used by the entry points that take no vkVolume (vk_compute_normals,
+ * vk_filter_depths, vk_compute_frame_mask, the step-wise tracer functions) and copied into
+ * vkVolume::math_mode by vk_volume_create.  Plain host configuration, no device state. */
+int vk_set_default_math_mode(int mode);
+int vk_get_default_math_mode(void);
+
+/* Division by loop-invariant divisors (block length, voxel length, truncation length, image
+ * size) uses a reciprocal + one FMA residual step instead of the IEEE division sequence, after
+ * the library has checked on the device, for that divisor, that the result equals __fdiv_rn for
+ * all 2^32 dividends (cached per value).  Returns 1 if the fast path is proven for d, 0 if the
+ * library will use plain IEEE division for it. */
+int vk_div_prepare(float d, void* stream);
 
 #ifdef __cplusplus
 }

@@ -6,8 +6,14 @@
 // baseline.
 //
 // Each function restates one reference kernel with plain IEEE float arithmetic (build
-// with -ffp-contract=off: one rounding per source operation, in the reference's source
-// order) and cites the reference lines it follows (paths relative to /root/reference).
+// with -ffp-contract=off so that the compiler never fuses anything by itself) and cites the
+// reference lines it follows (paths relative to /root/reference).  Two arithmetic modes
+// (vo_set_math_mode), same association order in both:
+//   0  "reference": a*b+c pairs are fused (std::fmaf) exactly where nvcc 12.9 -O3 with its default
+//      -fmad=true fuses them when it builds the reference's sources for sm_100a - the pattern
+//      was read off the SASS of that build (DESIGN.md "FMA map") and is pinned by the golden
+//      vectors in tests/golden/ (outputs of that build on a B200);
+//   1  "strict": one rounding per source operation (the reference built with -fmad=false).
 // The reference has no CPU implementation of this path and stores no golden vectors
 // (SURVEY.md 8c); parity of this oracle is pinned by running the reference's own CUDA
 // sources (oracle/_ref, built by oracle/build_ref.sh) on a B200 on identical inputs —
@@ -50,15 +56,31 @@ enum { ALLOC_NONE = 0, ALLOC_MAIN = 1, ALLOC_EXCESS = 2 };  // include/vulcan/ty
 
 struct V3 { float x, y, z; };
 
+int g_fma = 1;  // math mode 0 (reference contraction pattern) by default
+inline float mad(float a, float b, float c) { return g_fma ? std::fmaf(a, b, c) : a * b + c; }    // a*b + c
+inline float nmad(float a, float b, float c) { return g_fma ? std::fmaf(-a, b, c) : c - a * b; }  // c - a*b
+inline float msub(float a, float b, float c) { return g_fma ? std::fmaf(a, b, -c) : a * b - c; }  // a*b - c
+
 // column-major 4x4, include/vulcan/matrix.h:320-333
 inline float M(const float* m, int r, int c) { return m[c * 4 + r]; }
 
 // Transform::operator*(Vector4f), include/vulcan/transform.h:43-58
+// M(r,0)*x + M(r,1)*y + M(r,2)*z + M(r,3)*w, left to right.  Reference SASS: FMUL y*m1;
+// FFMA x*m0 + .; FFMA z*m2 + .; then FADD m3 (w == 1) or FFMA 0*m3 + . (w == 0).
+inline float row_acc(const float* m, int r, float x, float y, float z) {
+  return mad(z, M(m, r, 2), mad(x, M(m, r, 0), y * M(m, r, 1)));
+}
 inline V3 xform(const float* m, float x, float y, float z, float w) {
   V3 o;
-  o.x = M(m, 0, 0) * x + M(m, 0, 1) * y + M(m, 0, 2) * z + M(m, 0, 3) * w;
-  o.y = M(m, 1, 0) * x + M(m, 1, 1) * y + M(m, 1, 2) * z + M(m, 1, 3) * w;
-  o.z = M(m, 2, 0) * x + M(m, 2, 1) * y + M(m, 2, 2) * z + M(m, 2, 3) * w;
+  if (w == 1.0f) {
+    o.x = row_acc(m, 0, x, y, z) + M(m, 0, 3);
+    o.y = row_acc(m, 1, x, y, z) + M(m, 1, 3);
+    o.z = row_acc(m, 2, x, y, z) + M(m, 2, 3);
+  } else {  // w == 0
+    o.x = mad(0.0f, M(m, 0, 3), row_acc(m, 0, x, y, z));
+    o.y = mad(0.0f, M(m, 1, 3), row_acc(m, 1, x, y, z));
+    o.z = mad(0.0f, M(m, 2, 3), row_acc(m, 2, x, y, z));
+  }
   return o;
 }
 
@@ -67,8 +89,8 @@ struct Proj { float fx, fy, cx, cy; };
 // Projection::Project, include/vulcan/projection.h:63-71
 inline void project(const Proj& P, const V3& X, float& u, float& v) {
   const float inv_w = 1.0f / X.z;
-  u = inv_w * P.fx * X.x + P.cx;
-  v = inv_w * P.fy * X.y + P.cy;
+  u = mad(inv_w * P.fx, X.x, P.cx);   // FMUL inv_w*fx ; FFMA . * X.x + cx
+  v = mad(inv_w * P.fy, X.y, P.cy);
 }
 
 // Projection::Unproject, include/vulcan/projection.h:80-89
@@ -76,18 +98,18 @@ inline V3 unproject(const Proj& P, float u, float v) {
   const float ifx = 1.0f / P.fx;
   const float ify = 1.0f / P.fy;
   V3 o;
-  o.x = ifx * u - P.cx * ifx;
-  o.y = ify * v - P.cy * ify;
+  o.x = msub(ifx, u, P.cx * ifx);      // FMUL cx*ifx ; FFMA ifx*u - .
+  o.y = msub(ify, v, P.cy * ify);
   o.z = 1;
   return o;
 }
 
 // Matrix::Dot, include/vulcan/matrix.h:158-171
 inline float dot(const V3& a, const V3& b) {
-  float r = 0;
-  r += a.x * b.x;
-  r += a.y * b.y;
-  r += a.z * b.z;
+  float r = 0;                  // FFMA chain from 0
+  r = mad(a.x, b.x, r);
+  r = mad(a.y, b.y, r);
+  r = mad(a.z, b.z, r);
   return r;
 }
 
@@ -180,6 +202,10 @@ void vo_destroy(void* h) {
   delete v;
 }
 
+// 0 = reference contraction pattern (default), 1 = strict (one rounding per operation)
+void vo_set_math_mode(int mode) { g_fma = (mode == 0) ? 1 : 0; }
+int vo_get_math_mode(void) { return g_fma ? 0 : 1; }
+
 void vo_set_params(void* h, float voxel_length, float trunc_length, float min_depth, float max_depth) {
   Volume* v = (Volume*)h;
   v->voxel_length = voxel_length;
@@ -226,10 +252,14 @@ long long create_requests(Volume* v, const float* depths, int w, int h, const Pr
       const V3 origin = {M(Twd, 0, 3), M(Twd, 1, 3), M(Twd, 2, 3)};
       const float depth = depths[y * w + x];
       if (depth < v->min_depth || depth > v->max_depth) continue;
-      const V3 Xwp = plus(origin, scale(direction, depth));
+      // origin + depth * direction: FFMA dir*depth + origin
+      const V3 Xwp = {mad(direction.x, depth, origin.x), mad(direction.y, depth, origin.y),
+                      mad(direction.z, depth, origin.z)};
       direction = normalized(direction);
-      const V3 begin = minus(Xwp, scale(direction, trunc));
-      const V3 end = plus(Xwp, scale(direction, trunc));
+      // X -/+ trunc * direction: FFMA -/+dir*trunc + X
+      const V3 begin = {nmad(direction.x, trunc, Xwp.x), nmad(direction.y, trunc, Xwp.y),
+                        nmad(direction.z, trunc, Xwp.z)};
+      const V3 end = {mad(direction.x, trunc, Xwp.x), mad(direction.y, trunc, Xwp.y), mad(direction.z, trunc, Xwp.z)};
       const int step_x = (direction.x < 0) ? -1 : 1;
       const int step_y = (direction.y < 0) ? -1 : 1;
       const int step_z = (direction.z < 0) ? -1 : 1;
@@ -240,9 +270,10 @@ long long create_requests(Volume* v, const float* depths, int w, int h, const Pr
       const int ex = (int)floorf(end.x * inv_block_length);
       const int ey = (int)floorf(end.y * inv_block_length);
       const int ez = (int)floorf(end.z * inv_block_length);
-      const float ox = block_length * (bx + vmax(0, step_x)) - begin.x;
-      const float oy = block_length * (by + vmax(0, step_y)) - begin.y;
-      const float oz = block_length * (bz + vmax(0, step_z)) - begin.z;
+      // block_length * (b + max(0, step)) - begin: FFMA bf*L - begin
+      const float ox = msub((float)(bx + vmax(0, step_x)), block_length, begin.x);
+      const float oy = msub((float)(by + vmax(0, step_y)), block_length, begin.y);
+      const float oz = msub((float)(bz + vmax(0, step_z)), block_length, begin.z);
       float tmax_x = ox / direction.x;
       float tmax_y = oy / direction.y;
       float tmax_z = oz / direction.z;
@@ -405,9 +436,10 @@ void matmul4(const float* A, const float* Bm, float* C) {
 inline V3 voxel_world(const HashEntry& e, float block_length, float voxel_length, int x, int y, int z) {
   // src/depth_integrator.cu:36-39
   V3 Xwp;
-  Xwp.x = block_length * (float)e.block[0] + voxel_length * ((float)x + 0.5f);
-  Xwp.y = block_length * (float)e.block[1] + voxel_length * ((float)y + 0.5f);
-  Xwp.z = block_length * (float)e.block[2] + voxel_length * ((float)z + 0.5f);
+  // FMUL origin*L ; FFMA (v + 0.5)*l + .
+  Xwp.x = mad((float)x + 0.5f, voxel_length, block_length * (float)e.block[0]);
+  Xwp.y = mad((float)y + 0.5f, voxel_length, block_length * (float)e.block[1]);
+  Xwp.z = mad((float)z + 0.5f, voxel_length, block_length * (float)e.block[2]);
   return Xwp;
 }
 
@@ -435,11 +467,11 @@ void integrate_depth(Volume* v, const float* depths, int w, int h, const Proj& P
             const float distance = depth - Xdp.z;
             if (distance > -trunc) {
               Voxel& voxel = v->voxels[(long long)entry.data * 512 + z * 64 + y * 8 + x];
-              const float prev_dist = voxel.distance_weight * voxel.distance;
               const float curr_dist = vmin(1.0f, distance / trunc);
               const float dist_weight = voxel.distance_weight + 1;
+              // (w*D + cur) / (w + 1): FFMA D*w + cur ; IEEE division (Q9b)
+              voxel.distance = mad(voxel.distance, (float)voxel.distance_weight, curr_dist) / dist_weight;
               voxel.distance_weight = (int16_t)vmin(max_dist_weight, dist_weight);
-              voxel.distance = (prev_dist + curr_dist) / dist_weight;  // Q9b
             }
           }
         }
@@ -469,7 +501,7 @@ void integrate_color(Volume* v, const float* colors, int w, int h, const Proj& P
               const float cw = voxel.color_weight;
               const float color_weight = voxel.color_weight + 1;
               const float inv = 1.0f / color_weight;  // Matrix::operator/=, include/vulcan/matrix.h:288-295
-              for (int k = 0; k < 3; ++k) voxel.color[k] = (voxel.color[k] * cw + c[k]) * inv;
+              for (int k = 0; k < 3; ++k) voxel.color[k] = mad(voxel.color[k], cw, c[k]) * inv;  // FFMA C*cw + c
               voxel.color_weight = (int16_t)vmin(max_color_weight, color_weight);
             }
           }
@@ -539,11 +571,11 @@ void integrate_light_color(Volume* v, const float* mask, const float* colors, co
           const float shading = intensity * cos_theta / distance_squared;
           if (shading > 0.05f) {
             const float inv_s = 1.0f / shading;
-            for (int k = 0; k < 3; ++k) cur[k] *= inv_s;
             const float cw = voxel.color_weight;
             const float color_weight = voxel.color_weight + 1;
             const float inv = 1.0f / color_weight;
-            for (int k = 0; k < 3; ++k) voxel.color[k] = (voxel.color[k] * cw + cur[k]) * inv;
+            // prev + curr/shading: FMUL C*cw ; FFMA cur*(1/s) + .
+            for (int k = 0; k < 3; ++k) voxel.color[k] = mad(cur[k], inv_s, voxel.color[k] * cw) * inv;
             voxel.color_weight = (int16_t)vmin(max_color_weight, color_weight);
           }
         }
@@ -598,13 +630,16 @@ void vo_integrate_light(void* h, const float* depth, int w, int hgt, const float
 
 namespace {
 
-// float -> short like the device conversion the reference relies on (saturating,
-// NaN -> 0); in-range values truncate toward zero exactly like a C cast
+// `(short)floorf(u)` as the reference's machine code does it (F2I to a saturating s32,
+// NaN -> 0, then 16-bit VIMNMX on the low half of that register): in-range values truncate
+// like a C cast, wild values (blocks behind the camera) wrap instead of saturating
 inline int16_t to_short(float f) {
-  if (f != f) return 0;
-  if (f >= 32767.0f) return 32767;
-  if (f <= -32768.0f) return -32768;
-  return (int16_t)f;
+  int32_t i;
+  if (f != f) i = 0;
+  else if (f >= 2147483648.0f) i = INT32_MAX;
+  else if (f <= -2147483648.0f) i = INT32_MIN;
+  else i = (int32_t)f;
+  return (int16_t)(uint16_t)((uint32_t)i & 0xffffu);
 }
 
 // ComputePatchesKernel, src/tracer.cu:13-87, for one block; returns patch count
@@ -688,9 +723,10 @@ Tap get_voxel(const Volume* v, int bx, int by, int bz, int vx, int vy, int vz, F
 // GetInterpolatedDistance, src/tracer.cu:190-315
 void interpolate(const Volume* v, float block_length, float voxel_length, int bx, int by, int bz, int data,
                  const V3& p, float& sdf, float* color, Fetch& f) {
-  const float wx = (p.x - bx * block_length) / voxel_length;
-  const float wy = (p.y - by * block_length) / voxel_length;
-  const float wz = (p.z - bz * block_length) / voxel_length;
+  // (p - b*L) / l: FFMA -b*L + p ; IEEE division
+  const float wx = nmad((float)bx, block_length, p.x) / voxel_length;
+  const float wy = nmad((float)by, block_length, p.y) / voxel_length;
+  const float wz = nmad((float)bz, block_length, p.z) / voxel_length;
   const int i0x = (int)floorf(wx - 0.5f);
   const int i0y = (int)floorf(wy - 0.5f);
   const int i0z = (int)floorf(wz - 0.5f);
@@ -704,12 +740,13 @@ void interpolate(const Volume* v, float block_length, float voxel_length, int bx
   }
   const float w1[3] = {wx - (i0x + 0.5f), wy - (i0y + 0.5f), wz - (i0z + 0.5f)};
   const float w0[3] = {1.0f - w1[0], 1.0f - w1[1], 1.0f - w1[2]};
-  const float n00 = t[0].distance * w0[0] + t[1].distance * w1[0];
-  const float n01 = t[2].distance * w0[0] + t[3].distance * w1[0];
-  const float n10 = t[4].distance * w0[0] + t[5].distance * w1[0];
-  const float n11 = t[6].distance * w0[0] + t[7].distance * w1[0];
-  const float n0 = n00 * w0[1] + n01 * w1[1];
-  const float n1 = n10 * w0[1] + n11 * w1[1];
+  // a*w0 + b*w1: FMUL b*w1 ; FFMA a*w0 + .
+  const float n00 = mad(t[0].distance, w0[0], t[1].distance * w1[0]);
+  const float n01 = mad(t[2].distance, w0[0], t[3].distance * w1[0]);
+  const float n10 = mad(t[4].distance, w0[0], t[5].distance * w1[0]);
+  const float n11 = mad(t[6].distance, w0[0], t[7].distance * w1[0]);
+  const float n0 = mad(n00, w0[1], n01 * w1[1]);
+  const float n1 = mad(n10, w0[1], n11 * w1[1]);
   float total = 0;
   float col[3] = {0, 0, 0};
   for (int c = 0; c < 8; ++c) {
@@ -719,14 +756,20 @@ void interpolate(const Volume* v, float block_length, float voxel_length, int bx
     // Q15: `wz * wy * wx * (cw > 0) ? 1 : 0`
     const float weight = (wz_ * wy_ * wx_ * (t[c].color_weight > 0)) ? 1 : 0;
     total += weight;
-    for (int k = 0; k < 3; ++k) col[k] += t[c].color[k] * weight;
+    for (int k = 0; k < 3; ++k) col[k] = mad(weight, t[c].color[k], col[k]);  // FFMA chain from 0
   }
   if (total > 0) {
     const float inv = 1.0f / total;
     for (int k = 0; k < 3; ++k) col[k] *= inv;
   }
   color[0] = col[0]; color[1] = col[1]; color[2] = col[2];
-  sdf = n0 * w0[2] + n1 * w1[2];
+  sdf = mad(n0, w0[2], n1 * w1[2]);
+}
+
+// p += dir * s (include/vulcan/matrix.h:212): FFMA dir*s + p
+inline V3 step(const V3& p, const V3& dir, float s) {
+  V3 o = {mad(dir.x, s, p.x), mad(dir.y, s, p.y), mad(dir.z, s, p.z)};
+  return o;
 }
 
 // ComputeNormalsKernel<16>, src/frame.cu:7-122
@@ -748,10 +791,10 @@ void normals(const float* depths, const Proj& P, float* out, int w, int h) {
         const V3 dx = minus(q[0], q[1]);
         const V3 dy = minus(q[2], q[3]);
         if (dot(dx, dx) > 0 && dot(dy, dy) > 0) {
-          V3 c;  // dy.Cross(dx), include/vulcan/matrix.h:174-183
-          c.x = (dy.y * dx.z) - (dy.z * dx.y);
-          c.y = (dy.z * dx.x) - (dy.x * dx.z);
-          c.z = (dy.x * dx.y) - (dy.y * dx.x);
+          V3 c;  // dy.Cross(dx), include/vulcan/matrix.h:174-183: FMUL a.z*b.y ; FFMA a.y*b.z - .
+          c.x = msub(dy.y, dx.z, dy.z * dx.y);
+          c.y = msub(dy.z, dx.x, dy.x * dx.z);
+          c.z = msub(dy.x, dx.y, dy.y * dx.x);
           c = normalized(c);
           n[0] = c.x; n[1] = c.y; n[2] = c.z;
         }
@@ -834,30 +877,30 @@ void vo_compute_points(void* h, const float* bounds, const float* T, const float
           const int bz = (int)floorf(p.z / block_length);
           const int data = find_data(v, bx, by, bz, f);
           if (data != -1) {
-            const float wx = (p.x - bx * block_length) / voxel_length;
-            const float wy = (p.y - by * block_length) / voxel_length;
-            const float wz = (p.z - bz * block_length) / voxel_length;
+            const float wx = nmad((float)bx, block_length, p.x) / voxel_length;
+            const float wy = nmad((float)by, block_length, p.y) / voxel_length;
+            const float wz = nmad((float)bz, block_length, p.z) / voxel_length;
             const int vx = (int)wx, vy = (int)wy, vz = (int)wz;  // Q22
             float sdf = v->voxels[(long long)data * 512 + vz * 64 + vy * 8 + vx].distance;
             ++f.voxels;
             if (sdf <= 0.1f && sdf >= -0.5f) interpolate(v, block_length, voxel_length, bx, by, bz, data, p, sdf, color, f);
             if (sdf <= 0.0f) {
-              p = plus(p, scale(dir, trunc * sdf));
+              p = step(p, dir, trunc * sdf);
               const int bx2 = (int)floorf(p.x / block_length);
               const int by2 = (int)floorf(p.y / block_length);
               const int bz2 = (int)floorf(p.z / block_length);
               const int data2 = find_data(v, bx2, by2, bz2, f);
               if (data2 != -1) {
                 interpolate(v, block_length, voxel_length, bx2, by2, bz2, data2, p, sdf, color, f);
-                p = plus(p, scale(dir, trunc * sdf));
+                p = step(p, dir, trunc * sdf);
               }
               final_depth = xform(Tcw, p.x, p.y, p.z, 1.0f).z;
               break;
             } else {
-              p = plus(p, scale(dir, vmax(voxel_length, trunc * sdf)));
+              p = step(p, dir, vmax(voxel_length, trunc * sdf));
             }
           } else {
-            p = plus(p, scale(dir, block_length));
+            p = step(p, dir, block_length);
           }
           depth = xform(Tcw, p.x, p.y, p.z, 1.0f).z;
           if (++iters >= 500) { color[0] = 1; color[1] = 0; color[2] = 0; break; }

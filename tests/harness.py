@@ -38,6 +38,8 @@ def oracle_lib():
         lib.vo_create.argtypes = [_I, _I]
         lib.vo_destroy.argtypes = [_P]
         lib.vo_set_params.argtypes = [_P, _F, _F, _F, _F]
+        lib.vo_set_math_mode.argtypes = [_I]
+        lib.vo_get_math_mode.restype = _I
         for n in ("vo_voxels", "vo_entries", "vo_visibility", "vo_visible"):
             getattr(lib, n).restype = _P
             getattr(lib, n).argtypes = [_P]
@@ -295,10 +297,52 @@ def entry_keys(entries):
     return e0 | (e1 << 32)
 
 
-def allocated_table(entries):
-    """(sorted keys, data ids in the same order) of the allocated entries (numpy)."""
+def block_hash(keys, K):
+    """Q1 hash of packed block keys (src/volume.cu:168-180)."""
+    k = np.asarray(keys, dtype=np.int64)
+    m = np.int64(0xFFFFFFFF)
+    bx, by, bz = k & 0xFFFF, (k >> 16) & 0xFFFF, (k >> 32) & 0xFFFF
+    sx = np.where(bx >= 0x8000, bx - 0x10000, bx)
+    sy = np.where(by >= 0x8000, by - 0x10000, by)
+    sz = np.where(bz >= 0x8000, bz - 0x10000, bz)
+    h = ((sx * 73856093) & m) ^ ((sy * 19349669) & m) ^ ((sz * 83492791) & m)
+    return (h % K).astype(np.int64)
+
+
+def reachable_mask(entries, M):
+    """Per entry: allocated AND found at its own index by a lookup of its coordinates (bucket
+    head, then the `next` chain).  An allocated entry that is not reachable sits in a bucket its
+    coordinates do not hash to - only the reference's torn request writes (Q24) produce those."""
+    entries = np.asarray(entries)
+    keys = entry_keys(entries)
+    alloc = entries[:, 2] != -1
+    idx = np.nonzero(alloc)[0]
+    cur = block_hash(keys[idx], M)
+    found = np.full(len(idx), -1, dtype=np.int64)
+    active = np.ones(len(idx), dtype=bool)
+    for _ in range(256):
+        if not active.any():
+            break
+        c = cur[active]
+        hit = (keys[c] == keys[idx[active]]) & (entries[c, 2] != -1)
+        a_idx = np.nonzero(active)[0]
+        found[a_idx[hit]] = c[hit]
+        nxt = entries[c, 3].astype(np.int64)
+        cont = (~hit) & (nxt != -1)
+        active[a_idx[~cont]] = False
+        cur[a_idx[cont]] = nxt[cont]
+    out = np.zeros(len(entries), dtype=bool)
+    out[idx[found == idx]] = True
+    return out
+
+
+def allocated_table(entries, M=None):
+    """(sorted keys, data ids, entry indices) of the allocated entries (numpy).  With M given,
+    entries that a lookup cannot reach are left out (see reachable_mask)."""
     entries = np.asarray(entries)
     mask = entries[:, 2] != -1
+    if M is not None:
+        mask = reachable_mask(entries, M)
     keys = entry_keys(entries[mask])
     order = np.argsort(keys, kind="stable")
     return keys[order], entries[mask][order, 2], np.nonzero(mask)[0][order]
@@ -349,8 +393,9 @@ def raw32(R, t):
     return np.concatenate([m.T.reshape(-1), i.T.reshape(-1)]).astype(np.float32)
 
 
-def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2):
-    """Sphere-on-plane scenarios.  frames = orbit indices."""
+def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2, math=0):
+    """Sphere-on-plane scenarios.  frames = orbit indices; math = 0 (reference
+    contraction pattern) or 1 (strict)."""
     cfg = {
         "tiny": dict(w=64, h=48, voxel=0.016, M=4096, E=1024),
         "small": dict(w=160, h=120, voxel=0.008, M=32768, E=8192),
@@ -359,7 +404,8 @@ def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2):
     }[name]
     w, h = cfg["w"], cfg["h"]
     K = synth.intrinsics(w, h)
-    scn = dict(cfg, name=name, mode=mode, K=np.array(K, dtype=np.float32), trunc=5 * cfg["voxel"], frames=[])
+    scn = dict(cfg, name=name, mode=mode, math=math, K=np.array(K, dtype=np.float32), trunc=5 * cfg["voxel"],
+               frames=[])
     for k in frames:
         if k == 0 and step_deg == 1.2:
             R, t = np.eye(3), np.zeros(3)   # C1: identity pose
@@ -376,14 +422,16 @@ def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2):
     return scn
 
 
-def _pack_result(entries, voxels, visibility, visible, traced):
-    keys, data, idx = allocated_table(entries)
+def _pack_result(entries, voxels, visibility, visible, traced, M):
+    keys, data, idx = allocated_table(entries, M)
     return dict(keys=keys, voxels=gather_blocks(voxels, data), vis_flags=np.asarray(visibility)[idx],
-                visible_keys=visible_keys(entries, visible), depth=traced[0], color=traced[1], normal=traced[2])
+                visible_keys=visible_keys(entries, visible), depth=traced[0], color=traced[1], normal=traced[2],
+                unreachable=int((np.asarray(entries)[:, 2] != -1).sum() - len(keys)))
 
 
 def run_oracle(scn):
     ov = OracleVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"])
+    ov.lib.vo_set_math_mode(scn.get("math", 0))
     K = scn["K"]
     for fr in scn["frames"]:
         ov.set_view_converged(fr["depth"], K, fr["T"])
@@ -398,13 +446,16 @@ def run_oracle(scn):
                                np.array(scn["light"][1], dtype=np.float32))
     last = scn["frames"][-1]
     d, c, n, _ = ov.trace(scn["w"], scn["h"], K, last["T"])
-    res = _pack_result(ov.entries(), ov.voxels(), ov.visibility(), ov.visible(), (d, c, n))
+    res = _pack_result(ov.entries(), ov.voxels(), ov.visibility(), ov.visible(), (d, c, n), scn["M"])
     res["fetches"] = ov.fetch_counts()
     assert ov.dropped() == 0
     return res
 
 
-def run_ref(scn, nofmad=False):
+def run_ref(scn, nofmad=None):
+    """The reference's own CUDA build: release (-fmad=true) for math mode 0, -fmad=false for 1."""
+    if nofmad is None:
+        nofmad = bool(scn.get("math", 0))
     rv = RefVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"], nofmad=nofmad)
     try:
         K = scn["K"]
@@ -420,12 +471,13 @@ def run_ref(scn, nofmad=False):
         rv.trace(scn["w"], scn["h"], K, last["T"])
         d, c, n = rv.traced(scn["w"], scn["h"])
         entries = rv.entries().cpu().numpy()
-        keys, data, idx = allocated_table(entries)
+        keys, data, idx = allocated_table(entries, scn["M"])
         import torch
         vox = rv.voxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy()
         return dict(keys=keys, voxels=vox, vis_flags=rv.visibility().cpu().numpy()[idx],
                     visible_keys=visible_keys(entries, rv.visible().cpu().numpy()), depth=d.cpu().numpy(),
-                    color=c.cpu().numpy(), normal=n.cpu().numpy())
+                    color=c.cpu().numpy(), normal=n.cpu().numpy(),
+                    unreachable=int((entries[:, 2] != -1).sum() - len(keys)))
     finally:
         rv.close()
 
@@ -433,6 +485,7 @@ def run_ref(scn, nofmad=False):
 def run_ours(scn, shard=None):
     import torch
     import vulcan_b200 as vb
+    vb.SetDefaultMathMode(scn.get("math", 0))
     vol = vb.Volume(scn["M"], scn["E"])
     vol.SetVoxelLength(scn["voxel"])
     vol.SetTruncationLength(scn["trunc"])
@@ -469,12 +522,13 @@ def run_ours(scn, shard=None):
     n_vis, counters = vol.SyncCounters()
     assert counters[4] == 0, "pool overflow"
     entries = vol.GetHashEntries().cpu().numpy()
-    keys, data, idx = allocated_table(entries)
+    keys, data, idx = allocated_table(entries, scn["M"])
     vox = vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy()
     res = dict(keys=keys, voxels=vox, vis_flags=vol.GetBlockVisibility().cpu().numpy()[idx],
                visible_keys=visible_keys(entries, vol.GetVisibleBlocks().cpu().numpy()),
                depth=out.depth_image.cpu().numpy(), color=out.color_image.cpu().numpy(),
-               normal=out.normal_image.cpu().numpy(), counters=counters)
+               normal=out.normal_image.cpu().numpy(), counters=counters,
+               unreachable=int((entries[:, 2] != -1).sum() - len(keys)))
     del vol
     return res
 
@@ -503,7 +557,7 @@ def compare(a, b, trunc):
     rep["alloc_counts"] = (int(len(a["keys"])), int(len(b["keys"])))
     rep["alloc_only_a"] = int(len(ka) - len(common))
     rep["alloc_only_b"] = int(len(kb) - len(common))
-    rep["alloc_dup_a"], rep["alloc_dup_b"] = dupa, dupb
+    rep["alloc_dup_a"], rep["alloc_dup_b"] = dupa + a.get("unreachable", 0), dupb + b.get("unreachable", 0)
     va, vb_ = np.unique(a["visible_keys"]), np.unique(b["visible_keys"])
     rep["visible_equal"] = bool(len(a["visible_keys"]) == len(b["visible_keys"]) and
                                 np.array_equal(a["visible_keys"], b["visible_keys"]))

@@ -16,6 +16,7 @@ VK_CNT_OVERFLOW = 4
 VK_CNT_ALLOCATED = 6
 VK_CNT_COUNT = 16
 VK_E_OVERFLOW = -3
+VK_MATH_REFERENCE, VK_MATH_STRICT = 0, 1
 BOUNDS_W, BOUNDS_H = 80, 60
 
 
@@ -40,7 +41,7 @@ class vkVolume(C.Structure):
         ("voxel_length", C.c_float), ("trunc_length", C.c_float),
         ("min_depth", C.c_float), ("max_depth", C.c_float),
         ("shard_rank", C.c_int32), ("shard_count", C.c_int32), ("shard_shift", C.c_int32),
-        ("visible_slot", C.c_int32), ("view_id", C.c_int32), ("reserved", C.c_int32),
+        ("visible_slot", C.c_int32), ("view_id", C.c_int32), ("math_mode", C.c_int32),
     ]
 
 
@@ -77,6 +78,9 @@ SYMBOLS = {
     "vk_compute_normals": [_P, C.POINTER(vkProjection), _P, _I, _I, _P],
     "vk_filter_depths": [_I, _I, _P, _P, _P],
     "vk_version": [],
+    "vk_set_default_math_mode": [_I],
+    "vk_get_default_math_mode": [],
+    "vk_div_prepare": [_F, _P],
     "vk_launch_count": [],
 }
 

@@ -25,6 +25,15 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def SetDefaultMathMode(mode):
+    """Math mode of the entry points that take no Volume (Frame.ComputeNormals, ...) and of new volumes."""
+    check(lib.vk_set_default_math_mode(int(mode)), "SetDefaultMathMode")
+
+
+def GetDefaultMathMode():
+    return lib.vk_get_default_math_mode()
+
+
 class _DevView:
     """Zero-copy torch view of library-owned device memory."""
 
@@ -209,6 +218,16 @@ class Volume:
 
     def SetTruncationLength(self, length):
         self._v.trunc_length = length
+
+    def GetMathMode(self):
+        return self._v.math_mode
+
+    def SetMathMode(self, mode):
+        """VK_MATH_REFERENCE (0, default): multiply-adds fused exactly where the reference's release
+        build fuses them; VK_MATH_STRICT (1): one rounding per operation (-fmad=false build)."""
+        if mode not in (_lib.VK_MATH_REFERENCE, _lib.VK_MATH_STRICT):
+            raise VulcanError("invalid math mode")
+        self._v.math_mode = mode
 
     def SetSharding(self, rank, count, shift=3):
         self._v.shard_rank, self._v.shard_count, self._v.shard_shift = rank, count, shift

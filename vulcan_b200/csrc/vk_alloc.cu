@@ -37,9 +37,9 @@ struct AllocParams {
   int w, h;
   vkProjection proj;
   float Twd[12];  // rows 0..2 of depth_to_world, row-major 3x4
-  uint32_t K;
+  Mod K;
   int B;
-  float block_length, trunc, min_depth, max_depth;
+  float block_length, inv_block_length, trunc, min_depth, max_depth;
   int view_id;
   int shard_rank, shard_count, shard_shift;
 };
@@ -129,6 +129,12 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
 
 // CreateAllocationRequestsKernel (src/volume.cu:86-301) + HandleAllocationRequestsKernel
 // (src/volume.cu:303-368) to their common fixed point.
+// FMA map (reference release SASS of CreateAllocationRequestsKernel):
+//   dir   = Twd * (unproj, 0)      FMUL y*m1; FFMA x*m0 + .; FADD m2 (z == 1); FFMA 0*m3 + .
+//   X     = origin + depth * dir   FFMA dir*depth + origin
+//   begin = X - trunc * dir        FFMA -dir*trunc + X     end = FFMA dir*trunc + X
+//   tmax  = (L*(b + max(0,step)) - begin) / dir     FFMA bf*L - begin ; IEEE div
+template <bool F>
 __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -144,34 +150,34 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
     const float depth = __ldg(p.depth + y * p.w + x);
     if (depth < p.min_depth || depth > p.max_depth) active = false;
     if (active) {
-      const float u = (float)x + 0.5f, v = (float)y + 0.5f;
-      const Vec3 d0 = unproject(p.proj, u, v);
-      // direction = Twd * (d, 0)
-      Vec3 dir;
-      dir.x = add(add(add(mul(p.Twd[0], d0.x), mul(p.Twd[1], d0.y)), mul(p.Twd[2], d0.z)), mul(p.Twd[3], 0.0f));
-      dir.y = add(add(add(mul(p.Twd[4], d0.x), mul(p.Twd[5], d0.y)), mul(p.Twd[6], d0.z)), mul(p.Twd[7], 0.0f));
-      dir.z = add(add(add(mul(p.Twd[8], d0.x), mul(p.Twd[9], d0.y)), mul(p.Twd[10], d0.z)), mul(p.Twd[11], 0.0f));
-      const float Xx = add(p.Twd[3], mul(dir.x, depth));
-      const float Xy = add(p.Twd[7], mul(dir.y, depth));
-      const float Xz = add(p.Twd[11], mul(dir.z, depth));
-      dir = normalized(dir);
-      const float bgx = sub(Xx, mul(dir.x, p.trunc)), bgy = sub(Xy, mul(dir.y, p.trunc)),
-                  bgz = sub(Xz, mul(dir.z, p.trunc));
-      const float enx = add(Xx, mul(dir.x, p.trunc)), eny = add(Xy, mul(dir.y, p.trunc)),
-                  enz = add(Xz, mul(dir.z, p.trunc));
+      const float u = add((float)x, 0.5f), v = add((float)y, 0.5f);
+      Unprojector un;
+      un.init(p.proj);
+      const float d0x = un.x<F>(u), d0y = un.y<F>(v);
+      Mat34 Twd;
+      Twd.load(p.Twd);
+      Vec3 dir = xform0<F>(Twd, d0x, d0y, 1.0f);
+      const float Xx = FP<F>::mad(dir.x, depth, p.Twd[3]);
+      const float Xy = FP<F>::mad(dir.y, depth, p.Twd[7]);
+      const float Xz = FP<F>::mad(dir.z, depth, p.Twd[11]);
+      dir = normalized<F>(dir);
+      const float bgx = FP<F>::nmad(dir.x, p.trunc, Xx), bgy = FP<F>::nmad(dir.y, p.trunc, Xy),
+                  bgz = FP<F>::nmad(dir.z, p.trunc, Xz);
+      const float enx = FP<F>::mad(dir.x, p.trunc, Xx), eny = FP<F>::mad(dir.y, p.trunc, Xy),
+                  enz = FP<F>::mad(dir.z, p.trunc, Xz);
       sx = (dir.x < 0) ? -1 : 1;
       sy = (dir.y < 0) ? -1 : 1;
       sz = (dir.z < 0) ? -1 : 1;
-      const float inv = fdiv(1.0f, p.block_length);
+      const float inv = p.inv_block_length;
       bx = (int)floorf(mul(bgx, inv));
       by = (int)floorf(mul(bgy, inv));
       bz = (int)floorf(mul(bgz, inv));
       ex = (int)floorf(mul(enx, inv));
       ey = (int)floorf(mul(eny, inv));
       ez = (int)floorf(mul(enz, inv));
-      const float ox = sub(mul(p.block_length, (float)(bx + max(0, sx))), bgx);
-      const float oy = sub(mul(p.block_length, (float)(by + max(0, sy))), bgy);
-      const float oz = sub(mul(p.block_length, (float)(bz + max(0, sz))), bgz);
+      const float ox = FP<F>::msub((float)(bx + max(0, sx)), p.block_length, bgx);
+      const float oy = FP<F>::msub((float)(by + max(0, sy)), p.block_length, bgy);
+      const float oz = FP<F>::msub((float)(bz + max(0, sz)), p.block_length, bgz);
       tmx = fdiv(ox, dir.x);
       tmy = fdiv(oy, dir.y);
       tmz = fdiv(oz, dir.z);
@@ -231,6 +237,7 @@ struct CarryParams {
 
 // UpdateBlockVisibilityKernel (src/volume.cu:23-84) restricted to the entries that can
 // be VISIBILITY_UNKNOWN, i.e. the previous visible list.
+template <bool F>
 __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
   const int n_prev = p.counters[p.prev_slot];
   const int lane = threadIdx.x & 31;
@@ -242,22 +249,18 @@ __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
       e = p.prev_list[i];
       if (p.stamps[e] != p.view_id) {
         const int4 ent = ld_entry(p.entries + e);
-        const int ox = (int)(int16_t)(ent.x & 0xffff);
-        const int oy = (int)(int16_t)((uint32_t)ent.x >> 16);
-        const int oz = (int)(int16_t)(ent.y & 0xffff);
+        int ox, oy, oz;
+        entry_origin(ent, ox, oy, oz);
         Mat34 M;
-#pragma unroll
-        for (int r = 0; r < 3; ++r)
-#pragma unroll
-          for (int c = 0; c < 4; ++c) M.r[r][c] = p.Tdw[r * 4 + c];
+        M.load(p.Tdw);
         for (int c = 0; c < 8; ++c) {
           const float X = mul(p.block_length, (float)(ox + ((c & 1) >> 0)));
           const float Y = mul(p.block_length, (float)(oy + ((c & 2) >> 1)));
           const float Z = mul(p.block_length, (float)(oz + ((c & 4) >> 2)));
-          const Vec3 Xd = xform(M, X, Y, Z, 1.0f);
+          const Vec3 Xd = xform1<F>(M, X, Y, Z);
           if (Xd.z < 0) continue;
           float u, v;
-          project(p.proj, Xd, u, v);
+          project<F>(p.proj, Xd, u, v);
           if (u >= 0 && u <= (float)p.w && v >= 0 && v <= (float)p.h) { keep = true; break; }
         }
         p.visibility[e] = keep ? VK_VIS_UNKNOWN : VK_VIS_FALSE;
@@ -320,11 +323,6 @@ __global__ void vk_fill_pools_kernel(uint4* voxels16, size_t n16, vkHashEntry* e
 
 using namespace vk;
 
-static void rows34(const float* colmajor, float* out12) {
-  for (int r = 0; r < 3; ++r)
-    for (int c = 0; c < 4; ++c) out12[r * 4 + c] = colmajor[c * 4 + r];
-}
-
 extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   if (!v || !v->voxels) return VK_E_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
@@ -365,6 +363,7 @@ extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks,
   v->shard_rank = 0;
   v->shard_count = 1;
   v->shard_shift = 3;
+  v->math_mode = g_default_math_mode.load();
   cudaError_t err;
 #define VK_TRY(x) if ((err = (x)) != cudaSuccess) { vk_volume_destroy(v); return (int)err; }
   VK_TRY(cudaMalloc((void**)&v->voxels, B * VK_BLOCK_VOXELS * sizeof(vkVoxel)));
@@ -420,9 +419,10 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.h = f->depth_h;
   a.proj = f->depth_proj;
   rows34(f->depth_to_world.m, a.Twd);
-  a.K = (uint32_t)v->main_blocks;
+  a.K = make_mod((uint32_t)v->main_blocks);
   a.B = v->main_blocks + v->excess_blocks;
   a.block_length = VK_BLOCK_RES * v->voxel_length;
+  a.inv_block_length = 1.0f / a.block_length;   // src/volume.cu:131 (1.0f / block_length, IEEE)
   a.trunc = v->trunc_length;
   a.min_depth = v->min_depth;
   a.max_depth = v->max_depth;
@@ -431,7 +431,9 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.shard_count = v->shard_count;
   a.shard_shift = v->shard_shift;
   dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
-  vk_alloc_kernel<<<grid, 256, 0, s>>>(a);
+  const bool strict = (v->math_mode == VK_MATH_STRICT);
+  if (strict) vk_alloc_kernel<false><<<grid, 256, 0, s>>>(a);
+  else vk_alloc_kernel<true><<<grid, 256, 0, s>>>(a);
   VK_COUNT_LAUNCH();
 
   CarryParams c;
@@ -451,7 +453,8 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   c.block_length = a.block_length;
   c.view_id = v->view_id;
   c.ticket = v->counters + VK_CNT_COUNT;
-  vk_carry_kernel<<<148, 256, 0, s>>>(c);
+  if (strict) vk_carry_kernel<false><<<sm_count(), 256, 0, s>>>(c);
+  else vk_carry_kernel<true><<<sm_count(), 256, 0, s>>>(c);
   VK_COUNT_LAUNCH();
   v->visible_slot = cur;
   return (int)cudaGetLastError();

@@ -32,38 +32,41 @@ struct IntegrateParams {
   int dw, dh, cw, ch;
   vkProjection dproj, cproj;
   float Tdw[12], Tcw[12], Tcd[12];
-  float voxel_length, block_length, trunc;
+  float voxel_length, block_length;
+  Div trunc;
   float min_depth, max_depth, max_dw, max_cw;
   vkLight light;
 };
 
-__device__ __forceinline__ void load_rows(Mat34& M, const float* rows) {
-#pragma unroll
-  for (int r = 0; r < 3; ++r)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) M.r[r][c] = rows[r * 4 + c];
-}
-
-template <int MODE>
+// FMA map (reference release SASS, see vk_math.cuh):
+//   Xw      = L*o + l*(v+0.5)          FMUL o*L ; FFMA (v+0.5)*l + .      depth_integrator.cu:36-39
+//   D'      = (w*D + cur) / (w+1)      FFMA D*w + cur ; IEEE div         depth_integrator.cu:68-76
+//   C'      = (cw*C + c) * (1/(cw+1))  FFMA C*cw + c ; FMUL              color_integrator.cu:121-126
+//   C'light = (cw*C + c*(1/s)) * ...   FMUL C*cw ; FFMA c*(1/s) + . ; FMUL  light_integrator.cu:238-241
+template <int MODE, bool F>
 __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams p) {
   const int n = *p.count;
   const int t = threadIdx.x;
   const int vz = t >> 4, vy = (t >> 1) & 7, vx0 = (t & 1) * 4;
   Mat34 Tdw, Tcw;
-  load_rows(Tdw, p.Tdw);
-  if (MODE != MODE_DEPTH) load_rows(Tcw, p.Tcw);
+  Tdw.load(p.Tdw);
+  if (MODE != MODE_DEPTH) Tcw.load(p.Tcw);
   unsigned n_updated = 0;
+  const float fy = add((float)vy, 0.5f), fz = add((float)vz, 0.5f);
 
-  for (int bi = blockIdx.x; bi < n; bi += gridDim.x) {
-    const int e = __ldg(p.visible + bi);
-    const int4 ent = ld_entry(p.entries + e);
-    const float ox = (float)(int)(int16_t)(ent.x & 0xffff);
-    const float oy = (float)(int)(int16_t)((uint32_t)ent.x >> 16);
-    const float oz = (float)(int)(int16_t)(ent.y & 0xffff);
-    // Xwp = block_length * origin + voxel_length * (xyz + 0.5)   (src/depth_integrator.cu:36-39)
-    const float Xy = add(mul(oy, p.block_length), mul(add((float)vy, 0.5f), p.voxel_length));
-    const float Xz = add(mul(oz, p.block_length), mul(add((float)vz, 0.5f), p.voxel_length));
-    const float bxl = mul(ox, p.block_length);
+  int bi = blockIdx.x;
+  int e_next = (bi < n) ? __ldg(p.visible + bi) : 0;
+  int4 ent_next = ld_entry(p.entries + e_next);
+  for (; bi < n; bi += gridDim.x) {
+    const int4 ent = ent_next;
+    // next block's list slot and entry are fetched while this block is processed
+    const int bn = bi + gridDim.x;
+    if (bn < n) e_next = __ldg(p.visible + bn);
+    int iox, ioy, ioz;
+    entry_origin(ent, iox, ioy, ioz);
+    const float Xy = FP<F>::mad(fy, p.voxel_length, mul((float)ioy, p.block_length));
+    const float Xz = FP<F>::mad(fz, p.voxel_length, mul((float)ioz, p.block_length));
+    const float bxl = mul((float)iox, p.block_length);
 
     bool dpass[4];          // depth update applies
     float dcur[4];          // depth - Xd.z
@@ -75,10 +78,10 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
 
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float Xx = add(bxl, mul(add((float)(vx0 + k), 0.5f), p.voxel_length));
-      const Vec3 Xd = xform(Tdw, Xx, Xy, Xz, 1.0f);
+      const float Xx = FP<F>::mad(add((float)(vx0 + k), 0.5f), p.voxel_length, bxl);
+      const Vec3 Xd = xform1<F>(Tdw, Xx, Xy, Xz);
       float u, v;
-      project(p.dproj, Xd, u, v);
+      project<F>(p.dproj, Xd, u, v);
       const bool din = (u >= 0 && u < (float)p.dw && v >= 0 && v < (float)p.dh);
       dpass[k] = false;
       dcur[k] = 0.f;
@@ -88,22 +91,22 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
         const float d = __ldg(p.depth + di);
         if (!(d < p.min_depth || d > p.max_depth)) {
           const float s = sub(d, Xd.z);
-          if (s > -p.trunc) { dpass[k] = true; dcur[k] = s; }
+          if (s > -p.trunc.d) { dpass[k] = true; dcur[k] = s; }
         }
       }
       need |= dpass[k];
       if (MODE == MODE_COLOR) {
-        Xc[k] = xform(Tcw, Xx, Xy, Xz, 1.0f);
+        Xc[k] = xform1<F>(Tcw, Xx, Xy, Xz);
         float cu, cv;
-        project(p.cproj, Xc[k], cu, cv);
+        project<F>(p.cproj, Xc[k], cu, cv);
         cin[k] = (cu >= 0 && cu < (float)p.cw && cv >= 0 && cv < (float)p.ch);
         cidx[k] = cin[k] ? (int)cv * p.cw + (int)cu : 0;
         need |= cin[k];
       } else if (MODE == MODE_LIGHT) {
         // both projections are tested against the depth image size (src/light_integrator.cu:207-215,335-336)
-        Xc[k] = xform(Tcw, Xx, Xy, Xz, 1.0f);
+        Xc[k] = xform1<F>(Tcw, Xx, Xy, Xz);
         float cu, cv;
-        project(p.cproj, Xc[k], cu, cv);
+        project<F>(p.cproj, Xc[k], cu, cv);
         bool ok = din && (cu >= 0 && cu < (float)p.dw && cv >= 0 && cv < (float)p.dh);
         didx[k] = di;
         cidx[k] = ok ? (int)cv * p.dw + (int)cu : 0;
@@ -112,6 +115,7 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
         need |= ok;
       }
     }
+    if (bn < n) ent_next = ld_entry(p.entries + e_next);
     if (!need) continue;
 
     uint4* tile = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) +
@@ -131,51 +135,55 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
       int cwt = (int)(int16_t)(w[5 * k + 4] >> 16);
       if (dpass[k]) {
         // src/depth_integrator.cu:68-76
-        const float prev = mul((float)dwt, D);
-        const float cur = vmin(1.0f, fdiv(dcur[k], p.trunc));
-        const float wn = add((float)dwt, 1.0f);
+        const float cur = vmin(1.0f, divc(dcur[k], p.trunc));
+        const float wn = (float)(dwt + 1);
+        D = fdiv(FP<F>::mad(D, (float)dwt, cur), wn);
         dwt = (int)(short)vmin(p.max_dw, wn);
-        D = fdiv(add(prev, cur), wn);
         w[5 * k] = __float_as_uint(D);
         dirty |= (1u << (5 * k)) | (1u << (5 * k + 4));
       }
       if (MODE != MODE_DEPTH) {
         if (cin[k] && fabsf(D) < 1.0f) {
-          float cr = __ldg(p.color + 3 * (size_t)cidx[k] + 0);
-          float cg = __ldg(p.color + 3 * (size_t)cidx[k] + 1);
-          float cb = __ldg(p.color + 3 * (size_t)cidx[k] + 2);
+          const float cr = __ldg(p.color + 3 * (size_t)cidx[k] + 0);
+          const float cg = __ldg(p.color + 3 * (size_t)cidx[k] + 1);
+          const float cb = __ldg(p.color + 3 * (size_t)cidx[k] + 2);
+          const float fw = (float)cwt;
+          const float wn = (float)(cwt + 1);
+          const float r0 = __uint_as_float(w[5 * k + 1]);
+          const float g0 = __uint_as_float(w[5 * k + 2]);
+          const float b0 = __uint_as_float(w[5 * k + 3]);
           bool ok = true;
+          float sr, sg, sb;
           if (MODE == MODE_LIGHT) {
-            // src/light_integrator.cu:229-237, include/vulcan/light.h:52-60
+            // src/light_integrator.cu:229-241, include/vulcan/light.h:52-60
             const float nx = __ldg(p.normal + 3 * (size_t)didx[k] + 0);
             const float ny = __ldg(p.normal + 3 * (size_t)didx[k] + 1);
             const float nz = __ldg(p.normal + 3 * (size_t)didx[k] + 2);
             Mat34 Tcd;
-            load_rows(Tcd, p.Tcd);
-            const Vec3 Xcn = xform(Tcd, nx, ny, nz, 0.0f);
-            Vec3 delta = {sub(p.light.position[0], Xc[k].x), sub(p.light.position[1], Xc[k].y),
-                          sub(p.light.position[2], Xc[k].z)};
-            const Vec3 dirn = normalized(delta);
-            const float dist2 = dot3(delta, delta);
-            const float cos_theta = dot3(Xcn, dirn);
+            Tcd.load(p.Tcd);
+            const Vec3 Xcn = xform0<F>(Tcd, nx, ny, nz);
+            const Vec3 delta = {sub(p.light.position[0], Xc[k].x), sub(p.light.position[1], Xc[k].y),
+                                sub(p.light.position[2], Xc[k].z)};
+            const float dist2 = dot3<F>(delta, delta);
+            const float invn = rcp(__fsqrt_rn(dist2));
+            const Vec3 dirn = {mul(delta.x, invn), mul(delta.y, invn), mul(delta.z, invn)};
+            const float cos_theta = dot3<F>(Xcn, dirn);
             const float shading = fdiv(mul(p.light.intensity, cos_theta), dist2);
             ok = shading > 0.05f;
-            if (ok) {
-              const float inv = fdiv(1.0f, shading);
-              cr = mul(cr, inv); cg = mul(cg, inv); cb = mul(cb, inv);
-            }
+            const float inv_s = rcp(shading);
+            sr = FP<F>::mad(cr, inv_s, mul(r0, fw));
+            sg = FP<F>::mad(cg, inv_s, mul(g0, fw));
+            sb = FP<F>::mad(cb, inv_s, mul(b0, fw));
+          } else {
+            sr = FP<F>::mad(r0, fw, cr);
+            sg = FP<F>::mad(g0, fw, cg);
+            sb = FP<F>::mad(b0, fw, cb);
           }
           if (ok) {
-            // src/color_integrator.cu:121-126
-            const float fw = (float)cwt;
-            const float wn = add(fw, 1.0f);
-            const float inv = fdiv(1.0f, wn);
-            const float r0 = __uint_as_float(w[5 * k + 1]);
-            const float g0 = __uint_as_float(w[5 * k + 2]);
-            const float b0 = __uint_as_float(w[5 * k + 3]);
-            w[5 * k + 1] = __float_as_uint(mul(add(mul(r0, fw), cr), inv));
-            w[5 * k + 2] = __float_as_uint(mul(add(mul(g0, fw), cg), inv));
-            w[5 * k + 3] = __float_as_uint(mul(add(mul(b0, fw), cb), inv));
+            const float inv = rcp(wn);
+            w[5 * k + 1] = __float_as_uint(mul(sr, inv));
+            w[5 * k + 2] = __float_as_uint(mul(sg, inv));
+            w[5 * k + 3] = __float_as_uint(mul(sb, inv));
             cwt = (int)(short)vmin(p.max_cw, wn);
             dirty |= (0xeu << (5 * k)) | (1u << (5 * k + 4));
           }
@@ -235,13 +243,8 @@ __global__ void __launch_bounds__(256) vk_frame_mask_kernel(int width, int heigh
 
 using namespace vk;
 
-static void rows34(const float* colmajor, float* out12) {
-  for (int r = 0; r < 3; ++r)
-    for (int c = 0; c < 4; ++c) out12[r * 4 + c] = colmajor[c * 4 + r];
-}
-
 // Matrix::operator* (include/vulcan/matrix.h:296-316), evaluated on the host like the
-// reference does for Tcw = Tcd * Tdw (src/color_integrator.cu:191-193).
+// reference does for Tcw = Tcd * Tdw (src/color_integrator.cu:191-193; host code, no FMA).
 static void matmul4(const float* A, const float* Bm, float* C) {
   for (int p = 0; p < 4; ++p)
     for (int m = 0; m < 4; ++m) {
@@ -255,7 +258,7 @@ static void matmul4(const float* A, const float* Bm, float* C) {
 }
 
 static int fill_params(IntegrateParams& p, vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
-                       float max_dw, float max_cw) {
+                       float max_dw, float max_cw, cudaStream_t s) {
   if (!v || !f || !v->voxels || !f->depth) return VK_E_INVALID;
   p.visible = v->visible[v->visible_slot];
   p.count = v->counters + VK_CNT_VISIBLE0 + v->visible_slot;
@@ -276,7 +279,7 @@ static int fill_params(IntegrateParams& p, vkVolume* v, const vkFrame* f, float 
   rows34(f->depth_to_color.m, p.Tcd);
   p.voxel_length = v->voxel_length;
   p.block_length = VK_BLOCK_RES * v->voxel_length;
-  p.trunc = v->trunc_length;
+  p.trunc = make_div(v->trunc_length, s);
   p.min_depth = min_depth; p.max_depth = max_depth;
   p.max_dw = max_dw; p.max_cw = max_cw;
   p.light.intensity = 1.0f;
@@ -284,27 +287,45 @@ static int fill_params(IntegrateParams& p, vkVolume* v, const vkFrame* f, float 
   return 0;
 }
 
-static const int kIntegrateGrid = 148 * 12;
+// persistent grid: one wave of resident CTAs
+template <int MODE, bool F>
+static int integrate_grid() {
+  static int grid = 0;
+  if (grid == 0) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vk_integrate_kernel<MODE, F>, 128, 0) != cudaSuccess ||
+        per_sm <= 0)
+      per_sm = 8;
+    grid = per_sm * sm_count();
+  }
+  return grid;
+}
+
+template <int MODE>
+static int launch_integrate(const IntegrateParams& p, int math_mode, cudaStream_t s) {
+  if (math_mode == VK_MATH_STRICT)
+    vk_integrate_kernel<MODE, false><<<integrate_grid<MODE, false>(), 128, 0, s>>>(p);
+  else
+    vk_integrate_kernel<MODE, true><<<integrate_grid<MODE, true>(), 128, 0, s>>>(p);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
 
 extern "C" int vk_integrate_depth(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
                                   float max_distance_weight, void* stream) {
   IntegrateParams p;
-  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, 16.f);
+  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, 16.f, (cudaStream_t)stream);
   if (rc) return rc;
-  vk_integrate_kernel<MODE_DEPTH><<<kIntegrateGrid, 128, 0, (cudaStream_t)stream>>>(p);
-  VK_COUNT_LAUNCH();
-  return (int)cudaGetLastError();
+  return launch_integrate<MODE_DEPTH>(p, v->math_mode, (cudaStream_t)stream);
 }
 
 extern "C" int vk_integrate_color(vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
                                   float max_distance_weight, float max_color_weight, void* stream) {
   IntegrateParams p;
-  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, max_color_weight);
+  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, max_color_weight, (cudaStream_t)stream);
   if (rc) return rc;
   if (!f->color || f->color_w <= 0 || f->color_h <= 0) return VK_E_INVALID;
-  vk_integrate_kernel<MODE_COLOR><<<kIntegrateGrid, 128, 0, (cudaStream_t)stream>>>(p);
-  VK_COUNT_LAUNCH();
-  return (int)cudaGetLastError();
+  return launch_integrate<MODE_COLOR>(p, v->math_mode, (cudaStream_t)stream);
 }
 
 extern "C" int vk_compute_frame_mask(const vkFrame* f, float depth_threshold, float* mask, void* stream) {
@@ -320,14 +341,12 @@ extern "C" int vk_integrate_light(vkVolume* v, const vkFrame* f, float min_depth
                                   float max_distance_weight, float max_color_weight, const vkLight* light,
                                   float depth_threshold, float* mask, void* stream) {
   IntegrateParams p;
-  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, max_color_weight);
+  int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, max_color_weight, (cudaStream_t)stream);
   if (rc) return rc;
   if (!f->color || !f->normal || !mask || !light) return VK_E_INVALID;
   rc = vk_compute_frame_mask(f, depth_threshold, mask, stream);
   if (rc) return rc;
   p.mask = mask;
   p.light = *light;
-  vk_integrate_kernel<MODE_LIGHT><<<kIntegrateGrid, 128, 0, (cudaStream_t)stream>>>(p);
-  VK_COUNT_LAUNCH();
-  return (int)cudaGetLastError();
+  return launch_integrate<MODE_LIGHT>(p, v->math_mode, (cudaStream_t)stream);
 }

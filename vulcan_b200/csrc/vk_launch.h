@@ -4,10 +4,28 @@
 #include <atomic>
 #include <cstring>
 #include <cuda_runtime.h>
+#include "vk_math.cuh"
 
 namespace vk {
 // number of kernels this library has launched since load (vk_launch_count)
 extern std::atomic<unsigned long long> g_launches;
+// process-wide default of vkVolume::math_mode for entry points without a volume argument
+extern std::atomic<int> g_default_math_mode;
+
+// rows 0..2 of a column-major 4x4 (vulcan::Matrix4f) as row-major 3x4
+inline void rows34(const float* colmajor, float* out12) {
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 4; ++c) out12[r * 4 + c] = colmajor[c * 4 + r];
+}
+
+// Divisor descriptor for vk::divc.  The first use of a divisor value in the process runs the
+// exhaustive device check (all 2^32 dividends against __fdiv_rn, ~1 ms) on `stream` and waits
+// for it; later uses hit a host-side cache.  Returns fast = 0 (plain IEEE division) if the
+// check fails or cannot run.
+Div make_div(float d, cudaStream_t stream);
+
+// number of SMs of the current device (cached per device)
+int sm_count();
 }  // namespace vk
 
 #define VK_COUNT_LAUNCH() (::vk::g_launches.fetch_add(1, std::memory_order_relaxed))

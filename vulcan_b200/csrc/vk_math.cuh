@@ -1,12 +1,22 @@
-// vk_math.cuh — device math with a fixed, contraction-free evaluation order.
+// vk_math.cuh — device math with a fixed evaluation order and a fixed fusion pattern.
 //
-// Every formula on the hot path is a knife-edge decision somewhere (which block a
-// DDA step lands in, which pixel int(uv) picks, `distance > -tau`), so results are
-// only reproducible if each multiply and add rounds exactly where the reference's
-// source says it does.  The __f*_rn intrinsics are never fused by nvcc, so the
-// functions below evaluate the reference's expressions operation by operation in
-// source order; the CPU oracle (oracle/, built with -ffp-contract=off) and the
-// reference built with -fmad=false produce the same bits.
+// Every formula on the hot path is a knife-edge decision somewhere (which block a DDA
+// step lands in, which pixel int(uv) picks, `distance > -tau`), so results are only
+// reproducible if each multiply and add rounds exactly where the reference's machine code
+// rounds.  Nothing here is left to the compiler: every operation is an explicit
+// __fmul_rn / __fadd_rn / __fmaf_rn (never re-fused or split by nvcc), in one of two modes
+//
+//   FP<true>   VK_MATH_REFERENCE: the mul+add pairs that nvcc 12.9 contracts into FFMA when it
+//              builds the reference's own sources with its default flags (-O3, -fmad=true) are
+//              fused here in the same places.  The pattern was read off the SASS of that build
+//              (oracle/_ref/libvulcan_ref.so, see DESIGN.md "FMA map"); each helper below cites
+//              the reference expression it mirrors.
+//   FP<false>  VK_MATH_STRICT: one rounding per source operation (the reference built with
+//              -fmad=false, and the CPU oracle built with -ffp-contract=off).
+//
+// Both modes use the same association order, so a helper is written once in terms of
+// mad / nmad / msub.  Division, reciprocal and square root are IEEE correctly rounded in the
+// reference (nvcc defaults -prec-div=true -prec-sqrt=true) and here.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -19,72 +29,156 @@ __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b);
 __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float rcp(float a) { return __frcp_rn(a); }   // == 1.0f / a, correctly rounded
 
-struct Vec3 { float x, y, z; };
-
-// Rows 0..2 of a column-major 4x4 matrix, loaded once per kernel.
-struct Mat34 {
-  float r[3][4];
-  __device__ __forceinline__ void load(const float* m) {
-#pragma unroll
-    for (int i = 0; i < 3; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) r[i][j] = m[j * 4 + i];
+template <bool FMA>
+struct FP {
+  // a * b + c
+  static __device__ __forceinline__ float mad(float a, float b, float c) {
+    return FMA ? __fmaf_rn(a, b, c) : __fadd_rn(__fmul_rn(a, b), c);
+  }
+  // c - a * b
+  static __device__ __forceinline__ float nmad(float a, float b, float c) {
+    return FMA ? __fmaf_rn(-a, b, c) : __fsub_rn(c, __fmul_rn(a, b));
+  }
+  // a * b - c
+  static __device__ __forceinline__ float msub(float a, float b, float c) {
+    return FMA ? __fmaf_rn(a, b, -c) : __fsub_rn(__fmul_rn(a, b), c);
   }
 };
 
-// Transform::operator*(Vector4f) (include/vulcan/transform.h:43-58):
-// M(r,0)*x + M(r,1)*y + M(r,2)*z + M(r,3)*w, left to right.
-__device__ __forceinline__ Vec3 xform(const Mat34& M, float x, float y, float z, float w) {
+struct Vec3 { float x, y, z; };
+
+// Rows 0..2 of a 4x4 transform, row-major 3x4 (the host passes rows, see rows34()).
+struct Mat34 {
+  float r[3][4];
+  __device__ __forceinline__ void load(const float* rows) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) r[i][j] = rows[i * 4 + j];
+  }
+};
+
+// Transform::operator*(Vector4f) (include/vulcan/transform.h:43-58), one row:
+//   M(r,0)*x + M(r,1)*y + M(r,2)*z + M(r,3)*w   evaluated left to right.
+// Reference SASS: FMUL y*m1; FFMA x*m0 + .; FFMA z*m2 + .; then w == 1: FADD m3,
+// w == 0: FFMA 0*m3 + .
+template <bool F>
+__device__ __forceinline__ float row_acc(const float* m, float x, float y, float z) {
+  return FP<F>::mad(z, m[2], FP<F>::mad(x, m[0], mul(y, m[1])));
+}
+template <bool F>
+__device__ __forceinline__ Vec3 xform1(const Mat34& M, float x, float y, float z) {  // w = 1
   Vec3 o;
-  o.x = add(add(add(mul(M.r[0][0], x), mul(M.r[0][1], y)), mul(M.r[0][2], z)), mul(M.r[0][3], w));
-  o.y = add(add(add(mul(M.r[1][0], x), mul(M.r[1][1], y)), mul(M.r[1][2], z)), mul(M.r[1][3], w));
-  o.z = add(add(add(mul(M.r[2][0], x), mul(M.r[2][1], y)), mul(M.r[2][2], z)), mul(M.r[2][3], w));
+  o.x = add(row_acc<F>(M.r[0], x, y, z), M.r[0][3]);
+  o.y = add(row_acc<F>(M.r[1], x, y, z), M.r[1][3]);
+  o.z = add(row_acc<F>(M.r[2], x, y, z), M.r[2][3]);
+  return o;
+}
+template <bool F>
+__device__ __forceinline__ float xform1_z(const Mat34& M, float x, float y, float z) {
+  return add(row_acc<F>(M.r[2], x, y, z), M.r[2][3]);
+}
+template <bool F>
+__device__ __forceinline__ Vec3 xform0(const Mat34& M, float x, float y, float z) {  // w = 0
+  Vec3 o;
+  o.x = FP<F>::mad(0.0f, M.r[0][3], row_acc<F>(M.r[0], x, y, z));
+  o.y = FP<F>::mad(0.0f, M.r[1][3], row_acc<F>(M.r[1], x, y, z));
+  o.z = FP<F>::mad(0.0f, M.r[2][3], row_acc<F>(M.r[2], x, y, z));
   return o;
 }
 
-// Projection::Project (include/vulcan/projection.h:63-71)
+// Projection::Project (include/vulcan/projection.h:63-71):
+//   inv_w = 1.0f / X.z;  u = inv_w * fx * X.x + cx     (FMUL inv_w*fx; FFMA . * X.x + cx)
+template <bool F>
 __device__ __forceinline__ void project(const vkProjection& P, const Vec3& X, float& u, float& v) {
-  const float inv_w = fdiv(1.0f, X.z);
-  u = add(mul(mul(inv_w, P.fx), X.x), P.cx);
-  v = add(mul(mul(inv_w, P.fy), X.y), P.cy);
+  const float inv_w = rcp(X.z);
+  u = FP<F>::mad(mul(inv_w, P.fx), X.x, P.cx);
+  v = FP<F>::mad(mul(inv_w, P.fy), X.y, P.cy);
 }
 
-// Projection::Unproject(uv) (include/vulcan/projection.h:80-89)
-__device__ __forceinline__ Vec3 unproject(const vkProjection& P, float u, float v) {
-  const float ifx = fdiv(1.0f, P.fx);
-  const float ify = fdiv(1.0f, P.fy);
-  Vec3 o;
-  o.x = sub(mul(ifx, u), mul(P.cx, ifx));
-  o.y = sub(mul(ify, v), mul(P.cy, ify));
-  o.z = 1.0f;
-  return o;
-}
+// Projection::Unproject(uv) (include/vulcan/projection.h:80-89):
+//   ifx * u - cx * ifx                                  (FMUL cx*ifx; FFMA ifx*u - .)
+struct Unprojector {
+  float ifx, ify, cxi, cyi;
+  __device__ __forceinline__ void init(const vkProjection& P) {
+    ifx = rcp(P.fx);
+    ify = rcp(P.fy);
+    cxi = mul(P.cx, ifx);
+    cyi = mul(P.cy, ify);
+  }
+  template <bool F>
+  __device__ __forceinline__ float x(float u) const { return FP<F>::msub(ifx, u, cxi); }
+  template <bool F>
+  __device__ __forceinline__ float y(float v) const { return FP<F>::msub(ify, v, cyi); }
+};
 
-// Vector3f::Dot (include/vulcan/matrix.h:158-171): result starts at 0.
+// Vector3f::Dot (include/vulcan/matrix.h:158-171): r = 0; r += a[i] * b[i]  (FFMA chain from 0)
+template <bool F>
 __device__ __forceinline__ float dot3(const Vec3& a, const Vec3& b) {
-  float r = 0.0f;
-  r = add(r, mul(a.x, b.x));
-  r = add(r, mul(a.y, b.y));
-  r = add(r, mul(a.z, b.z));
+  float r = FP<F>::mad(a.x, b.x, 0.0f);
+  r = FP<F>::mad(a.y, b.y, r);
+  r = FP<F>::mad(a.z, b.z, r);
   return r;
 }
 
-// Vector3f::Normalize (include/vulcan/matrix.h:132-141): scale by 1/sqrt(dot).
+// Vector3f::Normalize (include/vulcan/matrix.h:132-141): scale by 1 / sqrt(dot)
+template <bool F>
 __device__ __forceinline__ Vec3 normalized(const Vec3& a) {
-  const float inv = fdiv(1.0f, __fsqrt_rn(dot3(a, a)));
+  const float inv = rcp(__fsqrt_rn(dot3<F>(a, a)));
   Vec3 o = {mul(a.x, inv), mul(a.y, inv), mul(a.z, inv)};
   return o;
-}
-
-// Block hash, Q1 (src/volume.cu:168-180, src/tracer.cu:151-155)
-__device__ __forceinline__ uint32_t block_hash(int bx, int by, int bz, uint32_t K) {
-  return (((uint32_t)bx * 73856093u) ^ ((uint32_t)by * 19349669u) ^ ((uint32_t)bz * 83492791u)) % K;
 }
 
 // vulcan::min / vulcan::max (include/vulcan/math.h:9-21)
 __device__ __forceinline__ float vmin(float a, float b) { return (b < a) ? b : a; }
 __device__ __forceinline__ float vmax(float a, float b) { return (b > a) ? b : a; }
+
+// ---- correctly rounded division by a loop-invariant divisor ------------------------------
+// q = RN(x / d) from r = RN(1 / d) with one FMA residual step:
+//   q0 = RN(x * r);  e = x - q0 * d (exact, FMA);  q = RN(q0 + e * r)
+// For a given d this is either right for every x in the guarded range or it is not; the host
+// proves it per divisor by running it against __fdiv_rn over ALL 2^32 bit patterns of x once
+// (vk_div_prepare, vk_divcheck.cu) and clears `fast` otherwise.  Outside the guarded range
+// (tiny / huge / non-finite quotients) the IEEE division instruction sequence is used.
+struct Div {
+  float d, r;
+  int fast;
+};
+__device__ __forceinline__ float divc(float x, const Div& dv) {
+  const float q0 = __fmul_rn(x, dv.r);
+  const float a = fabsf(q0), ax = fabsf(x);
+  // both the quotient and the dividend well inside the normal range: the residual e is then
+  // exactly representable (no underflow) and nothing overflows
+  if (dv.fast && a > 1e-25f && a < 1e25f && ax > 1e-25f && ax < 1e25f) {
+    const float e = __fmaf_rn(-q0, dv.d, x);
+    return __fmaf_rn(e, dv.r, q0);
+  }
+  return __fdiv_rn(x, dv.d);
+}
+
+// ---- block hash, Q1 (src/volume.cu:168-180, src/tracer.cu:151-155) -------------------------
+// h = (bx*P1 ^ by*P2 ^ bz*P3) % K with a precomputed multiplier instead of a hardware-less
+// 32-bit modulo (~25 instructions): m = floor(2^32 / K); q = umulhi(h, m) <= h / K < q + 2.
+struct Mod {
+  uint32_t K, m;
+};
+__host__ __device__ __forceinline__ Mod make_mod(uint32_t K) {
+  Mod o;
+  o.K = K;
+  o.m = (K <= 1) ? 0xffffffffu : (uint32_t)(0x100000000ull / K);
+  return o;
+}
+__device__ __forceinline__ uint32_t fastmod(uint32_t h, const Mod& md) {
+  uint32_t r = h - __umulhi(h, md.m) * md.K;
+  if (r >= md.K) r -= md.K;
+  if (r >= md.K) r -= md.K;
+  return r;
+}
+__device__ __forceinline__ uint32_t block_hash(int bx, int by, int bz, const Mod& md) {
+  return fastmod(((uint32_t)bx * 73856093u) ^ ((uint32_t)by * 19349669u) ^ ((uint32_t)bz * 83492791u), md);
+}
 
 // 64-bit image of a block coordinate triple (pad forced to 0) for register compares.
 __device__ __forceinline__ unsigned long long pack_block(int bx, int by, int bz) {
@@ -105,6 +199,11 @@ __device__ __forceinline__ unsigned long long entry_block(const int4& e) {
   // x = block.x | block.y<<16, y = block.z | pad<<16 ; pad is not initialised by the
   // reference (include/vulcan/block.h:83-85), always 0 here.
   return (unsigned long long)(uint32_t)e.x | ((unsigned long long)((uint32_t)e.y & 0xffffu) << 32);
+}
+__device__ __forceinline__ void entry_origin(const int4& e, int& ox, int& oy, int& oz) {
+  ox = (int)(int16_t)(e.x & 0xffff);
+  oy = (int)(int16_t)((uint32_t)e.x >> 16);
+  oz = (int)(int16_t)(e.y & 0xffff);
 }
 
 // ---- spatial sharding (no reference counterpart) ------------------

@@ -1,0 +1,104 @@
+// vk_runtime.cu — library-wide host state: launch counter, default math mode, SM count and
+// the per-divisor proof that vk::divc is correctly rounded.
+#include "vk_launch.h"
+
+#include <map>
+#include <mutex>
+
+namespace vk {
+
+std::atomic<unsigned long long> g_launches{0};
+std::atomic<int> g_default_math_mode{VK_MATH_REFERENCE};
+
+// Compares the one-step FMA division against the IEEE division for every dividend bit pattern.
+__global__ void __launch_bounds__(256) vk_divcheck_kernel(float d, float r, unsigned int* mismatches) {
+  Div dv;
+  dv.d = d;
+  dv.r = r;
+  dv.fast = 1;
+  unsigned int bad = 0;
+  const unsigned int stride = gridDim.x * blockDim.x;
+  unsigned int bits = blockIdx.x * blockDim.x + threadIdx.x;
+  // 2^32 patterns, grid-strided; stride divides 2^32 so every thread runs the same trip count
+  const unsigned int trips = (unsigned int)(0x100000000ull / stride);
+  for (unsigned int k = 0; k < trips; ++k, bits += stride) {
+    const float x = __uint_as_float(bits);
+    const float a = divc(x, dv);
+    const float b = __fdiv_rn(x, d);
+    // NaNs compare by class, everything else by bits
+    const bool same = (__float_as_uint(a) == __float_as_uint(b)) || (a != a && b != b);
+    bad += same ? 0u : 1u;
+    if (!same) atomicMin(mismatches + 1, bits);  // smallest failing pattern, for diagnostics
+  }
+  bad = __reduce_add_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0 && bad) atomicAdd(mismatches, bad);
+}
+
+static std::mutex g_div_mutex;
+static std::map<uint32_t, int> g_div_cache;
+static unsigned int g_div_last[2] = {0, 0};  // mismatch count / smallest failing dividend of the last check
+
+Div make_div(float d, cudaStream_t stream) {
+  Div dv;
+  dv.d = d;
+  dv.r = 1.0f / d;  // host division is IEEE correctly rounded
+  dv.fast = 0;
+  uint32_t bits;
+  memcpy(&bits, &d, 4);
+  const uint32_t mant = bits & 0x7fffffu;
+  const uint32_t expo = (bits >> 23) & 0xffu;
+  if (!(d == d) || expo < 64 || expo > 190 || mant == 0x7fffffu) return dv;  // keep it simple: moderate, normal
+  std::lock_guard<std::mutex> lock(g_div_mutex);
+  auto it = g_div_cache.find(bits);
+  if (it != g_div_cache.end()) {
+    dv.fast = it->second;
+    return dv;
+  }
+  unsigned int* dev = nullptr;
+  unsigned int host[2] = {1u, 0xffffffffu};
+  int ok = 0;
+  if (cudaMalloc((void**)&dev, 2 * sizeof(unsigned int)) == cudaSuccess) {
+    if (cudaMemcpyAsync(dev, host, sizeof(host), cudaMemcpyHostToDevice, stream) == cudaSuccess &&
+        cudaMemsetAsync(dev, 0, sizeof(unsigned int), stream) == cudaSuccess) {
+      vk_divcheck_kernel<<<4096, 256, 0, stream>>>(d, dv.r, dev);  // 2^20 threads x 4096 trips
+      VK_COUNT_LAUNCH();
+      if (cudaMemcpyAsync(host, dev, sizeof(host), cudaMemcpyDeviceToHost, stream) == cudaSuccess &&
+          cudaStreamSynchronize(stream) == cudaSuccess)
+        ok = (host[0] == 0) ? 1 : 0;
+    }
+    cudaFree(dev);
+  }
+  g_div_last[0] = host[0];
+  g_div_last[1] = host[1];
+  cudaGetLastError();
+  g_div_cache[bits] = ok;
+  dv.fast = ok;
+  return dv;
+}
+
+int sm_count() {
+  static std::atomic<int> cached{0};
+  int n = cached.load();
+  if (n > 0) return n;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return 148;
+  cached.store(prop.multiProcessorCount);
+  return prop.multiProcessorCount;
+}
+
+}  // namespace vk
+
+extern "C" int vk_version(void) { return 110; }
+extern "C" unsigned long long vk_launch_count(void) { return vk::g_launches.load(); }
+extern "C" int vk_set_default_math_mode(int mode) {
+  if (mode != VK_MATH_REFERENCE && mode != VK_MATH_STRICT) return VK_E_INVALID;
+  vk::g_default_math_mode.store(mode);
+  return 0;
+}
+extern "C" int vk_get_default_math_mode(void) { return vk::g_default_math_mode.load(); }
+
+// Test hook: runs the exhaustive division check for `d` and reports whether the fast path is on.
+extern "C" int vk_div_prepare(float d, void* stream) { return vk::make_div(d, (cudaStream_t)stream).fast; }
+extern "C" void vk_div_last_check(unsigned int out[2]) { out[0] = vk::g_div_last[0]; out[1] = vk::g_div_last[1]; }

@@ -2,14 +2,24 @@
 //
 // Reference (src/tracer.cpp:41-47): ComputePatches (20-barrier scan + blocking D2H read
 // of the patch count) -> FillKernel -> ComputeBounds (float CAS loops) -> ComputePoints
-// (16x16 tiles, scalar loads, a full hash walk per trilinear tap on block faces) ->
-// ComputeNormals.
+// (16x16 tiles, scalar loads, two inlined copies of the 8-tap interpolation with colour, a full
+// hash walk per trilinear tap on block faces) -> ComputeNormals.
 //
-// Here: the visible blocks are rasterised straight into the 80x60 bounds grid with
-// native integer atomicMin/atomicMax (positive floats order like ints), no patch list
-// and no host read-back; the ray marcher maps a warp to an 8x4 pixel tile, loads hash
-// entries and voxels with 128-bit / read-only loads and memoises the last block lookup
-// per lane; the step-wise entry points of include/vulcan/tracer.cuh are kept as well.
+// Here:
+//   vk_bounds_kernel    the visible blocks are rasterised straight into the 80x60 bounds grid:
+//                       per-CTA privatised grid in shared memory (native integer atomicMin/Max on
+//                       float bits), merged into the global grid by the cells a CTA touched.  No
+//                       patch list, no host read-back of a count.
+//   vk_raycast_kernel   a warp marches an 8x4 pixel tile.  The march is a per-lane state machine
+//                       (MARCH -> REFINE -> DONE) so that the trilinear interpolation exists once in
+//                       the instruction stream and lanes at different phases share it; the
+//                       interpolation fetches only the 8 distances (the reference's colour blend is
+//                       evaluated once per ray, for the last interpolation, after the march);
+//                       taps that cross a block face resolve each distinct neighbour block once;
+//                       the hash modulo and the divisions by block / voxel length are strength
+//                       reduced (vk_math.cuh) - all bit-exact with the reference's arithmetic.
+//   vk_normals_kernel   32x8 tile + 2 px halo in shared memory.
+// The step-wise entry points of include/vulcan/tracer.cuh are kept as well.
 #include "vk_math.cuh"
 #include "vk_launch.h"
 #include <cfloat>
@@ -19,7 +29,7 @@ namespace vk {
 // ---- ray bounds -------------------------------------------------------------------
 
 struct BlockBox {
-  short bminx, bminy, bmaxx, bmaxy;
+  int bminx, bminy, bmaxx, bmaxy;
   float zlo, zhi;
   int gx, gy;
 };
@@ -42,35 +52,52 @@ __device__ __forceinline__ T vclamp(T v, T lo, T hi) {
   return (a < hi) ? a : hi;
 }
 
-// body of ComputePatchesKernel (src/tracer.cu:13-66) for one block
-__device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw, const vkProjection& proj,
-                                              float block_length, float min_depth, float max_depth,
-                                              int image_w, int image_h, int bw, int bh) {
-  const int ox = (int)(int16_t)(ent.x & 0xffff);
-  const int oy = (int)(int16_t)((uint32_t)ent.x >> 16);
-  const int oz = (int)(int16_t)(ent.y & 0xffff);
-  short bmaxx = -1, bmaxy = -1;
-  short bminx = (short)bw, bminy = (short)bh;
+// `(short)floorf(u)` as the reference's machine code does it: F2I to a saturating s32
+// (NaN -> 0), then the low 16 bits (VIMNMX.S16x2 on the s32 register).
+__device__ __forceinline__ int to_short(float f) { return (int)(short)(int)f; }
+
+struct BoundsParams {
+  const int32_t* visible;
+  const int32_t* count;
+  const vkHashEntry* entries;
+  float Tcw[12];
+  vkProjection proj;
+  float block_length, min_depth, max_depth;
+  Div image_w, image_h;
+  int bw, bh;
+  float* bounds;
+};
+
+// body of ComputePatchesKernel (src/tracer.cu:13-66) for one block.
+// FMA map: corner = L * (i + origin) FMUL; Tcw * corner rows as xform1; Project;
+//          u' = bounds_width * u / image_width   FMUL then IEEE division.
+template <bool F>
+__device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw, const BoundsParams& p) {
+  int ox, oy, oz;
+  entry_origin(ent, ox, oy, oz);
+  int bmaxx = -1, bmaxy = -1;
+  int bminx = (short)p.bw, bminy = (short)p.bh;
   float zlo = +FLT_MAX, zhi = -FLT_MAX;
+  const int cw = (short)(p.bw - 1), ch = (short)(p.bh - 1);
   for (int z = 0; z <= 1; ++z) {
-    const float Z = mul(block_length, (float)(z + oz));
+    const float Z = mul(p.block_length, (float)(z + oz));
     for (int y = 0; y <= 1; ++y) {
-      const float Y = mul(block_length, (float)(y + oy));
+      const float Y = mul(p.block_length, (float)(y + oy));
       for (int x = 0; x <= 1; ++x) {
-        const float X = mul(block_length, (float)(x + ox));
-        const Vec3 Xc = xform(Tcw, X, Y, Z, 1.0f);
+        const float X = mul(p.block_length, (float)(x + ox));
+        const Vec3 Xc = xform1<F>(Tcw, X, Y, Z);
         float u, v;
-        project(proj, Xc, u, v);
-        u = fdiv(mul((float)bw, u), (float)image_w);
-        v = fdiv(mul((float)bh, v), (float)image_h);
-        const short fu = (short)floorf(u), fv = (short)floorf(v);
-        const short cu = (short)ceilf(u), cv = (short)ceilf(v);
-        bminx = vclamp<short>((fu < bminx) ? fu : bminx, 0, (short)(bw - 1));
-        bminy = vclamp<short>((fv < bminy) ? fv : bminy, 0, (short)(bh - 1));
-        bmaxx = vclamp<short>((cu > bmaxx) ? cu : bmaxx, 0, (short)(bw - 1));
-        bmaxy = vclamp<short>((cv > bmaxy) ? cv : bmaxy, 0, (short)(bh - 1));
-        zlo = vclamp<float>(vmin(Xc.z, zlo), min_depth, max_depth);
-        zhi = vclamp<float>(vmax(Xc.z, zhi), min_depth, max_depth);
+        project<F>(p.proj, Xc, u, v);
+        u = divc(mul((float)p.bw, u), p.image_w);
+        v = divc(mul((float)p.bh, v), p.image_h);
+        const int fu = to_short(floorf(u)), fv = to_short(floorf(v));
+        const int cu = to_short(ceilf(u)), cv = to_short(ceilf(v));
+        bminx = vclamp<int>((fu < bminx) ? fu : bminx, 0, cw);
+        bminy = vclamp<int>((fv < bminy) ? fv : bminy, 0, ch);
+        bmaxx = vclamp<int>((cu > bmaxx) ? cu : bmaxx, 0, cw);
+        bmaxy = vclamp<int>((cv > bmaxy) ? cv : bmaxy, 0, ch);
+        zlo = vclamp<float>(vmin(Xc.z, zlo), p.min_depth, p.max_depth);
+        zhi = vclamp<float>(vmax(Xc.z, zhi), p.min_depth, p.max_depth);
       }
     }
   }
@@ -84,40 +111,46 @@ __device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw,
   return b;
 }
 
-struct BoundsParams {
-  const int32_t* visible;
-  const int32_t* count;
-  const vkHashEntry* entries;
-  float Tcw[12];
-  vkProjection proj;
-  float block_length, min_depth, max_depth;
-  int image_w, image_h, bw, bh;
-  float* bounds;
-};
-
-// K10 + K11 fused: the union of a block's patches is the cell rectangle
-// [bmin, min(bmax, bmin + 16*g - 1)] (src/tracer.cu:67-86), merged with integer atomics.
-__global__ void __launch_bounds__(256) vk_bounds_kernel(const BoundsParams p) {
+// K13 + K10 + K11 fused: the union of a block's patches is the cell rectangle
+// [bmin, min(bmax, bmin + 16*g - 1)] (src/tracer.cu:67-86).  The global grid must hold
+// (+FLT_MAX, -FLT_MAX) on entry (vk_reset_bounds).  Each CTA accumulates into a private copy
+// of the grid in shared memory and then merges the cells it touched.
+template <bool F>
+__global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
+  extern __shared__ float s_cells[];  // bw*bh*2
+  const int ncell = p.bw * p.bh;
+  for (int i = threadIdx.x; i < ncell; i += blockDim.x) {
+    s_cells[2 * i] = +FLT_MAX;
+    s_cells[2 * i + 1] = -FLT_MAX;
+  }
+  __syncthreads();
   const int n = *p.count;
   Mat34 Tcw;
-#pragma unroll
-  for (int r = 0; r < 3; ++r)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) Tcw.r[r][c] = p.Tcw[r * 4 + c];
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  Tcw.load(p.Tcw);
+  // contiguous chunk of the visible list per CTA: neighbouring list entries are neighbouring
+  // blocks (the list is built tile by tile), so a CTA touches few cells
+  const int per_cta = (n + gridDim.x - 1) / gridDim.x;
+  const int begin = blockIdx.x * per_cta;
+  const int end = min(n, begin + per_cta);
+  for (int i = begin + threadIdx.x; i < end; i += blockDim.x) {
     const int e = __ldg(p.visible + i);
     const int4 ent = ld_entry(p.entries + e);
-    const BlockBox b = block_box(ent, Tcw, p.proj, p.block_length, p.min_depth, p.max_depth, p.image_w,
-                                 p.image_h, p.bw, p.bh);
+    const BlockBox b = block_box<F>(ent, Tcw, p);
     if (b.gx * b.gy == 0) continue;
-    const int x1 = min((int)b.bmaxx, (int)b.bminx + 16 * b.gx - 1);
-    const int y1 = min((int)b.bmaxy, (int)b.bminy + 16 * b.gy - 1);
+    const int x1 = min(b.bmaxx, b.bminx + 16 * b.gx - 1);
+    const int y1 = min(b.bmaxy, b.bminy + 16 * b.gy - 1);
     for (int y = b.bminy; y <= y1; ++y)
       for (int x = b.bminx; x <= x1; ++x) {
-        float* cell = p.bounds + 2 * (y * p.bw + x);
+        float* cell = s_cells + 2 * (y * p.bw + x);
         atomic_min_float(cell, b.zlo);
         atomic_max_float(cell + 1, b.zhi);
       }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < ncell; i += blockDim.x) {
+    const float lo = s_cells[2 * i], hi = s_cells[2 * i + 1];
+    if (lo != +FLT_MAX) atomic_min_float(p.bounds + 2 * i, lo);
+    if (hi != -FLT_MAX) atomic_max_float(p.bounds + 2 * i + 1, hi);
   }
 }
 
@@ -128,21 +161,19 @@ __global__ void vk_reset_bounds_kernel(float2* bounds, int count) {
 
 // ComputePatchesKernel (src/tracer.cu:13-87) with a warp-aggregated append in place of
 // the shared-memory scan; patch order is unspecified in the reference too (Q7-like).
+template <bool F>
 __global__ void __launch_bounds__(256) vk_patches_kernel(const int* indices, const vkHashEntry* entries,
                                                          const BoundsParams p, int block_count,
                                                          vkPatch* patches, int* patch_count) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
   Mat34 Tcw;
-#pragma unroll
-  for (int r = 0; r < 3; ++r)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) Tcw.r[r][c] = p.Tcw[r * 4 + c];
+  Tcw.load(p.Tcw);
   BlockBox b;
   b.gx = b.gy = 0;
   if (i < block_count) {
     const int4 ent = ld_entry(entries + indices[i]);
-    b = block_box(ent, Tcw, p.proj, p.block_length, p.min_depth, p.max_depth, p.image_w, p.image_h, p.bw, p.bh);
+    b = block_box<F>(ent, Tcw, p);
   }
   const int cnt = b.gx * b.gy;
   // inclusive warp scan of cnt
@@ -194,8 +225,9 @@ struct TraceParams {
   const vkHashEntry* entries;
   const vkVoxel* voxels;
   const float* bounds;
-  uint32_t K;
-  float block_length, voxel_length, trunc;
+  Mod K;
+  Div block_length, voxel_length;
+  float trunc;
   float Twc[12], Tcw[12];
   vkProjection proj;
   float* depths;
@@ -214,174 +246,278 @@ struct Lookup {
 
 // `while (entry.block != b && entry.HasNext()) entry = entries[entry.next];`
 // `entry.block == b && entry.IsAllocated()`  (src/tracer.cu:363-371, :151-175)
+__device__ __forceinline__ int lookup_block(const TraceParams& p, int bx, int by, int bz) {
+  const unsigned long long key = pack_block(bx, by, bz);
+  int4 e = ld_entry(p.entries + block_hash(bx, by, bz, p.K));
+  while (entry_block(e) != key && e.w != -1) e = ld_entry(p.entries + e.w);
+  return (entry_block(e) == key) ? e.z : -1;
+}
 __device__ __forceinline__ int find_data(const TraceParams& p, Lookup& memo, int bx, int by, int bz) {
   const unsigned long long key = pack_block(bx, by, bz);
   if (key == memo.key) return memo.data;
-  int4 e = ld_entry(p.entries + block_hash(bx, by, bz, p.K));
-  while (entry_block(e) != key && e.w != -1) e = ld_entry(p.entries + e.w);
-  const int data = (entry_block(e) == key) ? e.z : -1;
+  const int data = lookup_block(p, bx, by, bz);
   memo.key = key;
   memo.data = data;
   return data;
 }
 
-struct Tap {
-  float distance;
-  float r, g, b;
-  int cw;
+__device__ __forceinline__ const uint32_t* voxel_words(const TraceParams& p, int data, int voxel_offset) {
+  // Voxel is 20 bytes, 4-byte aligned: distance, rgb, (dw | cw << 16)
+  return reinterpret_cast<const uint32_t*>(p.voxels) + ((size_t)data * VK_BLOCK_VOXELS + (size_t)voxel_offset) * 5;
+}
+
+// The 8 taps of GetInterpolatedDistance (src/tracer.cu:190-256): per axis the tap pair
+// (i0, i0 + 1), i0 = floor(w - 0.5) in [-1, 7]; a tap outside [0, 8) lives in the neighbouring
+// block (GetVoxel, src/tracer.cu:114-188: one wrap per axis), which is looked up ONCE per
+// distinct neighbour instead of once per tap; a missing neighbour reads as Voxel::Empty() (Q16).
+struct Taps {
+  int data[8];   // voxel-block id per tap (index = z*4 + y*2 + x), -1 = empty
+  int off[8];    // voxel offset inside that block
+  float w1x, w1y, w1z;
 };
 
-__device__ __forceinline__ Tap load_tap(const TraceParams& p, int data, int voxel_offset) {
-  // Voxel is 20 bytes, 4-byte aligned: distance, rgb, (dw | cw << 16)
-  const uint32_t* w = reinterpret_cast<const uint32_t*>(p.voxels) +
-                      ((size_t)data * VK_BLOCK_VOXELS + (size_t)voxel_offset) * 5;
-  Tap t;
-  t.distance = __uint_as_float(__ldg(w));
-  t.r = __uint_as_float(__ldg(w + 1));
-  t.g = __uint_as_float(__ldg(w + 2));
-  t.b = __uint_as_float(__ldg(w + 3));
-  t.cw = (int)(int16_t)(__ldg(w + 4) >> 16);
-  return t;
-}
-
-// GetVoxel (src/tracer.cu:114-188)
-__device__ __forceinline__ Tap get_voxel(const TraceParams& p, Lookup& memo, int bx, int by, int bz, int vx,
-                                         int vy, int vz) {
-  if (vx < 0) { --bx; vx += 8; } else if (vx >= 8) { ++bx; vx -= 8; }
-  if (vy < 0) { --by; vy += 8; } else if (vy >= 8) { ++by; vy -= 8; }
-  if (vz < 0) { --bz; vz += 8; } else if (vz >= 8) { ++bz; vz -= 8; }
-  const int data = find_data(p, memo, bx, by, bz);
-  if (data != -1) return load_tap(p, data, vz * 64 + vy * 8 + vx);
-  Tap t;  // Voxel::Empty()
-  t.distance = 1.0f; t.r = t.g = t.b = 0.0f; t.cw = 0;
-  return t;
-}
-
-// GetInterpolatedDistance (src/tracer.cu:190-315); Q15 colour weights, Q16 empty taps
-__device__ __forceinline__ void interpolate(const TraceParams& p, Lookup& memo, int bx, int by, int bz, int data,
-                                            const Vec3& pt, float& sdf, Vec3& color) {
-  const float wx = fdiv(sub(pt.x, mul((float)bx, p.block_length)), p.voxel_length);
-  const float wy = fdiv(sub(pt.y, mul((float)by, p.block_length)), p.voxel_length);
-  const float wz = fdiv(sub(pt.z, mul((float)bz, p.block_length)), p.voxel_length);
-  const int i0x = (int)floorf(sub(wx, 0.5f));
-  const int i0y = (int)floorf(sub(wy, 0.5f));
-  const int i0z = (int)floorf(sub(wz, 0.5f));
-  Tap v[8];  // index = z*4 + y*2 + x
-  if (i0x >= 0 && i0y >= 0 && i0z >= 0 && i0x < 7 && i0y < 7 && i0z < 7) {
+__device__ __forceinline__ void resolve_taps(const TraceParams& p, int bx, int by, int bz, int home, float wx,
+                                             float wy, float wz, Taps& t) {
+  const int i0x = (int)floorf(add(wx, -0.5f));
+  const int i0y = (int)floorf(add(wy, -0.5f));
+  const int i0z = (int)floorf(add(wz, -0.5f));
+  // w1 = w - (i0 + 0.5)  (src/tracer.cu:258-261)
+  t.w1x = sub(wx, add((float)i0x, 0.5f));
+  t.w1y = sub(wy, add((float)i0y, 0.5f));
+  t.w1z = sub(wz, add((float)i0z, 0.5f));
+  // block offset and in-block coordinate of tap 0 / tap 1 per axis
+  int ox[2], oy[2], oz[2], cx[2], cy[2], cz[2];
+#define VK_AXIS(i0, o, c)                                   \
+  o[0] = (i0 < 0) ? -1 : 0;  c[0] = (i0 < 0) ? i0 + 8 : i0; \
+  o[1] = (i0 + 1 >= 8) ? 1 : 0;  c[1] = (i0 + 1 >= 8) ? i0 + 1 - 8 : i0 + 1;
+  VK_AXIS(i0x, ox, cx)
+  VK_AXIS(i0y, oy, cy)
+  VK_AXIS(i0z, oz, cz)
+#undef VK_AXIS
+  // axes on which the two taps lie in different blocks
+  const int cross = ((ox[0] != ox[1]) ? 1 : 0) | ((oy[0] != oy[1]) ? 2 : 0) | ((oz[0] != oz[1]) ? 4 : 0);
 #pragma unroll
-    for (int c = 0; c < 8; ++c)
-      v[c] = load_tap(p, data, (i0z + (c >> 2)) * 64 + (i0y + ((c >> 1) & 1)) * 8 + (i0x + (c & 1)));
-  } else {
+  for (int c = 0; c < 8; ++c) {
+    const int tx = c & 1, ty = (c >> 1) & 1, tz = c >> 2;
+    t.off[c] = cz[tz] * 64 + cy[ty] * 8 + cx[tx];
+    const int r = c & cross;  // representative tap: same block as tap c
+    int d;
+    if (r == c) {
+      const int dx = ox[tx], dy = oy[ty], dz = oz[tz];
+      d = ((dx | dy | dz) == 0) ? home : lookup_block(p, bx + dx, by + dy, bz + dz);
+    } else {
+      d = t.data[0];
 #pragma unroll
-    for (int c = 0; c < 8; ++c)
-      v[c] = get_voxel(p, memo, bx, by, bz, i0x + (c & 1), i0y + ((c >> 1) & 1), i0z + (c >> 2));
+      for (int s = 1; s < 8; ++s)
+        if (s < c && (s & c) == s && r == s) d = t.data[s];
+    }
+    t.data[c] = d;
   }
-  const float w1x = sub(wx, add((float)i0x, 0.5f));
-  const float w1y = sub(wy, add((float)i0y, 0.5f));
-  const float w1z = sub(wz, add((float)i0z, 0.5f));
-  const float w0x = sub(1.0f, w1x), w0y = sub(1.0f, w1y), w0z = sub(1.0f, w1z);
+}
 
-  const float n00 = add(mul(v[0].distance, w0x), mul(v[1].distance, w1x));
-  const float n01 = add(mul(v[2].distance, w0x), mul(v[3].distance, w1x));
-  const float n10 = add(mul(v[4].distance, w0x), mul(v[5].distance, w1x));
-  const float n11 = add(mul(v[6].distance, w0x), mul(v[7].distance, w1x));
-  const float n0 = add(mul(n00, w0y), mul(n01, w1y));
-  const float n1 = add(mul(n10, w0y), mul(n11, w1y));
+// trilinear SDF (src/tracer.cu:265-280,312).
+// FMA map: n00 = v000*w0x + v001*w1x -> FMUL v001*w1x ; FFMA v000*w0x + .   (same for y and z)
+template <bool F>
+__device__ __forceinline__ float interp_distance(const TraceParams& p, const Taps& t) {
+  float n[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    n[c] = 1.0f;  // Voxel::Empty()
+    if (t.data[c] != -1) n[c] = __uint_as_float(__ldg(voxel_words(p, t.data[c], t.off[c])));
+  }
+  const float w0x = sub(1.0f, t.w1x), w0y = sub(1.0f, t.w1y), w0z = sub(1.0f, t.w1z);
+  const float n00 = FP<F>::mad(n[0], w0x, mul(n[1], t.w1x));
+  const float n01 = FP<F>::mad(n[2], w0x, mul(n[3], t.w1x));
+  const float n10 = FP<F>::mad(n[4], w0x, mul(n[5], t.w1x));
+  const float n11 = FP<F>::mad(n[6], w0x, mul(n[7], t.w1x));
+  const float n0 = FP<F>::mad(n00, w0y, mul(n01, t.w1y));
+  const float n1 = FP<F>::mad(n10, w0y, mul(n11, t.w1y));
+  return FP<F>::mad(n0, w0z, mul(n1, t.w1z));
+}
 
+// colour blend of the same 8 taps (src/tracer.cu:282-310), Q15: each weight is 1 if the trilinear
+// weight is non-zero and the voxel has colour, else 0.
+// FMA map: color += w * c -> FFMA chain from 0; color /= total -> reciprocal, FMUL.
+template <bool F>
+__device__ __forceinline__ Vec3 interp_color(const TraceParams& p, const Taps& t) {
+  const float w0x = sub(1.0f, t.w1x), w0y = sub(1.0f, t.w1y), w0z = sub(1.0f, t.w1z);
   float total = 0.0f;
   float cr = 0.0f, cg = 0.0f, cb = 0.0f;
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
-    const float wz_ = (c >> 2) ? w1z : w0z;
-    const float wy_ = ((c >> 1) & 1) ? w1y : w0y;
-    const float wx_ = (c & 1) ? w1x : w0x;
-    const float prod = mul(mul(mul(wz_, wy_), wx_), (v[c].cw > 0) ? 1.0f : 0.0f);
+    float r = 0.f, g = 0.f, b = 0.f;
+    int cw = 0;
+    if (t.data[c] != -1) {
+      const uint32_t* w = voxel_words(p, t.data[c], t.off[c]);
+      r = __uint_as_float(__ldg(w + 1));
+      g = __uint_as_float(__ldg(w + 2));
+      b = __uint_as_float(__ldg(w + 3));
+      cw = (int)(int16_t)(__ldg(w + 4) >> 16);
+    }
+    const float wz_ = (c >> 2) ? t.w1z : w0z;
+    const float wy_ = ((c >> 1) & 1) ? t.w1y : w0y;
+    const float wx_ = (c & 1) ? t.w1x : w0x;
+    const float prod = mul(mul(mul(wz_, wy_), wx_), (cw > 0) ? 1.0f : 0.0f);
     const float wgt = (prod != 0.0f) ? 1.0f : 0.0f;  // `a * b * c * (cw > 0) ? 1 : 0`
     total = add(total, wgt);
-    cr = add(cr, mul(v[c].r, wgt));
-    cg = add(cg, mul(v[c].g, wgt));
-    cb = add(cb, mul(v[c].b, wgt));
+    cr = FP<F>::mad(wgt, r, cr);
+    cg = FP<F>::mad(wgt, g, cg);
+    cb = FP<F>::mad(wgt, b, cb);
   }
   if (total > 0) {
-    const float inv = fdiv(1.0f, total);
+    const float inv = rcp(total);
     cr = mul(cr, inv); cg = mul(cg, inv); cb = mul(cb, inv);
   }
-  color.x = cr; color.y = cg; color.z = cb;
-  sdf = add(mul(n0, w0z), mul(n1, w1z));
+  Vec3 o = {cr, cg, cb};
+  return o;
 }
 
-// ComputePointsKernel (src/tracer.cu:317-451)
-template <bool KEYS>
-__global__ void __launch_bounds__(256) vk_raycast_kernel(const TraceParams p) {
+}  // namespace vk
+
+namespace vk {
+
+enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
+
+// ComputePointsKernel (src/tracer.cu:317-451).
+// FMA map (reference release SASS):
+//   Xcp = lo * Unproject(uv)             FMUL
+//   p   = Twc * (Xcp, 1), dir = Twc * (Xcp, 0)   shared row sum; FADD m3 / FFMA 0*m3 + .
+//   b   = floor(p / L)                   IEEE division
+//   w   = (p - b*L) / l                  FFMA -b*L + p ; IEEE division
+//   p  += dir * s                        FFMA dir*s + p   (s = L | max(l, trunc*sdf) | trunc*sdf)
+//   depth = (Tcw * (p,1)).z              xform1 row 2
+template <bool F, bool KEYS>
+__global__ void __launch_bounds__(64) vk_raycast_kernel(const TraceParams p) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int x = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
-  const int y = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
-  if (x >= p.w || y >= p.h) return;
+  // CTA tile 8x8 pixels, warp tile 8x4
+  const int x = blockIdx.x * 8 + (lane & 7);
+  const int y = blockIdx.y * 8 + warp * 4 + (lane >> 3);
+  const bool inside = (x < p.w && y < p.h);
 
-  const int px = p.bw * x / p.w;
-  const int py = p.bh * y / p.h;
-  const float2 bound = __ldg(reinterpret_cast<const float2*>(p.bounds) + py * p.bw + px);
+  float lo = 0.f, hi = 0.f;
+  if (inside) {
+    const int px = p.bw * x / p.w;
+    const int py = p.bh * y / p.h;
+    const float2 bound = __ldg(reinterpret_cast<const float2*>(p.bounds) + py * p.bw + px);
+    lo = bound.x;
+    hi = bound.y;
+  }
 
-  float depth = 0, final_depth = 0;
-  Vec3 color = {0.f, 0.f, 0.f};
+  int state = (inside && lo < hi) ? ST_MARCH : ST_DONE;
+  float final_depth = 0.f;
+  bool red = false;         // iteration cap hit: colour (1, 0, 0)
+  bool has_interp = false;  // an interpolation happened: colour comes from its taps
   bool owned_hit = false;
+  Vec3 pt = {0.f, 0.f, 0.f}, dir = {0.f, 0.f, 0.f};
+  Vec3 ipt = {0.f, 0.f, 0.f};  // point of the last interpolation
+  Mat34 Tcw;
+  Tcw.load(p.Tcw);
+  int iters = 0;
+  Lookup memo;
+  memo.key = ~0ull;
+  memo.data = -1;
 
-  if (bound.x < bound.y) {
-    Mat34 Twc, Tcw;
-#pragma unroll
-    for (int r = 0; r < 3; ++r)
-#pragma unroll
-      for (int c = 0; c < 4; ++c) { Twc.r[r][c] = p.Twc[r * 4 + c]; Tcw.r[r][c] = p.Tcw[r * 4 + c]; }
-    const Vec3 un = unproject(p.proj, (float)x + 0.5f, (float)y + 0.5f);
-    const Vec3 Xc = {mul(un.x, bound.x), mul(un.y, bound.x), mul(un.z, bound.x)};
-    Vec3 pt = xform(Twc, Xc.x, Xc.y, Xc.z, 1.0f);
-    const Vec3 dir = normalized(xform(Twc, Xc.x, Xc.y, Xc.z, 0.0f));
-    Lookup memo;
-    memo.key = ~0ull;
-    memo.data = -1;
-    depth = bound.x;
-    int iters = 0;
-    do {
-      const int bx = (int)floorf(fdiv(pt.x, p.block_length));
-      const int by = (int)floorf(fdiv(pt.y, p.block_length));
-      const int bz = (int)floorf(fdiv(pt.z, p.block_length));
+  if (state == ST_MARCH) {
+    Mat34 Twc;
+    Twc.load(p.Twc);
+    Unprojector un;
+    un.init(p.proj);
+    const float ux = un.x<F>(add((float)x, 0.5f)), uy = un.y<F>(add((float)y, 0.5f));
+    const float cx = mul(ux, lo), cy = mul(uy, lo), cz = lo;
+    pt = xform1<F>(Twc, cx, cy, cz);
+    dir = normalized<F>(xform0<F>(Twc, cx, cy, cz));
+  }
+
+  while (__any_sync(0xffffffffu, state != ST_DONE)) {
+    if (state != ST_DONE) {
+      // ---- phase A: block under p -----------------------------------------------------
+      const int bx = (int)floorf(divc(pt.x, p.block_length));
+      const int by = (int)floorf(divc(pt.y, p.block_length));
+      const int bz = (int)floorf(divc(pt.z, p.block_length));
       const int data = find_data(p, memo, bx, by, bz);
+      bool want_interp = false;
+      bool stepped = false;   // MARCH lane that advanced: depth / iteration test follows
+      float sdf = 0.f;
+      float wx = 0.f, wy = 0.f, wz = 0.f;
       if (data != -1) {
-        const float wx = fdiv(sub(pt.x, mul((float)bx, p.block_length)), p.voxel_length);
-        const float wy = fdiv(sub(pt.y, mul((float)by, p.block_length)), p.voxel_length);
-        const float wz = fdiv(sub(pt.z, mul((float)bz, p.block_length)), p.voxel_length);
-        const int vx = (int)wx, vy = (int)wy, vz = (int)wz;  // Q22: may be 8 on a face
-        const uint32_t* vw = reinterpret_cast<const uint32_t*>(p.voxels) +
-                             ((size_t)data * VK_BLOCK_VOXELS + (size_t)(vz * 64 + vy * 8 + vx)) * 5;
-        float sdf = __uint_as_float(__ldg(vw));
-        if (sdf <= 0.1f && sdf >= -0.5f) interpolate(p, memo, bx, by, bz, data, pt, sdf, color);
-        if (sdf <= 0.0f) {
-          if (KEYS) owned_hit = (shard_owner(bx, by, bz, p.shard_shift, p.shard_count) == p.shard_rank);
-          float s = mul(p.trunc, sdf);
-          pt.x = add(pt.x, mul(dir.x, s)); pt.y = add(pt.y, mul(dir.y, s)); pt.z = add(pt.z, mul(dir.z, s));
-          const int bx2 = (int)floorf(fdiv(pt.x, p.block_length));
-          const int by2 = (int)floorf(fdiv(pt.y, p.block_length));
-          const int bz2 = (int)floorf(fdiv(pt.z, p.block_length));
-          const int data2 = find_data(p, memo, bx2, by2, bz2);
-          if (data2 != -1) {
-            interpolate(p, memo, bx2, by2, bz2, data2, pt, sdf, color);
-            s = mul(p.trunc, sdf);
-            pt.x = add(pt.x, mul(dir.x, s)); pt.y = add(pt.y, mul(dir.y, s)); pt.z = add(pt.z, mul(dir.z, s));
-          }
-          final_depth = xform(Tcw, pt.x, pt.y, pt.z, 1.0f).z;
-          break;
+        wx = divc(FP<F>::nmad((float)bx, p.block_length.d, pt.x), p.voxel_length);
+        wy = divc(FP<F>::nmad((float)by, p.block_length.d, pt.y), p.voxel_length);
+        wz = divc(FP<F>::nmad((float)bz, p.block_length.d, pt.z), p.voxel_length);
+        if (state == ST_MARCH) {
+          const int vx = (int)wx, vy = (int)wy, vz = (int)wz;  // Q22: may be 8 on a face
+          sdf = __uint_as_float(__ldg(voxel_words(p, data, vz * 64 + vy * 8 + vx)));
+          want_interp = (sdf <= 0.1f && sdf >= -0.5f);
         } else {
-          const float s = vmax(p.voxel_length, mul(p.trunc, sdf));
-          pt.x = add(pt.x, mul(dir.x, s)); pt.y = add(pt.y, mul(dir.y, s)); pt.z = add(pt.z, mul(dir.z, s));
+          want_interp = true;
         }
+      } else if (state == ST_MARCH) {
+        pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
+        pt.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
+        pt.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
+        stepped = true;
       } else {
-        pt.x = add(pt.x, mul(dir.x, p.block_length));
-        pt.y = add(pt.y, mul(dir.y, p.block_length));
-        pt.z = add(pt.z, mul(dir.z, p.block_length));
+        // REFINE without a block under the backed-up point: no second interpolation
+        final_depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
+        state = ST_DONE;
       }
-      depth = xform(Tcw, pt.x, pt.y, pt.z, 1.0f).z;
-      if (++iters >= 500) { color.x = 1.f; color.y = 0.f; color.z = 0.f; break; }
-    } while (depth < bound.y);
+      // ---- phase B: interpolation, one copy for first hit test and refinement ------------
+      if (want_interp) {
+        Taps taps;
+        resolve_taps(p, bx, by, bz, data, wx, wy, wz, taps);
+        sdf = interp_distance<F>(p, taps);
+        ipt = pt;
+        has_interp = true;
+      }
+      // ---- phase C: transitions ------------------------------------------------------------
+      if (data != -1) {
+        if (state == ST_MARCH) {
+          if (sdf <= 0.0f) {
+            if (KEYS) owned_hit = (shard_owner(bx, by, bz, p.shard_shift, p.shard_count) == p.shard_rank);
+            const float s = mul(p.trunc, sdf);
+            pt.x = FP<F>::mad(dir.x, s, pt.x);
+            pt.y = FP<F>::mad(dir.y, s, pt.y);
+            pt.z = FP<F>::mad(dir.z, s, pt.z);
+            state = ST_REFINE;
+          } else {
+            const float s = vmax(p.voxel_length.d, mul(p.trunc, sdf));
+            pt.x = FP<F>::mad(dir.x, s, pt.x);
+            pt.y = FP<F>::mad(dir.y, s, pt.y);
+            pt.z = FP<F>::mad(dir.z, s, pt.z);
+            stepped = true;
+          }
+        } else {  // ST_REFINE, block found: second refinement step, then the final depth
+          const float s = mul(p.trunc, sdf);
+          pt.x = FP<F>::mad(dir.x, s, pt.x);
+          pt.y = FP<F>::mad(dir.y, s, pt.y);
+          pt.z = FP<F>::mad(dir.z, s, pt.z);
+          final_depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
+          state = ST_DONE;
+        }
+      }
+      if (stepped) {
+        const float depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
+        if (++iters >= 500) { red = true; state = ST_DONE; }
+        else if (!(depth < hi)) state = ST_DONE;
+      }
+    }
+  }
+
+  if (!inside) return;
+  // colour of the last interpolation (Q13: kept even on a miss), evaluated once per ray
+  Vec3 color = {0.f, 0.f, 0.f};
+  if (red) {
+    color.x = 1.f;
+  } else if (has_interp) {
+    const int bx = (int)floorf(divc(ipt.x, p.block_length));
+    const int by = (int)floorf(divc(ipt.y, p.block_length));
+    const int bz = (int)floorf(divc(ipt.z, p.block_length));
+    const int data = lookup_block(p, bx, by, bz);
+    const float wx = divc(FP<F>::nmad((float)bx, p.block_length.d, ipt.x), p.voxel_length);
+    const float wy = divc(FP<F>::nmad((float)by, p.block_length.d, ipt.y), p.voxel_length);
+    const float wz = divc(FP<F>::nmad((float)bz, p.block_length.d, ipt.z), p.voxel_length);
+    Taps taps;
+    resolve_taps(p, bx, by, bz, data, wx, wy, wz, taps);
+    color = interp_color<F>(p, taps);
   }
 
   const int pixel = y * p.w + x;
@@ -423,7 +559,10 @@ __global__ void __launch_bounds__(256) vk_resolve_keys_kernel(const unsigned lon
 
 namespace vk {
 
-// ComputeNormalsKernel<16> (src/frame.cu:7-122): 32x8 tile + 2 px halo, zero outside
+// ComputeNormalsKernel<16> (src/frame.cu:7-122): 32x8 tile + 2 px halo, zero outside.
+// FMA map: Unproject as in vk_math.cuh; dot FFMA chains; cross a.y*b.z - a.z*b.y ->
+// FMUL a.z*b.y ; FFMA a.y*b.z - .   (include/vulcan/matrix.h:174-183)
+template <bool F>
 __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, const vkProjection proj,
                                                          float* normals, int w, int h) {
   constexpr int TW = 32, TH = 8, PAD = 2, SW = TW + 2 * PAD, SH = TH + 2 * PAD;
@@ -442,9 +581,9 @@ __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, co
   const float depth = tile[(ty + PAD) * SW + tx + PAD];
   float nx = 0, ny = 0, nz = 0;
   if (depth > 0) {
-    const float fx = (float)x + 0.5f, fy = (float)y + 0.5f;
-    const Vec3 u0 = unproject(proj, fx, fy);
-    const Vec3 z0 = {mul(u0.x, depth), mul(u0.y, depth), mul(u0.z, depth)};
+    Unprojector un;
+    un.init(proj);
+    const Vec3 z0 = {mul(un.x<F>(add((float)x, 0.5f)), depth), mul(un.y<F>(add((float)y, 0.5f)), depth), depth};
     Vec3 q[4];
     const int ox[4] = {-PAD, +PAD, 0, 0}, oy[4] = {0, 0, -PAD, +PAD};
 #pragma unroll
@@ -453,19 +592,19 @@ __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, co
       if (d == 0) {
         q[k] = z0;
       } else {
-        const Vec3 un = unproject(proj, (float)(x + ox[k]) + 0.5f, (float)(y + oy[k]) + 0.5f);
-        q[k].x = mul(un.x, d); q[k].y = mul(un.y, d); q[k].z = mul(un.z, d);
+        q[k].x = mul(un.x<F>(add((float)(x + ox[k]), 0.5f)), d);
+        q[k].y = mul(un.y<F>(add((float)(y + oy[k]), 0.5f)), d);
+        q[k].z = d;
       }
     }
     const Vec3 dx = {sub(q[0].x, q[1].x), sub(q[0].y, q[1].y), sub(q[0].z, q[1].z)};
     const Vec3 dy = {sub(q[2].x, q[3].x), sub(q[2].y, q[3].y), sub(q[2].z, q[3].z)};
-    if (dot3(dx, dx) > 0 && dot3(dy, dy) > 0) {
-      // dy.Cross(dx) (include/vulcan/matrix.h:174-183)
-      Vec3 n;
-      n.x = sub(mul(dy.y, dx.z), mul(dy.z, dx.y));
-      n.y = sub(mul(dy.z, dx.x), mul(dy.x, dx.z));
-      n.z = sub(mul(dy.x, dx.y), mul(dy.y, dx.x));
-      n = normalized(n);
+    if (dot3<F>(dx, dx) > 0 && dot3<F>(dy, dy) > 0) {
+      Vec3 n;  // dy.Cross(dx)
+      n.x = FP<F>::msub(dy.y, dx.z, mul(dy.z, dx.y));
+      n.y = FP<F>::msub(dy.z, dx.x, mul(dy.x, dx.z));
+      n.z = FP<F>::msub(dy.x, dx.y, mul(dy.y, dx.x));
+      n = normalized<F>(n);
       nx = n.x; ny = n.y; nz = n.z;
     }
   }
@@ -511,11 +650,6 @@ __global__ void __launch_bounds__(256) vk_filter_depths_kernel(int w, int h, con
 
 using namespace vk;
 
-static void rows34(const float* colmajor, float* out12) {
-  for (int r = 0; r < 3; ++r)
-    for (int c = 0; c < 4; ++c) out12[r * 4 + c] = colmajor[c * 4 + r];
-}
-
 extern "C" int vk_reset_bounds(float* bounds, int count, void* stream) {
   if (!bounds || count < 0) return VK_E_INVALID;
   if (count == 0) return 0;
@@ -525,15 +659,17 @@ extern "C" int vk_reset_bounds(float* bounds, int count, void* stream) {
   return (int)cudaGetLastError();
 }
 
-static void fill_bounds_params(BoundsParams& b, const vkTransform* Tcw_is_inverse_of, bool use_inverse,
-                               const vkProjection* proj, float block_length, float min_depth, float max_depth,
-                               int image_w, int image_h, int bw, int bh, float* bounds) {
-  rows34(use_inverse ? Tcw_is_inverse_of->inv : Tcw_is_inverse_of->m, b.Tcw);
+static void fill_bounds_params(BoundsParams& b, const float* Tcw_colmajor, const vkProjection* proj,
+                               float block_length, float min_depth, float max_depth, int image_w, int image_h,
+                               int bw, int bh, float* bounds, cudaStream_t s) {
+  rows34(Tcw_colmajor, b.Tcw);
   b.proj = *proj;
   b.block_length = block_length;
   b.min_depth = min_depth;
   b.max_depth = max_depth;
-  b.image_w = image_w; b.image_h = image_h; b.bw = bw; b.bh = bh;
+  b.image_w = make_div((float)image_w, s);
+  b.image_h = make_div((float)image_h, s);
+  b.bw = bw; b.bh = bh;
   b.bounds = bounds;
   b.visible = nullptr; b.count = nullptr; b.entries = nullptr;
 }
@@ -544,11 +680,15 @@ extern "C" int vk_compute_patches(const int* indices, const vkHashEntry* entries
                                   int bounds_h, vkPatch* patches, int* patch_count, void* stream) {
   if (!indices || !entries || !Tcw || !proj || !patches || !patch_count || block_count < 0) return VK_E_INVALID;
   if (block_count == 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
   BoundsParams b;
-  fill_bounds_params(b, Tcw, false, proj, block_length, min_depth, max_depth, image_w, image_h, bounds_w,
-                     bounds_h, nullptr);
-  vk_patches_kernel<<<(block_count + 255) / 256, 256, 0, (cudaStream_t)stream>>>(indices, entries, b, block_count,
-                                                                                patches, patch_count);
+  fill_bounds_params(b, Tcw->m, proj, block_length, min_depth, max_depth, image_w, image_h, bounds_w, bounds_h,
+                     nullptr, s);
+  const int grid = (block_count + 255) / 256;
+  if (g_default_math_mode.load() == VK_MATH_STRICT)
+    vk_patches_kernel<false><<<grid, 256, 0, s>>>(indices, entries, b, block_count, patches, patch_count);
+  else
+    vk_patches_kernel<true><<<grid, 256, 0, s>>>(indices, entries, b, block_count, patches, patch_count);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
@@ -565,13 +705,14 @@ extern "C" int vk_compute_bounds(const vkPatch* patches, float* bounds, int boun
 
 static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const vkVoxel* voxels,
                               const float* bounds, int K, float block_length, float voxel_length, float trunc,
-                              const vkTransform* Twc, const vkProjection* proj, int w, int h, int bw, int bh) {
+                              const vkTransform* Twc, const vkProjection* proj, int w, int h, int bw, int bh,
+                              cudaStream_t s) {
   t.entries = entries;
   t.voxels = voxels;
   t.bounds = bounds;
-  t.K = (uint32_t)K;
-  t.block_length = block_length;
-  t.voxel_length = voxel_length;
+  t.K = make_mod((uint32_t)K);
+  t.block_length = make_div(block_length, s);
+  t.voxel_length = make_div(voxel_length, s);
   t.trunc = trunc;
   rows34(Twc->m, t.Twc);
   rows34(Twc->inv, t.Tcw);
@@ -581,30 +722,51 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.shard_rank = 0; t.shard_count = 1; t.shard_shift = 0;
 }
 
-extern "C" int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxels, const float* bounds,
-                                 int block_count, float block_length, float voxel_length, float trunc_length,
-                                 const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
-                                 int image_w, int image_h, int bounds_w, int bounds_h, void* stream) {
+template <bool KEYS>
+static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
+  dim3 grid((t.w + 7) / 8, (t.h + 7) / 8);
+  if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, KEYS><<<grid, 64, 0, s>>>(t);
+  else vk_raycast_kernel<true, KEYS><<<grid, 64, 0, s>>>(t);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
+
+static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels, const float* bounds,
+                               int block_count, float block_length, float voxel_length, float trunc_length,
+                               const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
+                               int image_w, int image_h, int bounds_w, int bounds_h, int math_mode, cudaStream_t s) {
   if (!entries || !voxels || !bounds || !Twc || !proj || !depths || !colors || image_w <= 0 || image_h <= 0)
     return VK_E_INVALID;
   TraceParams t;
   fill_trace_params(t, entries, voxels, bounds, block_count, block_length, voxel_length, trunc_length, Twc, proj,
-                    image_w, image_h, bounds_w, bounds_h);
+                    image_w, image_h, bounds_w, bounds_h, s);
   t.depths = depths;
   t.colors = colors;
+  return launch_raycast<false>(t, math_mode, s);
+}
+
+extern "C" int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxels, const float* bounds,
+                                 int block_count, float block_length, float voxel_length, float trunc_length,
+                                 const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
+                                 int image_w, int image_h, int bounds_w, int bounds_h, void* stream) {
+  return compute_points_mode(entries, voxels, bounds, block_count, block_length, voxel_length, trunc_length, Twc,
+                             proj, depths, colors, image_w, image_h, bounds_w, bounds_h,
+                             g_default_math_mode.load(), (cudaStream_t)stream);
+}
+
+static int normals_mode(const float* depths, const vkProjection* proj, float* normals, int image_w, int image_h,
+                        int math_mode, cudaStream_t s) {
+  if (!depths || !proj || !normals || image_w <= 0 || image_h <= 0) return VK_E_INVALID;
   dim3 grid((image_w + 31) / 32, (image_h + 7) / 8);
-  vk_raycast_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(t);
+  if (math_mode == VK_MATH_STRICT) vk_normals_kernel<false><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h);
+  else vk_normals_kernel<true><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
 
 extern "C" int vk_compute_normals(const float* depths, const vkProjection* proj, float* normals, int image_w,
                                   int image_h, void* stream) {
-  if (!depths || !proj || !normals || image_w <= 0 || image_h <= 0) return VK_E_INVALID;
-  dim3 grid((image_w + 31) / 32, (image_h + 7) / 8);
-  vk_normals_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(depths, *proj, normals, image_w, image_h);
-  VK_COUNT_LAUNCH();
-  return (int)cudaGetLastError();
+  return normals_mode(depths, proj, normals, image_w, image_h, g_default_math_mode.load(), (cudaStream_t)stream);
 }
 
 extern "C" int vk_filter_depths(int image_w, int image_h, const float* src, float* dst, void* stream) {
@@ -615,18 +777,22 @@ extern "C" int vk_filter_depths(int image_w, int image_h, const float* src, floa
   return (int)cudaGetLastError();
 }
 
+static const int kBoundsGrid = 32;
+
 static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, float* bounds,
                         cudaStream_t s) {
   // Tracer::ComputePatches + ComputeBounds (src/tracer.cpp:49-76), 80x60 grid hard coded
   int rc = vk_reset_bounds(bounds, VK_BOUNDS_W * VK_BOUNDS_H, s);
   if (rc) return rc;
   BoundsParams b;
-  fill_bounds_params(b, &view->depth_to_world, true, &view->depth_proj, VK_BLOCK_RES * v->voxel_length, min_depth,
-                     max_depth, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, bounds);
+  fill_bounds_params(b, view->depth_to_world.inv, &view->depth_proj, VK_BLOCK_RES * v->voxel_length, min_depth,
+                     max_depth, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, bounds, s);
   b.visible = v->visible[v->visible_slot];
   b.count = v->counters + VK_CNT_VISIBLE0 + v->visible_slot;
   b.entries = v->entries;
-  vk_bounds_kernel<<<148, 256, 0, s>>>(b);
+  const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float);
+  if (v->math_mode == VK_MATH_STRICT) vk_bounds_kernel<false><<<kBoundsGrid, 512, smem, s>>>(b);
+  else vk_bounds_kernel<true><<<kBoundsGrid, 512, smem, s>>>(b);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
@@ -637,11 +803,12 @@ extern "C" int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth,
   cudaStream_t s = (cudaStream_t)stream;
   int rc = trace_bounds(v, view, min_depth, max_depth, bounds, s);
   if (rc) return rc;
-  rc = vk_compute_points(v->entries, v->voxels, bounds, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
-                         v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, out_depth,
-                         out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, stream);
+  rc = compute_points_mode(v->entries, v->voxels, bounds, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
+                           v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, out_depth,
+                           out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, v->math_mode, s);
   if (rc) return rc;
-  if (out_normal) rc = vk_compute_normals(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, stream);
+  if (out_normal)
+    rc = normals_mode(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, v->math_mode, s);
   return rc;
 }
 
@@ -654,15 +821,12 @@ extern "C" int vk_trace_keys(const vkVolume* v, const vkFrame* view, float min_d
   TraceParams t;
   fill_trace_params(t, v->entries, v->voxels, bounds, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
                     v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, view->depth_w,
-                    view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H);
+                    view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
   t.keys = out_keys;
   t.shard_rank = v->shard_rank;
   t.shard_count = v->shard_count;
   t.shard_shift = v->shard_shift;
-  dim3 grid((view->depth_w + 31) / 32, (view->depth_h + 7) / 8);
-  vk_raycast_kernel<true><<<grid, 256, 0, s>>>(t);
-  VK_COUNT_LAUNCH();
-  return (int)cudaGetLastError();
+  return launch_raycast<true>(t, v->math_mode, s);
 }
 
 extern "C" int vk_resolve_keys(const unsigned long long* keys, const vkFrame* view, float* out_depth,
@@ -676,7 +840,3 @@ extern "C" int vk_resolve_keys(const unsigned long long* keys, const vkFrame* vi
   if (out_normal) rc = vk_compute_normals(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, stream);
   return rc;
 }
-
-namespace vk { std::atomic<unsigned long long> g_launches{0}; }
-extern "C" int vk_version(void) { return 100; }
-extern "C" unsigned long long vk_launch_count(void) { return vk::g_launches.load(); }
