@@ -111,6 +111,7 @@ typedef struct vkVolume {
   int32_t*     visible[2];    /* [M+E] each; visible[visible_slot] is current       */
   int32_t*     stamps;        /* [M+E] id of the last SetView that touched an entry */
   int32_t*     locks;         /* [M]   per-bucket insertion locks                   */
+  uint32_t*    bucket_bits;   /* [ceil(M/32)] bit h set <=> bucket head h allocated */
   int32_t*     counters;      /* [VK_CNT_COUNT] device                              */
   int32_t*     host_counters; /* [VK_CNT_COUNT] pinned host mirror                  */
   int32_t      main_blocks;   /* M (also the hash modulus K)                        */

@@ -654,7 +654,12 @@ int block_patches(const HashEntry& entry, const float* Tcw, const Proj& P, float
       const float Y = block_length * (y + entry.block[1]);
       for (int x = 0; x <= 1; ++x) {
         const float X = block_length * (x + entry.block[0]);
-        const V3 Xcp = xform(Tcw, X, Y, Z, 1);
+        // rows fused the other way round here (x and y products hoisted out of the corner loops):
+        // FMUL x*m0 ; FFMA y*m1 + . ; FFMA z*m2 + . ; FADD m3
+        V3 Xcp;
+        Xcp.x = mad(Z, M(Tcw, 0, 2), mad(Y, M(Tcw, 0, 1), X * M(Tcw, 0, 0))) + M(Tcw, 0, 3);
+        Xcp.y = mad(Z, M(Tcw, 1, 2), mad(Y, M(Tcw, 1, 1), X * M(Tcw, 1, 0))) + M(Tcw, 1, 3);
+        Xcp.z = mad(Z, M(Tcw, 2, 2), mad(Y, M(Tcw, 2, 1), X * M(Tcw, 2, 0))) + M(Tcw, 2, 3);
         float u, v;
         project(P, Xcp, u, v);
         u = bw * u / image_w;

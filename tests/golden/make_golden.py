@@ -21,19 +21,19 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import harness as H  # noqa: E402
 
 SCENARIOS = [
-    ("tiny", (0,), "depth", 1.2),
-    ("tiny", (0, 8), "depth", 5.0),
-    ("tiny", (0, 3), "color", 5.0),
-    ("tiny", (0, 3), "light", 5.0),
+    ("micro", (0,), "depth", 1.2),
+    ("micro", (0, 8), "depth", 5.0),
+    ("micro", (0, 3), "color", 5.0),
+    ("micro", (0, 3), "light", 5.0),
 ]
 
 
 def stable_ref(scn, nofmad):
     prev = None
-    for _ in range(12):
+    for _ in range(40):
         r = H.run_ref(scn, nofmad=nofmad)
         keys = r["keys"]
-        clean = len(np.unique(keys)) == len(keys)
+        clean = len(np.unique(keys)) == len(keys) and r.get("unreachable", 0) == 0
         if clean and prev is not None and np.array_equal(prev, keys):
             return r
         prev = keys if clean else None

@@ -397,6 +397,7 @@ def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2, math=0)
     """Sphere-on-plane scenarios.  frames = orbit indices; math = 0 (reference
     contraction pattern) or 1 (strict)."""
     cfg = {
+        "micro": dict(w=48, h=36, voxel=0.02, M=2048, E=512),
         "tiny": dict(w=64, h=48, voxel=0.016, M=4096, E=1024),
         "small": dict(w=160, h=120, voxel=0.008, M=32768, E=8192),
         "c1": dict(w=640, h=480, voxel=0.004, M=262144, E=65536),

@@ -29,6 +29,7 @@ struct AllocParams {
   uint8_t* visibility;
   int32_t* stamps;
   int32_t* locks;
+  uint32_t* bucket_bits;
   const int32_t* free_list;
   int32_t* counters;
   int32_t* visible_out;
@@ -99,6 +100,7 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
             __stcg(dst, make_int2(ne.x, ne.y));
             __threadfence();
             __stcg(reinterpret_cast<int*>(p.entries + slot) + 2, data);
+            atomicOr(p.bucket_bits + (h >> 5), 1u << (h & 31));
           } else {
             ne.z = data;
             __stcg(reinterpret_cast<int4*>(p.entries + slot), ne);
@@ -338,6 +340,8 @@ extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   for (int i = 0; i < VK_CNT_COUNT; ++i) v->host_counters[i] = init[i];
   cudaError_t err = cudaMemcpyAsync(v->counters, v->host_counters, sizeof(init), cudaMemcpyHostToDevice, s);
   if (err != cudaSuccess) return (int)err;
+  err = cudaMemsetAsync(v->bucket_bits, 0, ((size_t)v->main_blocks + 31) / 32 * sizeof(uint32_t), s);
+  if (err != cudaSuccess) return (int)err;
   err = cudaMemsetAsync(v->counters + VK_CNT_COUNT, 0, sizeof(int), s);  // ticket
   if (err != cudaSuccess) return (int)err;
   err = cudaStreamSynchronize(s);  // host_counters is reused by kernels afterwards
@@ -374,6 +378,7 @@ extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks,
   VK_TRY(cudaMalloc((void**)&v->visible[1], B * sizeof(int32_t)));
   VK_TRY(cudaMalloc((void**)&v->stamps, B * sizeof(int32_t)));
   VK_TRY(cudaMalloc((void**)&v->locks, (size_t)main_blocks * sizeof(int32_t)));
+  VK_TRY(cudaMalloc((void**)&v->bucket_bits, ((size_t)main_blocks + 31) / 32 * sizeof(uint32_t)));
   VK_TRY(cudaMalloc((void**)&v->counters, (VK_CNT_COUNT + 4) * sizeof(int32_t)));
   VK_TRY(cudaHostAlloc((void**)&v->host_counters, VK_CNT_COUNT * sizeof(int32_t), cudaHostAllocMapped));
 #undef VK_TRY
@@ -390,6 +395,7 @@ extern "C" int vk_volume_destroy(vkVolume* v) {
   cudaFree(v->visible[1]);
   cudaFree(v->stamps);
   cudaFree(v->locks);
+  cudaFree(v->bucket_bits);
   cudaFree(v->counters);
   if (v->host_counters) cudaFreeHost(v->host_counters);
   const int m = v->main_blocks, e = v->excess_blocks;
@@ -410,6 +416,7 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.visibility = v->visibility;
   a.stamps = v->stamps;
   a.locks = v->locks;
+  a.bucket_bits = v->bucket_bits;
   a.free_list = v->free_list;
   a.counters = v->counters;
   a.visible_out = v->visible[cur];

@@ -76,6 +76,19 @@ __device__ __forceinline__ Vec3 xform1(const Mat34& M, float x, float y, float z
   o.z = add(row_acc<F>(M.r[2], x, y, z), M.r[2][3]);
   return o;
 }
+// Same sum in ComputePatchesKernel (src/tracer.cu:31-49), where the compiler hoists the x and y
+// products out of the corner loops and fuses the other way round:
+//   FMUL x*m0; FFMA y*m1 + .; FFMA z*m2 + .; FADD m3
+template <bool F>
+__device__ __forceinline__ Vec3 xform1_xfirst(const Mat34& M, float x, float y, float z) {
+  Vec3 o;
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float acc = FP<F>::mad(z, M.r[r][2], FP<F>::mad(y, M.r[r][1], mul(x, M.r[r][0])));
+    (r == 0 ? o.x : r == 1 ? o.y : o.z) = add(acc, M.r[r][3]);
+  }
+  return o;
+}
 template <bool F>
 __device__ __forceinline__ float xform1_z(const Mat34& M, float x, float y, float z) {
   return add(row_acc<F>(M.r[2], x, y, z), M.r[2][3]);
@@ -148,10 +161,10 @@ struct Div {
 };
 __device__ __forceinline__ float divc(float x, const Div& dv) {
   const float q0 = __fmul_rn(x, dv.r);
-  const float a = fabsf(q0), ax = fabsf(x);
-  // both the quotient and the dividend well inside the normal range: the residual e is then
-  // exactly representable (no underflow) and nothing overflows
-  if (dv.fast && a > 1e-25f && a < 1e25f && ax > 1e-25f && ax < 1e25f) {
+  // dividend exponent in [2^-40, 2^40) and (make_div) divisor in [2^-63, 2^64): quotient, residual
+  // and correction are all normal numbers far from overflow, so e is exact
+  const uint32_t ex = (__float_as_uint(x) >> 23) & 0xffu;
+  if (dv.fast && (ex - 87u) < 80u) {
     const float e = __fmaf_rn(-q0, dv.d, x);
     return __fmaf_rn(e, dv.r, q0);
   }
@@ -171,8 +184,8 @@ __host__ __device__ __forceinline__ Mod make_mod(uint32_t K) {
   return o;
 }
 __device__ __forceinline__ uint32_t fastmod(uint32_t h, const Mod& md) {
+  // 2^32 = m*K + g, 0 <= g < K  =>  h*m/2^32 = h/K - h*g/(K*2^32) > h/K - 1  =>  r in [0, 2K)
   uint32_t r = h - __umulhi(h, md.m) * md.K;
-  if (r >= md.K) r -= md.K;
   if (r >= md.K) r -= md.K;
   return r;
 }

@@ -69,7 +69,7 @@ struct BoundsParams {
 };
 
 // body of ComputePatchesKernel (src/tracer.cu:13-66) for one block.
-// FMA map: corner = L * (i + origin) FMUL; Tcw * corner rows as xform1; Project;
+// FMA map: corner = L * (i + origin) FMUL; Tcw * corner rows as xform1_xfirst; Project;
 //          u' = bounds_width * u / image_width   FMUL then IEEE division.
 template <bool F>
 __device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw, const BoundsParams& p) {
@@ -85,7 +85,7 @@ __device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw,
       const float Y = mul(p.block_length, (float)(y + oy));
       for (int x = 0; x <= 1; ++x) {
         const float X = mul(p.block_length, (float)(x + ox));
-        const Vec3 Xc = xform1<F>(Tcw, X, Y, Z);
+        const Vec3 Xc = xform1_xfirst<F>(Tcw, X, Y, Z);
         float u, v;
         project<F>(p.proj, Xc, u, v);
         u = divc(mul((float)p.bw, u), p.image_w);
@@ -225,6 +225,7 @@ struct TraceParams {
   const vkHashEntry* entries;
   const vkVoxel* voxels;
   const float* bounds;
+  const uint32_t* bucket_bits;  // optional: bit h set <=> bucket head h allocated (vkVolume::bucket_bits)
   Mod K;
   Div block_length, voxel_length;
   float trunc;
@@ -248,7 +249,11 @@ struct Lookup {
 // `entry.block == b && entry.IsAllocated()`  (src/tracer.cu:363-371, :151-175)
 __device__ __forceinline__ int lookup_block(const TraceParams& p, int bx, int by, int bz) {
   const unsigned long long key = pack_block(bx, by, bz);
-  int4 e = ld_entry(p.entries + block_hash(bx, by, bz, p.K));
+  const uint32_t h = block_hash(bx, by, bz, p.K);
+  // an unallocated bucket head has no chain: most steps through free space end here, on a
+  // 32 KB bitmap that stays in L1, instead of on a 16-byte entry fetched from L2
+  if (p.bucket_bits && !((__ldg(p.bucket_bits + (h >> 5)) >> (h & 31)) & 1u)) return -1;
+  int4 e = ld_entry(p.entries + h);
   while (entry_block(e) != key && e.w != -1) e = ld_entry(p.entries + e.w);
   return (entry_block(e) == key) ? e.z : -1;
 }
@@ -263,7 +268,7 @@ __device__ __forceinline__ int find_data(const TraceParams& p, Lookup& memo, int
 
 __device__ __forceinline__ const uint32_t* voxel_words(const TraceParams& p, int data, int voxel_offset) {
   // Voxel is 20 bytes, 4-byte aligned: distance, rgb, (dw | cw << 16)
-  return reinterpret_cast<const uint32_t*>(p.voxels) + ((size_t)data * VK_BLOCK_VOXELS + (size_t)voxel_offset) * 5;
+  return reinterpret_cast<const uint32_t*>(p.voxels) + (size_t)data * (VK_BLOCK_VOXELS * 5) + voxel_offset * 5;
 }
 
 // The 8 taps of GetInterpolatedDistance (src/tracer.cu:190-256): per axis the tap pair
@@ -704,12 +709,13 @@ extern "C" int vk_compute_bounds(const vkPatch* patches, float* bounds, int boun
 }
 
 static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const vkVoxel* voxels,
-                              const float* bounds, int K, float block_length, float voxel_length, float trunc,
+                              const float* bounds, const uint32_t* bucket_bits, int K, float block_length, float voxel_length, float trunc,
                               const vkTransform* Twc, const vkProjection* proj, int w, int h, int bw, int bh,
                               cudaStream_t s) {
   t.entries = entries;
   t.voxels = voxels;
   t.bounds = bounds;
+  t.bucket_bits = bucket_bits;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
   t.voxel_length = make_div(voxel_length, s);
@@ -732,14 +738,14 @@ static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
 }
 
 static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels, const float* bounds,
-                               int block_count, float block_length, float voxel_length, float trunc_length,
+                               const uint32_t* bucket_bits, int block_count, float block_length, float voxel_length, float trunc_length,
                                const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
                                int image_w, int image_h, int bounds_w, int bounds_h, int math_mode, cudaStream_t s) {
   if (!entries || !voxels || !bounds || !Twc || !proj || !depths || !colors || image_w <= 0 || image_h <= 0)
     return VK_E_INVALID;
   TraceParams t;
-  fill_trace_params(t, entries, voxels, bounds, block_count, block_length, voxel_length, trunc_length, Twc, proj,
-                    image_w, image_h, bounds_w, bounds_h, s);
+  fill_trace_params(t, entries, voxels, bounds, bucket_bits, block_count, block_length, voxel_length, trunc_length,
+                    Twc, proj, image_w, image_h, bounds_w, bounds_h, s);
   t.depths = depths;
   t.colors = colors;
   return launch_raycast<false>(t, math_mode, s);
@@ -749,7 +755,7 @@ extern "C" int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxe
                                  int block_count, float block_length, float voxel_length, float trunc_length,
                                  const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
                                  int image_w, int image_h, int bounds_w, int bounds_h, void* stream) {
-  return compute_points_mode(entries, voxels, bounds, block_count, block_length, voxel_length, trunc_length, Twc,
+  return compute_points_mode(entries, voxels, bounds, nullptr, block_count, block_length, voxel_length, trunc_length, Twc,
                              proj, depths, colors, image_w, image_h, bounds_w, bounds_h,
                              g_default_math_mode.load(), (cudaStream_t)stream);
 }
@@ -803,7 +809,7 @@ extern "C" int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth,
   cudaStream_t s = (cudaStream_t)stream;
   int rc = trace_bounds(v, view, min_depth, max_depth, bounds, s);
   if (rc) return rc;
-  rc = compute_points_mode(v->entries, v->voxels, bounds, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
+  rc = compute_points_mode(v->entries, v->voxels, bounds, v->bucket_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
                            v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, out_depth,
                            out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, v->math_mode, s);
   if (rc) return rc;
@@ -819,7 +825,7 @@ extern "C" int vk_trace_keys(const vkVolume* v, const vkFrame* view, float min_d
   int rc = trace_bounds(v, view, min_depth, max_depth, bounds, s);
   if (rc) return rc;
   TraceParams t;
-  fill_trace_params(t, v->entries, v->voxels, bounds, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
+  fill_trace_params(t, v->entries, v->voxels, bounds, v->bucket_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
                     v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, view->depth_w,
                     view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
   t.keys = out_keys;
