@@ -41,6 +41,7 @@ extern "C" {
 #define VK_BLOCK_VOXELS  512    /* Block::voxel_count, include/vulcan/block.h:15   */
 #define VK_BOUNDS_W      80     /* hard coded in src/tracer.cpp:56                 */
 #define VK_BOUNDS_H      60     /* hard coded in src/tracer.cpp:57                 */
+#define VK_SPACE_WORDS   65536  /* 128^3 bits, see vkVolume::space_bits            */
 
 /* byte image of vulcan::Voxel (include/vulcan/voxel.h:41-49), 20 bytes */
 typedef struct vkVoxel {
@@ -112,6 +113,8 @@ typedef struct vkVolume {
   int32_t*     stamps;        /* [M+E] id of the last SetView that touched an entry */
   int32_t*     locks;         /* [M]   per-bucket insertion locks                   */
   uint32_t*    bucket_bits;   /* [ceil(M/32)] bit h set <=> bucket head h allocated */
+  uint32_t*    space_bits;    /* [VK_SPACE_WORDS] bit of (x,y,z) mod 128 set <=> some block with    */
+                              /* those low coordinate bits is allocated (free-space filter)       */
   int32_t*     counters;      /* [VK_CNT_COUNT] device                              */
   int32_t*     host_counters; /* [VK_CNT_COUNT] pinned host mirror                  */
   int32_t      main_blocks;   /* M (also the hash modulus K)                        */

@@ -849,6 +849,10 @@ void vo_compute_normals(const float* depth, const float* proj4, float* out, int 
   normals(depth, P, out, w, hgt);
 }
 
+// diagnostics: per-pixel march iteration counts of the next vo_compute_points (tools/ray_stats.py)
+static int* g_iter_out = nullptr;
+void vo_set_iter_output(int* buf) { g_iter_out = buf; }
+
 // ComputePointsKernel, src/tracer.cu:317-451
 void vo_compute_points(void* h, const float* bounds, const float* T, const float* proj4, float* depths,
                        float* colors, int w, int hgt, int bw, int bh) {
@@ -869,6 +873,7 @@ void vo_compute_points(void* h, const float* bounds, const float* T, const float
       const float lo = bounds[2 * (py * bw + px)], hi = bounds[2 * (py * bw + px) + 1];
       float depth = 0, final_depth = 0;
       float color[3] = {0, 0, 0};
+      int iters_done = 0;
       if (lo < hi) {
         const V3 Xcp = scale(unproject(P, x + 0.5f, y + 0.5f), lo);
         const V3 Xwp = xform(Twc, Xcp.x, Xcp.y, Xcp.z, 1.0f);
@@ -910,7 +915,9 @@ void vo_compute_points(void* h, const float* bounds, const float* T, const float
           depth = xform(Tcw, p.x, p.y, p.z, 1.0f).z;
           if (++iters >= 500) { color[0] = 1; color[1] = 0; color[2] = 0; break; }
         } while (depth < hi);
+        iters_done = iters + 1;
       }
+      if (g_iter_out) g_iter_out[(long long)y * w + x] = iters_done;
       const long long pixel = (long long)y * w + x;
       depths[pixel] = final_depth;
       colors[3 * pixel] = color[0]; colors[3 * pixel + 1] = color[1]; colors[3 * pixel + 2] = color[2];

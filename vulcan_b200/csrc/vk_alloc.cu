@@ -30,6 +30,7 @@ struct AllocParams {
   int32_t* stamps;
   int32_t* locks;
   uint32_t* bucket_bits;
+  uint32_t* space_bits;
   const int32_t* free_list;
   int32_t* counters;
   int32_t* visible_out;
@@ -90,6 +91,11 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
         const int vtop = atomicSub(p.counters + VK_CNT_VOXEL_PTR, 1);
         if (slot < p.B && vtop >= 0) {
           const int data = p.free_list[vtop];
+          {  // set before the entry is published: a reader that can find the block sees the bit
+            uint32_t sw, sb;
+            space_bit_index(bx, by, bz, sw, sb);
+            atomicOr(p.space_bits + sw, 1u << sb);
+          }
           int4 ne;
           ne.x = (int)((uint32_t)(uint16_t)(int16_t)bx | ((uint32_t)(uint16_t)(int16_t)by << 16));
           ne.y = (int)(uint32_t)(uint16_t)(int16_t)bz;
@@ -220,6 +226,151 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
   }
 }
 
+// Same fixed point, organised for memory-level parallelism.  vk_alloc_kernel above looks a block
+// up as soon as one ray of a warp reaches it: a dependent L2 round trip per DDA step with one or
+// two lanes working.  Here a CTA (32x8 pixels) first walks all of its rays - pure arithmetic - and
+// collects the distinct blocks in a shared-memory set (a tile of 256 rays touches a few dozen
+// blocks); then every thread takes one distinct block: find-or-insert in the hash, stamp,
+// and the newly visible entries of the whole CTA are appended with ONE global atomic.
+constexpr int kSetSlots = 1024;           // power of two
+constexpr unsigned long long kEmptyKey = ~0ull;
+
+__device__ __forceinline__ unsigned set_slot(unsigned long long key) {
+  return (unsigned)((key * 0x9E3779B97F4A7C15ull) >> 54);  // top 10 bits
+}
+
+// first toucher of an entry in this view marks it visible; returns true for the first toucher
+__device__ __forceinline__ bool stamp_entry(const AllocParams& p, int idx) {
+  if (__ldcg(p.stamps + idx) == p.view_id) return false;
+  if (atomicExch(p.stamps + idx, p.view_id) == p.view_id) return false;
+  p.visibility[idx] = VK_VIS_TRUE;
+  return true;
+}
+
+__device__ __forceinline__ int resolve_block(const AllocParams& p, unsigned long long key) {
+  const int bx = (int)(int16_t)(key & 0xffff), by = (int)(int16_t)((key >> 16) & 0xffff),
+            bz = (int)(int16_t)((key >> 32) & 0xffff);
+  const uint32_t h = block_hash(bx, by, bz, p.K);
+  int tail;
+  bool head_empty;
+  int idx = find_block(p.entries, h, key, tail, head_empty);
+  if (idx < 0 && shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank))
+    idx = insert_block(p, h, bx, by, bz, key);
+  return idx;
+}
+
+template <bool F>
+__global__ void __launch_bounds__(256) vk_alloc_tile_kernel(const AllocParams p) {
+  __shared__ unsigned long long s_set[kSetSlots];
+  __shared__ int s_list[kSetSlots + 256];
+  __shared__ int s_count, s_base;
+  for (int i = threadIdx.x; i < kSetSlots; i += 256) s_set[i] = kEmptyKey;
+  if (threadIdx.x == 0) s_count = 0;
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  // CTA tile 32x8 pixels, warp tile 8x4
+  const int x = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
+  const int y = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
+
+  bool active = (x < p.w && y < p.h);
+  int bx = 0, by = 0, bz = 0, ex = 0, ey = 0, ez = 0, sx = 1, sy = 1, sz = 1;
+  float tmx = 0, tmy = 0, tmz = 0, tdx = 0, tdy = 0, tdz = 0;
+
+  if (active) {
+    const float depth = __ldg(p.depth + y * p.w + x);
+    if (depth < p.min_depth || depth > p.max_depth) active = false;
+    if (active) {
+      const float u = add((float)x, 0.5f), v = add((float)y, 0.5f);
+      Unprojector un;
+      un.init(p.proj);
+      const float d0x = un.x<F>(u), d0y = un.y<F>(v);
+      Mat34 Twd;
+      Twd.load(p.Twd);
+      Vec3 dir = xform0<F>(Twd, d0x, d0y, 1.0f);
+      const float Xx = FP<F>::mad(dir.x, depth, p.Twd[3]);
+      const float Xy = FP<F>::mad(dir.y, depth, p.Twd[7]);
+      const float Xz = FP<F>::mad(dir.z, depth, p.Twd[11]);
+      dir = normalized<F>(dir);
+      const float bgx = FP<F>::nmad(dir.x, p.trunc, Xx), bgy = FP<F>::nmad(dir.y, p.trunc, Xy),
+                  bgz = FP<F>::nmad(dir.z, p.trunc, Xz);
+      const float enx = FP<F>::mad(dir.x, p.trunc, Xx), eny = FP<F>::mad(dir.y, p.trunc, Xy),
+                  enz = FP<F>::mad(dir.z, p.trunc, Xz);
+      sx = (dir.x < 0) ? -1 : 1;
+      sy = (dir.y < 0) ? -1 : 1;
+      sz = (dir.z < 0) ? -1 : 1;
+      const float inv = p.inv_block_length;
+      bx = (int)floorf(mul(bgx, inv));
+      by = (int)floorf(mul(bgy, inv));
+      bz = (int)floorf(mul(bgz, inv));
+      ex = (int)floorf(mul(enx, inv));
+      ey = (int)floorf(mul(eny, inv));
+      ez = (int)floorf(mul(enz, inv));
+      const float ox = FP<F>::msub((float)(bx + max(0, sx)), p.block_length, bgx);
+      const float oy = FP<F>::msub((float)(by + max(0, sy)), p.block_length, bgy);
+      const float oz = FP<F>::msub((float)(bz + max(0, sz)), p.block_length, bgz);
+      tmx = fdiv(ox, dir.x);
+      tmy = fdiv(oy, dir.y);
+      tmz = fdiv(oz, dir.z);
+      if (dir.x == 0) tmx = 1E20f;
+      if (dir.y == 0) tmy = 1E20f;
+      if (dir.z == 0) tmz = 1E20f;
+      tdx = fdiv(mul((float)sx, p.block_length), dir.x);
+      tdy = fdiv(mul((float)sy, p.block_length), dir.y);
+      tdz = fdiv(mul((float)sz, p.block_length), dir.z);
+    }
+  }
+
+  // ---- phase 1: walk the rays, collect distinct blocks ---------------------------------------
+  unsigned long long last_key = kEmptyKey;
+  while (__any_sync(0xffffffffu, active)) {
+    const unsigned long long key = active ? pack_block(bx, by, bz) : kEmptyKey;
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const bool leader = active && (lane == (__ffs(peers) - 1)) && key != last_key;
+    if (leader) {
+      last_key = key;
+      unsigned slot = set_slot(key);
+      bool placed = false;
+      for (int probe = 0; probe < 64 && !placed; ++probe) {
+        const unsigned long long seen = atomicCAS(&s_set[slot], kEmptyKey, key);
+        placed = (seen == kEmptyKey || seen == key);
+        slot = (slot + 1) & (kSetSlots - 1);
+      }
+      if (!placed) {  // set (nearly) full: resolve on the spot
+        const int idx = resolve_block(p, key);
+        if (idx >= 0) touch_entry(p, idx);
+      }
+    }
+    if (active) {
+      // Amanatides-Woo step with the reference's comparison tree (src/volume.cu:241-295)
+      if (tmx < tmy) {
+        if (tmx < tmz) { bx += sx; if (bx == ex + sx) active = false; tmx = add(tmx, tdx); }
+        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
+      } else {
+        if (tmy < tmz) { by += sy; if (by == ey + sy) active = false; tmy = add(tmy, tdy); }
+        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- phase 2: one thread per distinct block --------------------------------------------------
+  for (int i = threadIdx.x; i < kSetSlots; i += 256) {
+    const unsigned long long key = s_set[i];
+    if (key == kEmptyKey) continue;
+    const int idx = resolve_block(p, key);
+    if (idx >= 0 && stamp_entry(p, idx)) s_list[atomicAdd(&s_count, 1)] = idx;
+  }
+  __syncthreads();
+  const int cnt = s_count;
+  if (cnt == 0) return;
+  if (threadIdx.x == 0) s_base = atomicAdd(p.counters + p.cnt_slot, cnt);
+  __syncthreads();
+  const int base = s_base;
+  for (int i = threadIdx.x; i < cnt; i += 256) p.visible_out[base + i] = s_list[i];
+}
+
 struct CarryParams {
   const vkHashEntry* entries;
   uint8_t* visibility;
@@ -342,6 +493,8 @@ extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   if (err != cudaSuccess) return (int)err;
   err = cudaMemsetAsync(v->bucket_bits, 0, ((size_t)v->main_blocks + 31) / 32 * sizeof(uint32_t), s);
   if (err != cudaSuccess) return (int)err;
+  err = cudaMemsetAsync(v->space_bits, 0, VK_SPACE_WORDS * sizeof(uint32_t), s);
+  if (err != cudaSuccess) return (int)err;
   err = cudaMemsetAsync(v->counters + VK_CNT_COUNT, 0, sizeof(int), s);  // ticket
   if (err != cudaSuccess) return (int)err;
   err = cudaStreamSynchronize(s);  // host_counters is reused by kernels afterwards
@@ -379,6 +532,7 @@ extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks,
   VK_TRY(cudaMalloc((void**)&v->stamps, B * sizeof(int32_t)));
   VK_TRY(cudaMalloc((void**)&v->locks, (size_t)main_blocks * sizeof(int32_t)));
   VK_TRY(cudaMalloc((void**)&v->bucket_bits, ((size_t)main_blocks + 31) / 32 * sizeof(uint32_t)));
+  VK_TRY(cudaMalloc((void**)&v->space_bits, VK_SPACE_WORDS * sizeof(uint32_t)));
   VK_TRY(cudaMalloc((void**)&v->counters, (VK_CNT_COUNT + 4) * sizeof(int32_t)));
   VK_TRY(cudaHostAlloc((void**)&v->host_counters, VK_CNT_COUNT * sizeof(int32_t), cudaHostAllocMapped));
 #undef VK_TRY
@@ -396,6 +550,7 @@ extern "C" int vk_volume_destroy(vkVolume* v) {
   cudaFree(v->stamps);
   cudaFree(v->locks);
   cudaFree(v->bucket_bits);
+  cudaFree(v->space_bits);
   cudaFree(v->counters);
   if (v->host_counters) cudaFreeHost(v->host_counters);
   const int m = v->main_blocks, e = v->excess_blocks;
@@ -417,6 +572,7 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.stamps = v->stamps;
   a.locks = v->locks;
   a.bucket_bits = v->bucket_bits;
+  a.space_bits = v->space_bits;
   a.free_list = v->free_list;
   a.counters = v->counters;
   a.visible_out = v->visible[cur];
@@ -439,8 +595,13 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.shard_shift = v->shard_shift;
   dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
   const bool strict = (v->math_mode == VK_MATH_STRICT);
-  if (strict) vk_alloc_kernel<false><<<grid, 256, 0, s>>>(a);
-  else vk_alloc_kernel<true><<<grid, 256, 0, s>>>(a);
+  if (g_tune[VK_TUNE_ALLOC_MODE].load() == 0) {
+    if (strict) vk_alloc_kernel<false><<<grid, 256, 0, s>>>(a);
+    else vk_alloc_kernel<true><<<grid, 256, 0, s>>>(a);
+  } else {
+    if (strict) vk_alloc_tile_kernel<false><<<grid, 256, 0, s>>>(a);
+    else vk_alloc_tile_kernel<true><<<grid, 256, 0, s>>>(a);
+  }
   VK_COUNT_LAUNCH();
 
   CarryParams c;

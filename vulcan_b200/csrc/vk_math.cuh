@@ -171,6 +171,23 @@ __device__ __forceinline__ float divc(float x, const Div& dv) {
   return __fdiv_rn(x, dv.d);
 }
 
+// Three quotients by the same divisor with ONE range guard instead of three (the guard is the
+// same dividend range divc was proven on; zero, tiny, huge and NaN components take the IEEE path).
+__device__ __forceinline__ void divc3(float x, float y, float z, const Div& dv, float& qx, float& qy, float& qz) {
+  const float ax = fabsf(x), ay = fabsf(y), az = fabsf(z);
+  const float lo = fminf(fminf(ax, ay), az), hi = fmaxf(fmaxf(ax, ay), az);
+  const float x0 = __fmul_rn(x, dv.r), y0 = __fmul_rn(y, dv.r), z0 = __fmul_rn(z, dv.r);
+  qx = __fmaf_rn(__fmaf_rn(-x0, dv.d, x), dv.r, x0);
+  qy = __fmaf_rn(__fmaf_rn(-y0, dv.d, y), dv.r, y0);
+  qz = __fmaf_rn(__fmaf_rn(-z0, dv.d, z), dv.r, z0);
+  // 2^-40 <= |.| < 2^40 for all three (exponent field 87..166, as in divc)
+  if (!(dv.fast && lo >= 9.094947017729282e-13f && hi < 1099511627776.0f)) {
+    qx = __fdiv_rn(x, dv.d);
+    qy = __fdiv_rn(y, dv.d);
+    qz = __fdiv_rn(z, dv.d);
+  }
+}
+
 // ---- block hash, Q1 (src/volume.cu:168-180, src/tracer.cu:151-155) -------------------------
 // h = (bx*P1 ^ by*P2 ^ bz*P3) % K with a precomputed multiplier instead of a hardware-less
 // 32-bit modulo (~25 instructions): m = floor(2^32 / K); q = umulhi(h, m) <= h / K < q + 2.
@@ -217,6 +234,19 @@ __device__ __forceinline__ void entry_origin(const int4& e, int& ox, int& oy, in
   ox = (int)(int16_t)(e.x & 0xffff);
   oy = (int)(int16_t)((uint32_t)e.x >> 16);
   oz = (int)(int16_t)(e.y & 0xffff);
+}
+
+// ---- free-space filter (vkVolume::space_bits) ------------------------------------------------
+// One bit per block coordinate triple modulo 128, set when a block with those low bits is
+// allocated (never cleared).  Unlike the hash-bucket bitmap it has spatial locality: a 32-bit word
+// covers 4x4x2 blocks and a 32-byte sector 8x8x4 blocks, so a ray stepping block by block through
+// free space, and its neighbours in the warp, keep hitting the same L1 sectors.  A clear bit
+// proves the block is not in the table; a set bit means "ask the table".
+__host__ __device__ __forceinline__ void space_bit_index(int bx, int by, int bz, uint32_t& word, uint32_t& bit) {
+  const uint32_t x = (uint32_t)bx & 127u, y = (uint32_t)by & 127u, z = (uint32_t)bz & 127u;
+  bit = (x & 3u) | ((y & 3u) << 2) | ((z & 1u) << 4);
+  const uint32_t wx = x >> 2, wy = y >> 2, wz = z >> 1;  // 32 x 32 x 64 words
+  word = ((wx & 1u) | ((wy & 1u) << 1) | ((wz & 1u) << 2)) | (((wx >> 1) + 16u * ((wy >> 1) + 16u * (wz >> 1))) << 3);
 }
 
 // ---- spatial sharding (no reference counterpart) ------------------

@@ -2,6 +2,8 @@
 // the per-divisor proof that vk::divc is correctly rounded.
 #include "vk_launch.h"
 
+#include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <mutex>
 
@@ -9,6 +11,7 @@ namespace vk {
 
 std::atomic<unsigned long long> g_launches{0};
 std::atomic<int> g_default_math_mode{VK_MATH_REFERENCE};
+std::atomic<int> g_tune[VK_TUNE_COUNT] = {{32}, {12}, {3}, {0}, {0}, {0}, {0}, {8}};
 
 // Compares the one-step FMA division against the IEEE division for every dividend bit pattern.
 __global__ void __launch_bounds__(256) vk_divcheck_kernel(float d, float r, unsigned int* mismatches) {
@@ -33,6 +36,18 @@ __global__ void __launch_bounds__(256) vk_divcheck_kernel(float d, float r, unsi
   bad = __reduce_add_sync(0xffffffffu, bad);
   if ((threadIdx.x & 31) == 0 && bad) atomicAdd(mismatches, bad);
 }
+
+// VK_TUNE="knob=value,knob=value" presets the tuning knobs at load (experiments only)
+static const bool g_tune_env = [] {
+  const char* e = getenv("VK_TUNE");
+  while (e && *e) {
+    int k = -1, v = 0, used = 0;
+    if (sscanf(e, "%d=%d%n", &k, &v, &used) == 2 && k >= 0 && k < VK_TUNE_COUNT) g_tune[k].store(v);
+    e = strchr(e, ',');
+    if (e) ++e;
+  }
+  return true;
+}();
 
 static std::mutex g_div_mutex;
 static std::map<uint32_t, int> g_div_cache;
@@ -96,6 +111,11 @@ extern "C" int vk_set_default_math_mode(int mode) {
   if (mode != VK_MATH_REFERENCE && mode != VK_MATH_STRICT) return VK_E_INVALID;
   vk::g_default_math_mode.store(mode);
   return 0;
+}
+// Experiment hook (not part of the ABI header): sets a tuning knob, returns its previous value.
+extern "C" int vk_tune(int knob, int value) {
+  if (knob < 0 || knob >= vk::VK_TUNE_COUNT) return VK_E_INVALID;
+  return vk::g_tune[knob].exchange(value);
 }
 extern "C" int vk_get_default_math_mode(void) { return vk::g_default_math_mode.load(); }
 

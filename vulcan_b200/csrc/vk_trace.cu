@@ -226,6 +226,8 @@ struct TraceParams {
   const vkVoxel* voxels;
   const float* bounds;
   const uint32_t* bucket_bits;  // optional: bit h set <=> bucket head h allocated (vkVolume::bucket_bits)
+  const uint32_t* space_bits;   // optional: free-space filter (vkVolume::space_bits)
+  int free_run;                 // max free-space steps per lane per trip (0 = filter off)
   Mod K;
   Div block_length, voxel_length;
   float trunc;
@@ -236,13 +238,36 @@ struct TraceParams {
   unsigned long long* keys;
   int w, h, bw, bh;
   int shard_rank, shard_count, shard_shift;
+  int batch_lanes, batch_wait;  // phase-B batching of the ray marcher (see vk_raycast_kernel)
+  int debug_only_x;             // diagnostics: march only the tile column starting at this x
+  int lookahead;                // prefetch distance of the ray marcher in voxel steps (0 = off)
+  unsigned long long* timeline; // diagnostics: per-warp (start, end) globaltimer, or NULL
 };
 
-// memo of the last hash lookup of this lane; the table is read-only during a trace so
-// replaying a lookup from the memo is exact
-struct Lookup {
-  unsigned long long key;
-  int data;
+// Per-lane cache of block lookups in shared memory: kCacheSlots (coordinates -> voxel-block id,
+// or -1 = no such block) per lane, direct mapped.  The hash table is read-only during a trace, so
+// replaying a lookup from the cache is exact.  A ray looks up the same few blocks over and over
+// (the block under it for ~8 steps, and its face neighbours for the interpolation taps); the
+// cache turns those hash walks into one shared-memory probe, and lets the look-ahead prefetch
+// resolve blocks without ever waiting on the table.
+constexpr int kCacheSlots = 8;
+constexpr int kMaxRayThreads = 64;
+struct BlockCache {
+  unsigned long long* keys;  // [kCacheSlots][blockDim.x], this lane's column
+  int* data;
+  int stride;
+  __device__ __forceinline__ static int slot(int bx, int by, int bz) { return (bx + 3 * by + 5 * bz) & (kCacheSlots - 1); }
+  __device__ __forceinline__ bool peek(int bx, int by, int bz, int& out) const {
+    const int s = slot(bx, by, bz) * stride;
+    if (keys[s] != pack_block(bx, by, bz)) return false;
+    out = data[s];
+    return true;
+  }
+  __device__ __forceinline__ void put(int bx, int by, int bz, int value) {
+    const int s = slot(bx, by, bz) * stride;
+    keys[s] = pack_block(bx, by, bz);
+    data[s] = value;
+  }
 };
 
 // `while (entry.block != b && entry.HasNext()) entry = entries[entry.next];`
@@ -252,17 +277,16 @@ __device__ __forceinline__ int lookup_block(const TraceParams& p, int bx, int by
   const uint32_t h = block_hash(bx, by, bz, p.K);
   // an unallocated bucket head has no chain: most steps through free space end here, on a
   // 32 KB bitmap that stays in L1, instead of on a 16-byte entry fetched from L2
-  if (p.bucket_bits && !((__ldg(p.bucket_bits + (h >> 5)) >> (h & 31)) & 1u)) return -1;
+  if (p.bucket_bits && !p.space_bits && !((__ldg(p.bucket_bits + (h >> 5)) >> (h & 31)) & 1u)) return -1;
   int4 e = ld_entry(p.entries + h);
   while (entry_block(e) != key && e.w != -1) e = ld_entry(p.entries + e.w);
   return (entry_block(e) == key) ? e.z : -1;
 }
-__device__ __forceinline__ int find_data(const TraceParams& p, Lookup& memo, int bx, int by, int bz) {
-  const unsigned long long key = pack_block(bx, by, bz);
-  if (key == memo.key) return memo.data;
-  const int data = lookup_block(p, bx, by, bz);
-  memo.key = key;
-  memo.data = data;
+__device__ __forceinline__ int find_data(const TraceParams& p, BlockCache& cache, int bx, int by, int bz) {
+  int data;
+  if (cache.peek(bx, by, bz, data)) return data;
+  data = lookup_block(p, bx, by, bz);
+  cache.put(bx, by, bz, data);
   return data;
 }
 
@@ -281,8 +305,11 @@ struct Taps {
   float w1x, w1y, w1z;
 };
 
-__device__ __forceinline__ void resolve_taps(const TraceParams& p, int bx, int by, int bz, int home, float wx,
-                                             float wy, float wz, Taps& t) {
+// PEEK: resolve neighbour blocks from the cache only (a miss reads as "no block"); used by the
+// look-ahead prefetch, which must never wait on the hash table.
+template <bool PEEK>
+__device__ __forceinline__ void resolve_taps(const TraceParams& p, BlockCache& cache, int bx, int by, int bz,
+                                             int home, float wx, float wy, float wz, Taps& t) {
   const int i0x = (int)floorf(add(wx, -0.5f));
   const int i0y = (int)floorf(add(wy, -0.5f));
   const int i0z = (int)floorf(add(wz, -0.5f));
@@ -309,7 +336,9 @@ __device__ __forceinline__ void resolve_taps(const TraceParams& p, int bx, int b
     int d;
     if (r == c) {
       const int dx = ox[tx], dy = oy[ty], dz = oz[tz];
-      d = ((dx | dy | dz) == 0) ? home : lookup_block(p, bx + dx, by + dy, bz + dz);
+      if ((dx | dy | dz) == 0) d = home;
+      else if (PEEK) { if (!cache.peek(bx + dx, by + dy, bz + dz, d)) d = -1; }
+      else d = find_data(p, cache, bx + dx, by + dy, bz + dz);
     } else {
       d = t.data[0];
 #pragma unroll
@@ -381,6 +410,39 @@ __device__ __forceinline__ Vec3 interp_color(const TraceParams& p, const Taps& t
 
 namespace vk {
 
+constexpr int kFreeUnroll = 4;
+
+__device__ __forceinline__ bool space_bit(const TraceParams& p, int bx, int by, int bz) {
+  uint32_t sw, sb;
+  space_bit_index(bx, by, bz, sw, sb);
+  return (__ldg(p.space_bits + sw) >> sb) & 1u;
+}
+
+// Look-ahead prefetch.  Inside the interpolation band a marching ray advances by exactly one voxel
+// length per trip (step = max(l, trunc * sdf) with sdf <= 0.1), and every trip would otherwise
+// wait for voxels nobody has touched yet: the kernel's duration was the latency chain of the
+// longest grazing ray (120 trips x ~1.1 us).  So each such trip prefetches the distances of the
+// 8 taps around p + k * l * dir into L1.  Addresses come from plain (not bit-exact) arithmetic
+// and from the lane's block cache only; a wrong guess costs a useless prefetch, never a result.
+__device__ __forceinline__ void prefetch_ahead(const TraceParams& p, BlockCache& cache, const Vec3& pt,
+                                               const Vec3& dir, float k) {
+  const float s = k * p.voxel_length.d;
+  const float qx = fmaf(dir.x, s, pt.x), qy = fmaf(dir.y, s, pt.y), qz = fmaf(dir.z, s, pt.z);
+  const int bx = (int)floorf(qx * p.block_length.r);
+  const int by = (int)floorf(qy * p.block_length.r);
+  const int bz = (int)floorf(qz * p.block_length.r);
+  int home;
+  if (!cache.peek(bx, by, bz, home) || home == -1) return;
+  const float wx = (qx - (float)bx * p.block_length.d) * p.voxel_length.r;
+  const float wy = (qy - (float)by * p.block_length.d) * p.voxel_length.r;
+  const float wz = (qz - (float)bz * p.block_length.d) * p.voxel_length.r;
+  Taps t;
+  resolve_taps<true>(p, cache, bx, by, bz, home, wx, wy, wz, t);
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    if (t.data[c] != -1) asm volatile("prefetch.global.L1 [%0];" ::"l"(voxel_words(p, t.data[c], t.off[c])));
+}
+
 enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
 
 // ComputePointsKernel (src/tracer.cu:317-451).
@@ -391,13 +453,28 @@ enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
 //   w   = (p - b*L) / l                  FFMA -b*L + p ; IEEE division
 //   p  += dir * s                        FFMA dir*s + p   (s = L | max(l, trunc*sdf) | trunc*sdf)
 //   depth = (Tcw * (p,1)).z              xform1 row 2
+//
+// One warp marches an 8x4 pixel tile.  Every lane is a small state machine; a loop trip is
+//   phase A (cheap, every running lane): block under p, hash lookup, nearest-voxel sample;
+//   phase B (expensive, ~4x phase A): the 8-tap interpolation for lanes that asked for one.
+// Lanes that need phase B PARK (keep their block / voxel coordinates in registers) while the
+// other lanes keep taking cheap steps; phase B runs for all parked lanes at once when at least
+// `batch_lanes` are parked, when nobody else can advance, or after `batch_wait` trips - so the
+// expensive instructions run with most lanes active instead of 7-9 of 32.  The order of
+// operations of each ray is unchanged, so the result is bit-identical to the per-ray loop.
 template <bool F, bool KEYS>
-__global__ void __launch_bounds__(64) vk_raycast_kernel(const TraceParams p) {
+__global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const TraceParams p) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  // CTA tile 8x8 pixels, warp tile 8x4
+  const int wpc = blockDim.x >> 5;
+  // warp tile 8x4 pixels, CTA = wpc tiles stacked in y
   const int x = blockIdx.x * 8 + (lane & 7);
-  const int y = blockIdx.y * 8 + warp * 4 + (lane >> 3);
+  const int y = (blockIdx.y * wpc + warp) * 4 + (lane >> 3);
   const bool inside = (x < p.w && y < p.h);
+  unsigned long long t_start = 0;
+  if (p.timeline) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+  const long long c_start = clock64();
+  int dbg_trips = 0;
+  long long c_free = 0, c_a = 0, c_b = 0, c_t = 0;
 
   float lo = 0.f, hi = 0.f;
   if (inside) {
@@ -409,6 +486,7 @@ __global__ void __launch_bounds__(64) vk_raycast_kernel(const TraceParams p) {
   }
 
   int state = (inside && lo < hi) ? ST_MARCH : ST_DONE;
+  if (p.debug_only_x && (int)(blockIdx.x * 8) != p.debug_only_x) state = ST_DONE;  // diagnostics
   float final_depth = 0.f;
   bool red = false;         // iteration cap hit: colour (1, 0, 0)
   bool has_interp = false;  // an interpolation happened: colour comes from its taps
@@ -418,9 +496,14 @@ __global__ void __launch_bounds__(64) vk_raycast_kernel(const TraceParams p) {
   Mat34 Tcw;
   Tcw.load(p.Tcw);
   int iters = 0;
-  Lookup memo;
-  memo.key = ~0ull;
-  memo.data = -1;
+  __shared__ unsigned long long s_keys[kCacheSlots * kMaxRayThreads];
+  __shared__ int s_data[kCacheSlots * kMaxRayThreads];
+  BlockCache cache;
+  cache.keys = s_keys + threadIdx.x;
+  cache.data = s_data + threadIdx.x;
+  cache.stride = blockDim.x;
+#pragma unroll
+  for (int i = 0; i < kCacheSlots; ++i) cache.keys[i * cache.stride] = ~0ull;
 
   if (state == ST_MARCH) {
     Mat34 Twc;
@@ -433,80 +516,173 @@ __global__ void __launch_bounds__(64) vk_raycast_kernel(const TraceParams p) {
     dir = normalized<F>(xform0<F>(Twc, cx, cy, cz));
   }
 
+  // parked lane: waits for phase B with the block / voxel coordinates of its point
+  bool parked = false;
+  int kbx = 0, kby = 0, kbz = 0, kdata = -1;
+  float kwx = 0.f, kwy = 0.f, kwz = 0.f;
+  int waited = 0;  // warp-uniform: trips since a lane parked without phase B running
+
+  // transitions of a lane whose block was found, given the distance the reference would hold in
+  // `sdf` at that point (src/tracer.cu:398-437)
+  auto advance = [&](float sdf, int bx, int by, int bz) -> bool {
+    if (state == ST_MARCH) {
+      if (sdf <= 0.0f) {
+        if (KEYS) owned_hit = (shard_owner(bx, by, bz, p.shard_shift, p.shard_count) == p.shard_rank);
+        const float s = mul(p.trunc, sdf);
+        pt.x = FP<F>::mad(dir.x, s, pt.x);
+        pt.y = FP<F>::mad(dir.y, s, pt.y);
+        pt.z = FP<F>::mad(dir.z, s, pt.z);
+        state = ST_REFINE;
+        return false;
+      }
+      const float s = vmax(p.voxel_length.d, mul(p.trunc, sdf));
+      pt.x = FP<F>::mad(dir.x, s, pt.x);
+      pt.y = FP<F>::mad(dir.y, s, pt.y);
+      pt.z = FP<F>::mad(dir.z, s, pt.z);
+      return true;  // stepped: depth / iteration test follows
+    }
+    // ST_REFINE, block found: second refinement step, then the final depth
+    const float s = mul(p.trunc, sdf);
+    pt.x = FP<F>::mad(dir.x, s, pt.x);
+    pt.y = FP<F>::mad(dir.y, s, pt.y);
+    pt.z = FP<F>::mad(dir.z, s, pt.z);
+    final_depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
+    state = ST_DONE;
+    return false;
+  };
+  auto after_step = [&]() {
+    const float depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
+    if (++iters >= 500) { red = true; state = ST_DONE; }
+    else if (!(depth < hi)) state = ST_DONE;
+  };
+
+  auto block_of = [&](const Vec3& q, int& ix, int& iy, int& iz) {
+    float fx, fy, fz;
+    divc3(q.x, q.y, q.z, p.block_length, fx, fy, fz);
+    ix = (int)floorf(fx);
+    iy = (int)floorf(fy);
+    iz = (int)floorf(fz);
+  };
+
   while (__any_sync(0xffffffffu, state != ST_DONE)) {
-    if (state != ST_DONE) {
-      // ---- phase A: block under p -----------------------------------------------------
-      const int bx = (int)floorf(divc(pt.x, p.block_length));
-      const int by = (int)floorf(divc(pt.y, p.block_length));
-      const int bz = (int)floorf(divc(pt.z, p.block_length));
-      const int data = find_data(p, memo, bx, by, bz);
-      bool want_interp = false;
-      bool stepped = false;   // MARCH lane that advanced: depth / iteration test follows
-      float sdf = 0.f;
-      float wx = 0.f, wy = 0.f, wz = 0.f;
+    ++dbg_trips;
+    if (p.timeline) c_t = clock64();
+    // ---- phase A: block under p, nearest voxel ---------------------------------------------
+    int bx = 0, by = 0, bz = 0;
+    if (state != ST_DONE && !parked) {
+      block_of(pt, bx, by, bz);
+      // Free-space run.  While the filter proves that no block exists under p, the reference's
+      // trip is "block not found": p += L * dir, then the depth / iteration test - so the next
+      // kFreeUnroll positions are known in advance.  They are evaluated together (independent
+      // division / filter-load chains instead of one dependent chain per step: a lone warp issues
+      // ~1 instruction per 10 cycles, and the kernel's duration is its longest ray) and then
+      // committed in order up to the first position that is occupied, out of range or the cap.
+      if (state == ST_MARCH && p.free_run > 0 && !space_bit(p, bx, by, bz)) {
+        for (int n = 0; n < p.free_run && state == ST_MARCH; ++n) {
+          Vec3 q[kFreeUnroll];
+          float qd[kFreeUnroll];
+          int qb[kFreeUnroll][3];
+          bool occ[kFreeUnroll];
+          Vec3 c = pt;
+#pragma unroll
+          for (int k = 0; k < kFreeUnroll; ++k) {
+            c.x = FP<F>::mad(dir.x, p.block_length.d, c.x);
+            c.y = FP<F>::mad(dir.y, p.block_length.d, c.y);
+            c.z = FP<F>::mad(dir.z, p.block_length.d, c.z);
+            q[k] = c;
+          }
+#pragma unroll
+          for (int k = 0; k < kFreeUnroll; ++k) {
+            qd[k] = xform1_z<F>(Tcw, q[k].x, q[k].y, q[k].z);
+            block_of(q[k], qb[k][0], qb[k][1], qb[k][2]);
+            occ[k] = space_bit(p, qb[k][0], qb[k][1], qb[k][2]);
+          }
+          bool stop = false;
+#pragma unroll
+          for (int k = 0; k < kFreeUnroll; ++k) {
+            if (!stop) {
+              pt = q[k];
+              bx = qb[k][0]; by = qb[k][1]; bz = qb[k][2];
+              if (++iters >= 500) { red = true; state = ST_DONE; stop = true; }
+              else if (!(qd[k] < hi)) { state = ST_DONE; stop = true; }
+              else if (occ[k]) stop = true;
+            }
+          }
+          if (stop) break;
+        }
+      }
+    }
+    if (p.timeline) { const long long c = clock64(); c_free += c - c_t; c_t = c; }
+    if (state != ST_DONE && !parked) {
+      const int data = find_data(p, cache, bx, by, bz);
       if (data != -1) {
-        wx = divc(FP<F>::nmad((float)bx, p.block_length.d, pt.x), p.voxel_length);
-        wy = divc(FP<F>::nmad((float)by, p.block_length.d, pt.y), p.voxel_length);
-        wz = divc(FP<F>::nmad((float)bz, p.block_length.d, pt.z), p.voxel_length);
+        float wx, wy, wz;
+        divc3(FP<F>::nmad((float)bx, p.block_length.d, pt.x), FP<F>::nmad((float)by, p.block_length.d, pt.y),
+              FP<F>::nmad((float)bz, p.block_length.d, pt.z), p.voxel_length, wx, wy, wz);
+        bool want = true;
+        float sdf = 0.f;
         if (state == ST_MARCH) {
           const int vx = (int)wx, vy = (int)wy, vz = (int)wz;  // Q22: may be 8 on a face
           sdf = __uint_as_float(__ldg(voxel_words(p, data, vz * 64 + vy * 8 + vx)));
-          want_interp = (sdf <= 0.1f && sdf >= -0.5f);
-        } else {
-          want_interp = true;
+          want = (sdf <= 0.1f && sdf >= -0.5f);
+        }
+        if (want) {
+          parked = true;
+          kbx = bx; kby = by; kbz = bz; kdata = data;
+          kwx = wx; kwy = wy; kwz = wz;
+        } else if (advance(sdf, bx, by, bz)) {
+          after_step();
         }
       } else if (state == ST_MARCH) {
         pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
         pt.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
         pt.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
-        stepped = true;
+        after_step();
       } else {
         // REFINE without a block under the backed-up point: no second interpolation
         final_depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
         state = ST_DONE;
       }
-      // ---- phase B: interpolation, one copy for first hit test and refinement ------------
-      if (want_interp) {
-        Taps taps;
-        resolve_taps(p, bx, by, bz, data, wx, wy, wz, taps);
-        sdf = interp_distance<F>(p, taps);
-        ipt = pt;
-        has_interp = true;
-      }
-      // ---- phase C: transitions ------------------------------------------------------------
-      if (data != -1) {
-        if (state == ST_MARCH) {
-          if (sdf <= 0.0f) {
-            if (KEYS) owned_hit = (shard_owner(bx, by, bz, p.shard_shift, p.shard_count) == p.shard_rank);
-            const float s = mul(p.trunc, sdf);
-            pt.x = FP<F>::mad(dir.x, s, pt.x);
-            pt.y = FP<F>::mad(dir.y, s, pt.y);
-            pt.z = FP<F>::mad(dir.z, s, pt.z);
-            state = ST_REFINE;
-          } else {
-            const float s = vmax(p.voxel_length.d, mul(p.trunc, sdf));
-            pt.x = FP<F>::mad(dir.x, s, pt.x);
-            pt.y = FP<F>::mad(dir.y, s, pt.y);
-            pt.z = FP<F>::mad(dir.z, s, pt.z);
-            stepped = true;
-          }
-        } else {  // ST_REFINE, block found: second refinement step, then the final depth
-          const float s = mul(p.trunc, sdf);
-          pt.x = FP<F>::mad(dir.x, s, pt.x);
-          pt.y = FP<F>::mad(dir.y, s, pt.y);
-          pt.z = FP<F>::mad(dir.z, s, pt.z);
-          final_depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
-          state = ST_DONE;
+    }
+    // ---- phase B: interpolation for the parked lanes, batched ------------------------------
+    if (p.timeline) { const long long c = clock64(); c_a += c - c_t; c_t = c; }
+    const unsigned pm = __ballot_sync(0xffffffffu, parked);
+    if (pm) {
+      const unsigned fm = __ballot_sync(0xffffffffu, state != ST_DONE && !parked);
+      if (fm == 0 || __popc(pm) >= p.batch_lanes || waited >= p.batch_wait) {
+        if (parked) {
+          Taps taps;
+          resolve_taps<false>(p, cache, kbx, kby, kbz, kdata, kwx, kwy, kwz, taps);
+          if (state == ST_MARCH && p.lookahead > 0) prefetch_ahead(p, cache, pt, dir, (float)p.lookahead);
+          const float sdf = interp_distance<F>(p, taps);
+          ipt = pt;
+          has_interp = true;
+          parked = false;
+          if (advance(sdf, kbx, kby, kbz)) after_step();
         }
-      }
-      if (stepped) {
-        const float depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
-        if (++iters >= 500) { red = true; state = ST_DONE; }
-        else if (!(depth < hi)) state = ST_DONE;
+        waited = 0;
+      } else {
+        ++waited;
       }
     }
+    if (p.timeline) { const long long c = clock64(); c_b += c - c_t; c_t = c; }
   }
 
+  if (p.timeline && lane == 0) {
+    unsigned long long t_end;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+    const size_t wid = ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * wpc + warp;
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    p.timeline[8 * wid] = t_start;
+    p.timeline[8 * wid + 1] = t_end;
+    p.timeline[8 * wid + 2] = ((unsigned long long)smid << 32) | (unsigned)dbg_trips;
+    p.timeline[8 * wid + 3] = (unsigned long long)(clock64() - c_start);
+    p.timeline[8 * wid + 4] = (unsigned long long)c_free;
+    p.timeline[8 * wid + 5] = (unsigned long long)c_a;
+    p.timeline[8 * wid + 6] = (unsigned long long)c_b;
+    p.timeline[8 * wid + 7] = (unsigned long long)(c_t - c_start);
+  }
   if (!inside) return;
   // colour of the last interpolation (Q13: kept even on a miss), evaluated once per ray
   Vec3 color = {0.f, 0.f, 0.f};
@@ -516,12 +692,12 @@ __global__ void __launch_bounds__(64) vk_raycast_kernel(const TraceParams p) {
     const int bx = (int)floorf(divc(ipt.x, p.block_length));
     const int by = (int)floorf(divc(ipt.y, p.block_length));
     const int bz = (int)floorf(divc(ipt.z, p.block_length));
-    const int data = lookup_block(p, bx, by, bz);
+    const int data = find_data(p, cache, bx, by, bz);
     const float wx = divc(FP<F>::nmad((float)bx, p.block_length.d, ipt.x), p.voxel_length);
     const float wy = divc(FP<F>::nmad((float)by, p.block_length.d, ipt.y), p.voxel_length);
     const float wz = divc(FP<F>::nmad((float)bz, p.block_length.d, ipt.z), p.voxel_length);
     Taps taps;
-    resolve_taps(p, bx, by, bz, data, wx, wy, wz, taps);
+    resolve_taps<false>(p, cache, bx, by, bz, data, wx, wy, wz, taps);
     color = interp_color<F>(p, taps);
   }
 
@@ -655,6 +831,10 @@ __global__ void __launch_bounds__(256) vk_filter_depths_kernel(int w, int h, con
 
 using namespace vk;
 
+// diagnostics hook (tools/tune_bench.py --timeline): device buffer of 2 x u64 per ray-march warp
+static std::atomic<unsigned long long*> g_trace_timeline{nullptr};
+extern "C" void vk_debug_trace_timeline(unsigned long long* device_buffer) { g_trace_timeline.store(device_buffer); }
+
 extern "C" int vk_reset_bounds(float* bounds, int count, void* stream) {
   if (!bounds || count < 0) return VK_E_INVALID;
   if (count == 0) return 0;
@@ -716,6 +896,8 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.voxels = voxels;
   t.bounds = bounds;
   t.bucket_bits = bucket_bits;
+  t.space_bits = nullptr;
+  t.free_run = 0;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
   t.voxel_length = make_div(voxel_length, s);
@@ -726,19 +908,27 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.depths = nullptr; t.colors = nullptr; t.keys = nullptr;
   t.w = w; t.h = h; t.bw = bw; t.bh = bh;
   t.shard_rank = 0; t.shard_count = 1; t.shard_shift = 0;
+  t.batch_lanes = g_tune[VK_TUNE_RAY_BATCH_LANES].load();
+  t.batch_wait = g_tune[VK_TUNE_RAY_BATCH_WAIT].load();
+  t.lookahead = g_tune[VK_TUNE_RAY_LOOKAHEAD].load();
+  t.debug_only_x = g_tune[6].load();
+  t.timeline = g_trace_timeline.load();
 }
 
 template <bool KEYS>
 static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
-  dim3 grid((t.w + 7) / 8, (t.h + 7) / 8);
-  if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, KEYS><<<grid, 64, 0, s>>>(t);
-  else vk_raycast_kernel<true, KEYS><<<grid, 64, 0, s>>>(t);
+  const int threads = (g_tune[VK_TUNE_RAY_CTA_THREADS].load() == 64) ? 64 : 32;
+  const int rows = 4 * (threads / 32);
+  dim3 grid((t.w + 7) / 8, (t.h + rows - 1) / rows);
+  if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, KEYS><<<grid, threads, 0, s>>>(t);
+  else vk_raycast_kernel<true, KEYS><<<grid, threads, 0, s>>>(t);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
 
 static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels, const float* bounds,
-                               const uint32_t* bucket_bits, int block_count, float block_length, float voxel_length, float trunc_length,
+                               const uint32_t* bucket_bits, const uint32_t* space_bits, int block_count, float block_length,
+                               float voxel_length, float trunc_length,
                                const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
                                int image_w, int image_h, int bounds_w, int bounds_h, int math_mode, cudaStream_t s) {
   if (!entries || !voxels || !bounds || !Twc || !proj || !depths || !colors || image_w <= 0 || image_h <= 0)
@@ -748,6 +938,10 @@ static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels
                     Twc, proj, image_w, image_h, bounds_w, bounds_h, s);
   t.depths = depths;
   t.colors = colors;
+  if (space_bits) {
+    t.space_bits = space_bits;
+    t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
+  }
   return launch_raycast<false>(t, math_mode, s);
 }
 
@@ -755,7 +949,7 @@ extern "C" int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxe
                                  int block_count, float block_length, float voxel_length, float trunc_length,
                                  const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
                                  int image_w, int image_h, int bounds_w, int bounds_h, void* stream) {
-  return compute_points_mode(entries, voxels, bounds, nullptr, block_count, block_length, voxel_length, trunc_length, Twc,
+  return compute_points_mode(entries, voxels, bounds, nullptr, nullptr, block_count, block_length, voxel_length, trunc_length, Twc,
                              proj, depths, colors, image_w, image_h, bounds_w, bounds_h,
                              g_default_math_mode.load(), (cudaStream_t)stream);
 }
@@ -809,7 +1003,7 @@ extern "C" int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth,
   cudaStream_t s = (cudaStream_t)stream;
   int rc = trace_bounds(v, view, min_depth, max_depth, bounds, s);
   if (rc) return rc;
-  rc = compute_points_mode(v->entries, v->voxels, bounds, v->bucket_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
+  rc = compute_points_mode(v->entries, v->voxels, bounds, v->bucket_bits, v->space_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
                            v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, out_depth,
                            out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, v->math_mode, s);
   if (rc) return rc;
@@ -829,6 +1023,8 @@ extern "C" int vk_trace_keys(const vkVolume* v, const vkFrame* view, float min_d
                     v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, view->depth_w,
                     view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
   t.keys = out_keys;
+  t.space_bits = v->space_bits;
+  t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
   t.shard_rank = v->shard_rank;
   t.shard_count = v->shard_count;
   t.shard_shift = v->shard_shift;
