@@ -22,7 +22,7 @@ import harness as H  # noqa: E402
 import vulcan_b200 as vb  # noqa: E402
 
 W, Hh = 640, 480
-KNOB = {"ray_threads": 0, "ray_lanes": 1, "ray_wait": 2, "int_ctas": 3, "alloc_mode": 4, "ray_ahead": 5, "free_run": 7}
+KNOB = {"ray_threads": 0, "ray_lanes": 1, "ray_wait": 2, "int_ctas": 3, "alloc_mode": 4, "coop": 5, "free_run": 7}
 
 
 def main():
@@ -103,25 +103,26 @@ def main():
             print("  long warp tile (x=%d,y=%d): start %.1f dur %.1f  sm %d trips %d cycles %d (%.0f cyc/trip)" % (
                 (w_ % (W // 8)) * 8, (w_ // (W // 8)) * 4, start[w_], dur[w_], t[w_, 2] >> 32, t[w_, 2] & 0xffffffff,
                 t[w_, 3], t[w_, 3] / max(1, t[w_, 2] & 0xffffffff)))
-            print("      cycles: free-run %d  phase A %d  phase B %d  loop-end at %d" % (t[w_, 4], t[w_, 5], t[w_, 6], t[w_, 7]))
+            print("      cycles: free-run %d  phase A %d  phase B %d  max-lane free steps %d rounds %d" % (t[w_, 4], t[w_, 5], t[w_, 6], t[w_, 7] & 0xffffffff, t[w_, 7] >> 32))
         trips = (t[:, 2] & 0xffffffff).astype(np.float64)
         print("  all warps: trips total %d, cycles/trip mean %.0f" % (trips.sum(), t[:, 3].sum() / trips.sum()))
         np.save(os.path.join(ROOT, "gpurun_out", "trace_timeline.npy"), t)
     if "ray" in what:
         ref = None
-        for threads, ahead, lanes, wait, frun in ((32, 0, 1, 0, 0), (32, 0, 1, 0, 1), (32, 0, 1, 0, 4), (32, 0, 1, 0, 8),
-                                                  (32, 0, 1, 0, 32), (32, 0, 12, 3, 8), (32, 0, 16, 4, 8), (64, 0, 1, 0, 8),
-                                                  (64, 0, 12, 3, 8), (32, 2, 1, 0, 8)):
+        # (threads per CTA, cooperative-run lane threshold, phase-B batch lanes, batch wait, free-run steps per trip)
+        for threads, ahead, lanes, wait, frun in ((32, 0, 1, 0, 8), (32, 2, 1, 0, 8), (32, 4, 1, 0, 8), (32, 8, 1, 0, 8),
+                                                  (32, 16, 1, 0, 8), (32, 4, 1, 0, 2), (32, 4, 1, 0, 16), (32, 4, 12, 3, 8),
+                                                  (64, 4, 1, 0, 8), (64, 8, 1, 0, 8), (64, 4, 12, 3, 8)):
             if True:
                 lib.vk_tune(KNOB["free_run"], frun)
-                lib.vk_tune(KNOB["ray_ahead"], ahead)
+                lib.vk_tune(KNOB["coop"], ahead)
                 lib.vk_tune(KNOB["ray_threads"], threads)
                 lib.vk_tune(KNOB["ray_lanes"], lanes)
                 lib.vk_tune(KNOB["ray_wait"], wait)
                 med, mn = timed(lambda: tracer.Trace(out))
                 d = digest()
                 ref = ref or d
-                results.append(dict(phase="trace", threads=threads, free_run=frun, ahead=ahead, lanes=lanes, wait=wait, med_us=med, min_us=mn,
+                results.append(dict(phase="trace", threads=threads, free_run=frun, coop=ahead, lanes=lanes, wait=wait, med_us=med, min_us=mn,
                                     same=(d == ref)))
                 print(json.dumps(results[-1]), flush=True)
     if "int" in what:

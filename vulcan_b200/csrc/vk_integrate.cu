@@ -9,9 +9,11 @@
 // list (no host read-back of the count).  A thread owns 4 consecutive voxels of a row
 // (80 bytes = 5 aligned 16-byte chunks of the AoS tile), decides from the projection
 // and the depth image alone whether any of them can change, and only then moves the
-// 80 bytes - asynchronously, through a two-stage shared-memory ring (cp.async), one block
-// ahead of the update; depth and colour updates happen in one pass, and only the 16-byte
-// chunks that changed are written back.
+// 80 bytes with 128-bit loads; depth and colour updates happen on the registers in
+// one pass, and only the 16-byte chunks that changed are written back.
+// (A cp.async double-buffered variant that staged the 80-byte pieces through shared memory one
+// block ahead was measured on B200 and was slower: 68 us against 55 us per frame on the bench
+// workload - the loads of ~36 resident warps per SM already cover the latency.)
 #include "vk_math.cuh"
 #include "vk_launch.h"
 #include <cfloat>
@@ -39,124 +41,104 @@ struct IntegrateParams {
   vkLight light;
 };
 
-// 16-byte asynchronous global -> shared copy (LDGSTS), L2 only: voxel tiles are streamed once
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
-
-// What a thread knows about its 4 voxels of one block before it has seen the voxels: which of
-// them the frame can change, from the projection and the images alone.
-template <int MODE>
-struct Geo {
-  float dcur[4];                         // depth - Xd.z where the depth update applies
-  int cidx[MODE == MODE_DEPTH ? 1 : 4];  // colour pixel
-  int didx[MODE == MODE_LIGHT ? 4 : 1];  // depth pixel (light mode)
-  unsigned flags;                        // bit k: depth update applies; bit 4+k: colour-side test passes
-};
-
 // FMA map (reference release SASS, see vk_math.cuh):
 //   Xw      = L*o + l*(v+0.5)          FMUL o*L ; FFMA (v+0.5)*l + .      depth_integrator.cu:36-39
 //   D'      = (w*D + cur) / (w+1)      FFMA D*w + cur ; IEEE div         depth_integrator.cu:68-76
 //   C'      = (cw*C + c) * (1/(cw+1))  FFMA C*cw + c ; FMUL              color_integrator.cu:121-126
 //   C'light = (cw*C + c*(1/s)) * ...   FMUL C*cw ; FFMA c*(1/s) + . ; FMUL  light_integrator.cu:238-241
-//
-// Software pipeline per CTA over its blocks b0, b1, ... (two shared-memory stages of 128 x 80 B):
-//   trip i:  geometry(b[i+1]) (depth-image gathers)  ->  cp.async of b[i+1]'s needed 80-byte
-//            pieces into stage (i+1)&1  ->  wait for stage i&1  ->  update b[i] from shared memory,
-//            write back the dirty 16-byte chunks.
-// So the voxel bytes of the next block and the image gathers of the one after are in flight
-// while a block is updated; a thread only ever reads the bytes it copied itself, hence no barrier.
 template <int MODE, bool F>
 __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams p) {
-  __shared__ uint4 s_tile[2 * 5 * 128];  // [stage][chunk][thread]
   const int n = *p.count;
   const int t = threadIdx.x;
   const int vz = t >> 4, vy = (t >> 1) & 7, vx0 = (t & 1) * 4;
+  Mat34 Tdw, Tcw;
+  Tdw.load(p.Tdw);
+  if (MODE != MODE_DEPTH) Tcw.load(p.Tcw);
   unsigned n_updated = 0;
   const float fy = add((float)vy, 0.5f), fz = add((float)vz, 0.5f);
-  const int G = gridDim.x;
 
-  auto voxel_x = [&](int iox, int k) {
-    return FP<F>::mad(add((float)(vx0 + k), 0.5f), p.voxel_length, mul((float)iox, p.block_length));
-  };
-
-  auto geometry = [&](const int4& ent, Geo<MODE>& g) {
-    Mat34 Tdw, Tcw;
-    Tdw.load(p.Tdw);
-    if (MODE != MODE_DEPTH) Tcw.load(p.Tcw);
+  int bi = blockIdx.x;
+  int e_next = (bi < n) ? __ldg(p.visible + bi) : 0;
+  int4 ent_next = ld_entry(p.entries + e_next);
+  for (; bi < n; bi += gridDim.x) {
+    const int4 ent = ent_next;
+    // next block's list slot and entry are fetched while this block is processed
+    const int bn = bi + gridDim.x;
+    if (bn < n) e_next = __ldg(p.visible + bn);
     int iox, ioy, ioz;
     entry_origin(ent, iox, ioy, ioz);
     const float Xy = FP<F>::mad(fy, p.voxel_length, mul((float)ioy, p.block_length));
     const float Xz = FP<F>::mad(fz, p.voxel_length, mul((float)ioz, p.block_length));
-    g.flags = 0;
+    const float bxl = mul((float)iox, p.block_length);
+
+    bool dpass[4];          // depth update applies
+    float dcur[4];          // depth - Xd.z
+    bool cin[4];            // colour-side geometric test passes
+    int cidx[4];            // colour pixel
+    int didx[4];            // depth pixel (light mode)
+    Vec3 Xc[4];
+    bool need = false;
+
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const float Xx = voxel_x(iox, k);
+      const float Xx = FP<F>::mad(add((float)(vx0 + k), 0.5f), p.voxel_length, bxl);
       const Vec3 Xd = xform1<F>(Tdw, Xx, Xy, Xz);
       float u, v;
       project<F>(p.dproj, Xd, u, v);
       const bool din = (u >= 0 && u < (float)p.dw && v >= 0 && v < (float)p.dh);
-      g.dcur[k] = 0.f;
+      dpass[k] = false;
+      dcur[k] = 0.f;
       int di = 0;
       if (din) {
         di = (int)v * p.dw + (int)u;
         const float d = __ldg(p.depth + di);
         if (!(d < p.min_depth || d > p.max_depth)) {
           const float s = sub(d, Xd.z);
-          if (s > -p.trunc.d) { g.flags |= 1u << k; g.dcur[k] = s; }
+          if (s > -p.trunc.d) { dpass[k] = true; dcur[k] = s; }
         }
       }
+      need |= dpass[k];
       if (MODE == MODE_COLOR) {
-        const Vec3 Xc = xform1<F>(Tcw, Xx, Xy, Xz);
+        Xc[k] = xform1<F>(Tcw, Xx, Xy, Xz);
         float cu, cv;
-        project<F>(p.cproj, Xc, cu, cv);
-        const bool ok = (cu >= 0 && cu < (float)p.cw && cv >= 0 && cv < (float)p.ch);
-        g.cidx[k] = ok ? (int)cv * p.cw + (int)cu : 0;
-        if (ok) g.flags |= 16u << k;
+        project<F>(p.cproj, Xc[k], cu, cv);
+        cin[k] = (cu >= 0 && cu < (float)p.cw && cv >= 0 && cv < (float)p.ch);
+        cidx[k] = cin[k] ? (int)cv * p.cw + (int)cu : 0;
+        need |= cin[k];
       } else if (MODE == MODE_LIGHT) {
         // both projections are tested against the depth image size (src/light_integrator.cu:207-215,335-336)
-        const Vec3 Xc = xform1<F>(Tcw, Xx, Xy, Xz);
+        Xc[k] = xform1<F>(Tcw, Xx, Xy, Xz);
         float cu, cv;
-        project<F>(p.cproj, Xc, cu, cv);
+        project<F>(p.cproj, Xc[k], cu, cv);
         bool ok = din && (cu >= 0 && cu < (float)p.dw && cv >= 0 && cv < (float)p.dh);
-        g.didx[k] = di;
-        g.cidx[k] = ok ? (int)cv * p.dw + (int)cu : 0;
+        didx[k] = di;
+        cidx[k] = ok ? (int)cv * p.dw + (int)cu : 0;
         if (ok) ok = __ldg(p.mask + di) > 0.5f;
-        if (ok) g.flags |= 16u << k;
+        cin[k] = ok;
+        need |= ok;
       }
     }
-  };
+    if (bn < n) ent_next = ld_entry(p.entries + e_next);
+    if (!need) continue;
 
-  auto tile_ptr = [&](int data) {
-    return reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) +
-                                    (size_t)data * (VK_BLOCK_VOXELS * sizeof(vkVoxel)) + (size_t)t * 80);
-  };
-  auto fetch = [&](int stage, int data) {
-    const uint4* src = tile_ptr(data);
-#pragma unroll
-    for (int c = 0; c < 5; ++c) cp_async16(&s_tile[(stage * 5 + c) * 128 + t], src + c);
-  };
-
-  auto update = [&](int stage, const int4& ent, const Geo<MODE>& g) {
+    uint4* tile = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) +
+                                           (size_t)ent.z * (VK_BLOCK_VOXELS * sizeof(vkVoxel)) + (size_t)t * 80);
     uint32_t w[20];
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
-      const uint4 q = s_tile[(stage * 5 + c) * 128 + t];
+      const uint4 q = tile[c];
       w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
     }
     uint32_t dirty = 0;  // bit per word
+
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       float D = __uint_as_float(w[5 * k]);
       int dwt = (int)(int16_t)(w[5 * k + 4] & 0xffff);
       int cwt = (int)(int16_t)(w[5 * k + 4] >> 16);
-      if (g.flags & (1u << k)) {
+      if (dpass[k]) {
         // src/depth_integrator.cu:68-76
-        const float cur = vmin(1.0f, divc(g.dcur[k], p.trunc));
+        const float cur = vmin(1.0f, divc(dcur[k], p.trunc));
         const float wn = (float)(dwt + 1);
         D = fdiv(FP<F>::mad(D, (float)dwt, cur), wn);
         dwt = (int)(short)vmin(p.max_dw, wn);
@@ -164,11 +146,10 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
         dirty |= (1u << (5 * k)) | (1u << (5 * k + 4));
       }
       if (MODE != MODE_DEPTH) {
-        if ((g.flags & (16u << k)) && fabsf(D) < 1.0f) {
-          const int ci = g.cidx[MODE == MODE_DEPTH ? 0 : k];
-          const float cr = __ldg(p.color + 3 * (size_t)ci + 0);
-          const float cg = __ldg(p.color + 3 * (size_t)ci + 1);
-          const float cb = __ldg(p.color + 3 * (size_t)ci + 2);
+        if (cin[k] && fabsf(D) < 1.0f) {
+          const float cr = __ldg(p.color + 3 * (size_t)cidx[k] + 0);
+          const float cg = __ldg(p.color + 3 * (size_t)cidx[k] + 1);
+          const float cb = __ldg(p.color + 3 * (size_t)cidx[k] + 2);
           const float fw = (float)cwt;
           const float wn = (float)(cwt + 1);
           const float r0 = __uint_as_float(w[5 * k + 1]);
@@ -178,21 +159,14 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
           float sr, sg, sb;
           if (MODE == MODE_LIGHT) {
             // src/light_integrator.cu:229-241, include/vulcan/light.h:52-60
-            const int di = g.didx[MODE == MODE_LIGHT ? k : 0];
-            const float nx = __ldg(p.normal + 3 * (size_t)di + 0);
-            const float ny = __ldg(p.normal + 3 * (size_t)di + 1);
-            const float nz = __ldg(p.normal + 3 * (size_t)di + 2);
-            Mat34 Tcd, Tcw;
+            const float nx = __ldg(p.normal + 3 * (size_t)didx[k] + 0);
+            const float ny = __ldg(p.normal + 3 * (size_t)didx[k] + 1);
+            const float nz = __ldg(p.normal + 3 * (size_t)didx[k] + 2);
+            Mat34 Tcd;
             Tcd.load(p.Tcd);
-            Tcw.load(p.Tcw);
-            int iox, ioy, ioz;
-            entry_origin(ent, iox, ioy, ioz);
-            const float Xy = FP<F>::mad(fy, p.voxel_length, mul((float)ioy, p.block_length));
-            const float Xz = FP<F>::mad(fz, p.voxel_length, mul((float)ioz, p.block_length));
-            const Vec3 Xc = xform1<F>(Tcw, voxel_x(iox, k), Xy, Xz);
             const Vec3 Xcn = xform0<F>(Tcd, nx, ny, nz);
-            const Vec3 delta = {sub(p.light.position[0], Xc.x), sub(p.light.position[1], Xc.y),
-                                sub(p.light.position[2], Xc.z)};
+            const Vec3 delta = {sub(p.light.position[0], Xc[k].x), sub(p.light.position[1], Xc[k].y),
+                                sub(p.light.position[2], Xc[k].z)};
             const float dist2 = dot3<F>(delta, delta);
             const float invn = rcp(__fsqrt_rn(dist2));
             const Vec3 dirn = {mul(delta.x, invn), mul(delta.y, invn), mul(delta.z, invn)};
@@ -220,47 +194,13 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
       }
       w[5 * k + 4] = ((uint32_t)(uint16_t)(int16_t)dwt) | ((uint32_t)(uint16_t)(int16_t)cwt << 16);
     }
-    uint4* tile = tile_ptr(ent.z);
+
 #pragma unroll
     for (int c = 0; c < 5; ++c) {
       if ((dirty >> (4 * c)) & 0xfu) tile[c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
     }
     // voxels written = voxels whose weight word is dirty (bit 5k+4)
     n_updated += __popc(dirty & 0x84210u);
-  };
-
-  int bi = blockIdx.x;
-  if (bi < n) {
-    // prologue: block a = b[0] is fetched into stage 0, the entry of b[1] is on its way
-    int4 ent_a = ld_entry(p.entries + __ldg(p.visible + bi));
-    Geo<MODE> geo_a;
-    geometry(ent_a, geo_a);
-    if (geo_a.flags) fetch(0, ent_a.z);
-    cp_async_commit();
-    int4 ent_b = ent_a;
-    if (bi + G < n) ent_b = ld_entry(p.entries + __ldg(p.visible + bi + G));
-    int stage = 0;
-    for (; bi < n; bi += G) {
-      const int bn = bi + G, bnn = bi + 2 * G;
-      int e_c = 0;
-      if (bnn < n) e_c = __ldg(p.visible + bnn);
-      Geo<MODE> geo_b;
-      geo_b.flags = 0;
-      if (bn < n) {
-        geometry(ent_b, geo_b);
-        if (geo_b.flags) fetch(stage ^ 1, ent_b.z);
-      }
-      cp_async_commit();
-      int4 ent_c = ent_b;
-      if (bnn < n) ent_c = ld_entry(p.entries + e_c);
-      cp_async_wait<1>();
-      if (geo_a.flags) update(stage, ent_a, geo_a);
-      geo_a = geo_b;
-      ent_a = ent_b;
-      ent_b = ent_c;
-      stage ^= 1;
-    }
-    cp_async_wait<0>();
   }
   n_updated = __reduce_add_sync(0xffffffffu, n_updated);
   if ((threadIdx.x & 31) == 0 && n_updated) atomicAdd(p.updated, (unsigned long long)n_updated);

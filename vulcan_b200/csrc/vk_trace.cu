@@ -66,6 +66,8 @@ struct BoundsParams {
   Div image_w, image_h;
   int bw, bh;
   float* bounds;
+  const uint32_t* warm;  // optional: table the ray marcher will gather from (vkVolume::space_bits)
+  int warm_lines;        // its size in 128-byte lines
 };
 
 // body of ComputePatchesKernel (src/tracer.cu:13-66) for one block.
@@ -118,6 +120,12 @@ __device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw,
 template <bool F>
 __global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
   extern __shared__ float s_cells[];  // bw*bh*2
+  // The ray marcher that follows walks free space through the occupancy filter with dependent
+  // gathers; its longest rays set the duration of the whole trace.  Pull the filter into L2 now
+  // (this kernel leaves most of the machine idle) so those gathers are L2 hits, not DRAM misses.
+  if (p.warm)
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.warm_lines; i += gridDim.x * blockDim.x)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(p.warm + (size_t)i * 32));
   const int ncell = p.bw * p.bh;
   for (int i = threadIdx.x; i < ncell; i += blockDim.x) {
     s_cells[2 * i] = +FLT_MAX;
@@ -228,6 +236,7 @@ struct TraceParams {
   const uint32_t* bucket_bits;  // optional: bit h set <=> bucket head h allocated (vkVolume::bucket_bits)
   const uint32_t* space_bits;   // optional: free-space filter (vkVolume::space_bits)
   int free_run;                 // max free-space steps per lane per trip (0 = filter off)
+  int coop_lanes, coop_rounds;  // cooperative free-space runs when at most coop_lanes lanes are in free space
   Mod K;
   Div block_length, voxel_length;
   float trunc;
@@ -239,8 +248,9 @@ struct TraceParams {
   int w, h, bw, bh;
   int shard_rank, shard_count, shard_shift;
   int batch_lanes, batch_wait;  // phase-B batching of the ray marcher (see vk_raycast_kernel)
+  int debug_flags;              // diagnostics: 1 = skip the filter load, 2 = skip the block division
+  int debug_only_y;
   int debug_only_x;             // diagnostics: march only the tile column starting at this x
-  int lookahead;                // prefetch distance of the ray marcher in voxel steps (0 = off)
   unsigned long long* timeline; // diagnostics: per-warp (start, end) globaltimer, or NULL
 };
 
@@ -418,31 +428,6 @@ __device__ __forceinline__ bool space_bit(const TraceParams& p, int bx, int by, 
   return (__ldg(p.space_bits + sw) >> sb) & 1u;
 }
 
-// Look-ahead prefetch.  Inside the interpolation band a marching ray advances by exactly one voxel
-// length per trip (step = max(l, trunc * sdf) with sdf <= 0.1), and every trip would otherwise
-// wait for voxels nobody has touched yet: the kernel's duration was the latency chain of the
-// longest grazing ray (120 trips x ~1.1 us).  So each such trip prefetches the distances of the
-// 8 taps around p + k * l * dir into L1.  Addresses come from plain (not bit-exact) arithmetic
-// and from the lane's block cache only; a wrong guess costs a useless prefetch, never a result.
-__device__ __forceinline__ void prefetch_ahead(const TraceParams& p, BlockCache& cache, const Vec3& pt,
-                                               const Vec3& dir, float k) {
-  const float s = k * p.voxel_length.d;
-  const float qx = fmaf(dir.x, s, pt.x), qy = fmaf(dir.y, s, pt.y), qz = fmaf(dir.z, s, pt.z);
-  const int bx = (int)floorf(qx * p.block_length.r);
-  const int by = (int)floorf(qy * p.block_length.r);
-  const int bz = (int)floorf(qz * p.block_length.r);
-  int home;
-  if (!cache.peek(bx, by, bz, home) || home == -1) return;
-  const float wx = (qx - (float)bx * p.block_length.d) * p.voxel_length.r;
-  const float wy = (qy - (float)by * p.block_length.d) * p.voxel_length.r;
-  const float wz = (qz - (float)bz * p.block_length.d) * p.voxel_length.r;
-  Taps t;
-  resolve_taps<true>(p, cache, bx, by, bz, home, wx, wy, wz, t);
-#pragma unroll
-  for (int c = 0; c < 8; ++c)
-    if (t.data[c] != -1) asm volatile("prefetch.global.L1 [%0];" ::"l"(voxel_words(p, t.data[c], t.off[c])));
-}
-
 enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
 
 // ComputePointsKernel (src/tracer.cu:317-451).
@@ -475,6 +460,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   const long long c_start = clock64();
   int dbg_trips = 0;
   long long c_free = 0, c_a = 0, c_b = 0, c_t = 0;
+  int dbg_steps = 0, dbg_rounds = 0;
 
   float lo = 0.f, hi = 0.f;
   if (inside) {
@@ -487,6 +473,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
 
   int state = (inside && lo < hi) ? ST_MARCH : ST_DONE;
   if (p.debug_only_x && (int)(blockIdx.x * 8) != p.debug_only_x) state = ST_DONE;  // diagnostics
+  if (p.debug_only_y && (y & ~3) != p.debug_only_y) state = ST_DONE;
   float final_depth = 0.f;
   bool red = false;         // iteration cap hit: colour (1, 0, 0)
   bool has_interp = false;  // an interpolation happened: colour comes from its taps
@@ -571,44 +558,78 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     int bx = 0, by = 0, bz = 0;
     if (state != ST_DONE && !parked) {
       block_of(pt, bx, by, bz);
-      // Free-space run.  While the filter proves that no block exists under p, the reference's
-      // trip is "block not found": p += L * dir, then the depth / iteration test - so the next
-      // kFreeUnroll positions are known in advance.  They are evaluated together (independent
-      // division / filter-load chains instead of one dependent chain per step: a lone warp issues
-      // ~1 instruction per 10 cycles, and the kernel's duration is its longest ray) and then
-      // committed in order up to the first position that is occupied, out of range or the cap.
-      if (state == ST_MARCH && p.free_run > 0 && !space_bit(p, bx, by, bz)) {
-        for (int n = 0; n < p.free_run && state == ST_MARCH; ++n) {
-          Vec3 q[kFreeUnroll];
-          float qd[kFreeUnroll];
-          int qb[kFreeUnroll][3];
-          bool occ[kFreeUnroll];
-          Vec3 c = pt;
-#pragma unroll
-          for (int k = 0; k < kFreeUnroll; ++k) {
-            c.x = FP<F>::mad(dir.x, p.block_length.d, c.x);
-            c.y = FP<F>::mad(dir.y, p.block_length.d, c.y);
-            c.z = FP<F>::mad(dir.z, p.block_length.d, c.z);
-            q[k] = c;
-          }
-#pragma unroll
-          for (int k = 0; k < kFreeUnroll; ++k) {
-            qd[k] = xform1_z<F>(Tcw, q[k].x, q[k].y, q[k].z);
-            block_of(q[k], qb[k][0], qb[k][1], qb[k][2]);
-            occ[k] = space_bit(p, qb[k][0], qb[k][1], qb[k][2]);
-          }
-          bool stop = false;
-#pragma unroll
-          for (int k = 0; k < kFreeUnroll; ++k) {
-            if (!stop) {
-              pt = q[k];
-              bx = qb[k][0]; by = qb[k][1]; bz = qb[k][2];
-              if (++iters >= 500) { red = true; state = ST_DONE; stop = true; }
-              else if (!(qd[k] < hi)) { state = ST_DONE; stop = true; }
-              else if (occ[k]) stop = true;
+    }
+    // Free-space run.  While the occupancy filter proves that no block exists under p, the
+    // reference's trip is "block not found": p += L * dir, then the depth / iteration test.  All
+    // lanes in free space take those steps TOGETHER in a lean warp-uniform loop (the duration of
+    // the kernel is its longest ray, a lone warp issues one instruction per ~5 cycles, and lanes
+    // that loop on their own would serialise), up to free_run steps per trip so that lanes
+    // waiting in other states are not starved.
+    if (p.free_run > 0) {
+      bool freeing = (state == ST_MARCH && !parked && !space_bit(p, bx, by, bz));
+      unsigned fmask = __ballot_sync(0xffffffffu, freeing);
+      // Few lanes in free space (the tail of the kernel: a handful of rays that graze the
+      // surface and then cross metres of empty space): all 32 lanes evaluate the next 32
+      // positions of ONE such ray at a time - lane j takes the position after j+1 steps, computed
+      // by the same chain of FMAs the ray itself would run - and the ray jumps to the first
+      // position that is occupied, out of range or at the iteration cap.
+      for (int round = 0; round < p.coop_rounds && fmask != 0 && __popc(fmask) <= p.coop_lanes; ++round) {
+        unsigned todo = fmask;
+        while (todo) {
+          const int f = __ffs(todo) - 1;
+          todo &= todo - 1;
+          Vec3 c = {__shfl_sync(0xffffffffu, pt.x, f), __shfl_sync(0xffffffffu, pt.y, f),
+                    __shfl_sync(0xffffffffu, pt.z, f)};
+          const float dx = __shfl_sync(0xffffffffu, dir.x, f), dy = __shfl_sync(0xffffffffu, dir.y, f),
+                      dz = __shfl_sync(0xffffffffu, dir.z, f);
+          const float fhi = __shfl_sync(0xffffffffu, hi, f);
+          const int fit = __shfl_sync(0xffffffffu, iters, f);
+#pragma unroll 4
+          for (int k = 0; k < 32; ++k) {
+            if (k <= lane) {
+              c.x = FP<F>::mad(dx, p.block_length.d, c.x);
+              c.y = FP<F>::mad(dy, p.block_length.d, c.y);
+              c.z = FP<F>::mad(dz, p.block_length.d, c.z);
             }
           }
-          if (stop) break;
+          const float depth = xform1_z<F>(Tcw, c.x, c.y, c.z);
+          int cbx, cby, cbz;
+          block_of(c, cbx, cby, cbz);
+          const bool occ = space_bit(p, cbx, cby, cbz);
+          const bool cap = (fit + lane + 1 >= 500);
+          const bool out = !(depth < fhi);
+          const unsigned sm = __ballot_sync(0xffffffffu, cap || out || occ);
+          const int w = sm ? __ffs(sm) - 1 : 31;  // first position where the run ends, else the last one
+          const float rx = __shfl_sync(0xffffffffu, c.x, w), ry = __shfl_sync(0xffffffffu, c.y, w),
+                      rz = __shfl_sync(0xffffffffu, c.z, w);
+          const int rbx = __shfl_sync(0xffffffffu, cbx, w), rby = __shfl_sync(0xffffffffu, cby, w),
+                    rbz = __shfl_sync(0xffffffffu, cbz, w);
+          const int rflags = __shfl_sync(0xffffffffu, (cap ? 1 : 0) | (out ? 2 : 0) | (occ ? 4 : 0), w);
+          if (lane == f) {
+            dbg_steps += w + 1;
+            pt.x = rx; pt.y = ry; pt.z = rz;
+            bx = rbx; by = rby; bz = rbz;
+            iters = fit + w + 1;
+            if (rflags & 1) { red = true; state = ST_DONE; freeing = false; }
+            else if (rflags & 2) { state = ST_DONE; freeing = false; }
+            else if (rflags & 4) freeing = false;
+          }
+        }
+        fmask = __ballot_sync(0xffffffffu, freeing);
+      }
+      // Many lanes in free space: they take the steps together, one step per loop trip.
+      for (int n = 0; n < p.free_run && __any_sync(0xffffffffu, freeing); ++n) {
+        if (freeing) {
+          ++dbg_steps;
+          pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
+          pt.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
+          pt.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
+          after_step();
+          freeing = false;
+          if (state == ST_MARCH) {
+            block_of(pt, bx, by, bz);
+            freeing = !space_bit(p, bx, by, bz);
+          }
         }
       }
     }
@@ -653,7 +674,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         if (parked) {
           Taps taps;
           resolve_taps<false>(p, cache, kbx, kby, kbz, kdata, kwx, kwy, kwz, taps);
-          if (state == ST_MARCH && p.lookahead > 0) prefetch_ahead(p, cache, pt, dir, (float)p.lookahead);
           const float sdf = interp_distance<F>(p, taps);
           ipt = pt;
           has_interp = true;
@@ -668,6 +688,10 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     if (p.timeline) { const long long c = clock64(); c_b += c - c_t; c_t = c; }
   }
 
+  if (p.timeline) {
+    dbg_steps = __reduce_max_sync(0xffffffffu, dbg_steps);
+    dbg_rounds = __reduce_max_sync(0xffffffffu, dbg_rounds);
+  }
   if (p.timeline && lane == 0) {
     unsigned long long t_end;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
@@ -681,7 +705,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     p.timeline[8 * wid + 4] = (unsigned long long)c_free;
     p.timeline[8 * wid + 5] = (unsigned long long)c_a;
     p.timeline[8 * wid + 6] = (unsigned long long)c_b;
-    p.timeline[8 * wid + 7] = (unsigned long long)(c_t - c_start);
+    p.timeline[8 * wid + 7] = ((unsigned long long)dbg_rounds << 32) | (unsigned)dbg_steps;
   }
   if (!inside) return;
   // colour of the last interpolation (Q13: kept even on a miss), evaluated once per ray
@@ -857,6 +881,7 @@ static void fill_bounds_params(BoundsParams& b, const float* Tcw_colmajor, const
   b.bw = bw; b.bh = bh;
   b.bounds = bounds;
   b.visible = nullptr; b.count = nullptr; b.entries = nullptr;
+  b.warm = nullptr; b.warm_lines = 0;
 }
 
 extern "C" int vk_compute_patches(const int* indices, const vkHashEntry* entries, const vkTransform* Tcw,
@@ -898,6 +923,8 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.bucket_bits = bucket_bits;
   t.space_bits = nullptr;
   t.free_run = 0;
+  t.coop_lanes = g_tune[VK_TUNE_RAY_COOP_LANES].load();
+  t.coop_rounds = 4;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
   t.voxel_length = make_div(voxel_length, s);
@@ -910,8 +937,9 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.shard_rank = 0; t.shard_count = 1; t.shard_shift = 0;
   t.batch_lanes = g_tune[VK_TUNE_RAY_BATCH_LANES].load();
   t.batch_wait = g_tune[VK_TUNE_RAY_BATCH_WAIT].load();
-  t.lookahead = g_tune[VK_TUNE_RAY_LOOKAHEAD].load();
-  t.debug_only_x = g_tune[6].load();
+  t.debug_only_x = g_tune[6].load() & 0x3ff;
+  t.debug_only_y = (g_tune[6].load() >> 10) & 0x3ff;
+  t.debug_flags = g_tune[6].load() >> 20;
   t.timeline = g_trace_timeline.load();
 }
 
@@ -990,6 +1018,8 @@ static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth,
   b.visible = v->visible[v->visible_slot];
   b.count = v->counters + VK_CNT_VISIBLE0 + v->visible_slot;
   b.entries = v->entries;
+  b.warm = v->space_bits;
+  b.warm_lines = VK_SPACE_WORDS / 32;
   const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float);
   if (v->math_mode == VK_MATH_STRICT) vk_bounds_kernel<false><<<kBoundsGrid, 512, smem, s>>>(b);
   else vk_bounds_kernel<true><<<kBoundsGrid, 512, smem, s>>>(b);
