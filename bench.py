@@ -94,25 +94,6 @@ def make_frames(n, start=0):
     return np.array(K, dtype=np.float32), frames
 
 
-def shard_owner_torch(entries, shift, count):
-    """torch restatement of vk::shard_owner for counting owned blocks (outside timed regions)."""
-    import torch
-    e0 = entries[:, 0].long()
-    e1 = entries[:, 1].long()
-    def s16(v):
-        v = v & 0xFFFF
-        return torch.where(v >= 0x8000, v - 0x10000, v)
-    bx, by, bz = s16(e0), s16(e0 >> 16), s16(e1)
-    m = 0xFFFFFFFF
-    h = (((bx >> shift) & m) * 0x9E3779B1 & m) ^ (((by >> shift) & m) * 0x85EBCA77 & m) ^ (((bz >> shift) & m) * 0xC2B2AE3D & m)
-    h ^= h >> 16
-    h = h * 0x7FEB352D & m
-    h ^= h >> 15
-    h = h * 0x846CA68B & m
-    h ^= h >> 16
-    return h % count
-
-
 def algorithmic_bytes_integrate(updated_voxels, visible_blocks):
     """40 B per updated voxel + 20 B per visible block + 4*W*H."""
     return 40.0 * updated_voxels + 20.0 * visible_blocks + 4.0 * W * H
@@ -122,6 +103,7 @@ def run_ours(args, rank, world):
     import torch
     import torch.distributed as dist
     import vulcan_b200 as vb
+    from vulcan_b200 import sharding
 
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
     torch.cuda.set_device(dev)
@@ -170,7 +152,7 @@ def run_ours(args, rank, world):
         if ev: ev[2].record()
         if world > 1:
             vb.api.check(lib.vk_trace_keys(v, C.byref(cout), 0.1, 5.0, bounds.data_ptr(), keys.data_ptr(), s), "vk_trace_keys")
-            dist.all_reduce(keys, op=dist.ReduceOp.MIN)
+            sharding.merge_keys(keys)
             vb.api.check(lib.vk_resolve_keys(keys.data_ptr(), C.byref(cout), outs[0].data_ptr(), outs[1].data_ptr(),
                                              outs[2].data_ptr(), s), "vk_resolve_keys")
         else:
@@ -210,8 +192,8 @@ def run_ours(args, rank, world):
         step(vol, cin[k], cout[k], outs, evs[k])
         if world > 1:
             torch.cuda.current_stream().synchronize()
-            ent = vol.GetHashEntries()[vol.GetVisibleBlocks().long()]
-            count_log[k] = (shard_owner_torch(ent, 3, world) == rank).sum()
+            ent = vol.GetHashEntries()[vol.GetVisibleBlocks().long()].cpu().numpy()
+            count_log[k] = int((sharding.shard_owner(*sharding.entry_coords(ent), 3, world) == rank).sum())
         else:
             count_log[k:k + 1].copy_(counters[vol._v.visible_slot:vol._v.visible_slot + 1])
     barrier()

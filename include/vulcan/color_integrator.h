@@ -1,0 +1,25 @@
+// vulcan/color_integrator.h (reference: include/vulcan/color_integrator.h:8-21, src/color_integrator.cu).
+// Integrate = depth update + colour update of the same voxels in ONE pass over the voxel tiles
+// (the reference streams them twice); the protected IntegrateDepth / IntegrateColor pair of the
+// reference is kept for subclasses: IntegrateDepth does the depth part alone, IntegrateColor the
+// fused pass is not separable, so it throws when called on its own.
+#pragma once
+
+#include <vulcan/integrator.h>
+
+namespace vulcan
+{
+
+class ColorIntegrator : public Integrator
+{
+  public:
+
+    ColorIntegrator(std::shared_ptr<Volume> volume);
+    void Integrate(const Frame& frame) override;
+
+  protected:
+
+    void IntegrateDepth(const Frame& frame);
+};
+
+} // namespace vulcan

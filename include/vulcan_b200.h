@@ -236,6 +236,14 @@ int vk_compute_normals(const float* depths, const vkProjection* proj, float* nor
 /* Frame::FilterDepths / vulcan::FilterDepths (src/frame.cu:124-181,194-203). */
 int vk_filter_depths(int image_w, int image_h, const float* src, float* dst, void* stream);
 
+/* ---- sharding (no reference counterpart) -------------------------------------- */
+
+/* Rank that owns block (bx, by, bz) when a volume is split over `count` ranks: a pure function
+ * of the brick (bx >> shift, by >> shift, bz >> shift).  Host function; the kernels use the
+ * same arithmetic.  A rank also stores the 26 neighbours of every block it owns (halo), so
+ * that interpolation never leaves the shard; only owned hits enter the merge keys. */
+int vk_shard_owner(int bx, int by, int bz, int shift, int count);
+
 /* ---- misc -------------------------------------------------------------------- */
 
 /* Library version and the number of kernels launched by this library since load

@@ -77,6 +77,7 @@ SYMBOLS = {
     "vk_compute_points": [_P, _P, _P, _I, _F, _F, _F, C.POINTER(vkTransform), C.POINTER(vkProjection), _P, _P, _I, _I, _I, _I, _P],
     "vk_compute_normals": [_P, C.POINTER(vkProjection), _P, _I, _I, _P],
     "vk_filter_depths": [_I, _I, _P, _P, _P],
+    "vk_shard_owner": [_I, _I, _I, _I, _I],
     "vk_version": [],
     "vk_set_default_math_mode": [_I],
     "vk_get_default_math_mode": [],

@@ -105,6 +105,10 @@ int sm_count() {
 
 }  // namespace vk
 
+extern "C" int vk_shard_owner(int bx, int by, int bz, int shift, int count) {
+  if (count <= 0 || shift < 0 || shift > 15) return VK_E_INVALID;
+  return vk::shard_owner(bx, by, bz, shift, count);
+}
 extern "C" int vk_version(void) { return 110; }
 extern "C" unsigned long long vk_launch_count(void) { return vk::g_launches.load(); }
 extern "C" int vk_set_default_math_mode(int mode) {
