@@ -42,6 +42,7 @@ extern "C" {
 #define VK_BOUNDS_W      80     /* hard coded in src/tracer.cpp:56                 */
 #define VK_BOUNDS_H      60     /* hard coded in src/tracer.cpp:57                 */
 #define VK_SPACE_WORDS   65536  /* 128^3 bits, see vkVolume::space_bits            */
+#define VK_MAX_SHARDS    8      /* ranks of one sharded volume (one NVSwitch box)  */
 
 /* byte image of vulcan::Voxel (include/vulcan/voxel.h:41-49), 20 bytes */
 typedef struct vkVoxel {
@@ -237,6 +238,40 @@ int vk_compute_normals(const float* depths, const vkProjection* proj, float* nor
 int vk_filter_depths(int image_w, int image_h, const float* src, float* dst, void* stream);
 
 /* ---- sharding (no reference counterpart) -------------------------------------- */
+
+/* Tables of all ranks of a sharded volume as seen from one rank: its own pointers in slot
+ * `rank`, the others mapped from their processes (vk_ipc_open) over NVLink / NVSwitch. */
+typedef struct vkPeerTable {
+  int32_t            count, rank;
+  const vkHashEntry* entries[VK_MAX_SHARDS];
+  const vkVoxel*     voxels[VK_MAX_SHARDS];
+} vkPeerTable;
+
+/* CUDA IPC handles of a volume's hash entries and voxel pool (2 x cudaIpcMemHandle_t). */
+typedef struct vkIpcHandles {
+  unsigned char entries[64];
+  unsigned char voxels[64];
+} vkIpcHandles;
+
+/* Exact ray casting of a block-sharded volume.  Every rank holds the blocks it owns (plus a
+ * one-block halo) and renders a band of image rows; a block that is not in the local shard is
+ * read from its owner's tables through peer memory, so each ray takes exactly the steps it
+ * takes in an unsharded volume.  Per traced view and rank:
+ *   vk_trace_bounds   ray bounds of the LOCAL visible blocks into `bounds` (80 x 60 x 2 floats);
+ *                     the caller combines the ranks' grids (min of [0], max of [1]; one small
+ *                     all-reduce, which is also the barrier that orders every rank's integration
+ *                     before any rank's peer reads);
+ *   vk_trace_rows     marches rows [row_begin - 2, row_end + 2) of the view into the full-size
+ *                     images and computes the normals of rows [row_begin, row_end); the caller
+ *                     all-gathers the bands.  peers == NULL or count 1: plain unsharded trace. */
+int vk_trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth,
+                    float* bounds, void* stream);
+int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const vkFrame* view, const float* bounds,
+                  int row_begin, int row_end, float* out_depth, float* out_color, float* out_normal,
+                  void* stream);
+int vk_ipc_export(const vkVolume* v, vkIpcHandles* out);
+int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels);
+int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels);
 
 /* Rank that owns block (bx, by, bz) when a volume is split over `count` ranks: a pure function
  * of the brick (bx >> shift, by >> shift, bz >> shift).  Host function; the kernels use the

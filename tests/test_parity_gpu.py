@@ -138,27 +138,18 @@ def test_fast_division_is_proven_exact():
         assert vb.lib.vk_div_prepare(np.float32(d), s) == 1, d
 
 
-@pytest.mark.parametrize("count", [2, 4])
-def test_sharded_volume_matches_single_gpu(count):
-    """Block-sharded mode, emulated on one GPU (the ranks run one after the other, the MIN all-reduce
-    is an element-wise minimum): union of owned blocks == unsharded block set, owned voxels bit-identical,
-    merged ray cast within 0.5 mm / 0.1 % of the unsharded one (colour is RGB8 in the keys)."""
+def _build_shards(scn, count, shift):
+    """`count` block-sharded volumes of one scenario in this process (ranks emulated one after the other)."""
     import torch
     import vulcan_b200 as vb
-    from vulcan_b200 import sharding as S
-    scn = H.make_scenario("small", (0, 10, 20), "depth")
-    single = H.run_ours(scn)
     K = scn["K"]
-    shift = 2
-    keys_all, owned_keys, owned_vox = None, [], []
+    vols, frame = [], None
     for rank in range(count):
         vol = vb.Volume(scn["M"], scn["E"])
         vol.SetVoxelLength(scn["voxel"])
         vol.SetTruncationLength(scn["trunc"])
         vol.SetSharding(rank, count, shift)
         integ = vb.DepthIntegrator(vol)
-        tracer = vb.Tracer(vol)
-        frame = None
         for fr in scn["frames"]:
             frame = vb.Frame()
             frame.depth_projection = vb.Projection(*K)
@@ -167,36 +158,90 @@ def test_sharded_volume_matches_single_gpu(count):
             frame.depth_image = torch.from_numpy(fr["depth"]).cuda()
             vol.SetView(frame)
             integ.Integrate(frame)
-        keys = torch.empty((scn["h"], scn["w"]), dtype=torch.int64, device="cuda")
-        tracer.TraceKeys(frame, keys)
-        keys_all = keys if keys_all is None else torch.minimum(keys_all, keys)
         assert vol.SyncCounters()[1][4] == 0
+        vols.append(vol)
+    return vols, frame
+
+
+@pytest.mark.parametrize("count", [2, 4, 8])
+def test_sharded_volume_is_exact(count):
+    """Block-sharded mode, emulated on one GPU (ranks run one after the other; their tables are plain
+    pointers of this process instead of IPC mappings; the bounds all-reduce is an element-wise min/max):
+    union of owned blocks == unsharded block set, owned voxels bit-identical, and the ray cast over
+    peer tables is BIT-IDENTICAL to the unsharded one (depth, colour, normals)."""
+    import torch
+    import vulcan_b200 as vb
+    from vulcan_b200 import sharding as S
+    scn = H.make_scenario("small", (0, 10, 20), "depth")
+    single = H.run_ours(scn)
+    shift = 2
+    vols, frame = _build_shards(scn, count, shift)
+    owned_keys, owned_vox = [], []
+    for rank, vol in enumerate(vols):
         entries = vol.GetHashEntries().cpu().numpy()
         tkeys, data, idx = H.allocated_table(entries, scn["M"])
         bx, by, bz = S.entry_coords(entries[idx])
         mine = S.shard_owner(bx, by, bz, shift, count) == rank
         owned_keys.append(tkeys[mine])
-        vox = vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data[mine], device="cuda").long()].cpu().numpy()
-        owned_vox.append(vox)
+        owned_vox.append(vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data[mine], device="cuda").long()].cpu().numpy())
         assert len(tkeys) < len(single["keys"]), "a shard stores only its bricks plus the halo"
-        del vol
     allk = np.concatenate(owned_keys)
     order = np.argsort(allk, kind="stable")
     assert np.array_equal(allk[order], single["keys"]), "union of owned blocks != unsharded block set"
     assert np.array_equal(np.concatenate(owned_vox)[order], single["voxels"]), "owned voxels differ from unsharded"
+
+    tracers = [vb.Tracer(v) for v in vols]
+    for t in tracers:
+        t.TraceBounds(frame)
+    lo = torch.stack([t.bounds_[..., 0] for t in tracers]).min(0).values
+    hi = torch.stack([t.bounds_[..., 1] for t in tracers]).max(0).values
     out = vb.Frame()
     out.depth_projection = frame.depth_projection
     out.depth_to_world_transform = frame.depth_to_world_transform
     out.depth_image = torch.zeros((scn["h"], scn["w"]), dtype=torch.float32, device="cuda")
-    tracer2 = vb.Tracer(vb.Volume(64, 16))
-    tracer2.ResolveKeys(out, keys_all)
+    for rank, t in enumerate(tracers):
+        t.bounds_[..., 0] = lo
+        t.bounds_[..., 1] = hi
+        peers = S.peer_table(rank, [v._v.entries for v in vols], [v._v.voxels for v in vols])
+        band = vb.Frame()
+        band.depth_projection, band.depth_to_world_transform = out.depth_projection, out.depth_to_world_transform
+        band.depth_image = torch.zeros_like(out.depth_image)
+        y0, y1 = S.row_band(scn["h"], rank, count)
+        t.TraceRows(band, peers, y0, y1)
+        if out.color_image is None:
+            out.color_image, out.normal_image = torch.zeros_like(band.color_image), torch.zeros_like(band.normal_image)
+        for dst, src in ((out.depth_image, band.depth_image), (out.color_image, band.color_image),
+                         (out.normal_image, band.normal_image)):
+            dst[y0:y1] = src[y0:y1]
+    for name, img in (("depth", out.depth_image), ("color", out.color_image), ("normal", out.normal_image)):
+        got = img.cpu().numpy()
+        assert np.array_equal(got.view(np.int32), single[name].view(np.int32)), "sharded %s image differs" % name
+
+
+def test_key_merge_is_only_approximate():
+    """The nearest-hit key merge (every rank marches its own shard, MIN all-reduce of 64-bit keys) needs
+    no peer mappings but is not exact: rays step differently where their blocks live on another rank.
+    Pinned here so that the numbers in DESIGN.md stay honest."""
+    import torch
+    import vulcan_b200 as vb
+    scn = H.make_scenario("small", (0, 10, 20), "depth")
+    single = H.run_ours(scn)
+    count = 2
+    vols, frame = _build_shards(scn, count, 2)
+    keys_all = None
+    for vol in vols:
+        keys = torch.empty((scn["h"], scn["w"]), dtype=torch.int64, device="cuda")
+        vb.Tracer(vol).TraceKeys(frame, keys)
+        keys_all = keys if keys_all is None else torch.minimum(keys_all, keys)
+    out = vb.Frame()
+    out.depth_projection = frame.depth_projection
+    out.depth_to_world_transform = frame.depth_to_world_transform
+    out.depth_image = torch.zeros((scn["h"], scn["w"]), dtype=torch.float32, device="cuda")
+    vb.Tracer(vols[0]).ResolveKeys(out, keys_all)
     d = out.depth_image.cpu().numpy()
     ha, hb = d > 0, single["depth"] > 0
     both = ha & hb
     rep = dict(hit_mismatch=float((ha != hb).mean()),
-               depth_gt_half_mm=float((np.abs(d - single["depth"])[both] > 0.0005).mean()),
-               depth_max_mm=float(np.abs(d - single["depth"])[both].max() * 1000),
-               color_max=float(np.abs(out.color_image.cpu().numpy() - single["color"])[both].max()))
-    _dump("sharded_%d" % count, rep)
-    assert rep["hit_mismatch"] <= 1e-3 and rep["depth_gt_half_mm"] <= 1e-3, rep
-    assert rep["color_max"] <= 1.0 / 255 + 1e-6, rep
+               depth_gt_half_mm=float((np.abs(d - single["depth"])[both] > 0.0005).mean()))
+    _dump("key_merge_2", rep)
+    assert rep["hit_mismatch"] <= 0.02 and rep["depth_gt_half_mm"] <= 0.15, rep

@@ -45,6 +45,18 @@ class vkVolume(C.Structure):
     ]
 
 
+MAX_SHARDS = 8
+
+
+class vkPeerTable(C.Structure):
+    _fields_ = [("count", C.c_int32), ("rank", C.c_int32), ("entries", C.c_void_p * MAX_SHARDS),
+                ("voxels", C.c_void_p * MAX_SHARDS)]
+
+
+class vkIpcHandles(C.Structure):
+    _fields_ = [("entries", C.c_ubyte * 64), ("voxels", C.c_ubyte * 64)]
+
+
 class vkFrame(C.Structure):
     _fields_ = [
         ("depth", C.c_void_p), ("color", C.c_void_p), ("normal", C.c_void_p),
@@ -78,6 +90,11 @@ SYMBOLS = {
     "vk_compute_normals": [_P, C.POINTER(vkProjection), _P, _I, _I, _P],
     "vk_filter_depths": [_I, _I, _P, _P, _P],
     "vk_shard_owner": [_I, _I, _I, _I, _I],
+    "vk_trace_bounds": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _P, _P],
+    "vk_trace_rows": [C.POINTER(vkVolume), C.POINTER(vkPeerTable), C.POINTER(vkFrame), _P, _I, _I, _P, _P, _P, _P],
+    "vk_ipc_export": [C.POINTER(vkVolume), C.POINTER(vkIpcHandles)],
+    "vk_ipc_open": [C.POINTER(vkIpcHandles), C.POINTER(_P), C.POINTER(_P)],
+    "vk_ipc_close": [_P, _P],
     "vk_version": [],
     "vk_set_default_math_mode": [_I],
     "vk_get_default_math_mode": [],

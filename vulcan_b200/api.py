@@ -386,6 +386,31 @@ class Tracer:
                            self.bounds_.data_ptr(), frame.depth_image.data_ptr(), frame.color_image.data_ptr(),
                            frame.normal_image.data_ptr(), _stream()), "Trace")
 
+    def _ensure_outputs(self, frame):
+        if frame.depth_image is None:
+            raise VulcanError("missing depth image")
+        h, w = frame.depth_image.shape
+        if frame.color_image is None or tuple(frame.color_image.shape) != (h, w, 3):
+            frame.color_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+        if frame.normal_image is None or tuple(frame.normal_image.shape) != (h, w, 3):
+            frame.normal_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+
+    def TraceBounds(self, frame):
+        """Ray bounds of the local visible blocks into self.bounds_ (sharded mode: combine them
+        over the ranks before TraceRows, see vulcan_b200.sharding.ShardedTracer)."""
+        f = frame.to_c()
+        check(lib.vk_trace_bounds(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0], self.depth_range_[1],
+                                  self.bounds_.data_ptr(), _stream()), "TraceBounds")
+
+    def TraceRows(self, frame, peers, row_begin, row_end):
+        """Marches rows [row_begin - 2, row_end + 2) with the given bounds and peer tables (or None)
+        and computes the normals of rows [row_begin, row_end)."""
+        self._ensure_outputs(frame)
+        f = frame.to_c()
+        check(lib.vk_trace_rows(C.byref(self.volume_._v), C.byref(peers) if peers is not None else None, C.byref(f),
+                                self.bounds_.data_ptr(), int(row_begin), int(row_end), frame.depth_image.data_ptr(),
+                                frame.color_image.data_ptr(), frame.normal_image.data_ptr(), _stream()), "TraceRows")
+
     def TraceKeys(self, frame, keys):
         f = frame.to_c()
         check(lib.vk_trace_keys(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0], self.depth_range_[1],

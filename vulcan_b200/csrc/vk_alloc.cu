@@ -73,6 +73,15 @@ __device__ __forceinline__ void touch_entry(const AllocParams& p, int idx) {
   }
 }
 
+// Sharded volumes: every rank walks every ray, so every rank sees every block of the scene; blocks
+// it does not store still go into its occupancy filter, which therefore equals the filter of the
+// unsharded volume on all ranks (the ray marcher relies on "bit clear => no such block anywhere").
+__device__ __forceinline__ void mark_space(const AllocParams& p, int bx, int by, int bz) {
+  uint32_t sw, sb;
+  space_bit_index(bx, by, bz, sw, sb);
+  if (!((__ldcg(p.space_bits + sw) >> sb) & 1u)) atomicOr(p.space_bits + sw, 1u << sb);
+}
+
 __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int bx, int by, int bz,
                                          unsigned long long key) {
   int result = -1;
@@ -209,8 +218,10 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
       int tail;
       bool head_empty;
       int idx = find_block(p.entries, h, key, tail, head_empty);
-      if (idx < 0 && shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank))
-        idx = insert_block(p, h, bx, by, bz, key);
+      if (idx < 0) {
+        if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank)) idx = insert_block(p, h, bx, by, bz, key);
+        else mark_space(p, bx, by, bz);  // exists on another rank: the filter is global
+      }
       if (idx >= 0) touch_entry(p, idx);
     }
     if (active) {
@@ -254,8 +265,10 @@ __device__ __forceinline__ int resolve_block(const AllocParams& p, unsigned long
   int tail;
   bool head_empty;
   int idx = find_block(p.entries, h, key, tail, head_empty);
-  if (idx < 0 && shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank))
-    idx = insert_block(p, h, bx, by, bz, key);
+  if (idx < 0) {
+    if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank)) idx = insert_block(p, h, bx, by, bz, key);
+    else mark_space(p, bx, by, bz);
+  }
   return idx;
 }
 

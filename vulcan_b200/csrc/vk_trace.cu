@@ -248,6 +248,12 @@ struct TraceParams {
   int w, h, bw, bh;
   int shard_rank, shard_count, shard_shift;
   int batch_lanes, batch_wait;  // phase-B batching of the ray marcher (see vk_raycast_kernel)
+  // Sharded volumes: the tables of every rank (own pointers in slot peer_rank, the others mapped
+  // over NVLink).  A block id in the marcher is (rank << kPeerShift) | voxel-block id.
+  const vkHashEntry* peer_entries[VK_MAX_SHARDS];
+  const vkVoxel* peer_voxels[VK_MAX_SHARDS];
+  int peer_count, peer_rank;
+  int y_begin, y_end;           // image rows marched by this launch
   int debug_flags;              // diagnostics: 1 = skip the filter load, 2 = skip the block division
   int debug_only_y;
   int debug_only_x;             // diagnostics: march only the tile column starting at this x
@@ -282,9 +288,26 @@ struct BlockCache {
 
 // `while (entry.block != b && entry.HasNext()) entry = entries[entry.next];`
 // `entry.block == b && entry.IsAllocated()`  (src/tracer.cu:363-371, :151-175)
+constexpr int kPeerShift = 26;
+
+__device__ __forceinline__ int walk_chain(const vkHashEntry* entries, uint32_t h, unsigned long long key) {
+  int4 e = ld_entry(entries + h);
+  while (entry_block(e) != key && e.w != -1) e = ld_entry(entries + e.w);
+  return (entry_block(e) == key) ? e.z : -1;
+}
+
 __device__ __forceinline__ int lookup_block(const TraceParams& p, int bx, int by, int bz) {
   const unsigned long long key = pack_block(bx, by, bz);
   const uint32_t h = block_hash(bx, by, bz, p.K);
+  if (p.peer_count > 1) {
+    // own shard first (owned blocks and the halo are local), then the owner's table over NVLink
+    int data = walk_chain(p.entries, h, key);
+    if (data != -1) return (p.peer_rank << kPeerShift) | data;
+    const int owner = shard_owner(bx, by, bz, p.shard_shift, p.peer_count);
+    if (owner == p.peer_rank) return -1;
+    data = walk_chain(p.peer_entries[owner], h, key);
+    return (data != -1) ? ((owner << kPeerShift) | data) : -1;
+  }
   // an unallocated bucket head has no chain: most steps through free space end here, on a
   // 32 KB bitmap that stays in L1, instead of on a 16-byte entry fetched from L2
   if (p.bucket_bits && !p.space_bits && !((__ldg(p.bucket_bits + (h >> 5)) >> (h & 31)) & 1u)) return -1;
@@ -302,7 +325,9 @@ __device__ __forceinline__ int find_data(const TraceParams& p, BlockCache& cache
 
 __device__ __forceinline__ const uint32_t* voxel_words(const TraceParams& p, int data, int voxel_offset) {
   // Voxel is 20 bytes, 4-byte aligned: distance, rgb, (dw | cw << 16)
-  return reinterpret_cast<const uint32_t*>(p.voxels) + (size_t)data * (VK_BLOCK_VOXELS * 5) + voxel_offset * 5;
+  const vkVoxel* pool = (p.peer_count > 1) ? p.peer_voxels[data >> kPeerShift] : p.voxels;
+  return reinterpret_cast<const uint32_t*>(pool) + (size_t)(data & ((1 << kPeerShift) - 1)) * (VK_BLOCK_VOXELS * 5) +
+         voxel_offset * 5;
 }
 
 // The 8 taps of GetInterpolatedDistance (src/tracer.cu:190-256): per axis the tap pair
@@ -453,8 +478,8 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   const int wpc = blockDim.x >> 5;
   // warp tile 8x4 pixels, CTA = wpc tiles stacked in y
   const int x = blockIdx.x * 8 + (lane & 7);
-  const int y = (blockIdx.y * wpc + warp) * 4 + (lane >> 3);
-  const bool inside = (x < p.w && y < p.h);
+  const int y = p.y_begin + (blockIdx.y * wpc + warp) * 4 + (lane >> 3);
+  const bool inside = (x < p.w && y < p.y_end);
   unsigned long long t_start = 0;
   if (p.timeline) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
   const long long c_start = clock64();
@@ -769,10 +794,10 @@ namespace vk {
 // FMUL a.z*b.y ; FFMA a.y*b.z - .   (include/vulcan/matrix.h:174-183)
 template <bool F>
 __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, const vkProjection proj,
-                                                         float* normals, int w, int h) {
+                                                         float* normals, int w, int h, int y_begin, int y_end) {
   constexpr int TW = 32, TH = 8, PAD = 2, SW = TW + 2 * PAD, SH = TH + 2 * PAD;
   __shared__ float tile[SH * SW];
-  const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+  const int x0 = blockIdx.x * TW, y0 = y_begin + blockIdx.y * TH;
   for (int s = threadIdx.x; s < SH * SW; s += TW * TH) {
     const int gx = x0 - PAD + (s % SW), gy = y0 - PAD + (s / SW);
     float d = 0;
@@ -782,7 +807,7 @@ __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, co
   __syncthreads();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int x = x0 + tx, y = y0 + ty;
-  if (x >= w || y >= h) return;
+  if (x >= w || y >= y_end) return;
   const float depth = tile[(ty + PAD) * SW + tx + PAD];
   float nx = 0, ny = 0, nz = 0;
   if (depth > 0) {
@@ -935,6 +960,9 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.depths = nullptr; t.colors = nullptr; t.keys = nullptr;
   t.w = w; t.h = h; t.bw = bw; t.bh = bh;
   t.shard_rank = 0; t.shard_count = 1; t.shard_shift = 0;
+  t.peer_count = 1; t.peer_rank = 0;
+  for (int i = 0; i < VK_MAX_SHARDS; ++i) { t.peer_entries[i] = entries; t.peer_voxels[i] = voxels; }
+  t.y_begin = 0; t.y_end = h;
   t.batch_lanes = g_tune[VK_TUNE_RAY_BATCH_LANES].load();
   t.batch_wait = g_tune[VK_TUNE_RAY_BATCH_WAIT].load();
   t.debug_only_x = g_tune[6].load() & 0x3ff;
@@ -947,7 +975,8 @@ template <bool KEYS>
 static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
   const int threads = (g_tune[VK_TUNE_RAY_CTA_THREADS].load() == 64) ? 64 : 32;
   const int rows = 4 * (threads / 32);
-  dim3 grid((t.w + 7) / 8, (t.h + rows - 1) / rows);
+  if (t.y_end <= t.y_begin) return 0;
+  dim3 grid((t.w + 7) / 8, (t.y_end - t.y_begin + rows - 1) / rows);
   if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, KEYS><<<grid, threads, 0, s>>>(t);
   else vk_raycast_kernel<true, KEYS><<<grid, threads, 0, s>>>(t);
   VK_COUNT_LAUNCH();
@@ -983,11 +1012,15 @@ extern "C" int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxe
 }
 
 static int normals_mode(const float* depths, const vkProjection* proj, float* normals, int image_w, int image_h,
-                        int math_mode, cudaStream_t s) {
+                        int math_mode, cudaStream_t s, int y_begin = 0, int y_end = -1) {
   if (!depths || !proj || !normals || image_w <= 0 || image_h <= 0) return VK_E_INVALID;
-  dim3 grid((image_w + 31) / 32, (image_h + 7) / 8);
-  if (math_mode == VK_MATH_STRICT) vk_normals_kernel<false><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h);
-  else vk_normals_kernel<true><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h);
+  if (y_end < 0) y_end = image_h;
+  if (y_end <= y_begin) return 0;
+  dim3 grid((image_w + 31) / 32, (y_end - y_begin + 7) / 8);
+  if (math_mode == VK_MATH_STRICT)
+    vk_normals_kernel<false><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h, y_begin, y_end);
+  else
+    vk_normals_kernel<true><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h, y_begin, y_end);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
@@ -1071,4 +1104,80 @@ extern "C" int vk_resolve_keys(const unsigned long long* keys, const vkFrame* vi
   if (rc) return rc;
   if (out_normal) rc = vk_compute_normals(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, stream);
   return rc;
+}
+
+// ---- sharded volumes: exact ray casting over peer memory ---------------------------------------
+
+extern "C" int vk_trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth,
+                               float* bounds, void* stream) {
+  if (!v || !view || !v->voxels || !bounds) return VK_E_INVALID;
+  return trace_bounds(v, view, min_depth, max_depth, bounds, (cudaStream_t)stream);
+}
+
+extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const vkFrame* view, const float* bounds,
+                             int row_begin, int row_end, float* out_depth, float* out_color, float* out_normal,
+                             void* stream) {
+  if (!v || !view || !v->voxels || !bounds || !out_depth || !out_color) return VK_E_INVALID;
+  if (row_begin < 0 || row_end > view->depth_h || row_begin > row_end) return VK_E_INVALID;
+  if (peers && (peers->count < 1 || peers->count > VK_MAX_SHARDS || peers->rank < 0 || peers->rank >= peers->count))
+    return VK_E_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  TraceParams t;
+  fill_trace_params(t, v->entries, v->voxels, bounds, v->bucket_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
+                    v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, view->depth_w,
+                    view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
+  t.depths = out_depth;
+  t.colors = out_color;
+  t.space_bits = v->space_bits;
+  t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
+  t.shard_shift = v->shard_shift;
+  if (peers && peers->count > 1) {
+    t.peer_count = peers->count;
+    t.peer_rank = peers->rank;
+    for (int i = 0; i < peers->count; ++i) {
+      if (!peers->entries[i] || !peers->voxels[i]) return VK_E_INVALID;
+      t.peer_entries[i] = peers->entries[i];
+      t.peer_voxels[i] = peers->voxels[i];
+    }
+  }
+  // the normals of the band need the depth of two more rows on each side (src/frame.cu:23-32)
+  t.y_begin = (row_begin - 2 > 0) ? row_begin - 2 : 0;
+  t.y_end = (row_end + 2 < view->depth_h) ? row_end + 2 : view->depth_h;
+  if (row_end == row_begin) return 0;
+  int rc = launch_raycast<false>(t, v->math_mode, s);
+  if (rc) return rc;
+  if (out_normal)
+    rc = normals_mode(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, v->math_mode, s,
+                      row_begin, row_end);
+  return rc;
+}
+
+extern "C" int vk_ipc_export(const vkVolume* v, vkIpcHandles* out) {
+  if (!v || !v->entries || !v->voxels || !out) return VK_E_INVALID;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "vkIpcHandles holds two CUDA IPC handles");
+  cudaError_t err = cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->entries), v->entries);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->voxels), v->voxels);
+  return (int)err;
+}
+
+extern "C" int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels) {
+  if (!handles || !entries || !voxels) return VK_E_INVALID;
+  cudaIpcMemHandle_t h;
+  void* ptr = nullptr;
+  memcpy(&h, handles->entries, sizeof(h));
+  cudaError_t err = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+  if (err != cudaSuccess) return (int)err;
+  *entries = static_cast<const vkHashEntry*>(ptr);
+  memcpy(&h, handles->voxels, sizeof(h));
+  err = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+  if (err != cudaSuccess) { cudaIpcCloseMemHandle(const_cast<vkHashEntry*>(*entries)); *entries = nullptr; return (int)err; }
+  *voxels = static_cast<const vkVoxel*>(ptr);
+  return 0;
+}
+
+extern "C" int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels) {
+  cudaError_t e1 = entries ? cudaIpcCloseMemHandle(const_cast<vkHashEntry*>(entries)) : cudaSuccess;
+  cudaError_t e2 = voxels ? cudaIpcCloseMemHandle(const_cast<vkVoxel*>(voxels)) : cudaSuccess;
+  return (int)(e1 != cudaSuccess ? e1 : e2);
 }
