@@ -1,8 +1,7 @@
 // vulcan/color_integrator.h (reference: include/vulcan/color_integrator.h:8-21, src/color_integrator.cu).
 // Integrate = depth update + colour update of the same voxels in ONE pass over the voxel tiles
-// (the reference streams them twice); the protected IntegrateDepth / IntegrateColor pair of the
-// reference is kept for subclasses: IntegrateDepth does the depth part alone, IntegrateColor the
-// fused pass is not separable, so it throws when called on its own.
+// (the reference streams them twice through its protected IntegrateDepth / IntegrateColor pair).
+// IntegrateDepth is kept for subclasses; the colour half is not separable from the fused pass.
 #pragma once
 
 #include <vulcan/integrator.h>

@@ -1,0 +1,23 @@
+#!/bin/bash
+# One GPU call that produces the round's evidence under gpurun_out/: GPU test log, both bench arms,
+# ncu launch list and one full capture of the hot kernels.  Usage: gpurun -- 'bash tools/round_evidence.sh'
+mkdir -p gpurun_out
+(timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -6) > gpurun_out/pytest_gpu.log; cat gpurun_out/pytest_gpu.log
+timeout 300 python bench.py --steps 40 --warmup 5 > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err
+timeout 300 python bench.py --impl reference --steps 40 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
+python - <<'PY'
+import json
+for n in ("ours", "ref"):
+    try:
+        d = json.load(open("gpurun_out/bench_%s.json" % n))
+        print(n, "ms/step %.4f" % d["ms_per_step"], {k: round(v, 4) for k, v in d["phases"].items() if k.endswith("_ms")},
+              "e2e ms %.4f" % d["e2e"]["ms_per_step"], "roofline", d.get("roofline", {}).get("frac"))
+    except Exception as e:
+        print(n, "failed", e)
+PY
+python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
+    python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"vk_(raycast|integrate|alloc|bounds|carry|normals)_kernel" \
+    -s 18 -c 6 -o gpurun_out/prof_full python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
+tail -2 gpurun_out/ncu_full.log

@@ -296,10 +296,11 @@ __device__ __forceinline__ int walk_chain(const vkHashEntry* entries, uint32_t h
   return (entry_block(e) == key) ? e.z : -1;
 }
 
+template <bool PEERS>
 __device__ __forceinline__ int lookup_block(const TraceParams& p, int bx, int by, int bz) {
   const unsigned long long key = pack_block(bx, by, bz);
   const uint32_t h = block_hash(bx, by, bz, p.K);
-  if (p.peer_count > 1) {
+  if (PEERS) {
     // own shard first (owned blocks and the halo are local), then the owner's table over NVLink
     int data = walk_chain(p.entries, h, key);
     if (data != -1) return (p.peer_rank << kPeerShift) | data;
@@ -315,17 +316,20 @@ __device__ __forceinline__ int lookup_block(const TraceParams& p, int bx, int by
   while (entry_block(e) != key && e.w != -1) e = ld_entry(p.entries + e.w);
   return (entry_block(e) == key) ? e.z : -1;
 }
+template <bool PEERS>
 __device__ __forceinline__ int find_data(const TraceParams& p, BlockCache& cache, int bx, int by, int bz) {
   int data;
   if (cache.peek(bx, by, bz, data)) return data;
-  data = lookup_block(p, bx, by, bz);
+  data = lookup_block<PEERS>(p, bx, by, bz);
   cache.put(bx, by, bz, data);
   return data;
 }
 
+template <bool PEERS>
 __device__ __forceinline__ const uint32_t* voxel_words(const TraceParams& p, int data, int voxel_offset) {
   // Voxel is 20 bytes, 4-byte aligned: distance, rgb, (dw | cw << 16)
-  const vkVoxel* pool = (p.peer_count > 1) ? p.peer_voxels[data >> kPeerShift] : p.voxels;
+  if (!PEERS) return reinterpret_cast<const uint32_t*>(p.voxels) + (size_t)data * (VK_BLOCK_VOXELS * 5) + voxel_offset * 5;
+  const vkVoxel* pool = p.peer_voxels[data >> kPeerShift];
   return reinterpret_cast<const uint32_t*>(pool) + (size_t)(data & ((1 << kPeerShift) - 1)) * (VK_BLOCK_VOXELS * 5) +
          voxel_offset * 5;
 }
@@ -340,9 +344,7 @@ struct Taps {
   float w1x, w1y, w1z;
 };
 
-// PEEK: resolve neighbour blocks from the cache only (a miss reads as "no block"); used by the
-// look-ahead prefetch, which must never wait on the hash table.
-template <bool PEEK>
+template <bool PEERS>
 __device__ __forceinline__ void resolve_taps(const TraceParams& p, BlockCache& cache, int bx, int by, int bz,
                                              int home, float wx, float wy, float wz, Taps& t) {
   const int i0x = (int)floorf(add(wx, -0.5f));
@@ -372,8 +374,7 @@ __device__ __forceinline__ void resolve_taps(const TraceParams& p, BlockCache& c
     if (r == c) {
       const int dx = ox[tx], dy = oy[ty], dz = oz[tz];
       if ((dx | dy | dz) == 0) d = home;
-      else if (PEEK) { if (!cache.peek(bx + dx, by + dy, bz + dz, d)) d = -1; }
-      else d = find_data(p, cache, bx + dx, by + dy, bz + dz);
+      else d = find_data<PEERS>(p, cache, bx + dx, by + dy, bz + dz);
     } else {
       d = t.data[0];
 #pragma unroll
@@ -386,13 +387,13 @@ __device__ __forceinline__ void resolve_taps(const TraceParams& p, BlockCache& c
 
 // trilinear SDF (src/tracer.cu:265-280,312).
 // FMA map: n00 = v000*w0x + v001*w1x -> FMUL v001*w1x ; FFMA v000*w0x + .   (same for y and z)
-template <bool F>
+template <bool F, bool PEERS>
 __device__ __forceinline__ float interp_distance(const TraceParams& p, const Taps& t) {
   float n[8];
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     n[c] = 1.0f;  // Voxel::Empty()
-    if (t.data[c] != -1) n[c] = __uint_as_float(__ldg(voxel_words(p, t.data[c], t.off[c])));
+    if (t.data[c] != -1) n[c] = __uint_as_float(__ldg(voxel_words<PEERS>(p, t.data[c], t.off[c])));
   }
   const float w0x = sub(1.0f, t.w1x), w0y = sub(1.0f, t.w1y), w0z = sub(1.0f, t.w1z);
   const float n00 = FP<F>::mad(n[0], w0x, mul(n[1], t.w1x));
@@ -407,7 +408,7 @@ __device__ __forceinline__ float interp_distance(const TraceParams& p, const Tap
 // colour blend of the same 8 taps (src/tracer.cu:282-310), Q15: each weight is 1 if the trilinear
 // weight is non-zero and the voxel has colour, else 0.
 // FMA map: color += w * c -> FFMA chain from 0; color /= total -> reciprocal, FMUL.
-template <bool F>
+template <bool F, bool PEERS>
 __device__ __forceinline__ Vec3 interp_color(const TraceParams& p, const Taps& t) {
   const float w0x = sub(1.0f, t.w1x), w0y = sub(1.0f, t.w1y), w0z = sub(1.0f, t.w1z);
   float total = 0.0f;
@@ -417,7 +418,7 @@ __device__ __forceinline__ Vec3 interp_color(const TraceParams& p, const Taps& t
     float r = 0.f, g = 0.f, b = 0.f;
     int cw = 0;
     if (t.data[c] != -1) {
-      const uint32_t* w = voxel_words(p, t.data[c], t.off[c]);
+      const uint32_t* w = voxel_words<PEERS>(p, t.data[c], t.off[c]);
       r = __uint_as_float(__ldg(w + 1));
       g = __uint_as_float(__ldg(w + 2));
       b = __uint_as_float(__ldg(w + 3));
@@ -472,7 +473,7 @@ enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
 // `batch_lanes` are parked, when nobody else can advance, or after `batch_wait` trips - so the
 // expensive instructions run with most lanes active instead of 7-9 of 32.  The order of
 // operations of each ray is unchanged, so the result is bit-identical to the per-ray loop.
-template <bool F, bool KEYS>
+template <bool F, bool KEYS, bool PEERS>
 __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const TraceParams p) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int wpc = blockDim.x >> 5;
@@ -660,7 +661,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     }
     if (p.timeline) { const long long c = clock64(); c_free += c - c_t; c_t = c; }
     if (state != ST_DONE && !parked) {
-      const int data = find_data(p, cache, bx, by, bz);
+      const int data = find_data<PEERS>(p, cache, bx, by, bz);
       if (data != -1) {
         float wx, wy, wz;
         divc3(FP<F>::nmad((float)bx, p.block_length.d, pt.x), FP<F>::nmad((float)by, p.block_length.d, pt.y),
@@ -669,7 +670,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         float sdf = 0.f;
         if (state == ST_MARCH) {
           const int vx = (int)wx, vy = (int)wy, vz = (int)wz;  // Q22: may be 8 on a face
-          sdf = __uint_as_float(__ldg(voxel_words(p, data, vz * 64 + vy * 8 + vx)));
+          sdf = __uint_as_float(__ldg(voxel_words<PEERS>(p, data, vz * 64 + vy * 8 + vx)));
           want = (sdf <= 0.1f && sdf >= -0.5f);
         }
         if (want) {
@@ -698,8 +699,8 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       if (fm == 0 || __popc(pm) >= p.batch_lanes || waited >= p.batch_wait) {
         if (parked) {
           Taps taps;
-          resolve_taps<false>(p, cache, kbx, kby, kbz, kdata, kwx, kwy, kwz, taps);
-          const float sdf = interp_distance<F>(p, taps);
+          resolve_taps<PEERS>(p, cache, kbx, kby, kbz, kdata, kwx, kwy, kwz, taps);
+          const float sdf = interp_distance<F, PEERS>(p, taps);
           ipt = pt;
           has_interp = true;
           parked = false;
@@ -741,13 +742,13 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     const int bx = (int)floorf(divc(ipt.x, p.block_length));
     const int by = (int)floorf(divc(ipt.y, p.block_length));
     const int bz = (int)floorf(divc(ipt.z, p.block_length));
-    const int data = find_data(p, cache, bx, by, bz);
+    const int data = find_data<PEERS>(p, cache, bx, by, bz);
     const float wx = divc(FP<F>::nmad((float)bx, p.block_length.d, ipt.x), p.voxel_length);
     const float wy = divc(FP<F>::nmad((float)by, p.block_length.d, ipt.y), p.voxel_length);
     const float wz = divc(FP<F>::nmad((float)bz, p.block_length.d, ipt.z), p.voxel_length);
     Taps taps;
-    resolve_taps<false>(p, cache, bx, by, bz, data, wx, wy, wz, taps);
-    color = interp_color<F>(p, taps);
+    resolve_taps<PEERS>(p, cache, bx, by, bz, data, wx, wy, wz, taps);
+    color = interp_color<F, PEERS>(p, taps);
   }
 
   const int pixel = y * p.w + x;
@@ -977,8 +978,13 @@ static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
   const int rows = 4 * (threads / 32);
   if (t.y_end <= t.y_begin) return 0;
   dim3 grid((t.w + 7) / 8, (t.y_end - t.y_begin + rows - 1) / rows);
-  if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, KEYS><<<grid, threads, 0, s>>>(t);
-  else vk_raycast_kernel<true, KEYS><<<grid, threads, 0, s>>>(t);
+  if (!KEYS && t.peer_count > 1) {  // sharded volume: lookups may go to the owner's tables
+    if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, false, true><<<grid, threads, 0, s>>>(t);
+    else vk_raycast_kernel<true, false, true><<<grid, threads, 0, s>>>(t);
+  } else {
+    if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, KEYS, false><<<grid, threads, 0, s>>>(t);
+    else vk_raycast_kernel<true, KEYS, false><<<grid, threads, 0, s>>>(t);
+  }
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
