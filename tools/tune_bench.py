@@ -126,7 +126,7 @@ def main():
                                     same=(d == ref)))
                 print(json.dumps(results[-1]), flush=True)
     if "int" in what:
-        for ctas in (0, 6, 8, 9, 10, 11):
+        for ctas in (0, 4, 5, 6, 7, 8, 9):
             lib.vk_tune(KNOB["int_ctas"], ctas)
             med, mn = timed(lambda: integ.Integrate(frame))
             results.append(dict(phase="integrate", ctas_per_sm=ctas, med_us=med, min_us=mn))

@@ -95,12 +95,7 @@ class Transform:
         return np.concatenate([self.matrix.T.reshape(-1), self.inv_matrix.T.reshape(-1)]).astype(np.float32)
 
     def to_c(self):
-        t = _lib.vkTransform()
-        raw = self.raw32()
-        for k in range(16):
-            t.m[k] = raw[k]
-            t.inv[k] = raw[16 + k]
-        return t
+        return _lib.vkTransform.from_buffer_copy(self.raw32().tobytes())
 
 
 def _matmul4(a, b):

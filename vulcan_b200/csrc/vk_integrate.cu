@@ -11,9 +11,10 @@
 // and the depth image alone whether any of them can change, and only then moves the
 // 80 bytes with 128-bit loads; depth and colour updates happen on the registers in
 // one pass, and only the 16-byte chunks that changed are written back.
-// (A cp.async double-buffered variant that staged the 80-byte pieces through shared memory one
-// block ahead was measured on B200 and was slower: 68 us against 55 us per frame on the bench
-// workload - the loads of ~36 resident warps per SM already cover the latency.)
+// The loop is software-pipelined: the image tests of the next block run under the tile loads of
+// the current one (see the kernel).  A cp.async double-buffered variant that staged the 80-byte
+// pieces through shared memory one block ahead was measured on B200 and was slower (68 us against
+// 55 us per frame on the bench workload).
 #include "vk_math.cuh"
 #include "vk_launch.h"
 #include <cfloat>
@@ -46,8 +47,98 @@ struct IntegrateParams {
 //   D'      = (w*D + cur) / (w+1)      FFMA D*w + cur ; IEEE div         depth_integrator.cu:68-76
 //   C'      = (cw*C + c) * (1/(cw+1))  FFMA C*cw + c ; FMUL              color_integrator.cu:121-126
 //   C'light = (cw*C + c*(1/s)) * ...   FMUL C*cw ; FFMA c*(1/s) + . ; FMUL  light_integrator.cu:238-241
+// Outcome of the geometric tests of a thread's 4 voxels against the images: everything that can be
+// decided without touching the voxel tile.
+template <int MODE>
+struct VoxelTests {
+  uint32_t dmask;  // bit k: depth update applies to voxel k
+  uint32_t cmask;  // bit k: colour-side geometric test passes
+  float dcur[4];   // depth - Xd.z
+  int cidx[MODE == MODE_DEPTH ? 1 : 4];   // colour pixel
+  int didx[MODE == MODE_LIGHT ? 4 : 1];   // depth pixel (light mode)
+  Vec3 Xc[MODE == MODE_LIGHT ? 4 : 1];    // voxel centre in the colour camera (light mode)
+};
+
 template <int MODE, bool F>
-__global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams p) {
+__device__ __forceinline__ void test_voxels(const IntegrateParams& p, const Mat34& Tdw, const Mat34& Tcw,
+                                            const int4 ent, int vx0, float fy, float fz, VoxelTests<MODE>& r) {
+  int iox, ioy, ioz;
+  entry_origin(ent, iox, ioy, ioz);
+  const float Xy = FP<F>::mad(fy, p.voxel_length, mul((float)ioy, p.block_length));
+  const float Xz = FP<F>::mad(fz, p.voxel_length, mul((float)ioz, p.block_length));
+  const float bxl = mul((float)iox, p.block_length);
+  r.dmask = 0;
+  r.cmask = 0;
+  // all four depth gathers are issued before any of them is looked at (pixel 0 stands in for
+  // voxels that project outside the image; its value is not used)
+  float Xx[4], zd[4], d[4];
+  int di[4];
+  uint32_t inside = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    Xx[k] = FP<F>::mad(add((float)(vx0 + k), 0.5f), p.voxel_length, bxl);
+    const Vec3 Xd = xform1<F>(Tdw, Xx[k], Xy, Xz);
+    float u, v;
+    project<F>(p.dproj, Xd, u, v);
+    const bool din = (u >= 0 && u < (float)p.dw && v >= 0 && v < (float)p.dh);
+    zd[k] = Xd.z;
+    di[k] = din ? (int)v * p.dw + (int)u : 0;
+    if (din) inside |= 1u << k;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) d[k] = __ldg(p.depth + di[k]);
+  float m[4];
+  if (MODE == MODE_LIGHT) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) m[k] = __ldg(p.mask + di[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const bool din = (inside >> k) & 1u;
+    const float s = sub(d[k], zd[k]);
+    const bool pass = din && !(d[k] < p.min_depth || d[k] > p.max_depth) && s > -p.trunc.d;
+    r.dcur[k] = pass ? s : 0.f;
+    if (pass) r.dmask |= 1u << k;
+    if (MODE == MODE_COLOR) {
+      const Vec3 Xc = xform1<F>(Tcw, Xx[k], Xy, Xz);
+      float cu, cv;
+      project<F>(p.cproj, Xc, cu, cv);
+      const bool ok = (cu >= 0 && cu < (float)p.cw && cv >= 0 && cv < (float)p.ch);
+      r.cidx[k] = ok ? (int)cv * p.cw + (int)cu : 0;
+      if (ok) r.cmask |= 1u << k;
+    } else if (MODE == MODE_LIGHT) {
+      // both projections are tested against the depth image size (src/light_integrator.cu:207-215,335-336)
+      const Vec3 Xc = xform1<F>(Tcw, Xx[k], Xy, Xz);
+      r.Xc[k] = Xc;
+      float cu, cv;
+      project<F>(p.cproj, Xc, cu, cv);
+      const bool ok = din && (cu >= 0 && cu < (float)p.dw && cv >= 0 && cv < (float)p.dh) && m[k] > 0.5f;
+      r.didx[k] = di[k];
+      r.cidx[k] = ok ? (int)cv * p.dw + (int)cu : 0;
+      if (ok) r.cmask |= 1u << k;
+    }
+  }
+}
+
+// 128-bit tile accesses as volatile asm so that the loads stay where they are written: ahead of
+// the next block's image tests, whose latency they overlap.
+__device__ __forceinline__ uint4 ld_tile(const uint4* ptr) {
+  uint4 q;
+  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "l"(ptr));
+  return q;
+}
+
+// Software pipeline over the CTA's blocks: the tile loads of block i are issued, then the image
+// tests of block i+1 run (projection + depth gathers, independent of the tile), then block i is
+// updated in registers and its changed chunks are stored.  The entry of block i+2 is in flight
+// meanwhile.  One iteration costs max(tile latency, gather latency) instead of their sum.
+// resident CTAs per SM the register allocation is held to (measured on B200: the depth kernel at
+// 8 CTAs/SM, 60 registers, beats 7 CTAs at 70 registers)
+template <int MODE>
+constexpr int integrate_min_ctas() { return MODE == MODE_DEPTH ? 8 : (MODE == MODE_COLOR ? 6 : 4); }
+
+template <int MODE, bool F>
+__global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_kernel(const IntegrateParams p) {
   const int n = *p.count;
   const int t = threadIdx.x;
   const int vz = t >> 4, vy = (t >> 1) & 7, vx0 = (t & 1) * 4;
@@ -56,151 +147,109 @@ __global__ void __launch_bounds__(128) vk_integrate_kernel(const IntegrateParams
   if (MODE != MODE_DEPTH) Tcw.load(p.Tcw);
   unsigned n_updated = 0;
   const float fy = add((float)vy, 0.5f), fz = add((float)vz, 0.5f);
+  const int G = gridDim.x;
 
   int bi = blockIdx.x;
-  int e_next = (bi < n) ? __ldg(p.visible + bi) : 0;
-  int4 ent_next = ld_entry(p.entries + e_next);
-  for (; bi < n; bi += gridDim.x) {
-    const int4 ent = ent_next;
-    // next block's list slot and entry are fetched while this block is processed
-    const int bn = bi + gridDim.x;
-    if (bn < n) e_next = __ldg(p.visible + bn);
-    int iox, ioy, ioz;
-    entry_origin(ent, iox, ioy, ioz);
-    const float Xy = FP<F>::mad(fy, p.voxel_length, mul((float)ioy, p.block_length));
-    const float Xz = FP<F>::mad(fz, p.voxel_length, mul((float)ioz, p.block_length));
-    const float bxl = mul((float)iox, p.block_length);
+  if (bi >= n) return;
+  int4 ent = ld_entry(p.entries + __ldg(p.visible + bi));
+  int4 ent_n = make_int4(0, 0, 0, 0), ent_nn = make_int4(0, 0, 0, 0);
+  if (bi + G < n) ent_n = ld_entry(p.entries + __ldg(p.visible + bi + G));
+  VoxelTests<MODE> cur, nxt;
+  test_voxels<MODE, F>(p, Tdw, Tcw, ent, vx0, fy, fz, cur);
 
-    bool dpass[4];          // depth update applies
-    float dcur[4];          // depth - Xd.z
-    bool cin[4];            // colour-side geometric test passes
-    int cidx[4];            // colour pixel
-    int didx[4];            // depth pixel (light mode)
-    Vec3 Xc[4];
-    bool need = false;
-
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float Xx = FP<F>::mad(add((float)(vx0 + k), 0.5f), p.voxel_length, bxl);
-      const Vec3 Xd = xform1<F>(Tdw, Xx, Xy, Xz);
-      float u, v;
-      project<F>(p.dproj, Xd, u, v);
-      const bool din = (u >= 0 && u < (float)p.dw && v >= 0 && v < (float)p.dh);
-      dpass[k] = false;
-      dcur[k] = 0.f;
-      int di = 0;
-      if (din) {
-        di = (int)v * p.dw + (int)u;
-        const float d = __ldg(p.depth + di);
-        if (!(d < p.min_depth || d > p.max_depth)) {
-          const float s = sub(d, Xd.z);
-          if (s > -p.trunc.d) { dpass[k] = true; dcur[k] = s; }
-        }
-      }
-      need |= dpass[k];
-      if (MODE == MODE_COLOR) {
-        Xc[k] = xform1<F>(Tcw, Xx, Xy, Xz);
-        float cu, cv;
-        project<F>(p.cproj, Xc[k], cu, cv);
-        cin[k] = (cu >= 0 && cu < (float)p.cw && cv >= 0 && cv < (float)p.ch);
-        cidx[k] = cin[k] ? (int)cv * p.cw + (int)cu : 0;
-        need |= cin[k];
-      } else if (MODE == MODE_LIGHT) {
-        // both projections are tested against the depth image size (src/light_integrator.cu:207-215,335-336)
-        Xc[k] = xform1<F>(Tcw, Xx, Xy, Xz);
-        float cu, cv;
-        project<F>(p.cproj, Xc[k], cu, cv);
-        bool ok = din && (cu >= 0 && cu < (float)p.dw && cv >= 0 && cv < (float)p.dh);
-        didx[k] = di;
-        cidx[k] = ok ? (int)cv * p.dw + (int)cu : 0;
-        if (ok) ok = __ldg(p.mask + di) > 0.5f;
-        cin[k] = ok;
-        need |= ok;
-      }
-    }
-    if (bn < n) ent_next = ld_entry(p.entries + e_next);
-    if (!need) continue;
-
+  for (; bi < n; bi += G) {
+    const bool need = (cur.dmask | cur.cmask) != 0;
     uint4* tile = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) +
                                            (size_t)ent.z * (VK_BLOCK_VOXELS * sizeof(vkVoxel)) + (size_t)t * 80);
     uint32_t w[20];
+    if (need) {
 #pragma unroll
-    for (int c = 0; c < 5; ++c) {
-      const uint4 q = tile[c];
-      w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
-    }
-    uint32_t dirty = 0;  // bit per word
-
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      float D = __uint_as_float(w[5 * k]);
-      int dwt = (int)(int16_t)(w[5 * k + 4] & 0xffff);
-      int cwt = (int)(int16_t)(w[5 * k + 4] >> 16);
-      if (dpass[k]) {
-        // src/depth_integrator.cu:68-76
-        const float cur = vmin(1.0f, divc(dcur[k], p.trunc));
-        const float wn = (float)(dwt + 1);
-        D = fdiv(FP<F>::mad(D, (float)dwt, cur), wn);
-        dwt = (int)(short)vmin(p.max_dw, wn);
-        w[5 * k] = __float_as_uint(D);
-        dirty |= (1u << (5 * k)) | (1u << (5 * k + 4));
+      for (int c = 0; c < 5; ++c) {
+        const uint4 q = ld_tile(tile + c);
+        w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
       }
-      if (MODE != MODE_DEPTH) {
-        if (cin[k] && fabsf(D) < 1.0f) {
-          const float cr = __ldg(p.color + 3 * (size_t)cidx[k] + 0);
-          const float cg = __ldg(p.color + 3 * (size_t)cidx[k] + 1);
-          const float cb = __ldg(p.color + 3 * (size_t)cidx[k] + 2);
-          const float fw = (float)cwt;
-          const float wn = (float)(cwt + 1);
-          const float r0 = __uint_as_float(w[5 * k + 1]);
-          const float g0 = __uint_as_float(w[5 * k + 2]);
-          const float b0 = __uint_as_float(w[5 * k + 3]);
-          bool ok = true;
-          float sr, sg, sb;
-          if (MODE == MODE_LIGHT) {
-            // src/light_integrator.cu:229-241, include/vulcan/light.h:52-60
-            const float nx = __ldg(p.normal + 3 * (size_t)didx[k] + 0);
-            const float ny = __ldg(p.normal + 3 * (size_t)didx[k] + 1);
-            const float nz = __ldg(p.normal + 3 * (size_t)didx[k] + 2);
-            Mat34 Tcd;
-            Tcd.load(p.Tcd);
-            const Vec3 Xcn = xform0<F>(Tcd, nx, ny, nz);
-            const Vec3 delta = {sub(p.light.position[0], Xc[k].x), sub(p.light.position[1], Xc[k].y),
-                                sub(p.light.position[2], Xc[k].z)};
-            const float dist2 = dot3<F>(delta, delta);
-            const float invn = rcp(__fsqrt_rn(dist2));
-            const Vec3 dirn = {mul(delta.x, invn), mul(delta.y, invn), mul(delta.z, invn)};
-            const float cos_theta = dot3<F>(Xcn, dirn);
-            const float shading = fdiv(mul(p.light.intensity, cos_theta), dist2);
-            ok = shading > 0.05f;
-            const float inv_s = rcp(shading);
-            sr = FP<F>::mad(cr, inv_s, mul(r0, fw));
-            sg = FP<F>::mad(cg, inv_s, mul(g0, fw));
-            sb = FP<F>::mad(cb, inv_s, mul(b0, fw));
-          } else {
-            sr = FP<F>::mad(r0, fw, cr);
-            sg = FP<F>::mad(g0, fw, cg);
-            sb = FP<F>::mad(b0, fw, cb);
-          }
-          if (ok) {
-            const float inv = rcp(wn);
-            w[5 * k + 1] = __float_as_uint(mul(sr, inv));
-            w[5 * k + 2] = __float_as_uint(mul(sg, inv));
-            w[5 * k + 3] = __float_as_uint(mul(sb, inv));
-            cwt = (int)(short)vmin(p.max_cw, wn);
-            dirty |= (0xeu << (5 * k)) | (1u << (5 * k + 4));
+    }
+    if (bi + 2 * G < n) ent_nn = ld_entry(p.entries + __ldg(p.visible + bi + 2 * G));
+    if (bi + G < n) test_voxels<MODE, F>(p, Tdw, Tcw, ent_n, vx0, fy, fz, nxt);
+
+    if (need) {
+      uint32_t dirty = 0;  // bit per word
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float D = __uint_as_float(w[5 * k]);
+        int dwt = (int)(int16_t)(w[5 * k + 4] & 0xffff);
+        int cwt = (int)(int16_t)(w[5 * k + 4] >> 16);
+        if ((cur.dmask >> k) & 1u) {
+          // src/depth_integrator.cu:68-76
+          const float c = vmin(1.0f, divc(cur.dcur[k], p.trunc));
+          const float wn = (float)(dwt + 1);
+          D = fdiv(FP<F>::mad(D, (float)dwt, c), wn);
+          dwt = (int)(short)vmin(p.max_dw, wn);
+          w[5 * k] = __float_as_uint(D);
+          dirty |= (1u << (5 * k)) | (1u << (5 * k + 4));
+        }
+        if (MODE != MODE_DEPTH) {
+          if (((cur.cmask >> k) & 1u) && fabsf(D) < 1.0f) {
+            const size_t ci = 3 * (size_t)cur.cidx[MODE == MODE_DEPTH ? 0 : k];
+            const float cr = __ldg(p.color + ci + 0);
+            const float cg = __ldg(p.color + ci + 1);
+            const float cb = __ldg(p.color + ci + 2);
+            const float fw = (float)cwt;
+            const float wn = (float)(cwt + 1);
+            const float r0 = __uint_as_float(w[5 * k + 1]);
+            const float g0 = __uint_as_float(w[5 * k + 2]);
+            const float b0 = __uint_as_float(w[5 * k + 3]);
+            bool ok = true;
+            float sr, sg, sb;
+            if (MODE == MODE_LIGHT) {
+              // src/light_integrator.cu:229-241, include/vulcan/light.h:52-60
+              const size_t ni = 3 * (size_t)cur.didx[MODE == MODE_LIGHT ? k : 0];
+              const float nx = __ldg(p.normal + ni + 0);
+              const float ny = __ldg(p.normal + ni + 1);
+              const float nz = __ldg(p.normal + ni + 2);
+              Mat34 Tcd;
+              Tcd.load(p.Tcd);
+              const Vec3 Xcn = xform0<F>(Tcd, nx, ny, nz);
+              const Vec3 Xc = cur.Xc[MODE == MODE_LIGHT ? k : 0];
+              const Vec3 delta = {sub(p.light.position[0], Xc.x), sub(p.light.position[1], Xc.y),
+                                  sub(p.light.position[2], Xc.z)};
+              const float dist2 = dot3<F>(delta, delta);
+              const float invn = rcp(__fsqrt_rn(dist2));
+              const Vec3 dirn = {mul(delta.x, invn), mul(delta.y, invn), mul(delta.z, invn)};
+              const float cos_theta = dot3<F>(Xcn, dirn);
+              const float shading = fdiv(mul(p.light.intensity, cos_theta), dist2);
+              ok = shading > 0.05f;
+              const float inv_s = rcp(shading);
+              sr = FP<F>::mad(cr, inv_s, mul(r0, fw));
+              sg = FP<F>::mad(cg, inv_s, mul(g0, fw));
+              sb = FP<F>::mad(cb, inv_s, mul(b0, fw));
+            } else {
+              sr = FP<F>::mad(r0, fw, cr);
+              sg = FP<F>::mad(g0, fw, cg);
+              sb = FP<F>::mad(b0, fw, cb);
+            }
+            if (ok) {
+              const float inv = rcp(wn);
+              w[5 * k + 1] = __float_as_uint(mul(sr, inv));
+              w[5 * k + 2] = __float_as_uint(mul(sg, inv));
+              w[5 * k + 3] = __float_as_uint(mul(sb, inv));
+              cwt = (int)(short)vmin(p.max_cw, wn);
+              dirty |= (0xeu << (5 * k)) | (1u << (5 * k + 4));
+            }
           }
         }
+        w[5 * k + 4] = ((uint32_t)(uint16_t)(int16_t)dwt) | ((uint32_t)(uint16_t)(int16_t)cwt << 16);
       }
-      w[5 * k + 4] = ((uint32_t)(uint16_t)(int16_t)dwt) | ((uint32_t)(uint16_t)(int16_t)cwt << 16);
-    }
-
 #pragma unroll
-    for (int c = 0; c < 5; ++c) {
-      if ((dirty >> (4 * c)) & 0xfu) tile[c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+      for (int c = 0; c < 5; ++c) {
+        if ((dirty >> (4 * c)) & 0xfu) tile[c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+      }
+      // voxels written = voxels whose weight word is dirty (bit 5k+4)
+      n_updated += __popc(dirty & 0x84210u);
     }
-    // voxels written = voxels whose weight word is dirty (bit 5k+4)
-    n_updated += __popc(dirty & 0x84210u);
+    cur = nxt;
+    ent = ent_n;
+    ent_n = ent_nn;
   }
   n_updated = __reduce_add_sync(0xffffffffu, n_updated);
   if ((threadIdx.x & 31) == 0 && n_updated) atomicAdd(p.updated, (unsigned long long)n_updated);
