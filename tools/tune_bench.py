@@ -22,7 +22,7 @@ import harness as H  # noqa: E402
 import vulcan_b200 as vb  # noqa: E402
 
 W, Hh = 640, 480
-KNOB = {"ray_threads": 0, "ray_lanes": 1, "ray_wait": 2, "int_ctas": 3, "alloc_mode": 4, "coop": 5, "free_run": 7}
+KNOB = {"ray_threads": 0, "ray_lanes": 1, "ray_wait": 2, "int_ctas": 3, "alloc_mode": 4, "coop": 5, "free_run": 7, "coop_rounds": 8, "sample_steps": 9}
 
 
 def main():
@@ -30,6 +30,7 @@ def main():
     ap.add_argument("--frames", type=int, default=8)
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--what", default="ray,int,set")
+    ap.add_argument("--ctas", default="0,6,7,8,9,10", help="integrate CTAs/SM values to sweep (0 = occupancy default)")
     args = ap.parse_args()
     lib = vb.lib
     lib.vk_tune.argtypes = [C.c_int, C.c_int]
@@ -109,12 +110,16 @@ def main():
         np.save(os.path.join(ROOT, "gpurun_out", "trace_timeline.npy"), t)
     if "ray" in what:
         ref = None
-        # (threads per CTA, cooperative-run lane threshold, phase-B batch lanes, batch wait, free-run steps per trip)
-        for threads, ahead, lanes, wait, frun in ((32, 0, 1, 0, 8), (32, 2, 1, 0, 8), (32, 4, 1, 0, 8), (32, 8, 1, 0, 8),
-                                                  (32, 16, 1, 0, 8), (32, 4, 1, 0, 2), (32, 4, 1, 0, 16), (32, 4, 12, 3, 8),
-                                                  (64, 4, 1, 0, 8), (64, 8, 1, 0, 8), (64, 4, 12, 3, 8)):
+        # (threads per CTA, cooperative-run lane threshold, phase-B batch lanes, batch wait, free-run steps per trip,
+        #  cooperative rounds per trip)
+        for threads, ahead, lanes, wait, frun, rounds, ssteps in (
+                (64, 4, 12, 3, 8, 4, 1), (64, 4, 12, 3, 8, 4, 2), (64, 4, 12, 3, 8, 4, 3), (64, 4, 12, 3, 8, 4, 4),
+                (64, 4, 12, 3, 8, 4, 8), (64, 4, 12, 3, 4, 4, 2), (64, 4, 12, 3, 4, 4, 4), (64, 4, 12, 3, 16, 4, 4),
+                (64, 4, 6, 2, 8, 4, 4), (64, 4, 1, 0, 8, 4, 4), (32, 4, 12, 3, 8, 4, 4), (64, 8, 12, 3, 8, 8, 4)):
             if True:
                 lib.vk_tune(KNOB["free_run"], frun)
+                lib.vk_tune(KNOB["coop_rounds"], rounds)
+                lib.vk_tune(KNOB["sample_steps"], ssteps)
                 lib.vk_tune(KNOB["coop"], ahead)
                 lib.vk_tune(KNOB["ray_threads"], threads)
                 lib.vk_tune(KNOB["ray_lanes"], lanes)
@@ -122,11 +127,11 @@ def main():
                 med, mn = timed(lambda: tracer.Trace(out))
                 d = digest()
                 ref = ref or d
-                results.append(dict(phase="trace", threads=threads, free_run=frun, coop=ahead, lanes=lanes, wait=wait, med_us=med, min_us=mn,
+                results.append(dict(phase="trace", threads=threads, free_run=frun, coop=ahead, rounds=rounds, sample_steps=ssteps, lanes=lanes, wait=wait, med_us=med, min_us=mn,
                                     same=(d == ref)))
                 print(json.dumps(results[-1]), flush=True)
     if "int" in what:
-        for ctas in (0, 4, 5, 6, 7, 8, 9):
+        for ctas in [int(x) for x in args.ctas.split(',')]:
             lib.vk_tune(KNOB["int_ctas"], ctas)
             med, mn = timed(lambda: integ.Integrate(frame))
             results.append(dict(phase="integrate", ctas_per_sm=ctas, med_us=med, min_us=mn))

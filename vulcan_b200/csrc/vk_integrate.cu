@@ -120,20 +120,29 @@ __device__ __forceinline__ void test_voxels(const IntegrateParams& p, const Mat3
   }
 }
 
-// 128-bit tile accesses as volatile asm so that the loads stay where they are written: ahead of
-// the next block's image tests, whose latency they overlap.
-__device__ __forceinline__ uint4 ld_tile(const uint4* ptr) {
-  uint4 q;
-  asm volatile("ld.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "l"(ptr));
-  return q;
-}
+// Tile movement.  A thread's 4 voxels are 80 contiguous bytes, so direct per-thread 128-bit
+// accesses run at an 80-byte stride: every warp instruction touches 20 cache lines, and a plain
+// read of the same scattered tiles then tops out near 4.3 TB/s on B200 against 8 TB/s for
+// lane-contiguous accesses (tools/microbench/tile_copy.cu).  So a warp moves its 2560 bytes of
+// the tile lane-contiguously (5 x 512 B) through a private shared-memory buffer: cp.async in,
+// per-thread 80-byte rows out of shared memory (an 80-byte stride is conflict-free for 128-bit
+// shared accesses), and the changed 16-byte chunks back the same way.  Only chunks whose owner
+// thread has something to update are fetched, only changed chunks are stored.
+constexpr int kWarpChunks = 160;  // 16-byte chunks of a warp's part of a tile (32 threads x 5)
 
-// Software pipeline over the CTA's blocks: the tile loads of block i are issued, then the image
+__device__ __forceinline__ void cp_async16(uint4* smem_dst, const uint4* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+               "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Software pipeline over the CTA's blocks: the tile fetch of block i is issued, then the image
 // tests of block i+1 run (projection + depth gathers, independent of the tile), then block i is
 // updated in registers and its changed chunks are stored.  The entry of block i+2 is in flight
 // meanwhile.  One iteration costs max(tile latency, gather latency) instead of their sum.
-// resident CTAs per SM the register allocation is held to (measured on B200: the depth kernel at
-// 8 CTAs/SM, 60 registers, beats 7 CTAs at 70 registers)
+// resident CTAs per SM the register allocation is held to (measured on B200: the depth kernel
+// lands at 55 registers = 9 CTAs/SM; forcing 10 CTAs spills and is slower)
 template <int MODE>
 constexpr int integrate_min_ctas() { return MODE == MODE_DEPTH ? 8 : (MODE == MODE_COLOR ? 6 : 4); }
 
@@ -148,32 +157,51 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
   unsigned n_updated = 0;
   const float fy = add((float)vy, 0.5f), fz = add((float)vz, 0.5f);
   const int G = gridDim.x;
+  __shared__ uint4 s_tile[4][kWarpChunks];
+  const int lane = t & 31, warp = t >> 5;
+  uint4* const stage = s_tile[warp];
 
   int bi = blockIdx.x;
   if (bi >= n) return;
+  // list slots are read three blocks ahead and entries two blocks ahead, so that neither load
+  // is waited for where it is issued
   int4 ent = ld_entry(p.entries + __ldg(p.visible + bi));
   int4 ent_n = make_int4(0, 0, 0, 0), ent_nn = make_int4(0, 0, 0, 0);
   if (bi + G < n) ent_n = ld_entry(p.entries + __ldg(p.visible + bi + G));
+  int slot_nn = (bi + 2 * G < n) ? __ldg(p.visible + bi + 2 * G) : 0;
   VoxelTests<MODE> cur, nxt;
   test_voxels<MODE, F>(p, Tdw, Tcw, ent, vx0, fy, fz, cur);
 
   for (; bi < n; bi += G) {
     const bool need = (cur.dmask | cur.cmask) != 0;
-    uint4* tile = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) +
-                                           (size_t)ent.z * (VK_BLOCK_VOXELS * sizeof(vkVoxel)) + (size_t)t * 80);
-    uint32_t w[20];
-    if (need) {
+    const uint32_t need_mask = __ballot_sync(0xffffffffu, need);
+    // the warp's 2560 bytes of the tile
+    uint4* const tile = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) +
+                                                 (size_t)ent.z * (VK_BLOCK_VOXELS * sizeof(vkVoxel)) +
+                                                 (size_t)warp * (kWarpChunks * 16));
+    if (need_mask) {
 #pragma unroll
       for (int c = 0; c < 5; ++c) {
-        const uint4 q = ld_tile(tile + c);
-        w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
+        const int j = c * 32 + lane;         // chunk of the warp's span
+        const int owner = (j * 205) >> 10;   // j / 5: the lane whose voxels live in this chunk
+        if ((need_mask >> owner) & 1u) cp_async16(stage + j, tile + j);
       }
     }
-    if (bi + 2 * G < n) ent_nn = ld_entry(p.entries + __ldg(p.visible + bi + 2 * G));
+    cp_async_commit();
+    if (bi + 2 * G < n) ent_nn = ld_entry(p.entries + slot_nn);
+    if (bi + 3 * G < n) slot_nn = __ldg(p.visible + bi + 3 * G);
     if (bi + G < n) test_voxels<MODE, F>(p, Tdw, Tcw, ent_n, vx0, fy, fz, nxt);
+    cp_async_wait_all();
+    __syncwarp();
 
+    uint32_t dirty = 0;  // bit per word of the thread's 80 bytes
     if (need) {
-      uint32_t dirty = 0;  // bit per word
+      uint32_t w[20];
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const uint4 q = stage[lane * 5 + c];
+        w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
+      }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         float D = __uint_as_float(w[5 * k]);
@@ -242,11 +270,27 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
       }
 #pragma unroll
       for (int c = 0; c < 5; ++c) {
-        if ((dirty >> (4 * c)) & 0xfu) tile[c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+        if ((dirty >> (4 * c)) & 0xfu)
+          stage[lane * 5 + c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
       }
       // voxels written = voxels whose weight word is dirty (bit 5k+4)
       n_updated += __popc(dirty & 0x84210u);
     }
+    // changed chunks go back lane-contiguously
+    uint32_t chunk_dirty = 0;  // bit c: the thread's chunk c changed
+#pragma unroll
+    for (int c = 0; c < 5; ++c) chunk_dirty |= ((dirty >> (4 * c)) & 0xfu) ? (1u << c) : 0u;
+    if (__any_sync(0xffffffffu, chunk_dirty != 0)) {
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const int j = c * 32 + lane;
+        const int owner = (j * 205) >> 10;
+        const uint32_t m = __shfl_sync(0xffffffffu, chunk_dirty, owner);
+        if ((m >> (j - owner * 5)) & 1u) tile[j] = stage[j];
+      }
+    }
+    __syncwarp();  // the buffer is refilled by the next iteration
     cur = nxt;
     ent = ent_n;
     ent_n = ent_nn;

@@ -11,7 +11,7 @@ namespace vk {
 
 std::atomic<unsigned long long> g_launches{0};
 std::atomic<int> g_default_math_mode{VK_MATH_REFERENCE};
-std::atomic<int> g_tune[VK_TUNE_COUNT] = {{64}, {12}, {3}, {0}, {0}, {4}, {0}, {8}};
+std::atomic<int> g_tune[VK_TUNE_COUNT] = {{64}, {12}, {3}, {0}, {0}, {4}, {0}, {8}, {4}, {1}};
 
 // Compares the one-step FMA division against the IEEE division for every dividend bit pattern.
 __global__ void __launch_bounds__(256) vk_divcheck_kernel(float d, float r, unsigned int* mismatches) {
