@@ -402,6 +402,8 @@ def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2, math=0)
         "small": dict(w=160, h=120, voxel=0.008, M=32768, E=8192),
         "c1": dict(w=640, h=480, voxel=0.004, M=262144, E=65536),
         "c3": dict(w=1280, h=720, voxel=0.004, M=262144, E=65536),
+        # BASELINE config 4: 1080p depth, 2 mm voxels, the int-index ceiling of 4 194 303 blocks (42.9 GB pool)
+        "c4": dict(w=1920, h=1080, voxel=0.002, M=3145728, E=1048575),
     }[name]
     w, h = cfg["w"], cfg["h"]
     K = synth.intrinsics(w, h)

@@ -89,6 +89,7 @@ SCENARIOS = [
     ("small", (0, 5), "color", 1.2),
     ("small", (0, 5), "light", 1.2),
     ("small", (0, 1, 2, 3), "depth", 25.0),  # large view changes
+    ("small", tuple(range(8)), "depth", 45.0),  # BASELINE config 5 in small: 8 sensors around one volume
 ]
 MATH = [0, 1]
 
@@ -125,6 +126,23 @@ def test_c1_full_size_vs_reference(math):
     rep = _compare_with_ref(scn, ours)
     _dump("ref_m%d_c1" % math, rep)
     _assert_exact_ref(rep, "c1 ours vs reference")
+
+
+@pytest.mark.parametrize("name,frames,mode", [
+    ("c1", (0, 1, 2, 3), "depth"),   # config 2: the first frames of the 640x480 orbit (carried-over visibility)
+    ("c3", (0, 1), "color"),         # config 3: RGB-D 1280x720, ColorIntegrator
+    ("c4", (0,), "depth"),           # config 4: 1920x1080, 2 mm voxels, 4 194 303-block volume (42.9 GB pool)
+])
+def test_baseline_configs_full_size_vs_reference(name, frames, mode):
+    """The other BASELINE.json configurations at their full image / volume sizes against the
+    reference's own CUDA build (release arithmetic)."""
+    if not H.have_ref(nofmad=False):
+        pytest.fail("oracle/_ref/libvulcan_ref.so missing: run oracle/build_ref.sh")
+    scn = H.make_scenario(name, frames, mode, math=0)
+    ours = H.run_ours(scn)
+    rep = _compare_with_ref(scn, ours, tries=6)
+    _dump("ref_m0_%s_%s_%d_full" % (name, mode, len(frames)), rep)
+    _assert_exact_ref(rep, "%s ours vs reference" % name)
 
 
 def test_fast_division_is_proven_exact():
