@@ -257,13 +257,15 @@ typedef struct vkIpcHandles {
  * one-block halo) and renders a band of image rows; a block that is not in the local shard is
  * read from its owner's tables through peer memory, so each ray takes exactly the steps it
  * takes in an unsharded volume.  Per traced view and rank:
- *   vk_trace_bounds   ray bounds of the LOCAL visible blocks into `bounds` (80 x 60 x 2 floats);
- *                     the caller combines the ranks' grids (min of [0], max of [1]; one small
- *                     all-reduce, which is also the barrier that orders every rank's integration
- *                     before any rank's peer reads);
+ *   vk_trace_bounds   ray bounds of the LOCAL visible blocks into `bounds` (80 x 60 x 2 floats),
+ *                     each cell as (min depth, -max depth), +FLT_MAX where empty: the caller
+ *                     combines the ranks' grids with ONE element-wise MIN all-reduce, which is
+ *                     also the barrier that orders every rank's integration before any rank's
+ *                     peer reads;
  *   vk_trace_rows     marches rows [row_begin - 2, row_end + 2) of the view into the full-size
  *                     images and computes the normals of rows [row_begin, row_end); the caller
- *                     all-gathers the bands.  peers == NULL or count 1: plain unsharded trace. */
+ *                     all-gathers the bands.  `bounds` is in the (min, -max) format of
+ *                     vk_trace_bounds.  peers == NULL or count 1: plain unsharded trace. */
 int vk_trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth,
                     float* bounds, void* stream);
 int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const vkFrame* view, const float* bounds,

@@ -212,7 +212,7 @@ def test_sharded_volume_is_exact(count):
     for t in tracers:
         t.TraceBounds(frame)
     lo = torch.stack([t.bounds_[..., 0] for t in tracers]).min(0).values
-    hi = torch.stack([t.bounds_[..., 1] for t in tracers]).max(0).values
+    hi = torch.stack([t.bounds_[..., 1] for t in tracers]).min(0).values   # cells hold (min, -max)
     out = vb.Frame()
     out.depth_projection = frame.depth_projection
     out.depth_to_world_transform = frame.depth_to_world_transform

@@ -69,6 +69,7 @@ struct BoundsParams {
   float* bounds;
   const uint32_t* warm;  // optional: table the ray marcher will gather from (vkVolume::space_bits)
   int warm_lines;        // its size in 128-byte lines
+  bool negate_hi;        // cells hold (min, -max): an element-wise MIN over ranks combines both
 };
 
 // body of ComputePatchesKernel (src/tracer.cu:13-66) for one block.
@@ -159,13 +160,16 @@ __global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
   for (int i = threadIdx.x; i < ncell; i += blockDim.x) {
     const float lo = s_cells[2 * i], hi = s_cells[2 * i + 1];
     if (lo != +FLT_MAX) atomic_min_float(p.bounds + 2 * i, lo);
-    if (hi != -FLT_MAX) atomic_max_float(p.bounds + 2 * i + 1, hi);
+    if (hi != -FLT_MAX) {
+      if (p.negate_hi) atomic_min_float(p.bounds + 2 * i + 1, -hi);
+      else atomic_max_float(p.bounds + 2 * i + 1, hi);
+    }
   }
 }
 
-__global__ void vk_reset_bounds_kernel(float2* bounds, int count) {
+__global__ void vk_reset_bounds_kernel(float2* bounds, int count, float hi_init) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < count) bounds[i] = make_float2(+FLT_MAX, -FLT_MAX);
+  if (i < count) bounds[i] = make_float2(+FLT_MAX, hi_init);
 }
 
 // ComputePatchesKernel (src/tracer.cu:13-87) with a warp-aggregated append in place of
@@ -238,6 +242,7 @@ struct TraceParams {
   const uint32_t* space_bits;   // optional: free-space filter (vkVolume::space_bits)
   int free_run;                 // max free-space steps per lane per trip (0 = filter off)
   int sample_steps;             // max steps inside allocated space per lane per trip
+  bool negated_hi;              // bounds cells hold (min, -max) (vk_trace_bounds / vk_trace_rows)
   int coop_lanes, coop_rounds;  // cooperative free-space runs when at most coop_lanes lanes are in free space
   Mod K;
   Div block_length, voxel_length;
@@ -496,7 +501,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     const int py = p.bh * y / p.h;
     const float2 bound = __ldg(reinterpret_cast<const float2*>(p.bounds) + py * p.bw + px);
     lo = bound.x;
-    hi = bound.y;
+    hi = p.negated_hi ? -bound.y : bound.y;
   }
 
   int state = (inside && lo < hi) ? ST_MARCH : ST_DONE;
@@ -912,13 +917,16 @@ using namespace vk;
 static std::atomic<unsigned long long*> g_trace_timeline{nullptr};
 extern "C" void vk_debug_trace_timeline(unsigned long long* device_buffer) { g_trace_timeline.store(device_buffer); }
 
-extern "C" int vk_reset_bounds(float* bounds, int count, void* stream) {
+static int reset_bounds(float* bounds, int count, float hi_init, cudaStream_t s) {
   if (!bounds || count < 0) return VK_E_INVALID;
   if (count == 0) return 0;
-  vk_reset_bounds_kernel<<<(count + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
-      reinterpret_cast<float2*>(bounds), count);
+  vk_reset_bounds_kernel<<<(count + 255) / 256, 256, 0, s>>>(reinterpret_cast<float2*>(bounds), count, hi_init);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
+}
+
+extern "C" int vk_reset_bounds(float* bounds, int count, void* stream) {
+  return reset_bounds(bounds, count, -FLT_MAX, (cudaStream_t)stream);
 }
 
 static void fill_bounds_params(BoundsParams& b, const float* Tcw_colmajor, const vkProjection* proj,
@@ -935,6 +943,7 @@ static void fill_bounds_params(BoundsParams& b, const float* Tcw_colmajor, const
   b.bounds = bounds;
   b.visible = nullptr; b.count = nullptr; b.entries = nullptr;
   b.warm = nullptr; b.warm_lines = 0;
+  b.negate_hi = false;
 }
 
 extern "C" int vk_compute_patches(const int* indices, const vkHashEntry* entries, const vkTransform* Tcw,
@@ -979,6 +988,7 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.coop_lanes = std::min(8, g_tune[VK_TUNE_RAY_COOP_LANES].load());  // groups of >= 4 lanes per ray
   t.coop_rounds = g_tune[VK_TUNE_RAY_COOP_ROUNDS].load();
   t.sample_steps = std::max(1, g_tune[VK_TUNE_RAY_SAMPLE_STEPS].load());
+  t.negated_hi = false;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
   t.voxel_length = make_div(voxel_length, s);
@@ -1075,9 +1085,9 @@ extern "C" int vk_filter_depths(int image_w, int image_h, const float* src, floa
 static const int kBoundsGrid = 32;
 
 static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, float* bounds,
-                        cudaStream_t s) {
+                        cudaStream_t s, bool negate_hi = false) {
   // Tracer::ComputePatches + ComputeBounds (src/tracer.cpp:49-76), 80x60 grid hard coded
-  int rc = vk_reset_bounds(bounds, VK_BOUNDS_W * VK_BOUNDS_H, s);
+  int rc = reset_bounds(bounds, VK_BOUNDS_W * VK_BOUNDS_H, negate_hi ? +FLT_MAX : -FLT_MAX, s);
   if (rc) return rc;
   BoundsParams b;
   fill_bounds_params(b, view->depth_to_world.inv, &view->depth_proj, VK_BLOCK_RES * v->voxel_length, min_depth,
@@ -1087,6 +1097,7 @@ static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth,
   b.entries = v->entries;
   b.warm = v->space_bits;
   b.warm_lines = VK_SPACE_WORDS / 32;
+  b.negate_hi = negate_hi;
   const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float);
   if (v->math_mode == VK_MATH_STRICT) vk_bounds_kernel<false><<<kBoundsGrid, 512, smem, s>>>(b);
   else vk_bounds_kernel<true><<<kBoundsGrid, 512, smem, s>>>(b);
@@ -1145,7 +1156,8 @@ extern "C" int vk_resolve_keys(const unsigned long long* keys, const vkFrame* vi
 extern "C" int vk_trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth,
                                float* bounds, void* stream) {
   if (!v || !view || !v->voxels || !bounds) return VK_E_INVALID;
-  return trace_bounds(v, view, min_depth, max_depth, bounds, (cudaStream_t)stream);
+  // cells are (min depth, -max depth): see include/vulcan_b200.h
+  return trace_bounds(v, view, min_depth, max_depth, bounds, (cudaStream_t)stream, true);
 }
 
 extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const vkFrame* view, const float* bounds,
@@ -1162,6 +1174,7 @@ extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const 
                     view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
   t.depths = out_depth;
   t.colors = out_color;
+  t.negated_hi = true;
   t.space_bits = v->space_bits;
   t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
   t.shard_shift = v->shard_shift;

@@ -144,19 +144,25 @@ class ShardedTracer:
         t = self.tracer
         t._ensure_outputs(frame)
         t.TraceBounds(frame)
-        # bounds grid = (min depth, max depth) per cell: negate the maxima so that ONE min
-        # all-reduce combines both
-        t.bounds_[..., 1].neg_()
+        # cells are (min depth, -max depth): ONE min all-reduce combines both
         dist.all_reduce(t.bounds_, op=dist.ReduceOp.MIN, group=self.group)
-        t.bounds_[..., 1].neg_()
         h = frame.depth_image.shape[0]
         y0, y1 = row_band(h, self.rank, self.count)
         t.TraceRows(frame, self.peers, y0, y1)
         rows = (h + self.count - 1) // self.count
-        for img in (frame.depth_image, frame.color_image, frame.normal_image):
-            if rows * self.count == h:
-                dist.all_gather_into_tensor(img, img[y0:y1].clone(), group=self.group)
-            else:
+        images = (frame.depth_image, frame.color_image, frame.normal_image)
+        if rows * self.count == h:
+            # equal bands: the three images go out as one coalesced NCCL all-gather, each rank's
+            # band sent from where it already lies in the full image (in place)
+            try:
+                with dist._coalescing_manager(group=self.group, device=frame.depth_image.device):
+                    for img in images:
+                        dist.all_gather_into_tensor(img, img[y0:y1], group=self.group)
+            except (AttributeError, TypeError, RuntimeError):
+                for img in images:
+                    dist.all_gather_into_tensor(img, img[y0:y1].clone(), group=self.group)
+        else:
+            for img in images:
                 for r in range(self.count):
                     a, b = row_band(h, r, self.count)
                     if b > a:
