@@ -201,12 +201,8 @@ def run_ours(args, rank, world):
             t_wall0 = time.perf_counter()
         flush.zero_()  # L2 flush between steps, outside the per-step events
         step(vol, cin[k], cout[k], outs, evs[k])
-        if world > 1:
-            torch.cuda.current_stream().synchronize()
-            ent = vol.GetHashEntries()[vol.GetVisibleBlocks().long()].cpu().numpy()
-            count_log[k] = int((sharding.shard_owner(*sharding.entry_coords(ent), 3, world) == rank).sum())
-        else:
-            count_log[k:k + 1].copy_(counters[vol._v.visible_slot:vol._v.visible_slot + 1])
+        # visible blocks of THIS rank's shard (a rank lists only the blocks it owns)
+        count_log[k:k + 1].copy_(counters[vol._v.visible_slot:vol._v.visible_slot + 1])
     barrier()
     t_wall = time.perf_counter() - t_wall0
     launches = lib.vk_launch_count() - launches0
@@ -320,7 +316,7 @@ def run_ours(args, rank, world):
         "config": {"workload": "c2_orbit: 640x480 sphere-on-plane depth, 4 mm voxels, Volume(262144,65536), "
                                "1.2 deg/frame orbit, GT poses; step = SetView(fixed point)+DepthIntegrate+Trace",
                    "l2": "256 MiB device memset between steps, outside the per-step CUDA events",
-                   "sharding": "none" if world == 1 else "blocks by brick hash (8^3-block bricks, 1-block halo); each rank "
+                   "sharding": "none" if world == 1 else "blocks by brick hash (8^3-block bricks, a rank stores and integrates only the blocks it owns); each rank "
                                                          "ray-casts a band of rows reading remote blocks through peer memory "
                                                          "(NVLink), NCCL min all-reduce of the ray-bounds grid + all-gather of "
                                                          "the bands"},

@@ -57,7 +57,7 @@ class Volume
     int GetVisibleBlockCount() const;                      // synchronises the stream
     int GetAllocatedBlockCount() const;                    // synchronises the stream
     void Reset();                                          // back to the freshly constructed state
-    void SetSharding(int rank, int count, int brick_shift = 3);  // spatial block sharding (multi-GPU)
+    void SetSharding(int rank, int count, int brick_shift = 3, int halo = 0);  // spatial block sharding (multi-GPU)
     void SetStream(cudaStream_t stream) { stream_ = stream; }
     cudaStream_t GetStream() const { return stream_; }
     vkVolume* GetHandle() { return &volume_; }

@@ -127,6 +127,8 @@ typedef struct vkVolume {
   int32_t      shard_rank;    /* 0 when unsharded                                   */
   int32_t      shard_count;   /* 1 when unsharded                                   */
   int32_t      shard_shift;   /* log2 of the brick edge in blocks                   */
+  int32_t      shard_halo;    /* 0: a rank stores the blocks it owns (exact peer-memory ray cast);  */
+                              /* 1: also their 26 neighbours (for the key-merge ray cast)           */
   int32_t      visible_slot;  /* which of visible[] / VK_CNT_VISIBLE* is current    */
   int32_t      view_id;       /* number of vk_set_view calls so far                 */
   int32_t      math_mode;     /* VK_MATH_REFERENCE (default) or VK_MATH_STRICT       */
@@ -254,7 +256,7 @@ typedef struct vkIpcHandles {
 } vkIpcHandles;
 
 /* Exact ray casting of a block-sharded volume.  Every rank holds the blocks it owns (plus a
- * one-block halo) and renders a band of image rows; a block that is not in the local shard is
+ * one-block halo if shard_halo is set) and renders a band of image rows; a block of another rank is
  * read from its owner's tables through peer memory, so each ray takes exactly the steps it
  * takes in an unsharded volume.  Per traced view and rank:
  *   vk_trace_bounds   ray bounds of the LOCAL visible blocks into `bounds` (80 x 60 x 2 floats),
@@ -277,8 +279,9 @@ int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels);
 
 /* Rank that owns block (bx, by, bz) when a volume is split over `count` ranks: a pure function
  * of the brick (bx >> shift, by >> shift, bz >> shift).  Host function; the kernels use the
- * same arithmetic.  A rank also stores the 26 neighbours of every block it owns (halo), so
- * that interpolation never leaves the shard; only owned hits enter the merge keys. */
+ * same arithmetic.  With vkVolume::shard_halo = 1 a rank also stores the 26 neighbours of every
+ * block it owns, so that the interpolation of the key-merge ray cast (vk_trace_keys) never
+ * leaves the shard; only owned hits enter the merge keys. */
 int vk_shard_owner(int bx, int by, int bz, int shift, int count);
 
 /* ---- misc -------------------------------------------------------------------- */

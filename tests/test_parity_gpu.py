@@ -156,7 +156,7 @@ def test_fast_division_is_proven_exact():
         assert vb.lib.vk_div_prepare(np.float32(d), s) == 1, d
 
 
-def _build_shards(scn, count, shift):
+def _build_shards(scn, count, shift, halo=0):
     """`count` block-sharded volumes of one scenario in this process (ranks emulated one after the other)."""
     import torch
     import vulcan_b200 as vb
@@ -166,7 +166,7 @@ def _build_shards(scn, count, shift):
         vol = vb.Volume(scn["M"], scn["E"])
         vol.SetVoxelLength(scn["voxel"])
         vol.SetTruncationLength(scn["trunc"])
-        vol.SetSharding(rank, count, shift)
+        vol.SetSharding(rank, count, shift, halo)
         integ = vb.DepthIntegrator(vol)
         for fr in scn["frames"]:
             frame = vb.Frame()
@@ -202,7 +202,7 @@ def test_sharded_volume_is_exact(count):
         mine = S.shard_owner(bx, by, bz, shift, count) == rank
         owned_keys.append(tkeys[mine])
         owned_vox.append(vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data[mine], device="cuda").long()].cpu().numpy())
-        assert len(tkeys) < len(single["keys"]), "a shard stores only its bricks plus the halo"
+        assert len(tkeys) < len(single["keys"]), "a shard stores only the blocks it owns"
     allk = np.concatenate(owned_keys)
     order = np.argsort(allk, kind="stable")
     assert np.array_equal(allk[order], single["keys"]), "union of owned blocks != unsharded block set"
@@ -245,7 +245,7 @@ def test_key_merge_is_only_approximate():
     scn = H.make_scenario("small", (0, 10, 20), "depth")
     single = H.run_ours(scn)
     count = 2
-    vols, frame = _build_shards(scn, count, 2)
+    vols, frame = _build_shards(scn, count, 2, halo=1)
     keys_all = None
     for vol in vols:
         keys = torch.empty((scn["h"], scn["w"]), dtype=torch.int64, device="cuda")

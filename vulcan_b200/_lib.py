@@ -40,7 +40,7 @@ class vkVolume(C.Structure):
         ("main_blocks", C.c_int32), ("excess_blocks", C.c_int32),
         ("voxel_length", C.c_float), ("trunc_length", C.c_float),
         ("min_depth", C.c_float), ("max_depth", C.c_float),
-        ("shard_rank", C.c_int32), ("shard_count", C.c_int32), ("shard_shift", C.c_int32),
+        ("shard_rank", C.c_int32), ("shard_count", C.c_int32), ("shard_shift", C.c_int32), ("shard_halo", C.c_int32),
         ("visible_slot", C.c_int32), ("view_id", C.c_int32), ("math_mode", C.c_int32),
     ]
 

@@ -224,8 +224,10 @@ class Volume:
             raise VulcanError("invalid math mode")
         self._v.math_mode = mode
 
-    def SetSharding(self, rank, count, shift=3):
-        self._v.shard_rank, self._v.shard_count, self._v.shard_shift = rank, count, shift
+    def SetSharding(self, rank, count, shift=3, halo=0):
+        """Blocks are owned by brick hash (bricks of 2^shift blocks per edge); halo=1 also stores the
+        26 neighbours of every owned block (needed only by the key-merge ray cast, TraceKeys)."""
+        self._v.shard_rank, self._v.shard_count, self._v.shard_shift, self._v.shard_halo = rank, count, shift, halo
 
     def Reset(self):
         check(lib.vk_volume_reset(C.byref(self._v), _stream()), "Volume.Reset")

@@ -43,7 +43,7 @@ struct AllocParams {
   int B;
   float block_length, inv_block_length, trunc, min_depth, max_depth;
   int view_id;
-  int shard_rank, shard_count, shard_shift;
+  int shard_rank, shard_count, shard_shift, shard_halo;
 };
 
 // chain walk; returns entry index of block `key` or -1.  `tail` receives the last
@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
       bool head_empty;
       int idx = find_block(p.entries, h, key, tail, head_empty);
       if (idx < 0) {
-        if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank)) idx = insert_block(p, h, bx, by, bz, key);
+        if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) idx = insert_block(p, h, bx, by, bz, key);
         else mark_space(p, bx, by, bz);  // exists on another rank: the filter is global
       }
       if (idx >= 0) touch_entry(p, idx);
@@ -266,7 +266,7 @@ __device__ __forceinline__ int resolve_block(const AllocParams& p, unsigned long
   bool head_empty;
   int idx = find_block(p.entries, h, key, tail, head_empty);
   if (idx < 0) {
-    if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank)) idx = insert_block(p, h, bx, by, bz, key);
+    if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) idx = insert_block(p, h, bx, by, bz, key);
     else mark_space(p, bx, by, bz);
   }
   return idx;
@@ -533,6 +533,7 @@ extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks,
   v->shard_rank = 0;
   v->shard_count = 1;
   v->shard_shift = 3;
+  v->shard_halo = 0;
   v->math_mode = g_default_math_mode.load();
   cudaError_t err;
 #define VK_TRY(x) if ((err = (x)) != cudaSuccess) { vk_volume_destroy(v); return (int)err; }
@@ -606,6 +607,7 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.shard_rank = v->shard_rank;
   a.shard_count = v->shard_count;
   a.shard_shift = v->shard_shift;
+  a.shard_halo = v->shard_halo;
   dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
   const bool strict = (v->math_mode == VK_MATH_STRICT);
   if (g_tune[VK_TUNE_ALLOC_MODE].load() == 0) {

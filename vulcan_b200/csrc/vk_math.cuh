@@ -259,9 +259,10 @@ __device__ __host__ __forceinline__ uint32_t shard_mix(int x, int y, int z) {
 __device__ __host__ __forceinline__ int shard_owner(int bx, int by, int bz, int shift, int count) {
   return (int)(shard_mix(bx >> shift, by >> shift, bz >> shift) % (uint32_t)count);
 }
-// A rank stores a block if it owns it or any of its 26 neighbours (1-block halo).
-__device__ __forceinline__ bool shard_stores(int bx, int by, int bz, int shift, int count, int rank) {
+// A rank stores the blocks it owns and, with halo = 1, their 26 neighbours.
+__device__ __forceinline__ bool shard_stores(int bx, int by, int bz, int shift, int count, int rank, int halo) {
   if (count <= 1) return true;
+  if (halo <= 0) return shard_owner(bx, by, bz, shift, count) == rank;
   for (int dz = -1; dz <= 1; ++dz)
     for (int dy = -1; dy <= 1; ++dy)
       for (int dx = -1; dx <= 1; ++dx)

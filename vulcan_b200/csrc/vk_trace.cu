@@ -308,12 +308,9 @@ __device__ __forceinline__ int lookup_block(const TraceParams& p, int bx, int by
   const unsigned long long key = pack_block(bx, by, bz);
   const uint32_t h = block_hash(bx, by, bz, p.K);
   if (PEERS) {
-    // own shard first (owned blocks and the halo are local), then the owner's table over NVLink
-    int data = walk_chain(p.entries, h, key);
-    if (data != -1) return (p.peer_rank << kPeerShift) | data;
+    // the owner's table: the local one, or a peer's over NVLink (peer_entries[rank] is local)
     const int owner = shard_owner(bx, by, bz, p.shard_shift, p.peer_count);
-    if (owner == p.peer_rank) return -1;
-    data = walk_chain(p.peer_entries[owner], h, key);
+    const int data = walk_chain(p.peer_entries[owner], h, key);
     return (data != -1) ? ((owner << kPeerShift) | data) : -1;
   }
   // an unallocated bucket head has no chain: most steps through free space end here, on a

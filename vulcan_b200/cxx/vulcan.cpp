@@ -185,12 +185,14 @@ void Volume::Reset()
   RefreshViews();
 }
 
-void Volume::SetSharding(int rank, int count, int brick_shift)
+void Volume::SetSharding(int rank, int count, int brick_shift, int halo)
 {
   VULCAN_ASSERT(count >= 1 && rank >= 0 && rank < count && brick_shift >= 0 && brick_shift < 15);
+  VULCAN_ASSERT(halo == 0 || halo == 1);
   volume_.shard_rank = rank;
   volume_.shard_count = count;
   volume_.shard_shift = brick_shift;
+  volume_.shard_halo = halo;
 }
 
 // ---- Integrators (src/integrator.cu, depth_/color_/light_integrator.cu) -----------------------------

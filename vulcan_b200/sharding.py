@@ -2,8 +2,8 @@
 SURVEY.md 5.8 / 8e).
 
 Partition: a rank owns the blocks whose brick (block coordinates >> shift) hashes to it
-(vk_shard_owner in include/vulcan_b200.h) and also stores a one-block halo, so allocation and
-integration need no exchange.  Ray casting is where the ranks meet:
+(vk_shard_owner in include/vulcan_b200.h) and stores exactly those, so allocation and integration
+need no exchange and each rank does 1/N of the work.  Ray casting is where the ranks meet:
 
   ShardedTracer (exact)   every rank renders a band of image rows; a block outside the local shard is
       read from its owner's hash table and voxel pool through peer memory (CUDA IPC mappings over
