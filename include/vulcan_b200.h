@@ -277,6 +277,35 @@ int vk_ipc_export(const vkVolume* v, vkIpcHandles* out);
 int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels);
 int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels);
 
+/* Exchange of the rendered bands without a library collective.  Every rank owns one "exchange
+ * buffer" (vk_exchange_alloc: room for the full-size depth + colour + normal images of a view and
+ * VK_MAX_SHARDS arrival flags), maps the buffers of its peers (vk_exchange_export / _open, CUDA
+ * IPC) and renders its band INTO ITS OWN buffer (pass vk_exchange_depth/_color/_normal of it to
+ * vk_trace_rows).  vk_exchange_bands then (1) stores `epoch` into this rank's flag in every
+ * peer's buffer (release, system scope), (2) waits until all peers' flags in the local buffer
+ * have reached `epoch`, (3) copies every peer's band out of that peer's buffer into the caller's
+ * images over NVLink.  `epoch` must grow by one per call on all ranks.  A band may be overwritten
+ * by its owner only after all ranks have passed a later collective (the bounds all-reduce of the
+ * next view does that). */
+typedef struct vkExchange {
+  int32_t count, rank;                 /* ranks, this rank                                  */
+  int32_t width, height;               /* image size the buffers were allocated for         */
+  void*   buffers[VK_MAX_SHARDS];      /* exchange buffer of every rank (own one included)  */
+  int32_t row_begin[VK_MAX_SHARDS];    /* band of rank r: rows [row_begin[r], row_end[r])   */
+  int32_t row_end[VK_MAX_SHARDS];
+} vkExchange;
+
+int vk_exchange_alloc(int width, int height, void** buffer);
+int vk_exchange_free(void* buffer);
+int vk_exchange_export(const void* buffer, unsigned char handle[64]);
+int vk_exchange_open(const unsigned char handle[64], void** buffer);
+int vk_exchange_close(void* buffer);
+float* vk_exchange_depth(void* buffer, int width, int height);
+float* vk_exchange_color(void* buffer, int width, int height);
+float* vk_exchange_normal(void* buffer, int width, int height);
+int vk_exchange_bands(const vkExchange* x, int epoch, float* out_depth, float* out_color, float* out_normal,
+                      void* stream);
+
 /* Rank that owns block (bx, by, bz) when a volume is split over `count` ranks: a pure function
  * of the brick (bx >> shift, by >> shift, bz >> shift).  Host function; the kernels use the
  * same arithmetic.  With vkVolume::shard_halo = 1 a rank also stores the 26 neighbours of every

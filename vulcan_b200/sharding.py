@@ -8,8 +8,9 @@ need no exchange and each rank does 1/N of the work.  Ray casting is where the r
   ShardedTracer (exact)   every rank renders a band of image rows; a block outside the local shard is
       read from its owner's hash table and voxel pool through peer memory (CUDA IPC mappings over
       NVLink / NVSwitch), so each ray takes exactly the steps of the unsharded march.  Collectives per
-      view: one MIN all-reduce of the 80 x 60 ray-bounds grid (38 KB; also the barrier between every
-      rank's integration and any rank's peer reads) and one all-gather of the image bands.
+      view: one NCCL MIN all-reduce of the 80 x 60 ray-bounds grid (38 KB; also the barrier between
+      every rank's integration and any rank's peer reads); the image bands are then swapped by one
+      kernel per rank over peer memory (vk_exchange_bands: flag handshake + NVLink copies).
   key merge (approximate)  every rank ray-casts its own shard into 64-bit keys (depth bits << 32 |
       rgb8 << 8 | rank, +inf for "no owned hit") and a MIN all-reduce leaves the nearest hit per
       pixel.  No peer mappings needed, but rays step differently where their blocks live on another
@@ -137,34 +138,75 @@ class ShardedTracer:
         for e, v in self._opened:
             _lib.lib.vk_ipc_close(e, v)
         self._opened = []
+        self._drop_exchange()
+
+    def _drop_exchange(self):
+        from . import _lib
+        x = getattr(self, "_exchange", None)
+        if x is None:
+            return
+        for r in range(self.count):
+            if r != self.rank and x["buffers"][r]:
+                _lib.lib.vk_exchange_close(x["buffers"][r])
+        _lib.lib.vk_exchange_free(x["buffers"][self.rank])
+        self._exchange = None
+
+    def _ensure_exchange(self, h, w):
+        """Exchange buffers for h x w images (collective: every rank calls it with the same size)."""
+        import ctypes as C
+        import torch.distributed as dist
+        from . import _lib, api
+        x = getattr(self, "_exchange", None)
+        if x is not None and x["size"] == (h, w):
+            return x
+        self._drop_exchange()
+        mine = C.c_void_p()
+        api.check(_lib.lib.vk_exchange_alloc(w, h, C.byref(mine)), "vk_exchange_alloc")
+        handle = C.create_string_buffer(64)
+        api.check(_lib.lib.vk_exchange_export(mine, handle), "vk_exchange_export")
+        blobs = [None] * self.count
+        dist.all_gather_object(blobs, handle.raw, group=self.group)
+        buffers = []
+        for r, blob in enumerate(blobs):
+            if r == self.rank:
+                buffers.append(mine.value)
+                continue
+            p = C.c_void_p()
+            api.check(_lib.lib.vk_exchange_open(C.create_string_buffer(blob, 64), C.byref(p)), "vk_exchange_open")
+            buffers.append(p.value)
+        desc = _lib.vkExchange()
+        desc.count, desc.rank, desc.width, desc.height = self.count, self.rank, w, h
+        for r in range(self.count):
+            desc.buffers[r] = buffers[r]
+            desc.row_begin[r], desc.row_end[r] = row_band(h, r, self.count)
+        lib = _lib.lib
+        x = dict(size=(h, w), buffers=buffers, desc=desc, epoch=0,
+                 depth=lib.vk_exchange_depth(mine, w, h), color=lib.vk_exchange_color(mine, w, h),
+                 normal=lib.vk_exchange_normal(mine, w, h))
+        self._exchange = x
+        return x
 
     def Trace(self, frame):
-        """Fills frame.depth_image / color_image / normal_image on every rank (all bands gathered)."""
+        """Fills frame.depth_image / color_image / normal_image on every rank (all bands gathered).
+        Per view: one NCCL MIN all-reduce of the ray-bounds grid (38 KB; also the barrier between
+        every rank's integration and any rank's peer reads), the band of this rank rendered into
+        its exchange buffer, and one kernel that swaps the bands over peer memory."""
+        import ctypes as C
         import torch.distributed as dist
+        from . import _lib, api
         t = self.tracer
         t._ensure_outputs(frame)
+        h, w = frame.depth_image.shape
+        x = self._ensure_exchange(h, w)
         t.TraceBounds(frame)
         # cells are (min depth, -max depth): ONE min all-reduce combines both
         dist.all_reduce(t.bounds_, op=dist.ReduceOp.MIN, group=self.group)
-        h = frame.depth_image.shape[0]
         y0, y1 = row_band(h, self.rank, self.count)
-        t.TraceRows(frame, self.peers, y0, y1)
-        rows = (h + self.count - 1) // self.count
-        images = (frame.depth_image, frame.color_image, frame.normal_image)
-        if rows * self.count == h:
-            # equal bands: the three images go out as one coalesced NCCL all-gather, each rank's
-            # band sent from where it already lies in the full image (in place)
-            try:
-                with dist._coalescing_manager(group=self.group, device=frame.depth_image.device):
-                    for img in images:
-                        dist.all_gather_into_tensor(img, img[y0:y1], group=self.group)
-            except (AttributeError, TypeError, RuntimeError):
-                for img in images:
-                    dist.all_gather_into_tensor(img, img[y0:y1].clone(), group=self.group)
-        else:
-            for img in images:
-                for r in range(self.count):
-                    a, b = row_band(h, r, self.count)
-                    if b > a:
-                        dist.broadcast(img[a:b], src=dist.get_global_rank(self.group, r) if self.group else r,
-                                       group=self.group)
+        f = frame.to_c()
+        v = self.volume
+        api.check(_lib.lib.vk_trace_rows(C.byref(v._v), C.byref(self.peers), C.byref(f), t.bounds_.data_ptr(), y0, y1,
+                                         x["depth"], x["color"], x["normal"], api._stream()), "TraceRows")
+        x["epoch"] += 1
+        api.check(_lib.lib.vk_exchange_bands(C.byref(x["desc"]), x["epoch"], frame.depth_image.data_ptr(),
+                                             frame.color_image.data_ptr(), frame.normal_image.data_ptr(),
+                                             api._stream()), "vk_exchange_bands")
