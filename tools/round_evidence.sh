@@ -1,6 +1,7 @@
 #!/bin/bash
 # One GPU call that produces the round's evidence under gpurun_out/: GPU test log, both bench arms,
-# ncu launch list and one full capture of the hot kernels.  Usage: gpurun -- 'bash tools/round_evidence.sh'
+# and the ncu launch list.  Usage: gpurun -- 'bash tools/round_evidence.sh'; the full ncu capture of the
+# hot kernels is a second call: gpurun -- 'bash tools/round_ncu_full.sh'
 mkdir -p gpurun_out
 (timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -6) > gpurun_out/pytest_gpu.log; cat gpurun_out/pytest_gpu.log
 timeout 300 python bench.py --steps 40 --warmup 5 > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err
@@ -18,6 +19,3 @@ PY
 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"vk_(raycast|integrate|alloc|bounds|carry|normals)_kernel" \
-    -s 18 -c 6 -o gpurun_out/prof_full python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
-tail -2 gpurun_out/ncu_full.log
