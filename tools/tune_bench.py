@@ -112,14 +112,13 @@ def main():
         ref = None
         # (threads per CTA, cooperative-run lane threshold, phase-B batch lanes, batch wait, free-run steps per trip,
         #  cooperative rounds per trip)
-        for threads, ahead, lanes, wait, frun, rounds, ssteps in (
-                (64, 4, 12, 3, 8, 4, 1), (64, 4, 12, 3, 8, 4, 2), (64, 4, 12, 3, 8, 4, 3), (64, 4, 12, 3, 8, 4, 4),
-                (64, 4, 12, 3, 8, 4, 8), (64, 4, 12, 3, 4, 4, 2), (64, 4, 12, 3, 4, 4, 4), (64, 4, 12, 3, 16, 4, 4),
-                (64, 4, 6, 2, 8, 4, 4), (64, 4, 1, 0, 8, 4, 4), (32, 4, 12, 3, 8, 4, 4), (64, 8, 12, 3, 8, 8, 4)):
+        for threads, ahead, lanes, wait, frun in ((64, 0, 12, 3, 8), (64, 2, 12, 3, 8), (64, 4, 12, 3, 8), (64, 8, 12, 3, 8),
+                                                  (64, 4, 12, 3, 4), (64, 4, 12, 3, 16), (64, 4, 6, 2, 8), (64, 4, 1, 0, 8),
+                                                  (32, 4, 12, 3, 8)):
+            rounds = 4
             if True:
                 lib.vk_tune(KNOB["free_run"], frun)
                 lib.vk_tune(KNOB["coop_rounds"], rounds)
-                lib.vk_tune(KNOB["sample_steps"], ssteps)
                 lib.vk_tune(KNOB["coop"], ahead)
                 lib.vk_tune(KNOB["ray_threads"], threads)
                 lib.vk_tune(KNOB["ray_lanes"], lanes)
@@ -127,7 +126,7 @@ def main():
                 med, mn = timed(lambda: tracer.Trace(out))
                 d = digest()
                 ref = ref or d
-                results.append(dict(phase="trace", threads=threads, free_run=frun, coop=ahead, rounds=rounds, sample_steps=ssteps, lanes=lanes, wait=wait, med_us=med, min_us=mn,
+                results.append(dict(phase="trace", threads=threads, free_run=frun, coop=ahead, rounds=rounds, lanes=lanes, wait=wait, med_us=med, min_us=mn,
                                     same=(d == ref)))
                 print(json.dumps(results[-1]), flush=True)
     if "int" in what:

@@ -241,7 +241,6 @@ struct TraceParams {
   const uint32_t* bucket_bits;  // optional: bit h set <=> bucket head h allocated (vkVolume::bucket_bits)
   const uint32_t* space_bits;   // optional: free-space filter (vkVolume::space_bits)
   int free_run;                 // max free-space steps per lane per trip (0 = filter off)
-  int sample_steps;             // max steps inside allocated space per lane per trip
   bool negated_hi;              // bounds cells hold (min, -max) (vk_trace_bounds / vk_trace_rows)
   int coop_lanes, coop_rounds;  // cooperative free-space runs when at most coop_lanes lanes are in free space
   Mod K;
@@ -599,64 +598,58 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       bool freeing = (state == ST_MARCH && !parked && !space_bit(p, bx, by, bz));
       unsigned fmask = __ballot_sync(0xffffffffu, freeing);
       // Few lanes in free space (the tail of the kernel: a handful of rays that graze the
-      // surface and then cross metres of empty space): the 32 lanes are split into one group per
-      // such ray (32, 16, 8 or 4 lanes) and evaluate the ray's next positions TOGETHER - lane j of
-      // a group takes the position after j+1 steps, computed by the same chain of FMAs the ray
-      // itself would run - and each ray jumps to the first position that is occupied, out of
-      // range or at the iteration cap.
+      // surface and then cross metres of empty space): all 32 lanes evaluate the next 32
+      // positions of ONE such ray at a time - lane j takes the position after j+1 steps, computed
+      // by the same chain of FMAs the ray itself would run - and the ray jumps to the first
+      // position that is occupied, out of range or at the iteration cap.
       for (int round = 0; round < p.coop_rounds && fmask != 0 && __popc(fmask) <= p.coop_lanes; ++round) {
-        const int nf = __popc(fmask);
-        const int gshift = (nf <= 1) ? 5 : (nf <= 2) ? 4 : (nf <= 4) ? 3 : 2;  // log2(lanes per ray)
-        const int gs = 1 << gshift;
-        const int grp = lane >> gshift, j = lane & (gs - 1);
-        const bool valid = grp < nf;
-        const unsigned fsrc = __fns(fmask, 0, (valid ? grp : 0) + 1);  // lane of the group's ray
-        Vec3 c = {__shfl_sync(0xffffffffu, pt.x, fsrc), __shfl_sync(0xffffffffu, pt.y, fsrc),
-                  __shfl_sync(0xffffffffu, pt.z, fsrc)};
-        const float dx = __shfl_sync(0xffffffffu, dir.x, fsrc), dy = __shfl_sync(0xffffffffu, dir.y, fsrc),
-                    dz = __shfl_sync(0xffffffffu, dir.z, fsrc);
-        const float fhi = __shfl_sync(0xffffffffu, hi, fsrc);
-        const int fit = __shfl_sync(0xffffffffu, iters, fsrc);
-        for (int k = 0; k < gs; ++k) {
-          if (k <= j) {
-            c.x = FP<F>::mad(dx, p.block_length.d, c.x);
-            c.y = FP<F>::mad(dy, p.block_length.d, c.y);
-            c.z = FP<F>::mad(dz, p.block_length.d, c.z);
+        unsigned todo = fmask;
+        while (todo) {
+          const int f = __ffs(todo) - 1;
+          todo &= todo - 1;
+          Vec3 c = {__shfl_sync(0xffffffffu, pt.x, f), __shfl_sync(0xffffffffu, pt.y, f),
+                    __shfl_sync(0xffffffffu, pt.z, f)};
+          const float dx = __shfl_sync(0xffffffffu, dir.x, f), dy = __shfl_sync(0xffffffffu, dir.y, f),
+                      dz = __shfl_sync(0xffffffffu, dir.z, f);
+          const float fhi = __shfl_sync(0xffffffffu, hi, f);
+          const int fit = __shfl_sync(0xffffffffu, iters, f);
+#pragma unroll 4
+          for (int k = 0; k < 32; ++k) {
+            if (k <= lane) {
+              c.x = FP<F>::mad(dx, p.block_length.d, c.x);
+              c.y = FP<F>::mad(dy, p.block_length.d, c.y);
+              c.z = FP<F>::mad(dz, p.block_length.d, c.z);
+            }
           }
-        }
-        const float depth = xform1_z<F>(Tcw, c.x, c.y, c.z);
-        int cbx, cby, cbz;
-        block_of(c, cbx, cby, cbz);
-        const bool occ = valid && space_bit(p, cbx, cby, cbz);
-        const bool cap = (fit + j + 1 >= 500);
-        const bool out = !(depth < fhi);
-        const unsigned sm = __ballot_sync(0xffffffffu, cap || out || occ);
-        // the ray's own group: first lane where the run ends, else the group's last lane
-        const int rank = __popc(fmask & ((1u << lane) - 1u));
-        const unsigned gmask = (gs == 32 ? 0xffffffffu : ((1u << gs) - 1u)) << ((rank << gshift) & 31);
-        const int w = freeing ? ((sm & gmask) ? __ffs(sm & gmask) - 1 : (rank << gshift) + gs - 1) : lane;
-        const float rx = __shfl_sync(0xffffffffu, c.x, w), ry = __shfl_sync(0xffffffffu, c.y, w),
-                    rz = __shfl_sync(0xffffffffu, c.z, w);
-        const int rbx = __shfl_sync(0xffffffffu, cbx, w), rby = __shfl_sync(0xffffffffu, cby, w),
-                  rbz = __shfl_sync(0xffffffffu, cbz, w);
-        const int rflags = __shfl_sync(0xffffffffu, (cap ? 1 : 0) | (out ? 2 : 0) | (occ ? 4 : 0), w);
-        if (freeing) {
-          const int steps = w - (rank << gshift) + 1;
-          dbg_steps += steps;
-          ++dbg_rounds;
-          pt.x = rx; pt.y = ry; pt.z = rz;
-          bx = rbx; by = rby; bz = rbz;
-          iters += steps;
-          if (rflags & 1) { red = true; state = ST_DONE; freeing = false; }
-          else if (rflags & 2) { state = ST_DONE; freeing = false; }
-          else if (rflags & 4) freeing = false;
+          const float depth = xform1_z<F>(Tcw, c.x, c.y, c.z);
+          int cbx, cby, cbz;
+          block_of(c, cbx, cby, cbz);
+          const bool occ = space_bit(p, cbx, cby, cbz);
+          const bool cap = (fit + lane + 1 >= 500);
+          const bool out = !(depth < fhi);
+          const unsigned sm = __ballot_sync(0xffffffffu, cap || out || occ);
+          const int w = sm ? __ffs(sm) - 1 : 31;  // first position where the run ends, else the last one
+          const float rx = __shfl_sync(0xffffffffu, c.x, w), ry = __shfl_sync(0xffffffffu, c.y, w),
+                      rz = __shfl_sync(0xffffffffu, c.z, w);
+          const int rbx = __shfl_sync(0xffffffffu, cbx, w), rby = __shfl_sync(0xffffffffu, cby, w),
+                    rbz = __shfl_sync(0xffffffffu, cbz, w);
+          const int rflags = __shfl_sync(0xffffffffu, (cap ? 1 : 0) | (out ? 2 : 0) | (occ ? 4 : 0), w);
+          if (lane == f) {
+            dbg_steps += w + 1;
+            pt.x = rx; pt.y = ry; pt.z = rz;
+            bx = rbx; by = rby; bz = rbz;
+            iters = fit + w + 1;
+            if (rflags & 1) { red = true; state = ST_DONE; freeing = false; }
+            else if (rflags & 2) { state = ST_DONE; freeing = false; }
+            else if (rflags & 4) freeing = false;
+          }
         }
         fmask = __ballot_sync(0xffffffffu, freeing);
       }
       // Many lanes in free space: they take the steps together, one step per loop trip.
-      // (Measured and rejected on B200: evaluating 4 positions per lane and trip - 140 us against
-      // 132 us, a lone warp is bound by its instruction count, not by the latency of one test -
-      // and a shared-memory brick-level map for 4-step jumps - the 128^3 torus aliases too much.)
+      // (Measured and rejected on B200, see profiles/r01_raycast_tail.md: 4 positions per lane and
+      // trip, a brick-level map for 4-step jumps, one lane group per ray in the cooperative runs,
+      // several sampling steps per trip, a second pass for the rays that outlive their tile.)
       for (int n = 0; n < p.free_run && __any_sync(0xffffffffu, freeing); ++n) {
         if (freeing) {
           ++dbg_steps;
@@ -673,9 +666,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       }
     }
     if (p.timeline) { const long long c = clock64(); c_free += c - c_t; c_t = c; }
-    // One step of a lane at the block (bx, by, bz) under its point; true if the lane sampled a
-    // voxel, stepped on and is still marching (so that it may take another such step at once).
-    auto sample_step = [&]() -> bool {
+    if (state != ST_DONE && !parked) {
       const int data = find_data<PEERS>(p, cache, bx, by, bz);
       if (data != -1) {
         float wx, wy, wz;
@@ -694,7 +685,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
           kwx = wx; kwy = wy; kwz = wz;
         } else if (advance(sdf, bx, by, bz)) {
           after_step();
-          return state == ST_MARCH;
         }
       } else if (state == ST_MARCH) {
         pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
@@ -705,19 +695,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         // REFINE without a block under the backed-up point: no second interpolation
         final_depth = xform1_z<F>(Tcw, pt.x, pt.y, pt.z);
         state = ST_DONE;
-      }
-      return false;
-    };
-    bool more = false;
-    if (state != ST_DONE && !parked) more = sample_step();
-    // Lanes that stepped inside allocated space usually stay there for a few steps (a step is at
-    // most the truncation length, a block is 8 voxels): they take up to sample_steps of them per
-    // trip instead of waiting a whole trip (free-space run of the other lanes, phase B) for each.
-    for (int rep = 1; rep < p.sample_steps && __any_sync(0xffffffffu, more); ++rep) {
-      if (more) {
-        more = false;
-        block_of(pt, bx, by, bz);
-        if (p.free_run == 0 || space_bit(p, bx, by, bz)) more = sample_step();
       }
     }
     // ---- phase B: interpolation for the parked lanes, batched ------------------------------
@@ -982,9 +959,8 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.bucket_bits = bucket_bits;
   t.space_bits = nullptr;
   t.free_run = 0;
-  t.coop_lanes = std::min(8, g_tune[VK_TUNE_RAY_COOP_LANES].load());  // groups of >= 4 lanes per ray
+  t.coop_lanes = g_tune[VK_TUNE_RAY_COOP_LANES].load();
   t.coop_rounds = g_tune[VK_TUNE_RAY_COOP_ROUNDS].load();
-  t.sample_steps = std::max(1, g_tune[VK_TUNE_RAY_SAMPLE_STEPS].load());
   t.negated_hi = false;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
