@@ -267,25 +267,42 @@ def run_ours(args, rank, world):
         barrier()
         return time.perf_counter() - t0
 
+    host_submit = []
+
     def e2e_streamed():
         """vulcan_b200.pipeline.FramePipeline: the same copies and kernels for every frame, the
         copies of neighbouring frames overlapped with the kernels; the host takes frame k-1's
         images (and reads a pixel of each) while frame k is in flight."""
         from vulcan_b200.pipeline import FramePipeline
-        pipe = FramePipeline(vol, vb.DepthIntegrator(vol), vb.Tracer(vol), W, H, depth=2)
+        depth = args.pipeline_depth
+        lag = depth - 1
+        pipe = FramePipeline(vol, vb.DepthIntegrator(vol), vb.Tracer(vol), W, H, depth=depth)
         metas = [frame_for(k, None) for k in range(nfr)]
         acc = 0.0
+
+        def take(k):
+            hd, hc, hn = pipe.result(k)
+            return float(hd[H // 2, W // 2]) + float(hc[H // 2, W // 2, 0]) + float(hn[H // 2, W // 2, 2])
+
+        host_submit.clear()
+        taken = 0  # frames whose images the host has taken so far (each exactly once, in order)
         for k in range(nfr):
             if k == args.warmup:
+                while taken < k:
+                    acc += take(taken)
+                    taken += 1
                 pipe.drain()
                 barrier()
                 t0 = time.perf_counter()
+            h0 = time.perf_counter()
             pipe.submit(pinned_in[k], metas[k])
-            if k > 0:
-                hd, hc, hn = pipe.result(k - 1)
-                acc += float(hd[H // 2, W // 2]) + float(hc[H // 2, W // 2, 0]) + float(hn[H // 2, W // 2, 2])
-        hd, hc, hn = pipe.result(nfr - 1)
-        acc += float(hd[H // 2, W // 2])
+            host_submit.append(time.perf_counter() - h0)
+            while taken <= k - lag:
+                acc += take(taken)
+                taken += 1
+        while taken < nfr:
+            acc += take(taken)
+            taken += 1
         pipe.drain()
         barrier()
         return time.perf_counter() - t0, acc
@@ -328,11 +345,13 @@ def run_ours(args, rank, world):
         "clocks": clocks,
         "e2e": {"value": total_units / t_e2e, "unit": "voxel-updates/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": t_e2e * 1e3 / args.steps,
-                "what": ("vulcan_b200.pipeline.FramePipeline (depth 2): every frame's pinned host depth -> device, "
+                "what": ("vulcan_b200.pipeline.FramePipeline (depth %d): every frame's pinned host depth -> device, "
                          "SetView+Integrate+Trace, traced depth+colour+normal -> pinned host; copies of neighbouring "
-                         "frames overlap the kernels; the host takes frame k-1's images while frame k is in flight")
+                         "frames overlap the kernels; the host takes (and reads a pixel of) frame k-%d's images after "
+                         "submitting frame k" % (args.pipeline_depth, args.pipeline_depth - 1))
                 if e2e_mode == "streamed" else
                 "pinned host depth -> device, SetView+Integrate+Trace, traced depth+colour+normal -> pinned host, sync every step",
+                "host_submit_us_median": (float(np.median(host_submit[args.warmup:]) * 1e6) if host_submit else None),
                 "sync_every_step": {"value": total_units / t_sync, "ms_per_step": t_sync * 1e3 / args.steps}},
         "gpu_launches": int(launches),
         "wall_s_timed_region": t_wall,
@@ -469,6 +488,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pipeline-depth", type=int, default=3,
+                    help="frames in flight in the end-to-end leg (FramePipeline); the host takes frame k-depth+1")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", 0))

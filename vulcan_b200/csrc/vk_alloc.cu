@@ -153,6 +153,8 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
 //   tmax  = (L*(b + max(0,step)) - begin) / dir     FFMA bf*L - begin ; IEEE div
 template <bool F>
 __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   // CTA tile 32x8 pixels, warp tile 8x4
@@ -274,6 +276,8 @@ __device__ __forceinline__ int resolve_block(const AllocParams& p, unsigned long
 
 template <bool F>
 __global__ void __launch_bounds__(256) vk_alloc_tile_kernel(const AllocParams p) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   __shared__ unsigned long long s_set[kSetSlots];
   __shared__ int s_list[kSetSlots + 256];
   __shared__ int s_count, s_base;
@@ -405,16 +409,25 @@ struct CarryParams {
 // be VISIBILITY_UNKNOWN, i.e. the previous visible list.
 template <bool F>
 __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
+  // The previous list, its entries and the frustum test do not depend on the allocation kernel
+  // that precedes this one in the chain: they are evaluated while that kernel drains; only the
+  // stamps (is the entry already on the new list?) need it to have completed.
+  pdl_trigger();
+  bool waited = false;
   const int n_prev = p.counters[p.prev_slot];
   const int lane = threadIdx.x & 31;
   for (int base = blockIdx.x * blockDim.x; base < n_prev; base += gridDim.x * blockDim.x) {
     const int i = base + threadIdx.x;
     bool keep = false;
     int e = -1;
+    int4 ent = make_int4(0, 0, 0, 0);
     if (i < n_prev) {
       e = p.prev_list[i];
+      ent = ld_entry(p.entries + e);
+    }
+    if (!waited) { pdl_wait(); waited = true; }
+    if (i < n_prev) {
       if (p.stamps[e] != p.view_id) {
-        const int4 ent = ld_entry(p.entries + e);
         int ox, oy, oz;
         entry_origin(ent, ox, oy, oz);
         Mat34 M;
@@ -441,6 +454,7 @@ __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
       if (keep) p.visible_out[pos + __popc(m & ((1u << lane) - 1))] = e;
     }
   }
+  if (!waited) pdl_wait();
   // last CTA out: retire the previous list and mirror the counters to the host
   __shared__ bool last;
   __threadfence();
@@ -611,11 +625,11 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
   const bool strict = (v->math_mode == VK_MATH_STRICT);
   if (g_tune[VK_TUNE_ALLOC_MODE].load() == 0) {
-    if (strict) vk_alloc_kernel<false><<<grid, 256, 0, s>>>(a);
-    else vk_alloc_kernel<true><<<grid, 256, 0, s>>>(a);
+    if (strict) launch_chained(vk_alloc_kernel<false>, grid, dim3(256), 0, s, a);
+    else launch_chained(vk_alloc_kernel<true>, grid, dim3(256), 0, s, a);
   } else {
-    if (strict) vk_alloc_tile_kernel<false><<<grid, 256, 0, s>>>(a);
-    else vk_alloc_tile_kernel<true><<<grid, 256, 0, s>>>(a);
+    if (strict) launch_chained(vk_alloc_tile_kernel<false>, grid, dim3(256), 0, s, a);
+    else launch_chained(vk_alloc_tile_kernel<true>, grid, dim3(256), 0, s, a);
   }
   VK_COUNT_LAUNCH();
 
@@ -636,8 +650,8 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   c.block_length = a.block_length;
   c.view_id = v->view_id;
   c.ticket = v->counters + VK_CNT_COUNT;
-  if (strict) vk_carry_kernel<false><<<sm_count(), 256, 0, s>>>(c);
-  else vk_carry_kernel<true><<<sm_count(), 256, 0, s>>>(c);
+  if (strict) launch_chained(vk_carry_kernel<false>, dim3(sm_count()), dim3(256), 0, s, c);
+  else launch_chained(vk_carry_kernel<true>, dim3(sm_count()), dim3(256), 0, s, c);
   VK_COUNT_LAUNCH();
   v->visible_slot = cur;
   return (int)cudaGetLastError();

@@ -148,6 +148,8 @@ constexpr int integrate_min_ctas() { return MODE == MODE_DEPTH ? 8 : (MODE == MO
 
 template <int MODE, bool F>
 __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_kernel(const IntegrateParams p) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   const int n = *p.count;
   const int t = threadIdx.x;
   const int vz = t >> 4, vy = (t >> 1) & 7, vx0 = (t & 1) * 4;
@@ -304,6 +306,8 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
 // at [-3,+3] around (t + 3), so the window covers image offsets [-1,+5] of the pixel.
 __global__ void __launch_bounds__(256) vk_frame_mask_kernel(int width, int height, const float* depths,
                                                             const float* colors, float threshold, float* mask) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   constexpr int BD = 16, KS = 3, DIM = BD + 2 * KS;
   __shared__ float buf[DIM * DIM];
   const int x = blockIdx.x * BD + threadIdx.x;
@@ -402,9 +406,9 @@ static int integrate_grid() {
 template <int MODE>
 static int launch_integrate(const IntegrateParams& p, int math_mode, cudaStream_t s) {
   if (math_mode == VK_MATH_STRICT)
-    vk_integrate_kernel<MODE, false><<<integrate_grid<MODE, false>(), 128, 0, s>>>(p);
+    launch_chained(vk_integrate_kernel<MODE, false>, dim3(integrate_grid<MODE, false>()), dim3(128), 0, s, p);
   else
-    vk_integrate_kernel<MODE, true><<<integrate_grid<MODE, true>(), 128, 0, s>>>(p);
+    launch_chained(vk_integrate_kernel<MODE, true>, dim3(integrate_grid<MODE, true>()), dim3(128), 0, s, p);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
@@ -429,8 +433,8 @@ extern "C" int vk_integrate_color(vkVolume* v, const vkFrame* f, float min_depth
 extern "C" int vk_compute_frame_mask(const vkFrame* f, float depth_threshold, float* mask, void* stream) {
   if (!f || !f->depth || !f->color || !mask) return VK_E_INVALID;
   dim3 grid((f->depth_w + 15) / 16, (f->depth_h + 15) / 16), block(16, 16);
-  vk_frame_mask_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(f->depth_w, f->depth_h, f->depth, f->color,
-                                                                 depth_threshold, mask);
+  launch_chained(vk_frame_mask_kernel, grid, block, 0, (cudaStream_t)stream, f->depth_w, f->depth_h, f->depth, f->color,
+                 depth_threshold, mask);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }

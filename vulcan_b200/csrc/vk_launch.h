@@ -3,6 +3,7 @@
 
 #include <atomic>
 #include <cstring>
+#include <utility>
 #include <cuda_runtime.h>
 #include "vk_math.cuh"
 
@@ -15,7 +16,7 @@ extern std::atomic<int> g_default_math_mode;
 // Tuning knobs (vk_tune): launch shapes and batching thresholds, never results.
 enum { VK_TUNE_RAY_CTA_THREADS = 0, VK_TUNE_RAY_BATCH_LANES = 1, VK_TUNE_RAY_BATCH_WAIT = 2,
        VK_TUNE_INTEGRATE_CTAS_PER_SM = 3, VK_TUNE_ALLOC_MODE = 4, VK_TUNE_RAY_COOP_LANES = 5, VK_TUNE_DEBUG_X = 6, VK_TUNE_RAY_FREE_RUN = 7,
-       VK_TUNE_RAY_COOP_ROUNDS = 8, VK_TUNE_RAY_SAMPLE_STEPS = 9, VK_TUNE_COUNT = 10 };
+       VK_TUNE_RAY_COOP_ROUNDS = 8, VK_TUNE_PDL = 9, VK_TUNE_COUNT = 10 };
 extern std::atomic<int> g_tune[VK_TUNE_COUNT];
 
 // rows 0..2 of a column-major 4x4 (vulcan::Matrix4f) as row-major 3x4
@@ -32,6 +33,35 @@ Div make_div(float d, cudaStream_t stream);
 
 // number of SMs of the current device (cached per device)
 int sm_count();
+
+// Programmatic dependent launch (sm_90+): the kernels of a frame form a chain on one stream; a
+// kernel launched through launch_chained may be scheduled while the tail of its predecessor is
+// still running, and blocks in pdl_wait() until the predecessor has completed and its writes are
+// visible.  Hides the launch latency between the seven kernels of a step and lets a kernel do
+// work that does not depend on its predecessor first.  Every kernel launched this way calls
+// pdl_wait() in all of its threads before touching anything an earlier kernel wrote.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chained(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                  Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_tune[VK_TUNE_PDL].load() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 }  // namespace vk
+
+#ifdef __CUDACC__
+namespace vk {
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;"); }
+}  // namespace vk
+#endif
 
 #define VK_COUNT_LAUNCH() (::vk::g_launches.fetch_add(1, std::memory_order_relaxed))

@@ -121,6 +121,8 @@ __device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw,
 // of the grid in shared memory and then merges the cells it touched.
 template <bool F>
 __global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   extern __shared__ float s_cells[];  // bw*bh*2
   // The ray marcher that follows walks free space through the occupancy filter with dependent
   // gathers; its longest rays set the duration of the whole trace.  Pull the filter into L2 now
@@ -168,6 +170,8 @@ __global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
 }
 
 __global__ void vk_reset_bounds_kernel(float2* bounds, int count, float hi_init) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < count) bounds[i] = make_float2(+FLT_MAX, hi_init);
 }
@@ -478,6 +482,8 @@ enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
 // operations of each ray is unchanged, so the result is bit-identical to the per-ray loop.
 template <bool F, bool KEYS, bool PEERS>
 __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const TraceParams p) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int wpc = blockDim.x >> 5;
   // warp tile 8x4 pixels, CTA = wpc tiles stacked in y
@@ -802,6 +808,8 @@ namespace vk {
 template <bool F>
 __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, const vkProjection proj,
                                                          float* normals, int w, int h, int y_begin, int y_end) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
   constexpr int TW = 32, TH = 8, PAD = 2, SW = TW + 2 * PAD, SH = TH + 2 * PAD;
   __shared__ float tile[SH * SW];
   const int x0 = blockIdx.x * TW, y0 = y_begin + blockIdx.y * TH;
@@ -894,7 +902,8 @@ extern "C" void vk_debug_trace_timeline(unsigned long long* device_buffer) { g_t
 static int reset_bounds(float* bounds, int count, float hi_init, cudaStream_t s) {
   if (!bounds || count < 0) return VK_E_INVALID;
   if (count == 0) return 0;
-  vk_reset_bounds_kernel<<<(count + 255) / 256, 256, 0, s>>>(reinterpret_cast<float2*>(bounds), count, hi_init);
+  launch_chained(vk_reset_bounds_kernel, dim3((count + 255) / 256), dim3(256), 0, s, reinterpret_cast<float2*>(bounds), count,
+                 hi_init);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
@@ -990,11 +999,11 @@ static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
   if (t.y_end <= t.y_begin) return 0;
   dim3 grid((t.w + 7) / 8, (t.y_end - t.y_begin + rows - 1) / rows);
   if (!KEYS && t.peer_count > 1) {  // sharded volume: lookups may go to the owner's tables
-    if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, false, true><<<grid, threads, 0, s>>>(t);
-    else vk_raycast_kernel<true, false, true><<<grid, threads, 0, s>>>(t);
+    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, false, true>, grid, dim3(threads), 0, s, t);
+    else launch_chained(vk_raycast_kernel<true, false, true>, grid, dim3(threads), 0, s, t);
   } else {
-    if (math_mode == VK_MATH_STRICT) vk_raycast_kernel<false, KEYS, false><<<grid, threads, 0, s>>>(t);
-    else vk_raycast_kernel<true, KEYS, false><<<grid, threads, 0, s>>>(t);
+    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, KEYS, false>, grid, dim3(threads), 0, s, t);
+    else launch_chained(vk_raycast_kernel<true, KEYS, false>, grid, dim3(threads), 0, s, t);
   }
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
@@ -1035,9 +1044,9 @@ static int normals_mode(const float* depths, const vkProjection* proj, float* no
   if (y_end <= y_begin) return 0;
   dim3 grid((image_w + 31) / 32, (y_end - y_begin + 7) / 8);
   if (math_mode == VK_MATH_STRICT)
-    vk_normals_kernel<false><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h, y_begin, y_end);
+    launch_chained(vk_normals_kernel<false>, grid, dim3(256), 0, s, depths, *proj, normals, image_w, image_h, y_begin, y_end);
   else
-    vk_normals_kernel<true><<<grid, 256, 0, s>>>(depths, *proj, normals, image_w, image_h, y_begin, y_end);
+    launch_chained(vk_normals_kernel<true>, grid, dim3(256), 0, s, depths, *proj, normals, image_w, image_h, y_begin, y_end);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
@@ -1072,8 +1081,8 @@ static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth,
   b.warm_lines = VK_SPACE_WORDS / 32;
   b.negate_hi = negate_hi;
   const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float);
-  if (v->math_mode == VK_MATH_STRICT) vk_bounds_kernel<false><<<kBoundsGrid, 512, smem, s>>>(b);
-  else vk_bounds_kernel<true><<<kBoundsGrid, 512, smem, s>>>(b);
+  if (v->math_mode == VK_MATH_STRICT) launch_chained(vk_bounds_kernel<false>, dim3(kBoundsGrid), dim3(512), smem, s, b);
+  else launch_chained(vk_bounds_kernel<true>, dim3(kBoundsGrid), dim3(512), smem, s, b);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
