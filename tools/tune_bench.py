@@ -137,7 +137,7 @@ def main():
             print(json.dumps(results[-1]), flush=True)
         lib.vk_tune(KNOB["int_ctas"], 0)
     if "set" in what:
-        for mode in (0, 1):
+        for mode in (256, 128, 64, 1):
             lib.vk_tune(KNOB["alloc_mode"], mode)
             med, mn = timed(lambda: vol.SetView(frame))
             n = vol.GetVisibleCount()

@@ -156,10 +156,12 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
   pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
   pdl_trigger();  // the next one may be scheduled as this grid drains
   const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  // CTA tile 32x8 pixels, warp tile 8x4
-  const int x = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
-  const int y = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
+  // warp tile 8x4 pixels; the warps of the grid take the tiles row by row (the kernel has no
+  // CTA-level state, so the CTA size only sets the granularity of the waves)
+  const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int tiles_x = (p.w + 7) >> 3;
+  const int x = (tile % tiles_x) * 8 + (lane & 7);
+  const int y = (tile / tiles_x) * 4 + (lane >> 3);
 
   bool active = (x < p.w && y < p.h);
   int bx = 0, by = 0, bz = 0, ex = 0, ey = 0, ez = 0, sx = 1, sy = 1, sz = 1;
@@ -624,9 +626,13 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.shard_halo = v->shard_halo;
   dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
   const bool strict = (v->math_mode == VK_MATH_STRICT);
-  if (g_tune[VK_TUNE_ALLOC_MODE].load() == 0) {
-    if (strict) launch_chained(vk_alloc_kernel<false>, grid, dim3(256), 0, s, a);
-    else launch_chained(vk_alloc_kernel<true>, grid, dim3(256), 0, s, a);
+  const int mode = g_tune[VK_TUNE_ALLOC_MODE].load();  // 1: tile kernel; 64/128/256: CTA size of the warp kernel
+  if (mode != 1) {
+    const int threads = (mode == 64 || mode == 128) ? mode : 256;  // measured on B200: no difference (31.7 us)
+    const int tiles = ((a.w + 7) / 8) * ((a.h + 3) / 4), wpc = threads / 32;
+    const dim3 wgrid((tiles + wpc - 1) / wpc);
+    if (strict) launch_chained(vk_alloc_kernel<false>, wgrid, dim3(threads), 0, s, a);
+    else launch_chained(vk_alloc_kernel<true>, wgrid, dim3(threads), 0, s, a);
   } else {
     if (strict) launch_chained(vk_alloc_tile_kernel<false>, grid, dim3(256), 0, s, a);
     else launch_chained(vk_alloc_tile_kernel<true>, grid, dim3(256), 0, s, a);
