@@ -26,6 +26,10 @@ struct Frame
   // normals from depth; creates / resizes normal_image (src/frame.cu:7-122, src/frame.cpp:21-36)
   void ComputeNormals();
 
+  // addition: FilterDepths followed by ComputeNormals in one kernel; replaces depth_image by the
+  // filtered image (a new Image object: other holders of the old pointer keep the raw depth)
+  void Prepare();
+
   // tracker support (pyramids): outside the fusion hot path, throws "not implemented"
   void Downsample(Frame& frame) const;
 };

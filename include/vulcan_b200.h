@@ -239,6 +239,15 @@ int vk_compute_normals(const float* depths, const vkProjection* proj, float* nor
 /* Frame::FilterDepths / vulcan::FilterDepths (src/frame.cu:124-181,194-203). */
 int vk_filter_depths(int image_w, int image_h, const float* src, float* dst, void* stream);
 
+/* Input-side pre-pass of a sensor frame in one kernel: dst_depth = FilterDepths(src) and
+ * dst_normals = ComputeNormals(dst_depth), bit-identical to vk_filter_depths followed by
+ * vk_compute_normals (src/frame.cpp:8-36).  src and dst_depth must not alias.
+ * Note: in the reference's release build Frame::FilterDepths filters into a temporary and the
+ * copy back into the frame sits in CUDA_DEBUG(...), which NDEBUG removes (src/frame.cpp:18), so
+ * the frame stays unfiltered there; the free function vulcan::FilterDepths is what this mirrors. */
+int vk_prepare_frame(int image_w, int image_h, const float* src, const vkProjection* proj,
+                     float* dst_depth, float* dst_normals, void* stream);
+
 /* ---- sharding (no reference counterpart) -------------------------------------- */
 
 /* Tables of all ranks of a sharded volume as seen from one rank: its own pointers in slot

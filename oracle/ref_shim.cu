@@ -10,6 +10,7 @@
 #include <vulcan/hash.h>
 #include <vulcan/voxel.h>
 #include <vulcan/frame.h>
+#include <vulcan/frame.cuh>
 #include <vulcan/image.h>
 #include <vulcan/depth_integrator.h>
 #include <vulcan/color_integrator.h>
@@ -137,6 +138,22 @@ int ref_set_frame_device(void* h, const float* depth_dev, int w, int hgt, const 
     cudaMemcpyAsync(r->frame.depth_image->GetData(), depth_dev, sizeof(float) * w * hgt, cudaMemcpyDeviceToDevice, 0);
   set_pose(r->frame, dproj, nullptr, Twd, nullptr);
   return (int)cudaGetLastError();
+}
+
+// vulcan::FilterDepths (src/frame.cu:194-203) on caller-provided device buffers.  (Frame::FilterDepths
+// discards its result in a release build: the copy back is inside CUDA_DEBUG, src/frame.cpp:18.)
+int ref_filter_depths(int w, int hgt, const float* src_dev, float* dst_dev) {
+  vulcan::FilterDepths(w, hgt, src_dev, dst_dev);
+  return (int)cudaDeviceSynchronize();
+}
+
+// vulcan::ComputeNormals (src/frame.cu:183-192) on caller-provided device buffers
+int ref_compute_normals(const float* depth_dev, const float* dproj, float* normals_dev, int w, int hgt) {
+  vulcan::Projection P;
+  P.SetFocalLength(dproj[0], dproj[1]);
+  P.SetCenterPoint(dproj[2], dproj[3]);
+  vulcan::ComputeNormals(depth_dev, P, reinterpret_cast<vulcan::Vector3f*>(normals_dev), w, hgt);
+  return (int)cudaDeviceSynchronize();
 }
 
 int ref_compute_input_normals(void* h) {

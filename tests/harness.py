@@ -185,8 +185,26 @@ def ref_lib(nofmad=False):
         lib.ref_device_ptr.argtypes = [_P, _I]
         lib.ref_visible_count.argtypes = [_P]
         lib.ref_download.argtypes = [_P, _P, C.c_size_t]
+        lib.ref_filter_depths.argtypes = [_I, _I, _P, _P]
+        lib.ref_compute_normals.argtypes = [_P, _P, _P, _I, _I]
         _ref_libs[path] = lib
     return _ref_libs[path]
+
+
+def ref_prepare_frame(depth, K, nofmad=False):
+    """The reference's input-side pre-pass on the GPU: vulcan::FilterDepths then vulcan::ComputeNormals of the
+    filtered depth (src/frame.cu:124-203).  Returns (filtered depth, normals) as numpy arrays."""
+    import torch
+    lib = ref_lib(nofmad)
+    h, w = depth.shape
+    src = torch.from_numpy(np.ascontiguousarray(depth, dtype=np.float32)).cuda()
+    dst = torch.zeros_like(src)
+    nrm = torch.zeros((h, w, 3), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    assert lib.ref_filter_depths(w, h, src.data_ptr(), dst.data_ptr()) == 0
+    k = np.ascontiguousarray(K, dtype=np.float32)
+    assert lib.ref_compute_normals(dst.data_ptr(), k.ctypes.data_as(_P), nrm.data_ptr(), w, h) == 0
+    return dst.cpu().numpy(), nrm.cpu().numpy()
 
 
 class RefVolume:

@@ -94,6 +94,7 @@ SYMBOLS = {
     "vk_compute_points": [_P, _P, _P, _I, _F, _F, _F, C.POINTER(vkTransform), C.POINTER(vkProjection), _P, _P, _I, _I, _I, _I, _P],
     "vk_compute_normals": [_P, C.POINTER(vkProjection), _P, _I, _I, _P],
     "vk_filter_depths": [_I, _I, _P, _P, _P],
+    "vk_prepare_frame": [_I, _I, _P, C.POINTER(vkProjection), _P, _P, _P],
     "vk_shard_owner": [_I, _I, _I, _I, _I],
     "vk_trace_bounds": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _P, _P],
     "vk_trace_rows": [C.POINTER(vkVolume), C.POINTER(vkPeerTable), C.POINTER(vkFrame), _P, _I, _I, _P, _P, _P, _P],

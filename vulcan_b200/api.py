@@ -166,6 +166,20 @@ class Frame:
         check(lib.vk_compute_normals(self.depth_image.data_ptr(), C.byref(p), self.normal_image.data_ptr(), w, h,
                                      _stream()), "ComputeNormals")
 
+    def Prepare(self):
+        """FilterDepths + ComputeNormals of a sensor frame in one kernel (vk_prepare_frame); the depth
+        image is replaced by the filtered one."""
+        if self.depth_image is None:
+            raise VulcanError("missing depth image")
+        h, w = self.depth_image.shape
+        out = torch.empty_like(self.depth_image)
+        if self.normal_image is None or tuple(self.normal_image.shape) != (h, w, 3):
+            self.normal_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
+        p = self.depth_projection.to_c()
+        check(lib.vk_prepare_frame(w, h, self.depth_image.data_ptr(), C.byref(p), out.data_ptr(),
+                                   self.normal_image.data_ptr(), _stream()), "Prepare")
+        self.depth_image = out
+
     def FilterDepths(self):
         """Frame::FilterDepths (src/frame.cpp:8-19)."""
         if self.depth_image is None:

@@ -802,6 +802,44 @@ __global__ void __launch_bounds__(256) vk_resolve_keys_kernel(const unsigned lon
 
 namespace vk {
 
+// normal of pixel (x, y) from a shared-memory depth tile with a 2-pixel margin
+// (ComputeNormalsKernel<16>, src/frame.cu:7-122)
+template <bool F>
+__device__ __forceinline__ Vec3 normal_from_tile(const float* tile, int stride, int tx, int ty, int x, int y,
+                                                 const vkProjection& proj) {
+  constexpr int PAD = 2;
+  const float depth = tile[ty * stride + tx];
+  Vec3 out = {0.f, 0.f, 0.f};
+  if (depth > 0) {
+    Unprojector un;
+    un.init(proj);
+    const Vec3 z0 = {mul(un.x<F>(add((float)x, 0.5f)), depth), mul(un.y<F>(add((float)y, 0.5f)), depth), depth};
+    Vec3 q[4];
+    const int ox[4] = {-PAD, +PAD, 0, 0}, oy[4] = {0, 0, -PAD, +PAD};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float d = tile[(ty + oy[k]) * stride + tx + ox[k]];
+      if (d == 0) {
+        q[k] = z0;
+      } else {
+        q[k].x = mul(un.x<F>(add((float)(x + ox[k]), 0.5f)), d);
+        q[k].y = mul(un.y<F>(add((float)(y + oy[k]), 0.5f)), d);
+        q[k].z = d;
+      }
+    }
+    const Vec3 dx = {sub(q[0].x, q[1].x), sub(q[0].y, q[1].y), sub(q[0].z, q[1].z)};
+    const Vec3 dy = {sub(q[2].x, q[3].x), sub(q[2].y, q[3].y), sub(q[2].z, q[3].z)};
+    if (dot3<F>(dx, dx) > 0 && dot3<F>(dy, dy) > 0) {
+      Vec3 n;  // dy.Cross(dx)
+      n.x = FP<F>::msub(dy.y, dx.z, mul(dy.z, dx.y));
+      n.y = FP<F>::msub(dy.z, dx.x, mul(dy.x, dx.z));
+      n.z = FP<F>::msub(dy.x, dx.y, mul(dy.y, dx.x));
+      out = normalized<F>(n);
+    }
+  }
+  return out;
+}
+
 // ComputeNormalsKernel<16> (src/frame.cu:7-122): 32x8 tile + 2 px halo, zero outside.
 // FMA map: Unproject as in vk_math.cuh; dot FFMA chains; cross a.y*b.z - a.z*b.y ->
 // FMUL a.z*b.y ; FFMA a.y*b.z - .   (include/vulcan/matrix.h:174-183)
@@ -823,41 +861,37 @@ __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, co
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int x = x0 + tx, y = y0 + ty;
   if (x >= w || y >= y_end) return;
-  const float depth = tile[(ty + PAD) * SW + tx + PAD];
-  float nx = 0, ny = 0, nz = 0;
-  if (depth > 0) {
-    Unprojector un;
-    un.init(proj);
-    const Vec3 z0 = {mul(un.x<F>(add((float)x, 0.5f)), depth), mul(un.y<F>(add((float)y, 0.5f)), depth), depth};
-    Vec3 q[4];
-    const int ox[4] = {-PAD, +PAD, 0, 0}, oy[4] = {0, 0, -PAD, +PAD};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float d = tile[(ty + PAD + oy[k]) * SW + tx + PAD + ox[k]];
-      if (d == 0) {
-        q[k] = z0;
-      } else {
-        q[k].x = mul(un.x<F>(add((float)(x + ox[k]), 0.5f)), d);
-        q[k].y = mul(un.y<F>(add((float)(y + oy[k]), 0.5f)), d);
-        q[k].z = d;
-      }
-    }
-    const Vec3 dx = {sub(q[0].x, q[1].x), sub(q[0].y, q[1].y), sub(q[0].z, q[1].z)};
-    const Vec3 dy = {sub(q[2].x, q[3].x), sub(q[2].y, q[3].y), sub(q[2].z, q[3].z)};
-    if (dot3<F>(dx, dx) > 0 && dot3<F>(dy, dy) > 0) {
-      Vec3 n;  // dy.Cross(dx)
-      n.x = FP<F>::msub(dy.y, dx.z, mul(dy.z, dx.y));
-      n.y = FP<F>::msub(dy.z, dx.x, mul(dy.x, dx.z));
-      n.z = FP<F>::msub(dy.x, dx.y, mul(dy.y, dx.x));
-      n = normalized<F>(n);
-      nx = n.x; ny = n.y; nz = n.z;
-    }
-  }
+  const Vec3 n = normal_from_tile<F>(tile, SW, tx + PAD, ty + PAD, x, y, proj);
+  const float nx = n.x, ny = n.y, nz = n.z;
   const size_t o = 3 * ((size_t)y * w + x);
   normals[o] = nx; normals[o + 1] = ny; normals[o + 2] = nz;
 }
 
-// FilterDepthsKernel<16> (src/frame.cu:124-181): 7x7 bilateral, sigma_r^2 = 0.0004
+// FilterDepthsKernel<16> (src/frame.cu:124-181): 7x7 bilateral, sigma_r^2 = 0.0004.
+// FMA map (reference release SASS): only dn += ww * dk contracts; the spatial weight
+// expf(-(i*i + j*j) / 9) is a compile-time constant in both builds.
+template <bool F>
+__device__ __forceinline__ float bilateral7(const float* tile, int stride, int tx, int ty) {
+  constexpr int PAD = 3;
+  const float d0 = tile[ty * stride + tx];
+  float dn = 0, wsum = 0;
+#pragma unroll
+  for (int i = -PAD; i <= PAD; ++i)
+#pragma unroll
+    for (int j = -PAD; j <= PAD; ++j) {
+      const float dk = tile[(ty + i) * stride + tx + j];
+      const float delta = sub(d0, dk);
+      // Vector2f(i, j).SquaredNorm() / (pad * pad): float / int -> true division
+      const float wr = expf(-(float)(i * i + j * j) / (float)(PAD * PAD));
+      const float ws = expf(fdiv(-mul(delta, delta), 0.0004f));
+      const float ww = mul(wr, ws);
+      dn = FP<F>::mad(ww, dk, dn);
+      wsum = add(wsum, ww);
+    }
+  return fdiv(dn, wsum);
+}
+
+template <bool F>
 __global__ void __launch_bounds__(256) vk_filter_depths_kernel(int w, int h, const float* src, float* dst) {
   constexpr int TW = 32, TH = 8, PAD = 3, SW = TW + 2 * PAD, SH = TH + 2 * PAD;
   __shared__ float tile[SH * SW];
@@ -872,21 +906,45 @@ __global__ void __launch_bounds__(256) vk_filter_depths_kernel(int w, int h, con
   const int tx = (threadIdx.x & 31) + PAD, ty = (threadIdx.x >> 5) + PAD;
   const int x = x0 + tx - PAD, y = y0 + ty - PAD;
   if (x >= w || y >= h) return;
-  const float d0 = tile[ty * SW + tx];
-  float dn = 0, wsum = 0;
-  for (int i = -PAD; i <= PAD; ++i)
-    for (int j = -PAD; j <= PAD; ++j) {
-      const float dk = tile[(ty + i) * SW + tx + j];
-      const float delta = sub(d0, dk);
-      // Vector2f(i, j).SquaredNorm() / (pad * pad): float / int -> true division
-      const float sq = add(add(0.0f, mul((float)i, (float)i)), mul((float)j, (float)j));
-      const float wr = expf(fdiv(-sq, (float)(PAD * PAD)));
-      const float ws = expf(fdiv(-mul(delta, delta), 0.0004f));
-      const float ww = mul(wr, ws);
-      dn = add(dn, mul(ww, dk));
-      wsum = add(wsum, ww);
-    }
-  dst[y * w + x] = fdiv(dn, wsum);
+  dst[y * w + x] = bilateral7<F>(tile, SW, tx, ty);
+}
+
+// Input-side pre-pass of a sensor frame in ONE kernel: the bilateral filter of
+// Frame::FilterDepths followed by Frame::ComputeNormals on the filtered depth.  The raw depth
+// tile is read once with a 5-pixel margin, the filtered depth is kept in shared memory for the
+// tile plus the 2-pixel margin the normals need (0 outside the image, like the separate kernels
+// see it), and both images are written.  Results are bit-identical to the two separate calls.
+template <bool F>
+__global__ void __launch_bounds__(256) vk_prepare_frame_kernel(int w, int h, const float* src, const vkProjection proj,
+                                                               float* dst_depth, float* dst_normals) {
+  constexpr int TW = 32, TH = 8, P1 = 3, P2 = 2, PAD = P1 + P2;
+  constexpr int RW = TW + 2 * PAD, RH = TH + 2 * PAD;  // raw tile
+  constexpr int FW = TW + 2 * P2, FH = TH + 2 * P2;    // filtered tile
+  __shared__ float raw[RH * RW];
+  __shared__ float fil[FH * FW];
+  const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+  for (int s = threadIdx.x; s < RH * RW; s += TW * TH) {
+    const int gx = x0 - PAD + (s % RW), gy = y0 - PAD + (s / RW);
+    float d = 0;
+    if (gx >= 0 && gx < w && gy >= 0 && gy < h) d = __ldg(src + gy * w + gx);
+    raw[s] = d;
+  }
+  __syncthreads();
+  for (int s = threadIdx.x; s < FH * FW; s += TW * TH) {
+    const int fx = s % FW, fy = s / FW;
+    const int gx = x0 - P2 + fx, gy = y0 - P2 + fy;
+    float d = 0;
+    if (gx >= 0 && gx < w && gy >= 0 && gy < h) d = bilateral7<F>(raw, RW, fx + P1, fy + P1);
+    fil[s] = d;
+  }
+  __syncthreads();
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int x = x0 + tx, y = y0 + ty;
+  if (x >= w || y >= h) return;
+  dst_depth[y * w + x] = fil[(ty + P2) * FW + tx + P2];
+  const Vec3 n = normal_from_tile<F>(fil, FW, tx + P2, ty + P2, x, y, proj);
+  const size_t o = 3 * ((size_t)y * w + x);
+  dst_normals[o] = n.x; dst_normals[o + 1] = n.y; dst_normals[o + 2] = n.z;
 }
 
 }  // namespace vk
@@ -1059,7 +1117,25 @@ extern "C" int vk_compute_normals(const float* depths, const vkProjection* proj,
 extern "C" int vk_filter_depths(int image_w, int image_h, const float* src, float* dst, void* stream) {
   if (!src || !dst || image_w <= 0 || image_h <= 0) return VK_E_INVALID;
   dim3 grid((image_w + 31) / 32, (image_h + 7) / 8);
-  vk_filter_depths_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(image_w, image_h, src, dst);
+  if (g_default_math_mode.load() == VK_MATH_STRICT)
+    vk_filter_depths_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(image_w, image_h, src, dst);
+  else
+    vk_filter_depths_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(image_w, image_h, src, dst);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
+
+extern "C" int vk_prepare_frame(int image_w, int image_h, const float* src, const vkProjection* proj,
+                                float* dst_depth, float* dst_normals, void* stream) {
+  if (!src || !proj || !dst_depth || !dst_normals || src == dst_depth || image_w <= 0 || image_h <= 0)
+    return VK_E_INVALID;
+  dim3 grid((image_w + 31) / 32, (image_h + 7) / 8);
+  if (g_default_math_mode.load() == VK_MATH_STRICT)
+    vk_prepare_frame_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(image_w, image_h, src, *proj, dst_depth,
+                                                                           dst_normals);
+  else
+    vk_prepare_frame_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(image_w, image_h, src, *proj, dst_depth,
+                                                                          dst_normals);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }

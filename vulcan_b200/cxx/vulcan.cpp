@@ -69,6 +69,20 @@ void Frame::FilterDepths()
   CUDA_ASSERT(cudaStreamSynchronize(0));  // temp dies here
 }
 
+// FilterDepths + ComputeNormals in one kernel (vk_prepare_frame); not in the reference.
+void Frame::Prepare()
+{
+  VULCAN_ASSERT_MSG(depth_image != nullptr, "missing depth image");
+  const int w = depth_image->GetWidth(), h = depth_image->GetHeight();
+  auto filtered = std::make_shared<Image>(w, h);
+  EnsureColorImage(normal_image, w, h);
+  const vkProjection proj = ToC(depth_projection);
+  VK_ASSERT(vk_prepare_frame(w, h, depth_image->GetData(), &proj, filtered->GetData(),
+                             reinterpret_cast<float*>(normal_image->GetData()), nullptr));
+  CUDA_ASSERT(cudaStreamSynchronize(0));  // the unfiltered image may die here
+  depth_image = filtered;
+}
+
 void Frame::ComputeNormals()
 {
   VULCAN_ASSERT_MSG(depth_image != nullptr, "missing depth image");
