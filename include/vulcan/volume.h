@@ -10,6 +10,8 @@
 //   - the visible count stays on the device: GetVisibleBlocks() synchronises to learn its size.
 #pragma once
 
+#include <string>
+
 #include <cstdint>
 #include <vulcan/buffer.h>
 #include <vulcan/matrix.h>
@@ -58,6 +60,8 @@ class Volume
     int GetAllocatedBlockCount() const;                    // synchronises the stream
     void Reset();                                          // back to the freshly constructed state
     void SetSharding(int rank, int count, int brick_shift = 3, int halo = 0);  // spatial block sharding (multi-GPU)
+    void Save(const std::string& path) const;   // snapshot of the complete state (addition)
+    void Load(const std::string& path);         // into a volume of the same block counts
     void SetStream(cudaStream_t stream) { stream_ = stream; }
     cudaStream_t GetStream() const { return stream_; }
     vkVolume* GetHandle() { return &volume_; }

@@ -30,6 +30,7 @@ extern "C" {
 #define VK_E_OVERFLOW  (-3)  /* voxel pool or excess list exhausted (non fatal;     */
                              /* the reference drops such requests silently,         */
                              /* src/volume.cu:338-356)                              */
+#define VK_E_IO        (-4)  /* snapshot file missing, truncated or of another version */
 
 /* vkVolume::math_mode: where float multiply-adds round.                               */
 #define VK_MATH_REFERENCE 0  /* fused exactly where nvcc's default -fmad=true fuses them  */
@@ -176,6 +177,14 @@ int vk_set_view(vkVolume* v, const vkFrame* f, void* stream);
  * current visible-block count in *visible (Volume::GetBufferSize, src/volume.cu:537-543);
  * returns VK_E_OVERFLOW if any allocation has been dropped. */
 int vk_volume_sync_counters(vkVolume* v, int* visible, void* stream);
+
+/* Volume snapshots (no reference counterpart: the reference has no volume I/O).  vk_volume_save
+ * writes the complete state of a volume - hash entries, free list, visibility, visible lists,
+ * occupancy bitmaps, counters and the voxel blocks in use - to `path`; vk_volume_load restores it
+ * into a volume created with the same block counts, which then continues exactly as the saved one
+ * would have.  Both synchronise `stream`.  Little-endian, versioned; VK_E_IO on file errors. */
+int vk_volume_save(const vkVolume* v, const char* path, void* stream);
+int vk_volume_load(vkVolume* v, const char* path, void* stream);
 
 /* ---- Integrators ------------------------------------------------------------- */
 

@@ -81,6 +81,8 @@ SYMBOLS = {
     "vk_volume_destroy": [C.POINTER(vkVolume)],
     "vk_set_view": [C.POINTER(vkVolume), C.POINTER(vkFrame), _P],
     "vk_volume_sync_counters": [C.POINTER(vkVolume), C.POINTER(_I), _P],
+    "vk_volume_save": [C.POINTER(vkVolume), C.c_char_p, _P],
+    "vk_volume_load": [C.POINTER(vkVolume), C.c_char_p, _P],
     "vk_integrate_depth": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _F, _P],
     "vk_integrate_color": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _F, _F, _P],
     "vk_compute_frame_mask": [C.POINTER(vkFrame), _F, _P, _P],
@@ -144,5 +146,6 @@ def check(status, what):
         return
     if status > 0:
         raise VulcanError("%s: cuda error %d" % (what, status))
-    names = {-1: "invalid argument", -2: "no CUDA device", -3: "voxel/excess pool exhausted"}
+    names = {-1: "invalid argument", -2: "no CUDA device", -3: "voxel/excess pool exhausted",
+             -4: "snapshot file missing, truncated or of another version"}
     raise VulcanError("%s: %s" % (what, names.get(status, str(status))))

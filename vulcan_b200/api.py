@@ -246,6 +246,15 @@ class Volume:
     def Reset(self):
         check(lib.vk_volume_reset(C.byref(self._v), _stream()), "Volume.Reset")
 
+    def Save(self, path):
+        """Snapshot of the complete volume state (vk_volume_save); not in the reference."""
+        check(lib.vk_volume_save(C.byref(self._v), str(path).encode(), _stream()), "Volume.Save")
+
+    def Load(self, path):
+        """Restores a snapshot into this volume (same block counts); it then continues exactly as the
+        saved volume would have."""
+        check(lib.vk_volume_load(C.byref(self._v), str(path).encode(), _stream()), "Volume.Load")
+
     def SetView(self, frame):
         """One call reaches the fixed point of repeated reference SetView calls."""
         f = frame.to_c()

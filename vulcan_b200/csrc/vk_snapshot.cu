@@ -1,0 +1,213 @@
+// vk_snapshot.cu - volume snapshots (the reference has no volume I/O).
+//
+// vk_volume_save writes everything a volume needs to continue exactly where it was: the hash
+// entries, free list, visibility, both visible lists, stamps, occupancy bitmaps and counters in
+// full (a few MB), and the voxel blocks that some entry refers to (10 KB each; the other blocks
+// of the pool still hold Voxel::Empty()).  vk_volume_load restores them into a volume created
+// with the same block counts.  The file is little-endian and versioned; voxel blocks travel
+// through a pinned staging buffer in chunks, gathered / scattered by a kernel, so a 43 GB pool
+// with a few thousand allocated blocks costs a few MB, not 43 GB.
+#include "vk_math.cuh"
+#include "vk_launch.h"
+#include <cstdio>
+#include <vector>
+
+namespace vk {
+
+struct SnapshotHeader {
+  char magic[8];  // "VKVOL\0\0\1"
+  int32_t version;
+  int32_t main_blocks, excess_blocks;
+  float voxel_length, trunc_length, min_depth, max_depth;
+  int32_t shard_rank, shard_count, shard_shift, shard_halo;
+  int32_t visible_slot, view_id, math_mode;
+  int32_t counters[VK_CNT_COUNT + 4];
+  int64_t stored_blocks;  // voxel blocks that follow
+};
+
+constexpr int kSnapshotVersion = 1;
+constexpr size_t kChunkBlocks = 4096;  // 40 MB of voxels per staging round
+
+// dst[i] = pool[ids[i]] (gather) or pool[ids[i]] = src[i] (scatter), 10 KB per block, 16 B per thread
+__global__ void __launch_bounds__(256) vk_move_blocks_kernel(uint4* pool, uint4* staging, const int32_t* ids, int n,
+                                                             int scatter) {
+  constexpr int kQuads = VK_BLOCK_VOXELS * sizeof(vkVoxel) / 16;  // 640
+  for (int b = blockIdx.x; b < n; b += gridDim.x) {
+    uint4* p = pool + (size_t)ids[b] * kQuads;
+    uint4* s = staging + (size_t)b * kQuads;
+    for (int q = threadIdx.x; q < kQuads; q += blockDim.x) {
+      if (scatter) p[q] = s[q];
+      else s[q] = p[q];
+    }
+  }
+}
+
+struct File {
+  FILE* f = nullptr;
+  ~File() { if (f) fclose(f); }
+};
+
+static bool put(FILE* f, const void* p, size_t n) { return n == 0 || fwrite(p, 1, n, f) == n; }
+static bool get(FILE* f, void* p, size_t n) { return n == 0 || fread(p, 1, n, f) == n; }
+
+// device array <-> file through a host vector
+static int save_array(FILE* f, const void* dev, size_t bytes, cudaStream_t s) {
+  std::vector<char> host(bytes);
+  cudaError_t err = cudaMemcpyAsync(host.data(), dev, bytes, cudaMemcpyDeviceToHost, s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return (int)err;
+  return put(f, host.data(), bytes) ? 0 : VK_E_IO;
+}
+static int load_array(FILE* f, void* dev, size_t bytes, cudaStream_t s) {
+  std::vector<char> host(bytes);
+  if (!get(f, host.data(), bytes)) return VK_E_IO;
+  cudaError_t err = cudaMemcpyAsync(dev, host.data(), bytes, cudaMemcpyHostToDevice, s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  return (int)err;
+}
+
+}  // namespace vk
+
+using namespace vk;
+
+extern "C" int vk_volume_save(const vkVolume* v, const char* path, void* stream) {
+  if (!v || !v->voxels || !path) return VK_E_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t M = (size_t)v->main_blocks, B = M + (size_t)v->excess_blocks;
+  File file;
+  file.f = fopen(path, "wb");
+  if (!file.f) return VK_E_IO;
+
+  // entries first (on the host): they say which voxel blocks are in use
+  std::vector<vkHashEntry> entries(B);
+  cudaError_t err = cudaMemcpyAsync(entries.data(), v->entries, B * sizeof(vkHashEntry), cudaMemcpyDeviceToHost, s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return (int)err;
+  std::vector<int32_t> ids;
+  for (size_t i = 0; i < B; ++i) {
+    int32_t data;
+    memcpy(&data, reinterpret_cast<const char*>(&entries[i]) + 8, sizeof(data));  // HashEntry::data (hash.h:49-55)
+    if (data >= 0) ids.push_back(data);
+  }
+
+  SnapshotHeader h;
+  memset(&h, 0, sizeof(h));
+  memcpy(h.magic, "VKVOL\0\0\1", 8);
+  h.version = kSnapshotVersion;
+  h.main_blocks = v->main_blocks; h.excess_blocks = v->excess_blocks;
+  h.voxel_length = v->voxel_length; h.trunc_length = v->trunc_length;
+  h.min_depth = v->min_depth; h.max_depth = v->max_depth;
+  h.shard_rank = v->shard_rank; h.shard_count = v->shard_count; h.shard_shift = v->shard_shift;
+  h.shard_halo = v->shard_halo;
+  h.visible_slot = v->visible_slot; h.view_id = v->view_id; h.math_mode = v->math_mode;
+  err = cudaMemcpyAsync(h.counters, v->counters, sizeof(h.counters), cudaMemcpyDeviceToHost, s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return (int)err;
+  h.stored_blocks = (int64_t)ids.size();
+  if (!put(file.f, &h, sizeof(h))) return VK_E_IO;
+  if (!put(file.f, entries.data(), B * sizeof(vkHashEntry))) return VK_E_IO;
+
+  int rc;
+  if ((rc = save_array(file.f, v->free_list, B * sizeof(int32_t), s))) return rc;
+  if ((rc = save_array(file.f, v->visibility, B, s))) return rc;
+  if ((rc = save_array(file.f, v->visible[0], B * sizeof(int32_t), s))) return rc;
+  if ((rc = save_array(file.f, v->visible[1], B * sizeof(int32_t), s))) return rc;
+  if ((rc = save_array(file.f, v->stamps, B * sizeof(int32_t), s))) return rc;
+  if ((rc = save_array(file.f, v->bucket_bits, (M + 31) / 32 * sizeof(uint32_t), s))) return rc;
+  if ((rc = save_array(file.f, v->space_bits, VK_SPACE_WORDS * sizeof(uint32_t), s))) return rc;
+  if (!put(file.f, ids.data(), ids.size() * sizeof(int32_t))) return VK_E_IO;
+
+  // voxel blocks, gathered chunk by chunk
+  const size_t block_bytes = VK_BLOCK_VOXELS * sizeof(vkVoxel);
+  const size_t chunk = ids.size() < kChunkBlocks ? ids.size() : kChunkBlocks;
+  if (chunk) {
+    uint4* d_stage = nullptr;
+    int32_t* d_ids = nullptr;
+    char* h_stage = nullptr;
+    err = cudaMalloc((void**)&d_stage, chunk * block_bytes);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&d_ids, chunk * sizeof(int32_t));
+    if (err == cudaSuccess) err = cudaMallocHost((void**)&h_stage, chunk * block_bytes);
+    for (size_t at = 0; err == cudaSuccess && rc == 0 && at < ids.size(); at += chunk) {
+      const size_t n = (ids.size() - at < chunk) ? ids.size() - at : chunk;
+      err = cudaMemcpyAsync(d_ids, ids.data() + at, n * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+      if (err != cudaSuccess) break;
+      vk_move_blocks_kernel<<<sm_count() * 4, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), d_stage, d_ids, (int)n, 0);
+      VK_COUNT_LAUNCH();
+      err = cudaMemcpyAsync(h_stage, d_stage, n * block_bytes, cudaMemcpyDeviceToHost, s);
+      if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+      if (err == cudaSuccess && !put(file.f, h_stage, n * block_bytes)) rc = VK_E_IO;
+    }
+    cudaFree(d_stage);
+    cudaFree(d_ids);
+    cudaFreeHost(h_stage);
+    if (err != cudaSuccess) return (int)err;
+    if (rc) return rc;
+  }
+  return fflush(file.f) == 0 ? 0 : VK_E_IO;
+}
+
+extern "C" int vk_volume_load(vkVolume* v, const char* path, void* stream) {
+  if (!v || !v->voxels || !path) return VK_E_INVALID;
+  cudaStream_t s = (cudaStream_t)stream;
+  File file;
+  file.f = fopen(path, "rb");
+  if (!file.f) return VK_E_IO;
+  SnapshotHeader h;
+  if (!get(file.f, &h, sizeof(h))) return VK_E_IO;
+  if (memcmp(h.magic, "VKVOL\0\0\1", 8) != 0 || h.version != kSnapshotVersion) return VK_E_IO;
+  if (h.main_blocks != v->main_blocks || h.excess_blocks != v->excess_blocks) return VK_E_INVALID;
+  const size_t M = (size_t)v->main_blocks, B = M + (size_t)v->excess_blocks;
+  if (h.stored_blocks < 0 || (size_t)h.stored_blocks > B) return VK_E_IO;
+
+  // pools back to their initial state (all voxels Empty), then the saved state on top
+  int rc = vk_volume_reset(v, stream);
+  if (rc) return rc;
+  v->voxel_length = h.voxel_length; v->trunc_length = h.trunc_length;
+  v->min_depth = h.min_depth; v->max_depth = h.max_depth;
+  v->shard_rank = h.shard_rank; v->shard_count = h.shard_count; v->shard_shift = h.shard_shift;
+  v->shard_halo = h.shard_halo;
+  v->visible_slot = h.visible_slot; v->view_id = h.view_id; v->math_mode = h.math_mode;
+  if ((rc = load_array(file.f, v->entries, B * sizeof(vkHashEntry), s))) return rc;
+  if ((rc = load_array(file.f, v->free_list, B * sizeof(int32_t), s))) return rc;
+  if ((rc = load_array(file.f, v->visibility, B, s))) return rc;
+  if ((rc = load_array(file.f, v->visible[0], B * sizeof(int32_t), s))) return rc;
+  if ((rc = load_array(file.f, v->visible[1], B * sizeof(int32_t), s))) return rc;
+  if ((rc = load_array(file.f, v->stamps, B * sizeof(int32_t), s))) return rc;
+  if ((rc = load_array(file.f, v->bucket_bits, (M + 31) / 32 * sizeof(uint32_t), s))) return rc;
+  if ((rc = load_array(file.f, v->space_bits, VK_SPACE_WORDS * sizeof(uint32_t), s))) return rc;
+  cudaError_t err = cudaMemcpyAsync(v->counters, h.counters, sizeof(h.counters), cudaMemcpyHostToDevice, s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return (int)err;
+  memcpy(v->host_counters, h.counters, VK_CNT_COUNT * sizeof(int32_t));
+
+  std::vector<int32_t> ids((size_t)h.stored_blocks);
+  if (!get(file.f, ids.data(), ids.size() * sizeof(int32_t))) return VK_E_IO;
+  for (int32_t id : ids)
+    if (id < 0 || (size_t)id >= B) return VK_E_IO;
+  const size_t block_bytes = VK_BLOCK_VOXELS * sizeof(vkVoxel);
+  const size_t chunk = ids.size() < kChunkBlocks ? ids.size() : kChunkBlocks;
+  if (chunk) {
+    uint4* d_stage = nullptr;
+    int32_t* d_ids = nullptr;
+    char* h_stage = nullptr;
+    err = cudaMalloc((void**)&d_stage, chunk * block_bytes);
+    if (err == cudaSuccess) err = cudaMalloc((void**)&d_ids, chunk * sizeof(int32_t));
+    if (err == cudaSuccess) err = cudaMallocHost((void**)&h_stage, chunk * block_bytes);
+    for (size_t at = 0; err == cudaSuccess && rc == 0 && at < ids.size(); at += chunk) {
+      const size_t n = (ids.size() - at < chunk) ? ids.size() - at : chunk;
+      if (!get(file.f, h_stage, n * block_bytes)) { rc = VK_E_IO; break; }
+      err = cudaMemcpyAsync(d_ids, ids.data() + at, n * sizeof(int32_t), cudaMemcpyHostToDevice, s);
+      if (err == cudaSuccess) err = cudaMemcpyAsync(d_stage, h_stage, n * block_bytes, cudaMemcpyHostToDevice, s);
+      if (err != cudaSuccess) break;
+      vk_move_blocks_kernel<<<sm_count() * 4, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), d_stage, d_ids, (int)n, 1);
+      VK_COUNT_LAUNCH();
+      err = cudaStreamSynchronize(s);
+    }
+    cudaFree(d_stage);
+    cudaFree(d_ids);
+    cudaFreeHost(h_stage);
+    if (err != cudaSuccess) return (int)err;
+    if (rc) return rc;
+  }
+  return 0;
+}

@@ -199,6 +199,19 @@ void Volume::Reset()
   RefreshViews();
 }
 
+void Volume::Save(const std::string& path) const
+{
+  VK_ASSERT(vk_volume_save(&volume_, path.c_str(), stream_));
+}
+
+void Volume::Load(const std::string& path)
+{
+  VK_ASSERT(vk_volume_load(&volume_, path.c_str(), stream_));
+  depth_range_ = Vector2f(volume_.min_depth, volume_.max_depth);
+  visible_blocks_.SetSize(0);  // refreshed from the device counters on the next GetVisibleBlocks()
+  RefreshViews();
+}
+
 void Volume::SetSharding(int rank, int count, int brick_shift, int halo)
 {
   VULCAN_ASSERT(count >= 1 && rank >= 0 && rank < count && brick_shift >= 0 && brick_shift < 15);
