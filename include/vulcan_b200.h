@@ -323,6 +323,12 @@ float* vk_exchange_color(void* buffer, int width, int height);
 float* vk_exchange_normal(void* buffer, int width, int height);
 int vk_exchange_bands(const vkExchange* x, int epoch, float* out_depth, float* out_color, float* out_normal,
                       void* stream);
+/* The ray-bounds grids of vk_trace_bounds combined the same way (instead of a MIN all-reduce):
+ * every rank stores its 80 x 60 x 2 grid into its slot of every rank's exchange buffer, announces
+ * it, waits for the others and leaves the element-wise minimum of all grids in `bounds`.  It is
+ * also the barrier that orders every rank's integration before any rank's peer reads.  `epoch`
+ * as for vk_exchange_bands (the two calls keep separate flags; use the same counter for both). */
+int vk_exchange_bounds(const vkExchange* x, int epoch, float* bounds, void* stream);
 
 /* Rank that owns block (bx, by, bz) when a volume is split over `count` ranks: a pure function
  * of the brick (bx >> shift, by >> shift, bz >> shift).  Host function; the kernels use the

@@ -62,10 +62,19 @@ def main():
             for img in images:
                 dist.all_gather_into_tensor(img, img[y0:y1])
 
+    import ctypes as C
+    from vulcan_b200 import _lib, api
+    x = tracer._ensure_exchange(Hh, W)
+
+    def bounds_exchange():
+        x["epoch"] += 1
+        api.check(_lib.lib.vk_exchange_bounds(C.byref(x["desc"]), x["epoch"], t.bounds_.data_ptr(), api._stream()), "xb")
+
     parts = [("bounds", lambda: t.TraceBounds(out)),
-             ("allreduce_38KB", lambda: dist.all_reduce(t.bounds_, op=dist.ReduceOp.MIN)),
+             ("allreduce_38KB_nccl", lambda: dist.all_reduce(t.bounds_, op=dist.ReduceOp.MIN)),
+             ("bounds_exchange_peer", bounds_exchange),
              ("rows", lambda: t.TraceRows(out, tracer.peers, y0, y1)),
-             ("gather_8.6MB", gather)]
+             ("gather_8.6MB_nccl", gather)]
     rep = {"world": world}
     for name, fn in parts:
         ts = []

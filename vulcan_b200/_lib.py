@@ -112,6 +112,7 @@ SYMBOLS = {
     "vk_exchange_color": [_P, _I, _I],
     "vk_exchange_normal": [_P, _I, _I],
     "vk_exchange_bands": [C.POINTER(vkExchange), _I, _P, _P, _P, _P],
+    "vk_exchange_bounds": [C.POINTER(vkExchange), _I, _P, _P],
     "vk_version": [],
     "vk_set_default_math_mode": [_I],
     "vk_get_default_math_mode": [],

@@ -17,10 +17,14 @@
 
 namespace vk {
 
-// buffer layout: [depth H*W][colour H*W*3][normal H*W*3] floats, then VK_MAX_SHARDS flags (int)
+// buffer layout: [depth H*W][colour H*W*3][normal H*W*3] floats, 64 ints (band flags, one per
+// rank), then VK_MAX_SHARDS ray-bounds grids (one slot per rank, 80 x 60 x 2 floats each) and 64
+// more ints (bounds flags)
+constexpr int kBoundsFloats = VK_BOUNDS_W * VK_BOUNDS_H * 2;
 __host__ __device__ inline size_t exchange_floats(int w, int h) { return (size_t)w * h * 7; }
 __host__ __device__ inline size_t exchange_bytes(int w, int h) {
-  return exchange_floats(w, h) * sizeof(float) + 64 * sizeof(int);
+  return exchange_floats(w, h) * sizeof(float) + 64 * sizeof(int) +
+         (size_t)VK_MAX_SHARDS * kBoundsFloats * sizeof(float) + 64 * sizeof(int);
 }
 
 struct ExchangeParams {
@@ -32,6 +36,13 @@ struct ExchangeParams {
 
 __device__ __forceinline__ int* exchange_flags(float* buffer, int w, int h) {
   return reinterpret_cast<int*>(buffer + exchange_floats(w, h));
+}
+
+__device__ __forceinline__ float* exchange_bounds_slot(float* buffer, int w, int h, int rank) {
+  return reinterpret_cast<float*>(exchange_flags(buffer, w, h) + 64) + (size_t)rank * kBoundsFloats;
+}
+__device__ __forceinline__ int* exchange_bounds_flags(float* buffer, int w, int h) {
+  return reinterpret_cast<int*>(exchange_bounds_slot(buffer, w, h, VK_MAX_SHARDS));
 }
 
 __device__ __forceinline__ int ld_acquire_sys(const int* p) {
@@ -86,9 +97,62 @@ __global__ void __launch_bounds__(256) vk_exchange_kernel(const ExchangeParams p
   }
 }
 
+// Ray-bounds grids: every rank stores its grid into its slot of every rank's buffer, announces
+// it, waits for the others and leaves the element-wise minimum of all grids in `bounds` (cells
+// are (min, -max), so the minimum combines both).  One CTA: the grid is 38 KB.  Like the NCCL
+// all-reduce it replaces, this is also the barrier that orders every rank's integration (earlier
+// in its stream) before any rank's peer reads (later in theirs).
+__global__ void __launch_bounds__(1024) vk_exchange_bounds_kernel(const ExchangeParams p, float* bounds) {
+  for (int r = 0; r < p.count; ++r) {
+    float* slot = exchange_bounds_slot(p.buffers[r], p.w, p.h, p.rank);
+    for (int i = threadIdx.x; i < kBoundsFloats; i += blockDim.x) slot[i] = bounds[i];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < p.count && threadIdx.x != p.rank)
+    st_release_sys(exchange_bounds_flags(p.buffers[threadIdx.x], p.w, p.h) + p.rank, p.epoch);
+  if (threadIdx.x < p.count && threadIdx.x != p.rank) {
+    const int* flag = exchange_bounds_flags(p.buffers[p.rank], p.w, p.h) + threadIdx.x;
+    while (ld_acquire_sys(flag) < p.epoch) __nanosleep(100);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kBoundsFloats; i += blockDim.x) {
+    float m = bounds[i];
+    for (int r = 0; r < p.count; ++r)
+      if (r != p.rank) m = fminf(m, __ldcg(exchange_bounds_slot(p.buffers[p.rank], p.w, p.h, r) + i));
+    bounds[i] = m;
+  }
+}
+
 }  // namespace vk
 
 using namespace vk;
+
+static int fill_exchange_params(ExchangeParams& p, const vkExchange* x, int epoch) {
+  if (!x || x->count < 1 || x->count > VK_MAX_SHARDS || x->rank < 0 || x->rank >= x->count || x->width <= 0 ||
+      x->height <= 0 || epoch <= 0)
+    return VK_E_INVALID;
+  p.count = x->count; p.rank = x->rank; p.w = x->width; p.h = x->height; p.epoch = epoch;
+  for (int r = 0; r < VK_MAX_SHARDS; ++r) {
+    p.buffers[r] = (r < x->count) ? static_cast<float*>(x->buffers[r]) : nullptr;
+    p.row_begin[r] = (r < x->count) ? x->row_begin[r] : 0;
+    p.row_end[r] = (r < x->count) ? x->row_end[r] : 0;
+    if (r < x->count && (!p.buffers[r] || p.row_begin[r] < 0 || p.row_end[r] > x->height || p.row_begin[r] > p.row_end[r]))
+      return VK_E_INVALID;
+  }
+  p.depth = p.color = p.normal = nullptr;
+  return 0;
+}
+
+extern "C" int vk_exchange_bounds(const vkExchange* x, int epoch, float* bounds, void* stream) {
+  ExchangeParams p;
+  const int rc = fill_exchange_params(p, x, epoch);
+  if (rc) return rc;
+  if (!bounds) return VK_E_INVALID;
+  vk_exchange_bounds_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(p, bounds);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
 
 extern "C" int vk_exchange_alloc(int width, int height, void** buffer) {
   if (width <= 0 || height <= 0 || !buffer) return VK_E_INVALID;
@@ -131,18 +195,10 @@ extern "C" float* vk_exchange_normal(void* buffer, int width, int height) {
 
 extern "C" int vk_exchange_bands(const vkExchange* x, int epoch, float* out_depth, float* out_color,
                                  float* out_normal, void* stream) {
-  if (!x || !out_depth || !out_color || x->count < 1 || x->count > VK_MAX_SHARDS || x->rank < 0 ||
-      x->rank >= x->count || x->width <= 0 || x->height <= 0 || epoch <= 0)
-    return VK_E_INVALID;
   ExchangeParams p;
-  p.count = x->count; p.rank = x->rank; p.w = x->width; p.h = x->height; p.epoch = epoch;
-  for (int r = 0; r < VK_MAX_SHARDS; ++r) {
-    p.buffers[r] = (r < x->count) ? static_cast<float*>(x->buffers[r]) : nullptr;
-    p.row_begin[r] = (r < x->count) ? x->row_begin[r] : 0;
-    p.row_end[r] = (r < x->count) ? x->row_end[r] : 0;
-    if (r < x->count && (!p.buffers[r] || p.row_begin[r] < 0 || p.row_end[r] > x->height || p.row_begin[r] > p.row_end[r]))
-      return VK_E_INVALID;
-  }
+  const int rc = fill_exchange_params(p, x, epoch);
+  if (rc) return rc;
+  if (!out_depth || !out_color) return VK_E_INVALID;
   p.depth = out_depth; p.color = out_color; p.normal = out_normal;
   // every CTA spins on the flags, so all of them must be resident at once: one per SM
   vk_exchange_kernel<<<sm_count(), 256, 0, (cudaStream_t)stream>>>(p);

@@ -111,6 +111,7 @@ class ShardedTracer:
         import torch.distributed as dist
         from . import _lib, api
         self.volume, self.group = volume, group
+        self.use_nccl_bounds = False   # True: combine the ray-bounds grids with an NCCL all-reduce instead
         self.tracer = api.Tracer(volume)
         self.rank, self.count = dist.get_rank(group), dist.get_world_size(group)
         assert volume._v.shard_rank == self.rank and volume._v.shard_count == self.count, "call Volume.SetSharding first"
@@ -188,9 +189,10 @@ class ShardedTracer:
 
     def Trace(self, frame):
         """Fills frame.depth_image / color_image / normal_image on every rank (all bands gathered).
-        Per view: one NCCL MIN all-reduce of the ray-bounds grid (38 KB; also the barrier between
-        every rank's integration and any rank's peer reads), the band of this rank rendered into
-        its exchange buffer, and one kernel that swaps the bands over peer memory."""
+        Per view: the ray-bounds grids (38 KB) combined over peer memory (vk_exchange_bounds; also the
+        barrier between every rank's integration and any rank's peer reads), the band of this rank
+        rendered into its exchange buffer, and one kernel that swaps the bands over peer memory.
+        No library collective on the per-frame path."""
         import ctypes as C
         import torch.distributed as dist
         from . import _lib, api
@@ -199,14 +201,18 @@ class ShardedTracer:
         h, w = frame.depth_image.shape
         x = self._ensure_exchange(h, w)
         t.TraceBounds(frame)
-        # cells are (min depth, -max depth): ONE min all-reduce combines both
-        dist.all_reduce(t.bounds_, op=dist.ReduceOp.MIN, group=self.group)
+        x["epoch"] += 1
+        # cells are (min depth, -max depth): ONE element-wise minimum over the ranks combines both
+        if self.use_nccl_bounds:
+            dist.all_reduce(t.bounds_, op=dist.ReduceOp.MIN, group=self.group)
+        else:
+            api.check(_lib.lib.vk_exchange_bounds(C.byref(x["desc"]), x["epoch"], t.bounds_.data_ptr(), api._stream()),
+                      "vk_exchange_bounds")
         y0, y1 = row_band(h, self.rank, self.count)
         f = frame.to_c()
         v = self.volume
         api.check(_lib.lib.vk_trace_rows(C.byref(v._v), C.byref(self.peers), C.byref(f), t.bounds_.data_ptr(), y0, y1,
                                          x["depth"], x["color"], x["normal"], api._stream()), "TraceRows")
-        x["epoch"] += 1
         api.check(_lib.lib.vk_exchange_bands(C.byref(x["desc"]), x["epoch"], frame.depth_image.data_ptr(),
                                              frame.color_image.data_ptr(), frame.normal_image.data_ptr(),
                                              api._stream()), "vk_exchange_bands")
