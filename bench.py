@@ -509,6 +509,7 @@ def main():
                     help="frames in flight in the end-to-end leg (FramePipeline); the host takes frame k-depth+1")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    sys.setswitchinterval(2e-4)  # lets the clock-sampling thread run while the main thread issues launches
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
 
