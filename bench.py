@@ -249,8 +249,8 @@ def run_ours(args, rank, world):
         roof = {"bound": "hbm", "kernel": "vk_integrate_kernel<MODE_DEPTH>", "achieved": gbs,
                 "peak": peaks["hbm_gbs"], "peak_source": which, "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel in the committed
-                # `ncu --set full` capture of this command (profiles/r01_ncu_full_summary.csv: 106.59 + 42.79 MB)
-                "traffic": 149.38e6, "traffic_source": "profiles/r01_ncu_full_summary.csv",
+                # `ncu --set full` capture of this command (profiles/r01_ncu_full_summary.csv: 106.57 + 41.81 MB)
+                "traffic": 148.38e6, "traffic_source": "profiles/r01_ncu_full_summary.csv",
                 "algorithmic_bytes_per_launch": ab / args.steps,
                 "updated_voxels_per_launch": updated_timed / args.steps,
                 "launch_ms": int_ms / args.steps}
