@@ -480,7 +480,8 @@ enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
 // `batch_lanes` are parked, when nobody else can advance, or after `batch_wait` trips - so the
 // expensive instructions run with most lanes active instead of 7-9 of 32.  The order of
 // operations of each ray is unchanged, so the result is bit-identical to the per-ray loop.
-template <bool F, bool KEYS, bool PEERS>
+// DIAG: per-warp timeline / trip counters for tools/tune_bench.py (compiled out of the product kernels)
+template <bool F, bool KEYS, bool PEERS, bool DIAG>
 __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const TraceParams p) {
   pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
   pdl_trigger();  // the next one may be scheduled as this grid drains
@@ -490,9 +491,10 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   const int x = blockIdx.x * 8 + (lane & 7);
   const int y = p.y_begin + (blockIdx.y * wpc + warp) * 4 + (lane >> 3);
   const bool inside = (x < p.w && y < p.y_end);
+  unsigned long long* const timeline = DIAG ? p.timeline : nullptr;
   unsigned long long t_start = 0;
-  if (p.timeline) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-  const long long c_start = clock64();
+  if (timeline) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+  const long long c_start = DIAG ? clock64() : 0;
   int dbg_trips = 0;
   long long c_free = 0, c_a = 0, c_b = 0, c_t = 0;
   int dbg_steps = 0, dbg_rounds = 0;
@@ -588,7 +590,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
 
   while (__any_sync(0xffffffffu, state != ST_DONE)) {
     ++dbg_trips;
-    if (p.timeline) c_t = clock64();
+    if (timeline) c_t = clock64();
     // ---- phase A: block under p, nearest voxel ---------------------------------------------
     int bx = 0, by = 0, bz = 0;
     if (state != ST_DONE && !parked) {
@@ -671,7 +673,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         }
       }
     }
-    if (p.timeline) { const long long c = clock64(); c_free += c - c_t; c_t = c; }
+    if (timeline) { const long long c = clock64(); c_free += c - c_t; c_t = c; }
     if (state != ST_DONE && !parked) {
       const int data = find_data<PEERS>(p, cache, bx, by, bz);
       if (data != -1) {
@@ -704,7 +706,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       }
     }
     // ---- phase B: interpolation for the parked lanes, batched ------------------------------
-    if (p.timeline) { const long long c = clock64(); c_a += c - c_t; c_t = c; }
+    if (timeline) { const long long c = clock64(); c_a += c - c_t; c_t = c; }
     const unsigned pm = __ballot_sync(0xffffffffu, parked);
     if (pm) {
       const unsigned fm = __ballot_sync(0xffffffffu, state != ST_DONE && !parked);
@@ -723,27 +725,27 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         ++waited;
       }
     }
-    if (p.timeline) { const long long c = clock64(); c_b += c - c_t; c_t = c; }
+    if (timeline) { const long long c = clock64(); c_b += c - c_t; c_t = c; }
   }
 
-  if (p.timeline) {
+  if (timeline) {
     dbg_steps = __reduce_max_sync(0xffffffffu, dbg_steps);
     dbg_rounds = __reduce_max_sync(0xffffffffu, dbg_rounds);
   }
-  if (p.timeline && lane == 0) {
+  if (timeline && lane == 0) {
     unsigned long long t_end;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
     const size_t wid = ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * wpc + warp;
     unsigned smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    p.timeline[8 * wid] = t_start;
-    p.timeline[8 * wid + 1] = t_end;
-    p.timeline[8 * wid + 2] = ((unsigned long long)smid << 32) | (unsigned)dbg_trips;
-    p.timeline[8 * wid + 3] = (unsigned long long)(clock64() - c_start);
-    p.timeline[8 * wid + 4] = (unsigned long long)c_free;
-    p.timeline[8 * wid + 5] = (unsigned long long)c_a;
-    p.timeline[8 * wid + 6] = (unsigned long long)c_b;
-    p.timeline[8 * wid + 7] = ((unsigned long long)dbg_rounds << 32) | (unsigned)dbg_steps;
+    timeline[8 * wid] = t_start;
+    timeline[8 * wid + 1] = t_end;
+    timeline[8 * wid + 2] = ((unsigned long long)smid << 32) | (unsigned)dbg_trips;
+    timeline[8 * wid + 3] = (unsigned long long)(clock64() - c_start);
+    timeline[8 * wid + 4] = (unsigned long long)c_free;
+    timeline[8 * wid + 5] = (unsigned long long)c_a;
+    timeline[8 * wid + 6] = (unsigned long long)c_b;
+    timeline[8 * wid + 7] = ((unsigned long long)dbg_rounds << 32) | (unsigned)dbg_steps;
   }
   if (!inside) return;
   // colour of the last interpolation (Q13: kept even on a miss), evaluated once per ray
@@ -1057,11 +1059,14 @@ static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
   if (t.y_end <= t.y_begin) return 0;
   dim3 grid((t.w + 7) / 8, (t.y_end - t.y_begin + rows - 1) / rows);
   if (!KEYS && t.peer_count > 1) {  // sharded volume: lookups may go to the owner's tables
-    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, false, true>, grid, dim3(threads), 0, s, t);
-    else launch_chained(vk_raycast_kernel<true, false, true>, grid, dim3(threads), 0, s, t);
+    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, false, true, false>, grid, dim3(threads), 0, s, t);
+    else launch_chained(vk_raycast_kernel<true, false, true, false>, grid, dim3(threads), 0, s, t);
+  } else if (!KEYS && t.timeline) {  // diagnostics build of the plain kernel
+    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, false, false, true>, grid, dim3(threads), 0, s, t);
+    else launch_chained(vk_raycast_kernel<true, false, false, true>, grid, dim3(threads), 0, s, t);
   } else {
-    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, KEYS, false>, grid, dim3(threads), 0, s, t);
-    else launch_chained(vk_raycast_kernel<true, KEYS, false>, grid, dim3(threads), 0, s, t);
+    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, KEYS, false, false>, grid, dim3(threads), 0, s, t);
+    else launch_chained(vk_raycast_kernel<true, KEYS, false, false>, grid, dim3(threads), 0, s, t);
   }
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
