@@ -142,9 +142,10 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // updated in registers and its changed chunks are stored.  The entry of block i+2 is in flight
 // meanwhile.  One iteration costs max(tile latency, gather latency) instead of their sum.
 // resident CTAs per SM the register allocation is held to (measured on B200: the depth kernel
-// lands at 55 registers = 9 CTAs/SM; forcing 10 CTAs spills and is slower)
+// lands at 55 registers = 9 CTAs/SM; forcing 10 CTAs spills and is slower; colour 70 registers / 7 CTAs;
+// light 80 registers / 6 CTAs with 72 bytes of spills, 7 % faster than 110 registers / 4 CTAs)
 template <int MODE>
-constexpr int integrate_min_ctas() { return MODE == MODE_DEPTH ? 8 : (MODE == MODE_COLOR ? 6 : 4); }
+constexpr int integrate_min_ctas() { return MODE == MODE_DEPTH ? 8 : (MODE == MODE_COLOR ? 7 : 6); }
 
 template <int MODE, bool F>
 __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_kernel(const IntegrateParams p) {
