@@ -248,6 +248,7 @@ def run_ours(args, rank, world):
         gbs = ab / (int_ms * 1e-3) / 1e9
         roof = {"bound": "hbm", "kernel": "vk_integrate_kernel<MODE_DEPTH>", "achieved": gbs,
                 "peak": peaks["hbm_gbs"], "peak_source": which, "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                "frac_of_spec_8000": gbs / 8000.0,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel in the committed
                 # `ncu --set full` capture of this command (profiles/r01_ncu_full_summary.csv: 106.57 + 41.81 MB)
                 "traffic": 148.38e6, "traffic_source": "profiles/r01_ncu_full_summary.csv",
@@ -478,6 +479,7 @@ def cpu_baseline(sample_frames=6):
     ov = Hh.OracleVolume(MAIN, EXCESS, VOXEL, TRUNC)
     units = 0
     t_int = t_trc = t_set = 0.0
+    ray_bytes = []
     for depth, T in frames:
         t0 = time.perf_counter()
         ov.set_view_converged(depth, K, T)
@@ -486,6 +488,9 @@ def cpu_baseline(sample_frames=6):
         t2 = time.perf_counter()
         ov.trace(W, H, K, T)
         t3 = time.perf_counter()
+        vox, ent = ov.lib.vo_voxel_fetches(ov.h), ov.lib.vo_entry_fetches(ov.h)
+        # requested bytes of the reference algorithm for one traced view
+        ray_bytes.append(32.0 * W * H + 8.0 * W * H + 20.0 * vox + 16.0 * ent)
         units += len(ov.visible()) * 512
         t_set += t1 - t0
         t_int += t2 - t1
@@ -495,7 +500,8 @@ def cpu_baseline(sample_frames=6):
             "sample": "first %d frames of the same orbit through oracle/vulcan_oracle.cpp (OpenMP, %d threads; "
                       "allocation sequential)" % (sample_frames, threads),
             "ms_per_step": tot * 1e3 / sample_frames,
-            "integrate_voxel_updates_per_s": units / t_int, "trace_rays_per_s": W * H * sample_frames / t_trc}
+            "integrate_voxel_updates_per_s": units / t_int, "trace_rays_per_s": W * H * sample_frames / t_trc,
+            "trace_algorithmic_bytes_per_view": float(ray_bytes[-1])}
 
 
 def main():
@@ -531,6 +537,13 @@ def main():
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
+            # ray cast: requested bytes of the reference algorithm (counted by the oracle on frame 5 of the same
+            # orbit) over our Trace time - a latency-bound gather kernel, given for completeness
+            rb = line["cpu_baseline"]["trace_algorithmic_bytes_per_view"]
+            peaks, _ = load_peaks()
+            gbs = rb / (line["phases"]["trace_ms"] * 1e-3) / 1e9
+            line["phases"]["trace_algorithmic_gbs"] = gbs
+            line["phases"]["trace_frac_of_hbm_peak"] = gbs / peaks["hbm_gbs"]
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as dist
