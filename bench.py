@@ -250,8 +250,8 @@ def run_ours(args, rank, world):
                 "peak": peaks["hbm_gbs"], "peak_source": which, "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
                 "frac_of_spec_8000": gbs / 8000.0,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel in the committed
-                # `ncu --set full` capture of this command (profiles/r01_ncu_full_summary.csv: 106.57 + 41.81 MB)
-                "traffic": 148.38e6, "traffic_source": "profiles/r01_ncu_full_summary.csv",
+                # `ncu --set full` capture of this command (profiles/r01_ncu_full_summary.csv: 106.58 + 42.01 MB)
+                "traffic": 148.60e6, "traffic_source": "profiles/r01_ncu_full_summary.csv",
                 "algorithmic_bytes_per_launch": ab / args.steps,
                 "updated_voxels_per_launch": updated_timed / args.steps,
                 "launch_ms": int_ms / args.steps}
