@@ -219,6 +219,9 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
     if (leader) {
       last_key = key;
       const uint32_t h = block_hash(bx, by, bz, p.K);
+      // most blocks sit at the head of their bucket, whose index is known before the entry
+      // arrives: its stamp is fetched together with the entry instead of after it
+      const int head_stamp = __ldcg(p.stamps + h);
       int tail;
       bool head_empty;
       int idx = find_block(p.entries, h, key, tail, head_empty);
@@ -226,7 +229,7 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
         if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) idx = insert_block(p, h, bx, by, bz, key);
         else mark_space(p, bx, by, bz);  // exists on another rank: the filter is global
       }
-      if (idx >= 0) touch_entry(p, idx);
+      if (idx >= 0 && !(idx == (int)h && head_stamp == p.view_id)) touch_entry(p, idx);
     }
     if (active) {
       // Amanatides-Woo step with the reference's comparison tree (src/volume.cu:241-295)
