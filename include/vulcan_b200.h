@@ -337,6 +337,41 @@ int vk_exchange_bounds(const vkExchange* x, int epoch, float* bounds, void* stre
  * leaves the shard; only owned hits enter the merge keys. */
 int vk_shard_owner(int bx, int by, int bz, int shift, int count);
 
+/* ---- image pyramid + depth tracker (the caller side of Tracer::Trace) ---- */
+
+#define VK_TRACK_STATE_FLOATS 80  /* solver state at the head of a tracker workspace */
+
+/* Frame::Downsample (src/frame.cpp:38-57; kernels src/image.cu:101-165,183-274) in one launch:
+ * depth and normals by nearest sample, colour by 2x2 average, into the device buffers dst already
+ * points to (dst->depth / color / normal are written through although vkFrame declares them
+ * const); sizes, halved intrinsics and the transforms are filled in.  Images that are NULL in src
+ * are skipped.  Odd image sizes -> VK_E_INVALID ("even image dimensions required"). */
+int vk_downsample_frame(const vkFrame* src, vkFrame* dst, void* stream);
+/* Image::Downsample / ColorImage::Downsample (src/image.cu:183-274): channels 1 or 3 */
+int vk_downsample_image(const float* src, int src_w, int src_h, int channels, int nearest, float* dst,
+                        void* stream);
+
+/* DepthTracker::ComputeResiduals / ComputeJacobian (src/depth_tracker.cu:279-344): one float /
+ * six floats per frame pixel (Jacobian columns 3..5 are 0 with translation disabled). */
+int vk_track_residuals(const vkFrame* keyframe, const vkFrame* frame, float* residuals, void* stream);
+int vk_track_jacobian(const vkFrame* keyframe, const vkFrame* frame, int translation_enabled,
+                      float* jacobian, void* stream);
+/* floats a tracker workspace (device memory) needs on the current device */
+int vk_track_workspace_floats(void);
+/* DepthTracker::ComputeSystem (src/depth_tracker.cu:346-378): packed lower triangle of J^T J
+ * (21 or 6 floats, row r column c <= r at r(r+1)/2+c) and J^T r (6 or 3 floats), device buffers.
+ * Sums are deterministic (fixed order), unlike the reference's atomicAdd of CTA sums. */
+int vk_track_system(const vkFrame* keyframe, const vkFrame* frame, int translation_enabled,
+                    float* workspace, float* hessian, float* gradient, void* stream);
+/* Tracker::Track (src/tracker.cpp:57-67) for the DepthTracker: up to max_iterations Gauss-Newton
+ * steps, each ONE kernel that evaluates the system, solves it and applies
+ * DepthTracker::ApplyUpdate (src/depth_tracker.cpp:23-88) to the pose in device memory; stops
+ * like Tracker::ComputeUpdate when |update| < 1e-6 (src/tracker.cpp:152).  On return (the call
+ * waits for the stream) frame->depth_to_world holds the tracked pose; *iterations = systems
+ * solved. */
+int vk_track_depth(const vkFrame* keyframe, vkFrame* frame, int translation_enabled, int max_iterations,
+                   float* workspace, int* iterations, float* last_update_norm, void* stream);
+
 /* ---- misc -------------------------------------------------------------------- */
 
 /* Library version and the number of kernels launched by this library since load

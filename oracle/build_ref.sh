@@ -5,7 +5,7 @@
 #   libvulcan_ref_nofmad.so  same with -fmad=false             (contraction-free parity target)
 # Only nvcc on the few source files; the reference's CMake build is not run (needs
 # OpenCV / Eigen / HAL / gflags / glog, all absent).  OpenCV is replaced by
-# oracle/ref_stub/opencv2/opencv.hpp; `-include cfloat` supplies FLT_MAX for
+# oracle/ref_stub/opencv2/opencv.hpp, the few Eigen types of the tracker by oracle/ref_stub/Eigen/Eigen; `-include cfloat` supplies FLT_MAX for
 # src/light_integrator.cu:79-80.
 set -e
 HERE="$(cd "$(dirname "$0")" && pwd)"
@@ -13,11 +13,11 @@ REF="${VULCAN_REFERENCE:-/root/reference}"
 OUT="$HERE/_ref"
 if [ ! -d "$REF/src" ]; then echo "build_ref.sh: $REF not present, keeping prebuilt $OUT"; exit 0; fi
 mkdir -p "$OUT"
-SRCS="volume.cu integrator.cu depth_integrator.cu color_integrator.cu light_integrator.cu tracer.cu tracer.cpp frame.cu frame.cpp image.cu"
+SRCS="volume.cu integrator.cu depth_integrator.cu color_integrator.cu light_integrator.cu tracer.cu tracer.cpp frame.cu frame.cpp image.cu tracker.cpp depth_tracker.cpp depth_tracker.cu"
 FILES=""
 for s in $SRCS; do FILES="$FILES $REF/src/$s"; done
 COMMON="-std=c++17 -gencode arch=compute_100a,code=sm_100a -O3 -DNDEBUG -lineinfo -include cfloat -x cu -w \
-  -I$HERE/ref_stub -I$REF/include -Xcompiler -fPIC -Xlinker -Bsymbolic -shared"
+  -I$HERE/ref_stub -I$REF/include -Xcompiler -fPIC -Xlinker -Bsymbolic -shared -lcublas"
 nvcc $COMMON -o "$OUT/libvulcan_ref.so" $FILES "$HERE/ref_shim.cu" &
 nvcc $COMMON -fmad=false -o "$OUT/libvulcan_ref_nofmad.so" $FILES "$HERE/ref_shim.cu" &
 wait

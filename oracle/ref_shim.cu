@@ -17,6 +17,7 @@
 #include <vulcan/light_integrator.h>
 #include <vulcan/light.h>
 #include <vulcan/tracer.h>
+#include <vulcan/depth_tracker.h>
 #include <cstring>
 #include <memory>
 
@@ -220,6 +221,159 @@ int ref_visible_count(void* h) { return (int)((Ref*)h)->volume->GetVisibleBlocks
 
 int ref_download(void* dst, const void* src_dev, size_t bytes) {
   return (int)cudaMemcpy(dst, src_dev, bytes, cudaMemcpyDeviceToHost);
+}
+
+
+// ---- image pyramid + DepthTracker (src/frame.cpp:38-57, src/tracker.cpp, src/depth_tracker.{cpp,cu}) ----
+
+namespace {
+struct OpenDepthTracker : public DepthTracker {
+  void system(const Frame& f) {
+    BeginSolve(f);  // ResizeBuffers (src/tracker.cpp:75-81)
+    ComputeSystem(f);
+  }
+  const float* hessian() const { return hessian_.GetData(); }
+  const float* gradient() const { return gradient_.GetData(); }
+  int iteration() const { return iteration_; }
+};
+struct RefTrack {
+  OpenDepthTracker tracker;
+  std::shared_ptr<Frame> frames[2];  // 0 keyframe, 1 frame
+  Frame half, quarter;               // last ref_track_downsample results
+};
+void upload_frame(Frame& f, const float* depth, const float* normal, const float* color, int w, int h,
+                  const float* dproj, const float* Twd) {
+  if (!f.depth_image) f.depth_image = std::make_shared<Image>();
+  if (!f.normal_image) f.normal_image = std::make_shared<ColorImage>();
+  if (!f.color_image) f.color_image = std::make_shared<ColorImage>();
+  f.depth_image->Resize(w, h);
+  f.normal_image->Resize(w, h);
+  f.color_image->Resize(w, h);
+  cudaMemcpy(f.depth_image->GetData(), depth, sizeof(float) * w * h, cudaMemcpyHostToDevice);
+  cudaMemcpy(f.normal_image->GetData(), normal, sizeof(float) * 3 * w * h, cudaMemcpyHostToDevice);
+  if (color) cudaMemcpy(f.color_image->GetData(), color, sizeof(float) * 3 * w * h, cudaMemcpyHostToDevice);
+  else cudaMemset(f.color_image->GetData(), 0, sizeof(float) * 3 * w * h);
+  set_pose(f, dproj, dproj, Twd, nullptr);
+}
+void get_pose(const Frame& f, float* out32) {
+  std::memcpy(out32, &f.depth_to_world_transform.GetMatrix(), 64);
+  std::memcpy(out32 + 16, &f.depth_to_world_transform.GetInverseMatrix(), 64);
+}
+}  // namespace
+
+void* ref_track_create() {
+  try {
+    RefTrack* t = new RefTrack();
+    t->frames[0] = std::make_shared<Frame>();
+    t->frames[1] = std::make_shared<Frame>();
+    return t;
+  } catch (...) { return nullptr; }
+}
+void ref_track_destroy(void* h) { delete (RefTrack*)h; }
+
+// which: 0 keyframe, 1 frame; host images of one size; colour may be NULL (zeros)
+int ref_track_set_frame(void* h, int which, const float* depth, const float* normal, const float* color, int w,
+                        int hgt, const float* dproj, const float* Twd) {
+  RefTrack* t = (RefTrack*)h;
+  try {
+    upload_frame(*t->frames[which], depth, normal, color, w, hgt, dproj, Twd);
+    t->tracker.SetKeyframe(t->frames[0]);
+    return (int)cudaGetLastError();
+  } catch (...) { return -1; }
+}
+
+int ref_track_residuals(void* h, float* out_host) {
+  RefTrack* t = (RefTrack*)h;
+  try {
+    Buffer<float> r;
+    t->tracker.ComputeResiduals(*t->frames[1], r);
+    return (int)cudaMemcpy(out_host, r.GetData(), sizeof(float) * r.GetSize(), cudaMemcpyDeviceToHost);
+  } catch (...) { return -1; }
+}
+
+int ref_track_jacobian(void* h, int translation, float* out_host) {
+  RefTrack* t = (RefTrack*)h;
+  try {
+    Buffer<Vector6f> j;
+    t->tracker.SetTranslationEnabled(translation != 0);
+    t->tracker.ComputeJacobian(*t->frames[1], j);
+    return (int)cudaMemcpy(out_host, j.GetData(), sizeof(float) * 6 * j.GetSize(), cudaMemcpyDeviceToHost);
+  } catch (...) { return -1; }
+}
+
+// packed lower triangle (21 or 6) and gradient (6 or 3) as the reference's kernel leaves them
+int ref_track_system(void* h, int translation, float* hessian_host, float* gradient_host) {
+  RefTrack* t = (RefTrack*)h;
+  try {
+    t->tracker.SetTranslationEnabled(translation != 0);
+    t->tracker.system(*t->frames[1]);
+    cudaMemcpy(hessian_host, t->tracker.hessian(), sizeof(float) * (translation ? 21 : 6), cudaMemcpyDeviceToHost);
+    return (int)cudaMemcpy(gradient_host, t->tracker.gradient(), sizeof(float) * (translation ? 6 : 3),
+                           cudaMemcpyDeviceToHost);
+  } catch (...) { return -1; }
+}
+
+// Tracker::Track on the frame; pose_out = matrix + inverse (32 floats)
+int ref_track(void* h, int translation, int max_iterations, float* pose_out) {
+  RefTrack* t = (RefTrack*)h;
+  try {
+    t->tracker.SetTranslationEnabled(translation != 0);
+    t->tracker.SetMaxIterations(max_iterations);
+    t->tracker.SetKeyframe(t->frames[0]);
+    t->tracker.Track(*t->frames[1]);
+    cudaDeviceSynchronize();
+    get_pose(*t->frames[1], pose_out);
+    return (int)cudaGetLastError();
+  } catch (...) { return -1; }
+}
+
+// Frame::Downsample of frame `which` (twice: half and quarter); level 1 = half, 2 = quarter copied to host.
+// proj_out = depth fx fy cx cy
+int ref_track_downsample(void* h, int which, int level, float* depth_out, float* color_out, float* normal_out,
+                         float* proj_out) {
+  RefTrack* t = (RefTrack*)h;
+  try {
+    t->frames[which]->Downsample(t->half);
+    t->half.Downsample(t->quarter);
+    const Frame& f = level == 1 ? t->half : t->quarter;
+    const size_t n = (size_t)f.depth_image->GetWidth() * f.depth_image->GetHeight();
+    cudaMemcpy(depth_out, f.depth_image->GetData(), 4 * n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(color_out, f.color_image->GetData(), 12 * n, cudaMemcpyDeviceToHost);
+    cudaMemcpy(normal_out, f.normal_image->GetData(), 12 * n, cudaMemcpyDeviceToHost);
+    proj_out[0] = f.depth_projection.GetFocalLength()[0];
+    proj_out[1] = f.depth_projection.GetFocalLength()[1];
+    proj_out[2] = f.depth_projection.GetCenterPoint()[0];
+    proj_out[3] = f.depth_projection.GetCenterPoint()[1];
+    return (int)cudaGetLastError();
+  } catch (...) { return -1; }
+}
+
+// The live part of PyramidTracker<DepthTracker>::Track (src/pyramid_tracker.cpp:52-90), whose own source
+// file cannot be compiled here (it instantiates the colour and light trackers): both pyramids, 15
+// iterations at half size, 20 at full size.
+int ref_track_pyramid(void* h, float* pose_out) {
+  RefTrack* t = (RefTrack*)h;
+  try {
+    Frame half_frame, quarter_frame;
+    auto half_key = std::make_shared<Frame>();
+    auto quarter_key = std::make_shared<Frame>();
+    t->frames[1]->Downsample(half_frame);
+    half_frame.Downsample(quarter_frame);
+    t->frames[0]->Downsample(*half_key);
+    half_key->Downsample(*quarter_key);
+    t->tracker.SetMaxIterations(15);
+    t->tracker.SetTranslationEnabled(true);
+    half_frame.depth_to_world_transform = quarter_frame.depth_to_world_transform;
+    t->tracker.SetKeyframe(half_key);
+    t->tracker.Track(half_frame);
+    t->tracker.SetMaxIterations(20);
+    t->frames[1]->depth_to_world_transform = half_frame.depth_to_world_transform;
+    t->tracker.SetKeyframe(t->frames[0]);
+    t->tracker.Track(*t->frames[1]);
+    cudaDeviceSynchronize();
+    get_pose(*t->frames[1], pose_out);
+    return (int)cudaGetLastError();
+  } catch (...) { return -1; }
 }
 
 }  // extern "C"

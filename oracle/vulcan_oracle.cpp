@@ -949,3 +949,207 @@ void vo_trace(void* h, const float* T, const float* proj4, int w, int hgt, float
 }
 
 }  // extern "C"
+
+// ---- image pyramid + DepthTracker ----------------------------------------
+
+namespace {
+
+// Evaluate<>, src/depth_tracker.cu:16-99.  Returns false when the pixel contributes nothing.
+// Twc, Twm, Tmw: column-major 4x4 (frame pose, keyframe pose, keyframe pose inverse).
+bool track_evaluate(const float* Twc, const float* Twm, const float* Tmw, const float* key_depth,
+                    const float* key_normal, const Proj& kP, int kw, int kh, const float* depth, const float* normal,
+                    const Proj& P, int w, int x, int y, float& residual, float* J) {
+  const int index = y * w + x;
+  const float d = depth[index];
+  if (!(d > 0)) return false;
+  const V3 Xc = scale(unproject(P, x + 0.5f, y + 0.5f), d);           // :38-40
+  const V3 Xw = xform(Twc, Xc.x, Xc.y, Xc.z, 1.0f);                    // :41
+  const V3 Xm = xform(Tmw, Xw.x, Xw.y, Xw.z, 1.0f);                    // :42
+  float ku, kv;
+  project(kP, Xm, ku, kv);                                            // :43
+  if (!(ku >= 0 && ku < kw && kv >= 0 && kv < kh)) return false;      // :45-46
+  const int kindex = (int)kv * kw + (int)ku;                          // :48-50
+  const float kd = key_depth[kindex];
+  if (!(kd > 0)) return false;                                        // :53
+  const V3 fn = xform(Twc, normal[3 * index], normal[3 * index + 1], normal[3 * index + 2], 0.0f);             // :55-56
+  const V3 kn = xform(Twm, key_normal[3 * kindex], key_normal[3 * kindex + 1], key_normal[3 * kindex + 2], 0.0f);  // :58-59
+  if (!(dot(kn, kn) > 0.0f && dot(fn, kn) > 0.5f)) return false;      // :61-62
+  const V3 Ym = scale(unproject(kP, std::floor(ku) + 0.5f, std::floor(kv) + 0.5f), kd);  // :64-67
+  const V3 Yw = xform(Twm, Ym.x, Ym.y, Ym.z, 1.0f);                    // :68
+  const V3 delta = minus(Xw, Yw);
+  if (!(dot(delta, delta) < 0.05f)) return false;                     // :71
+  residual = dot(delta, kn);                                          // :73
+  J[0] = msub(kn.z, Xw.y, kn.y * Xw.z);                                // :77-79
+  J[1] = msub(kn.x, Xw.z, kn.z * Xw.x);
+  J[2] = msub(kn.y, Xw.x, kn.x * Xw.y);
+  J[3] = kn.x; J[4] = kn.y; J[5] = kn.z;                               // :83-85
+  return true;
+}
+
+// 4x4 column-major product, include/vulcan/matrix.h:299-317
+void mat4_mul(const float* A, const float* B, float* out) {
+  float r[16];
+  for (int p = 0; p < 4; ++p)
+    for (int m = 0; m < 4; ++m) {
+      float acc = 0;
+      for (int n = 0; n < 4; ++n) acc += A[n * 4 + m] * B[p * 4 + n];
+      r[p * 4 + m] = acc;
+    }
+  std::memcpy(out, r, sizeof(r));
+}
+
+// H x = -g by LDL^T in double; H packed lower triangle (src/depth_tracker.cu:214-223,
+// src/tracker.cpp:133-147 solve it with Eigen::LDLT<float>, absent here)
+void track_solve(const double* packed, const double* g, int n, float* x) {
+  double L[6][6], D[6], y[6];
+  for (int r = 0; r < n; ++r)
+    for (int c = 0; c <= r; ++c) L[r][c] = packed[r * (r + 1) / 2 + c];
+  for (int j = 0; j < n; ++j) {
+    double d = L[j][j];
+    for (int k = 0; k < j; ++k) d -= L[j][k] * L[j][k] * D[k];
+    D[j] = d;
+    const double inv = std::fabs(d) > 1e-30 ? 1.0 / d : 0.0;
+    for (int i = j + 1; i < n; ++i) {
+      double s = L[i][j];
+      for (int k = 0; k < j; ++k) s -= L[i][k] * L[j][k] * D[k];
+      L[i][j] = s * inv;
+    }
+  }
+  for (int i = 0; i < n; ++i) {
+    double s = -g[i];
+    for (int k = 0; k < i; ++k) s -= L[i][k] * y[k];
+    y[i] = s;
+  }
+  for (int i = 0; i < n; ++i) y[i] = std::fabs(D[i]) > 1e-30 ? y[i] / D[i] : 0.0;
+  for (int i = n - 1; i >= 0; --i) {
+    double s = y[i];
+    for (int k = i + 1; k < n; ++k) s -= L[k][i] * y[k];
+    y[i] = s;
+  }
+  for (int i = 0; i < 6; ++i) x[i] = i < n ? (float)y[i] : 0.0f;
+}
+
+// DepthTracker::ApplyUpdate, src/depth_tracker.cpp:23-88.  T = matrix + inverse (32 floats).
+void track_apply_update(const float* u, float* T) {
+  float Tinc[16];
+  for (int i = 0; i < 16; ++i) Tinc[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+#define AT(m, r, c) (m)[(c) * 4 + (r)]
+  AT(Tinc, 0, 1) = -u[2]; AT(Tinc, 0, 2) = +u[1]; AT(Tinc, 0, 3) = +u[3];
+  AT(Tinc, 1, 0) = +u[2]; AT(Tinc, 1, 2) = +u[0]; AT(Tinc, 1, 3) = +u[4];   // :38-41 (the sign of (1,2) is the reference's)
+  AT(Tinc, 2, 0) = -u[1]; AT(Tinc, 2, 1) = +u[0]; AT(Tinc, 2, 3) = +u[5];
+  float Mx[16];
+  mat4_mul(Tinc, T, Mx);                                                    // :53
+  V3 X = {AT(Mx, 0, 0), AT(Mx, 1, 0), AT(Mx, 2, 0)};
+  V3 Y = {AT(Mx, 0, 1), AT(Mx, 1, 1), AT(Mx, 2, 1)};
+  auto plain_dot = [](const V3& a, const V3& b) { float r = 0; r += a.x * b.x; r += a.y * b.y; r += a.z * b.z; return r; };
+  auto norm = [&](V3& a) { const float inv = 1.0f / std::sqrt(plain_dot(a, a)); a.x *= inv; a.y *= inv; a.z *= inv; };
+  auto cross = [](const V3& a, const V3& b) {
+    V3 o = {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+    return o;
+  };
+  norm(X); norm(Y);                                                         // :59-60
+  const V3 Z = cross(X, Y);                                                 // :61
+  Y = cross(Z, X);                                                          // :62
+  float R4[16], Rt4[16], Tt[16], Tti[16];
+  for (int i = 0; i < 16; ++i) R4[i] = Rt4[i] = Tt[i] = Tti[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+  const float xs[3] = {X.x, X.y, X.z}, ys[3] = {Y.x, Y.y, Y.z}, zs[3] = {Z.x, Z.y, Z.z};
+  for (int r = 0; r < 3; ++r) {
+    AT(R4, r, 0) = xs[r]; AT(R4, r, 1) = ys[r]; AT(R4, r, 2) = zs[r];
+    AT(Rt4, 0, r) = xs[r]; AT(Rt4, 1, r) = ys[r]; AT(Rt4, 2, r) = zs[r];
+    AT(Tt, r, 3) = AT(Mx, r, 3);
+    AT(Tti, r, 3) = -AT(Mx, r, 3);
+  }
+#undef AT
+  mat4_mul(Tt, R4, T);            // Translate(t) * Rotate(R), include/vulcan/transform.h:60-64
+  mat4_mul(Rt4, Tti, T + 16);
+}
+
+void track_system(const float* T, const float* Tk, const float* key_depth, const float* key_normal, const Proj& kP,
+                  int kw, int kh, const float* depth, const float* normal, const Proj& P, int w, int h,
+                  int translation, double* H, double* g) {
+  const int n = translation ? 6 : 3;
+  for (int i = 0; i < 21; ++i) H[i] = 0;
+  for (int i = 0; i < 6; ++i) g[i] = 0;
+  for (int y = 0; y < h; ++y)
+    for (int x = 0; x < w; ++x) {
+      float r = 0, J[6];
+      if (!track_evaluate(T, Tk, Tk + 16, key_depth, key_normal, kP, kw, kh, depth, normal, P, w, x, y, r, J)) continue;
+      for (int a = 0, k = 0; a < n; ++a)
+        for (int b = 0; b <= a; ++b, ++k) H[k] += (double)(J[a] * J[b]);   // float products, as the kernel forms them
+      for (int a = 0; a < n; ++a) g[a] += (double)(J[a] * r);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// DownsampleKernel, src/image.cu:101-165 (channels 1 or 3; dst is (w/2) x (h/2))
+void vo_downsample(const float* src, int w, int h, int channels, int nearest, float* dst) {
+  const int dw = w / 2, dh = h / 2;
+  for (int y = 0; y < dh; ++y)
+    for (int x = 0; x < dw; ++x)
+      for (int c = 0; c < channels; ++c) {
+        const float* s = src + ((size_t)(2 * y) * w + 2 * x) * channels + c;
+        float v;
+        if (nearest) v = s[0];
+        else {
+          v = 0;
+          v += s[channels]; v += s[0]; v += s[(size_t)w * channels + channels]; v += s[(size_t)w * channels];
+          v *= 0.25f;
+        }
+        dst[((size_t)y * dw + x) * channels + c] = v;
+      }
+}
+
+// DepthTracker::ComputeResiduals / ComputeJacobian, src/depth_tracker.cu:101-144.  T, Tk: frame / keyframe
+// depth_to_world matrix + inverse (32 floats each); proj4 fx fy cx cy.  Either output may be NULL.
+void vo_track_pixels(const float* T, const float* Tk, const float* key_depth, const float* key_normal,
+                     const float* kproj4, int kw, int kh, const float* depth, const float* normal, const float* proj4,
+                     int w, int h, int translation, float* residuals, float* jacobian) {
+  const Proj kP = {kproj4[0], kproj4[1], kproj4[2], kproj4[3]}, P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  for (int y = 0; y < h; ++y)
+    for (int x = 0; x < w; ++x) {
+      float r = 0, J[6] = {0, 0, 0, 0, 0, 0};
+      const bool ok = track_evaluate(T, Tk, Tk + 16, key_depth, key_normal, kP, kw, kh, depth, normal, P, w, x, y, r, J);
+      const size_t i = (size_t)y * w + x;
+      if (residuals) residuals[i] = ok ? r : 0.0f;
+      if (jacobian)
+        for (int k = 0; k < 6; ++k) jacobian[6 * i + k] = (ok && (translation || k < 3)) ? J[k] : 0.0f;
+    }
+}
+
+// DepthTracker::ComputeSystem, src/depth_tracker.cu:146-274, accumulated in double
+void vo_track_system(const float* T, const float* Tk, const float* key_depth, const float* key_normal,
+                     const float* kproj4, int kw, int kh, const float* depth, const float* normal, const float* proj4,
+                     int w, int h, int translation, double* hessian21, double* gradient6) {
+  const Proj kP = {kproj4[0], kproj4[1], kproj4[2], kproj4[3]}, P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  track_system(T, Tk, key_depth, key_normal, kP, kw, kh, depth, normal, P, w, h, translation, hessian21, gradient6);
+}
+
+// Tracker::Track, src/tracker.cpp:57-67,112-153 with DepthTracker::ApplyUpdate.  T (32 floats) is updated in
+// place; returns the number of systems solved.
+int vo_track_depth(float* T, const float* Tk, const float* key_depth, const float* key_normal, const float* kproj4,
+                   int kw, int kh, const float* depth, const float* normal, const float* proj4, int w, int h,
+                   int translation, int max_iterations) {
+  const Proj kP = {kproj4[0], kproj4[1], kproj4[2], kproj4[3]}, P = {proj4[0], proj4[1], proj4[2], proj4[3]};
+  int iteration = 0, solved = 0;
+  while (iteration < max_iterations) {
+    double H[21], g[6];
+    track_system(T, Tk, key_depth, key_normal, kP, kw, kh, depth, normal, P, w, h, translation, H, g);
+    float x[6];
+    track_solve(H, g, translation ? 6 : 3, x);
+    track_apply_update(x, T);
+    ++solved;
+    float nn = 0;
+    for (int i = 0; i < 6; ++i) nn += x[i] * x[i];
+    if (std::sqrt(nn) < 1e-6f) iteration = max_iterations;
+    ++iteration;
+  }
+  return solved;
+}
+
+// DepthTracker::ApplyUpdate alone (for the host-logic tests)
+void vo_track_apply_update(const float* update6, float* T) { track_apply_update(update6, T); }
+
+}  // extern "C"

@@ -63,6 +63,11 @@ def oracle_lib():
         lib.vo_compute_normals.argtypes = [_P, _P, _P, _I, _I]
         lib.vo_compute_points.argtypes = [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I]
         lib.vo_trace.argtypes = [_P, _P, _P, _I, _I, _F, _F, _P, _P, _P, _P]
+        lib.vo_downsample.argtypes = [_P, _I, _I, _I, _I, _P]
+        lib.vo_track_pixels.argtypes = [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _I, _I, _I, _P, _P]
+        lib.vo_track_system.argtypes = [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _I, _I, _I, _P, _P]
+        lib.vo_track_depth.argtypes = [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _I, _I, _I, _I]
+        lib.vo_track_apply_update.argtypes = [_P, _P]
         _oracle = lib
     return _oracle
 
@@ -187,6 +192,15 @@ def ref_lib(nofmad=False):
         lib.ref_download.argtypes = [_P, _P, C.c_size_t]
         lib.ref_filter_depths.argtypes = [_I, _I, _P, _P]
         lib.ref_compute_normals.argtypes = [_P, _P, _P, _I, _I]
+        lib.ref_track_create.restype = _P
+        lib.ref_track_destroy.argtypes = [_P]
+        lib.ref_track_set_frame.argtypes = [_P, _I, _P, _P, _P, _I, _I, _P, _P]
+        lib.ref_track_residuals.argtypes = [_P, _P]
+        lib.ref_track_jacobian.argtypes = [_P, _I, _P]
+        lib.ref_track_system.argtypes = [_P, _I, _P, _P]
+        lib.ref_track.argtypes = [_P, _I, _I, _P]
+        lib.ref_track_downsample.argtypes = [_P, _I, _I, _P, _P, _P, _P]
+        lib.ref_track_pyramid.argtypes = [_P, _P]
         _ref_libs[path] = lib
     return _ref_libs[path]
 
@@ -612,3 +626,164 @@ def compare(a, b, trunc):
     rep["normal_img_max_abs"] = float(np.abs(a["normal"] - b["normal"])[both].max()) if both.any() else 0.0
     rep["normal_bits_mismatch"] = int((a["normal"].view(np.int32) != b["normal"].view(np.int32)).sum())
     return rep
+
+
+# ---- image pyramid + depth tracker -------------------------------------------------
+
+def track_scenario(w=160, h=120, rot_deg=0.8, shift=(0.015, -0.01, 0.02), seed=7, dropouts=0.01):
+    """Keyframe and frame of the room scene (walls along all three axes + boxes: every degree of freedom
+    of the pose is observable) a small rigid motion apart.  Normals come from the CPU oracle's
+    ComputeNormals, so every implementation is fed the same arrays.  Returns a dict of float32 arrays:
+    K, key/frame depth, normal, colour, raw32 poses (key, true frame pose)."""
+    K = np.array(synth.intrinsics(w, h), dtype=np.float32)
+    R0 = synth.rotation_y(25.0)
+    t0 = np.array([0.3, 0.2, -0.5])
+    a = np.deg2rad(rot_deg)
+    Rx = np.array([[1, 0, 0], [0, np.cos(a), -np.sin(a)], [0, np.sin(a), np.cos(a)]])
+    R1 = synth.rotation_y(25.0 + rot_deg) @ Rx
+    t1 = t0 + np.asarray(shift)
+    rng = np.random.RandomState(seed)
+    out = {"K": K, "w": w, "h": h}
+    lib = oracle_lib()
+    mode = lib.vo_get_math_mode()
+    lib.vo_set_math_mode(0)  # the input normals are part of the scenario: one arithmetic mode, always
+    for name, (R, t) in (("key", (R0, t0)), ("frame", (R1, t1))):
+        d = synth.render_room(w, h, K.astype(np.float64), R, t)
+        d = np.ascontiguousarray(d, dtype=np.float32)
+        d[rng.rand(h, w) < dropouts] = 0.0
+        n = np.zeros((h, w, 3), dtype=np.float32)
+        lib.vo_compute_normals(_ptr(d), _ptr(K), _ptr(n), w, h)
+        yy, xx = np.mgrid[0:h, 0:w]
+        c = np.stack([(xx % 17) / 17.0, (yy % 13) / 13.0, ((xx + yy) % 7) / 7.0], axis=-1).astype(np.float32)
+        c = np.ascontiguousarray(c * rng.uniform(0.5, 1.0, size=(h, w, 1)).astype(np.float32))
+        out[name + "_depth"], out[name + "_normal"], out[name + "_color"] = d, n, c
+        out[name + "_pose"] = raw32(R, t)
+    lib.vo_set_math_mode(mode)
+    return out
+
+
+def pose_error(T32, truth32):
+    """(rotation error in degrees, translation error in metres) between two raw32 poses."""
+    A = np.asarray(T32[:16], dtype=np.float64).reshape(4, 4).T
+    B = np.asarray(truth32[:16], dtype=np.float64).reshape(4, 4).T
+    dR = A[:3, :3].T @ B[:3, :3]
+    # sin(angle) from the antisymmetric part: exact for small angles where arccos(trace) loses half the digits
+    ang = np.degrees(np.arcsin(np.clip(np.linalg.norm(dR - dR.T) / (2 * np.sqrt(2)), 0, 1)))
+    return float(ang), float(np.linalg.norm(A[:3, 3] - B[:3, 3]))
+
+
+def oracle_downsample(img, nearest):
+    img = np.ascontiguousarray(img, dtype=np.float32)
+    h, w = img.shape[:2]
+    ch = 1 if img.ndim == 2 else 3
+    out = np.zeros((h // 2, w // 2) + (() if ch == 1 else (3,)), dtype=np.float32)
+    oracle_lib().vo_downsample(_ptr(img), w, h, ch, int(nearest), _ptr(out))
+    return out
+
+
+def oracle_track_pixels(s, pose32, translation=1):
+    w, h = s["w"], s["h"]
+    r = np.zeros((h, w), dtype=np.float32)
+    J = np.zeros((h, w, 6), dtype=np.float32)
+    pose = np.ascontiguousarray(pose32, dtype=np.float32)
+    oracle_lib().vo_track_pixels(_ptr(pose), _ptr(s["key_pose"]), _ptr(s["key_depth"]), _ptr(s["key_normal"]),
+                                 _ptr(s["K"]), w, h, _ptr(s["frame_depth"]), _ptr(s["frame_normal"]), _ptr(s["K"]),
+                                 w, h, int(translation), _ptr(r), _ptr(J))
+    return r, J
+
+
+def oracle_track_system(s, pose32, translation=1):
+    w, h = s["w"], s["h"]
+    H = np.zeros(21, dtype=np.float64)
+    g = np.zeros(6, dtype=np.float64)
+    pose = np.ascontiguousarray(pose32, dtype=np.float32)
+    oracle_lib().vo_track_system(_ptr(pose), _ptr(s["key_pose"]), _ptr(s["key_depth"]), _ptr(s["key_normal"]),
+                                 _ptr(s["K"]), w, h, _ptr(s["frame_depth"]), _ptr(s["frame_normal"]), _ptr(s["K"]),
+                                 w, h, int(translation), _ptr(H), _ptr(g))
+    n = 6 if translation else 3
+    return H[:n * (n + 1) // 2], g[:n]
+
+
+def oracle_track(s, pose32, translation=1, max_iterations=20):
+    w, h = s["w"], s["h"]
+    pose = np.array(pose32, dtype=np.float32)
+    oracle_lib().vo_track_depth.restype = _I
+    it = oracle_lib().vo_track_depth(_ptr(pose), _ptr(s["key_pose"]), _ptr(s["key_depth"]), _ptr(s["key_normal"]),
+                                     _ptr(s["K"]), w, h, _ptr(s["frame_depth"]), _ptr(s["frame_normal"]),
+                                     _ptr(s["K"]), w, h, int(translation), int(max_iterations))
+    return pose, it
+
+
+class RefTracker:
+    """The reference's DepthTracker / Frame::Downsample (oracle/_ref) on a track_scenario."""
+
+    def __init__(self, s, pose32, nofmad=False):
+        self.lib = ref_lib(nofmad)
+        self.s = s
+        self.h = self.lib.ref_track_create()
+        assert self.h
+        w, h = s["w"], s["h"]
+        pose = np.ascontiguousarray(pose32, dtype=np.float32)
+        assert self.lib.ref_track_set_frame(self.h, 0, _ptr(s["key_depth"]), _ptr(s["key_normal"]),
+                                            _ptr(s["key_color"]), w, h, _ptr(s["K"]), _ptr(s["key_pose"])) == 0
+        assert self.lib.ref_track_set_frame(self.h, 1, _ptr(s["frame_depth"]), _ptr(s["frame_normal"]),
+                                            _ptr(s["frame_color"]), w, h, _ptr(s["K"]), _ptr(pose)) == 0
+
+    def close(self):
+        if self.h:
+            self.lib.ref_track_destroy(self.h)
+            self.h = None
+
+    def residuals(self):
+        r = np.zeros((self.s["h"], self.s["w"]), dtype=np.float32)
+        assert self.lib.ref_track_residuals(self.h, _ptr(r)) == 0
+        return r
+
+    def jacobian(self, translation=1):
+        J = np.zeros((self.s["h"], self.s["w"], 6), dtype=np.float32)
+        assert self.lib.ref_track_jacobian(self.h, int(translation), _ptr(J)) == 0
+        return J
+
+    def system(self, translation=1):
+        H = np.zeros(21, dtype=np.float32)
+        g = np.zeros(6, dtype=np.float32)
+        assert self.lib.ref_track_system(self.h, int(translation), _ptr(H), _ptr(g)) == 0
+        n = 6 if translation else 3
+        return H[:n * (n + 1) // 2], g[:n]
+
+    def track(self, translation=1, max_iterations=20):
+        pose = np.zeros(32, dtype=np.float32)
+        assert self.lib.ref_track(self.h, int(translation), int(max_iterations), _ptr(pose)) == 0
+        return pose
+
+    def track_pyramid(self):
+        pose = np.zeros(32, dtype=np.float32)
+        assert self.lib.ref_track_pyramid(self.h, _ptr(pose)) == 0
+        return pose
+
+    def downsample(self, which, level):
+        w, h = self.s["w"] >> level, self.s["h"] >> level
+        d = np.zeros((h, w), dtype=np.float32)
+        c = np.zeros((h, w, 3), dtype=np.float32)
+        n = np.zeros((h, w, 3), dtype=np.float32)
+        k = np.zeros(4, dtype=np.float32)
+        assert self.lib.ref_track_downsample(self.h, which, level, _ptr(d), _ptr(c), _ptr(n), _ptr(k)) == 0
+        return d, c, n, k
+
+
+def ours_track_frames(s, pose32):
+    """(keyframe, frame) as vulcan_b200 Frames on the GPU."""
+    import torch
+    import vulcan_b200 as vb
+    frames = []
+    for name, pose in (("key", s["key_pose"]), ("frame", pose32)):
+        f = vb.Frame()
+        f.depth_projection = vb.Projection(*s["K"])
+        f.color_projection = vb.Projection(*s["K"])
+        f.depth_image = torch.from_numpy(s[name + "_depth"]).cuda()
+        f.normal_image = torch.from_numpy(s[name + "_normal"]).cuda()
+        f.color_image = torch.from_numpy(s[name + "_color"]).cuda()
+        p = np.asarray(pose, dtype=np.float32)
+        f.depth_to_world_transform = vb.Transform(p[:16].reshape(4, 4).T.copy(), p[16:].reshape(4, 4).T.copy())
+        frames.append(f)
+    return frames

@@ -113,6 +113,13 @@ SYMBOLS = {
     "vk_exchange_normal": [_P, _I, _I],
     "vk_exchange_bands": [C.POINTER(vkExchange), _I, _P, _P, _P, _P],
     "vk_exchange_bounds": [C.POINTER(vkExchange), _I, _P, _P],
+    "vk_downsample_frame": [C.POINTER(vkFrame), C.POINTER(vkFrame), _P],
+    "vk_downsample_image": [_P, _I, _I, _I, _I, _P, _P],
+    "vk_track_residuals": [C.POINTER(vkFrame), C.POINTER(vkFrame), _P, _P],
+    "vk_track_jacobian": [C.POINTER(vkFrame), C.POINTER(vkFrame), _I, _P, _P],
+    "vk_track_workspace_floats": [],
+    "vk_track_system": [C.POINTER(vkFrame), C.POINTER(vkFrame), _I, _P, _P, _P, _P],
+    "vk_track_depth": [C.POINTER(vkFrame), C.POINTER(vkFrame), _I, _I, _P, C.POINTER(_I), C.POINTER(_F), _P],
     "vk_version": [],
     "vk_set_default_math_mode": [_I],
     "vk_get_default_math_mode": [],

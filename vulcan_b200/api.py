@@ -6,6 +6,8 @@ and error behaviour as the reference's C++ classes:
   Integrator etc.   include/vulcan/integrator.h:16-34, depth_/color_/light_integrator.h
   Tracer            include/vulcan/tracer.h:24-76
   Frame             include/vulcan/frame.h:11-32
+  DepthTracker      include/vulcan/tracker.h:16-103, depth_tracker.h:9-27
+  PyramidTracker    include/vulcan/pyramid_tracker.h
   Transform         include/vulcan/transform.h:9-171
   Projection        include/vulcan/projection.h:11-114
 
@@ -179,6 +181,31 @@ class Frame:
         check(lib.vk_prepare_frame(w, h, self.depth_image.data_ptr(), C.byref(p), out.data_ptr(),
                                    self.normal_image.data_ptr(), _stream()), "Prepare")
         self.depth_image = out
+
+    def Downsample(self, frame):
+        """Frame::Downsample (src/frame.cpp:38-57): depth and normals by nearest sample, colour by 2x2
+        average, intrinsics halved, transforms copied - one kernel for the three images."""
+        if self.depth_image is None or self.color_image is None or self.normal_image is None:
+            raise VulcanError("Downsample: depth, color and normal images required")  # frame.cpp:40-42
+        h, w = self.depth_image.shape
+        ch, cw = self.color_image.shape[:2]
+        if (w | h | cw | ch) & 1:
+            raise VulcanError("even image dimensions required")  # src/image.cu:185-186
+        if frame.depth_image is None or tuple(frame.depth_image.shape) != (h // 2, w // 2):
+            frame.depth_image = torch.empty((h // 2, w // 2), dtype=torch.float32, device="cuda")
+        if frame.normal_image is None or tuple(frame.normal_image.shape) != (h // 2, w // 2, 3):
+            frame.normal_image = torch.empty((h // 2, w // 2, 3), dtype=torch.float32, device="cuda")
+        if frame.color_image is None or tuple(frame.color_image.shape) != (ch // 2, cw // 2, 3):
+            frame.color_image = torch.empty((ch // 2, cw // 2, 3), dtype=torch.float32, device="cuda")
+        src = self.to_c()
+        dst = frame.to_c()
+        check(lib.vk_downsample_frame(C.byref(src), C.byref(dst), _stream()), "Downsample")
+        frame.depth_projection = Projection(dst.depth_proj.fx, dst.depth_proj.fy, dst.depth_proj.cx, dst.depth_proj.cy)
+        frame.color_projection = Projection(dst.color_proj.fx, dst.color_proj.fy, dst.color_proj.cx, dst.color_proj.cy)
+        frame.depth_to_world_transform = Transform(self.depth_to_world_transform.matrix,
+                                                   self.depth_to_world_transform.inv_matrix)
+        frame.depth_to_color_transform = Transform(self.depth_to_color_transform.matrix,
+                                                   self.depth_to_color_transform.inv_matrix)
 
     def FilterDepths(self):
         """Frame::FilterDepths (src/frame.cpp:8-19)."""
@@ -446,3 +473,134 @@ class Tracer:
         check(lib.vk_resolve_keys(keys.data_ptr(), C.byref(f), frame.depth_image.data_ptr(),
                                   frame.color_image.data_ptr(), frame.normal_image.data_ptr(), _stream()),
               "ResolveKeys")
+
+
+def _transform_from_c(t):
+    m = np.frombuffer(bytes(t), dtype=np.float32)
+    return Transform(m[:16].reshape(4, 4).T.copy(), m[16:].reshape(4, 4).T.copy())
+
+
+class DepthTracker:
+    """Tracker + DepthTracker (include/vulcan/tracker.h:16-103, depth_tracker.h:9-27; src/tracker.cpp,
+    src/depth_tracker.{cpp,cu}): projective point-to-plane alignment of a frame to the keyframe.
+    Every Gauss-Newton iteration is one kernel (system, solve and pose update on the device)."""
+
+    def __init__(self):
+        self.translation_enabled_ = True   # src/tracker.cpp:11-12
+        self.max_iterations_ = 20
+        self.keyframe_ = None
+        self.iterations_ = 0
+        self.last_update_norm_ = 0.0
+        self._workspace = torch.zeros(lib.vk_track_workspace_floats(), dtype=torch.float32, device="cuda")
+
+    def GetKeyframe(self):
+        return self.keyframe_
+
+    def SetKeyframe(self, keyframe):
+        self.keyframe_ = keyframe
+
+    def GetTranslationEnabled(self):
+        return self.translation_enabled_
+
+    def SetTranslationEnabled(self, enabled):
+        self.translation_enabled_ = bool(enabled)
+
+    def GetMaxIterations(self):
+        return self.max_iterations_
+
+    def SetMaxIterations(self, iterations):
+        if iterations <= 0:
+            raise VulcanError("iterations > 0")  # src/tracker.cpp:52
+        self.max_iterations_ = int(iterations)
+
+    def _validate(self, frame):
+        # Tracker::ValidateKeyframe / ValidateFrame (src/tracker.cpp:83-110)
+        if self.keyframe_ is None:
+            raise VulcanError("keyframe has not been assigned")
+        for f, name in ((self.keyframe_, "keyframe"), (frame, "frame")):
+            if f.depth_image is None:
+                raise VulcanError("%s missing depth image" % name)
+            if f.normal_image is None:
+                raise VulcanError("%s missing normal image" % name)
+            if tuple(f.normal_image.shape[:2]) != tuple(f.depth_image.shape):
+                raise VulcanError("%s image size mismatch" % name)
+
+    def Track(self, frame):
+        """Tracker::Track (src/tracker.cpp:57-67): frame.depth_to_world_transform is updated in place."""
+        self._validate(frame)
+        k = self.keyframe_.to_c()
+        f = frame.to_c()
+        it = C.c_int(0)
+        norm = C.c_float(0)
+        check(lib.vk_track_depth(C.byref(k), C.byref(f), int(self.translation_enabled_), self.max_iterations_,
+                                 self._workspace.data_ptr(), C.byref(it), C.byref(norm), _stream()), "Track")
+        frame.depth_to_world_transform = _transform_from_c(f.depth_to_world)
+        self.iterations_, self.last_update_norm_ = it.value, norm.value
+
+    def ComputeResiduals(self, frame):
+        """DepthTracker::ComputeResiduals (src/depth_tracker.cu:279-306) -> (H, W) tensor."""
+        self._validate(frame)
+        h, w = frame.depth_image.shape
+        out = torch.empty((h, w), dtype=torch.float32, device="cuda")
+        k, f = self.keyframe_.to_c(), frame.to_c()
+        check(lib.vk_track_residuals(C.byref(k), C.byref(f), out.data_ptr(), _stream()), "ComputeResiduals")
+        return out
+
+    def ComputeJacobian(self, frame):
+        """DepthTracker::ComputeJacobian (src/depth_tracker.cu:308-344) -> (H, W, 6) tensor."""
+        self._validate(frame)
+        h, w = frame.depth_image.shape
+        out = torch.empty((h, w, 6), dtype=torch.float32, device="cuda")
+        k, f = self.keyframe_.to_c(), frame.to_c()
+        check(lib.vk_track_jacobian(C.byref(k), C.byref(f), int(self.translation_enabled_), out.data_ptr(), _stream()),
+              "ComputeJacobian")
+        return out
+
+    def ComputeSystem(self, frame):
+        """DepthTracker::ComputeSystem (src/depth_tracker.cu:346-378) -> (packed Hessian, gradient) tensors."""
+        self._validate(frame)
+        n = 6 if self.translation_enabled_ else 3
+        hessian = torch.zeros(n * (n + 1) // 2, dtype=torch.float32, device="cuda")
+        gradient = torch.zeros(n, dtype=torch.float32, device="cuda")
+        k, f = self.keyframe_.to_c(), frame.to_c()
+        check(lib.vk_track_system(C.byref(k), C.byref(f), int(self.translation_enabled_), self._workspace.data_ptr(),
+                                  hessian.data_ptr(), gradient.data_ptr(), _stream()), "ComputeSystem")
+        return hessian, gradient
+
+
+class PyramidTracker:
+    """PyramidTracker<DepthTracker> (include/vulcan/pyramid_tracker.h, src/pyramid_tracker.cpp:52-90): both
+    pyramids are built, the half-size level is tracked with 15 iterations, the full size with 20."""
+
+    def __init__(self):
+        self.tracker_ = DepthTracker()
+        self.keyframe_ = None
+        self.half_keyframe_, self.quarter_keyframe_ = Frame(), Frame()
+
+    def GetTracker(self):
+        return self.tracker_
+
+    def GetKeyframe(self):
+        return self.keyframe_
+
+    def SetKeyframe(self, keyframe):
+        self.keyframe_ = keyframe
+
+    def Track(self, frame):
+        if self.keyframe_ is None:
+            raise VulcanError("keyframe has not been assigned")
+        half_frame, quarter_frame = Frame(), Frame()
+        frame.Downsample(half_frame)
+        half_frame.Downsample(quarter_frame)
+        self.keyframe_.Downsample(self.half_keyframe_)
+        self.half_keyframe_.Downsample(self.quarter_keyframe_)
+        t = self.tracker_
+        t.SetMaxIterations(15)
+        t.SetTranslationEnabled(True)
+        half_frame.depth_to_world_transform = quarter_frame.depth_to_world_transform
+        t.SetKeyframe(self.half_keyframe_)
+        t.Track(half_frame)
+        t.SetMaxIterations(20)
+        frame.depth_to_world_transform = half_frame.depth_to_world_transform
+        t.SetKeyframe(self.keyframe_)
+        t.Track(frame)
