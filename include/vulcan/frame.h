@@ -30,7 +30,8 @@ struct Frame
   // filtered image (a new Image object: other holders of the old pointer keep the raw depth)
   void Prepare();
 
-  // tracker support (pyramids): outside the fusion hot path, throws "not implemented"
+  // half-size pyramid level into `frame`: depth and normals by nearest sample, colour by 2x2 average,
+  // intrinsics halved, transforms copied; one kernel for the three images (src/frame.cpp:38-57)
   void Downsample(Frame& frame) const;
 };
 

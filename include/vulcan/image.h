@@ -103,6 +103,8 @@ class Image : public detail::DeviceImage<float, 1>
   public:
     Image() {}
     Image(int w, int h) : detail::DeviceImage<float, 1>(w, h) {}
+    // half-size image, nearest sample or 2x2 average (src/image.cu:183-212)
+    void Downsample(Image& image, bool nearest) const;
 };
 
 class ColorImage : public detail::DeviceImage<Vector3f, 3>
@@ -110,6 +112,8 @@ class ColorImage : public detail::DeviceImage<Vector3f, 3>
   public:
     ColorImage() {}
     ColorImage(int w, int h) : detail::DeviceImage<Vector3f, 3>(w, h) {}
+    // src/image.cu:234-263
+    void Downsample(ColorImage& image, bool nearest) const;
 };
 
 } // namespace vulcan

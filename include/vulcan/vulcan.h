@@ -6,6 +6,7 @@
 #include <vulcan/buffer.h>
 #include <vulcan/color_integrator.h>
 #include <vulcan/depth_integrator.h>
+#include <vulcan/depth_tracker.h>
 #include <vulcan/device.h>
 #include <vulcan/exception.h>
 #include <vulcan/frame.h>
@@ -17,8 +18,10 @@
 #include <vulcan/math.h>
 #include <vulcan/matrix.h>
 #include <vulcan/projection.h>
+#include <vulcan/pyramid_tracker.h>
 #include <vulcan/tracer.h>
 #include <vulcan/tracer.cuh>
+#include <vulcan/tracker.h>
 #include <vulcan/transform.h>
 #include <vulcan/types.h>
 #include <vulcan/volume.h>

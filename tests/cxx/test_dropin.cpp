@@ -4,6 +4,7 @@
 //   tests/buffer_test.cu:17-182      Buffer semantics
 //   tests/integrator_test.cu:82-221  per-voxel host recomputation of one / two integrations (1e-5)
 //   tests/tracer_test.cu:246-390     wall at 1.5 m: traced depth within 0.01 m, colour within 1e-3
+//   (new) Frame::Downsample and DepthTracker / PyramidTracker on a wall 2 cm closer
 //   tests/voxel_test.cpp, hash_test.cpp, block_test.cpp   layouts (static_asserts in the headers)
 // Needs a GPU.  Exit code 0 = all passed.
 #include <vulcan/vulcan.h>
@@ -275,11 +276,102 @@ static void TestTwoVolumes()
   CHECK(b.GetAllocatedBlockCount() == allocated);
 }
 
+// Frame::Downsample (src/frame.cpp:38-57): sizes, halved intrinsics, nearest depth, averaged colour
+static void TestDownsample()
+{
+  const int w = 64, h = 48;
+  Frame frame;
+  std::vector<float> depth((size_t)w * h);
+  std::vector<Vector3f> color((size_t)w * h);
+  for (int y = 0; y < h; ++y)
+    for (int x = 0; x < w; ++x)
+    {
+      depth[y * w + x] = 1.0f + 0.01f * x + 0.001f * y;
+      color[y * w + x] = Vector3f(0.25f * (x % 4), 0.125f * (y % 8), 0.5f);
+    }
+  frame.depth_image = std::make_shared<Image>(w, h);
+  frame.depth_image->CopyFromHost(depth.data());
+  frame.color_image = std::make_shared<ColorImage>(w, h);
+  frame.color_image->CopyFromHost(color.data());
+  frame.depth_projection.SetFocalLength(50, 52);
+  frame.depth_projection.SetCenterPoint(32, 24);
+  frame.ComputeNormals();
+  Frame half;
+  frame.Downsample(half);
+  CHECK(half.depth_image->GetWidth() == 32 && half.depth_image->GetHeight() == 24);
+  CHECK(half.color_image->GetWidth() == 32 && half.normal_image->GetHeight() == 24);
+  CHECK_NEAR(half.depth_projection.GetFocalLength()[1], 26, 0);
+  CHECK_NEAR(half.depth_projection.GetCenterPoint()[0], 16, 0);
+  std::vector<float> hd(32 * 24);
+  std::vector<Vector3f> hc(32 * 24);
+  half.depth_image->CopyToHost(hd.data());
+  half.color_image->CopyToHost(hc.data());
+  for (int y = 0; y < 24; ++y)
+    for (int x = 0; x < 32; ++x)
+    {
+      CHECK(hd[y * 32 + x] == depth[(2 * y) * w + 2 * x]);
+      const float want = 0.25f * (color[(2 * y) * w + 2 * x + 1][0] + color[(2 * y) * w + 2 * x][0] +
+                                  color[(2 * y + 1) * w + 2 * x + 1][0] + color[(2 * y + 1) * w + 2 * x][0]);
+      CHECK_NEAR(hc[y * 32 + x][0], want, 1e-6);
+    }
+  Image odd(5, 4), out;
+  bool thrown = false;
+  try { odd.Downsample(out, true); } catch (const Exception&) { thrown = true; }
+  CHECK(thrown);
+}
+
+// DepthTracker on a fronto-parallel wall: the camera moved 2 cm towards the wall.  Only the translation
+// along the wall normal is observable; the other pivots of the normal equations vanish and their
+// components stay 0 (what an LDL^T does with a zero pivot), so Track recovers exactly that motion.
+static void TestDepthTrackerWall()
+{
+  const int w = 160, h = 120;
+  auto keyframe = std::make_shared<Frame>();
+  keyframe->depth_image = ConstantDepth(w, h, 1.5f);
+  keyframe->depth_projection.SetFocalLength(125, 125);
+  keyframe->depth_projection.SetCenterPoint(80, 60);
+  keyframe->ComputeNormals();
+  Frame frame;
+  frame.depth_image = ConstantDepth(w, h, 1.48f);
+  frame.depth_projection = keyframe->depth_projection;
+  frame.ComputeNormals();
+  DepthTracker tracker;
+  tracker.SetKeyframe(keyframe);
+  Buffer<float> residuals;
+  tracker.ComputeResiduals(frame, residuals);
+  CHECK(residuals.GetSize() == (size_t)w * h);
+  const std::vector<float> r = Download(residuals);
+  CHECK_NEAR(std::fabs(r[(h / 2) * w + w / 2]), 0.02, 1e-5);
+  tracker.Track(frame);
+  const Vector3f t = frame.depth_to_world_transform.GetTranslation();
+  CHECK_NEAR(t[0], 0, 1e-5);
+  CHECK_NEAR(t[1], 0, 1e-5);
+  CHECK_NEAR(t[2], 0.02, 1e-5);
+  CHECK(tracker.GetIterations() >= 1 && tracker.GetIterations() <= 20);
+  tracker.ComputeResiduals(frame, residuals);
+  CHECK_NEAR(Download(residuals)[(h / 2) * w + w / 2], 0, 1e-5);
+  // the pyramid schedule reaches the same pose
+  Frame again;
+  again.depth_image = ConstantDepth(w, h, 1.48f);
+  again.color_image = ConstantColor(w, h, Vector3f(0.5f, 0.5f, 0.5f));
+  again.depth_projection = keyframe->depth_projection;
+  again.ComputeNormals();
+  keyframe->color_image = ConstantColor(w, h, Vector3f(0.5f, 0.5f, 0.5f));
+  PyramidTracker<DepthTracker> pyramid;
+  pyramid.SetKeyframe(keyframe);
+  pyramid.Track(again);
+  CHECK_NEAR(again.depth_to_world_transform.GetTranslation()[2], 0.02, 1e-5);
+  bool thrown = false;
+  try { DepthTracker().Track(frame); } catch (const Exception&) { thrown = true; }  // no keyframe
+  CHECK(thrown);
+}
+
 int main()
 {
   struct { const char* name; void (*fn)(); } tests[] = {
     {"Volume.Constructor", TestVolumeConstructor}, {"Buffer", TestBuffer}, {"Integrator.Integrate", TestIntegrate},
     {"Tracer.TraceWall", TestTraceWall}, {"Volume.TwoVolumes", TestTwoVolumes},
+    {"Frame.Downsample", TestDownsample}, {"DepthTracker.Wall", TestDepthTrackerWall},
   };
   for (auto& t : tests)
   {

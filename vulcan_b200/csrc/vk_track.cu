@@ -103,6 +103,9 @@ struct TrackState {
   unsigned ticket;
   int max_iterations;
   int evaluations;    // systems solved
+  int pad_;
+  unsigned long long stamps[6];  // %globaltimer of the last iteration's last CTA: entry, pixels done, ticket,
+                                 // sums folded, solved; [5] = entry of CTA 0 (tools/track_once.py)
 };
 static_assert(sizeof(TrackState) <= VK_TRACK_STATE_FLOATS * sizeof(float), "VK_TRACK_STATE_FLOATS too small");
 
@@ -113,7 +116,12 @@ __device__ __forceinline__ bool track_evaluate(const TrackImages& im, const Mat3
                                                const Mat34& Tmw, const Unprojector& up, const Unprojector& kup, int x,
                                                int y, float& residual, float* J) {
   const int index = y * im.w + x;
+  // the frame's depth and normal are fetched together, the keyframe's depth and normal likewise (the
+  // normal speculatively: kindex is inside the image once the bounds test passed): two dependent round
+  // trips per pixel instead of three
   const float d = __ldg(im.depth + index);
+  const float fnx = __ldg(im.normal + 3 * (size_t)index), fny = __ldg(im.normal + 3 * (size_t)index + 1),
+              fnz = __ldg(im.normal + 3 * (size_t)index + 2);
   if (!(d > 0)) return false;
   const float u = (float)x + 0.5f, v = (float)y + 0.5f;
   // Unproject(u, v, d) = d * Unproject(uv)  (include/vulcan/projection.h:80-101)
@@ -126,12 +134,11 @@ __device__ __forceinline__ bool track_evaluate(const TrackImages& im, const Mat3
   const int kx = (int)ku, ky = (int)kv;
   const int kindex = ky * im.kw + kx;
   const float kd = __ldg(im.key_depth + kindex);
+  const float knx = __ldg(im.key_normal + 3 * (size_t)kindex), kny = __ldg(im.key_normal + 3 * (size_t)kindex + 1),
+              knz = __ldg(im.key_normal + 3 * (size_t)kindex + 2);
   if (!(kd > 0)) return false;
-  const Vec3 fn = xform0<F>(Twc, __ldg(im.normal + 3 * (size_t)index), __ldg(im.normal + 3 * (size_t)index + 1),
-                            __ldg(im.normal + 3 * (size_t)index + 2));
-  const Vec3 kn = xform0<F>(Twm, __ldg(im.key_normal + 3 * (size_t)kindex),
-                            __ldg(im.key_normal + 3 * (size_t)kindex + 1),
-                            __ldg(im.key_normal + 3 * (size_t)kindex + 2));
+  const Vec3 fn = xform0<F>(Twc, fnx, fny, fnz);
+  const Vec3 kn = xform0<F>(Twm, knx, kny, knz);
   if (!(dot3<F>(kn, kn) > 0.0f && dot3<F>(fn, kn) > 0.5f)) return false;
   const float fu = floorf(ku) + 0.5f, fv = floorf(kv) + 0.5f;
   const float yx = mul(kup.x<F>(fu), kd), yy = mul(kup.y<F>(fv), kd), yz = mul(1.0f, kd);
@@ -146,6 +153,12 @@ __device__ __forceinline__ bool track_evaluate(const TrackImages& im, const Mat3
   J[4] = kn.y;
   J[5] = kn.z;
   return true;
+}
+
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
 }
 
 __device__ __forceinline__ void load_rows_colmajor(Mat34& M, const float* colmajor) {
@@ -183,33 +196,47 @@ __global__ void __launch_bounds__(256) vk_track_pixels_kernel(TrackImages im, co
 // (row r, column c <= r at r (r + 1) / 2 + c), as the reference's kernel stores it
 // (src/depth_tracker.cu:214-223, unpacked in src/tracker.cpp:133-143).  A vanishing pivot zeroes its
 // component (no valid pixel -> no motion).
-__device__ void track_solve(const float* packed, const float* g, int n, float* x) {
-  double L[6][6], D[6], y[6];
-  for (int r = 0; r < n; ++r)
+template <int N>
+__device__ __forceinline__ void track_solve(const float* packed, const float* g, float* x) {
+  // fully unrolled: L, D and y live in registers
+  double L[N][N], D[N], invD[N], y[N];
+#pragma unroll
+  for (int r = 0; r < N; ++r)
+#pragma unroll
     for (int c = 0; c <= r; ++c) L[r][c] = (double)packed[r * (r + 1) / 2 + c];
-  for (int j = 0; j < n; ++j) {
+#pragma unroll
+  for (int j = 0; j < N; ++j) {
     double d = L[j][j];
+#pragma unroll
     for (int k = 0; k < j; ++k) d -= L[j][k] * L[j][k] * D[k];
     D[j] = d;
-    const double inv = fabs(d) > 1e-30 ? 1.0 / d : 0.0;
-    for (int i = j + 1; i < n; ++i) {
+    invD[j] = fabs(d) > 1e-30 ? 1.0 / d : 0.0;
+#pragma unroll
+    for (int i = j + 1; i < N; ++i) {
       double s = L[i][j];
+#pragma unroll
       for (int k = 0; k < j; ++k) s -= L[i][k] * L[j][k] * D[k];
-      L[i][j] = s * inv;
+      L[i][j] = s * invD[j];
     }
   }
-  for (int i = 0; i < n; ++i) {
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
     double s = -(double)g[i];
+#pragma unroll
     for (int k = 0; k < i; ++k) s -= L[i][k] * y[k];
     y[i] = s;
   }
-  for (int i = 0; i < n; ++i) y[i] = fabs(D[i]) > 1e-30 ? y[i] / D[i] : 0.0;
-  for (int i = n - 1; i >= 0; --i) {
+#pragma unroll
+  for (int i = 0; i < N; ++i) y[i] = y[i] * invD[i];
+#pragma unroll
+  for (int i = N - 1; i >= 0; --i) {
     double s = y[i];
-    for (int k = i + 1; k < n; ++k) s -= L[k][i] * y[k];
+#pragma unroll
+    for (int k = i + 1; k < N; ++k) s -= L[k][i] * y[k];
     y[i] = s;
   }
-  for (int i = 0; i < 6; ++i) x[i] = i < n ? (float)y[i] : 0.0f;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) x[i] = i < N ? (float)y[i] : 0.0f;
 }
 
 // DepthTracker::ApplyUpdate (src/depth_tracker.cpp:23-88) in single precision, one rounding per
@@ -217,14 +244,18 @@ __device__ void track_solve(const float* packed, const float* g, int n, float* x
 __device__ void track_apply_update(const float* u, float* Twc, float* Twc_inv) {
 #define MAT(m, r, c) (m)[(c) * 4 + (r)]
   float T[16];
+#pragma unroll
   for (int i = 0; i < 16; ++i) T[i] = (i % 5 == 0) ? 1.0f : 0.0f;
   MAT(T, 0, 1) = -u[2]; MAT(T, 0, 2) = +u[1]; MAT(T, 0, 3) = +u[3];
   MAT(T, 1, 0) = +u[2]; MAT(T, 1, 2) = +u[0]; MAT(T, 1, 3) = +u[4];  // sign of (1,2) as in the reference
   MAT(T, 2, 0) = -u[1]; MAT(T, 2, 1) = +u[0]; MAT(T, 2, 3) = +u[5];
   float M[16];
+#pragma unroll
   for (int p = 0; p < 4; ++p)
+#pragma unroll
     for (int m = 0; m < 4; ++m) {
       float acc = 0;
+#pragma unroll
       for (int n = 0; n < 4; ++n) acc = add(acc, mul(MAT(T, m, n), MAT(Twc, n, p)));
       MAT(M, m, p) = acc;
     }
@@ -233,12 +264,16 @@ __device__ void track_apply_update(const float* u, float* Twc, float* Twc_inv) {
   float Z[3];
   {
     float s = 0;
+#pragma unroll
     for (int i = 0; i < 3; ++i) s = add(s, mul(X[i], X[i]));
     const float inv = fdiv(1.0f, __fsqrt_rn(s));
+#pragma unroll
     for (int i = 0; i < 3; ++i) X[i] = mul(X[i], inv);
     s = 0;
+#pragma unroll
     for (int i = 0; i < 3; ++i) s = add(s, mul(Y[i], Y[i]));
     const float invy = fdiv(1.0f, __fsqrt_rn(s));
+#pragma unroll
     for (int i = 0; i < 3; ++i) Y[i] = mul(Y[i], invy);
   }
   Z[0] = sub(mul(X[1], Y[2]), mul(X[2], Y[1]));
@@ -251,16 +286,21 @@ __device__ void track_apply_update(const float* u, float* Twc, float* Twc_inv) {
   // Transform::Translate(t) * Transform::Rotate(R): matrix = [R | t]; inverse = R^T * Translate(-t)
   // evaluated as the 4x4 product the reference forms (include/vulcan/transform.h:60-64, matrix.h:299-317)
   float R4[16], Rt4[16], Tt[16], Tti[16];
+#pragma unroll
   for (int i = 0; i < 16; ++i) R4[i] = Rt4[i] = Tt[i] = Tti[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+#pragma unroll
   for (int r = 0; r < 3; ++r) {
     MAT(R4, r, 0) = X[r]; MAT(R4, r, 1) = Y[r]; MAT(R4, r, 2) = Z[r];
     MAT(Rt4, 0, r) = X[r]; MAT(Rt4, 1, r) = Y[r]; MAT(Rt4, 2, r) = Z[r];
     MAT(Tt, r, 3) = t[r];
     MAT(Tti, r, 3) = -t[r];
   }
+#pragma unroll
   for (int p = 0; p < 4; ++p)
+#pragma unroll
     for (int m = 0; m < 4; ++m) {
       float a = 0, b = 0;
+#pragma unroll
       for (int n = 0; n < 4; ++n) {
         a = add(a, mul(MAT(Tt, m, n), MAT(R4, n, p)));
         b = add(b, mul(MAT(Rt4, m, n), MAT(Tti, n, p)));
@@ -271,28 +311,42 @@ __device__ void track_apply_update(const float* u, float* Twc, float* Twc_inv) {
 #undef MAT
 }
 
-// Sum of acc[k] over the lanes of each warp into warp_sums[warp][k] (256-thread CTA), then a barrier.
+// Warp sums of K <= 32 values per lane with 31 shuffles instead of 5 K: at every butterfly step a lane
+// hands the half of its values that its partner keeps and adds the partner's half of the ones it keeps, so
+// the number of live values halves with the distance.  Afterwards lane L holds the sum over the warp of
+// value L.  The tree is fixed: the same inputs give the same bits.
 template <int K>
-__device__ __forceinline__ void block_sums(const float* acc, float (*warp_sums)[K], int lane, int warp) {
+__device__ __forceinline__ float warp_sums_transposed(const float* acc, int lane) {
+  float v[32];
 #pragma unroll
-  for (int k = 0; k < K; ++k) {
-    float s = acc[k];
+  for (int i = 0; i < 32; ++i) v[i] = i < K ? acc[i] : 0.0f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) warp_sums[warp][k] = s;
+  for (int o = 16; o >= 1; o >>= 1) {
+    const bool up = (lane & o) != 0;
+#pragma unroll
+    for (int i = 0; i < o; ++i) {
+      const float send = up ? v[i] : v[i + o];
+      const float keep = up ? v[i + o] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+    }
   }
-  __syncthreads();
+  return v[0];
 }
 
 // One Gauss-Newton iteration (or, with solve == 0, only ComputeSystem).  Each thread accumulates its
 // pixels' J^T r and the packed lower triangle of J^T J in registers; CTA sums go to partials[cta][27];
 // the last CTA to arrive adds them in CTA order and, when solving, advances the state.
 template <bool F, bool TRANS>
-__global__ void __launch_bounds__(256) vk_track_iter_kernel(TrackImages im, TrackState* __restrict__ st,
+__global__ void __launch_bounds__(256, 3) vk_track_iter_kernel(TrackImages im, TrackState* __restrict__ st,
                                                             float* __restrict__ partials, int solve) {
   constexpr int P = TRANS ? 6 : 3, H = TRANS ? 21 : 6, K = H + P;
   pdl_wait();  // the previous iteration's kernel wrote the state
   if (solve && *(volatile int*)&st->done) return;
+  unsigned long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+  if (threadIdx.x == 0) {
+    t0 = gtime();
+    if (blockIdx.x == 0) st->stamps[5] = t0;
+  }
   Mat34 Twc, Twm, Tmw;
   load_rows_colmajor(Twc, st->Twc);
   Twm.load(im.Twm);
@@ -318,14 +372,21 @@ __global__ void __launch_bounds__(256) vk_track_iter_kernel(TrackImages im, Trac
 #pragma unroll
     for (int a = 0; a < P; ++a) acc[H + a] = __fmaf_rn(J[a], r, acc[H + a]);
   }
+  if (threadIdx.x == 0) t1 = gtime();
   __shared__ float warp_sums[8][K];
+  __shared__ float s_system[27];
   __shared__ bool last;
-  block_sums<K>(acc, warp_sums, lx, ly);
+  {
+    const float mine = warp_sums_transposed<K>(acc, lx);
+    if (lx < K) warp_sums[ly][lx] = mine;
+  }
+  __syncthreads();
+  // partials are stored value-major ([value][CTA]) so that the fold below reads them coalesced
   if (threadIdx.x < K) {
     float s = 0;
 #pragma unroll
     for (int w = 0; w < 8; ++w) s += warp_sums[w][threadIdx.x];
-    partials[(size_t)blockIdx.x * 27 + threadIdx.x] = s;
+    partials[(size_t)threadIdx.x * gridDim.x + blockIdx.x] = s;
   }
   __threadfence();
   __syncthreads();
@@ -333,31 +394,52 @@ __global__ void __launch_bounds__(256) vk_track_iter_kernel(TrackImages im, Trac
   __syncthreads();
   if (!last) return;
   __threadfence();
-  // the last CTA folds the CTA sums: thread t takes CTAs t, t + 256, ... (a fixed order), then the same
-  // block reduction - every run adds the same numbers in the same order
+  if (threadIdx.x == 0) t2 = gtime();
+  // the last CTA folds the CTA sums: thread t takes CTAs t and t + 256 of every value (all loads
+  // independent and coalesced: one round trip to L2), then the same fixed reduction tree as above - every
+  // run adds the same numbers in the same order.  (track_grid keeps the grid below 512 CTAs.)
 #pragma unroll
-  for (int k = 0; k < K; ++k) acc[k] = 0;
-  for (unsigned b = threadIdx.x; b < gridDim.x; b += 256) {
-#pragma unroll
-    for (int k = 0; k < K; ++k) acc[k] += __ldcg(partials + (size_t)b * 27 + k);
+  for (int k = 0; k < K; ++k) {
+    const float* col = partials + (size_t)k * gridDim.x;
+    const float p0 = threadIdx.x < gridDim.x ? __ldcg(col + threadIdx.x) : 0.0f;
+    const float p1 = threadIdx.x + 256 < gridDim.x ? __ldcg(col + threadIdx.x + 256) : 0.0f;
+    acc[k] = p0 + p1;
+  }
+  __syncthreads();  // warp_sums is reused
+  {
+    const float mine = warp_sums_transposed<K>(acc, lx);
+    if (lx < K) warp_sums[ly][lx] = mine;
   }
   __syncthreads();
-  block_sums<K>(acc, warp_sums, lx, ly);
   if (threadIdx.x < K) {
     float s = 0;
 #pragma unroll
     for (int w = 0; w < 8; ++w) s += warp_sums[w][threadIdx.x];
     // Hessian entries first, gradient at 21.. (both layouts of the reference's buffers)
     const int slot = threadIdx.x < H ? threadIdx.x : 21 + (threadIdx.x - H);
+    s_system[slot] = s;
     st->system[slot] = s;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
+    t3 = gtime();
     st->ticket = 0;
     if (solve) {
       float x[6];
-      track_solve(st->system, st->system + 21, P, x);
-      track_apply_update(x, st->Twc, st->Twc_inv);
+      track_solve<P>(s_system, s_system + 21, x);
+      // pose in registers: one round trip in, one out
+      float T[16], Ti[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        T[i] = st->Twc[i];
+        Ti[i] = st->Twc_inv[i];
+      }
+      track_apply_update(x, T, Ti);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        st->Twc[i] = T[i];
+        st->Twc_inv[i] = Ti[i];
+      }
       float nn = 0;
       for (int i = 0; i < P; ++i) nn += x[i] * x[i];
       const float norm = sqrtf(nn);
@@ -370,6 +452,7 @@ __global__ void __launch_bounds__(256) vk_track_iter_kernel(TrackImages im, Trac
       st->evaluations += 1;
       if (it >= st->max_iterations) st->done = 1;
     }
+    st->stamps[0] = t0; st->stamps[1] = t1; st->stamps[2] = t2; st->stamps[3] = t3; st->stamps[4] = gtime();
   }
 }
 
@@ -394,9 +477,13 @@ static int fill_images(TrackImages& im, const vkFrame* key, const vkFrame* frame
 }
 
 static int track_grid(const TrackImages& im) {
+  // 84 registers x 256 threads: three CTAs per SM are resident.  The tiles are spread evenly over the
+  // fewest passes that fit (a grid of exactly `cap` CTAs would leave a nearly empty last pass).
   const int tiles = ((im.w + 31) / 32) * ((im.h + 7) / 8);
-  const int cap = 2 * sm_count();
-  return tiles < cap ? tiles : cap;
+  int cap = 3 * sm_count();
+  if (cap > 512) cap = 512;  // the fold of the CTA sums takes two CTAs per thread
+  const int passes = (tiles + cap - 1) / cap;
+  return (tiles + passes - 1) / passes;
 }
 
 extern "C" int vk_downsample_frame(const vkFrame* src, vkFrame* dst, void* stream) {
@@ -505,7 +592,7 @@ static int init_state(TrackState* dev, const vkFrame* frame, int max_iterations,
   return (int)cudaMemcpyAsync(dev, &h, sizeof(h), cudaMemcpyHostToDevice, s);
 }
 
-extern "C" int vk_track_workspace_floats(void) { return VK_TRACK_STATE_FLOATS + 27 * 2 * sm_count(); }
+extern "C" int vk_track_workspace_floats(void) { return VK_TRACK_STATE_FLOATS + 27 * 3 * sm_count(); }
 
 extern "C" int vk_track_system(const vkFrame* keyframe, const vkFrame* frame, int translation_enabled, float* workspace,
                                float* hessian, float* gradient, void* stream) {

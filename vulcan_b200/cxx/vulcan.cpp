@@ -93,9 +93,124 @@ void Frame::ComputeNormals()
                                nullptr));
 }
 
-void Frame::Downsample(Frame&) const
+void Frame::Downsample(Frame& frame) const
 {
-  VULCAN_THROW("not implemented");  // tracker support, outside the fusion hot path
+  VULCAN_ASSERT_MSG(depth_image && color_image && normal_image, "depth, color and normal images required");
+  if (!frame.depth_image) frame.depth_image = std::make_shared<Image>();
+  if (!frame.color_image) frame.color_image = std::make_shared<ColorImage>();
+  if (!frame.normal_image) frame.normal_image = std::make_shared<ColorImage>();
+  frame.depth_image->Resize(depth_image->GetWidth() / 2, depth_image->GetHeight() / 2);
+  frame.normal_image->Resize(depth_image->GetWidth() / 2, depth_image->GetHeight() / 2);
+  frame.color_image->Resize(color_image->GetWidth() / 2, color_image->GetHeight() / 2);
+  const vkFrame src = ToC(*this);
+  vkFrame dst = ToC(frame);
+  const int status = vk_downsample_frame(&src, &dst, nullptr);
+  VULCAN_ASSERT_MSG(status != VK_E_INVALID, "even image dimensions required");  // src/image.cu:185-186
+  VK_ASSERT(status);
+  std::memcpy(static_cast<void*>(&frame.depth_projection), &dst.depth_proj, sizeof(dst.depth_proj));
+  std::memcpy(static_cast<void*>(&frame.color_projection), &dst.color_proj, sizeof(dst.color_proj));
+  frame.depth_to_world_transform = depth_to_world_transform;
+  frame.depth_to_color_transform = depth_to_color_transform;
+}
+
+void Image::Downsample(Image& image, bool nearest) const
+{
+  VULCAN_ASSERT_MSG(GetWidth() % 2 == 0 && GetHeight() % 2 == 0, "even image dimensions required");
+  image.Resize(GetWidth() / 2, GetHeight() / 2);
+  VK_ASSERT(vk_downsample_image(GetData(), GetWidth(), GetHeight(), 1, nearest, image.GetData(), nullptr));
+}
+
+void ColorImage::Downsample(ColorImage& image, bool nearest) const
+{
+  VULCAN_ASSERT_MSG(GetWidth() % 2 == 0 && GetHeight() % 2 == 0, "even image dimensions required");
+  image.Resize(GetWidth() / 2, GetHeight() / 2);
+  VK_ASSERT(vk_downsample_image(reinterpret_cast<const float*>(GetData()), GetWidth(), GetHeight(), 3, nearest,
+                                reinterpret_cast<float*>(image.GetData()), nullptr));
+}
+
+// ---- Tracker / DepthTracker (src/tracker.cpp, src/depth_tracker.cpp, src/depth_tracker.cu) --------
+
+Tracker::Tracker() : translation_enabled_(true), max_iterations_(20), iterations_(0), last_update_norm_(0)
+{
+  workspace_.Resize(vk_track_workspace_floats());
+}
+
+Tracker::~Tracker() {}
+
+void Tracker::SetMaxIterations(int iterations)
+{
+  VULCAN_ASSERT(iterations > 0);
+  max_iterations_ = iterations;
+}
+
+void Tracker::ValidateKeyframe() const
+{
+  VULCAN_ASSERT_MSG(keyframe_ != nullptr, "keyframe has not been assigned");
+  VULCAN_ASSERT_MSG(keyframe_->depth_image != nullptr, "keyframe missing depth image");
+  VULCAN_ASSERT_MSG(keyframe_->normal_image != nullptr, "keyframe missing normal image");
+  const int dw = keyframe_->depth_image->GetWidth(), dh = keyframe_->depth_image->GetHeight();
+  VULCAN_ASSERT_MSG(dw > 0 && dh > 0, "invalid keyframe depth image size");
+  VULCAN_ASSERT_MSG(dw == keyframe_->normal_image->GetWidth() && dh == keyframe_->normal_image->GetHeight(),
+                    "keyframe image size mismatch");
+}
+
+void Tracker::ValidateFrame(const Frame& frame) const
+{
+  VULCAN_ASSERT_MSG(frame.depth_image != nullptr, "frame missing depth image");
+  VULCAN_ASSERT_MSG(frame.normal_image != nullptr, "frame missing normal image");
+  const int dw = frame.depth_image->GetWidth(), dh = frame.depth_image->GetHeight();
+  VULCAN_ASSERT_MSG(dw > 0 && dh > 0, "invalid frame depth image size");
+  VULCAN_ASSERT_MSG(dw == frame.normal_image->GetWidth() && dh == frame.normal_image->GetHeight(),
+                    "frame image size mismatch");
+}
+
+void Tracker::Track(Frame& frame)
+{
+  ValidateKeyframe();
+  ValidateFrame(frame);
+  Solve(frame);
+}
+
+DepthTracker::DepthTracker() {}
+DepthTracker::~DepthTracker() {}
+
+void DepthTracker::Solve(Frame& frame)
+{
+  const vkFrame key = ToC(*keyframe_);
+  vkFrame f = ToC(frame);
+  VK_ASSERT(vk_track_depth(&key, &f, translation_enabled_, max_iterations_, workspace_.GetData(), &iterations_,
+                           &last_update_norm_, nullptr));
+  std::memcpy(static_cast<void*>(&frame.depth_to_world_transform), &f.depth_to_world, sizeof(f.depth_to_world));
+}
+
+void DepthTracker::ComputeResiduals(const Frame& frame, Buffer<float>& residuals) const
+{
+  ValidateKeyframe();
+  ValidateFrame(frame);
+  residuals.Resize((size_t)frame.depth_image->GetWidth() * frame.depth_image->GetHeight());
+  const vkFrame key = ToC(*keyframe_), f = ToC(frame);
+  VK_ASSERT(vk_track_residuals(&key, &f, residuals.GetData(), nullptr));
+}
+
+void DepthTracker::ComputeJacobian(const Frame& frame, Buffer<Vector6f>& jacobian) const
+{
+  ValidateKeyframe();
+  ValidateFrame(frame);
+  jacobian.Resize((size_t)frame.depth_image->GetWidth() * frame.depth_image->GetHeight());
+  const vkFrame key = ToC(*keyframe_), f = ToC(frame);
+  VK_ASSERT(vk_track_jacobian(&key, &f, translation_enabled_, reinterpret_cast<float*>(jacobian.GetData()), nullptr));
+}
+
+void DepthTracker::ComputeSystem(const Frame& frame, Buffer<float>& hessian, Buffer<float>& gradient)
+{
+  ValidateKeyframe();
+  ValidateFrame(frame);
+  const int n = GetParameterCount();
+  hessian.Resize(n * (n + 1) / 2);
+  gradient.Resize(n);
+  const vkFrame key = ToC(*keyframe_), f = ToC(frame);
+  VK_ASSERT(vk_track_system(&key, &f, translation_enabled_, workspace_.GetData(), hessian.GetData(),
+                            gradient.GetData(), nullptr));
 }
 
 // ---- Volume (src/volume.cu:370-463) ----------------------------------------------------------
