@@ -205,3 +205,17 @@ def test_tracker_validation_errors():
         t.Track(frame)               # frame missing normal image
     with pytest.raises(vb.VulcanError):
         t.SetMaxIterations(0)
+
+
+def test_frame_to_model_tracking_closes_the_loop():
+    """The reference app's loop with tracking on (apps/vulcan/vulcan.cu:296-325): every pose after the
+    first comes from the PyramidTracker against the ray-cast model.  The drift over the trajectory stays
+    a small fraction of the motion."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(H.ROOT, "tools"))
+    import tracked_orbit
+    r = tracked_orbit.run(frames=12, w=320, h=240)
+    assert r["pool_overflow"] == 0
+    assert r["trajectory_deg_m"][0] > 5.0 and r["trajectory_deg_m"][1] > 0.1
+    assert r["max_error_deg"] < 0.3 and r["max_error_m"] < 0.01, r
