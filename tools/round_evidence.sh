@@ -19,3 +19,14 @@ PY
 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1
+# pyramid + depth tracker: ours against the reference build, closed-loop drift, launch list,
+# one full capture of the iteration kernel
+timeout 300 python tools/track_bench.py > gpurun_out/track_bench.json 2> gpurun_out/track_bench.err
+timeout 300 python tools/tracked_orbit.py --frames 36 > gpurun_out/tracked_orbit.json 2> gpurun_out/tracked_orbit.err
+python tools/track_once.py > gpurun_out/track_once.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/track_launches.csv \
+    python tools/track_once.py > gpurun_out/track_ncu_list.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"vk_track_iter_kernel|vk_downsample_frame_kernel" -s 4 -c 3 \
+    -o gpurun_out/prof_track -f python tools/track_once.py > gpurun_out/track_ncu_full.log 2>&1
+ncu -i gpurun_out/prof_track.ncu-rep --page raw --csv > gpurun_out/track_ncu_full_raw.csv 2>/dev/null
+tail -2 gpurun_out/track_ncu_full.log

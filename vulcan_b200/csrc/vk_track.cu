@@ -109,19 +109,30 @@ struct TrackState {
 };
 static_assert(sizeof(TrackState) <= VK_TRACK_STATE_FLOATS * sizeof(float), "VK_TRACK_STATE_FLOATS too small");
 
+// depth and normal of one frame pixel
+struct FramePixel { float d, nx, ny, nz; };
+__device__ __forceinline__ FramePixel load_frame_pixel(const TrackImages& im, int x, int y) {
+  FramePixel p = {0.0f, 0.0f, 0.0f, 0.0f};
+  if (x < im.w && y < im.h) {
+    const size_t index = (size_t)y * im.w + x;
+    p.d = __ldg(im.depth + index);
+    p.nx = __ldg(im.normal + 3 * index);
+    p.ny = __ldg(im.normal + 3 * index + 1);
+    p.nz = __ldg(im.normal + 3 * index + 2);
+  }
+  return p;
+}
+
 // Evaluate<> (src/depth_tracker.cu:16-99).  Returns false when the pixel contributes nothing
 // (residual 0, Jacobian 0).
 template <bool F>
 __device__ __forceinline__ bool track_evaluate(const TrackImages& im, const Mat34& Twc, const Mat34& Twm,
                                                const Mat34& Tmw, const Unprojector& up, const Unprojector& kup, int x,
-                                               int y, float& residual, float* J) {
-  const int index = y * im.w + x;
-  // the frame's depth and normal are fetched together, the keyframe's depth and normal likewise (the
-  // normal speculatively: kindex is inside the image once the bounds test passed): two dependent round
-  // trips per pixel instead of three
-  const float d = __ldg(im.depth + index);
-  const float fnx = __ldg(im.normal + 3 * (size_t)index), fny = __ldg(im.normal + 3 * (size_t)index + 1),
-              fnz = __ldg(im.normal + 3 * (size_t)index + 2);
+                                               int y, const FramePixel& px, float& residual, float* J) {
+  // the frame's depth and normal are fetched together by the caller (load_frame_pixel, one tile ahead in
+  // the iteration kernel), the keyframe's depth and normal together here (the normal speculatively: kindex
+  // is inside the image once the bounds test passed): two dependent round trips per pixel instead of three
+  const float d = px.d, fnx = px.nx, fny = px.ny, fnz = px.nz;
   if (!(d > 0)) return false;
   const float u = (float)x + 0.5f, v = (float)y + 0.5f;
   // Unproject(u, v, d) = d * Unproject(uv)  (include/vulcan/projection.h:80-101)
@@ -182,7 +193,8 @@ __global__ void __launch_bounds__(256) vk_track_pixels_kernel(TrackImages im, co
   const int n = im.w * im.h;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     float r = 0, J[6] = {0, 0, 0, 0, 0, 0};
-    const bool ok = track_evaluate<F>(im, Twc, Twm, Tmw, up, kup, i % im.w, i / im.w, r, J);
+    const FramePixel px = load_frame_pixel(im, i % im.w, i / im.w);
+    const bool ok = track_evaluate<F>(im, Twc, Twm, Tmw, up, kup, i % im.w, i / im.w, px, r, J);
     if (MODE == 0) {
       out[i] = ok ? r : 0.0f;
     } else {
@@ -360,11 +372,18 @@ __global__ void __launch_bounds__(256, 3) vk_track_iter_kernel(TrackImages im, T
   // 32 x 8 pixel tiles per CTA pass: neighbouring lanes gather neighbouring keyframe pixels
   const int tiles_x = (im.w + 31) >> 5, tiles_y = (im.h + 7) >> 3;
   const int lx = threadIdx.x & 31, ly = threadIdx.x >> 5;
-  for (int t = blockIdx.x; t < tiles_x * tiles_y; t += gridDim.x) {
+  const int tiles = tiles_x * tiles_y;
+  // the frame pixel of the next pass is fetched before the current one is evaluated
+  FramePixel px = {0.0f, 0.0f, 0.0f, 0.0f};
+  if ((int)blockIdx.x < tiles) px = load_frame_pixel(im, (blockIdx.x % tiles_x) * 32 + lx, (blockIdx.x / tiles_x) * 8 + ly);
+  for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
     const int x = (t % tiles_x) * 32 + lx, y = (t / tiles_x) * 8 + ly;
+    const FramePixel cur = px;
+    const int tn = t + gridDim.x;
+    if (tn < tiles) px = load_frame_pixel(im, (tn % tiles_x) * 32 + lx, (tn / tiles_x) * 8 + ly);
     if (x >= im.w || y >= im.h) continue;
     float r = 0, J[6];
-    if (!track_evaluate<F>(im, Twc, Twm, Tmw, up, kup, x, y, r, J)) continue;
+    if (!track_evaluate<F>(im, Twc, Twm, Tmw, up, kup, x, y, cur, r, J)) continue;
 #pragma unroll
     for (int a = 0, k = 0; a < P; ++a)
 #pragma unroll
