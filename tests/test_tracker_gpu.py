@@ -35,7 +35,7 @@ def math(request):
     H.oracle_lib().vo_set_math_mode(0)
 
 
-@pytest.mark.parametrize("size", [(160, 120), (640, 480)])
+@pytest.mark.parametrize("size", [(160, 120), (640, 480), (1920, 1080), (36, 20)])
 def test_downsample_matches_reference(size, math):
     import vulcan_b200 as vb
     _need_ref(math)
@@ -69,7 +69,7 @@ def test_downsample_rejects_odd_sizes():
         f.Downsample(vb.Frame())
 
 
-@pytest.mark.parametrize("size", [(160, 120), (640, 480)])
+@pytest.mark.parametrize("size", [(160, 120), (640, 480), (333, 201), (1920, 1080)])  # ragged: partial tiles
 def test_residuals_and_jacobian_match_reference(size, math):
     import vulcan_b200 as vb
     _need_ref(math)
@@ -109,7 +109,7 @@ def test_residuals_and_jacobian_match_reference(size, math):
 
 
 @pytest.mark.parametrize("trans", [1, 0])
-@pytest.mark.parametrize("size", [(160, 120), (640, 480)])
+@pytest.mark.parametrize("size", [(160, 120), (640, 480), (333, 201), (1920, 1080)])
 def test_system_matches_reference(size, trans, math):
     import vulcan_b200 as vb
     _need_ref(math)
