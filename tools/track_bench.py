@@ -52,6 +52,17 @@ def main():
         res["ours_track20_ms"] = med(ours_track)
         res["ours_track20_iterations"] = t.iterations_
         res["ours_track20_err"] = H.pose_error(frame.depth_to_world_transform.raw32(), s["frame_pose"])
+        # the same call at the C ABI with the descriptors built once (what a C++ caller pays; the Python
+        # mirror above rebuilds both vkFrame structs on every call)
+        import ctypes as C
+        kc, fc = key.to_c(), frame.to_c()
+        start_c = start.to_c()
+        it, norm = C.c_int(0), C.c_float(0)
+
+        def cabi_track():
+            fc.depth_to_world = start_c
+            vb.lib.vk_track_depth(C.byref(kc), C.byref(fc), 1, 20, t._workspace.data_ptr(), C.byref(it), C.byref(norm), None)
+        res["ours_track20_cabi_ms"] = med(cabi_track)
         p = vb.PyramidTracker()
         p.SetKeyframe(key)
 
