@@ -372,6 +372,18 @@ int vk_track_system(const vkFrame* keyframe, const vkFrame* frame, int translati
 int vk_track_depth(const vkFrame* keyframe, vkFrame* frame, int translation_enabled, int max_iterations,
                    float* workspace, int* iterations, float* last_update_norm, void* stream);
 
+/* ---- surface points (first slice; no finished reference counterpart) ------- */
+
+/* Marching-cubes vertices of the whole volume: the zero crossings of the TSDF on the three lattice
+ * edges every voxel owns (+x, +y, +z neighbour - edges 0, 3, 8 of its cube, the edge set of
+ * src/extractor.cu:52-117), over all allocated blocks and across block faces, both end points
+ * observed (distance_weight > 0) and of different sign; position and colour interpolated linearly.
+ * points / colors: device float[3 * capacity] (colors may be NULL); *count (device int) receives the
+ * number of crossings found, which may exceed capacity (then only the first `capacity` appended
+ * are stored: call again with a larger buffer).  Order is arbitrary. */
+int vk_extract_points(const vkVolume* v, float* points, float* colors, int capacity, int* count,
+                      void* stream);
+
 /* ---- misc -------------------------------------------------------------------- */
 
 /* Library version and the number of kernels launched by this library since load

@@ -1153,3 +1153,51 @@ int vo_track_depth(float* T, const float* Tk, const float* key_depth, const floa
 void vo_track_apply_update(const float* update6, float* T) { track_apply_update(update6, T); }
 
 }  // extern "C"
+
+// ---- surface points (first slice) -------------------------------------------
+// The reference's extractor is unfinished (src/extractor.cu:386 emits edge midpoints of one block, the
+// index / face kernels at :391-413 are empty), so this restates the DEFINITION used by
+// vulcan_b200/csrc/vk_extract.cu, not reference code: zero crossings of the TSDF on the three lattice
+// edges each voxel owns (+x, +y, +z neighbour; edges 0, 3, 8 of its cube, src/extractor.cu:52-117), both
+// end points observed (distance_weight > 0) and of different sign (`distance > 0`, src/extractor.cu:199),
+// position and colour interpolated linearly.  "Parity unpinned" with respect to the reference.
+extern "C" long long vo_extract_points(void* h, float* points, float* colors, long long capacity) {
+  Volume* v = (Volume*)h;
+  const float l = v->voxel_length, L = 8 * v->voxel_length;
+  long long n = 0;
+  Fetch f = {0, 0};
+  for (int ei = 0; ei < v->B_; ++ei) {
+    const HashEntry& e = v->entries[ei];
+    if (e.data == -1) continue;
+    const int bx = e.block[0], by = e.block[1], bz = e.block[2];
+    for (int t = 0; t < 512; ++t) {
+      const int vx = t & 7, vy = (t >> 3) & 7, vz = t >> 6;
+      const Voxel& a = v->voxels[(long long)e.data * 512 + t];
+      if (a.distance_weight <= 0) continue;
+      const float base[3] = {(float)bx * L + ((float)vx + 0.5f) * l, (float)by * L + ((float)vy + 0.5f) * l,
+                             (float)bz * L + ((float)vz + 0.5f) * l};
+      for (int ax = 0; ax < 3; ++ax) {
+        const int nx = vx + (ax == 0), ny = vy + (ax == 1), nz = vz + (ax == 2);
+        int data = e.data;
+        if (nx > 7 || ny > 7 || nz > 7) {
+          const int cx = bx + (nx >> 3), cy = by + (ny >> 3), cz = bz + (nz >> 3);
+          if (cx > 32767 || cy > 32767 || cz > 32767) continue;
+          data = find_data(v, cx, cy, cz, f);
+          if (data == -1) continue;
+        }
+        const Voxel& b = v->voxels[(long long)data * 512 + (((nz & 7) << 6) | ((ny & 7) << 3) | (nx & 7))];
+        if (b.distance_weight <= 0 || ((a.distance > 0) == (b.distance > 0))) continue;
+        const float tt = a.distance / (a.distance - b.distance);
+        if (n < capacity) {
+          float* o = points + 3 * n;
+          o[0] = base[0]; o[1] = base[1]; o[2] = base[2];
+          o[ax] = base[ax] + tt * l;
+          if (colors)
+            for (int c = 0; c < 3; ++c) colors[3 * n + c] = a.color[c] + tt * (b.color[c] - a.color[c]);
+        }
+        ++n;
+      }
+    }
+  }
+  return n;
+}

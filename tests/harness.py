@@ -63,6 +63,8 @@ def oracle_lib():
         lib.vo_compute_normals.argtypes = [_P, _P, _P, _I, _I]
         lib.vo_compute_points.argtypes = [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I]
         lib.vo_trace.argtypes = [_P, _P, _P, _I, _I, _F, _F, _P, _P, _P, _P]
+        lib.vo_extract_points.restype = C.c_longlong
+        lib.vo_extract_points.argtypes = [_P, _P, _P, C.c_longlong]
         lib.vo_downsample.argtypes = [_P, _I, _I, _I, _I, _P]
         lib.vo_track_pixels.argtypes = [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _I, _I, _I, _P, _P]
         lib.vo_track_system.argtypes = [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _I, _I, _I, _P, _P]
@@ -787,3 +789,42 @@ def ours_track_frames(s, pose32):
         f.depth_to_world_transform = vb.Transform(p[:16].reshape(4, 4).T.copy(), p[16:].reshape(4, 4).T.copy())
         frames.append(f)
     return frames
+
+
+# ---- surface points ---------------------------------------------------------------
+
+def oracle_volume_for(scn):
+    """The oracle volume after the scenario's frames (run_oracle without the trace)."""
+    ov = OracleVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"])
+    ov.lib.vo_set_math_mode(scn.get("math", 0))
+    for fr in scn["frames"]:
+        ov.set_view_converged(fr["depth"], scn["K"], fr["T"])
+        if scn["mode"] == "color":
+            ov.integrate_color(fr["depth"], scn["K"], fr["T"], fr["color"], scn["K"], scn["Tcd"])
+        else:
+            ov.integrate_depth(fr["depth"], scn["K"], fr["T"])
+    assert ov.dropped() == 0
+    return ov
+
+
+def oracle_extract_points(ov):
+    n = ov.lib.vo_extract_points(ov.h, None, None, 0)
+    pts = np.zeros((n, 3), dtype=np.float32)
+    col = np.zeros((n, 3), dtype=np.float32)
+    assert ov.lib.vo_extract_points(ov.h, _ptr(pts), _ptr(col), n) == n
+    return pts, col
+
+
+def sorted_rows(pts, col):
+    """Rows of [points | colours] in a canonical order (bit patterns), for set comparison."""
+    rows = np.concatenate([pts, col], axis=1).astype(np.float32).view(np.uint32)
+    order = np.lexsort(rows.T[::-1])
+    return rows[order]
+
+
+def sphere_plane_distance(pts, sphere_c=(0.0, 0.0, 2.0), sphere_r=0.5, plane_y=0.5):
+    """Distance of points to the analytic sphere-on-plane surface of synth.render_sphere_plane."""
+    p = pts.astype(np.float64)
+    ds = np.abs(np.linalg.norm(p - np.asarray(sphere_c), axis=1) - sphere_r)
+    dp = np.abs(p[:, 1] - plane_y)
+    return np.minimum(ds, dp)

@@ -1,0 +1,35 @@
+"""Surface points on the CPU oracle: the extracted marching-cubes vertices lie on the
+analytic surface the depth maps were rendered from.  (The reference's extractor is unfinished - there are
+no reference outputs to pin against; see oracle/vulcan_oracle.cpp: vo_extract_points.)"""
+import numpy as np
+
+import harness as H
+
+
+def test_oracle_points_lie_on_the_scene_surface():
+    scn = H.make_scenario("tiny", (0, 6), "depth", 5.0)
+    ov = H.oracle_volume_for(scn)
+    pts, col = H.oracle_extract_points(ov)
+    assert len(pts) > 2000
+    dist = H.sphere_plane_distance(pts)
+    # zero crossings of a projective TSDF fused from nearest-pixel depth samples: accurate to a fraction of
+    # the pixel footprint at the scene's depth (2.5 m / f), far inside the truncation band
+    footprint = 2.5 / float(scn["K"][0])
+    assert np.median(dist) < 0.25 * footprint
+    assert np.quantile(dist, 0.95) < 1.0 * footprint
+    assert dist.max() < scn["trunc"]
+    # one point per owned edge at most: no duplicates
+    assert len(np.unique(H.sorted_rows(pts, col), axis=0)) == len(pts)
+
+
+def test_oracle_extract_capacity_and_empty_volume():
+    ov = H.OracleVolume(2048, 512, 0.02, 0.1)
+    assert ov.lib.vo_extract_points(ov.h, None, None, 0) == 0
+    scn = H.make_scenario("micro", (0,), "color", 1.2)
+    ov = H.oracle_volume_for(scn)
+    n = ov.lib.vo_extract_points(ov.h, None, None, 0)
+    pts = np.zeros((10, 3), dtype=np.float32)
+    assert ov.lib.vo_extract_points(ov.h, H._ptr(pts), None, 10) == n and n > 10   # counts on, stores 10
+    full, col = H.oracle_extract_points(ov)
+    assert np.array_equal(full[:10], pts)
+    assert (col >= 0).all() and (col <= 1).all()

@@ -604,3 +604,66 @@ class PyramidTracker:
         frame.depth_to_world_transform = half_frame.depth_to_world_transform
         t.SetKeyframe(self.keyframe_)
         t.Track(frame)
+
+
+class Mesh:
+    """include/vulcan/mesh.h:11-21: points (N,3), faces (F,3); `colors` (N,3) is an addition."""
+
+    def __init__(self):
+        self.points = np.zeros((0, 3), dtype=np.float32)
+        self.colors = np.zeros((0, 3), dtype=np.float32)
+        self.faces = np.zeros((0, 3), dtype=np.int32)
+
+
+class Extractor:
+    """Extractor (include/vulcan/extractor.h, src/extractor.cu:660-740).  The reference's extractor is
+    unfinished (edge midpoints of one block, no faces); this one returns the marching-cubes vertices of
+    the whole volume (vk_extract_points) and, like the reference today, no faces."""
+
+    def __init__(self, volume):
+        self.volume_ = volume
+
+    def GetVolume(self):
+        return self.volume_
+
+    def Extract(self, mesh=None, capacity=1 << 20):
+        mesh = mesh if mesh is not None else Mesh()
+        while True:
+            pts = torch.empty((capacity, 3), dtype=torch.float32, device="cuda")
+            col = torch.empty((capacity, 3), dtype=torch.float32, device="cuda")
+            cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+            check(lib.vk_extract_points(C.byref(self.volume_._v), pts.data_ptr(), col.data_ptr(), capacity,
+                                        cnt.data_ptr(), _stream()), "Extract")
+            n = int(cnt.item())
+            if n <= capacity:
+                break
+            capacity = n
+        mesh.points = pts[:n].cpu().numpy()
+        mesh.colors = col[:n].cpu().numpy()
+        mesh.faces = np.zeros((0, 3), dtype=np.int32)
+        return mesh
+
+
+class Exporter:
+    """Exporter (include/vulcan/exporter.h, src/exporter.cpp:19-71): ASCII PLY with the reference's header
+    (x y z, uchar red green blue, face list).  Colours are the fused voxel colours (the reference writes a
+    z ramp marked REMOVE)."""
+
+    def __init__(self, file):
+        self.file_ = file
+
+    def GetFile(self):
+        return self.file_
+
+    def Export(self, mesh):
+        rgb = np.clip(np.rint(mesh.colors * 255.0), 0, 255).astype(np.uint8) if len(mesh.colors) == len(mesh.points) \
+            else np.full((len(mesh.points), 3), 128, dtype=np.uint8)
+        with open(self.file_, "w") as f:
+            f.write("ply\nformat ascii 1.0\nelement vertex %d\n" % len(mesh.points))
+            f.write("property float x\nproperty float y\nproperty float z\n")
+            f.write("property uchar red\nproperty uchar green\nproperty uchar blue\n")
+            f.write("element face %d\nproperty list uchar int vertex_indices\nend_header\n" % len(mesh.faces))
+            for p, c in zip(mesh.points, rgb):
+                f.write("%.9g %.9g %.9g %d %d %d\n" % (p[0], p[1], p[2], c[0], c[1], c[2]))
+            for t in mesh.faces:
+                f.write("3 %d %d %d\n" % (t[0], t[1], t[2]))
