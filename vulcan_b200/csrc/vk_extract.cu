@@ -14,7 +14,8 @@
 // One CTA takes 512 hash entries at a time, lists the allocated ones in shared memory, and for each
 // stages the block's 512 voxels (10 KB, coalesced 4-byte words) in shared memory; thread t owns voxel t.
 // Neighbours inside the block come from the tile, neighbours across a face from a hash lookup of the
-// adjacent block.  Points are appended with one atomicAdd per emitting thread; order is arbitrary.
+// adjacent block.  Points are appended with one atomicAdd per block (CTA-wide scan of the per-voxel
+// counts); the order of blocks in the output is arbitrary.
 #include <cuda_runtime.h>
 #include "vk_launch.h"
 #include "vk_math.cuh"
@@ -48,6 +49,8 @@ __global__ void __launch_bounds__(512) vk_extract_points_kernel(ExtractParams p)
   __shared__ uint32_t tile[VK_BLOCK_VOXELS * 5];
   __shared__ int list[512];
   __shared__ int list_count;
+  __shared__ int warp_totals[16];
+  __shared__ int block_base;
   const int tid = threadIdx.x;
   const int vx = tid & 7, vy = (tid >> 3) & 7, vz = tid >> 6;
   const int chunks = (p.total_entries + 511) / 512;
@@ -58,64 +61,108 @@ __global__ void __launch_bounds__(512) vk_extract_points_kernel(ExtractParams p)
     if (ei < p.total_entries && __ldg(&p.entries[ei].data) != -1) list[atomicAdd(&list_count, 1)] = ei;
     __syncthreads();
     const int n = list_count;
+    // the tile of block li + 1 is fetched into registers (five independent 4-byte words per thread) while
+    // block li is processed, so the DRAM latency of a block hides behind its predecessor's work
+    uint32_t r[5];
+    int4 e_next = make_int4(0, 0, -1, -1);
+    if (n > 0) {
+      e_next = ld_entry(p.entries + list[0]);
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(p.voxels + (size_t)e_next.z * VK_BLOCK_VOXELS);
+#pragma unroll
+      for (int k = 0; k < 5; ++k) r[k] = __ldg(src + tid + 512 * k);
+    }
     for (int li = 0; li < n; ++li) {
-      const int4 e = ld_entry(p.entries + list[li]);
+      const int4 e = e_next;
       int bx, by, bz;
       entry_origin(e, bx, by, bz);
-      const uint32_t* src = reinterpret_cast<const uint32_t*>(p.voxels + (size_t)e.z * VK_BLOCK_VOXELS);
       __syncthreads();  // the previous block's tile is no longer read
-      for (int i = tid; i < VK_BLOCK_VOXELS * 5; i += 512) tile[i] = __ldg(src + i);
+#pragma unroll
+      for (int k = 0; k < 5; ++k) tile[tid + 512 * k] = r[k];
       __syncthreads();
+      if (li + 1 < n) {
+        e_next = ld_entry(p.entries + list[li + 1]);
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(p.voxels + (size_t)e_next.z * VK_BLOCK_VOXELS);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) r[k] = __ldg(src + tid + 512 * k);
+      }
       const float d0 = __uint_as_float(tile[5 * tid]);
       const int w0 = (int)(int16_t)(tile[5 * tid + 4] & 0xffffu);
-      if (w0 <= 0) continue;
       const float c0[3] = {__uint_as_float(tile[5 * tid + 1]), __uint_as_float(tile[5 * tid + 2]),
                            __uint_as_float(tile[5 * tid + 3])};
       // voxel centre: L * b + l * (v + 0.5)   (src/depth_integrator.cu:44-52)
       const float base[3] = {add(mul((float)bx, p.block_length), mul(add((float)vx, 0.5f), p.voxel_length)),
                              add(mul((float)by, p.block_length), mul(add((float)vy, 0.5f), p.voxel_length)),
                              add(mul((float)bz, p.block_length), mul(add((float)vz, 0.5f), p.voxel_length))};
-      float out[3][6];
-      int emitted = 0;
+      float tpar[3];      // interpolation parameter per axis
+      float ncol[3][3];   // neighbour colour per axis
+      unsigned mask = 0;  // axes with a crossing
+      if (w0 > 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+          const int nx = vx + (a == 0), ny = vy + (a == 1), nz = vz + (a == 2);
+          Sample s;
+          if (nx < 8 && ny < 8 && nz < 8) {
+            const int j = (nz << 6) | (ny << 3) | nx;
+            s.d = __uint_as_float(tile[5 * j]);
+            s.r = __uint_as_float(tile[5 * j + 1]);
+            s.g = __uint_as_float(tile[5 * j + 2]);
+            s.b = __uint_as_float(tile[5 * j + 3]);
+            s.w = (int)(int16_t)(tile[5 * j + 4] & 0xffffu);
+          } else {
+            const int data = extract_lookup(p, bx + (nx >> 3), by + (ny >> 3), bz + (nz >> 3));
+            if (data == -1) continue;
+            const int j = ((nz & 7) << 6) | ((ny & 7) << 3) | (nx & 7);
+            const vkVoxel* q = p.voxels + (size_t)data * VK_BLOCK_VOXELS + j;
+            s.d = __ldg(&q->distance);
+            s.r = __ldg(&q->color[0]);
+            s.g = __ldg(&q->color[1]);
+            s.b = __ldg(&q->color[2]);
+            s.w = (int)__ldg(&q->distance_weight);
+          }
+          if (s.w <= 0 || ((d0 > 0) == (s.d > 0))) continue;
+          tpar[a] = fdiv(d0, sub(d0, s.d));
+          ncol[a][0] = s.r; ncol[a][1] = s.g; ncol[a][2] = s.b;
+          mask |= 1u << a;
+        }
+      }
+      // one atomicAdd per block: exclusive scan of the per-thread counts over the CTA
+      const int mine = __popc(mask);
+      int incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += up;
+      }
+      if ((tid & 31) == 31) warp_totals[tid >> 5] = incl;
+      __syncthreads();
+      if (tid < 32) {
+        int wt = tid < 16 ? warp_totals[tid] : 0;
+        int wi = wt;
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+          const int up = __shfl_up_sync(0xffffffffu, wi, o);
+          if (tid >= o) wi += up;
+        }
+        if (tid < 16) warp_totals[tid] = wi - wt;  // exclusive offset of the warp
+        if (tid == 15) block_base = wi ? atomicAdd(p.count, wi) : 0;
+      }
+      __syncthreads();
+      int at = block_base + warp_totals[tid >> 5] + incl - mine;
 #pragma unroll
       for (int a = 0; a < 3; ++a) {
-        const int nx = vx + (a == 0), ny = vy + (a == 1), nz = vz + (a == 2);
-        Sample s;
-        if (nx < 8 && ny < 8 && nz < 8) {
-          const int j = (nz << 6) | (ny << 3) | nx;
-          s.d = __uint_as_float(tile[5 * j]);
-          s.r = __uint_as_float(tile[5 * j + 1]);
-          s.g = __uint_as_float(tile[5 * j + 2]);
-          s.b = __uint_as_float(tile[5 * j + 3]);
-          s.w = (int)(int16_t)(tile[5 * j + 4] & 0xffffu);
-        } else {
-          const int data = extract_lookup(p, bx + (nx >> 3), by + (ny >> 3), bz + (nz >> 3));
-          if (data == -1) continue;
-          const int j = ((nz & 7) << 6) | ((ny & 7) << 3) | (nx & 7);
-          const vkVoxel* q = p.voxels + (size_t)data * VK_BLOCK_VOXELS + j;
-          s.d = __ldg(&q->distance);
-          s.r = __ldg(&q->color[0]);
-          s.g = __ldg(&q->color[1]);
-          s.b = __ldg(&q->color[2]);
-          s.w = (int)__ldg(&q->distance_weight);
+        if (!((mask >> a) & 1u)) continue;
+        if (at < p.capacity) {
+          const size_t o = 3 * (size_t)at;
+          p.points[o] = a == 0 ? add(base[0], mul(tpar[0], p.voxel_length)) : base[0];
+          p.points[o + 1] = a == 1 ? add(base[1], mul(tpar[1], p.voxel_length)) : base[1];
+          p.points[o + 2] = a == 2 ? add(base[2], mul(tpar[2], p.voxel_length)) : base[2];
+          if (p.colors) {
+            p.colors[o] = add(c0[0], mul(tpar[a], sub(ncol[a][0], c0[0])));
+            p.colors[o + 1] = add(c0[1], mul(tpar[a], sub(ncol[a][1], c0[1])));
+            p.colors[o + 2] = add(c0[2], mul(tpar[a], sub(ncol[a][2], c0[2])));
+          }
         }
-        if (s.w <= 0 || ((d0 > 0) == (s.d > 0))) continue;
-        const float t = fdiv(d0, sub(d0, s.d));
-        float* o = out[emitted++];
-        o[0] = base[0]; o[1] = base[1]; o[2] = base[2];
-        o[a] = add(base[a], mul(t, p.voxel_length));
-        o[3] = add(c0[0], mul(t, sub(s.r, c0[0])));
-        o[4] = add(c0[1], mul(t, sub(s.g, c0[1])));
-        o[5] = add(c0[2], mul(t, sub(s.b, c0[2])));
-      }
-      if (emitted) {
-        const int at = atomicAdd(p.count, emitted);
-        for (int k = 0; k < emitted; ++k) {
-          if (at + k >= p.capacity) break;
-          const size_t o = 3 * (size_t)(at + k);
-          p.points[o] = out[k][0]; p.points[o + 1] = out[k][1]; p.points[o + 2] = out[k][2];
-          if (p.colors) { p.colors[o] = out[k][3]; p.colors[o + 1] = out[k][4]; p.colors[o + 2] = out[k][5]; }
-        }
+        ++at;
       }
     }
     __syncthreads();
