@@ -9,6 +9,8 @@
 #include <vulcan/depth_tracker.h>
 #include <vulcan/device.h>
 #include <vulcan/exception.h>
+#include <vulcan/exporter.h>
+#include <vulcan/extractor.h>
 #include <vulcan/frame.h>
 #include <vulcan/hash.h>
 #include <vulcan/image.h>
@@ -17,6 +19,7 @@
 #include <vulcan/light_integrator.h>
 #include <vulcan/math.h>
 #include <vulcan/matrix.h>
+#include <vulcan/mesh.h>
 #include <vulcan/projection.h>
 #include <vulcan/pyramid_tracker.h>
 #include <vulcan/tracer.h>

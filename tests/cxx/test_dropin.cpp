@@ -11,6 +11,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <string>
 #include <vector>
 
 using namespace vulcan;
@@ -366,12 +367,60 @@ static void TestDepthTrackerWall()
   CHECK(thrown);
 }
 
+// Extractor / Exporter on the fused wall at 1.5 m: every vertex lies on the wall, carries the wall's
+// colour, and the PLY has the reference's header (src/exporter.cpp:24-35).
+static void TestExtractWall()
+{
+  const int w = 160, h = 120;
+  const Vector3f color(0.1f, 0.2f, 0.3f);
+  Frame frame;
+  frame.depth_projection.SetFocalLength(80, 80);
+  frame.depth_projection.SetCenterPoint(80, 60);
+  frame.color_projection = frame.depth_projection;
+  frame.depth_image = ConstantDepth(w, h, 1.5f);
+  frame.color_image = ConstantColor(w, h, color);
+  auto volume = std::make_shared<Volume>(16384, 4096);
+  volume->SetTruncationLength(0.04f);
+  volume->SetVoxelLength(0.008f);
+  volume->SetView(frame);
+  ColorIntegrator integrator(volume);
+  integrator.Integrate(frame);
+
+  Mesh mesh;
+  Extractor extractor(volume);
+  extractor.Extract(mesh);
+  CHECK(mesh.points.size() > 10000 && mesh.colors.size() == mesh.points.size() && mesh.faces.empty());
+  int on_wall = 0;
+  for (size_t i = 0; i < mesh.points.size(); ++i)
+  {
+    if (std::fabs(mesh.points[i][2] - 1.5f) < 1e-4f) ++on_wall;
+    CHECK_NEAR(mesh.colors[i][0], color[0], 1e-5);
+    CHECK_NEAR(mesh.colors[i][2], color[2], 1e-5);
+  }
+  CHECK(on_wall == (int)mesh.points.size());
+
+  const std::string file = "/tmp/vulcan_b200_test_wall.ply";
+  Exporter exporter(file);
+  exporter.Export(mesh);
+  FILE* f = fopen(file.c_str(), "r");
+  CHECK(f != nullptr);
+  char line[256];
+  CHECK(fgets(line, sizeof(line), f) && std::string(line) == "ply\n");
+  CHECK(fgets(line, sizeof(line), f) && std::string(line) == "format ascii 1.0\n");
+  size_t vertices = 0;
+  CHECK(fgets(line, sizeof(line), f) && sscanf(line, "element vertex %zu", &vertices) == 1);
+  CHECK(vertices == mesh.points.size());
+  fclose(f);
+  remove(file.c_str());
+}
+
 int main()
 {
   struct { const char* name; void (*fn)(); } tests[] = {
     {"Volume.Constructor", TestVolumeConstructor}, {"Buffer", TestBuffer}, {"Integrator.Integrate", TestIntegrate},
     {"Tracer.TraceWall", TestTraceWall}, {"Volume.TwoVolumes", TestTwoVolumes},
     {"Frame.Downsample", TestDownsample}, {"DepthTracker.Wall", TestDepthTrackerWall},
+    {"Extractor.Wall", TestExtractWall},
   };
   for (auto& t : tests)
   {

@@ -4,6 +4,7 @@
 // does in the reference (include/vulcan/device.h:14-17).
 #include <vulcan/vulcan.h>
 
+#include <cstdio>
 #include <cstring>
 
 namespace vulcan
@@ -211,6 +212,78 @@ void DepthTracker::ComputeSystem(const Frame& frame, Buffer<float>& hessian, Buf
   const vkFrame key = ToC(*keyframe_), f = ToC(frame);
   VK_ASSERT(vk_track_system(&key, &f, translation_enabled_, workspace_.GetData(), hessian.GetData(),
                             gradient.GetData(), nullptr));
+}
+
+// ---- Extractor / Exporter (src/extractor.cu:660-740, src/exporter.cpp:19-71) ------------------
+
+Extractor::Extractor(std::shared_ptr<const Volume> volume) : volume_(volume)
+{
+  VULCAN_ASSERT(volume_ != nullptr);
+}
+
+void Extractor::Extract(DeviceMesh& mesh) const
+{
+  Buffer<int> count(1);
+  size_t capacity = mesh.points.GetSize() > 0 ? mesh.points.GetSize() : (size_t)1 << 20;
+  for (;;)
+  {
+    mesh.points.Resize(capacity);
+    mesh.colors.Resize(capacity);
+    VK_ASSERT(vk_extract_points(volume_->GetHandle(), reinterpret_cast<float*>(mesh.points.GetData()),
+                                reinterpret_cast<float*>(mesh.colors.GetData()), (int)capacity, count.GetData(),
+                                nullptr));
+    int found = 0;
+    count.CopyToHost(&found);
+    if ((size_t)found <= capacity)
+    {
+      mesh.points.Resize(found);
+      mesh.colors.Resize(found);
+      break;
+    }
+    capacity = found;  // the kernel counted on: run again with room for all
+  }
+  mesh.faces.Resize(0);
+}
+
+void Extractor::Extract(Mesh& mesh) const
+{
+  DeviceMesh device;
+  Extract(device);
+  mesh.points.resize(device.points.GetSize());
+  mesh.colors.resize(device.colors.GetSize());
+  mesh.faces.clear();
+  if (!mesh.points.empty())
+  {
+    device.points.CopyToHost(mesh.points.data());
+    device.colors.CopyToHost(mesh.colors.data());
+  }
+}
+
+Exporter::Exporter(const std::string& file) : file_(file) {}
+
+void Exporter::Export(const Mesh& mesh) const
+{
+  FILE* f = fopen(file_.c_str(), "w");
+  VULCAN_ASSERT_MSG(f != nullptr, "cannot open output file");
+  fprintf(f, "ply\nformat ascii 1.0\nelement vertex %zu\n", mesh.points.size());
+  fprintf(f, "property float x\nproperty float y\nproperty float z\n");
+  fprintf(f, "property uchar red\nproperty uchar green\nproperty uchar blue\n");
+  fprintf(f, "element face %zu\nproperty list uchar int vertex_indices\nend_header\n", mesh.faces.size());
+  const bool colored = mesh.colors.size() == mesh.points.size();
+  for (size_t i = 0; i < mesh.points.size(); ++i)
+  {
+    int rgb[3] = {128, 128, 128};
+    if (colored)
+      for (int c = 0; c < 3; ++c)
+      {
+        const float v = 255.0f * mesh.colors[i][c] + 0.5f;
+        rgb[c] = v < 0 ? 0 : v > 255 ? 255 : (int)v;
+      }
+    fprintf(f, "%.9g %.9g %.9g %d %d %d\n", mesh.points[i][0], mesh.points[i][1], mesh.points[i][2], rgb[0], rgb[1],
+            rgb[2]);
+  }
+  for (const Vector3i& t : mesh.faces) fprintf(f, "3 %d %d %d\n", t[0], t[1], t[2]);
+  fclose(f);
 }
 
 // ---- Volume (src/volume.cu:370-463) ----------------------------------------------------------
