@@ -33,6 +33,34 @@ VOXEL = 0.004
 TRUNC = 5 * VOXEL
 MAIN, EXCESS = 262144, 65536
 METRIC = "voxel-updates/s (visible blocks x 512 per frame / SetView+Integrate+Trace time), 640x480, 4 mm"
+# one description of the workload for BOTH arms (the driver compares the dicts)
+CONFIG = {"workload": "c2_orbit: 640x480 sphere-on-plane depth, 4 mm voxels, Volume(262144,65536), "
+                      "1.2 deg/frame orbit, GT poses; step = SetView (to its fixed point)+DepthIntegrate+Trace",
+          "l2": "256 MiB device memset between steps, outside the per-step CUDA events"}
+
+
+def traffic_from_profiles(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the newest committed
+    `ncu --set full` summary under profiles/ (rNN_ncu_full_summary.csv); (bytes, file) or (None, None)."""
+    import csv
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_summary.csv")), reverse=True):
+        try:
+            with open(path) as f:
+                for row in csv.DictReader(f):
+                    if kernel in row.get("Kernel Name", ""):
+                        rd = [v for k, v in row.items() if k.startswith("dram__bytes_read.sum")]
+                        wr = [v for k, v in row.items() if k.startswith("dram__bytes_write.sum")]
+                        unit = [k for k in row if k.startswith("dram__bytes_read.sum")][0]
+                        scale = {"[Mbyte]": 1e6, "[Gbyte]": 1e9, "[Kbyte]": 1e3, "[byte]": 1.0}[unit.split()[-1]]
+                        return (float(rd[0]) + float(wr[0])) * scale, os.path.relpath(path, ROOT)
+        except Exception:
+            continue
+    return None, None
+
+
+SHARDING = ("blocks by brick hash (8^3-block bricks); a rank stores and integrates only the blocks it owns; "
+            "ray cast: see DESIGN.md 5")
 
 
 def load_peaks():
@@ -246,12 +274,13 @@ def run_ours(args, rank, world):
         vis_total = float(sum(counts))
         ab = 40.0 * updated_timed + 20.0 * vis_total + 4.0 * W * H * args.steps
         gbs = ab / (int_ms * 1e-3) / 1e9
+        traffic, traffic_src = traffic_from_profiles("vk_integrate_kernel<0")
         roof = {"bound": "hbm", "kernel": "vk_integrate_kernel<MODE_DEPTH>", "achieved": gbs,
                 "peak": peaks["hbm_gbs"], "peak_source": which, "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
                 "frac_of_spec_8000": gbs / 8000.0,
-                # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel in the committed
-                # `ncu --set full` capture of this command (profiles/r01_ncu_full_summary.csv: 106.58 + 42.01 MB)
-                "traffic": 148.60e6, "traffic_source": "profiles/r01_ncu_full_summary.csv",
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel, read from the
+                # committed `ncu --set full` capture of this command
+                "traffic": traffic, "traffic_source": traffic_src,
                 "algorithmic_bytes_per_launch": ab / args.steps,
                 "updated_voxels_per_launch": updated_timed / args.steps,
                 "launch_ms": int_ms / args.steps}
@@ -348,13 +377,8 @@ def run_ours(args, rank, world):
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": "c2_orbit: 640x480 sphere-on-plane depth, 4 mm voxels, Volume(262144,65536), "
-                               "1.2 deg/frame orbit, GT poses; step = SetView(fixed point)+DepthIntegrate+Trace",
-                   "l2": "256 MiB device memset between steps, outside the per-step CUDA events",
-                   "sharding": "none" if world == 1 else "blocks by brick hash (8^3-block bricks, a rank stores and integrates only the blocks it owns); each rank "
-                                                         "ray-casts a band of rows reading remote blocks through peer memory "
-                                                         "(NVLink), NCCL min all-reduce of the ray-bounds grid + all-gather of "
-                                                         "the bands"},
+        "config": dict(CONFIG),
+        "sharding": "none" if world == 1 else SHARDING,
         "phases": {"setview_ms": set_ms / args.steps, "integrate_ms": int_ms / args.steps,
                    "trace_ms": trc_ms / args.steps,
                    "integrate_voxel_updates_per_s": total_units / (int_ms * 1e-3),
@@ -456,10 +480,8 @@ def run_reference(args):
         "metric": METRIC, "value": units / (tot_ms * 1e-3), "unit": "voxel-updates/s", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "c2_orbit: 640x480 sphere-on-plane depth, 4 mm voxels, Volume(262144,65536), "
-                               "1.2 deg/frame orbit, GT poses; step = SetView (repeated until the visible count is "
-                               "stable)+DepthIntegrate+Trace",
-                   "l2": "256 MiB device memset between steps, outside the per-step CUDA events"},
+        "config": dict(CONFIG),
+        "setview": "Volume::SetView repeated until the visible count is stable (what the reference's callers do)",
         "phases": {"setview_ms": set_ms / args.steps, "integrate_ms": int_ms / args.steps,
                    "trace_ms": trc_ms / args.steps, "setview_passes_mean": float(np.mean(passes)),
                    "integrate_voxel_updates_per_s": units / (int_ms * 1e-3),
@@ -511,6 +533,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-variant", default="release", choices=["release", "asshipped"],
+                    help="reference arm: the -O3 -DNDEBUG build (the bar) or the reference's default build without "
+                         "NDEBUG (a device synchronisation after every launch), timed once for the record")
     ap.add_argument("--pipeline-depth", type=int, default=3,
                     help="frames in flight in the end-to-end leg (FramePipeline); the host takes frame k-depth+1")
     args = ap.parse_args()
@@ -522,7 +547,10 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
+        if args.ref_variant == "asshipped":
+            os.environ["VULCAN_REF_VARIANT"] = "asshipped"
         line = run_reference(args)
+        line["ref_build"] = args.ref_variant
         if "unavailable" not in line and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line))

@@ -400,8 +400,12 @@ int vk_get_default_math_mode(void);
 /* Division by loop-invariant divisors (block length, voxel length, truncation length, image
  * size) uses a reciprocal + one FMA residual step instead of the IEEE division sequence, after
  * the library has checked on the device, for that divisor, that the result equals __fdiv_rn for
- * all 2^32 dividends (cached per value).  Returns 1 if the fast path is proven for d, 0 if the
- * library will use plain IEEE division for it. */
+ * every dividend the fast path is used on (all 2^24 mantissas / signs of one binade - inside the
+ * guarded exponent range both sequences scale exactly with the dividend's exponent; ~20 us, cached
+ * per value).  The first use of a divisor value synchronises `stream`, so callers that capture CUDA
+ * graphs or stream frames call this once per length when a volume is configured (the C++ and Python
+ * layers do so in Set*Length).  Returns 1 if the fast path is proven for d, 0 if the library will
+ * use plain IEEE division for it. */
 int vk_div_prepare(float d, void* stream);
 
 #ifdef __cplusplus

@@ -17,6 +17,7 @@
 #include <vulcan/light_integrator.h>
 #include <vulcan/light.h>
 #include <vulcan/tracer.h>
+#include <vulcan/tracer.cuh>
 #include <vulcan/depth_tracker.h>
 #include <cstring>
 #include <memory>
@@ -38,12 +39,19 @@ struct OpenVolume : public Volume {
   const void* visibility() const { return block_visibility_.GetData(); }
 };
 
+struct OpenTracer : public Tracer {
+  explicit OpenTracer(std::shared_ptr<const Volume> v) : Tracer(v) {}
+  const void* bounds() const { return bounds_.GetData(); }
+  const void* patches() const { return patches_.GetData(); }
+  int patch_count() const { return (int)patches_.GetSize(); }
+};
+
 struct Ref {
   std::shared_ptr<OpenVolume> volume;
   std::unique_ptr<DepthIntegrator> depth_integrator;
   std::unique_ptr<ColorIntegrator> color_integrator;
   std::unique_ptr<LightIntegrator> light_integrator;
-  std::unique_ptr<Tracer> tracer;
+  std::unique_ptr<OpenTracer> tracer;
   Frame frame;   // input frame
   Frame trace;   // traced frame
 };
@@ -74,7 +82,7 @@ void* ref_create(int main_blocks, int excess_blocks, float voxel_length, float t
     r->depth_integrator.reset(new DepthIntegrator(r->volume));
     r->color_integrator.reset(new ColorIntegrator(r->volume));
     r->light_integrator.reset(new LightIntegrator(r->volume));
-    r->tracer.reset(new Tracer(r->volume));
+    r->tracer.reset(new OpenTracer(r->volume));
     r->frame.depth_image = std::make_shared<Image>();
     r->frame.color_image = std::make_shared<ColorImage>();
     r->frame.normal_image = std::make_shared<ColorImage>();
@@ -215,6 +223,52 @@ const void* ref_device_ptr(void* h, int which) {
     case 8: return r->frame.normal_image->GetData();
   }
   return nullptr;
+}
+
+// Tracer::bounds_ (80 x 60 x Vector2f) and Tracer::patches_ as the last Trace left them
+const void* ref_tracer_bounds(void* h) { return ((Ref*)h)->tracer->bounds(); }
+const void* ref_tracer_patches(void* h) { return ((Ref*)h)->tracer->patches(); }
+int ref_tracer_patch_count(void* h) { return ((Ref*)h)->tracer->patch_count(); }
+
+// The step-wise free functions of include/vulcan/tracer.cuh:14-32 on caller-provided device buffers
+// (what tests/tracer_test.cu:135,234-235,326-337 call).  Tcw32 / Twc32: matrix + inverse, 32 floats.
+int ref_compute_patches(const int* indices, const void* entries, const float* Tcw32, const float* proj4,
+                        float block_length, float min_depth, float max_depth, int block_count, int image_w,
+                        int image_h, int bounds_w, int bounds_h, void* patches, int* patch_count) {
+  try {
+    Projection P;
+    P.SetFocalLength(proj4[0], proj4[1]);
+    P.SetCenterPoint(proj4[2], proj4[3]);
+    vulcan::ComputePatches(indices, (const HashEntry*)entries, RawTransform(Tcw32), P, block_length, min_depth,
+                           max_depth, block_count, image_w, image_h, bounds_w, bounds_h, (Patch*)patches, patch_count);
+    return (int)cudaDeviceSynchronize();
+  } catch (...) { return -1; }
+}
+int ref_compute_bounds(const void* patches, float* bounds, int bounds_w, int patch_count) {
+  try {
+    vulcan::ComputeBounds((const Patch*)patches, (Vector2f*)bounds, bounds_w, patch_count);
+    return (int)cudaDeviceSynchronize();
+  } catch (...) { return -1; }
+}
+int ref_reset_bounds(float* bounds, int count) {
+  try {
+    vulcan::ResetBoundsBuffer((Vector2f*)bounds, count);
+    return (int)cudaDeviceSynchronize();
+  } catch (...) { return -1; }
+}
+int ref_compute_points(const void* entries, const void* voxels, const float* bounds, int block_count,
+                       float block_length, float voxel_length, float trunc_length, const float* Twc32,
+                       const float* proj4, float* depths, float* colors, int image_w, int image_h, int bounds_w,
+                       int bounds_h) {
+  try {
+    Projection P;
+    P.SetFocalLength(proj4[0], proj4[1]);
+    P.SetCenterPoint(proj4[2], proj4[3]);
+    vulcan::ComputePoints((const HashEntry*)entries, (const Voxel*)voxels, (const Vector2f*)bounds, block_count,
+                          block_length, voxel_length, trunc_length, RawTransform(Twc32), P, depths, (Vector3f*)colors,
+                          image_w, image_h, bounds_w, bounds_h);
+    return (int)cudaDeviceSynchronize();
+  } catch (...) { return -1; }
 }
 
 int ref_visible_count(void* h) { return (int)((Ref*)h)->volume->GetVisibleBlocks().GetSize(); }

@@ -175,6 +175,10 @@ _ref_libs = {}
 
 def ref_lib(nofmad=False):
     path = REF_LIB_NOFMAD if nofmad else REF_LIB
+    if os.environ.get("VULCAN_REF_VARIANT") == "asshipped" and not nofmad:
+        # the reference's default build: no NDEBUG, a device synchronisation after every launch (timed once
+        # for BASELINE.md 2.1, never used for parity)
+        path = os.path.join(ROOT, "oracle", "_ref", "libvulcan_ref_asshipped.so")
     if path not in _ref_libs:
         lib = C.CDLL(path)
         lib.ref_create.restype = _P
@@ -318,6 +322,13 @@ class RefVolume:
     def visible(self):
         return self.tensor(3, (self.B,), "<i4")[: self.visible_count()]
 
+    def bounds(self):
+        """The reference Tracer's own 80 x 60 ray-bounds buffer (Tracer::bounds_, include/vulcan/tracer.h:70)."""
+        self.lib.ref_tracer_bounds.restype = _P
+        self.lib.ref_tracer_bounds.argtypes = [_P]
+        from vulcan_b200.api import device_view
+        return device_view(self.lib.ref_tracer_bounds(self.h), (60, 80, 2), "<f4")
+
     def traced(self, w, h):
         return (self.tensor(4, (h, w), "<f4"), self.tensor(5, (h, w, 3), "<f4"), self.tensor(6, (h, w, 3), "<f4"))
 
@@ -354,9 +365,7 @@ def reachable_mask(entries, M):
     cur = block_hash(keys[idx], M)
     found = np.full(len(idx), -1, dtype=np.int64)
     active = np.ones(len(idx), dtype=bool)
-    for _ in range(256):
-        if not active.any():
-            break
+    while active.any():   # chains can be hundreds of entries long in the collision stress tests
         c = cur[active]
         hit = (keys[c] == keys[idx[active]]) & (entries[c, 2] != -1)
         a_idx = np.nonzero(active)[0]
@@ -427,36 +436,67 @@ def raw32(R, t):
     return np.concatenate([m.T.reshape(-1), i.T.reshape(-1)]).astype(np.float32)
 
 
-def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2, math=0):
-    """Sphere-on-plane scenarios.  frames = orbit indices; math = 0 (reference
-    contraction pattern) or 1 (strict)."""
+def room_pose(k, step_deg=15.0):
+    """Camera k of the C4 sweep: in-place rotation about the vertical axis at the room centre
+    (24 poses, 15 degree steps)."""
+    return synth.rotation_y(step_deg * k), np.zeros(3)
+
+
+def make_scenario(name="small", frames=(0,), mode="depth", step_deg=1.2, math=0, trace_each=False):
+    """Synthetic scenarios.  Sphere-on-plane: frames = orbit indices; room*: frames =
+    indices of the in-place rotation (15 degree steps).  math = 0 (reference contraction pattern) or 1
+    (strict).  trace_each: ray-cast the model after EVERY frame from that frame's pose (the per-frame loop
+    of BASELINE configs 2 and 5) instead of once after the last one; images are stacked (V, H, W[, 3])."""
     cfg = {
         "micro": dict(w=48, h=36, voxel=0.02, M=2048, E=512),
         "tiny": dict(w=64, h=48, voxel=0.016, M=4096, E=1024),
         "small": dict(w=160, h=120, voxel=0.008, M=32768, E=8192),
         "c1": dict(w=640, h=480, voxel=0.004, M=262144, E=65536),
         "c3": dict(w=1280, h=720, voxel=0.004, M=262144, E=65536),
-        # BASELINE config 4: 1080p depth, 2 mm voxels, the int-index ceiling of 4 194 303 blocks (42.9 GB pool)
+        # 1080p depth, 2 mm voxels, the int-index ceiling of 4 194 303 blocks (42.9 GB pool), sphere scene
         "c4": dict(w=1920, h=1080, voxel=0.002, M=3145728, E=1048575),
+        # BASELINE config 4: the 8 x 8 x 3 m room + 3 boxes seen from its centre, depth range widened to
+        # 8 m on Volume, Integrator and Tracer so that the room corners (5.7 m) stay valid
+        "room": dict(w=1920, h=1080, voxel=0.002, M=3145728, E=1048575, scene="room", depth_range=(0.1, 8.0)),
+        # the same geometry at sizes the CPU oracle handles (walls through many block faces, grazing floor rays)
+        "room_small": dict(w=240, h=136, voxel=0.016, M=65536, E=16384, scene="room", depth_range=(0.1, 8.0)),
+        "room_vga": dict(w=640, h=360, voxel=0.008, M=524288, E=131072, scene="room", depth_range=(0.1, 8.0)),
     }[name]
+    cfg.setdefault("scene", "sphere")
+    cfg.setdefault("depth_range", (0.1, 5.0))
     w, h = cfg["w"], cfg["h"]
     K = synth.intrinsics(w, h)
     scn = dict(cfg, name=name, mode=mode, math=math, K=np.array(K, dtype=np.float32), trunc=5 * cfg["voxel"],
-               frames=[])
+               frames=[], trace_each=bool(trace_each))
     for k in frames:
-        if k == 0 and step_deg == 1.2:
-            R, t = np.eye(3), np.zeros(3)   # C1: identity pose
+        if cfg["scene"] == "room":
+            R, t = room_pose(k, step_deg if step_deg != 1.2 else 15.0)
+            depth, color = synth.render_room(w, h, K, R, t, max_depth=cfg["depth_range"][1]), None
+            if mode != "depth":
+                yy, xx = np.mgrid[0:h, 0:w]
+                color = np.stack([0.2 + 0.6 * ((xx // 16 + yy // 16) % 2), np.full((h, w), 0.5),
+                                  0.2 + 0.6 * (yy / float(h))], axis=-1).astype(np.float32)
         else:
-            R, t = synth.orbit_pose(k, step_deg=step_deg)
-        if mode == "depth":
-            depth, color = synth.render_sphere_plane(w, h, K, R, t), None
-        else:
-            depth, color = synth.render_sphere_plane(w, h, K, R, t, with_color=True)
+            if k == 0 and step_deg == 1.2:
+                R, t = np.eye(3), np.zeros(3)   # C1: identity pose
+            else:
+                R, t = synth.orbit_pose(k, step_deg=step_deg)
+            if mode == "depth":
+                depth, color = synth.render_sphere_plane(w, h, K, R, t), None
+            else:
+                depth, color = synth.render_sphere_plane(w, h, K, R, t, with_color=True)
         scn["frames"].append(dict(depth=depth, color=color, T=raw32(R, t)))
     # depth -> colour camera: 25 mm baseline (App. D, C3)
     scn["Tcd"] = raw32(np.eye(3), np.array([0.025, 0.0, 0.0]))
     scn["light"] = (2.0, (0.025, 0.08, 0.0))
     return scn
+
+
+def _stack(views):
+    """Traced images of one or several views: a single view keeps its (H, W[, 3]) shape."""
+    if len(views) == 1:
+        return views[0]
+    return tuple(np.stack([v[i] for v in views]) for i in range(3))
 
 
 def _pack_result(entries, voxels, visibility, visible, traced, M):
@@ -467,23 +507,33 @@ def _pack_result(entries, voxels, visibility, visible, traced, M):
 
 
 def run_oracle(scn):
-    ov = OracleVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"])
+    dmin, dmax = scn.get("depth_range", (0.1, 5.0))
+    ov = OracleVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"], dmin, dmax)
     ov.lib.vo_set_math_mode(scn.get("math", 0))
     K = scn["K"]
+    views = []
     for fr in scn["frames"]:
-        ov.set_view_converged(fr["depth"], K, fr["T"])
+        passes = ov.set_view_converged(fr["depth"], K, fr["T"], scn.get("max_passes", 4096))
+        assert passes < scn.get("max_passes", 4096), "oracle allocation did not converge"
         if scn["mode"] == "depth":
-            ov.integrate_depth(fr["depth"], K, fr["T"])
+            ov.integrate_depth(fr["depth"], K, fr["T"], dmin, dmax)
         elif scn["mode"] == "color":
-            ov.integrate_color(fr["depth"], K, fr["T"], fr["color"], K, scn["Tcd"])
+            ov.integrate_color(fr["depth"], K, fr["T"], fr["color"], K, scn["Tcd"], dmin, dmax)
         else:
             nrm = np.zeros(fr["depth"].shape + (3,), dtype=np.float32)
             ov.lib.vo_compute_normals(_ptr(_f32(fr["depth"])), _ptr(_f32(K)), _ptr(nrm), scn["w"], scn["h"])
             ov.integrate_light(fr["depth"], K, fr["T"], fr["color"], nrm, K, scn["Tcd"], scn["light"][0],
-                               np.array(scn["light"][1], dtype=np.float32))
-    last = scn["frames"][-1]
-    d, c, n, _ = ov.trace(scn["w"], scn["h"], K, last["T"])
-    res = _pack_result(ov.entries(), ov.voxels(), ov.visibility(), ov.visible(), (d, c, n), scn["M"])
+                               np.array(scn["light"][1], dtype=np.float32), dmin, dmax)
+        if scn.get("trace_each"):
+            views.append(ov.trace(scn["w"], scn["h"], K, fr["T"], dmin, dmax)[:3])
+    if not views:
+        last = scn["frames"][-1]
+        d, c, n, bounds = ov.trace(scn["w"], scn["h"], K, last["T"], dmin, dmax)
+        views.append((d, c, n))
+    else:
+        bounds = ov.trace(scn["w"], scn["h"], K, scn["frames"][-1]["T"], dmin, dmax)[3]
+    res = _pack_result(ov.entries(), ov.voxels(), ov.visibility(), ov.visible(), _stack(views), scn["M"])
+    res["bounds"] = bounds
     res["fetches"] = ov.fetch_counts()
     assert ov.dropped() == 0
     return res
@@ -493,28 +543,38 @@ def run_ref(scn, nofmad=None):
     """The reference's own CUDA build: release (-fmad=true) for math mode 0, -fmad=false for 1."""
     if nofmad is None:
         nofmad = bool(scn.get("math", 0))
-    rv = RefVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"], nofmad=nofmad)
+    dmin, dmax = scn.get("depth_range", (0.1, 5.0))
+    rv = RefVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"], dmin, dmax, nofmad=nofmad)
     try:
         K = scn["K"]
         kind = {"depth": 0, "color": 1, "light": 2}[scn["mode"]]
+        rv.set_ranges(dmin, dmax, 16.0, 16.0, dmin, dmax)
         rv.set_light(*scn["light"])
+        views = []
         for fr in scn["frames"]:
             rv.set_frame(fr["depth"], K, fr["T"], color=fr["color"], cproj4=K, Tcd32=scn["Tcd"])
             if kind == 2:
                 rv.compute_input_normals()
             rv.set_view_converged()
             rv.integrate(kind)
-        last = scn["frames"][-1]
-        rv.trace(scn["w"], scn["h"], K, last["T"])
-        d, c, n = rv.traced(scn["w"], scn["h"])
+            if scn.get("trace_each"):
+                rv.trace(scn["w"], scn["h"], K, fr["T"])
+                views.append(tuple(x.cpu().numpy() for x in rv.traced(scn["w"], scn["h"])))
+        if not views:
+            last = scn["frames"][-1]
+            rv.trace(scn["w"], scn["h"], K, last["T"])
+            views.append(tuple(x.cpu().numpy() for x in rv.traced(scn["w"], scn["h"])))
+        d, c, n = _stack(views)
         entries = rv.entries().cpu().numpy()
         keys, data, idx = allocated_table(entries, scn["M"])
         import torch
         vox = rv.voxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy()
-        return dict(keys=keys, voxels=vox, vis_flags=rv.visibility().cpu().numpy()[idx],
-                    visible_keys=visible_keys(entries, rv.visible().cpu().numpy()), depth=d.cpu().numpy(),
-                    color=c.cpu().numpy(), normal=n.cpu().numpy(),
-                    unreachable=int((entries[:, 2] != -1).sum() - len(keys)))
+        res = dict(keys=keys, voxels=vox, vis_flags=rv.visibility().cpu().numpy()[idx],
+                   visible_keys=visible_keys(entries, rv.visible().cpu().numpy()), depth=d, color=c, normal=n,
+                   unreachable=int((entries[:, 2] != -1).sum() - len(keys)))
+        if hasattr(rv.lib, "ref_tracer_bounds"):
+            res["bounds"] = rv.bounds().cpu().numpy()   # the reference Tracer's 80 x 60 grid of the last view
+        return res
     finally:
         rv.close()
 
@@ -523,21 +583,34 @@ def run_ours(scn, shard=None):
     import torch
     import vulcan_b200 as vb
     vb.SetDefaultMathMode(scn.get("math", 0))
+    dmin, dmax = scn.get("depth_range", (0.1, 5.0))
     vol = vb.Volume(scn["M"], scn["E"])
     vol.SetVoxelLength(scn["voxel"])
     vol.SetTruncationLength(scn["trunc"])
+    vol.SetDepthRange(dmin, dmax)
     if shard:
         vol.SetSharding(*shard)
     integ = {"depth": vb.DepthIntegrator, "color": vb.ColorIntegrator, "light": vb.LightIntegrator}[scn["mode"]](vol)
+    integ.SetDepthRange(dmin, dmax)
     if scn["mode"] == "light":
         integ.SetLight(*scn["light"])
     tracer = vb.Tracer(vol)
+    tracer.SetDepthRange(dmin, dmax)
     K = scn["K"]
 
     def transform(raw):
         return vb.Transform(raw[:16].reshape(4, 4).T.copy(), raw[16:].reshape(4, 4).T.copy())
 
+    def trace_from(frame):
+        out = vb.Frame()
+        out.depth_projection = frame.depth_projection
+        out.depth_to_world_transform = frame.depth_to_world_transform
+        out.depth_image = torch.zeros((scn["h"], scn["w"]), dtype=torch.float32, device="cuda")
+        tracer.Trace(out)
+        return (out.depth_image.cpu().numpy(), out.color_image.cpu().numpy(), out.normal_image.cpu().numpy())
+
     frame = vb.Frame()
+    views = []
     for fr in scn["frames"]:
         frame = vb.Frame()
         frame.depth_projection = vb.Projection(*K)
@@ -551,11 +624,11 @@ def run_ours(scn, shard=None):
             frame.ComputeNormals()
         vol.SetView(frame)
         integ.Integrate(frame)
-    out = vb.Frame()
-    out.depth_projection = frame.depth_projection
-    out.depth_to_world_transform = frame.depth_to_world_transform
-    out.depth_image = torch.zeros((scn["h"], scn["w"]), dtype=torch.float32, device="cuda")
-    tracer.Trace(out)
+        if scn.get("trace_each"):
+            views.append(trace_from(frame))
+    if not views:
+        views.append(trace_from(frame))
+    d, c, n = _stack(views)
     n_vis, counters = vol.SyncCounters()
     assert counters[4] == 0, "pool overflow"
     entries = vol.GetHashEntries().cpu().numpy()
@@ -563,8 +636,8 @@ def run_ours(scn, shard=None):
     vox = vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy()
     res = dict(keys=keys, voxels=vox, vis_flags=vol.GetBlockVisibility().cpu().numpy()[idx],
                visible_keys=visible_keys(entries, vol.GetVisibleBlocks().cpu().numpy()),
-               depth=out.depth_image.cpu().numpy(), color=out.color_image.cpu().numpy(),
-               normal=out.normal_image.cpu().numpy(), counters=counters,
+               depth=d, color=c, normal=n, counters=counters,
+               bounds=tracer.bounds_.cpu().numpy(),
                unreachable=int((entries[:, 2] != -1).sum() - len(keys)))
     del vol
     return res
@@ -627,6 +700,10 @@ def compare(a, b, trunc):
     rep["color_img_max_abs"] = float(np.abs(a["color"] - b["color"]).max())
     rep["normal_img_max_abs"] = float(np.abs(a["normal"] - b["normal"])[both].max()) if both.any() else 0.0
     rep["normal_bits_mismatch"] = int((a["normal"].view(np.int32) != b["normal"].view(np.int32)).sum())
+    if "bounds" in a and "bounds" in b:
+        # the 80 x 60 ray-bounds grid of the last traced view (Tracer::bounds_), bit for bit
+        rep["bounds_bits_mismatch"] = int((np.ascontiguousarray(a["bounds"]).view(np.int32) !=
+                                           np.ascontiguousarray(b["bounds"]).view(np.int32)).sum())
     return rep
 
 
@@ -795,14 +872,15 @@ def ours_track_frames(s, pose32):
 
 def oracle_volume_for(scn):
     """The oracle volume after the scenario's frames (run_oracle without the trace)."""
-    ov = OracleVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"])
+    dmin, dmax = scn.get("depth_range", (0.1, 5.0))
+    ov = OracleVolume(scn["M"], scn["E"], scn["voxel"], scn["trunc"], dmin, dmax)
     ov.lib.vo_set_math_mode(scn.get("math", 0))
     for fr in scn["frames"]:
         ov.set_view_converged(fr["depth"], scn["K"], fr["T"])
         if scn["mode"] == "color":
-            ov.integrate_color(fr["depth"], scn["K"], fr["T"], fr["color"], scn["K"], scn["Tcd"])
+            ov.integrate_color(fr["depth"], scn["K"], fr["T"], fr["color"], scn["K"], scn["Tcd"], dmin, dmax)
         else:
-            ov.integrate_depth(fr["depth"], scn["K"], fr["T"])
+            ov.integrate_depth(fr["depth"], scn["K"], fr["T"], dmin, dmax)
     assert ov.dropped() == 0
     return ov
 

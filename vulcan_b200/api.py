@@ -248,12 +248,17 @@ class Volume:
 
     def SetVoxelLength(self, length):
         self._v.voxel_length = length
+        # prove the fast division for the voxel and block length now (vk_div_prepare synchronises the
+        # stream on the first use of a value), not inside the first frame
+        lib.vk_div_prepare(C.c_float(self._v.voxel_length), _stream())
+        lib.vk_div_prepare(C.c_float(np.float32(8) * np.float32(self._v.voxel_length)), _stream())
 
     def GetTruncationLength(self):
         return self._v.trunc_length
 
     def SetTruncationLength(self, length):
         self._v.trunc_length = length
+        lib.vk_div_prepare(C.c_float(self._v.trunc_length), _stream())
 
     def GetMathMode(self):
         return self._v.math_mode

@@ -482,9 +482,17 @@ __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
 
 // pool fills of Volume::Initialize (src/volume.cu:552-627)
 __global__ void vk_fill_pools_kernel(uint4* voxels16, size_t n16, vkHashEntry* entries, int32_t* free_list,
-                                     uint8_t* visibility, int32_t* stamps, int32_t* locks, int B, int M) {
+                                     uint8_t* visibility, int32_t* stamps, int32_t* locks, int32_t* counters, int B, int M) {
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
+  // counters (and the ticket behind them) are initialised HERE, in stream order, not copied from the
+  // pinned host mirror: a SetView still in flight on the stream writes that mirror when it retires
+  if (tid < VK_CNT_COUNT + 4) {
+    int32_t val = 0;
+    if (tid == VK_CNT_VOXEL_PTR) val = B - 1;     // src/volume.cu:595-601
+    if (tid == VK_CNT_EXCESS_PTR) val = M;        // src/volume.cu:579-584
+    counters[tid] = val;
+  }
   // Voxel::Empty() = {1.0f, 0,0,0, 0,0}: 5 words; a 16-byte chunk q starts at word 4q.
   for (size_t q = tid; q < n16; q += stride) {
     const uint32_t r = (uint32_t)((q * 4) % 5);
@@ -514,25 +522,21 @@ extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   const int B = v->main_blocks + v->excess_blocks;
   const size_t n16 = (size_t)B * VK_BLOCK_VOXELS * sizeof(vkVoxel) / 16;
   vk_fill_pools_kernel<<<148 * 8, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), n16, v->entries,
-                                               v->free_list, v->visibility, v->stamps, v->locks, B,
+                                               v->free_list, v->visibility, v->stamps, v->locks, v->counters, B,
                                                v->main_blocks);
   VK_COUNT_LAUNCH();
-  int32_t init[VK_CNT_COUNT] = {0};
-  init[VK_CNT_VOXEL_PTR] = B - 1;               // src/volume.cu:595-601
-  init[VK_CNT_EXCESS_PTR] = v->main_blocks;     // src/volume.cu:579-584
-  for (int i = 0; i < VK_CNT_COUNT; ++i) v->host_counters[i] = init[i];
-  cudaError_t err = cudaMemcpyAsync(v->counters, v->host_counters, sizeof(init), cudaMemcpyHostToDevice, s);
-  if (err != cudaSuccess) return (int)err;
-  err = cudaMemsetAsync(v->bucket_bits, 0, ((size_t)v->main_blocks + 31) / 32 * sizeof(uint32_t), s);
+  cudaError_t err = cudaMemsetAsync(v->bucket_bits, 0, ((size_t)v->main_blocks + 31) / 32 * sizeof(uint32_t), s);
   if (err != cudaSuccess) return (int)err;
   err = cudaMemsetAsync(v->space_bits, 0, VK_SPACE_WORDS * sizeof(uint32_t), s);
   if (err != cudaSuccess) return (int)err;
-  err = cudaMemsetAsync(v->counters + VK_CNT_COUNT, 0, sizeof(int), s);  // ticket
+  err = cudaStreamSynchronize(s);  // everything that could still write the host mirror has retired
   if (err != cudaSuccess) return (int)err;
-  err = cudaStreamSynchronize(s);  // host_counters is reused by kernels afterwards
+  for (int i = 0; i < VK_CNT_COUNT; ++i) v->host_counters[i] = 0;
+  v->host_counters[VK_CNT_VOXEL_PTR] = B - 1;
+  v->host_counters[VK_CNT_EXCESS_PTR] = v->main_blocks;
   v->visible_slot = 0;
   v->view_id = 0;
-  return (int)err;
+  return 0;
 }
 
 extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks, void* stream) {

@@ -179,6 +179,9 @@ using namespace vk;
 extern "C" int vk_extract_points(const vkVolume* v, float* points, float* colors, int capacity, int* count,
                                  void* stream) {
   if (!v || !v->voxels || !points || !count || capacity < 0) return VK_E_INVALID;
+  // A shard resolves face neighbours in its own table only: crossings into another rank's blocks would be
+  // dropped silently.  Extract from an unsharded volume (or gather the shards first).
+  if (v->shard_count > 1) return VK_E_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
   int rc = (int)cudaMemsetAsync(count, 0, sizeof(int), s);
   if (rc) return rc;

@@ -26,8 +26,8 @@ inline void rows34(const float* colmajor, float* out12) {
 }
 
 // Divisor descriptor for vk::divc.  The first use of a divisor value in the process runs the
-// exhaustive device check (all 2^32 dividends against __fdiv_rn, ~1 ms) on `stream` and waits
-// for it; later uses hit a host-side cache.  Returns fast = 0 (plain IEEE division) if the
+// device check (every mantissa of the dividend against __fdiv_rn, ~20 us; see vk_runtime.cu for why
+// one binade is a complete proof) on `stream` and waits for it; later uses hit a host-side cache.  Returns fast = 0 (plain IEEE division) if the
 // check fails or cannot run.
 Div make_div(float d, cudaStream_t stream);
 

@@ -152,9 +152,10 @@ __device__ __forceinline__ float vmax(float a, float b) { return (b > a) ? b : a
 // q = RN(x / d) from r = RN(1 / d) with one FMA residual step:
 //   q0 = RN(x * r);  e = x - q0 * d (exact, FMA);  q = RN(q0 + e * r)
 // For a given d this is either right for every x in the guarded range or it is not; the host
-// proves it per divisor by running it against __fdiv_rn over ALL 2^32 bit patterns of x once
-// (vk_div_prepare, vk_divcheck.cu) and clears `fast` otherwise.  Outside the guarded range
-// (tiny / huge / non-finite quotients) the IEEE division instruction sequence is used.
+// proves it per divisor by running it against __fdiv_rn over every mantissa of x once (one binade
+// is a complete proof inside the guarded range, where every step scales exactly with the exponent
+// of x: vk_divcheck_kernel in vk_runtime.cu) and clears `fast` otherwise.  Outside the guarded
+// range (tiny / huge / non-finite quotients) the IEEE division instruction sequence is used.
 struct Div {
   float d, r;
   int fast;

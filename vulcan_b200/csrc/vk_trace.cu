@@ -1230,6 +1230,9 @@ extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const 
   if (row_begin < 0 || row_end > view->depth_h || row_begin > row_end) return VK_E_INVALID;
   if (peers && (peers->count < 1 || peers->count > VK_MAX_SHARDS || peers->rank < 0 || peers->rank >= peers->count))
     return VK_E_INVALID;
+  // owners are computed from the peer table's rank count and the volume's brick shift: they must
+  // describe the same partition
+  if (peers && peers->count > 1 && (peers->count != v->shard_count || peers->rank != v->shard_rank)) return VK_E_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
   TraceParams t;
   fill_trace_params(t, v->entries, v->voxels, bounds, v->bucket_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,

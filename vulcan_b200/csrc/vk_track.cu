@@ -560,7 +560,10 @@ static int track_pixels(const vkFrame* key, const vkFrame* frame, int translatio
   cudaStream_t s = (cudaStream_t)stream;
   float* pose = nullptr;
   if ((rc = (int)cudaMallocAsync(&pose, 64, s))) return rc;
-  if ((rc = (int)cudaMemcpyAsync(pose, frame->depth_to_world.m, 64, cudaMemcpyHostToDevice, s))) return rc;
+  if ((rc = (int)cudaMemcpyAsync(pose, frame->depth_to_world.m, 64, cudaMemcpyHostToDevice, s))) {
+    cudaFreeAsync(pose, s);
+    return rc;
+  }
   const int n = im.w * im.h;
   int grid = (n + 255) / 256;
   const int cap = 8 * sm_count();

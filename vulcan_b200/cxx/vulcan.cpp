@@ -331,6 +331,10 @@ void Volume::SetVoxelLength(float length)
 {
   VULCAN_DEBUG(length > 0);
   volume_.voxel_length = length;
+  // the exact fast division by the voxel and block length is proven here (first use of a value
+  // synchronises the stream), not inside the first frame
+  vk_div_prepare(length, stream_);
+  vk_div_prepare(Block::resolution * length, stream_);
 }
 
 float Volume::GetTruncationLength() const { return volume_.trunc_length; }
@@ -339,6 +343,7 @@ void Volume::SetTruncationLength(float length)
 {
   VULCAN_DEBUG(length > 0);
   volume_.trunc_length = length;
+  vk_div_prepare(length, stream_);
 }
 
 void Volume::SetView(const Frame& frame)
