@@ -64,6 +64,12 @@ class Volume
     void Load(const std::string& path);         // into a volume of the same block counts
     void SetStream(cudaStream_t stream) { stream_ = stream; }
     cudaStream_t GetStream() const { return stream_; }
+    // The ray marcher samples a block-major mirror of Voxel::distance (vkVolume::sdf).  The non-const
+    // GetVoxels() hands out write access to the pool like the reference does, so it marks the mirror
+    // stale; Tracer::Trace rebuilds it (vk_volume_sync_sdf) before marching.  Callers that write the
+    // pool through a pointer obtained earlier call this themselves.
+    void MarkVoxelsWritten() const { sdf_stale_ = true; }
+    void SyncDistances() const;
     vkVolume* GetHandle() { return &volume_; }
     const vkVolume* GetHandle() const { return &volume_; }
 
@@ -76,6 +82,7 @@ class Volume
   protected:
 
     mutable vkVolume volume_;
+    mutable bool sdf_stale_ = false;
     cudaStream_t stream_;
     Vector2f depth_range_;
     mutable Buffer<Voxel> voxels_;

@@ -117,6 +117,10 @@ typedef struct vkVolume {
   uint32_t*    bucket_bits;   /* [ceil(M/32)] bit h set <=> bucket head h allocated */
   uint32_t*    space_bits;    /* [VK_SPACE_WORDS] bit of (x,y,z) mod 128 set <=> some block with    */
                               /* those low coordinate bits is allocated (free-space filter)       */
+  float*       sdf;           /* [(M+E)*512] mirror of Voxel::distance alone, block-major (2 KB per  */
+                              /* block, index z*64+y*8+x): what the ray marcher samples.  Kept in    */
+                              /* step by the integrators, vk_volume_reset and vk_volume_load; after  */
+                              /* writing `voxels` directly call vk_volume_sync_sdf.                  */
   int32_t*     counters;      /* [VK_CNT_COUNT] device                              */
   int32_t*     host_counters; /* [VK_CNT_COUNT] pinned host mirror                  */
   int32_t      main_blocks;   /* M (also the hash modulus K)                        */
@@ -172,6 +176,12 @@ int vk_volume_destroy(vkVolume* v);
  * tests/tracer_test.cu:298-303) — in one call, with no host synchronisation.
  * The visible count stays on the device (counters[VK_CNT_VISIBLE0 + visible_slot]). */
 int vk_set_view(vkVolume* v, const vkFrame* f, void* stream);
+
+/* Rebuilds vkVolume::sdf from `voxels` for every allocated block (stream-ordered).  Only needed after
+ * the voxel pool was written from outside the library (the reference hands out a mutable
+ * Buffer<Voxel>&, include/vulcan/volume.h:48-50; the C++ / Python layers call this before the next
+ * trace when that accessor was used). */
+int vk_volume_sync_sdf(vkVolume* v, void* stream);
 
 /* Copies the counters to host_counters and synchronises the stream.  Returns the
  * current visible-block count in *visible (Volume::GetBufferSize, src/volume.cu:537-543);
@@ -265,12 +275,14 @@ typedef struct vkPeerTable {
   int32_t            count, rank;
   const vkHashEntry* entries[VK_MAX_SHARDS];
   const vkVoxel*     voxels[VK_MAX_SHARDS];
+  const float*       sdf[VK_MAX_SHARDS];      /* vkVolume::sdf of every rank */
 } vkPeerTable;
 
-/* CUDA IPC handles of a volume's hash entries and voxel pool (2 x cudaIpcMemHandle_t). */
+/* CUDA IPC handles of a volume's hash entries, voxel pool and distance mirror (3 x cudaIpcMemHandle_t). */
 typedef struct vkIpcHandles {
   unsigned char entries[64];
   unsigned char voxels[64];
+  unsigned char sdf[64];
 } vkIpcHandles;
 
 /* Exact ray casting of a block-sharded volume.  Every rank holds the blocks it owns (plus a
@@ -292,8 +304,8 @@ int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const vkFrame* vi
                   int row_begin, int row_end, float* out_depth, float* out_color, float* out_normal,
                   void* stream);
 int vk_ipc_export(const vkVolume* v, vkIpcHandles* out);
-int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels);
-int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels);
+int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels, const float** sdf);
+int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels, const float* sdf);
 
 /* Exchange of the rendered bands without a library collective.  Every rank owns one "exchange
  * buffer" (vk_exchange_alloc: room for the full-size depth + colour + normal images of a view and

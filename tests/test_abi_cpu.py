@@ -55,7 +55,7 @@ def test_struct_layouts_match_header(tmp_path):
     assert got[6] == C.sizeof(L.vkVolume) and got[7] == C.sizeof(L.vkFrame)
     assert got[8] == L.vkVolume.math_mode.offset and got[9] == L.vkFrame.depth_to_color.offset
     assert got[10] == C.sizeof(L.vkPeerTable) and got[11] == C.sizeof(L.vkExchange)
-    assert got[12] == L.vkExchange.row_begin.offset and got[13] == C.sizeof(L.vkIpcHandles) == 128
+    assert got[12] == L.vkExchange.row_begin.offset and got[13] == C.sizeof(L.vkIpcHandles) == 192
 
 
 def test_no_device_is_an_error_not_a_fallback():

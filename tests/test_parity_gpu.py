@@ -242,7 +242,7 @@ def test_sharded_volume_is_exact(count):
     for rank, t in enumerate(tracers):
         t.bounds_[..., 0] = lo
         t.bounds_[..., 1] = hi
-        peers = S.peer_table(rank, [v._v.entries for v in vols], [v._v.voxels for v in vols])
+        peers = S.peer_table(rank, [v._v.entries for v in vols], [v._v.voxels for v in vols], [v._v.sdf for v in vols])
         band = vb.Frame()
         band.depth_projection, band.depth_to_world_transform = out.depth_projection, out.depth_to_world_transform
         band.depth_image = torch.zeros_like(out.depth_image)

@@ -36,7 +36,8 @@ class vkVolume(C.Structure):
     _fields_ = [
         ("voxels", C.c_void_p), ("entries", C.c_void_p), ("free_list", C.c_void_p),
         ("visibility", C.c_void_p), ("visible", C.c_void_p * 2), ("stamps", C.c_void_p),
-        ("locks", C.c_void_p), ("bucket_bits", C.c_void_p), ("space_bits", C.c_void_p), ("counters", C.c_void_p), ("host_counters", C.POINTER(C.c_int32)),
+        ("locks", C.c_void_p), ("bucket_bits", C.c_void_p), ("space_bits", C.c_void_p), ("sdf", C.c_void_p),
+        ("counters", C.c_void_p), ("host_counters", C.POINTER(C.c_int32)),
         ("main_blocks", C.c_int32), ("excess_blocks", C.c_int32),
         ("voxel_length", C.c_float), ("trunc_length", C.c_float),
         ("min_depth", C.c_float), ("max_depth", C.c_float),
@@ -50,11 +51,11 @@ MAX_SHARDS = 8
 
 class vkPeerTable(C.Structure):
     _fields_ = [("count", C.c_int32), ("rank", C.c_int32), ("entries", C.c_void_p * MAX_SHARDS),
-                ("voxels", C.c_void_p * MAX_SHARDS)]
+                ("voxels", C.c_void_p * MAX_SHARDS), ("sdf", C.c_void_p * MAX_SHARDS)]
 
 
 class vkIpcHandles(C.Structure):
-    _fields_ = [("entries", C.c_ubyte * 64), ("voxels", C.c_ubyte * 64)]
+    _fields_ = [("entries", C.c_ubyte * 64), ("voxels", C.c_ubyte * 64), ("sdf", C.c_ubyte * 64)]
 
 
 class vkExchange(C.Structure):
@@ -81,6 +82,7 @@ SYMBOLS = {
     "vk_volume_destroy": [C.POINTER(vkVolume)],
     "vk_set_view": [C.POINTER(vkVolume), C.POINTER(vkFrame), _P],
     "vk_volume_sync_counters": [C.POINTER(vkVolume), C.POINTER(_I), _P],
+    "vk_volume_sync_sdf": [C.POINTER(vkVolume), _P],
     "vk_volume_save": [C.POINTER(vkVolume), C.c_char_p, _P],
     "vk_volume_load": [C.POINTER(vkVolume), C.c_char_p, _P],
     "vk_integrate_depth": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _F, _P],
@@ -101,8 +103,8 @@ SYMBOLS = {
     "vk_trace_bounds": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _P, _P],
     "vk_trace_rows": [C.POINTER(vkVolume), C.POINTER(vkPeerTable), C.POINTER(vkFrame), _P, _I, _I, _P, _P, _P, _P],
     "vk_ipc_export": [C.POINTER(vkVolume), C.POINTER(vkIpcHandles)],
-    "vk_ipc_open": [C.POINTER(vkIpcHandles), C.POINTER(_P), C.POINTER(_P)],
-    "vk_ipc_close": [_P, _P],
+    "vk_ipc_open": [C.POINTER(vkIpcHandles), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)],
+    "vk_ipc_close": [_P, _P, _P],
     "vk_exchange_alloc": [_I, _I, C.POINTER(_P)],
     "vk_exchange_free": [_P],
     "vk_exchange_export": [_P, C.c_char_p],

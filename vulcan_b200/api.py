@@ -318,8 +318,24 @@ class Volume:
         return device_view(self._v.entries, (self._B, 4), "<i4")
 
     def GetVoxels(self):
-        """(B*512, 5) int32 view of the 20-byte voxels: distance, r, g, b bits, dw | cw<<16."""
+        """(B*512, 5) int32 view of the 20-byte voxels: distance, r, g, b bits, dw | cw<<16.  Read it; to
+        WRITE voxels use GetVoxelsMutable() (the ray marcher samples a mirror of the distances)."""
         return device_view(self._v.voxels, (self._B * 512, 5), "<i4")
+
+    def GetVoxelsMutable(self):
+        """The non-const Volume::GetVoxels() (include/vulcan/volume.h:48-50): marks the distance mirror
+        stale; the next Trace rebuilds it (vk_volume_sync_sdf)."""
+        self._sdf_stale = True
+        return self.GetVoxels()
+
+    def SyncDistances(self):
+        if getattr(self, "_sdf_stale", False):
+            check(lib.vk_volume_sync_sdf(C.byref(self._v), _stream()), "SyncDistances")
+            self._sdf_stale = False
+
+    def GetDistances(self):
+        """(B*512,) float32 view of vkVolume::sdf."""
+        return device_view(self._v.sdf, (self._B * 512,), "<f4")
 
     def GetBlockVisibility(self):
         return device_view(self._v.visibility, (self._B,), "|u1")
@@ -434,6 +450,7 @@ class Tracer:
         if frame.normal_image is None or tuple(frame.normal_image.shape) != (h, w, 3):
             frame.normal_image = torch.empty((h, w, 3), dtype=torch.float32, device="cuda")
         f = frame.to_c()
+        self.volume_.SyncDistances()
         check(lib.vk_trace(C.byref(self.volume_._v), C.byref(f), self.depth_range_[0], self.depth_range_[1],
                            self.bounds_.data_ptr(), frame.depth_image.data_ptr(), frame.color_image.data_ptr(),
                            frame.normal_image.data_ptr(), _stream()), "Trace")

@@ -481,7 +481,7 @@ __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
 }
 
 // pool fills of Volume::Initialize (src/volume.cu:552-627)
-__global__ void vk_fill_pools_kernel(uint4* voxels16, size_t n16, vkHashEntry* entries, int32_t* free_list,
+__global__ void vk_fill_pools_kernel(uint4* voxels16, size_t n16, float4* sdf4, vkHashEntry* entries, int32_t* free_list,
                                      uint8_t* visibility, int32_t* stamps, int32_t* locks, int32_t* counters, int B, int M) {
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -503,6 +503,9 @@ __global__ void vk_fill_pools_kernel(uint4* voxels16, size_t n16, vkHashEntry* e
     val.w = (r == 2) ? 0x3f800000u : 0u;
     voxels16[q] = val;
   }
+  // distance mirror: Voxel::Empty().distance everywhere
+  const size_t n4 = (size_t)B * (VK_BLOCK_VOXELS / 4);
+  for (size_t q = tid; q < n4; q += stride) sdf4[q] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
   for (size_t i = tid; i < (size_t)B; i += stride) {
     reinterpret_cast<int4*>(entries)[i] = make_int4(0, 0, -1, -1);
     free_list[i] = (int)i;
@@ -512,16 +515,40 @@ __global__ void vk_fill_pools_kernel(uint4* voxels16, size_t n16, vkHashEntry* e
   }
 }
 
+// vkVolume::sdf rebuilt from the voxel pool: one warp per allocated entry (strided 4-byte reads of
+// Voxel::distance, coalesced writes).  Maintenance path only (vk_volume_sync_sdf).
+__global__ void __launch_bounds__(256) vk_sdf_rebuild_kernel(const vkHashEntry* entries, const vkVoxel* voxels, float* sdf,
+                                                             int B) {
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int e = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; e < B; e += warps) {
+    const int data = ld_entry_cg(entries + e).z;
+    if (data < 0) continue;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(voxels) + (size_t)data * (VK_BLOCK_VOXELS * 5);
+    float* dst = sdf + (size_t)data * VK_BLOCK_VOXELS;
+#pragma unroll 4
+    for (int i = lane; i < VK_BLOCK_VOXELS; i += 32) dst[i] = __uint_as_float(src[5 * i]);
+  }
+}
+
 }  // namespace vk
 
 using namespace vk;
+
+extern "C" int vk_volume_sync_sdf(vkVolume* v, void* stream) {
+  if (!v || !v->voxels || !v->sdf) return VK_E_INVALID;
+  const int B = v->main_blocks + v->excess_blocks;
+  vk_sdf_rebuild_kernel<<<sm_count() * 8, 256, 0, (cudaStream_t)stream>>>(v->entries, v->voxels, v->sdf, B);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
 
 extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   if (!v || !v->voxels) return VK_E_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
   const int B = v->main_blocks + v->excess_blocks;
   const size_t n16 = (size_t)B * VK_BLOCK_VOXELS * sizeof(vkVoxel) / 16;
-  vk_fill_pools_kernel<<<148 * 8, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), n16, v->entries,
+  vk_fill_pools_kernel<<<148 * 8, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), n16, reinterpret_cast<float4*>(v->sdf), v->entries,
                                                v->free_list, v->visibility, v->stamps, v->locks, v->counters, B,
                                                v->main_blocks);
   VK_COUNT_LAUNCH();
@@ -570,6 +597,7 @@ extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks,
   VK_TRY(cudaMalloc((void**)&v->locks, (size_t)main_blocks * sizeof(int32_t)));
   VK_TRY(cudaMalloc((void**)&v->bucket_bits, ((size_t)main_blocks + 31) / 32 * sizeof(uint32_t)));
   VK_TRY(cudaMalloc((void**)&v->space_bits, VK_SPACE_WORDS * sizeof(uint32_t)));
+  VK_TRY(cudaMalloc((void**)&v->sdf, B * VK_BLOCK_VOXELS * sizeof(float)));
   VK_TRY(cudaMalloc((void**)&v->counters, (VK_CNT_COUNT + 4) * sizeof(int32_t)));
   VK_TRY(cudaHostAlloc((void**)&v->host_counters, VK_CNT_COUNT * sizeof(int32_t), cudaHostAllocMapped));
 #undef VK_TRY
@@ -588,6 +616,7 @@ extern "C" int vk_volume_destroy(vkVolume* v) {
   cudaFree(v->locks);
   cudaFree(v->bucket_bits);
   cudaFree(v->space_bits);
+  cudaFree(v->sdf);
   cudaFree(v->counters);
   if (v->host_counters) cudaFreeHost(v->host_counters);
   const int m = v->main_blocks, e = v->excess_blocks;

@@ -28,6 +28,7 @@ struct IntegrateParams {
   const int32_t* count;
   const vkHashEntry* entries;
   vkVoxel* voxels;
+  float* sdf;   // vkVolume::sdf, the block-major mirror of Voxel::distance the ray marcher reads
   const float* depth;
   const float* color;
   const float* normal;
@@ -278,6 +279,10 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
       }
       // voxels written = voxels whose weight word is dirty (bit 5k+4)
       n_updated += __popc(dirty & 0x84210u);
+      // the thread's 4 distances are one aligned 16-byte piece of the block's distance mirror
+      // (voxel index 4t): a warp writes 512 contiguous bytes
+      if (cur.dmask)
+        reinterpret_cast<uint4*>(p.sdf + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = make_uint4(w[0], w[5], w[10], w[15]);
     }
     // changed chunks go back lane-contiguously
     uint32_t chunk_dirty = 0;  // bit c: the thread's chunk c changed
@@ -360,11 +365,12 @@ static void matmul4(const float* A, const float* Bm, float* C) {
 
 static int fill_params(IntegrateParams& p, vkVolume* v, const vkFrame* f, float min_depth, float max_depth,
                        float max_dw, float max_cw, cudaStream_t s) {
-  if (!v || !f || !v->voxels || !f->depth) return VK_E_INVALID;
+  if (!v || !f || !v->voxels || !v->sdf || !f->depth) return VK_E_INVALID;
   p.visible = v->visible[v->visible_slot];
   p.count = v->counters + VK_CNT_VISIBLE0 + v->visible_slot;
   p.entries = v->entries;
   p.voxels = v->voxels;
+  p.sdf = v->sdf;
   p.depth = f->depth;
   p.color = f->color;
   p.normal = f->normal;

@@ -142,10 +142,12 @@ extern "C" int vk_volume_save(const vkVolume* v, const char* path, void* stream)
 }
 
 // blocks back to Voxel::Empty() (the pattern of vk_fill_pools_kernel: distance 1, everything else 0)
-__global__ void __launch_bounds__(256) vk_empty_blocks_kernel(uint4* pool, const int32_t* ids, int n) {
+__global__ void __launch_bounds__(256) vk_empty_blocks_kernel(uint4* pool, float4* sdf4, const int32_t* ids, int n) {
   constexpr int kQuads = VK_BLOCK_VOXELS * sizeof(vkVoxel) / 16;  // 640
   for (int b = blockIdx.x; b < n; b += gridDim.x) {
     uint4* p = pool + (size_t)ids[b] * kQuads;
+    float4* m = sdf4 + (size_t)ids[b] * (VK_BLOCK_VOXELS / 4);  // the distance mirror of the block
+    for (int q = threadIdx.x; q < VK_BLOCK_VOXELS / 4; q += blockDim.x) m[q] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
     for (int q = threadIdx.x; q < kQuads; q += blockDim.x) {
       const uint32_t r = (uint32_t)((q * 4) % 5);
       p[q] = make_uint4((r == 0) ? 0x3f800000u : 0u, (r == 4) ? 0x3f800000u : 0u, (r == 3) ? 0x3f800000u : 0u,
@@ -252,7 +254,8 @@ extern "C" int vk_volume_load(vkVolume* v, const char* path, void* stream) {
   if (err == cudaSuccess && !stale.empty()) {
     err = cudaMemcpyAsync(d_ids, stale.data(), stale.size() * sizeof(int32_t), cudaMemcpyHostToDevice, s);
     if (err == cudaSuccess) {
-      vk_empty_blocks_kernel<<<sm_count() * 4, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), d_ids, (int)stale.size());
+      vk_empty_blocks_kernel<<<sm_count() * 4, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels),
+                                                            reinterpret_cast<float4*>(v->sdf), d_ids, (int)stale.size());
       VK_COUNT_LAUNCH();
       err = cudaStreamSynchronize(s);
     }
@@ -284,6 +287,8 @@ extern "C" int vk_volume_load(vkVolume* v, const char* path, void* stream) {
   cudaFree(d_ids);
   cudaFreeHost(h_stage);
   if (err != cudaSuccess && rc == 0) rc = (int)err;
+  if (!rc) rc = vk_volume_sync_sdf(v, stream);   // the distance mirror of the restored blocks
+  if (!rc) rc = (int)cudaStreamSynchronize(s);
   if (rc) {
     vk_volume_reset(v, stream);
     return rc;

@@ -241,12 +241,14 @@ namespace vk {
 struct TraceParams {
   const vkHashEntry* entries;
   const vkVoxel* voxels;
+  const float* sdf;             // vkVolume::sdf: distances alone, block-major (SOA kernels); NULL for raw-pointer calls
   const float* bounds;
   const uint32_t* bucket_bits;  // optional: bit h set <=> bucket head h allocated (vkVolume::bucket_bits)
   const uint32_t* space_bits;   // optional: free-space filter (vkVolume::space_bits)
   int free_run;                 // max free-space steps per lane per trip (0 = filter off)
   bool negated_hi;              // bounds cells hold (min, -max) (vk_trace_bounds / vk_trace_rows)
   int coop_lanes, coop_rounds;  // cooperative free-space runs when at most coop_lanes lanes are in free space
+  int ahead_lanes;              // look-ahead prefetch for the rays of a warp with at most this many live lanes (0 = off)
   Mod K;
   Div block_length, voxel_length;
   float trunc;
@@ -262,6 +264,7 @@ struct TraceParams {
   // over NVLink).  A block id in the marcher is (rank << kPeerShift) | voxel-block id.
   const vkHashEntry* peer_entries[VK_MAX_SHARDS];
   const vkVoxel* peer_voxels[VK_MAX_SHARDS];
+  const float* peer_sdf[VK_MAX_SHARDS];
   int peer_count, peer_rank;
   int y_begin, y_end;           // image rows marched by this launch
   int debug_flags;              // diagnostics: 1 = skip the filter load, 2 = skip the block division
@@ -341,6 +344,18 @@ __device__ __forceinline__ const uint32_t* voxel_words(const TraceParams& p, int
          voxel_offset * 5;
 }
 
+// Voxel::distance of voxel `voxel_offset` of block `data`.  SOA: from the block-major distance mirror
+// (2 KB per block: a 128-byte line holds 32 voxels, against 1.6 voxels per 32-byte sector of the 20-byte
+// AoS voxels), which the integrators keep in step with the voxel pool; otherwise from the voxel itself.
+// Q22: voxel_offset may exceed 511 on an exact block face; both layouts then read the same voxel of
+// the next block of the pool.
+template <bool PEERS, bool SOA>
+__device__ __forceinline__ float load_distance(const TraceParams& p, int data, int voxel_offset) {
+  if (!SOA) return __uint_as_float(__ldg(voxel_words<PEERS>(p, data, voxel_offset)));
+  if (!PEERS) return __ldg(p.sdf + (size_t)data * VK_BLOCK_VOXELS + voxel_offset);
+  return __ldg(p.peer_sdf[data >> kPeerShift] + (size_t)(data & ((1 << kPeerShift) - 1)) * VK_BLOCK_VOXELS + voxel_offset);
+}
+
 // The 8 taps of GetInterpolatedDistance (src/tracer.cu:190-256): per axis the tap pair
 // (i0, i0 + 1), i0 = floor(w - 0.5) in [-1, 7]; a tap outside [0, 8) lives in the neighbouring
 // block (GetVoxel, src/tracer.cu:114-188: one wrap per axis), which is looked up ONCE per
@@ -394,13 +409,13 @@ __device__ __forceinline__ void resolve_taps(const TraceParams& p, BlockCache& c
 
 // trilinear SDF (src/tracer.cu:265-280,312).
 // FMA map: n00 = v000*w0x + v001*w1x -> FMUL v001*w1x ; FFMA v000*w0x + .   (same for y and z)
-template <bool F, bool PEERS>
+template <bool F, bool PEERS, bool SOA>
 __device__ __forceinline__ float interp_distance(const TraceParams& p, const Taps& t) {
   float n[8];
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     n[c] = 1.0f;  // Voxel::Empty()
-    if (t.data[c] != -1) n[c] = __uint_as_float(__ldg(voxel_words<PEERS>(p, t.data[c], t.off[c])));
+    if (t.data[c] != -1) n[c] = load_distance<PEERS, SOA>(p, t.data[c], t.off[c]);
   }
   const float w0x = sub(1.0f, t.w1x), w0y = sub(1.0f, t.w1y), w0z = sub(1.0f, t.w1z);
   const float n00 = FP<F>::mad(n[0], w0x, mul(n[1], t.w1x));
@@ -481,7 +496,7 @@ enum { ST_MARCH = 0, ST_REFINE = 1, ST_DONE = 2 };
 // expensive instructions run with most lanes active instead of 7-9 of 32.  The order of
 // operations of each ray is unchanged, so the result is bit-identical to the per-ray loop.
 // DIAG: per-warp timeline / trip counters for tools/tune_bench.py (compiled out of the product kernels)
-template <bool F, bool KEYS, bool PEERS, bool DIAG>
+template <bool F, bool KEYS, bool PEERS, bool DIAG, bool SOA>
 __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const TraceParams p) {
   pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
   pdl_trigger();  // the next one may be scheduled as this grid drains
@@ -541,6 +556,9 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   }
 
   // parked lane: waits for phase B with the block / voxel coordinates of its point
+  // Look-ahead (see below): distance along the ray that is still covered by the last prefetch round.
+  // Bookkeeping only - it decides when to prefetch, never what a ray computes.
+  float ahead = 0.f;
   bool parked = false;
   int kbx = 0, kby = 0, kbz = 0, kdata = -1;
   float kwx = 0.f, kwy = 0.f, kwz = 0.f;
@@ -563,6 +581,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       pt.x = FP<F>::mad(dir.x, s, pt.x);
       pt.y = FP<F>::mad(dir.y, s, pt.y);
       pt.z = FP<F>::mad(dir.z, s, pt.z);
+      ahead -= s;
       return true;  // stepped: depth / iteration test follows
     }
     // ST_REFINE, block found: second refinement step, then the final depth
@@ -644,6 +663,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
           const int rflags = __shfl_sync(0xffffffffu, (cap ? 1 : 0) | (out ? 2 : 0) | (occ ? 4 : 0), w);
           if (lane == f) {
             dbg_steps += w + 1;
+            ahead = 0.f;
             pt.x = rx; pt.y = ry; pt.z = rz;
             bx = rbx; by = rby; bz = rbz;
             iters = fit + w + 1;
@@ -664,6 +684,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
           pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
           pt.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
           pt.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
+          ahead -= p.block_length.d;
           after_step();
           freeing = false;
           if (state == ST_MARCH) {
@@ -674,6 +695,53 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       }
     }
     if (timeline) { const long long c = clock64(); c_free += c - c_t; c_t = c; }
+    // Look-ahead.  The duration of the kernel is its longest rays: a few silhouette-grazing rays that
+    // run alone in their warp through ~30 dependent trips (hash entry -> sample -> neighbour entries
+    // -> taps), every one a chain of cold misses.  When a warp is down to a few live lanes, its 32
+    // lanes walk AHEAD of one such ray - lane j takes the position (j + 1) voxel lengths further along
+    // it - resolve the blocks there (into the ray's own block cache) and pull the distance lines those
+    // positions sample into L1 with plain loads that nobody waits for.  The ray then finds its next
+    // ~32 voxels of path in shared memory / L1 instead of DRAM (or a peer GPU).  Positions are only
+    // approximate and nothing read here reaches a result: the ray still runs its own exact steps.
+    if (SOA && p.ahead_lanes > 0) {
+      const unsigned alive = __ballot_sync(0xffffffffu, state != ST_DONE);
+      if (__popc(alive) <= p.ahead_lanes) {
+        unsigned need = __ballot_sync(0xffffffffu, state != ST_DONE && !parked && ahead <= 0.f);
+        while (need) {
+          const int f = __ffs(need) - 1;
+          need &= need - 1;
+          const float step = p.voxel_length.d * (float)(lane + 1);
+          Vec3 c;
+          c.x = fmaf(__shfl_sync(0xffffffffu, dir.x, f), step, __shfl_sync(0xffffffffu, pt.x, f));
+          c.y = fmaf(__shfl_sync(0xffffffffu, dir.y, f), step, __shfl_sync(0xffffffffu, pt.y, f));
+          c.z = fmaf(__shfl_sync(0xffffffffu, dir.z, f), step, __shfl_sync(0xffffffffu, pt.z, f));
+          const float qx = c.x * p.block_length.r, qy = c.y * p.block_length.r, qz = c.z * p.block_length.r;
+          const int cbx = (int)floorf(qx), cby = (int)floorf(qy), cbz = (int)floorf(qz);
+          BlockCache fc;
+          fc.keys = s_keys + ((threadIdx.x & ~31) | f);
+          fc.data = s_data + ((threadIdx.x & ~31) | f);
+          fc.stride = cache.stride;
+          int d = -1;
+          const bool known = fc.peek(cbx, cby, cbz, d);
+          if (!known && space_bit(p, cbx, cby, cbz)) d = lookup_block<PEERS>(p, cbx, cby, cbz);
+          // one writer per slot of the ray's cache (a key and its id are two words)
+          const int slot = BlockCache::slot(cbx, cby, cbz);
+          const unsigned same = __match_any_sync(0xffffffffu, slot);
+          if (!known && lane == __ffs(same) - 1) fc.put(cbx, cby, cbz, d);
+          if (d != -1) {
+            const int vx = min(7, max(0, (int)((qx - (float)cbx) * 8.0f)));
+            const int vy = min(7, max(0, (int)((qy - (float)cby) * 8.0f)));
+            const int vz = min(7, max(0, (int)((qz - (float)cbz) * 8.0f)));
+            const float* base = PEERS ? p.peer_sdf[d >> kPeerShift] : p.sdf;
+            const float* line = base + (size_t)(d & ((1 << kPeerShift) - 1)) * VK_BLOCK_VOXELS + vz * 64 + vy * 8 + vx;
+            float sink;
+            asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(sink) : "l"(line));
+          }
+          __syncwarp();
+          if (lane == f) ahead = p.voxel_length.d * 30.0f;
+        }
+      }
+    }
     if (state != ST_DONE && !parked) {
       const int data = find_data<PEERS>(p, cache, bx, by, bz);
       if (data != -1) {
@@ -684,7 +752,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         float sdf = 0.f;
         if (state == ST_MARCH) {
           const int vx = (int)wx, vy = (int)wy, vz = (int)wz;  // Q22: may be 8 on a face
-          sdf = __uint_as_float(__ldg(voxel_words<PEERS>(p, data, vz * 64 + vy * 8 + vx)));
+          sdf = load_distance<PEERS, SOA>(p, data, vz * 64 + vy * 8 + vx);
           want = (sdf <= 0.1f && sdf >= -0.5f);
         }
         if (want) {
@@ -698,6 +766,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
         pt.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
         pt.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
+        ahead -= p.block_length.d;
         after_step();
       } else {
         // REFINE without a block under the backed-up point: no second interpolation
@@ -714,7 +783,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         if (parked) {
           Taps taps;
           resolve_taps<PEERS>(p, cache, kbx, kby, kbz, kdata, kwx, kwy, kwz, taps);
-          const float sdf = interp_distance<F, PEERS>(p, taps);
+          const float sdf = interp_distance<F, PEERS, SOA>(p, taps);
           ipt = pt;
           has_interp = true;
           parked = false;
@@ -1024,12 +1093,14 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
                               cudaStream_t s) {
   t.entries = entries;
   t.voxels = voxels;
+  t.sdf = nullptr;
   t.bounds = bounds;
   t.bucket_bits = bucket_bits;
   t.space_bits = nullptr;
   t.free_run = 0;
   t.coop_lanes = g_tune[VK_TUNE_RAY_COOP_LANES].load();
   t.coop_rounds = g_tune[VK_TUNE_RAY_COOP_ROUNDS].load();
+  t.ahead_lanes = g_tune[VK_TUNE_RAY_AHEAD_LANES].load();
   t.negated_hi = false;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
@@ -1042,7 +1113,7 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.w = w; t.h = h; t.bw = bw; t.bh = bh;
   t.shard_rank = 0; t.shard_count = 1; t.shard_shift = 0;
   t.peer_count = 1; t.peer_rank = 0;
-  for (int i = 0; i < VK_MAX_SHARDS; ++i) { t.peer_entries[i] = entries; t.peer_voxels[i] = voxels; }
+  for (int i = 0; i < VK_MAX_SHARDS; ++i) { t.peer_entries[i] = entries; t.peer_voxels[i] = voxels; t.peer_sdf[i] = nullptr; }
   t.y_begin = 0; t.y_end = h;
   t.batch_lanes = g_tune[VK_TUNE_RAY_BATCH_LANES].load();
   t.batch_wait = g_tune[VK_TUNE_RAY_BATCH_WAIT].load();
@@ -1058,21 +1129,27 @@ static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
   const int rows = 4 * (threads / 32);
   if (t.y_end <= t.y_begin) return 0;
   dim3 grid((t.w + 7) / 8, (t.y_end - t.y_begin + rows - 1) / rows);
-  if (!KEYS && t.peer_count > 1) {  // sharded volume: lookups may go to the owner's tables
-    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, false, true, false>, grid, dim3(threads), 0, s, t);
-    else launch_chained(vk_raycast_kernel<true, false, true, false>, grid, dim3(threads), 0, s, t);
-  } else if (!KEYS && t.timeline) {  // diagnostics build of the plain kernel
-    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, false, false, true>, grid, dim3(threads), 0, s, t);
-    else launch_chained(vk_raycast_kernel<true, false, false, true>, grid, dim3(threads), 0, s, t);
+  const bool strict = (math_mode == VK_MATH_STRICT);
+  // kernels of a volume (t.sdf set) sample the distance mirror; raw-pointer calls read the voxels
+#define VK_RAY(K, P, D, S)                                                                                    \
+  (strict ? launch_chained(vk_raycast_kernel<false, K, P, D, S>, grid, dim3(threads), 0, s, t)                \
+          : launch_chained(vk_raycast_kernel<true, K, P, D, S>, grid, dim3(threads), 0, s, t))
+  if (!t.sdf) {
+    if (KEYS || t.peer_count > 1) return VK_E_INVALID;
+    VK_RAY(false, false, false, false);
+  } else if (!KEYS && t.peer_count > 1) {  // sharded volume: lookups may go to the owner's tables
+    VK_RAY(false, true, false, true);
+  } else if (!KEYS && t.timeline) {        // diagnostics build of the plain kernel
+    VK_RAY(false, false, true, true);
   } else {
-    if (math_mode == VK_MATH_STRICT) launch_chained(vk_raycast_kernel<false, KEYS, false, false>, grid, dim3(threads), 0, s, t);
-    else launch_chained(vk_raycast_kernel<true, KEYS, false, false>, grid, dim3(threads), 0, s, t);
+    VK_RAY(KEYS, false, false, true);
   }
+#undef VK_RAY
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
 
-static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels, const float* bounds,
+static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels, const float* sdf, const float* bounds,
                                const uint32_t* bucket_bits, const uint32_t* space_bits, int block_count, float block_length,
                                float voxel_length, float trunc_length,
                                const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
@@ -1084,6 +1161,7 @@ static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels
                     Twc, proj, image_w, image_h, bounds_w, bounds_h, s);
   t.depths = depths;
   t.colors = colors;
+  t.sdf = g_tune[VK_TUNE_RAY_SOA].load() ? sdf : nullptr;   // A/B knob: 0 = sample the 20-byte voxels
   if (space_bits) {
     t.space_bits = space_bits;
     t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
@@ -1095,7 +1173,7 @@ extern "C" int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxe
                                  int block_count, float block_length, float voxel_length, float trunc_length,
                                  const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
                                  int image_w, int image_h, int bounds_w, int bounds_h, void* stream) {
-  return compute_points_mode(entries, voxels, bounds, nullptr, nullptr, block_count, block_length, voxel_length, trunc_length, Twc,
+  return compute_points_mode(entries, voxels, nullptr, bounds, nullptr, nullptr, block_count, block_length, voxel_length, trunc_length, Twc,
                              proj, depths, colors, image_w, image_h, bounds_w, bounds_h,
                              g_default_math_mode.load(), (cudaStream_t)stream);
 }
@@ -1174,7 +1252,7 @@ extern "C" int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth,
   cudaStream_t s = (cudaStream_t)stream;
   int rc = trace_bounds(v, view, min_depth, max_depth, bounds, s);
   if (rc) return rc;
-  rc = compute_points_mode(v->entries, v->voxels, bounds, v->bucket_bits, v->space_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
+  rc = compute_points_mode(v->entries, v->voxels, v->sdf, bounds, v->bucket_bits, v->space_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
                            v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, out_depth,
                            out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, v->math_mode, s);
   if (rc) return rc;
@@ -1194,6 +1272,7 @@ extern "C" int vk_trace_keys(const vkVolume* v, const vkFrame* view, float min_d
                     v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, view->depth_w,
                     view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
   t.keys = out_keys;
+  t.sdf = v->sdf;
   t.space_bits = v->space_bits;
   t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
   t.shard_rank = v->shard_rank;
@@ -1240,6 +1319,7 @@ extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const 
                     view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
   t.depths = out_depth;
   t.colors = out_color;
+  t.sdf = v->sdf;
   t.negated_hi = true;
   t.space_bits = v->space_bits;
   t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
@@ -1248,9 +1328,10 @@ extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const 
     t.peer_count = peers->count;
     t.peer_rank = peers->rank;
     for (int i = 0; i < peers->count; ++i) {
-      if (!peers->entries[i] || !peers->voxels[i]) return VK_E_INVALID;
+      if (!peers->entries[i] || !peers->voxels[i] || !peers->sdf[i]) return VK_E_INVALID;
       t.peer_entries[i] = peers->entries[i];
       t.peer_voxels[i] = peers->voxels[i];
+      t.peer_sdf[i] = peers->sdf[i];
     }
   }
   // the normals of the band need the depth of two more rows on each side (src/frame.cu:23-32)
@@ -1266,31 +1347,39 @@ extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const 
 }
 
 extern "C" int vk_ipc_export(const vkVolume* v, vkIpcHandles* out) {
-  if (!v || !v->entries || !v->voxels || !out) return VK_E_INVALID;
-  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "vkIpcHandles holds two CUDA IPC handles");
+  if (!v || !v->entries || !v->voxels || !v->sdf || !out) return VK_E_INVALID;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "vkIpcHandles holds CUDA IPC handles");
   cudaError_t err = cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->entries), v->entries);
   if (err != cudaSuccess) return (int)err;
   err = cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->voxels), v->voxels);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(out->sdf), v->sdf);
   return (int)err;
 }
 
-extern "C" int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels) {
-  if (!handles || !entries || !voxels) return VK_E_INVALID;
-  cudaIpcMemHandle_t h;
-  void* ptr = nullptr;
-  memcpy(&h, handles->entries, sizeof(h));
-  cudaError_t err = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
-  if (err != cudaSuccess) return (int)err;
-  *entries = static_cast<const vkHashEntry*>(ptr);
-  memcpy(&h, handles->voxels, sizeof(h));
-  err = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
-  if (err != cudaSuccess) { cudaIpcCloseMemHandle(const_cast<vkHashEntry*>(*entries)); *entries = nullptr; return (int)err; }
-  *voxels = static_cast<const vkVoxel*>(ptr);
+extern "C" int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels,
+                           const float** sdf) {
+  if (!handles || !entries || !voxels || !sdf) return VK_E_INVALID;
+  const unsigned char* blobs[3] = {handles->entries, handles->voxels, handles->sdf};
+  void* ptrs[3] = {nullptr, nullptr, nullptr};
+  for (int i = 0; i < 3; ++i) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, blobs[i], sizeof(h));
+    const cudaError_t err = cudaIpcOpenMemHandle(&ptrs[i], h, cudaIpcMemLazyEnablePeerAccess);
+    if (err != cudaSuccess) {
+      for (int j = 0; j < i; ++j) cudaIpcCloseMemHandle(ptrs[j]);
+      return (int)err;
+    }
+  }
+  *entries = static_cast<const vkHashEntry*>(ptrs[0]);
+  *voxels = static_cast<const vkVoxel*>(ptrs[1]);
+  *sdf = static_cast<const float*>(ptrs[2]);
   return 0;
 }
 
-extern "C" int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels) {
+extern "C" int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels, const float* sdf) {
   cudaError_t e1 = entries ? cudaIpcCloseMemHandle(const_cast<vkHashEntry*>(entries)) : cudaSuccess;
   cudaError_t e2 = voxels ? cudaIpcCloseMemHandle(const_cast<vkVoxel*>(voxels)) : cudaSuccess;
-  return (int)(e1 != cudaSuccess ? e1 : e2);
+  cudaError_t e3 = sdf ? cudaIpcCloseMemHandle(const_cast<float*>(sdf)) : cudaSuccess;
+  return (int)(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3));
 }

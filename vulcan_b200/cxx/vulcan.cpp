@@ -382,7 +382,18 @@ const Buffer<int>& Volume::GetVisibleBlocks() const
 }
 
 const Buffer<Voxel>& Volume::GetVoxels() const { return voxels_; }
-Buffer<Voxel>& Volume::GetVoxels() { return voxels_; }
+Buffer<Voxel>& Volume::GetVoxels()
+{
+  sdf_stale_ = true;  // the caller may write the pool: the distance mirror is rebuilt before the next trace
+  return voxels_;
+}
+
+void Volume::SyncDistances() const
+{
+  if (!sdf_stale_) return;
+  VK_ASSERT(vk_volume_sync_sdf(&volume_, stream_));
+  sdf_stale_ = false;
+}
 const Buffer<Visibility>& Volume::GetBlockVisibility() const { return block_visibility_; }
 
 void Volume::Reset()
@@ -532,6 +543,7 @@ void Tracer::Trace(Frame& frame)
   EnsureColorImage(frame.color_image, w, h);
   EnsureColorImage(frame.normal_image, w, h);
   const vkFrame f = ToC(frame);
+  volume_->SyncDistances();
   VK_ASSERT(vk_trace(volume_->GetHandle(), &f, depth_range_[0], depth_range_[1],
                      reinterpret_cast<float*>(bounds_.GetData()), frame.depth_image->GetData(),
                      reinterpret_cast<float*>(frame.color_image->GetData()),
@@ -541,6 +553,7 @@ void Tracer::Trace(Frame& frame)
 void Tracer::TraceKeys(const Frame& frame, unsigned long long* device_keys)
 {
   const vkFrame f = ToC(frame);
+  volume_->SyncDistances();
   VK_ASSERT(vk_trace_keys(volume_->GetHandle(), &f, depth_range_[0], depth_range_[1],
                           reinterpret_cast<float*>(bounds_.GetData()), device_keys, volume_->GetStream()));
 }

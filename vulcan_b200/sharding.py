@@ -86,14 +86,15 @@ def merge_keys(keys, group=None):
 
 # ---- exact sharded ray casting over peer memory ---------------------------------------------------
 
-def peer_table(rank, entries_ptrs, voxels_ptrs):
+def peer_table(rank, entries_ptrs, voxels_ptrs, sdf_ptrs):
     """vkPeerTable from per-rank device pointers (own pointers at index `rank`)."""
     from . import _lib
     t = _lib.vkPeerTable()
     t.count, t.rank = len(entries_ptrs), rank
-    for i, (e, v) in enumerate(zip(entries_ptrs, voxels_ptrs)):
+    for i, (e, v, d) in enumerate(zip(entries_ptrs, voxels_ptrs, sdf_ptrs)):
         t.entries[i] = e
         t.voxels[i] = v
+        t.sdf[i] = d
     return t
 
 
@@ -119,25 +120,27 @@ class ShardedTracer:
         api.check(_lib.lib.vk_ipc_export(C.byref(volume._v), C.byref(mine)), "vk_ipc_export")
         blobs = [None] * self.count
         dist.all_gather_object(blobs, bytes(mine), group=group)
-        entries, voxels = [], []
+        entries, voxels, sdf = [], [], []
         self._opened = []
         for r, blob in enumerate(blobs):
             if r == self.rank:
                 entries.append(volume._v.entries)
                 voxels.append(volume._v.voxels)
+                sdf.append(volume._v.sdf)
                 continue
             h = _lib.vkIpcHandles.from_buffer_copy(blob)
-            e, v = C.c_void_p(), C.c_void_p()
-            api.check(_lib.lib.vk_ipc_open(C.byref(h), C.byref(e), C.byref(v)), "vk_ipc_open")
-            self._opened.append((e.value, v.value))
+            e, v, d = C.c_void_p(), C.c_void_p(), C.c_void_p()
+            api.check(_lib.lib.vk_ipc_open(C.byref(h), C.byref(e), C.byref(v), C.byref(d)), "vk_ipc_open")
+            self._opened.append((e.value, v.value, d.value))
             entries.append(e.value)
             voxels.append(v.value)
-        self.peers = peer_table(self.rank, entries, voxels)
+            sdf.append(d.value)
+        self.peers = peer_table(self.rank, entries, voxels, sdf)
 
     def close(self):
         from . import _lib
-        for e, v in self._opened:
-            _lib.lib.vk_ipc_close(e, v)
+        for e, v, d in self._opened:
+            _lib.lib.vk_ipc_close(e, v, d)
         self._opened = []
         self._drop_exchange()
 
