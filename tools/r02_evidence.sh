@@ -45,3 +45,5 @@ timeout 600 compute-sanitizer --tool memcheck python tools/one_frame.py --small 
 timeout 900 compute-sanitizer --tool racecheck python tools/one_frame.py --small --frames 2 > gpurun_out/sanitizer_racecheck.log 2>&1
 timeout 600 compute-sanitizer --tool synccheck python tools/one_frame.py --small --frames 2 > gpurun_out/sanitizer_synccheck.log 2>&1
 tail -3 gpurun_out/sanitizer_*.log
+# ray marcher A/B on the bench workload: distance mirror (knob 10) and look-ahead (knob 11)
+timeout 300 python tools/ray_ab.py --sets "10=0,11=0;10=1,11=0;10=1,11=4;10=1,11=8;10=1,11=16;10=1,11=32" --out ray_ab_c2.json 2>&1 | tail -8
