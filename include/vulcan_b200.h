@@ -31,6 +31,7 @@ extern "C" {
                              /* the reference drops such requests silently,         */
                              /* src/volume.cu:338-356)                              */
 #define VK_E_IO        (-4)  /* snapshot file missing, truncated or of another version */
+#define VK_E_TIMEOUT   (-5)  /* sharded volume: a peer did not arrive at a handshake within ~2 s */
 
 /* vkVolume::math_mode: where float multiply-adds round.                               */
 #define VK_MATH_REFERENCE 0  /* fused exactly where nvcc's default -fmad=true fuses them  */
@@ -106,6 +107,7 @@ enum {
 /* One voxel-hash volume.  Replaces the data members of vulcan::Volume
  * (include/vulcan/volume.h:86-116).  All pointers are device pointers owned by
  * the library between vk_volume_create and vk_volume_destroy. */
+struct vkShard;
 typedef struct vkVolume {
   vkVoxel*     voxels;        /* [(M+E)*512], 256-byte aligned                      */
   vkHashEntry* entries;       /* [M+E]: [0,M) bucket heads, [M,M+E) excess          */
@@ -137,6 +139,10 @@ typedef struct vkVolume {
   int32_t      visible_slot;  /* which of visible[] / VK_CNT_VISIBLE* is current    */
   int32_t      view_id;       /* number of vk_set_view calls so far                 */
   int32_t      math_mode;     /* VK_MATH_REFERENCE (default) or VK_MATH_STRICT       */
+  int32_t      has_color;     /* a colour / light integrator has run (or voxels were written from outside):  */
+                              /* while 0 every Voxel::color_weight is 0, so the ray marcher writes the colour  */
+                              /* that implies - (0,0,0) - without gathering the 8 colour taps per ray          */
+  struct vkShard* shard;      /* replicated lookup structures of a block-sharded volume (vk_shard_create), or NULL */
 } vkVolume;
 
 /* One RGB-D frame on the device.  Replaces vulcan::Frame
@@ -341,6 +347,71 @@ int vk_exchange_bands(const vkExchange* x, int epoch, float* out_depth, float* o
  * also the barrier that orders every rank's integration before any rank's peer reads.  `epoch`
  * as for vk_exchange_bands (the two calls keep separate flags; use the same counter for both). */
 int vk_exchange_bounds(const vkExchange* x, int epoch, float* bounds, void* stream);
+
+/* ---- block-sharded volume with replicated lookup structures (the multi-GPU mode of bench.py) --------
+ *
+ * A rank stores, allocates and integrates exactly the blocks it owns (10 KB of voxels each).  What the
+ * ray marcher needs from a block - its hash entry (16 B) and its distances (vkVolume::sdf, 2 KB) - is
+ * REPLICATED: every rank keeps a local copy of every other rank's hash table and distance mirror, and
+ * the owner's allocation / integration kernels store each entry / each changed 16-byte piece of
+ * distances into all copies as they write their own (plain stores into peer memory over NVLink /
+ * NVSwitch: posted, nobody waits for them).  Ray casting is then purely LOCAL on every rank - every ray
+ * takes exactly the steps of the unsharded march, so the images are bit-identical - and each rank
+ * renders a band of rows.  Per traced view there are two flag handshakes over peer memory and no
+ * library collective:
+ *   1. ray bounds: the last CTA of the bounds kernel stores the rank's 80 x 60 grid into every peer's
+ *      buffer, announces it, waits for the others, leaves the element-wise minimum in place and splits
+ *      the image rows into `count` bands of equal active-cell counts.  This is also the barrier that
+ *      orders every rank's replica stores (earlier in its stream) before any rank's ray cast.
+ *   2. bands: each rank marches its band (+2 rows either side for the normals) into its own output
+ *      images, stores the band into every peer's output images and announces it; after the handshake
+ *      every rank holds the complete depth / colour / normal images.  With gather = 0 step 2 is left
+ *      out (the consumer is the host: each rank downloads only its band, vk_shard_band).
+ * Only the colour of a hit (8 taps of Voxel::color / color_weight, once per ray) is read from the
+ * owner's voxel pool through peer memory, and only if the volume has colour (vkVolume::has_color).
+ *
+ * Setup (host): vk_shard_create on every rank BEFORE the volume allocates anything, exchange the
+ * vkShardHandles (any byte transport: torch.distributed, MPI, a file), vk_shard_connect.  Ranks that
+ * share a process (one thread per GPU with peer access enabled, or the one-GPU emulation of the tests)
+ * call vk_shard_connect_local instead.  All volumes of a sharded set must have the same block counts. */
+typedef struct vkShard {
+  int32_t count, rank;
+  int32_t width, height;                      /* size of the output images                                   */
+  int32_t epoch;                              /* views traced so far                                         */
+  int32_t main_blocks, excess_blocks;
+  int32_t connected;                          /* 0 no, 1 IPC mappings (closed by vk_shard_destroy), 2 local  */
+  vkHashEntry*   entries[VK_MAX_SHARDS];      /* hash table of rank r as THIS rank reads it: the volume's    */
+  float*         sdf[VK_MAX_SHARDS];          /* own arrays for r == rank, local replicas otherwise          */
+  const vkVoxel* voxels[VK_MAX_SHARDS];       /* voxel pools: own / peer-mapped (colour gather only)         */
+  vkHashEntry*   push_entries[VK_MAX_SHARDS]; /* this rank's replica ON rank r (peer memory, write-only)     */
+  float*         push_sdf[VK_MAX_SHARDS];
+  void*          exchange[VK_MAX_SHARDS];     /* exchange + output buffer of every rank (own one included)   */
+} vkShard;
+
+/* What a rank publishes to its peers: CUDA IPC handles (cudaIpcMemHandle_t, 64 bytes each). */
+typedef struct vkShardHandles {
+  unsigned char voxels[64];
+  unsigned char exchange[64];
+  unsigned char rep_entries[VK_MAX_SHARDS][64];   /* [r]: this rank's replica of rank r's table (unused for r == rank) */
+  unsigned char rep_sdf[VK_MAX_SHARDS][64];
+} vkShardHandles;
+
+int vk_shard_create(vkShard* s, vkVolume* v, int rank, int count, int brick_shift, int width, int height,
+                    void* stream);
+int vk_shard_export(const vkShard* s, const vkVolume* v, vkShardHandles* out);
+int vk_shard_connect(vkShard* s, const vkShardHandles* all_ranks /* [count], own slot ignored */);
+int vk_shard_connect_local(vkShard* const* shards, vkVolume* const* volumes, int count);
+int vk_shard_destroy(vkShard* s, vkVolume* v);
+/* Tracer::Trace of a sharded volume (collective: every rank calls it for the same view).  *out_* receive
+ * this rank's output images (device memory inside its exchange buffer, valid until the second-next
+ * call); with gather != 0 they are complete on return of the stream, with gather == 0 only rows
+ * [band_begin, band_end) of vk_shard_band are. */
+int vk_trace_sharded(vkVolume* v, const vkFrame* view, float min_depth, float max_depth, int gather,
+                     float** out_depth, float** out_color, float** out_normal, void* stream);
+/* Rows this rank rendered in the last vk_trace_sharded call (synchronises the stream: the split is
+ * computed on the device from the merged ray bounds).  VK_E_TIMEOUT if a handshake of this rank was ever
+ * given up (a peer did not arrive within ~2 s; the images of that view are incomplete). */
+int vk_shard_band(const vkVolume* v, int* band_begin, int* band_end, void* stream);
 
 /* Rank that owns block (bx, by, bz) when a volume is split over `count` ranks: a pure function
  * of the brick (bx >> shift, by >> shift, bz >> shift).  Host function; the kernels use the

@@ -182,8 +182,9 @@ def test_patches_reference_scenario():
         Xc = np.array([(u - K[2]) / K[0] * d, (v - K[3]) / K[1] * d, d, 1.0])
         Xw = Minv @ Xc
         b = (Xw[:3] / float(block_length)).astype(np.int64)   # truncation, like the test's short conversion
-        entries[i] = [(int(b[0]) & 0xFFFF) | ((int(b[1]) & 0xFFFF) << 16), int(b[2]) & 0xFFFF, 0, -1]
-    entries = entries.astype(np.int32)
+        packed = np.array([(int(b[0]) & 0xFFFF) | ((int(b[1]) & 0xFFFF) << 16), int(b[2]) & 0xFFFF], dtype=np.uint32)
+        entries[i, :2] = packed.view(np.int32)
+        entries[i, 2:] = (0, -1)
     d_entries = torch.from_numpy(entries).cuda()
     d_idx = torch.arange(len(pts), dtype=torch.int32, device="cuda")
     cap = 4096

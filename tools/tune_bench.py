@@ -91,6 +91,10 @@ def main():
         torch.cuda.synchronize()
         lib.vk_debug_trace_timeline(None)
         t = tl.cpu().numpy().astype(np.int64)
+        alive_sum = t[:, 3] >> 40
+        t[:, 3] &= (1 << 40) - 1
+        c_la = t[:, 4] >> 40
+        t[:, 4] &= (1 << 40) - 1
         t0 = t[:, 0].min()
         dur = (t[:, 1] - t[:, 0]) / 1e3
         end = (t[:, 1] - t0) / 1e3
@@ -104,7 +108,8 @@ def main():
             print("  long warp tile (x=%d,y=%d): start %.1f dur %.1f  sm %d trips %d cycles %d (%.0f cyc/trip)" % (
                 (w_ % (W // 8)) * 8, (w_ // (W // 8)) * 4, start[w_], dur[w_], t[w_, 2] >> 32, t[w_, 2] & 0xffffffff,
                 t[w_, 3], t[w_, 3] / max(1, t[w_, 2] & 0xffffffff)))
-            print("      cycles: free-run %d  phase A %d  phase B %d  max-lane free steps %d rounds %d" % (t[w_, 4], t[w_, 5], t[w_, 6], t[w_, 7] & 0xffffffff, t[w_, 7] >> 32))
+            print("      cycles: free-run %d  look-ahead %d  phase A %d  phase B %d  max-lane free steps %d look-ahead rounds %d  mean live lanes %.1f" % (
+                t[w_, 4], c_la[w_], t[w_, 5], t[w_, 6], t[w_, 7] & 0xffffffff, t[w_, 7] >> 32, alive_sum[w_] / max(1, t[w_, 2] & 0xffffffff)))
         trips = (t[:, 2] & 0xffffffff).astype(np.float64)
         print("  all warps: trips total %d, cycles/trip mean %.0f" % (trips.sum(), t[:, 3].sum() / trips.sum()))
         np.save(os.path.join(ROOT, "gpurun_out", "trace_timeline.npy"), t)

@@ -42,7 +42,8 @@ class vkVolume(C.Structure):
         ("voxel_length", C.c_float), ("trunc_length", C.c_float),
         ("min_depth", C.c_float), ("max_depth", C.c_float),
         ("shard_rank", C.c_int32), ("shard_count", C.c_int32), ("shard_shift", C.c_int32), ("shard_halo", C.c_int32),
-        ("visible_slot", C.c_int32), ("view_id", C.c_int32), ("math_mode", C.c_int32),
+        ("visible_slot", C.c_int32), ("view_id", C.c_int32), ("math_mode", C.c_int32), ("has_color", C.c_int32),
+        ("shard", C.c_void_p),
     ]
 
 
@@ -52,6 +53,19 @@ MAX_SHARDS = 8
 class vkPeerTable(C.Structure):
     _fields_ = [("count", C.c_int32), ("rank", C.c_int32), ("entries", C.c_void_p * MAX_SHARDS),
                 ("voxels", C.c_void_p * MAX_SHARDS), ("sdf", C.c_void_p * MAX_SHARDS)]
+
+
+class vkShard(C.Structure):
+    _fields_ = [("count", C.c_int32), ("rank", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
+                ("epoch", C.c_int32), ("main_blocks", C.c_int32), ("excess_blocks", C.c_int32), ("connected", C.c_int32),
+                ("entries", C.c_void_p * MAX_SHARDS), ("sdf", C.c_void_p * MAX_SHARDS), ("voxels", C.c_void_p * MAX_SHARDS),
+                ("push_entries", C.c_void_p * MAX_SHARDS), ("push_sdf", C.c_void_p * MAX_SHARDS),
+                ("exchange", C.c_void_p * MAX_SHARDS)]
+
+
+class vkShardHandles(C.Structure):
+    _fields_ = [("voxels", C.c_ubyte * 64), ("exchange", C.c_ubyte * 64),
+                ("rep_entries", (C.c_ubyte * 64) * MAX_SHARDS), ("rep_sdf", (C.c_ubyte * 64) * MAX_SHARDS)]
 
 
 class vkIpcHandles(C.Structure):
@@ -115,6 +129,13 @@ SYMBOLS = {
     "vk_exchange_normal": [_P, _I, _I],
     "vk_exchange_bands": [C.POINTER(vkExchange), _I, _P, _P, _P, _P],
     "vk_exchange_bounds": [C.POINTER(vkExchange), _I, _P, _P],
+    "vk_shard_create": [C.POINTER(vkShard), C.POINTER(vkVolume), _I, _I, _I, _I, _I, _P],
+    "vk_shard_export": [C.POINTER(vkShard), C.POINTER(vkVolume), C.POINTER(vkShardHandles)],
+    "vk_shard_connect": [C.POINTER(vkShard), C.POINTER(vkShardHandles)],
+    "vk_shard_connect_local": [C.POINTER(C.POINTER(vkShard)), C.POINTER(C.POINTER(vkVolume)), _I],
+    "vk_shard_destroy": [C.POINTER(vkShard), C.POINTER(vkVolume)],
+    "vk_trace_sharded": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _I, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), _P],
+    "vk_shard_band": [C.POINTER(vkVolume), C.POINTER(_I), C.POINTER(_I), _P],
     "vk_downsample_frame": [C.POINTER(vkFrame), C.POINTER(vkFrame), _P],
     "vk_downsample_image": [_P, _I, _I, _I, _I, _P, _P],
     "vk_track_residuals": [C.POINTER(vkFrame), C.POINTER(vkFrame), _P, _P],
@@ -158,5 +179,6 @@ def check(status, what):
     if status > 0:
         raise VulcanError("%s: cuda error %d" % (what, status))
     names = {-1: "invalid argument", -2: "no CUDA device", -3: "voxel/excess pool exhausted",
-             -4: "snapshot file missing, truncated or of another version"}
+             -4: "snapshot file missing, truncated or of another version",
+             -5: "a peer of the sharded volume did not arrive at a handshake"}
     raise VulcanError("%s: %s" % (what, names.get(status, str(status))))

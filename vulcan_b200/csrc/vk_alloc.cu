@@ -44,6 +44,10 @@ struct AllocParams {
   float block_length, inv_block_length, trunc, min_depth, max_depth;
   int view_id;
   int shard_rank, shard_count, shard_shift, shard_halo;
+  // sharded volume with replicated lookup structures: this rank's hash table as its peers hold it
+  // (peer memory); every entry written here is stored there too.  push_count = 0: no replicas.
+  int push_count;
+  vkHashEntry* push_entries[VK_MAX_SHARDS];
 };
 
 // chain walk; returns entry index of block `key` or -1.  `tail` receives the last
@@ -109,6 +113,7 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
           ne.x = (int)((uint32_t)(uint16_t)(int16_t)bx | ((uint32_t)(uint16_t)(int16_t)by << 16));
           ne.y = (int)(uint32_t)(uint16_t)(int16_t)bz;
           ne.w = -1;
+          ne.z = data;
           if (head_empty) {
             // publish coordinates first, then the data id that makes the head "allocated"
             int2* dst = reinterpret_cast<int2*>(p.entries + slot);
@@ -117,10 +122,17 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
             __stcg(reinterpret_cast<int*>(p.entries + slot) + 2, data);
             atomicOr(p.bucket_bits + (h >> 5), 1u << (h & 31));
           } else {
-            ne.z = data;
             __stcg(reinterpret_cast<int4*>(p.entries + slot), ne);
             __threadfence();
             __stcg(reinterpret_cast<int*>(p.entries + tail) + 3, slot);
+          }
+          // the peers' copies of this table: same entry, same link (posted stores; the peers read them
+          // only after the next ray-bounds handshake, so their order does not matter)
+          for (int r = 0; r < p.push_count; ++r) {
+            if (r == p.shard_rank) continue;
+            vkHashEntry* rep = p.push_entries[r];
+            __stcg(reinterpret_cast<int4*>(rep + slot), ne);
+            if (!head_empty) __stcg(reinterpret_cast<int*>(rep + tail) + 3, slot);
           }
           atomicAdd(p.counters + VK_CNT_ALLOCATED, 1);
           idx = slot;
@@ -538,14 +550,21 @@ using namespace vk;
 extern "C" int vk_volume_sync_sdf(vkVolume* v, void* stream) {
   if (!v || !v->voxels || !v->sdf) return VK_E_INVALID;
   const int B = v->main_blocks + v->excess_blocks;
+  v->has_color = 1;   // voxels were written from outside: they may carry colour
   vk_sdf_rebuild_kernel<<<sm_count() * 8, 256, 0, (cudaStream_t)stream>>>(v->entries, v->voxels, v->sdf, B);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
 
+namespace vk { int shard_reset_replicas(vkShard* s, cudaStream_t st); }
+
 extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   if (!v || !v->voxels) return VK_E_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
+  if (v->shard) {
+    const int rc = shard_reset_replicas(v->shard, s);
+    if (rc) return rc;
+  }
   const int B = v->main_blocks + v->excess_blocks;
   const size_t n16 = (size_t)B * VK_BLOCK_VOXELS * sizeof(vkVoxel) / 16;
   vk_fill_pools_kernel<<<148 * 8, 256, 0, s>>>(reinterpret_cast<uint4*>(v->voxels), n16, reinterpret_cast<float4*>(v->sdf), v->entries,
@@ -563,6 +582,7 @@ extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   v->host_counters[VK_CNT_EXCESS_PTR] = v->main_blocks;
   v->visible_slot = 0;
   v->view_id = 0;
+  v->has_color = 0;
   return 0;
 }
 
@@ -660,6 +680,13 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.shard_count = v->shard_count;
   a.shard_shift = v->shard_shift;
   a.shard_halo = v->shard_halo;
+  a.push_count = 0;
+  for (int r = 0; r < VK_MAX_SHARDS; ++r) a.push_entries[r] = nullptr;
+  if (v->shard && v->shard->count > 1) {
+    if (!v->shard->connected) return VK_E_INVALID;
+    a.push_count = v->shard->count;
+    for (int r = 0; r < v->shard->count; ++r) a.push_entries[r] = v->shard->push_entries[r];
+  }
   dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
   const bool strict = (v->math_mode == VK_MATH_STRICT);
   const int mode = g_tune[VK_TUNE_ALLOC_MODE].load();  // 1: tile kernel; 64/128/256: CTA size of the warp kernel

@@ -12,6 +12,7 @@
 // each other in a cycle.  Latency: two NVLink round trips plus the copy at link bandwidth, against
 // ~40 us per call for a small NCCL collective.
 #include "vk_math.cuh"
+#include "vk_shard.cuh"
 #include "vk_launch.h"
 #include <cstring>
 
@@ -43,15 +44,6 @@ __device__ __forceinline__ float* exchange_bounds_slot(float* buffer, int w, int
 }
 __device__ __forceinline__ int* exchange_bounds_flags(float* buffer, int w, int h) {
   return reinterpret_cast<int*>(exchange_bounds_slot(buffer, w, h, VK_MAX_SHARDS));
-}
-
-__device__ __forceinline__ int ld_acquire_sys(const int* p) {
-  int v;
-  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(int* p, int v) {
-  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 __global__ void __launch_bounds__(256) vk_exchange_kernel(const ExchangeParams p) {
@@ -122,6 +114,57 @@ __global__ void __launch_bounds__(1024) vk_exchange_bounds_kernel(const Exchange
       if (r != p.rank) m = fminf(m, __ldcg(exchange_bounds_slot(p.buffers[p.rank], p.w, p.h, r) + i));
     bounds[i] = m;
   }
+}
+
+// Image bands of a sharded volume with replicated lookup structures (vk_trace_sharded): every rank has
+// rendered rows [bands[rank], bands[rank + 1]) into its own output images; it now STORES that band into
+// the same place of every peer's output images (posted writes over NVLink, nothing waits on a load),
+// and the last CTA to finish announces it and waits for the peers' announcements.  When the kernel
+// returns, every rank's output images are complete.
+__global__ void __launch_bounds__(256) vk_push_bands_kernel(const Xchg x, int w, int h) {
+  pdl_wait();
+  pdl_trigger();
+  void* mine = x.buf[x.rank];
+  const int* bands = xchg_bands(mine, x.parity);
+  const int b0 = bands[x.rank], b1 = bands[x.rank + 1];
+  const size_t plane = (size_t)w * h;
+  const size_t row0 = (size_t)b0 * w, rows = (b1 > b0) ? (size_t)(b1 - b0) * w : 0;
+  const float* src = xchg_images(mine, x.parity, w, h);
+  // depth | colour | normal: three contiguous segments per band
+  const size_t seg_off[3] = {row0, plane + 3 * row0, 4 * plane + 3 * row0};
+  const size_t seg_n[3] = {rows, 3 * rows, 3 * rows};
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
+  for (int r = 0; r < x.count; ++r) {
+    if (r == x.rank) continue;
+    float* dst = xchg_images(x.buf[r], x.parity, w, h);
+    for (int sgm = 0; sgm < 3; ++sgm) {
+      const float* a = src + seg_off[sgm];
+      float* b = dst + seg_off[sgm];
+      const size_t n = seg_n[sgm];
+      if ((((uintptr_t)a | (uintptr_t)b) & 15u) == 0) {
+        const size_t n4 = n / 4;
+        for (size_t i = tid; i < n4; i += nthr) reinterpret_cast<float4*>(b)[i] = __ldcg(reinterpret_cast<const float4*>(a) + i);
+        for (size_t i = n4 * 4 + tid; i < n; i += nthr) b[i] = __ldcg(a + i);
+      } else {
+        for (size_t i = tid; i < n; i += nthr) b[i] = __ldcg(a + i);
+      }
+    }
+  }
+  __shared__ bool last;
+  __threadfence_system();
+  __syncthreads();
+  int* ticket = xchg_ticket(mine) + 1;
+  if (threadIdx.x == 0) last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  if (threadIdx.x == 0) *ticket = 0;
+  xchg_handshake(x, true);
+}
+
+int exchange_push_bands(const Xchg& x, int w, int h, cudaStream_t s) {
+  launch_chained(vk_push_bands_kernel, dim3(sm_count() * 2), dim3(256), 0, s, x, w, h);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
 }
 
 }  // namespace vk

@@ -29,6 +29,8 @@ struct IntegrateParams {
   const vkHashEntry* entries;
   vkVoxel* voxels;
   float* sdf;   // vkVolume::sdf, the block-major mirror of Voxel::distance the ray marcher reads
+  int push_count, push_rank;          // sharded volume: the peers' copies of this rank's mirror (peer memory),
+  float* push_sdf[VK_MAX_SHARDS];     // written together with the mirror; push_count = 0: none
   const float* depth;
   const float* color;
   const float* normal;
@@ -281,8 +283,12 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
       n_updated += __popc(dirty & 0x84210u);
       // the thread's 4 distances are one aligned 16-byte piece of the block's distance mirror
       // (voxel index 4t): a warp writes 512 contiguous bytes
-      if (cur.dmask)
-        reinterpret_cast<uint4*>(p.sdf + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = make_uint4(w[0], w[5], w[10], w[15]);
+      if (cur.dmask) {
+        const uint4 d4 = make_uint4(w[0], w[5], w[10], w[15]);
+        reinterpret_cast<uint4*>(p.sdf + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = d4;
+        for (int r = 0; r < p.push_count; ++r)   // posted stores over NVLink; read after the next handshake
+          if (r != p.push_rank) reinterpret_cast<uint4*>(p.push_sdf[r] + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = d4;
+      }
     }
     // changed chunks go back lane-contiguously
     uint32_t chunk_dirty = 0;  // bit c: the thread's chunk c changed
@@ -371,6 +377,14 @@ static int fill_params(IntegrateParams& p, vkVolume* v, const vkFrame* f, float 
   p.entries = v->entries;
   p.voxels = v->voxels;
   p.sdf = v->sdf;
+  p.push_count = 0; p.push_rank = 0;
+  for (int r = 0; r < VK_MAX_SHARDS; ++r) p.push_sdf[r] = nullptr;
+  if (v->shard && v->shard->count > 1) {
+    if (!v->shard->connected) return VK_E_INVALID;
+    p.push_count = v->shard->count;
+    p.push_rank = v->shard->rank;
+    for (int r = 0; r < v->shard->count; ++r) p.push_sdf[r] = v->shard->push_sdf[r];
+  }
   p.depth = f->depth;
   p.color = f->color;
   p.normal = f->normal;
@@ -434,6 +448,7 @@ extern "C" int vk_integrate_color(vkVolume* v, const vkFrame* f, float min_depth
   int rc = fill_params(p, v, f, min_depth, max_depth, max_distance_weight, max_color_weight, (cudaStream_t)stream);
   if (rc) return rc;
   if (!f->color || f->color_w <= 0 || f->color_h <= 0) return VK_E_INVALID;
+  v->has_color = 1;
   return launch_integrate<MODE_COLOR>(p, v->math_mode, (cudaStream_t)stream);
 }
 
@@ -457,5 +472,6 @@ extern "C" int vk_integrate_light(vkVolume* v, const vkFrame* f, float min_depth
   if (rc) return rc;
   p.mask = mask;
   p.light = *light;
+  v->has_color = 1;
   return launch_integrate<MODE_LIGHT>(p, v->math_mode, (cudaStream_t)stream);
 }

@@ -173,6 +173,8 @@ static std::vector<int32_t> ids_in_use(const std::vector<vkHashEntry>& entries) 
 
 extern "C" int vk_volume_load(vkVolume* v, const char* path, void* stream) {
   if (!v || !v->voxels || !path) return VK_E_INVALID;
+  // the peers' copies of a sharded volume's tables could not follow a load
+  if (v->shard && v->shard->count > 1) return VK_E_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
   File file;
   file.f = fopen(path, "rb");

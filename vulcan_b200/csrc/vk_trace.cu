@@ -21,6 +21,7 @@
 //   vk_normals_kernel   32x8 tile + 2 px halo in shared memory.
 // The step-wise entry points of include/vulcan/tracer.cuh are kept as well.
 #include "vk_math.cuh"
+#include "vk_shard.cuh"
 #include "vk_launch.h"
 #include <algorithm>
 #include <cfloat>
@@ -70,6 +71,10 @@ struct BoundsParams {
   const uint32_t* warm;  // optional: table the ray marcher will gather from (vkVolume::space_bits)
   int warm_lines;        // its size in 128-byte lines
   bool negate_hi;        // cells hold (min, -max): an element-wise MIN over ranks combines both
+  // sharded volume (vk_trace_sharded): the last CTA combines the grid with the other ranks' grids over
+  // peer memory and splits the image rows into bands; has_x = 0 otherwise
+  int has_x, image_rows;
+  Xchg x;
 };
 
 // body of ComputePatchesKernel (src/tracer.cu:13-66) for one block.
@@ -166,6 +171,61 @@ __global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
       if (p.negate_hi) atomic_min_float(p.bounds + 2 * i + 1, -hi);
       else atomic_max_float(p.bounds + 2 * i + 1, hi);
     }
+  }
+  if (!p.has_x) return;
+  // ---- sharded volume: the last CTA to arrive holds the rank's complete grid -------------------------
+  __shared__ bool last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = (atomicAdd(xchg_ticket(p.x.buf[p.x.rank]), 1) == (int)gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  if (threadIdx.x == 0) *xchg_ticket(p.x.buf[p.x.rank]) = 0;
+  __threadfence();
+  const int nf = 2 * ncell;
+  // 1. the grid into this rank's slot of every peer's buffer (posted stores over NVLink), then the
+  //    handshake: every rank's grid - and everything the rank stored into its peers' replicas before this
+  //    kernel, i.e. its allocation and integration of this frame - is complete when it returns
+  for (int r = 0; r < p.x.count; ++r) {
+    if (r == p.x.rank) continue;
+    float* slot = xchg_bounds_slot(p.x.buf[r], p.x.parity, p.x.rank);
+    for (int i = threadIdx.x; i < nf; i += blockDim.x) slot[i] = __ldcg(p.bounds + i);
+  }
+  xchg_handshake(p.x, false);
+  // 2. element-wise minimum (cells are (min, -max)) - the same grid on every rank
+  for (int i = threadIdx.x; i < nf; i += blockDim.x) {
+    float m = __ldcg(p.bounds + i);
+    for (int r = 0; r < p.x.count; ++r)
+      if (r != p.x.rank) m = fminf(m, __ldcg(xchg_bounds_slot(p.x.buf[p.x.rank], p.x.parity, r) + i));
+    p.bounds[i] = m;
+    s_cells[i] = m;
+  }
+  __syncthreads();
+  // 3. row bands with equal numbers of active cells (cells some ray has to march): the same split on every
+  //    rank, computed from the same grid; rank r renders pixel rows [bands[r], bands[r + 1])
+  int* row_active = reinterpret_cast<int*>(s_cells + nf);
+  if (threadIdx.x < p.bh) {
+    int cnt = 0;
+    for (int cx = 0; cx < p.bw; ++cx) {
+      const float lo = s_cells[2 * (threadIdx.x * p.bw + cx)], nhi = s_cells[2 * (threadIdx.x * p.bw + cx) + 1];
+      cnt += (lo < -nhi) ? 1 : 0;
+    }
+    row_active[threadIdx.x] = cnt;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int* bands = xchg_bands(p.x.buf[p.x.rank], p.x.parity);
+    long long total = 0;
+    for (int r = 0; r < p.bh; ++r) total += row_active[r];
+    long long acc = 0;
+    int k = 1;
+    bands[0] = 0;
+    for (int r = 0; r < p.bh && k < p.x.count; ++r) {
+      acc += row_active[r];
+      // first pixel row of bounds row r + 1 (a pixel row y lies in bounds row bh * y / image_rows)
+      while (k < p.x.count && acc * p.x.count >= total * k) bands[k++] = ((r + 1) * p.image_rows + p.bh - 1) / p.bh;
+    }
+    while (k <= p.x.count) bands[k++] = p.image_rows;
   }
 }
 
@@ -267,6 +327,9 @@ struct TraceParams {
   const float* peer_sdf[VK_MAX_SHARDS];
   int peer_count, peer_rank;
   int y_begin, y_end;           // image rows marched by this launch
+  const int* bands;             // sharded volume: device table of row bands (this rank marches bands[band_rank] - 2 ..
+  int band_rank;                // bands[band_rank + 1] + 2); NULL: y_begin / y_end
+  int with_color;               // 0: the volume holds no colour (every color_weight is 0): skip the colour gather
   int debug_flags;              // diagnostics: 1 = skip the filter load, 2 = skip the block division
   int debug_only_y;
   int debug_only_x;             // diagnostics: march only the tile column starting at this x
@@ -505,13 +568,20 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   // warp tile 8x4 pixels, CTA = wpc tiles stacked in y
   const int x = blockIdx.x * 8 + (lane & 7);
   const int y = p.y_begin + (blockIdx.y * wpc + warp) * 4 + (lane >> 3);
-  const bool inside = (x < p.w && y < p.y_end);
+  int y_lo = p.y_begin, y_hi = p.y_end;
+  if (p.bands) {  // rows of this rank's band plus the two rows either side its normals need
+    const int b0 = p.bands[p.band_rank], b1 = p.bands[p.band_rank + 1];
+    y_lo = (b1 > b0) ? max(0, b0 - 2) : 0;
+    y_hi = (b1 > b0) ? min(p.h, b1 + 2) : 0;
+  }
+  const bool inside = (x < p.w && y >= y_lo && y < y_hi);
   unsigned long long* const timeline = DIAG ? p.timeline : nullptr;
   unsigned long long t_start = 0;
   if (timeline) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
   const long long c_start = DIAG ? clock64() : 0;
   int dbg_trips = 0;
-  long long c_free = 0, c_a = 0, c_b = 0, c_t = 0;
+  long long c_free = 0, c_a = 0, c_b = 0, c_t = 0, c_la = 0;
+  int dbg_alive_sum = 0;
   int dbg_steps = 0, dbg_rounds = 0;
 
   float lo = 0.f, hi = 0.f;
@@ -703,6 +773,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     // positions sample into L1 with plain loads that nobody waits for.  The ray then finds its next
     // ~32 voxels of path in shared memory / L1 instead of DRAM (or a peer GPU).  Positions are only
     // approximate and nothing read here reaches a result: the ray still runs its own exact steps.
+    if (timeline && lane == 0) dbg_alive_sum += __popc(__ballot_sync(0xffffffffu, state != ST_DONE));
     if (SOA && p.ahead_lanes > 0) {
       const unsigned alive = __ballot_sync(0xffffffffu, state != ST_DONE);
       if (__popc(alive) <= p.ahead_lanes) {
@@ -739,9 +810,11 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
           }
           __syncwarp();
           if (lane == f) ahead = p.voxel_length.d * 30.0f;
+          ++dbg_rounds;
         }
       }
     }
+    if (timeline) { const long long c = clock64(); c_la += c - c_t; c_t = c; }
     if (state != ST_DONE && !parked) {
       const int data = find_data<PEERS>(p, cache, bx, by, bz);
       if (data != -1) {
@@ -810,8 +883,8 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     timeline[8 * wid] = t_start;
     timeline[8 * wid + 1] = t_end;
     timeline[8 * wid + 2] = ((unsigned long long)smid << 32) | (unsigned)dbg_trips;
-    timeline[8 * wid + 3] = (unsigned long long)(clock64() - c_start);
-    timeline[8 * wid + 4] = (unsigned long long)c_free;
+    timeline[8 * wid + 3] = (unsigned long long)(clock64() - c_start) | ((unsigned long long)dbg_alive_sum << 40);
+    timeline[8 * wid + 4] = (unsigned long long)c_free | ((unsigned long long)c_la << 40) ;
     timeline[8 * wid + 5] = (unsigned long long)c_a;
     timeline[8 * wid + 6] = (unsigned long long)c_b;
     timeline[8 * wid + 7] = ((unsigned long long)dbg_rounds << 32) | (unsigned)dbg_steps;
@@ -821,7 +894,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   Vec3 color = {0.f, 0.f, 0.f};
   if (red) {
     color.x = 1.f;
-  } else if (has_interp) {
+  } else if (has_interp && p.with_color) {
     const int bx = (int)floorf(divc(ipt.x, p.block_length));
     const int by = (int)floorf(divc(ipt.y, p.block_length));
     const int bz = (int)floorf(divc(ipt.z, p.block_length));
@@ -916,12 +989,19 @@ __device__ __forceinline__ Vec3 normal_from_tile(const float* tile, int stride, 
 // FMUL a.z*b.y ; FFMA a.y*b.z - .   (include/vulcan/matrix.h:174-183)
 template <bool F>
 __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, const vkProjection proj,
-                                                         float* normals, int w, int h, int y_begin, int y_end) {
+                                                         float* normals, int w, int h, int y_begin, int y_end,
+                                                         const int* bands, int band_rank) {
   pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
   pdl_trigger();  // the next one may be scheduled as this grid drains
   constexpr int TW = 32, TH = 8, PAD = 2, SW = TW + 2 * PAD, SH = TH + 2 * PAD;
   __shared__ float tile[SH * SW];
   const int x0 = blockIdx.x * TW, y0 = y_begin + blockIdx.y * TH;
+  int y_lo = y_begin;
+  if (bands) {  // sharded volume: the grid covers the whole image, this rank writes the rows of its band
+    y_lo = bands[band_rank];
+    y_end = bands[band_rank + 1];
+    if (y0 >= y_end || y0 + TH <= y_lo) return;
+  }
   for (int s = threadIdx.x; s < SH * SW; s += TW * TH) {
     const int gx = x0 - PAD + (s % SW), gy = y0 - PAD + (s / SW);
     float d = 0;
@@ -931,7 +1011,7 @@ __global__ void __launch_bounds__(256) vk_normals_kernel(const float* depths, co
   __syncthreads();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int x = x0 + tx, y = y0 + ty;
-  if (x >= w || y >= y_end) return;
+  if (x >= w || y >= y_end || y < y_lo) return;
   const Vec3 n = normal_from_tile<F>(tile, SW, tx + PAD, ty + PAD, x, y, proj);
   const float nx = n.x, ny = n.y, nz = n.z;
   const size_t o = 3 * ((size_t)y * w + x);
@@ -1056,6 +1136,8 @@ static void fill_bounds_params(BoundsParams& b, const float* Tcw_colmajor, const
   b.visible = nullptr; b.count = nullptr; b.entries = nullptr;
   b.warm = nullptr; b.warm_lines = 0;
   b.negate_hi = false;
+  b.has_x = 0; b.image_rows = image_h;
+  memset(&b.x, 0, sizeof(b.x));
 }
 
 extern "C" int vk_compute_patches(const int* indices, const vkHashEntry* entries, const vkTransform* Tcw,
@@ -1115,6 +1197,8 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.peer_count = 1; t.peer_rank = 0;
   for (int i = 0; i < VK_MAX_SHARDS; ++i) { t.peer_entries[i] = entries; t.peer_voxels[i] = voxels; t.peer_sdf[i] = nullptr; }
   t.y_begin = 0; t.y_end = h;
+  t.bands = nullptr; t.band_rank = 0;
+  t.with_color = 1;
   t.batch_lanes = g_tune[VK_TUNE_RAY_BATCH_LANES].load();
   t.batch_wait = g_tune[VK_TUNE_RAY_BATCH_WAIT].load();
   t.debug_only_x = g_tune[6].load() & 0x3ff;
@@ -1124,7 +1208,7 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
 }
 
 template <bool KEYS>
-static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
+static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s, bool sharded = false) {
   const int threads = (g_tune[VK_TUNE_RAY_CTA_THREADS].load() == 64) ? 64 : 32;
   const int rows = 4 * (threads / 32);
   if (t.y_end <= t.y_begin) return 0;
@@ -1137,7 +1221,7 @@ static int launch_raycast(const TraceParams& t, int math_mode, cudaStream_t s) {
   if (!t.sdf) {
     if (KEYS || t.peer_count > 1) return VK_E_INVALID;
     VK_RAY(false, false, false, false);
-  } else if (!KEYS && t.peer_count > 1) {  // sharded volume: lookups may go to the owner's tables
+  } else if (!KEYS && (t.peer_count > 1 || sharded)) {  // sharded volume: lookups go to the owner's table (or its replica)
     VK_RAY(false, true, false, true);
   } else if (!KEYS && t.timeline) {        // diagnostics build of the plain kernel
     VK_RAY(false, false, true, true);
@@ -1153,7 +1237,8 @@ static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels
                                const uint32_t* bucket_bits, const uint32_t* space_bits, int block_count, float block_length,
                                float voxel_length, float trunc_length,
                                const vkTransform* Twc, const vkProjection* proj, float* depths, float* colors,
-                               int image_w, int image_h, int bounds_w, int bounds_h, int math_mode, cudaStream_t s) {
+                               int image_w, int image_h, int bounds_w, int bounds_h, int math_mode, cudaStream_t s,
+                               int with_color = 1) {
   if (!entries || !voxels || !bounds || !Twc || !proj || !depths || !colors || image_w <= 0 || image_h <= 0)
     return VK_E_INVALID;
   TraceParams t;
@@ -1161,6 +1246,7 @@ static int compute_points_mode(const vkHashEntry* entries, const vkVoxel* voxels
                     Twc, proj, image_w, image_h, bounds_w, bounds_h, s);
   t.depths = depths;
   t.colors = colors;
+  t.with_color = with_color;
   t.sdf = g_tune[VK_TUNE_RAY_SOA].load() ? sdf : nullptr;   // A/B knob: 0 = sample the 20-byte voxels
   if (space_bits) {
     t.space_bits = space_bits;
@@ -1179,15 +1265,18 @@ extern "C" int vk_compute_points(const vkHashEntry* entries, const vkVoxel* voxe
 }
 
 static int normals_mode(const float* depths, const vkProjection* proj, float* normals, int image_w, int image_h,
-                        int math_mode, cudaStream_t s, int y_begin = 0, int y_end = -1) {
+                        int math_mode, cudaStream_t s, int y_begin = 0, int y_end = -1, const int* bands = nullptr,
+                        int band_rank = 0) {
   if (!depths || !proj || !normals || image_w <= 0 || image_h <= 0) return VK_E_INVALID;
   if (y_end < 0) y_end = image_h;
   if (y_end <= y_begin) return 0;
   dim3 grid((image_w + 31) / 32, (y_end - y_begin + 7) / 8);
   if (math_mode == VK_MATH_STRICT)
-    launch_chained(vk_normals_kernel<false>, grid, dim3(256), 0, s, depths, *proj, normals, image_w, image_h, y_begin, y_end);
+    launch_chained(vk_normals_kernel<false>, grid, dim3(256), 0, s, depths, *proj, normals, image_w, image_h, y_begin, y_end,
+                   bands, band_rank);
   else
-    launch_chained(vk_normals_kernel<true>, grid, dim3(256), 0, s, depths, *proj, normals, image_w, image_h, y_begin, y_end);
+    launch_chained(vk_normals_kernel<true>, grid, dim3(256), 0, s, depths, *proj, normals, image_w, image_h, y_begin, y_end,
+                   bands, band_rank);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }
@@ -1226,7 +1315,7 @@ extern "C" int vk_prepare_frame(int image_w, int image_h, const float* src, cons
 static const int kBoundsGrid = 32;
 
 static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, float* bounds,
-                        cudaStream_t s, bool negate_hi = false) {
+                        cudaStream_t s, bool negate_hi = false, const Xchg* x = nullptr) {
   // Tracer::ComputePatches + ComputeBounds (src/tracer.cpp:49-76), 80x60 grid hard coded
   int rc = reset_bounds(bounds, VK_BOUNDS_W * VK_BOUNDS_H, negate_hi ? +FLT_MAX : -FLT_MAX, s);
   if (rc) return rc;
@@ -1239,7 +1328,8 @@ static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth,
   b.warm = v->space_bits;
   b.warm_lines = VK_SPACE_WORDS / 32;
   b.negate_hi = negate_hi;
-  const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float);
+  if (x) { b.has_x = 1; b.x = *x; }
+  const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float) + 64 * sizeof(int);
   if (v->math_mode == VK_MATH_STRICT) launch_chained(vk_bounds_kernel<false>, dim3(kBoundsGrid), dim3(512), smem, s, b);
   else launch_chained(vk_bounds_kernel<true>, dim3(kBoundsGrid), dim3(512), smem, s, b);
   VK_COUNT_LAUNCH();
@@ -1254,7 +1344,8 @@ extern "C" int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth,
   if (rc) return rc;
   rc = compute_points_mode(v->entries, v->voxels, v->sdf, bounds, v->bucket_bits, v->space_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
                            v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, out_depth,
-                           out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, v->math_mode, s);
+                           out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, v->math_mode, s,
+                           v->has_color);
   if (rc) return rc;
   if (out_normal)
     rc = normals_mode(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, v->math_mode, s);
@@ -1345,6 +1436,50 @@ extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const 
                       row_begin, row_end);
   return rc;
 }
+
+// ---- block-sharded volume with replicated lookup structures (vk_shard.cu) --------------------------
+
+namespace vk {
+
+int trace_sharded_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, const Xchg& x,
+                         cudaStream_t s) {
+  // the working grid lives in this rank's exchange buffer, cells as (min depth, -max depth)
+  return trace_bounds(v, view, min_depth, max_depth, xchg_grid(x.buf[x.rank]), s, true, &x);
+}
+
+int trace_sharded_band(const vkVolume* v, const vkFrame* view, const Xchg& x, float* depth, float* color, float* normal,
+                       cudaStream_t s) {
+  const vkShard* sh = v->shard;
+  TraceParams t;
+  fill_trace_params(t, v->entries, v->voxels, xchg_grid(x.buf[x.rank]), v->bucket_bits, v->main_blocks,
+                    VK_BLOCK_RES * v->voxel_length, v->voxel_length, v->trunc_length, &view->depth_to_world,
+                    &view->depth_proj, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, s);
+  t.depths = depth;
+  t.colors = color;
+  t.sdf = v->sdf;
+  t.negated_hi = true;
+  t.with_color = v->has_color;
+  t.space_bits = v->space_bits;
+  t.free_run = g_tune[VK_TUNE_RAY_FREE_RUN].load();
+  t.shard_shift = v->shard_shift;
+  // every table the march reads is LOCAL: the volume's own for blocks it owns, the replicas otherwise;
+  // only the colour taps of a hit go to the owner's voxel pool
+  t.peer_count = sh->count;
+  t.peer_rank = sh->rank;
+  for (int r = 0; r < sh->count; ++r) {
+    t.peer_entries[r] = sh->entries[r];
+    t.peer_sdf[r] = sh->sdf[r];
+    t.peer_voxels[r] = sh->voxels[r];
+  }
+  t.bands = xchg_bands(x.buf[x.rank], x.parity);
+  t.band_rank = x.rank;
+  int rc = launch_raycast<false>(t, v->math_mode, s, true);
+  if (rc) return rc;
+  return normals_mode(depth, &view->depth_proj, normal, view->depth_w, view->depth_h, v->math_mode, s, 0, -1, t.bands,
+                      t.band_rank);
+}
+
+}  // namespace vk
 
 extern "C" int vk_ipc_export(const vkVolume* v, vkIpcHandles* out) {
   if (!v || !v->entries || !v->voxels || !v->sdf || !out) return VK_E_INVALID;

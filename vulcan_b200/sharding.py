@@ -104,6 +104,101 @@ def row_band(height, rank, count):
     return min(height, rank * rows), min(height, (rank + 1) * rows)
 
 
+class Shard:
+    """One rank of a block-sharded volume with REPLICATED lookup structures (include/vulcan_b200.h,
+    vk_shard_*): the rank stores, allocates and integrates only the blocks it owns; its hash entries and
+    block distances are copied into every peer as they are written, so every rank ray-casts its band of
+    rows from local memory only, bit-identically to an unsharded volume.
+
+        shard = Shard(volume, rank, count, width, height)      # before the volume allocates anything
+        shard.connect(group)              # one process per GPU: IPC handles over torch.distributed
+        Shard.connect_local(shards)       # or: all ranks in this process (tests / one thread per GPU)
+        volume.SetView(frame); integrator.Integrate(frame)      # as usual, on every rank
+        shard.Trace(frame)                # collective: fills frame.depth_image / color_image / normal_image
+    """
+
+    def __init__(self, volume, rank, count, width, height, shift=3, depth_range=(0.1, 5.0)):
+        import ctypes as C
+        from . import _lib, api
+        self.volume, self.rank, self.count = volume, rank, count
+        self.width, self.height = int(width), int(height)
+        self.depth_range_ = depth_range
+        self._s = _lib.vkShard()
+        api.check(_lib.lib.vk_shard_create(C.byref(self._s), C.byref(volume._v), rank, count, shift, self.width,
+                                           self.height, api._stream()), "vk_shard_create")
+        self._alive = True
+
+    def SetDepthRange(self, dmin, dmax):
+        self.depth_range_ = (dmin, dmax)
+
+    def connect(self, group=None):
+        """Exchange the CUDA IPC handles of the replicas / output buffers over torch.distributed and map
+        the peers' memory (one process per GPU)."""
+        import ctypes as C
+        import torch.distributed as dist
+        from . import _lib, api
+        if self.count == 1:
+            return
+        mine = _lib.vkShardHandles()
+        api.check(_lib.lib.vk_shard_export(C.byref(self._s), C.byref(self.volume._v), C.byref(mine)), "vk_shard_export")
+        blobs = [None] * self.count
+        dist.all_gather_object(blobs, bytes(mine), group=group)
+        everyone = (_lib.vkShardHandles * self.count)()
+        for r, blob in enumerate(blobs):
+            everyone[r] = _lib.vkShardHandles.from_buffer_copy(blob)
+        api.check(_lib.lib.vk_shard_connect(C.byref(self._s), everyone), "vk_shard_connect")
+        dist.barrier(group=group)
+
+    @staticmethod
+    def connect_local(shards):
+        import ctypes as C
+        from . import _lib, api
+        n = len(shards)
+        sp = (C.POINTER(_lib.vkShard) * n)(*[C.pointer(s._s) for s in shards])
+        vp = (C.POINTER(_lib.vkVolume) * n)(*[C.pointer(s.volume._v) for s in shards])
+        api.check(_lib.lib.vk_shard_connect_local(sp, vp, n), "vk_shard_connect_local")
+
+    def Trace(self, frame, gather=True):
+        """Tracer::Trace of the sharded volume (collective).  frame's images become views of this rank's
+        output buffer (valid until the second-next Trace); with gather=False only this rank's band of rows
+        (self.band()) is rendered and nothing is exchanged but the 38 KB ray-bounds grids."""
+        import ctypes as C
+        from . import _lib, api
+        self.volume.SyncDistances()
+        f = self._pose_only(frame)   # the view supplies pose and intrinsics; the images are the shard's
+        d, c, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        api.check(_lib.lib.vk_trace_sharded(C.byref(self.volume._v), C.byref(f), self.depth_range_[0], self.depth_range_[1],
+                                            int(bool(gather)), C.byref(d), C.byref(c), C.byref(n), api._stream()),
+                  "vk_trace_sharded")
+        h, w = self.height, self.width
+        frame.depth_image = api.device_view(d.value, (h, w), "<f4")
+        frame.color_image = api.device_view(c.value, (h, w, 3), "<f4")
+        frame.normal_image = api.device_view(n.value, (h, w, 3), "<f4")
+
+    def _pose_only(self, frame):
+        from . import _lib
+        f = _lib.vkFrame()
+        f.depth_w, f.depth_h = self.width, self.height
+        f.depth_proj = frame.depth_projection.to_c()
+        f.depth_to_world = frame.depth_to_world_transform.to_c()
+        return f
+
+    def band(self):
+        """Rows [begin, end) this rank rendered in the last Trace (synchronises the stream)."""
+        import ctypes as C
+        from . import _lib, api
+        b0, b1 = C.c_int(0), C.c_int(0)
+        api.check(_lib.lib.vk_shard_band(C.byref(self.volume._v), C.byref(b0), C.byref(b1), api._stream()), "vk_shard_band")
+        return b0.value, b1.value
+
+    def close(self):
+        import ctypes as C
+        from . import _lib
+        if getattr(self, "_alive", False):
+            _lib.lib.vk_shard_destroy(C.byref(self._s), C.byref(self.volume._v))
+            self._alive = False
+
+
 class ShardedTracer:
     """Tracer of a block-sharded volume, one instance per rank (process)."""
 
