@@ -59,8 +59,10 @@ def traffic_from_profiles(kernel):
     return None, None
 
 
-SHARDING = ("blocks by brick hash (8^3-block bricks); a rank stores and integrates only the blocks it owns; "
-            "ray cast: see DESIGN.md 5")
+SHARDING = ("blocks owned by brick hash (8^3-block bricks): a rank stores, allocates and integrates only its own blocks; "
+            "hash entries and block distances are replicated into every rank over peer memory (NVLink) as they are "
+            "written; every rank ray-casts a band of rows (bands balanced from the merged ray bounds) from local "
+            "memory and stores it into its peers' images; two flag handshakes per view, no library collective")
 
 
 def load_peaks():
@@ -152,13 +154,26 @@ def run_ours(args, rank, world):
     K, frames = make_frames(args.warmup + args.steps)
     nfr = len(frames)
 
+    shards = {}
+
     def new_volume():
         vol = vb.Volume(MAIN, EXCESS)
         vol.SetVoxelLength(VOXEL)
         vol.SetTruncationLength(TRUNC)
         if world > 1:
-            vol.SetSharding(rank, world, 3)
+            # block-sharded volume with replicated lookup structures (include/vulcan_b200.h, vk_shard_*):
+            # created before anything is allocated; IPC handles travel over torch.distributed
+            sh = sharding.Shard(vol, rank, world, W, H, 3)
+            sh.connect()
+            shards[id(vol)] = sh
         return vol
+
+    def drop_volume(vol):
+        sh = shards.pop(id(vol), None)
+        if sh is not None:
+            barrier()
+            sh.close()
+            barrier()
 
     def transform(raw):
         return vb.Transform(raw[:16].reshape(4, 4).T.copy(), raw[16:].reshape(4, 4).T.copy())
@@ -182,7 +197,9 @@ def run_ours(args, rank, world):
         f.depth_image = depth_t
         return f.to_c()
 
-    def step(vol, cin, cout, outs, ev=None):
+    sharded_out = [C.c_void_p(), C.c_void_p(), C.c_void_p()]
+
+    def step(vol, cin, cout, outs, ev=None, gather=1):
         """One frame through the C ABI (include/vulcan_b200.h) with prebuilt descriptors."""
         s = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         v = C.byref(vol._v)
@@ -192,8 +209,9 @@ def run_ours(args, rank, world):
         vb.api.check(lib.vk_integrate_depth(v, C.byref(cin), 0.1, 5.0, 16.0, s), "vk_integrate_depth")
         if ev: ev[2].record()
         if world > 1:
-            # exact sharded ray cast: bounds all-reduce, row band over peer memory, band all-gather
-            tracers[id(vol)].Trace(out_frames[cout_index[id(cout)]])
+            # every rank ray-casts its band of rows from local memory; two flag handshakes over peer memory
+            vb.api.check(lib.vk_trace_sharded(v, C.byref(cout), 0.1, 5.0, gather, C.byref(sharded_out[0]),
+                                              C.byref(sharded_out[1]), C.byref(sharded_out[2]), s), "vk_trace_sharded")
         else:
             vb.api.check(lib.vk_trace(v, C.byref(cout), 0.1, 5.0, bounds.data_ptr(), outs[0].data_ptr(),
                                       outs[1].data_ptr(), outs[2].data_ptr(), s), "vk_trace")
@@ -206,19 +224,6 @@ def run_ours(args, rank, world):
         f.depth_image = depth_t
         return f
 
-    tracers, out_frames, cout_index = {}, [], {}
-
-    def sharded_setup(vol, cout):
-        if world > 1:
-            tracers[id(vol)] = sharding.ShardedTracer(vol)
-            out_frames.clear()
-            cout_index.clear()
-            for k in range(nfr):
-                f = frame_for(k, outs[0])
-                f.color_image, f.normal_image = outs[1], outs[2]
-                out_frames.append(f)
-                cout_index[id(cout[k])] = k
-
     # ---------------- device-resident leg -------------------------------------------------
     vol = new_volume()
     dev_depth = [torch.from_numpy(d).to(dev) for d, _ in frames]
@@ -227,7 +232,6 @@ def run_ours(args, rank, world):
             torch.zeros((H, W, 3), dtype=torch.float32, device=dev))
     cin = [cframe(k, dev_depth[k]) for k in range(nfr)]
     cout = [cframe(k, outs[0]) for k in range(nfr)]
-    sharded_setup(vol, cout)
     sampler = ClockSampler(dev.index)
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(nfr)]
     count_log = torch.zeros(nfr, dtype=torch.int32, device=dev)
@@ -286,30 +290,41 @@ def run_ours(args, rank, world):
                 "launch_ms": int_ms / args.steps}
 
     # ---------------- end-to-end leg (host buffers, copies inside the timed region) ---------
-    if world > 1:
-        tracers[id(vol)].close()
-        barrier()
+    drop_volume(vol)
     del vol
     torch.cuda.empty_cache()
     vol = new_volume()
-    sharded_setup(vol, cout)
     pinned_in = [torch.from_numpy(d).pin_memory() for d, _ in frames]
     d_in = torch.empty((H, W), dtype=torch.float32, device=dev)
     cin = [cframe(k, d_in) for k in range(nfr)]
     h_depth = torch.empty((H, W), dtype=torch.float32).pin_memory()
     h_color = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
     h_normal = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    band_rows = []
+
     def e2e_sync():
-        """One frame at a time: upload, SetView+Integrate+Trace, download, host sync."""
+        """One frame at a time: upload, SetView+Integrate+Trace, download, host sync.  Sharded: every rank
+        uploads the depth image, renders ITS band of rows (no image exchange: the consumer is the host) and
+        downloads that band only - the ranks' downloads together are one image set."""
         for k in range(nfr):
             if k == args.warmup:
                 barrier()
                 t0 = time.perf_counter()
             d_in.copy_(pinned_in[k], non_blocking=True)
-            step(vol, cin[k], cout[k], outs)
-            h_depth.copy_(outs[0], non_blocking=True)
-            h_color.copy_(outs[1], non_blocking=True)
-            h_normal.copy_(outs[2], non_blocking=True)
+            if world == 1:
+                step(vol, cin[k], cout[k], outs)
+                h_depth.copy_(outs[0], non_blocking=True)
+                h_color.copy_(outs[1], non_blocking=True)
+                h_normal.copy_(outs[2], non_blocking=True)
+            else:
+                step(vol, cin[k], cout[k], outs, gather=0)
+                b0, b1 = shards[id(vol)].band()   # synchronises: the split is computed on the device
+                if k >= args.warmup:
+                    band_rows.append(b1 - b0)
+                if b1 > b0:
+                    for host, ptr, ch in ((h_depth, sharded_out[0], 1), (h_color, sharded_out[1], 3), (h_normal, sharded_out[2], 3)):
+                        src = vb.api.device_view(ptr.value, (H, W) if ch == 1 else (H, W, 3), "<f4")
+                        host[b0:b1].copy_(src[b0:b1], non_blocking=True)
             torch.cuda.current_stream().synchronize()   # the caller reads the result every step
         barrier()
         return time.perf_counter() - t0
@@ -365,12 +380,18 @@ def run_ours(args, rank, world):
         barrier()
         t_e2e, _ = e2e_streamed()
         e2e_mode = "streamed"
+    else:
+        drop_volume(vol)
     t_e2e_t = torch.tensor([t_e2e, t_sync], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_e2e_t, op=dist.ReduceOp.MAX)
     t_e2e, t_sync = (float(x) for x in t_e2e_t.tolist())
-    h2d = W * H * 4
-    d2h = W * H * 4 * 7
+    h2d = W * H * 4 * world          # every rank uploads the depth image
+    d2h = W * H * 4 * 7              # one image set in total: a rank downloads only the rows it rendered
+    if world > 1:
+        rows = torch.tensor([float(sum(band_rows))], dtype=torch.float64, device=dev)
+        dist.all_reduce(rows, op=dist.ReduceOp.SUM)
+        d2h = int(round(float(rows.item()) / max(1, args.steps))) * W * 4 * 7
 
     line = {
         "metric": METRIC, "value": total_units / (tot_ms * 1e-3), "unit": "voxel-updates/s",
@@ -392,7 +413,9 @@ def run_ours(args, rank, world):
                          "frames overlap the kernels; the host takes (and reads a pixel of) frame k-%d's images after "
                          "submitting frame k" % (args.pipeline_depth, args.pipeline_depth - 1))
                 if e2e_mode == "streamed" else
-                "pinned host depth -> device, SetView+Integrate+Trace, traced depth+colour+normal -> pinned host, sync every step",
+                ("pinned host depth -> device on every rank, SetView+Integrate+Trace (each rank renders its band of rows), "
+                 "each rank's band of depth+colour+normal -> pinned host, sync every step" if world > 1 else
+                 "pinned host depth -> device, SetView+Integrate+Trace, traced depth+colour+normal -> pinned host, sync every step"),
                 "host_submit_us_median": (float(np.median(host_submit[args.warmup:]) * 1e6) if host_submit else None),
                 "sync_every_step": {"value": total_units / t_sync, "ms_per_step": t_sync * 1e3 / args.steps}},
         "gpu_launches": int(launches),

@@ -258,6 +258,35 @@ def test_sharded_volume_is_exact(count):
         assert np.array_equal(got.view(np.int32), single[name].view(np.int32)), "sharded %s image differs" % name
 
 
+def _warm_up_sharded_kernels(scn):
+    """One frame through a ONE-rank sharded volume: loads every kernel of the sharded path.  CUDA loads a
+    kernel lazily at its first launch, and that load waits for the device - which in the one-GPU emulation
+    below would be a rank spinning in a handshake its peer (same host thread) has not launched yet.  With
+    one process per GPU the situation cannot arise: a rank launches its side of a handshake before anything
+    that depends on it."""
+    import torch
+    import vulcan_b200 as vb
+    from vulcan_b200 import sharding as S
+    vol = vb.Volume(scn["M"], scn["E"])
+    vol.SetVoxelLength(scn["voxel"])
+    vol.SetTruncationLength(scn["trunc"])
+    sh = S.Shard(vol, 0, 1, scn["w"], scn["h"], 2, scn["depth_range"])
+    fr = scn["frames"][0]
+    frame = vb.Frame()
+    frame.depth_projection = vb.Projection(*scn["K"])
+    T = fr["T"]
+    frame.depth_to_world_transform = vb.Transform(T[:16].reshape(4, 4).T.copy(), T[16:].reshape(4, 4).T.copy())
+    frame.depth_image = torch.from_numpy(fr["depth"]).cuda()
+    vol.SetView(frame)
+    vb.DepthIntegrator(vol).Integrate(frame)
+    out = vb.Frame()
+    out.depth_projection, out.depth_to_world_transform = frame.depth_projection, frame.depth_to_world_transform
+    sh.Trace(out)
+    torch.cuda.synchronize()
+    assert sh.band() == (0, scn["h"])
+    sh.close()
+
+
 @pytest.mark.parametrize("count,name,frames,step", [
     (2, "small", (0, 10, 20), 1.2),
     (4, "small", (0, 1, 2, 3), 25.0),
@@ -283,6 +312,7 @@ def test_replicated_shards_are_exact(count, name, frames, step):
     vb.lib.vk_tune.argtypes = [C.c_int, C.c_int]
     pdl = vb.lib.vk_tune(9, 0)   # one GPU plays all ranks: kernels parked in griddepcontrol.wait would starve the peers
     try:
+        _warm_up_sharded_kernels(scn)
         streams = [torch.cuda.Stream() for _ in range(count)]
         vols, shards, integs = [], [], []
         for rank in range(count):

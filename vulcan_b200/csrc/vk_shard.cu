@@ -197,7 +197,7 @@ extern "C" int vk_trace_sharded(vkVolume* v, const vkFrame* view, float min_dept
   rc = trace_sharded_band(v, view, x, depth, color, normal, st);
   if (rc) return rc;
   // 3. bands to the peers, handshake
-  if (gather && s->count > 1) {
+  if (gather) {   // (a single rank: nothing to store, the handshake is trivial)
     rc = exchange_push_bands(x, s->width, s->height, st);
     if (rc) return rc;
   }

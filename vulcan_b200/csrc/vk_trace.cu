@@ -773,7 +773,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     // positions sample into L1 with plain loads that nobody waits for.  The ray then finds its next
     // ~32 voxels of path in shared memory / L1 instead of DRAM (or a peer GPU).  Positions are only
     // approximate and nothing read here reaches a result: the ray still runs its own exact steps.
-    if (timeline && lane == 0) dbg_alive_sum += __popc(__ballot_sync(0xffffffffu, state != ST_DONE));
+    if (timeline) dbg_alive_sum += __popc(__ballot_sync(0xffffffffu, state != ST_DONE));
     if (SOA && p.ahead_lanes > 0) {
       const unsigned alive = __ballot_sync(0xffffffffu, state != ST_DONE);
       if (__popc(alive) <= p.ahead_lanes) {
