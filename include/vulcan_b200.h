@@ -408,6 +408,13 @@ int vk_shard_destroy(vkShard* s, vkVolume* v);
  * [band_begin, band_end) of vk_shard_band are. */
 int vk_trace_sharded(vkVolume* v, const vkFrame* view, float min_depth, float max_depth, int gather,
                      float** out_depth, float** out_color, float** out_normal, void* stream);
+/* The same view in three parts, for ranks that SHARE a GPU (the one-GPU emulation of the tests): kernels
+ * of one device must never wait for one another, so every rank runs part 1 (local ray bounds, stored into
+ * the peers and announced), then every rank part 2 (combine the bounds - all announcements are in - split
+ * the rows, march the band, store it into the peers, announce), then every rank part 3 (nothing left to
+ * wait for).  stage = 1, 2, 3; same arguments for all three. */
+int vk_trace_sharded_staged(vkVolume* v, const vkFrame* view, float min_depth, float max_depth, int gather,
+                            int stage, float** out_depth, float** out_color, float** out_normal, void* stream);
 /* Rows this rank rendered in the last vk_trace_sharded call (synchronises the stream: the split is
  * computed on the device from the merged ray bounds).  VK_E_TIMEOUT if a handshake of this rank was ever
  * given up (a peer did not arrive within ~2 s; the images of that view are incomplete). */

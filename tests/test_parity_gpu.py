@@ -258,35 +258,6 @@ def test_sharded_volume_is_exact(count):
         assert np.array_equal(got.view(np.int32), single[name].view(np.int32)), "sharded %s image differs" % name
 
 
-def _warm_up_sharded_kernels(scn):
-    """One frame through a ONE-rank sharded volume: loads every kernel of the sharded path.  CUDA loads a
-    kernel lazily at its first launch, and that load waits for the device - which in the one-GPU emulation
-    below would be a rank spinning in a handshake its peer (same host thread) has not launched yet.  With
-    one process per GPU the situation cannot arise: a rank launches its side of a handshake before anything
-    that depends on it."""
-    import torch
-    import vulcan_b200 as vb
-    from vulcan_b200 import sharding as S
-    vol = vb.Volume(scn["M"], scn["E"])
-    vol.SetVoxelLength(scn["voxel"])
-    vol.SetTruncationLength(scn["trunc"])
-    sh = S.Shard(vol, 0, 1, scn["w"], scn["h"], 2, scn["depth_range"])
-    fr = scn["frames"][0]
-    frame = vb.Frame()
-    frame.depth_projection = vb.Projection(*scn["K"])
-    T = fr["T"]
-    frame.depth_to_world_transform = vb.Transform(T[:16].reshape(4, 4).T.copy(), T[16:].reshape(4, 4).T.copy())
-    frame.depth_image = torch.from_numpy(fr["depth"]).cuda()
-    vol.SetView(frame)
-    vb.DepthIntegrator(vol).Integrate(frame)
-    out = vb.Frame()
-    out.depth_projection, out.depth_to_world_transform = frame.depth_projection, frame.depth_to_world_transform
-    sh.Trace(out)
-    torch.cuda.synchronize()
-    assert sh.band() == (0, scn["h"])
-    sh.close()
-
-
 @pytest.mark.parametrize("count,name,frames,step", [
     (2, "small", (0, 10, 20), 1.2),
     (4, "small", (0, 1, 2, 3), 25.0),
@@ -296,12 +267,14 @@ def _warm_up_sharded_kernels(scn):
 def test_replicated_shards_are_exact(count, name, frames, step):
     """The multi-GPU mode of bench.py (vk_shard_*: blocks owned by brick hash, hash entries and block
     distances replicated into every rank as they are written, ray cast local on every rank, row bands
-    balanced from the merged ray bounds, bands pushed to the peers) - emulated on ONE GPU: the ranks are
-    volumes of this process on separate streams (their flag handshakes run concurrently), peer memory
-    is plain device memory.  After every frame each rank ray-casts the model (both epoch parities of the
-    exchange buffers are exercised); every rank's gathered images must be BIT-IDENTICAL to the unsharded
-    ones, the union of owned blocks must be the unsharded block set with identical voxels, and every
-    replica must equal its original."""
+    balanced from the merged ray bounds, bands stored into the peers) - emulated on ONE GPU: the ranks are
+    volumes of this process, peer memory is plain device memory, and because kernels of one device must
+    never wait for one another the collective runs in its three parts (vk_trace_sharded_staged: all ranks
+    announce, then all ranks consume).  The kernels are the ones the real multi-GPU mode runs.  After every
+    frame each rank ray-casts the model (both epoch parities of the exchange buffers are exercised); every
+    rank's gathered images must be BIT-IDENTICAL to the unsharded ones, the union of owned blocks must be
+    the unsharded block set with identical voxels, and every replica must equal its original.
+    (tools/sharded_check.py runs the fused form on real GPUs over CUDA IPC.)"""
     import torch
     import vulcan_b200 as vb
     from vulcan_b200 import sharding as S
@@ -309,83 +282,118 @@ def test_replicated_shards_are_exact(count, name, frames, step):
     single = H.run_ours(scn)
     dmin, dmax = scn["depth_range"]
     shift = 2
-    vb.lib.vk_tune.argtypes = [C.c_int, C.c_int]
-    pdl = vb.lib.vk_tune(9, 0)   # one GPU plays all ranks: kernels parked in griddepcontrol.wait would starve the peers
-    try:
-        _warm_up_sharded_kernels(scn)
-        streams = [torch.cuda.Stream() for _ in range(count)]
-        vols, shards, integs = [], [], []
+    vols, shards, integs = [], [], []
+    for rank in range(count):
+        vol = vb.Volume(scn["M"], scn["E"])
+        vol.SetVoxelLength(scn["voxel"])
+        vol.SetTruncationLength(scn["trunc"])
+        vol.SetDepthRange(dmin, dmax)
+        sh = S.Shard(vol, rank, count, scn["w"], scn["h"], shift, (dmin, dmax))
+        integ = vb.DepthIntegrator(vol)
+        integ.SetDepthRange(dmin, dmax)
+        vols.append(vol), shards.append(sh), integs.append(integ)
+    S.Shard.connect_local(shards)
+    K = scn["K"]
+    views = [[] for _ in range(count)]
+    bands_seen = []
+    for fr in scn["frames"]:
+        depth = torch.from_numpy(fr["depth"]).cuda()
+        T = fr["T"]
+        outs = []
         for rank in range(count):
-            vol = vb.Volume(scn["M"], scn["E"])
-            vol.SetVoxelLength(scn["voxel"])
-            vol.SetTruncationLength(scn["trunc"])
-            vol.SetDepthRange(dmin, dmax)
-            sh = S.Shard(vol, rank, count, scn["w"], scn["h"], shift, (dmin, dmax))
-            integ = vb.DepthIntegrator(vol)
-            integ.SetDepthRange(dmin, dmax)
-            vols.append(vol), shards.append(sh), integs.append(integ)
-        S.Shard.connect_local(shards)
+            frame = vb.Frame()
+            frame.depth_projection = vb.Projection(*K)
+            frame.depth_to_world_transform = vb.Transform(T[:16].reshape(4, 4).T.copy(), T[16:].reshape(4, 4).T.copy())
+            frame.depth_image = depth
+            vols[rank].SetView(frame)
+            integs[rank].Integrate(frame)
+            out = vb.Frame()
+            out.depth_projection, out.depth_to_world_transform = frame.depth_projection, frame.depth_to_world_transform
+            outs.append(out)
+        for stage in (1, 2, 3):
+            for rank in range(count):
+                shards[rank].TraceStage(outs[rank], stage)
         torch.cuda.synchronize()
-        K = scn["K"]
-        views = [[] for _ in range(count)]
-        bands_seen = []
-        for fr in scn["frames"]:
-            depth = torch.from_numpy(fr["depth"]).cuda()
-            T = fr["T"]
-            torch.cuda.synchronize()
-            outs = []
-            for rank in range(count):
-                with torch.cuda.stream(streams[rank]):
-                    frame = vb.Frame()
-                    frame.depth_projection = vb.Projection(*K)
-                    frame.depth_to_world_transform = vb.Transform(T[:16].reshape(4, 4).T.copy(), T[16:].reshape(4, 4).T.copy())
-                    frame.depth_image = depth
-                    vols[rank].SetView(frame)
-                    integs[rank].Integrate(frame)
-                    out = vb.Frame()
-                    out.depth_projection, out.depth_to_world_transform = frame.depth_projection, frame.depth_to_world_transform
-                    shards[rank].Trace(out)
-                    outs.append(out)
-            torch.cuda.synchronize()
-            bands_seen.append([shards[r].band() for r in range(count)])
-            for rank in range(count):
-                views[rank].append((outs[rank].depth_image.cpu().numpy().copy(), outs[rank].color_image.cpu().numpy().copy(),
-                                    outs[rank].normal_image.cpu().numpy().copy()))
-        # bands: a partition of the rows, the same on every rank's device table
-        for b in bands_seen:
-            assert b[0][0] == 0 and b[-1][1] == scn["h"] and all(b[i][1] == b[i + 1][0] for i in range(count - 1)), b
+        bands_seen.append([shards[r].band() for r in range(count)])
         for rank in range(count):
-            d, c, n = H._stack(views[rank])
-            for nm, got in (("depth", d), ("color", c), ("normal", n)):
-                assert np.array_equal(got.view(np.int32), single[nm].view(np.int32)), "rank %d: sharded %s differs" % (rank, nm)
-        owned_keys, owned_vox = [], []
-        for rank, vol in enumerate(vols):
-            assert vol.SyncCounters()[1][4] == 0
-            entries = vol.GetHashEntries().cpu().numpy()
-            tkeys, data, idx = H.allocated_table(entries, scn["M"])
-            bx, by, bz = S.entry_coords(entries[idx])
-            assert (S.shard_owner(bx, by, bz, shift, count) == rank).all(), "a rank stores a block it does not own"
-            owned_keys.append(tkeys)
-            owned_vox.append(vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy())
-            # every peer's replica of this rank: same entries, same distances
-            B = scn["M"] + scn["E"]
-            mirror = vol.GetDistances().cpu().numpy()
-            for peer in range(count):
-                if peer == rank:
-                    continue
-                rep_e = vb.api.device_view(shards[peer]._s.entries[rank], (B, 4), "<i4").cpu().numpy()
-                assert np.array_equal(rep_e, entries), "replica of rank %d's table on rank %d differs" % (rank, peer)
-                rep_d = vb.api.device_view(shards[peer]._s.sdf[rank], (B * 512,), "<f4").cpu().numpy()
-                assert np.array_equal(rep_d.view(np.int32), mirror.view(np.int32)), "replica of rank %d's distances differs" % rank
-        allk = np.concatenate(owned_keys)
-        order = np.argsort(allk, kind="stable")
-        assert np.array_equal(allk[order], single["keys"]), "union of owned blocks != unsharded block set"
-        assert np.array_equal(np.concatenate(owned_vox)[order], single["voxels"]), "owned voxels differ from unsharded"
-        _dump("replicated_shards_%d_%s" % (count, name), dict(count=count, bands=bands_seen, blocks=[int(len(k)) for k in owned_keys]))
-        for sh in shards:
-            sh.close()
-    finally:
-        vb.lib.vk_tune(9, pdl)
+            views[rank].append((outs[rank].depth_image.cpu().numpy().copy(), outs[rank].color_image.cpu().numpy().copy(),
+                                outs[rank].normal_image.cpu().numpy().copy()))
+    # bands: a partition of the rows, the same on every rank's device table
+    for b in bands_seen:
+        assert b[0][0] == 0 and b[-1][1] == scn["h"] and all(b[i][1] == b[i + 1][0] for i in range(count - 1)), b
+    for rank in range(count):
+        d, c, n = H._stack(views[rank])
+        for nm, got in (("depth", d), ("color", c), ("normal", n)):
+            assert np.array_equal(got.view(np.int32), single[nm].view(np.int32)), "rank %d: sharded %s differs" % (rank, nm)
+    owned_keys, owned_vox = [], []
+    for rank, vol in enumerate(vols):
+        assert vol.SyncCounters()[1][4] == 0
+        entries = vol.GetHashEntries().cpu().numpy()
+        tkeys, data, idx = H.allocated_table(entries, scn["M"])
+        bx, by, bz = S.entry_coords(entries[idx])
+        assert (S.shard_owner(bx, by, bz, shift, count) == rank).all(), "a rank stores a block it does not own"
+        owned_keys.append(tkeys)
+        owned_vox.append(vol.GetVoxels().view(-1, 512, 5)[torch.as_tensor(data, device="cuda").long()].cpu().numpy())
+        # every peer's replica of this rank: same entries, same distances
+        B = scn["M"] + scn["E"]
+        mirror = vol.GetDistances().cpu().numpy()
+        for peer in range(count):
+            if peer == rank:
+                continue
+            rep_e = vb.api.device_view(shards[peer]._s.entries[rank], (B, 4), "<i4").cpu().numpy()
+            assert np.array_equal(rep_e, entries), "replica of rank %d's table on rank %d differs" % (rank, peer)
+            rep_d = vb.api.device_view(shards[peer]._s.sdf[rank], (B * 512,), "<f4").cpu().numpy()
+            assert np.array_equal(rep_d.view(np.int32), mirror.view(np.int32)), "replica of rank %d's distances differs" % rank
+    allk = np.concatenate(owned_keys)
+    order = np.argsort(allk, kind="stable")
+    assert np.array_equal(allk[order], single["keys"]), "union of owned blocks != unsharded block set"
+    assert np.array_equal(np.concatenate(owned_vox)[order], single["voxels"]), "owned voxels differ from unsharded"
+    _dump("replicated_shards_%d_%s" % (count, name), dict(count=count, bands=bands_seen, blocks=[int(len(k)) for k in owned_keys]))
+    for sh in shards:
+        sh.close()
+
+
+def test_distance_mirror_tracks_the_voxels():
+    """vkVolume::sdf (what the ray marcher samples) equals Voxel::distance of every voxel after
+    integration, after Volume.Reset and after vk_volume_sync_sdf of voxels written from outside."""
+    import torch
+    import vulcan_b200 as vb
+    scn = H.make_scenario("small", (0, 10, 20), "color")
+    vol = vb.Volume(scn["M"], scn["E"])
+    vol.SetVoxelLength(scn["voxel"])
+    vol.SetTruncationLength(scn["trunc"])
+    integ = vb.ColorIntegrator(vol)
+    K = scn["K"]
+    f = None
+    for fr in scn["frames"]:
+        f = vb.Frame()
+        f.depth_projection = vb.Projection(*K)
+        f.color_projection = vb.Projection(*K)
+        T, Tcd = fr["T"], scn["Tcd"]
+        f.depth_to_world_transform = vb.Transform(T[:16].reshape(4, 4).T.copy(), T[16:].reshape(4, 4).T.copy())
+        f.depth_to_color_transform = vb.Transform(Tcd[:16].reshape(4, 4).T.copy(), Tcd[16:].reshape(4, 4).T.copy())
+        f.depth_image = torch.from_numpy(fr["depth"]).cuda()
+        f.color_image = torch.from_numpy(fr["color"]).cuda()
+        vol.SetView(f)
+        integ.Integrate(f)
+    dist = vol.GetVoxels()[:, 0].contiguous()
+    assert torch.equal(dist, vol.GetDistances().view(torch.int32)), "mirror differs from the voxels after integration"
+    assert (vol.GetDistances() != 1.0).sum().item() > 10000
+    # voxels written from outside: the mirror follows after SyncDistances
+    tracer = vb.Tracer(vol)
+    out = vb.Frame()
+    out.depth_projection, out.depth_to_world_transform = f.depth_projection, f.depth_to_world_transform
+    out.depth_image = torch.zeros((scn["h"], scn["w"]), dtype=torch.float32, device="cuda")
+    tracer.Trace(out)
+    before = out.depth_image.clone()
+    vox = vol.GetVoxelsMutable()
+    shifted = (vox[:, 0].view(torch.float32) + 0.25).clamp(max=1.0)
+    vox[:, 0] = shifted.view(torch.int32)
+    tracer.Trace(out)   # rebuilds the mirror first
+    assert torch.equal(vol.GetVoxels()[:, 0].contiguous(), vol.GetDistances().view(torch.int32))
+    assert not torch.equal(before, out.depth_image), "the ray marcher did not see the voxels written from outside"
+    vol.Reset()
+    assert bool((vol.GetDistances() == 1.0).all())
 
 
 def test_key_merge_is_only_approximate():

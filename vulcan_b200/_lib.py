@@ -135,6 +135,8 @@ SYMBOLS = {
     "vk_shard_connect_local": [C.POINTER(C.POINTER(vkShard)), C.POINTER(C.POINTER(vkVolume)), _I],
     "vk_shard_destroy": [C.POINTER(vkShard), C.POINTER(vkVolume)],
     "vk_trace_sharded": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _I, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), _P],
+    "vk_trace_sharded_staged": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _I, _I, C.POINTER(_P), C.POINTER(_P),
+                                C.POINTER(_P), _P],
     "vk_shard_band": [C.POINTER(vkVolume), C.POINTER(_I), C.POINTER(_I), _P],
     "vk_downsample_frame": [C.POINTER(vkFrame), C.POINTER(vkFrame), _P],
     "vk_downsample_image": [_P, _I, _I, _I, _I, _P, _P],

@@ -4,21 +4,8 @@
 // + per-pixel request kernel (one surviving request per bucket per pass, racy)
 // + per-bucket handler + a 20-barrier scan over all B entries + two blocking
 // symbol memcpys, and the caller has to repeat the whole thing until allocation
-// converges.  Here one call reaches that fixed point with two launches and no host
-// synchronisation:
-//
-//   vk_alloc_kernel    one warp per 8x4 pixel tile walks the truncation band of its
-//                      32 rays in lock step; identical block coordinates inside the
-//                      warp are merged with __match_any_sync so one lane per distinct
-//                      block does a find-or-insert in the hash (per-bucket lock only
-//                      on the insert path).  The first lane to touch an entry in
-//                      this view (atomicExch on a per-entry view stamp) marks it
-//                      VISIBILITY_TRUE and appends it to the new visible list.
-//   vk_carry_kernel    walks the *previous* visible list only (the UNKNOWN entries of
-//                      the reference are exactly that list): entries not touched in
-//                      this view get the 8-corner frustum test (Q6) and are carried
-//                      over (stay UNKNOWN, Q5) or dropped (FALSE).  O(V) instead of
-//                      O(M+E).
+// converges.  Here one call reaches that fixed point with ONE launch and no host
+// synchronisation (vk_setview_kernel below).
 #include "vk_math.cuh"
 #include "vk_launch.h"
 
@@ -63,17 +50,6 @@ __device__ __forceinline__ int find_block(const vkHashEntry* entries, uint32_t h
     if (e.w == -1) { tail = idx; return -1; }
     idx = e.w;
     e = ld_entry_cg(entries + idx);
-  }
-}
-
-__device__ __forceinline__ void touch_entry(const AllocParams& p, int idx) {
-  if (__ldcg(p.stamps + idx) != p.view_id) {
-    const int old = atomicExch(p.stamps + idx, p.view_id);
-    if (old != p.view_id) {
-      p.visibility[idx] = VK_VIS_TRUE;
-      const int pos = atomicAdd(p.counters + p.cnt_slot, 1);
-      p.visible_out[pos] = idx;
-    }
   }
 }
 
@@ -156,313 +132,201 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
   return result;
 }
 
-// CreateAllocationRequestsKernel (src/volume.cu:86-301) + HandleAllocationRequestsKernel
-// (src/volume.cu:303-368) to their common fixed point.
+// One launch per SetView.  CreateAllocationRequestsKernel (src/volume.cu:86-301) +
+// HandleAllocationRequestsKernel (src/volume.cu:303-368) to their common fixed point, then
+// UpdateBlockVisibilityKernel (src/volume.cu:23-84) restricted to the entries that can be
+// VISIBILITY_UNKNOWN, i.e. the previous visible list.
+//
+// A persistent grid (every CTA resident) in three phases:
+//   1. pixels.  A thread walks the truncation band of one depth pixel with the reference's
+//      Amanatides-Woo comparison tree.  A block costs two independent loads - its bucket head and that
+//      head's view stamp, issued one DDA step AHEAD of their use - and in the steady state (block at the
+//      head of its bucket, already stamped by a neighbouring ray) nothing else: no warp-wide matching, no
+//      atomics.  Lanes of a warp that ask for the same block load the same addresses (one transaction).
+//      Only the first ray to touch an entry in this view appends it (atomicExch on the stamp;
+//      warp-aggregated append), and only chain walks and inserts take the slow path.
+//   2. a grid-wide arrival counter (all CTAs are resident by construction: the grid is sized from the
+//      occupancy of this kernel): every entry touched by a ray is now stamped.
+//   3. the previous visible list: entries not stamped in this view get the 8-corner frustum test (Q6)
+//      and are carried over (stay UNKNOWN, Q5) or dropped (FALSE).  The corner tests themselves do not
+//      depend on phase 1 and run BEFORE the counter wait.  The last CTA mirrors the counters to the host.
 // FMA map (reference release SASS of CreateAllocationRequestsKernel):
 //   dir   = Twd * (unproj, 0)      FMUL y*m1; FFMA x*m0 + .; FADD m2 (z == 1); FFMA 0*m3 + .
 //   X     = origin + depth * dir   FFMA dir*depth + origin
 //   begin = X - trunc * dir        FFMA -dir*trunc + X     end = FFMA dir*trunc + X
 //   tmax  = (L*(b + max(0,step)) - begin) / dir     FFMA bf*L - begin ; IEEE div
-template <bool F>
-__global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
-  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
-  pdl_trigger();  // the next one may be scheduled as this grid drains
+struct CarryParams {
+  uint8_t* visibility;
+  int32_t* host_counters;
+  const int32_t* prev_list;
+  int prev_slot;
+  float Tdw[12];
+  int* ticket;   // [0] phase counter, [1] exit counter
+};
+
+// first toucher of an entry in this view: marks it visible and appends it.  The append is aggregated over
+// the lanes that arrive here together (one atomic per group).
+__device__ __forceinline__ void touch_entry(const AllocParams& p, int idx) {
+  const int old = atomicExch(p.stamps + idx, p.view_id);
+  const bool first = (old != p.view_id);
+  if (first) p.visibility[idx] = VK_VIS_TRUE;
+  const unsigned group = __activemask();
+  const unsigned firsts = __ballot_sync(group, first);
+  if (firsts == 0) return;
   const int lane = threadIdx.x & 31;
-  // warp tile 8x4 pixels; the warps of the grid take the tiles row by row (the kernel has no
-  // CTA-level state, so the CTA size only sets the granularity of the waves)
-  const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int tiles_x = (p.w + 7) >> 3;
-  const int x = (tile % tiles_x) * 8 + (lane & 7);
-  const int y = (tile / tiles_x) * 4 + (lane >> 3);
-
-  bool active = (x < p.w && y < p.h);
-  int bx = 0, by = 0, bz = 0, ex = 0, ey = 0, ez = 0, sx = 1, sy = 1, sz = 1;
-  float tmx = 0, tmy = 0, tmz = 0, tdx = 0, tdy = 0, tdz = 0;
-
-  if (active) {
-    const float depth = __ldg(p.depth + y * p.w + x);
-    if (depth < p.min_depth || depth > p.max_depth) active = false;
-    if (active) {
-      const float u = add((float)x, 0.5f), v = add((float)y, 0.5f);
-      Unprojector un;
-      un.init(p.proj);
-      const float d0x = un.x<F>(u), d0y = un.y<F>(v);
-      Mat34 Twd;
-      Twd.load(p.Twd);
-      Vec3 dir = xform0<F>(Twd, d0x, d0y, 1.0f);
-      const float Xx = FP<F>::mad(dir.x, depth, p.Twd[3]);
-      const float Xy = FP<F>::mad(dir.y, depth, p.Twd[7]);
-      const float Xz = FP<F>::mad(dir.z, depth, p.Twd[11]);
-      dir = normalized<F>(dir);
-      const float bgx = FP<F>::nmad(dir.x, p.trunc, Xx), bgy = FP<F>::nmad(dir.y, p.trunc, Xy),
-                  bgz = FP<F>::nmad(dir.z, p.trunc, Xz);
-      const float enx = FP<F>::mad(dir.x, p.trunc, Xx), eny = FP<F>::mad(dir.y, p.trunc, Xy),
-                  enz = FP<F>::mad(dir.z, p.trunc, Xz);
-      sx = (dir.x < 0) ? -1 : 1;
-      sy = (dir.y < 0) ? -1 : 1;
-      sz = (dir.z < 0) ? -1 : 1;
-      const float inv = p.inv_block_length;
-      bx = (int)floorf(mul(bgx, inv));
-      by = (int)floorf(mul(bgy, inv));
-      bz = (int)floorf(mul(bgz, inv));
-      ex = (int)floorf(mul(enx, inv));
-      ey = (int)floorf(mul(eny, inv));
-      ez = (int)floorf(mul(enz, inv));
-      const float ox = FP<F>::msub((float)(bx + max(0, sx)), p.block_length, bgx);
-      const float oy = FP<F>::msub((float)(by + max(0, sy)), p.block_length, bgy);
-      const float oz = FP<F>::msub((float)(bz + max(0, sz)), p.block_length, bgz);
-      tmx = fdiv(ox, dir.x);
-      tmy = fdiv(oy, dir.y);
-      tmz = fdiv(oz, dir.z);
-      if (dir.x == 0) tmx = 1E20f;
-      if (dir.y == 0) tmy = 1E20f;
-      if (dir.z == 0) tmz = 1E20f;
-      tdx = fdiv(mul((float)sx, p.block_length), dir.x);
-      tdy = fdiv(mul((float)sy, p.block_length), dir.y);
-      tdz = fdiv(mul((float)sz, p.block_length), dir.z);
-    }
-  }
-
-  unsigned long long last_key = ~0ull;  // block this lane handled last as leader
-  while (__any_sync(0xffffffffu, active)) {
-    const unsigned long long key = active ? pack_block(bx, by, bz) : ~0ull;
-    const unsigned peers = __match_any_sync(0xffffffffu, key);
-    const bool leader = active && (lane == (__ffs(peers) - 1)) && key != last_key;
-    if (leader) {
-      last_key = key;
-      const uint32_t h = block_hash(bx, by, bz, p.K);
-      // most blocks sit at the head of their bucket, whose index is known before the entry
-      // arrives: its stamp is fetched together with the entry instead of after it
-      const int head_stamp = __ldcg(p.stamps + h);
-      int tail;
-      bool head_empty;
-      int idx = find_block(p.entries, h, key, tail, head_empty);
-      if (idx < 0) {
-        if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) idx = insert_block(p, h, bx, by, bz, key);
-        else mark_space(p, bx, by, bz);  // exists on another rank: the filter is global
-      }
-      if (idx >= 0 && !(idx == (int)h && head_stamp == p.view_id)) touch_entry(p, idx);
-    }
-    if (active) {
-      // Amanatides-Woo step with the reference's comparison tree (src/volume.cu:241-295)
-      if (tmx < tmy) {
-        if (tmx < tmz) { bx += sx; if (bx == ex + sx) active = false; tmx = add(tmx, tdx); }
-        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
-      } else {
-        if (tmy < tmz) { by += sy; if (by == ey + sy) active = false; tmy = add(tmy, tdy); }
-        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
-      }
-    }
-  }
+  const int leader = __ffs(firsts) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(p.counters + p.cnt_slot, __popc(firsts));
+  base = __shfl_sync(group, base, leader);
+  if (first) p.visible_out[base + __popc(firsts & ((1u << lane) - 1))] = idx;
 }
 
-// Same fixed point, organised for memory-level parallelism.  vk_alloc_kernel above looks a block
-// up as soon as one ray of a warp reaches it: a dependent L2 round trip per DDA step with one or
-// two lanes working.  Here a CTA (32x8 pixels) first walks all of its rays - pure arithmetic - and
-// collects the distinct blocks in a shared-memory set (a tile of 256 rays touches a few dozen
-// blocks); then every thread takes one distinct block: find-or-insert in the hash, stamp,
-// and the newly visible entries of the whole CTA are appended with ONE global atomic.
-constexpr int kSetSlots = 1024;           // power of two
-constexpr unsigned long long kEmptyKey = ~0ull;
-
-__device__ __forceinline__ unsigned set_slot(unsigned long long key) {
-  return (unsigned)((key * 0x9E3779B97F4A7C15ull) >> 54);  // top 10 bits
-}
-
-// first toucher of an entry in this view marks it visible; returns true for the first toucher
-__device__ __forceinline__ bool stamp_entry(const AllocParams& p, int idx) {
-  if (__ldcg(p.stamps + idx) == p.view_id) return false;
-  if (atomicExch(p.stamps + idx, p.view_id) == p.view_id) return false;
-  p.visibility[idx] = VK_VIS_TRUE;
-  return true;
-}
-
-__device__ __forceinline__ int resolve_block(const AllocParams& p, unsigned long long key) {
-  const int bx = (int)(int16_t)(key & 0xffff), by = (int)(int16_t)((key >> 16) & 0xffff),
-            bz = (int)(int16_t)((key >> 32) & 0xffff);
-  const uint32_t h = block_hash(bx, by, bz, p.K);
+// everything that is not "block found at the head of its bucket": chain walk, insert, or a block that
+// another rank owns
+__device__ __noinline__ void resolve_slow(const AllocParams& p, uint32_t h, int bx, int by, int bz, unsigned long long key) {
   int tail;
   bool head_empty;
   int idx = find_block(p.entries, h, key, tail, head_empty);
-  if (idx < 0) {
-    if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) idx = insert_block(p, h, bx, by, bz, key);
-    else mark_space(p, bx, by, bz);
-  }
-  return idx;
+  if (idx < 0) idx = insert_block(p, h, bx, by, bz, key);
+  if (idx >= 0 && __ldcg(p.stamps + idx) != p.view_id) touch_entry(p, idx);
 }
 
 template <bool F>
-__global__ void __launch_bounds__(256) vk_alloc_tile_kernel(const AllocParams p) {
+__global__ void __launch_bounds__(256, 4) vk_setview_kernel(const AllocParams p, const CarryParams c) {
   pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
   pdl_trigger();  // the next one may be scheduled as this grid drains
-  __shared__ unsigned long long s_set[kSetSlots];
-  __shared__ int s_list[kSetSlots + 256];
-  __shared__ int s_count, s_base;
-  for (int i = threadIdx.x; i < kSetSlots; i += 256) s_set[i] = kEmptyKey;
-  if (threadIdx.x == 0) s_count = 0;
-  __syncthreads();
-
   const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  // CTA tile 32x8 pixels, warp tile 8x4
-  const int x = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
-  const int y = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
+  const int tiles_x = (p.w + 7) >> 3, tiles = tiles_x * ((p.h + 3) >> 2);
+  const int warps = gridDim.x * (blockDim.x >> 5);
+  Mat34 Twd;
+  Twd.load(p.Twd);
+  Unprojector un;
+  un.init(p.proj);
+  const bool sharded = p.shard_count > 1;
 
-  bool active = (x < p.w && y < p.h);
-  int bx = 0, by = 0, bz = 0, ex = 0, ey = 0, ez = 0, sx = 1, sy = 1, sz = 1;
-  float tmx = 0, tmy = 0, tmz = 0, tdx = 0, tdy = 0, tdz = 0;
-
-  if (active) {
+  // ---- phase 1: warp tiles of 8x4 pixels, taken grid-stride ---------------------------------------
+  for (int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); tile < tiles; tile += warps) {
+    const int x = (tile % tiles_x) * 8 + (lane & 7);
+    const int y = (tile / tiles_x) * 4 + (lane >> 3);
+    if (x >= p.w || y >= p.h) continue;
     const float depth = __ldg(p.depth + y * p.w + x);
-    if (depth < p.min_depth || depth > p.max_depth) active = false;
-    if (active) {
-      const float u = add((float)x, 0.5f), v = add((float)y, 0.5f);
-      Unprojector un;
-      un.init(p.proj);
-      const float d0x = un.x<F>(u), d0y = un.y<F>(v);
-      Mat34 Twd;
-      Twd.load(p.Twd);
-      Vec3 dir = xform0<F>(Twd, d0x, d0y, 1.0f);
-      const float Xx = FP<F>::mad(dir.x, depth, p.Twd[3]);
-      const float Xy = FP<F>::mad(dir.y, depth, p.Twd[7]);
-      const float Xz = FP<F>::mad(dir.z, depth, p.Twd[11]);
-      dir = normalized<F>(dir);
-      const float bgx = FP<F>::nmad(dir.x, p.trunc, Xx), bgy = FP<F>::nmad(dir.y, p.trunc, Xy),
-                  bgz = FP<F>::nmad(dir.z, p.trunc, Xz);
-      const float enx = FP<F>::mad(dir.x, p.trunc, Xx), eny = FP<F>::mad(dir.y, p.trunc, Xy),
-                  enz = FP<F>::mad(dir.z, p.trunc, Xz);
-      sx = (dir.x < 0) ? -1 : 1;
-      sy = (dir.y < 0) ? -1 : 1;
-      sz = (dir.z < 0) ? -1 : 1;
-      const float inv = p.inv_block_length;
-      bx = (int)floorf(mul(bgx, inv));
-      by = (int)floorf(mul(bgy, inv));
-      bz = (int)floorf(mul(bgz, inv));
-      ex = (int)floorf(mul(enx, inv));
-      ey = (int)floorf(mul(eny, inv));
-      ez = (int)floorf(mul(enz, inv));
-      const float ox = FP<F>::msub((float)(bx + max(0, sx)), p.block_length, bgx);
-      const float oy = FP<F>::msub((float)(by + max(0, sy)), p.block_length, bgy);
-      const float oz = FP<F>::msub((float)(bz + max(0, sz)), p.block_length, bgz);
-      tmx = fdiv(ox, dir.x);
-      tmy = fdiv(oy, dir.y);
-      tmz = fdiv(oz, dir.z);
-      if (dir.x == 0) tmx = 1E20f;
-      if (dir.y == 0) tmy = 1E20f;
-      if (dir.z == 0) tmz = 1E20f;
-      tdx = fdiv(mul((float)sx, p.block_length), dir.x);
-      tdy = fdiv(mul((float)sy, p.block_length), dir.y);
-      tdz = fdiv(mul((float)sz, p.block_length), dir.z);
-    }
-  }
+    if (depth < p.min_depth || depth > p.max_depth) continue;
+    const float u = add((float)x, 0.5f), v = add((float)y, 0.5f);
+    const float d0x = un.x<F>(u), d0y = un.y<F>(v);
+    Vec3 dir = xform0<F>(Twd, d0x, d0y, 1.0f);
+    const float Xx = FP<F>::mad(dir.x, depth, p.Twd[3]);
+    const float Xy = FP<F>::mad(dir.y, depth, p.Twd[7]);
+    const float Xz = FP<F>::mad(dir.z, depth, p.Twd[11]);
+    dir = normalized<F>(dir);
+    const float bgx = FP<F>::nmad(dir.x, p.trunc, Xx), bgy = FP<F>::nmad(dir.y, p.trunc, Xy),
+                bgz = FP<F>::nmad(dir.z, p.trunc, Xz);
+    const float enx = FP<F>::mad(dir.x, p.trunc, Xx), eny = FP<F>::mad(dir.y, p.trunc, Xy),
+                enz = FP<F>::mad(dir.z, p.trunc, Xz);
+    const int sx = (dir.x < 0) ? -1 : 1, sy = (dir.y < 0) ? -1 : 1, sz = (dir.z < 0) ? -1 : 1;
+    const float inv = p.inv_block_length;
+    int bx = (int)floorf(mul(bgx, inv)), by = (int)floorf(mul(bgy, inv)), bz = (int)floorf(mul(bgz, inv));
+    const int ex = (int)floorf(mul(enx, inv)), ey = (int)floorf(mul(eny, inv)), ez = (int)floorf(mul(enz, inv));
+    float tmx = fdiv(FP<F>::msub((float)(bx + max(0, sx)), p.block_length, bgx), dir.x);
+    float tmy = fdiv(FP<F>::msub((float)(by + max(0, sy)), p.block_length, bgy), dir.y);
+    float tmz = fdiv(FP<F>::msub((float)(bz + max(0, sz)), p.block_length, bgz), dir.z);
+    if (dir.x == 0) tmx = 1E20f;
+    if (dir.y == 0) tmy = 1E20f;
+    if (dir.z == 0) tmz = 1E20f;
+    const float tdx = fdiv(mul((float)sx, p.block_length), dir.x);
+    const float tdy = fdiv(mul((float)sy, p.block_length), dir.y);
+    const float tdz = fdiv(mul((float)sz, p.block_length), dir.z);
 
-  // ---- phase 1: walk the rays, collect distinct blocks ---------------------------------------
-  unsigned long long last_key = kEmptyKey;
-  while (__any_sync(0xffffffffu, active)) {
-    const unsigned long long key = active ? pack_block(bx, by, bz) : kEmptyKey;
-    const unsigned peers = __match_any_sync(0xffffffffu, key);
-    const bool leader = active && (lane == (__ffs(peers) - 1)) && key != last_key;
-    if (leader) {
-      last_key = key;
-      unsigned slot = set_slot(key);
-      bool placed = false;
-      for (int probe = 0; probe < 64 && !placed; ++probe) {
-        const unsigned long long seen = atomicCAS(&s_set[slot], kEmptyKey, key);
-        placed = (seen == kEmptyKey || seen == key);
-        slot = (slot + 1) & (kSetSlots - 1);
-      }
-      if (!placed) {  // set (nearly) full: resolve on the spot
-        const int idx = resolve_block(p, key);
-        if (idx >= 0) touch_entry(p, idx);
-      }
-    }
-    if (active) {
+    // lookup of the current block: issued here, used one DDA step later
+    uint32_t h = block_hash(bx, by, bz, p.K);
+    int4 ent = ld_entry_cg(p.entries + h);
+    int stamp = __ldcg(p.stamps + h);
+    bool more = true;
+    while (more) {
+      const int cx = bx, cy = by, cz = bz;
+      const uint32_t ch = h;
+      const int4 cent = ent;
+      const int cstamp = stamp;
       // Amanatides-Woo step with the reference's comparison tree (src/volume.cu:241-295)
       if (tmx < tmy) {
-        if (tmx < tmz) { bx += sx; if (bx == ex + sx) active = false; tmx = add(tmx, tdx); }
-        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
+        if (tmx < tmz) { bx += sx; if (bx == ex + sx) more = false; tmx = add(tmx, tdx); }
+        else           { bz += sz; if (bz == ez + sz) more = false; tmz = add(tmz, tdz); }
       } else {
-        if (tmy < tmz) { by += sy; if (by == ey + sy) active = false; tmy = add(tmy, tdy); }
-        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
+        if (tmy < tmz) { by += sy; if (by == ey + sy) more = false; tmy = add(tmy, tdy); }
+        else           { bz += sz; if (bz == ez + sz) more = false; tmz = add(tmz, tdz); }
+      }
+      if (more) {  // the next block's bucket head and stamp are on their way while this one is handled
+        h = block_hash(bx, by, bz, p.K);
+        ent = ld_entry_cg(p.entries + h);
+        stamp = __ldcg(p.stamps + h);
+      }
+      const unsigned long long key = pack_block(cx, cy, cz);
+      if (sharded && !shard_stores(cx, cy, cz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) {
+        mark_space(p, cx, cy, cz);  // exists on another rank: the free-space filter is global
+      } else if (entry_block(cent) == key && cent.z != -1) {
+        if (cstamp != p.view_id) touch_entry(p, (int)ch);
+      } else {
+        resolve_slow(p, ch, cx, cy, cz, key);
       }
     }
   }
-  __syncthreads();
 
-  // ---- phase 2: one thread per distinct block --------------------------------------------------
-  for (int i = threadIdx.x; i < kSetSlots; i += 256) {
-    const unsigned long long key = s_set[i];
-    if (key == kEmptyKey) continue;
-    const int idx = resolve_block(p, key);
-    if (idx >= 0 && stamp_entry(p, idx)) s_list[atomicAdd(&s_count, 1)] = idx;
+  // ---- phase 3a: corner tests of this thread's share of the previous list (independent of phase 1) ----
+  const int n_prev = p.counters[c.prev_slot];
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+  constexpr int kMaxShare = 4;   // entries per thread held in registers across the wait; more go through the loop below
+  int share_e[kMaxShare];
+  bool share_keep[kMaxShare];
+  Mat34 M;
+  M.load(c.Tdw);
+  auto in_frustum = [&](const int4& e4) {
+    int ox, oy, oz;
+    entry_origin(e4, ox, oy, oz);
+    for (int k = 0; k < 8; ++k) {
+      const float X = mul(p.block_length, (float)(ox + ((k & 1) >> 0)));
+      const float Y = mul(p.block_length, (float)(oy + ((k & 2) >> 1)));
+      const float Z = mul(p.block_length, (float)(oz + ((k & 4) >> 2)));
+      const Vec3 Xd = xform1<F>(M, X, Y, Z);
+      if (Xd.z < 0) continue;
+      float uu, vv;
+      project<F>(p.proj, Xd, uu, vv);
+      if (uu >= 0 && uu <= (float)p.w && vv >= 0 && vv <= (float)p.h) return true;
+    }
+    return false;
+  };
+#pragma unroll
+  for (int k = 0; k < kMaxShare; ++k) {
+    const int i = gtid + k * gsize;
+    share_e[k] = -1;
+    share_keep[k] = false;
+    if (i < n_prev) {
+      share_e[k] = c.prev_list[i];
+      share_keep[k] = in_frustum(ld_entry(p.entries + share_e[k]));
+    }
+  }
+
+  // ---- phase 2: every CTA has finished its pixels ----------------------------------------------------
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(c.ticket, 1);
+    // (the launch is cooperative: all CTAs are resident; the bound only keeps a broken device from hanging,
+    // and is reported through the overflow status)
+    long long spins = 0;
+    while (*reinterpret_cast<volatile int*>(c.ticket) < (int)gridDim.x) {
+      __nanosleep(32);
+      if (++spins > (1ll << 24)) { atomicAdd(p.counters + VK_CNT_OVERFLOW, 1); break; }
+    }
+    __threadfence();
   }
   __syncthreads();
-  const int cnt = s_count;
-  if (cnt == 0) return;
-  if (threadIdx.x == 0) s_base = atomicAdd(p.counters + p.cnt_slot, cnt);
-  __syncthreads();
-  const int base = s_base;
-  for (int i = threadIdx.x; i < cnt; i += 256) p.visible_out[base + i] = s_list[i];
-}
 
-struct CarryParams {
-  const vkHashEntry* entries;
-  uint8_t* visibility;
-  const int32_t* stamps;
-  int32_t* counters;
-  int32_t* host_counters;
-  const int32_t* prev_list;
-  int32_t* visible_out;
-  int prev_slot, cnt_slot;
-  int w, h;
-  vkProjection proj;
-  float Tdw[12];
-  float block_length;
-  int view_id;
-  int* ticket;
-};
-
-// UpdateBlockVisibilityKernel (src/volume.cu:23-84) restricted to the entries that can
-// be VISIBILITY_UNKNOWN, i.e. the previous visible list.
-template <bool F>
-__global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
-  // The previous list, its entries and the frustum test do not depend on the allocation kernel
-  // that precedes this one in the chain: they are evaluated while that kernel drains; only the
-  // stamps (is the entry already on the new list?) need it to have completed.
-  pdl_trigger();
-  bool waited = false;
-  const int n_prev = p.counters[p.prev_slot];
-  const int lane = threadIdx.x & 31;
-  for (int base = blockIdx.x * blockDim.x; base < n_prev; base += gridDim.x * blockDim.x) {
-    const int i = base + threadIdx.x;
+  // ---- phase 3b: carry over / drop --------------------------------------------------------------------
+  auto carry = [&](int e, bool keep_if_untouched) {
     bool keep = false;
-    int e = -1;
-    int4 ent = make_int4(0, 0, 0, 0);
-    if (i < n_prev) {
-      e = p.prev_list[i];
-      ent = ld_entry(p.entries + e);
+    if (e >= 0 && __ldcg(p.stamps + e) != p.view_id) {
+      keep = keep_if_untouched;
+      c.visibility[e] = keep ? VK_VIS_UNKNOWN : VK_VIS_FALSE;
     }
-    if (!waited) { pdl_wait(); waited = true; }
-    if (i < n_prev) {
-      if (p.stamps[e] != p.view_id) {
-        int ox, oy, oz;
-        entry_origin(ent, ox, oy, oz);
-        Mat34 M;
-        M.load(p.Tdw);
-        for (int c = 0; c < 8; ++c) {
-          const float X = mul(p.block_length, (float)(ox + ((c & 1) >> 0)));
-          const float Y = mul(p.block_length, (float)(oy + ((c & 2) >> 1)));
-          const float Z = mul(p.block_length, (float)(oz + ((c & 4) >> 2)));
-          const Vec3 Xd = xform1<F>(M, X, Y, Z);
-          if (Xd.z < 0) continue;
-          float u, v;
-          project<F>(p.proj, Xd, u, v);
-          if (u >= 0 && u <= (float)p.w && v >= 0 && v <= (float)p.h) { keep = true; break; }
-        }
-        p.visibility[e] = keep ? VK_VIS_UNKNOWN : VK_VIS_FALSE;
-      }
-    }
-    // warp-aggregated append
     const unsigned m = __ballot_sync(0xffffffffu, keep);
     if (m) {
       int pos = 0;
@@ -470,24 +334,37 @@ __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
       pos = __shfl_sync(0xffffffffu, pos, 0);
       if (keep) p.visible_out[pos + __popc(m & ((1u << lane) - 1))] = e;
     }
+  };
+#pragma unroll
+  for (int k = 0; k < kMaxShare; ++k) carry(share_e[k], share_keep[k]);
+  for (int base = kMaxShare * gsize; base < n_prev; base += gsize) {   // very long lists only
+    const int i = base + gtid;
+    int e = -1;
+    bool keep = false;
+    if (i < n_prev) {
+      e = c.prev_list[i];
+      keep = in_frustum(ld_entry(p.entries + e));
+    }
+    carry(e, keep);
   }
-  if (!waited) pdl_wait();
-  // last CTA out: retire the previous list and mirror the counters to the host
+
+  // ---- last CTA out: retire the previous list, mirror the counters to the host ------------------------
   __shared__ bool last;
   __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) last = (atomicAdd(p.ticket, 1) == (int)gridDim.x - 1);
+  if (threadIdx.x == 0) last = (atomicAdd(c.ticket + 1, 1) == (int)gridDim.x - 1);
   __syncthreads();
   if (last) {
     __threadfence();
     if (threadIdx.x == 0) {
-      p.counters[p.prev_slot] = 0;
-      *p.ticket = 0;
+      p.counters[c.prev_slot] = 0;
+      c.ticket[0] = 0;
+      c.ticket[1] = 0;
     }
-    if (threadIdx.x < VK_CNT_COUNT && p.host_counters) {
+    if (threadIdx.x < VK_CNT_COUNT && c.host_counters) {
       int val = __ldcg(p.counters + threadIdx.x);
-      if (threadIdx.x == p.prev_slot) val = 0;
-      p.host_counters[threadIdx.x] = val;
+      if (threadIdx.x == c.prev_slot) val = 0;
+      c.host_counters[threadIdx.x] = val;
     }
   }
 }
@@ -687,40 +564,27 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
     a.push_count = v->shard->count;
     for (int r = 0; r < v->shard->count; ++r) a.push_entries[r] = v->shard->push_entries[r];
   }
-  dim3 grid((a.w + 31) / 32, (a.h + 7) / 8);
   const bool strict = (v->math_mode == VK_MATH_STRICT);
-  const int mode = g_tune[VK_TUNE_ALLOC_MODE].load();  // 1: tile kernel; 64/128/256: CTA size of the warp kernel
-  if (mode != 1) {
-    const int threads = (mode == 64 || mode == 128) ? mode : 256;  // measured on B200: no difference (31.7 us)
-    const int tiles = ((a.w + 7) / 8) * ((a.h + 3) / 4), wpc = threads / 32;
-    const dim3 wgrid((tiles + wpc - 1) / wpc);
-    if (strict) launch_chained(vk_alloc_kernel<false>, wgrid, dim3(threads), 0, s, a);
-    else launch_chained(vk_alloc_kernel<true>, wgrid, dim3(threads), 0, s, a);
-  } else {
-    if (strict) launch_chained(vk_alloc_tile_kernel<false>, grid, dim3(256), 0, s, a);
-    else launch_chained(vk_alloc_tile_kernel<true>, grid, dim3(256), 0, s, a);
-  }
-  VK_COUNT_LAUNCH();
-
   CarryParams c;
-  c.entries = v->entries;
   c.visibility = v->visibility;
-  c.stamps = v->stamps;
-  c.counters = v->counters;
   c.host_counters = v->host_counters;
   c.prev_list = v->visible[prev];
-  c.visible_out = v->visible[cur];
   c.prev_slot = VK_CNT_VISIBLE0 + prev;
-  c.cnt_slot = VK_CNT_VISIBLE0 + cur;
-  c.w = f->depth_w;
-  c.h = f->depth_h;
-  c.proj = f->depth_proj;
   rows34(f->depth_to_world.inv, c.Tdw);
-  c.block_length = a.block_length;
-  c.view_id = v->view_id;
   c.ticket = v->counters + VK_CNT_COUNT;
-  if (strict) launch_chained(vk_carry_kernel<false>, dim3(sm_count()), dim3(256), 0, s, c);
-  else launch_chained(vk_carry_kernel<true>, dim3(sm_count()), dim3(256), 0, s, c);
+  // persistent grid: exactly the CTAs that are resident together (phase 2 waits for all of them)
+  static int per_sm[2] = {0, 0};
+  if (per_sm[strict] == 0) {
+    int n = 0;
+    cudaError_t oe = strict ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vk_setview_kernel<false>, 256, 0)
+                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vk_setview_kernel<true>, 256, 0);
+    per_sm[strict] = (oe == cudaSuccess && n > 0) ? (n < 4 ? n : 4) : 1;
+  }
+  const int forced = g_tune[VK_TUNE_ALLOC_MODE].load();   // experiments: CTAs per SM (1..4)
+  const dim3 grid(sm_count() * ((forced >= 1 && forced <= per_sm[strict]) ? forced : per_sm[strict]));
+  const cudaError_t le = strict ? launch_cooperative(vk_setview_kernel<false>, grid, dim3(256), 0, s, a, c)
+                                : launch_cooperative(vk_setview_kernel<true>, grid, dim3(256), 0, s, a, c);
+  if (le != cudaSuccess) return (int)le;
   VK_COUNT_LAUNCH();
   v->visible_slot = cur;
   return (int)cudaGetLastError();

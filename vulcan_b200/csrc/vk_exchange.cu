@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(256) vk_push_bands_kernel(const Xchg x, int w,
   const size_t seg_off[3] = {row0, plane + 3 * row0, 4 * plane + 3 * row0};
   const size_t seg_n[3] = {rows, 3 * rows, 3 * rows};
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
-  for (int r = 0; r < x.count; ++r) {
+  for (int r = 0; r < x.count && (x.stages & 1); ++r) {
     if (r == x.rank) continue;
     float* dst = xchg_images(x.buf[r], x.parity, w, h);
     for (int sgm = 0; sgm < 3; ++sgm) {
@@ -162,7 +162,8 @@ __global__ void __launch_bounds__(256) vk_push_bands_kernel(const Xchg x, int w,
 }
 
 int exchange_push_bands(const Xchg& x, int w, int h, cudaStream_t s) {
-  launch_chained(vk_push_bands_kernel, dim3(sm_count() * 2), dim3(256), 0, s, x, w, h);
+  // (wait-only stage of ranks that share a GPU: one CTA, the peers have all announced by then)
+  launch_chained(vk_push_bands_kernel, dim3((x.stages & 1) ? sm_count() * 2 : 1), dim3(256), 0, s, x, w, h);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }

@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
         const uint4 q = stage[lane * 5 + c];
         w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
       }
+      const uint4 d_old = make_uint4(w[0], w[5], w[10], w[15]);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         float D = __uint_as_float(w[5 * k]);
@@ -283,8 +284,10 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
       n_updated += __popc(dirty & 0x84210u);
       // the thread's 4 distances are one aligned 16-byte piece of the block's distance mirror
       // (voxel index 4t): a warp writes 512 contiguous bytes
-      if (cur.dmask) {
-        const uint4 d4 = make_uint4(w[0], w[5], w[10], w[15]);
+      // - written only when a distance really changed: free-space voxels in front of the surface keep
+      // D = 1 under the running average, and those are half of the updates
+      const uint4 d4 = make_uint4(w[0], w[5], w[10], w[15]);
+      if (cur.dmask && ((d4.x ^ d_old.x) | (d4.y ^ d_old.y) | (d4.z ^ d_old.z) | (d4.w ^ d_old.w))) {
         reinterpret_cast<uint4*>(p.sdf + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = d4;
         for (int r = 0; r < p.push_count; ++r)   // posted stores over NVLink; read after the next handshake
           if (r != p.push_rank) reinterpret_cast<uint4*>(p.push_sdf[r] + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = d4;

@@ -16,7 +16,7 @@ extern std::atomic<int> g_default_math_mode;
 // Tuning knobs (vk_tune): launch shapes and batching thresholds, never results.
 enum { VK_TUNE_RAY_CTA_THREADS = 0, VK_TUNE_RAY_BATCH_LANES = 1, VK_TUNE_RAY_BATCH_WAIT = 2,
        VK_TUNE_INTEGRATE_CTAS_PER_SM = 3, VK_TUNE_ALLOC_MODE = 4, VK_TUNE_RAY_COOP_LANES = 5, VK_TUNE_DEBUG_X = 6, VK_TUNE_RAY_FREE_RUN = 7,
-       VK_TUNE_RAY_COOP_ROUNDS = 8, VK_TUNE_PDL = 9, VK_TUNE_RAY_SOA = 10, VK_TUNE_RAY_AHEAD_LANES = 11, VK_TUNE_COUNT = 16 };
+       VK_TUNE_RAY_COOP_ROUNDS = 8, VK_TUNE_PDL = 9, VK_TUNE_RAY_SOA = 10, VK_TUNE_RAY_AHEAD_LANES = 11, VK_TUNE_RAY_WARM_SDF = 12, VK_TUNE_COUNT = 16 };
 extern std::atomic<int> g_tune[VK_TUNE_COUNT];
 
 // rows 0..2 of a column-major 4x4 (vulcan::Matrix4f) as row-major 3x4
@@ -54,6 +54,35 @@ inline cudaError_t launch_chained(void (*kernel)(KArgs...), dim3 grid, dim3 bloc
   cfg.attrs = attr;
   cfg.numAttrs = g_tune[VK_TUNE_PDL].load() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+// Launch of a persistent kernel whose CTAs wait for one another (a grid-wide arrival counter): a
+// COOPERATIVE launch, which the runtime only starts when the whole grid can be resident at once, also
+// next to other work on the device.  Chained like launch_chained when the runtime accepts both
+// attributes together, plain cooperative otherwise.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_cooperative(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                      Args&&... args) {
+  static std::atomic<int> chain_ok{1};
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  if (chain_ok.load() && g_tune[VK_TUNE_PDL].load()) {
+    cfg.numAttrs = 2;
+    const cudaError_t err = cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+    if (err == cudaSuccess) return err;
+    cudaGetLastError();
+    chain_ok.store(0);   // this runtime does not combine the two: cooperative only from now on
+  }
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 }  // namespace vk
 

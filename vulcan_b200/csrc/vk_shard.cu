@@ -175,34 +175,65 @@ extern "C" int vk_shard_destroy(vkShard* s, vkVolume* v) {
   return 0;
 }
 
-extern "C" int vk_trace_sharded(vkVolume* v, const vkFrame* view, float min_depth, float max_depth, int gather,
-                                float** out_depth, float** out_color, float** out_normal, void* stream) {
-  if (!v || !view || !v->voxels || !v->shard || !out_depth || !out_color || !out_normal) return VK_E_INVALID;
+// stage: 0 = the whole view; 1, 2, 3 = its three parts for ranks that share a GPU (see the header)
+static int trace_sharded(vkVolume* v, const vkFrame* view, float min_depth, float max_depth, int gather, int stage,
+                         float** out_depth, float** out_color, float** out_normal, void* stream) {
+  if (!v || !view || !v->voxels || !v->shard || !out_depth || !out_color || !out_normal || stage < 0 || stage > 3)
+    return VK_E_INVALID;
   vkShard* s = v->shard;
   if (!s->connected || view->depth_w != s->width || view->depth_h != s->height) return VK_E_INVALID;
   cudaStream_t st = (cudaStream_t)stream;
-  s->epoch += 1;
+  if (stage <= 1) s->epoch += 1;
   Xchg x;
   x.count = s->count; x.rank = s->rank; x.epoch = s->epoch; x.parity = s->epoch & 1;
+  x.stages = 3;
   for (int r = 0; r < VK_MAX_SHARDS; ++r) x.buf[r] = s->exchange[r];
   void* mine = s->exchange[s->rank];
   float* depth = xchg_depth(mine, x.parity, s->width, s->height);
   float* color = xchg_color(mine, x.parity, s->width, s->height);
   float* normal = xchg_normal(mine, x.parity, s->width, s->height);
+  int rc = 0;
   // 1. ray bounds of the local visible blocks, combined over the ranks; row bands (also the barrier that
   //    orders every rank's replica stores before any rank's ray cast)
-  int rc = trace_sharded_bounds(v, view, min_depth, max_depth, x, st);
-  if (rc) return rc;
-  // 2. this rank's band: ray march (+2 rows either side) and normals, all reads local
-  rc = trace_sharded_band(v, view, x, depth, color, normal, st);
-  if (rc) return rc;
-  // 3. bands to the peers, handshake
-  if (gather) {   // (a single rank: nothing to store, the handshake is trivial)
+  if (stage == 0 || stage == 1) {
+    x.stages = (stage == 0) ? 3 : 1;
+    rc = trace_sharded_bounds(v, view, min_depth, max_depth, x, st);
+    if (rc) return rc;
+  }
+  if (stage == 0 || stage == 2) {
+    if (stage == 2) {
+      x.stages = 2;
+      rc = trace_sharded_bounds(v, view, min_depth, max_depth, x, st);
+      if (rc) return rc;
+    }
+    // 2. this rank's band: ray march (+2 rows either side) and normals, all reads local
+    rc = trace_sharded_band(v, view, x, depth, color, normal, st);
+    if (rc) return rc;
+    // 3. the band into the peers' images, handshake
+    if (gather) {   // (a single rank: nothing to store, the handshake is trivial)
+      x.stages = (stage == 0) ? 3 : 1;
+      rc = exchange_push_bands(x, s->width, s->height, st);
+      if (rc) return rc;
+    }
+  }
+  if (stage == 3 && gather) {
+    x.stages = 2;
     rc = exchange_push_bands(x, s->width, s->height, st);
     if (rc) return rc;
   }
   *out_depth = depth; *out_color = color; *out_normal = normal;
   return 0;
+}
+
+extern "C" int vk_trace_sharded(vkVolume* v, const vkFrame* view, float min_depth, float max_depth, int gather,
+                                float** out_depth, float** out_color, float** out_normal, void* stream) {
+  return trace_sharded(v, view, min_depth, max_depth, gather, 0, out_depth, out_color, out_normal, stream);
+}
+
+extern "C" int vk_trace_sharded_staged(vkVolume* v, const vkFrame* view, float min_depth, float max_depth, int gather,
+                                       int stage, float** out_depth, float** out_color, float** out_normal, void* stream) {
+  if (stage < 1 || stage > 3) return VK_E_INVALID;
+  return trace_sharded(v, view, min_depth, max_depth, gather, stage, out_depth, out_color, out_normal, stream);
 }
 
 extern "C" int vk_shard_band(const vkVolume* v, int* band_begin, int* band_end, void* stream) {

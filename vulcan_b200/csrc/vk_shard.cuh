@@ -49,6 +49,9 @@ __host__ __device__ inline float* xchg_normal(void* buf, int parity, int w, int 
 // kernel-parameter view of the ranks' buffers for one collective
 struct Xchg {
   int count, rank, epoch, parity;
+  int stages;   // bit 0: store + announce, bit 1: wait + consume.  3 = both in one kernel (one rank per GPU);
+                // ranks that SHARE a GPU run the two halves as separate launches, all announcements first
+                // (vk_trace_sharded_staged): kernels of one device must never wait for one another
   void* buf[VK_MAX_SHARDS];
 };
 
@@ -71,9 +74,11 @@ __device__ __forceinline__ void xchg_handshake(const Xchg& x, bool bands) {
   __threadfence_system();
   __syncthreads();
   const int t = threadIdx.x;
-  if (t < x.count && t != x.rank) {
+  if ((x.stages & 1) && t < x.count && t != x.rank) {
     int* theirs = (bands ? xchg_bands_flags(x.buf[t], x.parity) : xchg_bounds_flags(x.buf[t], x.parity)) + x.rank;
     st_release_sys(theirs, x.epoch);
+  }
+  if ((x.stages & 2) && t < x.count && t != x.rank) {
     const int* mine = (bands ? xchg_bands_flags(x.buf[x.rank], x.parity) : xchg_bounds_flags(x.buf[x.rank], x.parity)) + t;
     // a peer that never arrives (crashed process, mismatched call sequence) must not hang the GPU: after
     // ~2 s the wait is given up and counted; vk_shard_band / vk_shard_status report VK_E_TIMEOUT

@@ -70,6 +70,7 @@ struct BoundsParams {
   float* bounds;
   const uint32_t* warm;  // optional: table the ray marcher will gather from (vkVolume::space_bits)
   int warm_lines;        // its size in 128-byte lines
+  const float* warm_sdf; // optional: vkVolume::sdf - the distance tiles of the visible blocks are pulled into L2
   bool negate_hi;        // cells hold (min, -max): an element-wise MIN over ranks combines both
   // sharded volume (vk_trace_sharded): the last CTA combines the grid with the other ranks' grids over
   // peer memory and splits the image rows into bands; has_x = 0 otherwise
@@ -120,6 +121,59 @@ __device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw,
   return b;
 }
 
+// Ray bounds of a sharded volume (one CTA; vk_trace_sharded).  Stage bit 0: this rank's grid goes into its
+// slot of every peer's buffer (posted stores over NVLink) and is announced.  Stage bit 1: wait for the peers'
+// announcements, leave the element-wise minimum in place (cells are (min, -max)) and split the image rows into
+// bands of equal active-cell counts.  The handshake is also the barrier that orders everything a rank stored
+// into its peers' replicas before this kernel - its allocation and integration of the frame - before any
+// rank's ray cast.
+__device__ __forceinline__ void bounds_exchange(const BoundsParams& p, float* s_cells) {
+  const int ncell = p.bw * p.bh, nf = 2 * ncell;
+  if (p.x.stages & 1)
+    for (int r = 0; r < p.x.count; ++r) {
+      if (r == p.x.rank) continue;
+      float* slot = xchg_bounds_slot(p.x.buf[r], p.x.parity, p.x.rank);
+      for (int i = threadIdx.x; i < nf; i += blockDim.x) slot[i] = __ldcg(p.bounds + i);
+    }
+  xchg_handshake(p.x, false);
+  if (!(p.x.stages & 2)) return;
+  // the same grid on every rank
+  for (int i = threadIdx.x; i < nf; i += blockDim.x) {
+    float m = __ldcg(p.bounds + i);
+    for (int r = 0; r < p.x.count; ++r)
+      if (r != p.x.rank) m = fminf(m, __ldcg(xchg_bounds_slot(p.x.buf[p.x.rank], p.x.parity, r) + i));
+    p.bounds[i] = m;
+    s_cells[i] = m;
+  }
+  __syncthreads();
+  // row bands with equal numbers of active cells (cells some ray has to march): the same split on every
+  // rank, computed from the same grid; rank r renders pixel rows [bands[r], bands[r + 1])
+  int* row_active = reinterpret_cast<int*>(s_cells + nf);
+  if (threadIdx.x < p.bh) {
+    int cnt = 0;
+    for (int cx = 0; cx < p.bw; ++cx) {
+      const float lo = s_cells[2 * (threadIdx.x * p.bw + cx)], nhi = s_cells[2 * (threadIdx.x * p.bw + cx) + 1];
+      cnt += (lo < -nhi) ? 1 : 0;
+    }
+    row_active[threadIdx.x] = cnt;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int* bands = xchg_bands(p.x.buf[p.x.rank], p.x.parity);
+    long long total = 0;
+    for (int r = 0; r < p.bh; ++r) total += row_active[r];
+    long long acc = 0;
+    int k = 1;
+    bands[0] = 0;
+    for (int r = 0; r < p.bh && k < p.x.count; ++r) {
+      acc += row_active[r];
+      // first pixel row of bounds row r + 1 (a pixel row y lies in bounds row bh * y / image_rows)
+      while (k < p.x.count && acc * p.x.count >= total * k) bands[k++] = ((r + 1) * p.image_rows + p.bh - 1) / p.bh;
+    }
+    while (k <= p.x.count) bands[k++] = p.image_rows;
+  }
+}
+
 // K13 + K10 + K11 fused: the union of a block's patches is the cell rectangle
 // [bmin, min(bmax, bmin + 16*g - 1)] (src/tracer.cu:67-86).  The global grid must hold
 // (+FLT_MAX, -FLT_MAX) on entry (vk_reset_bounds).  Each CTA accumulates into a private copy
@@ -152,6 +206,14 @@ __global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
   for (int i = begin + threadIdx.x; i < end; i += blockDim.x) {
     const int e = __ldg(p.visible + i);
     const int4 ent = ld_entry(p.entries + e);
+    // The ray marcher samples the distances of these very blocks through chains of dependent loads; its
+    // longest rays set the duration of the whole trace.  Their 2 KB distance tiles go to L2 now (16 lines
+    // per block, ~30 MB per view, nobody waits for them): a sample then costs an L2 hit, not a DRAM miss.
+    if (p.warm_sdf && ent.z >= 0) {
+      const float* tile = p.warm_sdf + (size_t)ent.z * VK_BLOCK_VOXELS;
+#pragma unroll
+      for (int l = 0; l < VK_BLOCK_VOXELS / 32; ++l) asm volatile("prefetch.global.L2 [%0];" ::"l"(tile + 32 * l));
+    }
     const BlockBox b = block_box<F>(ent, Tcw, p);
     if (b.gx * b.gy == 0) continue;
     const int x1 = min(b.bmaxx, b.bminx + 16 * b.gx - 1);
@@ -182,51 +244,16 @@ __global__ void __launch_bounds__(512) vk_bounds_kernel(const BoundsParams p) {
   if (!last) return;
   if (threadIdx.x == 0) *xchg_ticket(p.x.buf[p.x.rank]) = 0;
   __threadfence();
-  const int nf = 2 * ncell;
-  // 1. the grid into this rank's slot of every peer's buffer (posted stores over NVLink), then the
-  //    handshake: every rank's grid - and everything the rank stored into its peers' replicas before this
-  //    kernel, i.e. its allocation and integration of this frame - is complete when it returns
-  for (int r = 0; r < p.x.count; ++r) {
-    if (r == p.x.rank) continue;
-    float* slot = xchg_bounds_slot(p.x.buf[r], p.x.parity, p.x.rank);
-    for (int i = threadIdx.x; i < nf; i += blockDim.x) slot[i] = __ldcg(p.bounds + i);
-  }
-  xchg_handshake(p.x, false);
-  // 2. element-wise minimum (cells are (min, -max)) - the same grid on every rank
-  for (int i = threadIdx.x; i < nf; i += blockDim.x) {
-    float m = __ldcg(p.bounds + i);
-    for (int r = 0; r < p.x.count; ++r)
-      if (r != p.x.rank) m = fminf(m, __ldcg(xchg_bounds_slot(p.x.buf[p.x.rank], p.x.parity, r) + i));
-    p.bounds[i] = m;
-    s_cells[i] = m;
-  }
-  __syncthreads();
-  // 3. row bands with equal numbers of active cells (cells some ray has to march): the same split on every
-  //    rank, computed from the same grid; rank r renders pixel rows [bands[r], bands[r + 1])
-  int* row_active = reinterpret_cast<int*>(s_cells + nf);
-  if (threadIdx.x < p.bh) {
-    int cnt = 0;
-    for (int cx = 0; cx < p.bw; ++cx) {
-      const float lo = s_cells[2 * (threadIdx.x * p.bw + cx)], nhi = s_cells[2 * (threadIdx.x * p.bw + cx) + 1];
-      cnt += (lo < -nhi) ? 1 : 0;
-    }
-    row_active[threadIdx.x] = cnt;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int* bands = xchg_bands(p.x.buf[p.x.rank], p.x.parity);
-    long long total = 0;
-    for (int r = 0; r < p.bh; ++r) total += row_active[r];
-    long long acc = 0;
-    int k = 1;
-    bands[0] = 0;
-    for (int r = 0; r < p.bh && k < p.x.count; ++r) {
-      acc += row_active[r];
-      // first pixel row of bounds row r + 1 (a pixel row y lies in bounds row bh * y / image_rows)
-      while (k < p.x.count && acc * p.x.count >= total * k) bands[k++] = ((r + 1) * p.image_rows + p.bh - 1) / p.bh;
-    }
-    while (k <= p.x.count) bands[k++] = p.image_rows;
-  }
+  bounds_exchange(p, s_cells);
+}
+
+// The second half of bounds_exchange as a launch of its own (one CTA), for ranks that share a GPU
+// (vk_trace_sharded_staged): by then every rank's first half has run, so nothing waits.
+__global__ void __launch_bounds__(512) vk_bounds_merge_kernel(const BoundsParams p) {
+  pdl_wait();
+  pdl_trigger();
+  extern __shared__ float s_cells[];
+  bounds_exchange(p, s_cells);
 }
 
 __global__ void vk_reset_bounds_kernel(float2* bounds, int count, float hi_init) {
@@ -1135,6 +1162,7 @@ static void fill_bounds_params(BoundsParams& b, const float* Tcw_colmajor, const
   b.bounds = bounds;
   b.visible = nullptr; b.count = nullptr; b.entries = nullptr;
   b.warm = nullptr; b.warm_lines = 0;
+  b.warm_sdf = nullptr;
   b.negate_hi = false;
   b.has_x = 0; b.image_rows = image_h;
   memset(&b.x, 0, sizeof(b.x));
@@ -1327,6 +1355,7 @@ static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth,
   b.entries = v->entries;
   b.warm = v->space_bits;
   b.warm_lines = VK_SPACE_WORDS / 32;
+  b.warm_sdf = g_tune[VK_TUNE_RAY_WARM_SDF].load() ? v->sdf : nullptr;
   b.negate_hi = negate_hi;
   if (x) { b.has_x = 1; b.x = *x; }
   const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float) + 64 * sizeof(int);
@@ -1444,7 +1473,18 @@ namespace vk {
 int trace_sharded_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, const Xchg& x,
                          cudaStream_t s) {
   // the working grid lives in this rank's exchange buffer, cells as (min depth, -max depth)
-  return trace_bounds(v, view, min_depth, max_depth, xchg_grid(x.buf[x.rank]), s, true, &x);
+  if (x.stages & 1) return trace_bounds(v, view, min_depth, max_depth, xchg_grid(x.buf[x.rank]), s, true, &x);
+  // second half only (the first half ran in an earlier launch)
+  BoundsParams b;
+  fill_bounds_params(b, view->depth_to_world.inv, &view->depth_proj, VK_BLOCK_RES * v->voxel_length, min_depth, max_depth,
+                     view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, xchg_grid(x.buf[x.rank]), s);
+  b.negate_hi = true;
+  b.has_x = 1;
+  b.x = x;
+  const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float) + 64 * sizeof(int);
+  launch_chained(vk_bounds_merge_kernel, dim3(1), dim3(512), smem, s, b);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
 }
 
 int trace_sharded_band(const vkVolume* v, const vkFrame* view, const Xchg& x, float* depth, float* color, float* normal,

@@ -158,6 +158,23 @@ class Shard:
         vp = (C.POINTER(_lib.vkVolume) * n)(*[C.pointer(s.volume._v) for s in shards])
         api.check(_lib.lib.vk_shard_connect_local(sp, vp, n), "vk_shard_connect_local")
 
+    def TraceStage(self, frame, stage, gather=True):
+        """One of the three parts of Trace (vk_trace_sharded_staged) for ranks that share a GPU: every rank
+        runs part 1, then every rank part 2, then every rank part 3."""
+        import ctypes as C
+        from . import _lib, api
+        if stage == 1:
+            self.volume.SyncDistances()
+        f = self._pose_only(frame)
+        d, c, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        api.check(_lib.lib.vk_trace_sharded_staged(C.byref(self.volume._v), C.byref(f), self.depth_range_[0],
+                                                   self.depth_range_[1], int(bool(gather)), int(stage), C.byref(d),
+                                                   C.byref(c), C.byref(n), api._stream()), "vk_trace_sharded_staged")
+        h, w = self.height, self.width
+        frame.depth_image = api.device_view(d.value, (h, w), "<f4")
+        frame.color_image = api.device_view(c.value, (h, w, 3), "<f4")
+        frame.normal_image = api.device_view(n.value, (h, w, 3), "<f4")
+
     def Trace(self, frame, gather=True):
         """Tracer::Trace of the sharded volume (collective).  frame's images become views of this rank's
         output buffer (valid until the second-next Trace); with gather=False only this rank's band of rows
