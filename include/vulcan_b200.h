@@ -116,6 +116,7 @@ typedef struct vkVolume {
   int32_t*     visible[2];    /* [M+E] each; visible[visible_slot] is current       */
   int32_t*     stamps;        /* [M+E] id of the last SetView that touched an entry */
   int32_t*     locks;         /* [M]   per-bucket insertion locks                   */
+  uint64_t*    lock_tags;     /* [M]   block the bucket's inserter works on (lets rays of the same block move on) */
   uint32_t*    bucket_bits;   /* [ceil(M/32)] bit h set <=> bucket head h allocated */
   uint32_t*    space_bits;    /* [VK_SPACE_WORDS] bit of (x,y,z) mod 128 set <=> some block with    */
                               /* those low coordinate bits is allocated (free-space filter)       */

@@ -53,7 +53,8 @@ def _ref_extras(rep):
     runs of the reference itself) - never more than a handful."""
     extras = rep["alloc_only_b"] + rep["alloc_dup_b"]
     assert rep["alloc_only_a"] == 0 and rep["alloc_dup_a"] == 0, rep
-    assert extras <= max(6, rep["alloc_counts"][0] // 500), rep
+    # (a handful per run; more at coarse voxels, where more rays race on a bucket: at most 0.5 % of the blocks)
+    assert extras <= max(16, rep["alloc_counts"][0] // 200), rep
     assert rep["visible_only_a"] == 0 and rep["visible_only_b_known"] == 0, rep
     return extras
 

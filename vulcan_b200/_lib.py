@@ -36,7 +36,7 @@ class vkVolume(C.Structure):
     _fields_ = [
         ("voxels", C.c_void_p), ("entries", C.c_void_p), ("free_list", C.c_void_p),
         ("visibility", C.c_void_p), ("visible", C.c_void_p * 2), ("stamps", C.c_void_p),
-        ("locks", C.c_void_p), ("bucket_bits", C.c_void_p), ("space_bits", C.c_void_p), ("sdf", C.c_void_p),
+        ("locks", C.c_void_p), ("lock_tags", C.c_void_p), ("bucket_bits", C.c_void_p), ("space_bits", C.c_void_p), ("sdf", C.c_void_p),
         ("counters", C.c_void_p), ("host_counters", C.POINTER(C.c_int32)),
         ("main_blocks", C.c_int32), ("excess_blocks", C.c_int32),
         ("voxel_length", C.c_float), ("trunc_length", C.c_float),

@@ -4,8 +4,21 @@
 // + per-pixel request kernel (one surviving request per bucket per pass, racy)
 // + per-bucket handler + a 20-barrier scan over all B entries + two blocking
 // symbol memcpys, and the caller has to repeat the whole thing until allocation
-// converges.  Here one call reaches that fixed point with ONE launch and no host
-// synchronisation (vk_setview_kernel below).
+// converges.  Here one call reaches that fixed point with two launches (the second overlaps the
+// tail of the first through programmatic dependent launch) and no host synchronisation:
+//
+//   vk_alloc_kernel    one warp per 8x4 pixel tile walks the truncation band of its
+//                      32 rays in lock step; identical block coordinates inside the
+//                      warp are merged with __match_any_sync so one lane per distinct
+//                      block does a find-or-insert in the hash (per-bucket lock only
+//                      on the insert path).  The first lane to touch an entry in
+//                      this view (atomicExch on a per-entry view stamp) marks it
+//                      VISIBILITY_TRUE and appends it to the new visible list.
+//   vk_carry_kernel    walks the *previous* visible list only (the UNKNOWN entries of
+//                      the reference are exactly that list): entries not touched in
+//                      this view get the 8-corner frustum test (Q6) and are carried
+//                      over (stay UNKNOWN, Q5) or dropped (FALSE).  O(V) instead of
+//                      O(M+E).
 #include "vk_math.cuh"
 #include "vk_launch.h"
 
@@ -16,6 +29,7 @@ struct AllocParams {
   uint8_t* visibility;
   int32_t* stamps;
   int32_t* locks;
+  unsigned long long* lock_tags;   // per bucket: block (and view) its last / current inserter works on
   uint32_t* bucket_bits;
   uint32_t* space_bits;
   const int32_t* free_list;
@@ -53,6 +67,17 @@ __device__ __forceinline__ int find_block(const vkHashEntry* entries, uint32_t h
   }
 }
 
+__device__ __forceinline__ void touch_entry(const AllocParams& p, int idx) {
+  if (__ldcg(p.stamps + idx) != p.view_id) {
+    const int old = atomicExch(p.stamps + idx, p.view_id);
+    if (old != p.view_id) {
+      p.visibility[idx] = VK_VIS_TRUE;
+      const int pos = atomicAdd(p.counters + p.cnt_slot, 1);
+      p.visible_out[pos] = idx;
+    }
+  }
+}
+
 // Sharded volumes: every rank walks every ray, so every rank sees every block of the scene; blocks
 // it does not store still go into its occupancy filter, which therefore equals the filter of the
 // unsharded volume on all ranks (the ray marcher relies on "bit clear => no such block anywhere").
@@ -66,8 +91,13 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
                                          unsigned long long key) {
   int result = -1;
   bool done = false;
+  // what this lane is about to insert, readable by the lanes it keeps out: a ray that finds the bucket
+  // locked by an inserter of ITS block (in this view) has nothing left to do - the inserter also marks the
+  // block visible - instead of spinning until the lock is free
+  const unsigned long long tag = key | ((unsigned long long)(p.view_id & 0xffff) << 48);
   while (!done) {
     if (atomicCAS(p.locks + h, 0, 1) == 0) {
+      __stcg(p.lock_tags + h, tag);
       __threadfence();
       int tail;
       bool head_empty;
@@ -123,6 +153,7 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
       done = true;
     } else {
       // another lane is inserting into this bucket: it may be inserting our block
+      if (__ldcg(p.lock_tags + h) == tag) { result = -2; done = true; continue; }
       int tail;
       bool head_empty;
       const int idx = find_block(p.entries, h, key, tail, head_empty);
@@ -132,201 +163,164 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
   return result;
 }
 
-// One launch per SetView.  CreateAllocationRequestsKernel (src/volume.cu:86-301) +
-// HandleAllocationRequestsKernel (src/volume.cu:303-368) to their common fixed point, then
-// UpdateBlockVisibilityKernel (src/volume.cu:23-84) restricted to the entries that can be
-// VISIBILITY_UNKNOWN, i.e. the previous visible list.
-//
-// A persistent grid (every CTA resident) in three phases:
-//   1. pixels.  A thread walks the truncation band of one depth pixel with the reference's
-//      Amanatides-Woo comparison tree.  A block costs two independent loads - its bucket head and that
-//      head's view stamp, issued one DDA step AHEAD of their use - and in the steady state (block at the
-//      head of its bucket, already stamped by a neighbouring ray) nothing else: no warp-wide matching, no
-//      atomics.  Lanes of a warp that ask for the same block load the same addresses (one transaction).
-//      Only the first ray to touch an entry in this view appends it (atomicExch on the stamp;
-//      warp-aggregated append), and only chain walks and inserts take the slow path.
-//   2. a grid-wide arrival counter (all CTAs are resident by construction: the grid is sized from the
-//      occupancy of this kernel): every entry touched by a ray is now stamped.
-//   3. the previous visible list: entries not stamped in this view get the 8-corner frustum test (Q6)
-//      and are carried over (stay UNKNOWN, Q5) or dropped (FALSE).  The corner tests themselves do not
-//      depend on phase 1 and run BEFORE the counter wait.  The last CTA mirrors the counters to the host.
+// CreateAllocationRequestsKernel (src/volume.cu:86-301) + HandleAllocationRequestsKernel
+// (src/volume.cu:303-368) to their common fixed point.
 // FMA map (reference release SASS of CreateAllocationRequestsKernel):
 //   dir   = Twd * (unproj, 0)      FMUL y*m1; FFMA x*m0 + .; FADD m2 (z == 1); FFMA 0*m3 + .
 //   X     = origin + depth * dir   FFMA dir*depth + origin
 //   begin = X - trunc * dir        FFMA -dir*trunc + X     end = FFMA dir*trunc + X
 //   tmax  = (L*(b + max(0,step)) - begin) / dir     FFMA bf*L - begin ; IEEE div
-struct CarryParams {
-  uint8_t* visibility;
-  int32_t* host_counters;
-  const int32_t* prev_list;
-  int prev_slot;
-  float Tdw[12];
-  int* ticket;   // [0] phase counter, [1] exit counter
-};
-
-// first toucher of an entry in this view: marks it visible and appends it.  The append is aggregated over
-// the lanes that arrive here together (one atomic per group).
-__device__ __forceinline__ void touch_entry(const AllocParams& p, int idx) {
-  const int old = atomicExch(p.stamps + idx, p.view_id);
-  const bool first = (old != p.view_id);
-  if (first) p.visibility[idx] = VK_VIS_TRUE;
-  const unsigned group = __activemask();
-  const unsigned firsts = __ballot_sync(group, first);
-  if (firsts == 0) return;
-  const int lane = threadIdx.x & 31;
-  const int leader = __ffs(firsts) - 1;
-  int base = 0;
-  if (lane == leader) base = atomicAdd(p.counters + p.cnt_slot, __popc(firsts));
-  base = __shfl_sync(group, base, leader);
-  if (first) p.visible_out[base + __popc(firsts & ((1u << lane) - 1))] = idx;
-}
-
-// everything that is not "block found at the head of its bucket": chain walk, insert, or a block that
-// another rank owns
-__device__ __noinline__ void resolve_slow(const AllocParams& p, uint32_t h, int bx, int by, int bz, unsigned long long key) {
-  int tail;
-  bool head_empty;
-  int idx = find_block(p.entries, h, key, tail, head_empty);
-  if (idx < 0) idx = insert_block(p, h, bx, by, bz, key);
-  if (idx >= 0 && __ldcg(p.stamps + idx) != p.view_id) touch_entry(p, idx);
-}
-
 template <bool F>
-__global__ void __launch_bounds__(256, 4) vk_setview_kernel(const AllocParams p, const CarryParams c) {
+__global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
   pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
   pdl_trigger();  // the next one may be scheduled as this grid drains
   const int lane = threadIdx.x & 31;
-  const int tiles_x = (p.w + 7) >> 3, tiles = tiles_x * ((p.h + 3) >> 2);
-  const int warps = gridDim.x * (blockDim.x >> 5);
-  Mat34 Twd;
-  Twd.load(p.Twd);
-  Unprojector un;
-  un.init(p.proj);
-  const bool sharded = p.shard_count > 1;
+  // warp tile 8x4 pixels; the warps of the grid take the tiles row by row (the kernel has no
+  // CTA-level state, so the CTA size only sets the granularity of the waves)
+  const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int tiles_x = (p.w + 7) >> 3;
+  const int x = (tile % tiles_x) * 8 + (lane & 7);
+  const int y = (tile / tiles_x) * 4 + (lane >> 3);
 
-  // ---- phase 1: warp tiles of 8x4 pixels, taken grid-stride ---------------------------------------
-  for (int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); tile < tiles; tile += warps) {
-    const int x = (tile % tiles_x) * 8 + (lane & 7);
-    const int y = (tile / tiles_x) * 4 + (lane >> 3);
-    if (x >= p.w || y >= p.h) continue;
+  bool active = (x < p.w && y < p.h);
+  int bx = 0, by = 0, bz = 0, ex = 0, ey = 0, ez = 0, sx = 1, sy = 1, sz = 1;
+  float tmx = 0, tmy = 0, tmz = 0, tdx = 0, tdy = 0, tdz = 0;
+
+  if (active) {
     const float depth = __ldg(p.depth + y * p.w + x);
-    if (depth < p.min_depth || depth > p.max_depth) continue;
-    const float u = add((float)x, 0.5f), v = add((float)y, 0.5f);
-    const float d0x = un.x<F>(u), d0y = un.y<F>(v);
-    Vec3 dir = xform0<F>(Twd, d0x, d0y, 1.0f);
-    const float Xx = FP<F>::mad(dir.x, depth, p.Twd[3]);
-    const float Xy = FP<F>::mad(dir.y, depth, p.Twd[7]);
-    const float Xz = FP<F>::mad(dir.z, depth, p.Twd[11]);
-    dir = normalized<F>(dir);
-    const float bgx = FP<F>::nmad(dir.x, p.trunc, Xx), bgy = FP<F>::nmad(dir.y, p.trunc, Xy),
-                bgz = FP<F>::nmad(dir.z, p.trunc, Xz);
-    const float enx = FP<F>::mad(dir.x, p.trunc, Xx), eny = FP<F>::mad(dir.y, p.trunc, Xy),
-                enz = FP<F>::mad(dir.z, p.trunc, Xz);
-    const int sx = (dir.x < 0) ? -1 : 1, sy = (dir.y < 0) ? -1 : 1, sz = (dir.z < 0) ? -1 : 1;
-    const float inv = p.inv_block_length;
-    int bx = (int)floorf(mul(bgx, inv)), by = (int)floorf(mul(bgy, inv)), bz = (int)floorf(mul(bgz, inv));
-    const int ex = (int)floorf(mul(enx, inv)), ey = (int)floorf(mul(eny, inv)), ez = (int)floorf(mul(enz, inv));
-    float tmx = fdiv(FP<F>::msub((float)(bx + max(0, sx)), p.block_length, bgx), dir.x);
-    float tmy = fdiv(FP<F>::msub((float)(by + max(0, sy)), p.block_length, bgy), dir.y);
-    float tmz = fdiv(FP<F>::msub((float)(bz + max(0, sz)), p.block_length, bgz), dir.z);
-    if (dir.x == 0) tmx = 1E20f;
-    if (dir.y == 0) tmy = 1E20f;
-    if (dir.z == 0) tmz = 1E20f;
-    const float tdx = fdiv(mul((float)sx, p.block_length), dir.x);
-    const float tdy = fdiv(mul((float)sy, p.block_length), dir.y);
-    const float tdz = fdiv(mul((float)sz, p.block_length), dir.z);
+    if (depth < p.min_depth || depth > p.max_depth) active = false;
+    if (active) {
+      const float u = add((float)x, 0.5f), v = add((float)y, 0.5f);
+      Unprojector un;
+      un.init(p.proj);
+      const float d0x = un.x<F>(u), d0y = un.y<F>(v);
+      Mat34 Twd;
+      Twd.load(p.Twd);
+      Vec3 dir = xform0<F>(Twd, d0x, d0y, 1.0f);
+      const float Xx = FP<F>::mad(dir.x, depth, p.Twd[3]);
+      const float Xy = FP<F>::mad(dir.y, depth, p.Twd[7]);
+      const float Xz = FP<F>::mad(dir.z, depth, p.Twd[11]);
+      dir = normalized<F>(dir);
+      const float bgx = FP<F>::nmad(dir.x, p.trunc, Xx), bgy = FP<F>::nmad(dir.y, p.trunc, Xy),
+                  bgz = FP<F>::nmad(dir.z, p.trunc, Xz);
+      const float enx = FP<F>::mad(dir.x, p.trunc, Xx), eny = FP<F>::mad(dir.y, p.trunc, Xy),
+                  enz = FP<F>::mad(dir.z, p.trunc, Xz);
+      sx = (dir.x < 0) ? -1 : 1;
+      sy = (dir.y < 0) ? -1 : 1;
+      sz = (dir.z < 0) ? -1 : 1;
+      const float inv = p.inv_block_length;
+      bx = (int)floorf(mul(bgx, inv));
+      by = (int)floorf(mul(bgy, inv));
+      bz = (int)floorf(mul(bgz, inv));
+      ex = (int)floorf(mul(enx, inv));
+      ey = (int)floorf(mul(eny, inv));
+      ez = (int)floorf(mul(enz, inv));
+      const float ox = FP<F>::msub((float)(bx + max(0, sx)), p.block_length, bgx);
+      const float oy = FP<F>::msub((float)(by + max(0, sy)), p.block_length, bgy);
+      const float oz = FP<F>::msub((float)(bz + max(0, sz)), p.block_length, bgz);
+      tmx = fdiv(ox, dir.x);
+      tmy = fdiv(oy, dir.y);
+      tmz = fdiv(oz, dir.z);
+      if (dir.x == 0) tmx = 1E20f;
+      if (dir.y == 0) tmy = 1E20f;
+      if (dir.z == 0) tmz = 1E20f;
+      tdx = fdiv(mul((float)sx, p.block_length), dir.x);
+      tdy = fdiv(mul((float)sy, p.block_length), dir.y);
+      tdz = fdiv(mul((float)sz, p.block_length), dir.z);
+    }
+  }
 
-    // lookup of the current block: issued here, used one DDA step later
-    uint32_t h = block_hash(bx, by, bz, p.K);
-    int4 ent = ld_entry_cg(p.entries + h);
-    int stamp = __ldcg(p.stamps + h);
-    bool more = true;
-    while (more) {
-      const int cx = bx, cy = by, cz = bz;
-      const uint32_t ch = h;
-      const int4 cent = ent;
-      const int cstamp = stamp;
+  unsigned long long last_key = ~0ull;  // block this lane handled last as leader
+  while (__any_sync(0xffffffffu, active)) {
+    const unsigned long long key = active ? pack_block(bx, by, bz) : ~0ull;
+    const unsigned peers = __match_any_sync(0xffffffffu, key);
+    const bool leader = active && (lane == (__ffs(peers) - 1)) && key != last_key;
+    if (leader) {
+      last_key = key;
+      const uint32_t h = block_hash(bx, by, bz, p.K);
+      // most blocks sit at the head of their bucket, whose index is known before the entry
+      // arrives: its stamp is fetched together with the entry instead of after it
+      const int head_stamp = __ldcg(p.stamps + h);
+      int tail;
+      bool head_empty;
+      int idx = find_block(p.entries, h, key, tail, head_empty);
+      if (idx < 0) {
+        if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) idx = insert_block(p, h, bx, by, bz, key);
+        else mark_space(p, bx, by, bz);  // exists on another rank: the filter is global
+      }
+      if (idx >= 0 && !(idx == (int)h && head_stamp == p.view_id)) touch_entry(p, idx);
+    }
+    if (active) {
       // Amanatides-Woo step with the reference's comparison tree (src/volume.cu:241-295)
       if (tmx < tmy) {
-        if (tmx < tmz) { bx += sx; if (bx == ex + sx) more = false; tmx = add(tmx, tdx); }
-        else           { bz += sz; if (bz == ez + sz) more = false; tmz = add(tmz, tdz); }
+        if (tmx < tmz) { bx += sx; if (bx == ex + sx) active = false; tmx = add(tmx, tdx); }
+        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
       } else {
-        if (tmy < tmz) { by += sy; if (by == ey + sy) more = false; tmy = add(tmy, tdy); }
-        else           { bz += sz; if (bz == ez + sz) more = false; tmz = add(tmz, tdz); }
-      }
-      if (more) {  // the next block's bucket head and stamp are on their way while this one is handled
-        h = block_hash(bx, by, bz, p.K);
-        ent = ld_entry_cg(p.entries + h);
-        stamp = __ldcg(p.stamps + h);
-      }
-      const unsigned long long key = pack_block(cx, cy, cz);
-      if (sharded && !shard_stores(cx, cy, cz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) {
-        mark_space(p, cx, cy, cz);  // exists on another rank: the free-space filter is global
-      } else if (entry_block(cent) == key && cent.z != -1) {
-        if (cstamp != p.view_id) touch_entry(p, (int)ch);
-      } else {
-        resolve_slow(p, ch, cx, cy, cz, key);
+        if (tmy < tmz) { by += sy; if (by == ey + sy) active = false; tmy = add(tmy, tdy); }
+        else           { bz += sz; if (bz == ez + sz) active = false; tmz = add(tmz, tdz); }
       }
     }
   }
+}
 
-  // ---- phase 3a: corner tests of this thread's share of the previous list (independent of phase 1) ----
-  const int n_prev = p.counters[c.prev_slot];
-  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
-  constexpr int kMaxShare = 4;   // entries per thread held in registers across the wait; more go through the loop below
-  int share_e[kMaxShare];
-  bool share_keep[kMaxShare];
-  Mat34 M;
-  M.load(c.Tdw);
-  auto in_frustum = [&](const int4& e4) {
-    int ox, oy, oz;
-    entry_origin(e4, ox, oy, oz);
-    for (int k = 0; k < 8; ++k) {
-      const float X = mul(p.block_length, (float)(ox + ((k & 1) >> 0)));
-      const float Y = mul(p.block_length, (float)(oy + ((k & 2) >> 1)));
-      const float Z = mul(p.block_length, (float)(oz + ((k & 4) >> 2)));
-      const Vec3 Xd = xform1<F>(M, X, Y, Z);
-      if (Xd.z < 0) continue;
-      float uu, vv;
-      project<F>(p.proj, Xd, uu, vv);
-      if (uu >= 0 && uu <= (float)p.w && vv >= 0 && vv <= (float)p.h) return true;
-    }
-    return false;
-  };
-#pragma unroll
-  for (int k = 0; k < kMaxShare; ++k) {
-    const int i = gtid + k * gsize;
-    share_e[k] = -1;
-    share_keep[k] = false;
-    if (i < n_prev) {
-      share_e[k] = c.prev_list[i];
-      share_keep[k] = in_frustum(ld_entry(p.entries + share_e[k]));
-    }
-  }
+struct CarryParams {
+  const vkHashEntry* entries;
+  uint8_t* visibility;
+  const int32_t* stamps;
+  int32_t* counters;
+  int32_t* host_counters;
+  const int32_t* prev_list;
+  int32_t* visible_out;
+  int prev_slot, cnt_slot;
+  int w, h;
+  vkProjection proj;
+  float Tdw[12];
+  float block_length;
+  int view_id;
+  int* ticket;
+};
 
-  // ---- phase 2: every CTA has finished its pixels ----------------------------------------------------
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    atomicAdd(c.ticket, 1);
-    // (the launch is cooperative: all CTAs are resident; the bound only keeps a broken device from hanging,
-    // and is reported through the overflow status)
-    long long spins = 0;
-    while (*reinterpret_cast<volatile int*>(c.ticket) < (int)gridDim.x) {
-      __nanosleep(32);
-      if (++spins > (1ll << 24)) { atomicAdd(p.counters + VK_CNT_OVERFLOW, 1); break; }
-    }
-    __threadfence();
-  }
-  __syncthreads();
-
-  // ---- phase 3b: carry over / drop --------------------------------------------------------------------
-  auto carry = [&](int e, bool keep_if_untouched) {
+// UpdateBlockVisibilityKernel (src/volume.cu:23-84) restricted to the entries that can
+// be VISIBILITY_UNKNOWN, i.e. the previous visible list.
+template <bool F>
+__global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
+  // The previous list, its entries and the frustum test do not depend on the allocation kernel
+  // that precedes this one in the chain: they are evaluated while that kernel drains; only the
+  // stamps (is the entry already on the new list?) need it to have completed.
+  pdl_trigger();
+  bool waited = false;
+  const int n_prev = p.counters[p.prev_slot];
+  const int lane = threadIdx.x & 31;
+  for (int base = blockIdx.x * blockDim.x; base < n_prev; base += gridDim.x * blockDim.x) {
+    const int i = base + threadIdx.x;
     bool keep = false;
-    if (e >= 0 && __ldcg(p.stamps + e) != p.view_id) {
-      keep = keep_if_untouched;
-      c.visibility[e] = keep ? VK_VIS_UNKNOWN : VK_VIS_FALSE;
+    int e = -1;
+    int4 ent = make_int4(0, 0, 0, 0);
+    if (i < n_prev) {
+      e = p.prev_list[i];
+      ent = ld_entry(p.entries + e);
     }
+    if (!waited) { pdl_wait(); waited = true; }
+    if (i < n_prev) {
+      if (p.stamps[e] != p.view_id) {
+        int ox, oy, oz;
+        entry_origin(ent, ox, oy, oz);
+        Mat34 M;
+        M.load(p.Tdw);
+        for (int c = 0; c < 8; ++c) {
+          const float X = mul(p.block_length, (float)(ox + ((c & 1) >> 0)));
+          const float Y = mul(p.block_length, (float)(oy + ((c & 2) >> 1)));
+          const float Z = mul(p.block_length, (float)(oz + ((c & 4) >> 2)));
+          const Vec3 Xd = xform1<F>(M, X, Y, Z);
+          if (Xd.z < 0) continue;
+          float u, v;
+          project<F>(p.proj, Xd, u, v);
+          if (u >= 0 && u <= (float)p.w && v >= 0 && v <= (float)p.h) { keep = true; break; }
+        }
+        p.visibility[e] = keep ? VK_VIS_UNKNOWN : VK_VIS_FALSE;
+      }
+    }
+    // warp-aggregated append
     const unsigned m = __ballot_sync(0xffffffffu, keep);
     if (m) {
       int pos = 0;
@@ -334,37 +328,24 @@ __global__ void __launch_bounds__(256, 4) vk_setview_kernel(const AllocParams p,
       pos = __shfl_sync(0xffffffffu, pos, 0);
       if (keep) p.visible_out[pos + __popc(m & ((1u << lane) - 1))] = e;
     }
-  };
-#pragma unroll
-  for (int k = 0; k < kMaxShare; ++k) carry(share_e[k], share_keep[k]);
-  for (int base = kMaxShare * gsize; base < n_prev; base += gsize) {   // very long lists only
-    const int i = base + gtid;
-    int e = -1;
-    bool keep = false;
-    if (i < n_prev) {
-      e = c.prev_list[i];
-      keep = in_frustum(ld_entry(p.entries + e));
-    }
-    carry(e, keep);
   }
-
-  // ---- last CTA out: retire the previous list, mirror the counters to the host ------------------------
+  if (!waited) pdl_wait();
+  // last CTA out: retire the previous list and mirror the counters to the host
   __shared__ bool last;
   __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) last = (atomicAdd(c.ticket + 1, 1) == (int)gridDim.x - 1);
+  if (threadIdx.x == 0) last = (atomicAdd(p.ticket, 1) == (int)gridDim.x - 1);
   __syncthreads();
   if (last) {
     __threadfence();
     if (threadIdx.x == 0) {
-      p.counters[c.prev_slot] = 0;
-      c.ticket[0] = 0;
-      c.ticket[1] = 0;
+      p.counters[p.prev_slot] = 0;
+      *p.ticket = 0;
     }
-    if (threadIdx.x < VK_CNT_COUNT && c.host_counters) {
+    if (threadIdx.x < VK_CNT_COUNT && p.host_counters) {
       int val = __ldcg(p.counters + threadIdx.x);
-      if (threadIdx.x == c.prev_slot) val = 0;
-      c.host_counters[threadIdx.x] = val;
+      if (threadIdx.x == p.prev_slot) val = 0;
+      p.host_counters[threadIdx.x] = val;
     }
   }
 }
@@ -448,7 +429,9 @@ extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
                                                v->free_list, v->visibility, v->stamps, v->locks, v->counters, B,
                                                v->main_blocks);
   VK_COUNT_LAUNCH();
-  cudaError_t err = cudaMemsetAsync(v->bucket_bits, 0, ((size_t)v->main_blocks + 31) / 32 * sizeof(uint32_t), s);
+  cudaError_t err = cudaMemsetAsync(v->lock_tags, 0, (size_t)v->main_blocks * sizeof(unsigned long long), s);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaMemsetAsync(v->bucket_bits, 0, ((size_t)v->main_blocks + 31) / 32 * sizeof(uint32_t), s);
   if (err != cudaSuccess) return (int)err;
   err = cudaMemsetAsync(v->space_bits, 0, VK_SPACE_WORDS * sizeof(uint32_t), s);
   if (err != cudaSuccess) return (int)err;
@@ -492,6 +475,7 @@ extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks,
   VK_TRY(cudaMalloc((void**)&v->visible[1], B * sizeof(int32_t)));
   VK_TRY(cudaMalloc((void**)&v->stamps, B * sizeof(int32_t)));
   VK_TRY(cudaMalloc((void**)&v->locks, (size_t)main_blocks * sizeof(int32_t)));
+  VK_TRY(cudaMalloc((void**)&v->lock_tags, (size_t)main_blocks * sizeof(unsigned long long)));
   VK_TRY(cudaMalloc((void**)&v->bucket_bits, ((size_t)main_blocks + 31) / 32 * sizeof(uint32_t)));
   VK_TRY(cudaMalloc((void**)&v->space_bits, VK_SPACE_WORDS * sizeof(uint32_t)));
   VK_TRY(cudaMalloc((void**)&v->sdf, B * VK_BLOCK_VOXELS * sizeof(float)));
@@ -511,6 +495,7 @@ extern "C" int vk_volume_destroy(vkVolume* v) {
   cudaFree(v->visible[1]);
   cudaFree(v->stamps);
   cudaFree(v->locks);
+  cudaFree(v->lock_tags);
   cudaFree(v->bucket_bits);
   cudaFree(v->space_bits);
   cudaFree(v->sdf);
@@ -534,6 +519,7 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   a.visibility = v->visibility;
   a.stamps = v->stamps;
   a.locks = v->locks;
+  a.lock_tags = reinterpret_cast<unsigned long long*>(v->lock_tags);
   a.bucket_bits = v->bucket_bits;
   a.space_bits = v->space_bits;
   a.free_list = v->free_list;
@@ -565,26 +551,34 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
     for (int r = 0; r < v->shard->count; ++r) a.push_entries[r] = v->shard->push_entries[r];
   }
   const bool strict = (v->math_mode == VK_MATH_STRICT);
+  {
+    const int threads = 256;  // (64 / 128 / 256 measured the same on B200)
+    const int tiles = ((a.w + 7) / 8) * ((a.h + 3) / 4), wpc = threads / 32;
+    const dim3 wgrid((tiles + wpc - 1) / wpc);
+    if (strict) launch_chained(vk_alloc_kernel<false>, wgrid, dim3(threads), 0, s, a);
+    else launch_chained(vk_alloc_kernel<true>, wgrid, dim3(threads), 0, s, a);
+  }
+  VK_COUNT_LAUNCH();
+
   CarryParams c;
+  c.entries = v->entries;
   c.visibility = v->visibility;
+  c.stamps = v->stamps;
+  c.counters = v->counters;
   c.host_counters = v->host_counters;
   c.prev_list = v->visible[prev];
+  c.visible_out = v->visible[cur];
   c.prev_slot = VK_CNT_VISIBLE0 + prev;
+  c.cnt_slot = VK_CNT_VISIBLE0 + cur;
+  c.w = f->depth_w;
+  c.h = f->depth_h;
+  c.proj = f->depth_proj;
   rows34(f->depth_to_world.inv, c.Tdw);
+  c.block_length = a.block_length;
+  c.view_id = v->view_id;
   c.ticket = v->counters + VK_CNT_COUNT;
-  // persistent grid: exactly the CTAs that are resident together (phase 2 waits for all of them)
-  static int per_sm[2] = {0, 0};
-  if (per_sm[strict] == 0) {
-    int n = 0;
-    cudaError_t oe = strict ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vk_setview_kernel<false>, 256, 0)
-                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, vk_setview_kernel<true>, 256, 0);
-    per_sm[strict] = (oe == cudaSuccess && n > 0) ? (n < 4 ? n : 4) : 1;
-  }
-  const int forced = g_tune[VK_TUNE_ALLOC_MODE].load();   // experiments: CTAs per SM (1..4)
-  const dim3 grid(sm_count() * ((forced >= 1 && forced <= per_sm[strict]) ? forced : per_sm[strict]));
-  const cudaError_t le = strict ? launch_cooperative(vk_setview_kernel<false>, grid, dim3(256), 0, s, a, c)
-                                : launch_cooperative(vk_setview_kernel<true>, grid, dim3(256), 0, s, a, c);
-  if (le != cudaSuccess) return (int)le;
+  if (strict) launch_chained(vk_carry_kernel<false>, dim3(sm_count()), dim3(256), 0, s, c);
+  else launch_chained(vk_carry_kernel<true>, dim3(sm_count()), dim3(256), 0, s, c);
   VK_COUNT_LAUNCH();
   v->visible_slot = cur;
   return (int)cudaGetLastError();

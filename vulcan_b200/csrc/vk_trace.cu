@@ -558,7 +558,7 @@ __device__ __forceinline__ Vec3 interp_color(const TraceParams& p, const Taps& t
 
 namespace vk {
 
-constexpr int kFreeUnroll = 4;
+
 
 __device__ __forceinline__ bool space_bit(const TraceParams& p, int bx, int by, int bz) {
   uint32_t sw, sb;
