@@ -332,42 +332,43 @@ def run_ours(args, rank, world):
     host_submit = []
 
     def e2e_streamed():
-        """vulcan_b200.pipeline.FramePipeline: the same copies and kernels for every frame, the
-        copies of neighbouring frames overlapped with the kernels; the host takes frame k-1's
-        images (and reads a pixel of each) while frame k is in flight."""
-        from vulcan_b200.pipeline import FramePipeline
+        """vulcan::FramePipeline (include/vulcan/frame_pipeline.h, C++ host) through ONE C entry point,
+        vulcan_pipeline_run: the same copies and kernels for every frame, the copies of neighbouring frames
+        overlapped with the kernels; the host takes frame k-lag's images (and reads a pixel of each) after
+        submitting frame k; the call returns when every frame's images are in host memory."""
+        cxx = C.CDLL(os.path.join(ROOT, "vulcan_b200", "libvulcan.so"))
+        cxx.vulcan_pipeline_create.restype = C.c_void_p
+        cxx.vulcan_pipeline_create.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int]
+        cxx.vulcan_pipeline_run.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_int,
+                                            C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        cxx.vulcan_pipeline_destroy.argtypes = [C.c_void_p]
+        cxx.vulcan_pipeline_error.restype = C.c_char_p
+        cxx.vulcan_pipeline_error.argtypes = [C.c_void_p]
         depth = args.pipeline_depth
         lag = depth - 1
-        pipe = FramePipeline(vol, vb.DepthIntegrator(vol), vb.Tracer(vol), W, H, depth=depth)
-        metas = [frame_for(k, None) for k in range(nfr)]
-        acc = 0.0
+        h = cxx.vulcan_pipeline_create(MAIN, EXCESS, VOXEL, TRUNC, W, H, depth)
+        assert h, "vulcan_pipeline_create failed"
+        ptrs = (C.c_void_p * nfr)(*[t.data_ptr() for t in pinned_in])   # page-locked host images
+        all_poses = np.ascontiguousarray(np.stack([T for _, T in frames]), dtype=np.float32)
+        proj = np.ascontiguousarray(K, dtype=np.float32)
+        acc = C.c_double(0)
+        sub = (C.c_double * nfr)()
 
-        def take(k):
-            hd, hc, hn = pipe.result(k)
-            return float(hd[H // 2, W // 2]) + float(hc[H // 2, W // 2, 0]) + float(hn[H // 2, W // 2, 2])
+        def run(first, count):
+            sub_at = C.cast(C.addressof(sub) + 8 * first, C.POINTER(C.c_double))
+            rc = cxx.vulcan_pipeline_run(h, count, C.cast(C.addressof(ptrs) + 8 * first, C.POINTER(C.c_void_p)),
+                                         proj.ctypes.data, all_poses[first:].ctypes.data, lag, C.byref(acc), sub_at)
+            assert rc == 0, cxx.vulcan_pipeline_error(h)
 
-        host_submit.clear()
-        taken = 0  # frames whose images the host has taken so far (each exactly once, in order)
-        for k in range(nfr):
-            if k == args.warmup:
-                while taken < k:
-                    acc += take(taken)
-                    taken += 1
-                pipe.drain()
-                barrier()
-                t0 = time.perf_counter()
-            h0 = time.perf_counter()
-            pipe.submit(pinned_in[k], metas[k])
-            host_submit.append(time.perf_counter() - h0)
-            while taken <= k - lag:
-                acc += take(taken)
-                taken += 1
-        while taken < nfr:
-            acc += take(taken)
-            taken += 1
-        pipe.drain()
+        run(0, args.warmup)
         barrier()
-        return time.perf_counter() - t0, acc
+        t0 = time.perf_counter()
+        run(args.warmup, args.steps)
+        t = time.perf_counter() - t0
+        host_submit.clear()
+        host_submit.extend([0.0] * args.warmup + [sub[i] * 1e-6 for i in range(args.warmup, nfr)])
+        cxx.vulcan_pipeline_destroy(h)
+        return t, acc.value
 
     barrier()
     t_sync = e2e_sync()
@@ -376,9 +377,8 @@ def run_ours(args, rank, world):
     if world == 1:
         del vol
         torch.cuda.empty_cache()
-        vol = new_volume()
         barrier()
-        t_e2e, _ = e2e_streamed()
+        t_e2e, _ = e2e_streamed()   # the C++ pipeline owns its volume
         e2e_mode = "streamed"
     else:
         drop_volume(vol)
@@ -408,7 +408,8 @@ def run_ours(args, rank, world):
         "clocks": clocks,
         "e2e": {"value": total_units / t_e2e, "unit": "voxel-updates/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": t_e2e * 1e3 / args.steps,
-                "what": ("vulcan_b200.pipeline.FramePipeline (depth %d): every frame's pinned host depth -> device, "
+                "what": ("vulcan::FramePipeline (C++ host, include/vulcan/frame_pipeline.h; %d frames in flight) through the C "
+                         "entry point vulcan_pipeline_run: every frame's pinned host depth -> device, "
                          "SetView+Integrate+Trace, traced depth+colour+normal -> pinned host; copies of neighbouring "
                          "frames overlap the kernels; the host takes (and reads a pixel of) frame k-%d's images after "
                          "submitting frame k" % (args.pipeline_depth, args.pipeline_depth - 1))

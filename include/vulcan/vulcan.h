@@ -12,6 +12,7 @@
 #include <vulcan/exporter.h>
 #include <vulcan/extractor.h>
 #include <vulcan/frame.h>
+#include <vulcan/frame_pipeline.h>
 #include <vulcan/hash.h>
 #include <vulcan/image.h>
 #include <vulcan/integrator.h>

@@ -11,6 +11,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -414,13 +415,113 @@ static void TestExtractWall()
   remove(file.c_str());
 }
 
+// FramePipeline (addition): frames streamed from pinned host memory with three frames in flight must give
+// exactly the images of the synchronous calls, frame by frame; also through the C entry points.
+extern "C" {
+void* vulcan_pipeline_create(int, int, float, float, int, int, int);
+void vulcan_pipeline_destroy(void*);
+int vulcan_pipeline_run(void*, int, const float* const*, const float*, const float*, int, double*, double*);
+int vulcan_pipeline_result(void*, int, const float**, const float**, const float**);
+}
+
+static void TestFramePipeline()
+{
+  const int w = 160, h = 120, frames = 7;
+  const size_t n = (size_t)w * h;
+  Projection projection;
+  projection.SetFocalLength(80, 80);
+  projection.SetCenterPoint(80, 60);
+  // a wall that comes closer frame by frame, seen from a camera that moves sideways
+  std::vector<float*> depths;
+  std::vector<Frame> metas;
+  std::vector<float> poses;
+  for (int k = 0; k < frames; ++k)
+  {
+    float* d = FramePipeline::AllocHost(n);
+    for (size_t i = 0; i < n; ++i) d[i] = 1.5f - 0.01f * k + 0.0005f * (float)(i % w);
+    depths.push_back(d);
+    Frame f;
+    f.depth_projection = projection;
+    f.depth_to_world_transform = Transform::Translate(0.31f + 0.004f * k, 0.27f, 0.19f);
+    metas.push_back(f);
+    poses.insert(poses.end(), reinterpret_cast<const float*>(&f.depth_to_world_transform),
+                 reinterpret_cast<const float*>(&f.depth_to_world_transform) + 32);
+  }
+  auto make = [&](std::shared_ptr<Volume>& volume, std::shared_ptr<DepthIntegrator>& integrator, std::shared_ptr<Tracer>& tracer)
+  {
+    volume = std::make_shared<Volume>(8192, 2048);
+    volume->SetVoxelLength(0.008f);
+    volume->SetTruncationLength(0.04f);
+    integrator = std::make_shared<DepthIntegrator>(volume);
+    tracer = std::make_shared<Tracer>(volume);
+  };
+  // synchronous
+  std::shared_ptr<Volume> volume;
+  std::shared_ptr<DepthIntegrator> integrator;
+  std::shared_ptr<Tracer> tracer;
+  make(volume, integrator, tracer);
+  std::vector<std::vector<float>> want_d(frames, std::vector<float>(n)), want_n(frames, std::vector<float>(3 * n));
+  for (int k = 0; k < frames; ++k)
+  {
+    Frame f = metas[k];
+    f.depth_image = std::make_shared<Image>(w, h);
+    f.depth_image->CopyFromHost(depths[k]);
+    volume->SetView(f);
+    integrator->Integrate(f);
+    Frame traced;
+    traced.depth_projection = projection;
+    traced.depth_to_world_transform = f.depth_to_world_transform;
+    traced.depth_image = std::make_shared<Image>(w, h);
+    tracer->Trace(traced);
+    traced.depth_image->CopyToHost(want_d[k].data());
+    traced.normal_image->CopyToHost(want_n[k].data());
+  }
+  size_t hits = 0;
+  for (float d : want_d[frames - 1]) hits += d > 0;
+  CHECK(hits > n / 2);
+  // streamed through the class
+  make(volume, integrator, tracer);
+  {
+    FramePipeline pipeline(volume, integrator, tracer, w, h, 3);
+    for (int k = 0; k < frames; ++k)
+    {
+      CHECK(pipeline.Submit(depths[k], metas[k]) == k);
+      if (k >= 2)
+      {
+        const FramePipeline::Images im = pipeline.Result(k - 2);
+        CHECK(std::memcmp(im.depth, want_d[k - 2].data(), n * sizeof(float)) == 0);
+        CHECK(std::memcmp(im.normal, want_n[k - 2].data(), 3 * n * sizeof(float)) == 0);
+      }
+    }
+    for (int k = frames - 2; k < frames; ++k)
+      CHECK(std::memcmp(pipeline.Result(k).depth, want_d[k].data(), n * sizeof(float)) == 0);
+    pipeline.Drain();
+  }
+  // the volume is usable on its own stream again
+  CHECK(volume->GetVisibleBlockCount() > 0);
+  // streamed through the C entry points
+  void* handle = vulcan_pipeline_create(8192, 2048, 0.008f, 0.04f, w, h, 3);
+  CHECK(handle != nullptr);
+  const float proj4[4] = {80, 80, 80, 60};
+  double checksum = 0;
+  std::vector<double> submit_us(frames);
+  CHECK(vulcan_pipeline_run(handle, frames, depths.data(), proj4, poses.data(), 2, &checksum, submit_us.data()) == 0);
+  const float *d = nullptr, *c = nullptr, *nn = nullptr;
+  CHECK(vulcan_pipeline_result(handle, frames - 1, &d, &c, &nn) == 0);
+  CHECK(std::memcmp(d, want_d[frames - 1].data(), n * sizeof(float)) == 0);
+  CHECK(std::memcmp(nn, want_n[frames - 1].data(), 3 * n * sizeof(float)) == 0);
+  CHECK(checksum > 0);
+  vulcan_pipeline_destroy(handle);
+  for (float* p : depths) FramePipeline::FreeHost(p);
+}
+
 int main()
 {
   struct { const char* name; void (*fn)(); } tests[] = {
     {"Volume.Constructor", TestVolumeConstructor}, {"Buffer", TestBuffer}, {"Integrator.Integrate", TestIntegrate},
     {"Tracer.TraceWall", TestTraceWall}, {"Volume.TwoVolumes", TestTwoVolumes},
     {"Frame.Downsample", TestDownsample}, {"DepthTracker.Wall", TestDepthTrackerWall},
-    {"Extractor.Wall", TestExtractWall},
+    {"Extractor.Wall", TestExtractWall}, {"FramePipeline", TestFramePipeline},
   };
   for (auto& t : tests)
   {

@@ -35,7 +35,9 @@ def test_cxx_library_builds_and_exports_reference_classes():
                    "vulcan::Tracer::Trace(vulcan::Frame&)", "vulcan::Tracer::SetDepthRange(float, float)",
                    "vulcan::Frame::ComputeNormals()", "vulcan::Frame::FilterDepths()",
                    "vulcan::ComputePatches(", "vulcan::ComputeBounds(", "vulcan::ComputePoints(",
-                   "vulcan::ComputeNormals(", "vulcan::ResetBoundsBuffer("):
+                   "vulcan::ComputeNormals(", "vulcan::ResetBoundsBuffer(",
+                   "vulcan::FramePipeline::Submit(", "vulcan::FramePipeline::Result(int)",
+                   "vulcan_pipeline_create", "vulcan_pipeline_run", "vulcan_pipeline_submit", "vulcan_pipeline_result"):
         assert needle in syms, "libvulcan.so does not define " + needle
     assert os.path.exists(BIN)
 
