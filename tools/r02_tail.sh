@@ -1,7 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_cxx_dropin.py tests/test_pipeline_gpu.py -m gpu -q -x 2>&1 | tail -8
-timeout 300 python bench.py --steps 40 --warmup 5 2>gpurun_out/bench_tail.err > gpurun_out/bench_tail.json; python -c "
-import json
-d=json.loads(open('gpurun_out/bench_tail.json').read().strip().splitlines()[-1]); print('bench', d['ms_per_step'], d['phases'], 'e2e', d['e2e']['ms_per_step'], d['e2e']['host_submit_us_median'], d['e2e']['sync_every_step'], d['roofline']['frac'], d['gpu_launches'])"
-tail -3 gpurun_out/bench_tail.err
+VK_TUNE="14=1" timeout 600 python -m pytest tests/test_parity_gpu.py -m gpu -q -x -k "oracle_exact or c1_full or baseline_configs" 2>&1 | tail -4
+timeout 200 python tools/ray_ab.py --phase integrate --sets "14=0;14=1;14=1,3=4;14=1,3=5;14=1,3=6;14=1,3=7" --out int_ab_c2.json 2>&1 | tail -6
+timeout 300 python tools/ray_ab.py --phase integrate --scene room --frames 4 --sets "14=0;14=1;14=1,3=6;14=1,3=7" --out int_ab_room.json 2>&1 | tail -4

@@ -140,6 +140,93 @@ __device__ __forceinline__ void cp_async16(uint4* smem_dst, const uint4* gsrc) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
+// The update of a thread's 4 voxels (80 bytes = 20 words in w) given the outcome of the image tests: TSDF
+// running average and, in the same pass, colour / albedo; returns the mask of changed words.  Also keeps the
+// block's distance mirror (and its copies on the peers of a sharded volume) in step.
+template <int MODE, bool F>
+__device__ __forceinline__ uint32_t update_piece(const IntegrateParams& p, const VoxelTests<MODE>& q, uint32_t (&w)[20],
+                                                 int data, int t) {
+  uint32_t dirty = 0;  // bit per word of the thread's 80 bytes
+  const uint4 d_old = make_uint4(w[0], w[5], w[10], w[15]);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float D = __uint_as_float(w[5 * k]);
+    int dwt = (int)(int16_t)(w[5 * k + 4] & 0xffff);
+    int cwt = (int)(int16_t)(w[5 * k + 4] >> 16);
+    if ((q.dmask >> k) & 1u) {
+      // src/depth_integrator.cu:68-76
+      const float c = vmin(1.0f, divc(q.dcur[k], p.trunc));
+      const float wn = (float)(dwt + 1);
+      D = fdiv(FP<F>::mad(D, (float)dwt, c), wn);
+      dwt = (int)(short)vmin(p.max_dw, wn);
+      w[5 * k] = __float_as_uint(D);
+      dirty |= (1u << (5 * k)) | (1u << (5 * k + 4));
+    }
+    if (MODE != MODE_DEPTH) {
+      if (((q.cmask >> k) & 1u) && fabsf(D) < 1.0f) {
+        const size_t ci = 3 * (size_t)q.cidx[MODE == MODE_DEPTH ? 0 : k];
+        const float cr = __ldg(p.color + ci + 0);
+        const float cg = __ldg(p.color + ci + 1);
+        const float cb = __ldg(p.color + ci + 2);
+        const float fw = (float)cwt;
+        const float wn = (float)(cwt + 1);
+        const float r0 = __uint_as_float(w[5 * k + 1]);
+        const float g0 = __uint_as_float(w[5 * k + 2]);
+        const float b0 = __uint_as_float(w[5 * k + 3]);
+        bool ok = true;
+        float sr, sg, sb;
+        if (MODE == MODE_LIGHT) {
+          // src/light_integrator.cu:229-241, include/vulcan/light.h:52-60
+          const size_t ni = 3 * (size_t)q.didx[MODE == MODE_LIGHT ? k : 0];
+          const float nx = __ldg(p.normal + ni + 0);
+          const float ny = __ldg(p.normal + ni + 1);
+          const float nz = __ldg(p.normal + ni + 2);
+          Mat34 Tcd;
+          Tcd.load(p.Tcd);
+          const Vec3 Xcn = xform0<F>(Tcd, nx, ny, nz);
+          const Vec3 Xc = q.Xc[MODE == MODE_LIGHT ? k : 0];
+          const Vec3 delta = {sub(p.light.position[0], Xc.x), sub(p.light.position[1], Xc.y),
+                              sub(p.light.position[2], Xc.z)};
+          const float dist2 = dot3<F>(delta, delta);
+          const float invn = rcp(__fsqrt_rn(dist2));
+          const Vec3 dirn = {mul(delta.x, invn), mul(delta.y, invn), mul(delta.z, invn)};
+          const float cos_theta = dot3<F>(Xcn, dirn);
+          const float shading = fdiv(mul(p.light.intensity, cos_theta), dist2);
+          ok = shading > 0.05f;
+          const float inv_s = rcp(shading);
+          sr = FP<F>::mad(cr, inv_s, mul(r0, fw));
+          sg = FP<F>::mad(cg, inv_s, mul(g0, fw));
+          sb = FP<F>::mad(cb, inv_s, mul(b0, fw));
+        } else {
+          sr = FP<F>::mad(r0, fw, cr);
+          sg = FP<F>::mad(g0, fw, cg);
+          sb = FP<F>::mad(b0, fw, cb);
+        }
+        if (ok) {
+          const float inv = rcp(wn);
+          w[5 * k + 1] = __float_as_uint(mul(sr, inv));
+          w[5 * k + 2] = __float_as_uint(mul(sg, inv));
+          w[5 * k + 3] = __float_as_uint(mul(sb, inv));
+          cwt = (int)(short)vmin(p.max_cw, wn);
+          dirty |= (0xeu << (5 * k)) | (1u << (5 * k + 4));
+        }
+      }
+    }
+    w[5 * k + 4] = ((uint32_t)(uint16_t)(int16_t)dwt) | ((uint32_t)(uint16_t)(int16_t)cwt << 16);
+  }
+  // the thread's 4 distances are one aligned 16-byte piece of the block's distance mirror
+  // (voxel index 4t): a warp writes 512 contiguous bytes
+  // - written only when a distance really changed: free-space voxels in front of the surface keep
+  // D = 1 under the running average, and those are half of the updates
+  const uint4 d4 = make_uint4(w[0], w[5], w[10], w[15]);
+  if (q.dmask && ((d4.x ^ d_old.x) | (d4.y ^ d_old.y) | (d4.z ^ d_old.z) | (d4.w ^ d_old.w))) {
+    reinterpret_cast<uint4*>(p.sdf + (size_t)data * VK_BLOCK_VOXELS)[t] = d4;
+    for (int r = 0; r < p.push_count; ++r)   // posted stores over NVLink; read after the next handshake
+      if (r != p.push_rank) reinterpret_cast<uint4*>(p.push_sdf[r] + (size_t)data * VK_BLOCK_VOXELS)[t] = d4;
+  }
+  return dirty;
+}
+
 // Software pipeline over the CTA's blocks: the tile fetch of block i is issued, then the image
 // tests of block i+1 run (projection + depth gathers, independent of the tile), then block i is
 // updated in registers and its changed chunks are stored.  The entry of block i+2 is in flight
@@ -208,73 +295,7 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
         const uint4 q = stage[lane * 5 + c];
         w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
       }
-      const uint4 d_old = make_uint4(w[0], w[5], w[10], w[15]);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        float D = __uint_as_float(w[5 * k]);
-        int dwt = (int)(int16_t)(w[5 * k + 4] & 0xffff);
-        int cwt = (int)(int16_t)(w[5 * k + 4] >> 16);
-        if ((cur.dmask >> k) & 1u) {
-          // src/depth_integrator.cu:68-76
-          const float c = vmin(1.0f, divc(cur.dcur[k], p.trunc));
-          const float wn = (float)(dwt + 1);
-          D = fdiv(FP<F>::mad(D, (float)dwt, c), wn);
-          dwt = (int)(short)vmin(p.max_dw, wn);
-          w[5 * k] = __float_as_uint(D);
-          dirty |= (1u << (5 * k)) | (1u << (5 * k + 4));
-        }
-        if (MODE != MODE_DEPTH) {
-          if (((cur.cmask >> k) & 1u) && fabsf(D) < 1.0f) {
-            const size_t ci = 3 * (size_t)cur.cidx[MODE == MODE_DEPTH ? 0 : k];
-            const float cr = __ldg(p.color + ci + 0);
-            const float cg = __ldg(p.color + ci + 1);
-            const float cb = __ldg(p.color + ci + 2);
-            const float fw = (float)cwt;
-            const float wn = (float)(cwt + 1);
-            const float r0 = __uint_as_float(w[5 * k + 1]);
-            const float g0 = __uint_as_float(w[5 * k + 2]);
-            const float b0 = __uint_as_float(w[5 * k + 3]);
-            bool ok = true;
-            float sr, sg, sb;
-            if (MODE == MODE_LIGHT) {
-              // src/light_integrator.cu:229-241, include/vulcan/light.h:52-60
-              const size_t ni = 3 * (size_t)cur.didx[MODE == MODE_LIGHT ? k : 0];
-              const float nx = __ldg(p.normal + ni + 0);
-              const float ny = __ldg(p.normal + ni + 1);
-              const float nz = __ldg(p.normal + ni + 2);
-              Mat34 Tcd;
-              Tcd.load(p.Tcd);
-              const Vec3 Xcn = xform0<F>(Tcd, nx, ny, nz);
-              const Vec3 Xc = cur.Xc[MODE == MODE_LIGHT ? k : 0];
-              const Vec3 delta = {sub(p.light.position[0], Xc.x), sub(p.light.position[1], Xc.y),
-                                  sub(p.light.position[2], Xc.z)};
-              const float dist2 = dot3<F>(delta, delta);
-              const float invn = rcp(__fsqrt_rn(dist2));
-              const Vec3 dirn = {mul(delta.x, invn), mul(delta.y, invn), mul(delta.z, invn)};
-              const float cos_theta = dot3<F>(Xcn, dirn);
-              const float shading = fdiv(mul(p.light.intensity, cos_theta), dist2);
-              ok = shading > 0.05f;
-              const float inv_s = rcp(shading);
-              sr = FP<F>::mad(cr, inv_s, mul(r0, fw));
-              sg = FP<F>::mad(cg, inv_s, mul(g0, fw));
-              sb = FP<F>::mad(cb, inv_s, mul(b0, fw));
-            } else {
-              sr = FP<F>::mad(r0, fw, cr);
-              sg = FP<F>::mad(g0, fw, cg);
-              sb = FP<F>::mad(b0, fw, cb);
-            }
-            if (ok) {
-              const float inv = rcp(wn);
-              w[5 * k + 1] = __float_as_uint(mul(sr, inv));
-              w[5 * k + 2] = __float_as_uint(mul(sg, inv));
-              w[5 * k + 3] = __float_as_uint(mul(sb, inv));
-              cwt = (int)(short)vmin(p.max_cw, wn);
-              dirty |= (0xeu << (5 * k)) | (1u << (5 * k + 4));
-            }
-          }
-        }
-        w[5 * k + 4] = ((uint32_t)(uint16_t)(int16_t)dwt) | ((uint32_t)(uint16_t)(int16_t)cwt << 16);
-      }
+      dirty = update_piece<MODE, F>(p, cur, w, ent.z, t);
 #pragma unroll
       for (int c = 0; c < 5; ++c) {
         if ((dirty >> (4 * c)) & 0xfu)
@@ -282,16 +303,6 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
       }
       // voxels written = voxels whose weight word is dirty (bit 5k+4)
       n_updated += __popc(dirty & 0x84210u);
-      // the thread's 4 distances are one aligned 16-byte piece of the block's distance mirror
-      // (voxel index 4t): a warp writes 512 contiguous bytes
-      // - written only when a distance really changed: free-space voxels in front of the surface keep
-      // D = 1 under the running average, and those are half of the updates
-      const uint4 d4 = make_uint4(w[0], w[5], w[10], w[15]);
-      if (cur.dmask && ((d4.x ^ d_old.x) | (d4.y ^ d_old.y) | (d4.z ^ d_old.z) | (d4.w ^ d_old.w))) {
-        reinterpret_cast<uint4*>(p.sdf + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = d4;
-        for (int r = 0; r < p.push_count; ++r)   // posted stores over NVLink; read after the next handshake
-          if (r != p.push_rank) reinterpret_cast<uint4*>(p.push_sdf[r] + (size_t)ent.z * VK_BLOCK_VOXELS)[t] = d4;
-      }
     }
     // changed chunks go back lane-contiguously
     uint32_t chunk_dirty = 0;  // bit c: the thread's chunk c changed
@@ -311,6 +322,145 @@ __global__ void __launch_bounds__(128, integrate_min_ctas<MODE>()) vk_integrate_
     cur = nxt;
     ent = ent_n;
     ent_n = ent_nn;
+  }
+  n_updated = __reduce_add_sync(0xffffffffu, n_updated);
+  if ((threadIdx.x & 31) == 0 && n_updated) atomicAdd(p.updated, (unsigned long long)n_updated);
+}
+
+// ---- bulk-copy variant (TMA 1-D) --------------------------------------------------------------------
+// The same update, with the tile movement handed to the copy engine: a block's 10 240-byte tile is
+// fetched whole by ONE cp.async.bulk (global -> shared, completion on an mbarrier) issued by one thread,
+// kBulkStages tiles deep - the tiles of blocks i+1 and i+2 are in flight while block i is updated - so no
+// thread spends issue slots or registers on loads.  The price: 100 % of every visited tile crosses the
+// memory system, where the selective path above fetches the ~58 % of 16-byte pieces some voxel needs.
+// Changed pieces go back like above (lane-contiguous 16-byte stores of the dirty chunks only).
+// Selected with tuning knob VK_TUNE_INTEGRATE_BULK; A/B numbers in DESIGN.md 4.2.
+constexpr int kBulkStages = 3;
+constexpr int kTileBytes = VK_BLOCK_VOXELS * (int)sizeof(vkVoxel);   // 10 240
+constexpr int kTileChunks = kTileBytes / 16;                         // 640
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+template <int MODE, bool F>
+__global__ void __launch_bounds__(128, 6) vk_integrate_bulk_kernel(const IntegrateParams p) {
+  pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
+  pdl_trigger();  // the next one may be scheduled as this grid drains
+  extern __shared__ __align__(128) unsigned char s_raw[];
+  uint4* const tiles = reinterpret_cast<uint4*>(s_raw);                                           // [kBulkStages][640]
+  uint64_t* const full = reinterpret_cast<uint64_t*>(s_raw + (size_t)kBulkStages * kTileBytes);   // [kBulkStages]
+  const int n = *p.count;
+  const int t = threadIdx.x;
+  const int lane = t & 31, warp = t >> 5;
+  const int vz = t >> 4, vy = (t >> 1) & 7, vx0 = (t & 1) * 4;
+  const float fy = add((float)vy, 0.5f), fz = add((float)vz, 0.5f);
+  const int G = gridDim.x;
+  Mat34 Tdw, Tcw;
+  Tdw.load(p.Tdw);
+  if (MODE != MODE_DEPTH) Tcw.load(p.Tcw);
+  if (t == 0) {
+#pragma unroll
+    for (int s = 0; s < kBulkStages; ++s) mbar_init(full + s, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  int bi = blockIdx.x;
+  if (bi >= n) return;
+  unsigned n_updated = 0;
+  auto tile_of = [&](int data) {
+    return reinterpret_cast<const char*>(p.voxels) + (size_t)data * kTileBytes;
+  };
+  // entries one, two and three blocks ahead (every thread holds them: the loads are broadcasts)
+  int4 ent = ld_entry(p.entries + __ldg(p.visible + bi));
+  int4 ent_n = make_int4(0, 0, 0, 0), ent_nn = make_int4(0, 0, 0, 0);
+  if (bi + G < n) ent_n = ld_entry(p.entries + __ldg(p.visible + bi + G));
+  if (bi + 2 * G < n) ent_nn = ld_entry(p.entries + __ldg(p.visible + bi + 2 * G));
+  int slot_nnn = (bi + 3 * G < n) ? __ldg(p.visible + bi + 3 * G) : 0;
+  if (t == 0) {   // prologue: the first two tiles
+    mbar_expect_tx(full + 0, kTileBytes);
+    bulk_load(tiles, tile_of(ent.z), kTileBytes, full + 0);
+    if (bi + G < n) {
+      mbar_expect_tx(full + 1, kTileBytes);
+      bulk_load(tiles + kTileChunks, tile_of(ent_n.z), kTileBytes, full + 1);
+    }
+  }
+  VoxelTests<MODE> cur, nxt;
+  test_voxels<MODE, F>(p, Tdw, Tcw, ent, vx0, fy, fz, cur);
+  int k = 0;
+  for (; bi < n; bi += G, ++k) {
+    const int stage = k % kBulkStages;
+    // tile of block k + 2 into the stage block k - 1 used (all of its readers passed the barrier at the end
+    // of the previous iteration; the proxy fence orders their generic-proxy accesses before the copy engine's)
+    if (t == 0 && bi + 2 * G < n) {
+      const int s2 = (k + 2) % kBulkStages;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      mbar_expect_tx(full + s2, kTileBytes);
+      bulk_load(tiles + (size_t)s2 * kTileChunks, tile_of(ent_nn.z), kTileBytes, full + s2);
+    }
+    int4 ent_nnn = make_int4(0, 0, 0, 0);
+    if (bi + 3 * G < n) ent_nnn = ld_entry(p.entries + slot_nnn);
+    if (bi + 4 * G < n) slot_nnn = __ldg(p.visible + bi + 4 * G);
+    if (bi + G < n) test_voxels<MODE, F>(p, Tdw, Tcw, ent_n, vx0, fy, fz, nxt);
+    mbar_wait(full + stage, (uint32_t)((k / kBulkStages) & 1));
+    uint4* const stage_tile = tiles + (size_t)stage * kTileChunks;
+    uint4* const mine = stage_tile + warp * kWarpChunks;   // the warp's 2560 bytes
+    uint4* const gtile = reinterpret_cast<uint4*>(reinterpret_cast<char*>(p.voxels) + (size_t)ent.z * kTileBytes) +
+                         warp * kWarpChunks;
+    const bool need = (cur.dmask | cur.cmask) != 0;
+    uint32_t dirty = 0;
+    if (need) {
+      uint32_t w[20];
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const uint4 q = mine[lane * 5 + c];
+        w[4 * c + 0] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
+      }
+      dirty = update_piece<MODE, F>(p, cur, w, ent.z, t);
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        if ((dirty >> (4 * c)) & 0xfu) mine[lane * 5 + c] = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+      }
+      n_updated += __popc(dirty & 0x84210u);
+    }
+    uint32_t chunk_dirty = 0;
+#pragma unroll
+    for (int c = 0; c < 5; ++c) chunk_dirty |= ((dirty >> (4 * c)) & 0xfu) ? (1u << c) : 0u;
+    if (__any_sync(0xffffffffu, chunk_dirty != 0)) {
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < 5; ++c) {
+        const int j = c * 32 + lane;
+        const int owner = (j * 205) >> 10;
+        const uint32_t m = __shfl_sync(0xffffffffu, chunk_dirty, owner);
+        if ((m >> (j - owner * 5)) & 1u) gtile[j] = mine[j];
+      }
+    }
+    __syncthreads();   // every warp is done with this stage before it is refilled (next iteration)
+    cur = nxt;
+    ent = ent_n;
+    ent_n = ent_nn;
+    ent_nn = ent_nnn;
   }
   n_updated = __reduce_add_sync(0xffffffffu, n_updated);
   if ((threadIdx.x & 31) == 0 && n_updated) atomicAdd(p.updated, (unsigned long long)n_updated);
@@ -427,8 +577,28 @@ static int integrate_grid() {
   return grid;
 }
 
+template <int MODE, bool F>
+static int launch_integrate_bulk(const IntegrateParams& p, cudaStream_t s) {
+  const size_t smem = (size_t)kBulkStages * kTileBytes + kBulkStages * sizeof(uint64_t);
+  static int grid = 0;
+  if (grid == 0) {
+    cudaFuncSetAttribute(vk_integrate_bulk_kernel<MODE, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vk_integrate_bulk_kernel<MODE, F>, 128, smem) != cudaSuccess ||
+        per_sm <= 0)
+      per_sm = 4;
+    grid = per_sm * sm_count();
+  }
+  const int forced = g_tune[VK_TUNE_INTEGRATE_CTAS_PER_SM].load();
+  launch_chained(vk_integrate_bulk_kernel<MODE, F>, dim3(forced > 0 ? forced * sm_count() : grid), dim3(128), smem, s, p);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
+
 template <int MODE>
 static int launch_integrate(const IntegrateParams& p, int math_mode, cudaStream_t s) {
+  if (g_tune[VK_TUNE_INTEGRATE_BULK].load())   // A/B: tiles fetched whole by the copy engine
+    return (math_mode == VK_MATH_STRICT) ? launch_integrate_bulk<MODE, false>(p, s) : launch_integrate_bulk<MODE, true>(p, s);
   if (math_mode == VK_MATH_STRICT)
     launch_chained(vk_integrate_kernel<MODE, false>, dim3(integrate_grid<MODE, false>()), dim3(128), 0, s, p);
   else
