@@ -475,6 +475,18 @@ int vk_track_depth(const vkFrame* keyframe, vkFrame* frame, int translation_enab
 int vk_extract_points(const vkVolume* v, float* points, float* colors, int capacity, int* count,
                       void* stream);
 
+/* The triangle mesh of the whole volume: the vertices of vk_extract_points plus marching-cubes faces over
+ * them (the reference's ExtractVertexIndicesKernel / ExtractFacesKernel are empty, src/extractor.cu:392-413).
+ * One cube per voxel (the voxel and its +x / +y / +z neighbours, across block faces), meshed when all eight
+ * corners are observed; case bit c set where !(distance > 0); triangle table generated by
+ * tools/gen_mc_tables.py (segments on a cube face depend only on that face's corner signs, so neighbouring
+ * cubes agree and the mesh is watertight wherever the surface is surrounded by observed voxels; normals point
+ * towards positive distance).  faces: device int[3 * face_capacity], vertex indices into points; *point_count
+ * and *face_count (device ints) receive the numbers found, which may exceed the capacities (then call again
+ * with larger buffers).  Synchronises the stream (sizes its workspace from the allocated-block counter). */
+int vk_extract_mesh(const vkVolume* v, float* points, float* colors, int point_capacity, int* point_count,
+                    int* faces, int face_capacity, int* face_count, void* stream);
+
 /* ---- misc -------------------------------------------------------------------- */
 
 /* Library version and the number of kernels launched by this library since load

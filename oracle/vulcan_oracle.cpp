@@ -1201,3 +1201,98 @@ extern "C" long long vo_extract_points(void* h, float* points, float* colors, lo
   }
   return n;
 }
+
+// ---- triangles over the vertices of vo_extract_points (no finished reference counterpart: the reference's
+// ExtractVertexIndicesKernel / ExtractFacesKernel are empty, src/extractor.cu:392-413).  Restates the definition
+// of include/vulcan_b200.h (vk_extract_mesh): one marching-cubes cube per voxel (corner c at offset
+// (c & 1, (c >> 1) & 1, c >> 2), across block faces), meshed when all eight corners are observed; case bit c set
+// where !(distance > 0); triangles from the generated table (tools/gen_mc_tables.py), a triangle corner being
+// the vertex on the lattice edge (owner voxel, axis).  "Parity unpinned" with respect to the reference. --------
+#include "../vulcan_b200/csrc/vk_mc_tables.h"
+#include <unordered_map>
+
+extern "C" long long vo_extract_mesh(void* h, float* points, float* colors, long long point_capacity, int* faces,
+                                     long long face_capacity, long long* face_count) {
+  Volume* v = (Volume*)h;
+  const float l = v->voxel_length, L = 8 * v->voxel_length;
+  Fetch f = {0, 0};
+  std::unordered_map<long long, long long> vertex;   // (voxel-block id * 512 + voxel) * 3 + axis -> vertex index
+  long long n = 0;
+  // vertices: exactly the loop of vo_extract_points, remembering where each one went
+  for (int ei = 0; ei < v->B_; ++ei) {
+    const HashEntry& e = v->entries[ei];
+    if (e.data == -1) continue;
+    const int bx = e.block[0], by = e.block[1], bz = e.block[2];
+    for (int t = 0; t < 512; ++t) {
+      const int vx = t & 7, vy = (t >> 3) & 7, vz = t >> 6;
+      const Voxel& a = v->voxels[(long long)e.data * 512 + t];
+      if (a.distance_weight <= 0) continue;
+      const float base[3] = {(float)bx * L + ((float)vx + 0.5f) * l, (float)by * L + ((float)vy + 0.5f) * l,
+                             (float)bz * L + ((float)vz + 0.5f) * l};
+      for (int ax = 0; ax < 3; ++ax) {
+        const int nx = vx + (ax == 0), ny = vy + (ax == 1), nz = vz + (ax == 2);
+        int data = e.data;
+        if (nx > 7 || ny > 7 || nz > 7) {
+          const int cx = bx + (nx >> 3), cy = by + (ny >> 3), cz = bz + (nz >> 3);
+          if (cx > 32767 || cy > 32767 || cz > 32767) continue;
+          data = find_data(v, cx, cy, cz, f);
+          if (data == -1) continue;
+        }
+        const Voxel& b = v->voxels[(long long)data * 512 + (((nz & 7) << 6) | ((ny & 7) << 3) | (nx & 7))];
+        if (b.distance_weight <= 0 || ((a.distance > 0) == (b.distance > 0))) continue;
+        const float tt = a.distance / (a.distance - b.distance);
+        if (n < point_capacity) {
+          float* o = points + 3 * n;
+          o[0] = base[0]; o[1] = base[1]; o[2] = base[2];
+          o[ax] = base[ax] + tt * l;
+          if (colors)
+            for (int c = 0; c < 3; ++c) colors[3 * n + c] = a.color[c] + tt * (b.color[c] - a.color[c]);
+        }
+        vertex[((long long)e.data * 512 + t) * 3 + ax] = n;
+        ++n;
+      }
+    }
+  }
+  // faces
+  long long nf = 0;
+  for (int ei = 0; ei < v->B_; ++ei) {
+    const HashEntry& e = v->entries[ei];
+    if (e.data == -1) continue;
+    const int bx = e.block[0], by = e.block[1], bz = e.block[2];
+    int nb[8];
+    for (int k = 0; k < 8; ++k) {
+      const int cx = bx + (k & 1), cy = by + ((k >> 1) & 1), cz = bz + (k >> 2);
+      nb[k] = (k == 0) ? e.data : ((cx > 32767 || cy > 32767 || cz > 32767) ? -1 : find_data(v, cx, cy, cz, f));
+    }
+    for (int t = 0; t < 512; ++t) {
+      const int vx = t & 7, vy = (t >> 3) & 7, vz = t >> 6;
+      unsigned cube = 0;
+      bool ok = true;
+      for (int c = 0; c < 8 && ok; ++c) {
+        const int x = vx + (c & 1), y = vy + ((c >> 1) & 1), z = vz + (c >> 2);
+        const int data = nb[(x >> 3) | ((y >> 3) << 1) | ((z >> 3) << 2)];
+        if (data < 0) { ok = false; break; }
+        const Voxel& q = v->voxels[(long long)data * 512 + (((z & 7) << 6) | ((y & 7) << 3) | (x & 7))];
+        if (q.distance_weight <= 0) ok = false;
+        if (!(q.distance > 0)) cube |= 1u << c;
+      }
+      if (!ok) continue;
+      for (int k = 0; k < 5 && kMcTriTable[cube][3 * k] >= 0; ++k) {
+        int ids[3];
+        for (int j = 0; j < 3; ++j) {
+          const int edge = kMcTriTable[cube][3 * k + j];
+          const int corner = kMcEdgeCorner[edge], axis = kMcEdgeAxis[edge];
+          const int x = vx + (corner & 1), y = vy + ((corner >> 1) & 1), z = vz + (corner >> 2);
+          const int data = nb[(x >> 3) | ((y >> 3) << 1) | ((z >> 3) << 2)];
+          const long long key = ((long long)data * 512 + (((z & 7) << 6) | ((y & 7) << 3) | (x & 7))) * 3 + axis;
+          const auto it = vertex.find(key);
+          ids[j] = (it == vertex.end()) ? -1 : (int)it->second;
+        }
+        if (nf < face_capacity) { faces[3 * nf] = ids[0]; faces[3 * nf + 1] = ids[1]; faces[3 * nf + 2] = ids[2]; }
+        ++nf;
+      }
+    }
+  }
+  if (face_count) *face_count = nf;
+  return n;
+}

@@ -390,7 +390,18 @@ static void TestExtractWall()
   Mesh mesh;
   Extractor extractor(volume);
   extractor.Extract(mesh);
-  CHECK(mesh.points.size() > 10000 && mesh.colors.size() == mesh.points.size() && mesh.faces.empty());
+  CHECK(mesh.points.size() > 10000 && mesh.colors.size() == mesh.points.size());
+  // faces over the vertices: a flat wall seen head on - every triangle lies in the plane z = 1.5 and faces the camera
+  // (normals towards positive distance, i.e. towards -z)
+  CHECK(mesh.faces.size() > mesh.points.size());
+  for (const Vector3i& t : mesh.faces)
+  {
+    CHECK(t[0] >= 0 && t[1] >= 0 && t[2] >= 0 && t[0] < (int)mesh.points.size() && t[1] < (int)mesh.points.size() &&
+          t[2] < (int)mesh.points.size());
+    const Vector3f a = mesh.points[t[0]], b = mesh.points[t[1]], c = mesh.points[t[2]];
+    const float nz = (b[0] - a[0]) * (c[1] - a[1]) - (b[1] - a[1]) * (c[0] - a[0]);
+    CHECK(nz < 0);
+  }
   int on_wall = 0;
   for (size_t i = 0; i < mesh.points.size(); ++i)
   {

@@ -893,6 +893,46 @@ def oracle_extract_points(ov):
     return pts, col
 
 
+def oracle_extract_mesh(ov):
+    """(points, colours, faces) of the oracle's marching-cubes mesh (vo_extract_mesh)."""
+    lib = ov.lib
+    lib.vo_extract_mesh.restype = C.c_longlong
+    lib.vo_extract_mesh.argtypes = [_P, _P, _P, C.c_longlong, _P, C.c_longlong, _P]
+    nf = C.c_longlong(0)
+    n = lib.vo_extract_mesh(ov.h, None, None, 0, None, 0, C.byref(nf))
+    pts = np.zeros((n, 3), dtype=np.float32)
+    col = np.zeros((n, 3), dtype=np.float32)
+    faces = np.zeros((nf.value, 3), dtype=np.int32)
+    assert lib.vo_extract_mesh(ov.h, _ptr(pts), _ptr(col), n, _ptr(faces), nf.value, C.byref(nf)) == n
+    return pts, col, faces
+
+
+def canonical_triangles(pts, faces):
+    """Triangles as rows of 9 vertex-coordinate bit patterns, each rotated so that its smallest corner comes
+    first (winding kept), rows sorted: equal for two meshes iff they have the same oriented triangles."""
+    tri = np.ascontiguousarray(pts, dtype=np.float32).view(np.uint32)[faces]          # (F, 3, 3)
+    keys = tri[..., 0].astype(np.uint64) * np.uint64(1 << 42) + tri[..., 1].astype(np.uint64) * np.uint64(1 << 21) \
+        + tri[..., 2].astype(np.uint64) % np.uint64(1 << 21)
+    first = np.argmin(keys, axis=1)
+    idx = (first[:, None] + np.arange(3)[None, :]) % 3
+    rows = np.take_along_axis(tri, idx[:, :, None], axis=1).reshape(len(faces), 9)
+    return rows[np.lexsort(rows.T[::-1])]
+
+
+def mesh_edge_report(faces):
+    """Directed-edge statistics of a triangle mesh: a closed, consistently oriented surface uses every
+    directed edge once and always together with its opposite."""
+    f = np.asarray(faces, dtype=np.int64)
+    a = np.concatenate([f[:, 0], f[:, 1], f[:, 2]])
+    b = np.concatenate([f[:, 1], f[:, 2], f[:, 0]])
+    m = int(max(a.max(), b.max())) + 1
+    fwd = a * m + b
+    uniq, counts = np.unique(fwd, return_counts=True)
+    rev = np.isin(b * m + a, fwd)
+    return dict(edges=int(len(fwd)), repeated_directed=int((counts > 1).sum()), boundary=int((~rev).sum()),
+                degenerate=int(((f[:, 0] == f[:, 1]) | (f[:, 1] == f[:, 2]) | (f[:, 0] == f[:, 2])).sum()))
+
+
 def sorted_rows(pts, col):
     """Rows of [points | colours] in a canonical order (bit patterns), for set comparison."""
     rows = np.concatenate([pts, col], axis=1).astype(np.float32).view(np.uint32)

@@ -33,3 +33,32 @@ def test_oracle_extract_capacity_and_empty_volume():
     full, col = H.oracle_extract_points(ov)
     assert np.array_equal(full[:10], pts)
     assert (col >= 0).all() and (col <= 1).all()
+
+
+def test_oracle_mesh_is_consistent_and_faces_the_camera_side():
+    """vo_extract_mesh: the vertices are those of vo_extract_points in the same order; every face refers to
+    three distinct existing vertices; no directed edge is used twice (consistent orientation); open edges
+    only along the rim of the observed region; on the sphere the normals point away from its centre
+    (towards positive distance)."""
+    scn = H.make_scenario("tiny", tuple(range(8)), "depth", 45.0)
+    scn["M"], scn["E"] = 32768, 8192   # eight views of the scene
+    ov = H.oracle_volume_for(scn)
+    pts0, col0 = H.oracle_extract_points(ov)
+    pts, col, faces = H.oracle_extract_mesh(ov)
+    assert np.array_equal(pts, pts0) and np.array_equal(col, col0)
+    assert len(faces) > len(pts) and faces.min() >= 0 and faces.max() < len(pts)
+    rep = H.mesh_edge_report(faces)
+    assert rep["degenerate"] == 0 and rep["repeated_directed"] == 0, rep
+    assert rep["boundary"] < 0.08 * rep["edges"], rep
+    tri = pts[faces].astype(np.float64)
+    normal = np.cross(tri[:, 1] - tri[:, 0], tri[:, 2] - tri[:, 0])
+    centre = tri.mean(axis=1)
+    radial = centre - np.array([0.0, 0.0, 2.0])
+    on_sphere = (np.abs(np.linalg.norm(radial, axis=1) - 0.5) < 0.02) & (centre[:, 1] < 0.3)
+    assert on_sphere.sum() > 500
+    assert (np.einsum("ij,ij->i", normal, radial)[on_sphere] > 0).mean() > 0.995   # (a few slivers where fused views disagree)
+    # every vertex is used by some face except on the rim (cubes with an unobserved corner are not meshed)
+    used = np.zeros(len(pts), dtype=bool)
+    used[faces.reshape(-1)] = True
+    assert used.mean() > 0.9
+

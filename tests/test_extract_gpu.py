@@ -36,11 +36,19 @@ def test_points_match_oracle(name, frames, mode, step, tmp_path):
     import vulcan_b200 as vb
     scn = H.make_scenario(name, frames, mode, step)
     vol = _ours_volume(scn)
-    mesh = vb.Extractor(vol).Extract(capacity=1 << 12)   # too small on purpose: Extract grows the buffer
+    mesh = vb.Extractor(vol).Extract(capacity=1 << 12)   # too small on purpose: Extract grows the buffers
     ov = H.oracle_volume_for(scn)
-    pts, col = H.oracle_extract_points(ov)
+    pts, col, faces = H.oracle_extract_mesh(ov)
     assert len(mesh.points) == len(pts) and len(pts) > 1000
     assert np.array_equal(H.sorted_rows(mesh.points, mesh.colors), H.sorted_rows(pts, col))
+    # the triangles: the same oriented triangles as the oracle's, compared by the bits of their corner positions
+    assert len(mesh.faces) == len(faces) and len(faces) > len(pts)
+    assert mesh.faces.min() >= 0 and mesh.faces.max() < len(pts)
+    assert np.array_equal(H.canonical_triangles(mesh.points, mesh.faces), H.canonical_triangles(pts, faces))
+    rep = H.mesh_edge_report(mesh.faces)
+    assert rep["degenerate"] == 0 and rep["repeated_directed"] == 0, rep
+    points_only = vb.Extractor(vol).Extract(faces=False)
+    assert np.array_equal(H.sorted_rows(points_only.points, points_only.colors), H.sorted_rows(pts, col))
     dist = H.sphere_plane_distance(mesh.points)
     footprint = 2.5 / float(scn["K"][0])   # pixel footprint at the scene's depth: the accuracy of the fused TSDF
     assert np.median(dist) < 0.25 * footprint and np.quantile(dist, 0.95) < 1.0 * footprint
@@ -50,10 +58,47 @@ def test_points_match_oracle(name, frames, mode, step, tmp_path):
     vb.Exporter(path).Export(mesh)
     lines = open(path).read().splitlines()
     assert lines[0] == "ply" and lines[2] == "element vertex %d" % len(pts)
-    assert lines[9] == "element face 0" and lines[11] == "end_header"
-    assert len(lines) == 12 + len(pts)
+    assert lines[9] == "element face %d" % len(faces) and lines[11] == "end_header"
+    assert len(lines) == 12 + len(pts) + len(faces)
     x, y, z, r, g, b = lines[12].split()
     assert abs(float(x) - mesh.points[0][0]) < 1e-6 and 0 <= int(r) <= 255
+    assert lines[12 + len(pts)].split() == ["3"] + [str(i) for i in mesh.faces[0]]
+
+
+def test_mesh_of_a_closed_surface_is_watertight():
+    """A sphere written into the voxels of a volume fused from eight sensors around it (every voxel observed):
+    the extracted mesh is CLOSED - every directed edge exactly once, its opposite present - oriented outwards,
+    and encloses the sphere's volume."""
+    import torch
+    import vulcan_b200 as vb
+    scn = H.make_scenario("small", tuple(range(8)), "depth", 45.0)
+    vol = _ours_volume(scn)
+    entries = vol.GetHashEntries().cpu().numpy()
+    alloc = np.nonzero(entries[:, 2] != -1)[0]
+    bx, by, bz = (a.astype(np.float64) for a in __import__("vulcan_b200").sharding.entry_coords(entries[alloc]))
+    data = entries[alloc, 2].astype(np.int64)
+    l, L, tau = scn["voxel"], 8 * scn["voxel"], scn["trunc"]
+    t = np.arange(512)
+    ox, oy, oz = (t & 7) + 0.5, ((t >> 3) & 7) + 0.5, (t >> 6) + 0.5
+    X = bx[:, None] * L + ox[None, :] * l
+    Y = by[:, None] * L + oy[None, :] * l
+    Z = bz[:, None] * L + oz[None, :] * l
+    r = 0.5
+    sdf = np.clip((np.sqrt(X ** 2 + Y ** 2 + (Z - 2.0) ** 2) - r) / tau, -1.0, 1.0).astype(np.float32)
+    vox = vol.GetVoxelsMutable().view(-1, 512, 5)
+    idx = torch.as_tensor(data, device="cuda")
+    words = vox[idx]
+    words[:, :, 0] = torch.from_numpy(sdf.view(np.int32)).cuda()
+    words[:, :, 4] = 1   # distance_weight 1, color_weight 0
+    vox[idx] = words
+    vol.SyncDistances()
+    mesh = vb.Extractor(vol).Extract()
+    assert len(mesh.faces) > 10000
+    rep = H.mesh_edge_report(mesh.faces)
+    assert rep == dict(edges=3 * len(mesh.faces), repeated_directed=0, boundary=0, degenerate=0), rep
+    p = mesh.points[mesh.faces].astype(np.float64) - np.array([0.0, 0.0, 2.0])
+    volume = np.einsum("ij,ij->i", p[:, 0], np.cross(p[:, 1], p[:, 2])).sum() / 6.0
+    assert abs(volume - 4.0 / 3.0 * np.pi * r ** 3) < 0.01 * volume, volume
 
 
 def test_extract_empty_volume():

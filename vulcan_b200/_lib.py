@@ -146,6 +146,7 @@ SYMBOLS = {
     "vk_track_system": [C.POINTER(vkFrame), C.POINTER(vkFrame), _I, _P, _P, _P, _P],
     "vk_track_depth": [C.POINTER(vkFrame), C.POINTER(vkFrame), _I, _I, _P, C.POINTER(_I), C.POINTER(_F), _P],
     "vk_extract_points": [C.POINTER(vkVolume), _P, _P, _I, _P, _P],
+    "vk_extract_mesh": [C.POINTER(vkVolume), _P, _P, _I, _P, _P, _I, _P, _P],
     "vk_version": [],
     "vk_set_default_math_mode": [_I],
     "vk_get_default_math_mode": [],

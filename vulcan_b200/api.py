@@ -639,8 +639,9 @@ class Mesh:
 
 class Extractor:
     """Extractor (include/vulcan/extractor.h, src/extractor.cu:660-740).  The reference's extractor is
-    unfinished (edge midpoints of one block, no faces); this one returns the marching-cubes vertices of
-    the whole volume (vk_extract_points) and, like the reference today, no faces."""
+    unfinished (edge midpoints of one block; its index and face kernels are empty): this one returns the
+    marching-cubes mesh of the whole volume - interpolated vertices with colours (vk_extract_points) and
+    triangles over them (vk_extract_mesh)."""
 
     def __init__(self, volume):
         self.volume_ = volume
@@ -648,21 +649,27 @@ class Extractor:
     def GetVolume(self):
         return self.volume_
 
-    def Extract(self, mesh=None, capacity=1 << 20):
+    def Extract(self, mesh=None, capacity=1 << 20, faces=True):
         mesh = mesh if mesh is not None else Mesh()
+        fcap = 2 * capacity
         while True:
             pts = torch.empty((capacity, 3), dtype=torch.float32, device="cuda")
             col = torch.empty((capacity, 3), dtype=torch.float32, device="cuda")
-            cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
-            check(lib.vk_extract_points(C.byref(self.volume_._v), pts.data_ptr(), col.data_ptr(), capacity,
-                                        cnt.data_ptr(), _stream()), "Extract")
-            n = int(cnt.item())
-            if n <= capacity:
+            cnt = torch.zeros(2, dtype=torch.int32, device="cuda")
+            if faces:
+                tri = torch.empty((fcap, 3), dtype=torch.int32, device="cuda")
+                check(lib.vk_extract_mesh(C.byref(self.volume_._v), pts.data_ptr(), col.data_ptr(), capacity,
+                                          cnt.data_ptr(), tri.data_ptr(), fcap, cnt[1:].data_ptr(), _stream()), "Extract")
+            else:
+                check(lib.vk_extract_points(C.byref(self.volume_._v), pts.data_ptr(), col.data_ptr(), capacity,
+                                            cnt.data_ptr(), _stream()), "Extract")
+            n, nf = (int(x) for x in cnt.tolist())
+            if n <= capacity and nf <= fcap:
                 break
-            capacity = n
+            capacity, fcap = max(capacity, n), max(fcap, nf)
         mesh.points = pts[:n].cpu().numpy()
         mesh.colors = col[:n].cpu().numpy()
-        mesh.faces = np.zeros((0, 3), dtype=np.int32)
+        mesh.faces = tri[:nf].cpu().numpy() if faces else np.zeros((0, 3), dtype=np.int32)
         return mesh
 
 
@@ -688,4 +695,4 @@ class Exporter:
             for p, c in zip(mesh.points, rgb):
                 f.write("%.9g %.9g %.9g %d %d %d\n" % (p[0], p[1], p[2], c[0], c[1], c[2]))
             for t in mesh.faces:
-                f.write("3 %d %d %d\n" % (t[0], t[1], t[2]))
+                f.write("3 %d %d %d\n" % (t[0], t[1], t[2]))   # src/exporter.cpp:63-69

@@ -19,6 +19,7 @@
 #include <cuda_runtime.h>
 #include "vk_launch.h"
 #include "vk_math.cuh"
+#include "vk_mc_tables.h"
 
 namespace vk {
 
@@ -34,6 +35,14 @@ struct ExtractParams {
   int capacity;
   int* count;
   int chunk;  // hash entries a CTA lists at a time (<= kExtractChunkMax)
+  // mesh extraction (vk_extract_mesh): every block gets a slot, every lattice edge of the block the index of
+  // its vertex (or -1) at edge_index[slot * 1536 + voxel * 3 + axis]; all NULL for points only
+  int* block_slot;     // [M + E] slot of voxel block `data`
+  int* slot_counter;
+  int* edge_index;
+  int* faces;          // faces kernel: vertex index triples
+  int face_capacity;
+  int* face_count;
 };
 
 __device__ __forceinline__ int extract_lookup(const ExtractParams& p, int bx, int by, int bz) {
@@ -54,6 +63,7 @@ __global__ void __launch_bounds__(512, 3) vk_extract_points_kernel(ExtractParams
   __shared__ int list_count;
   __shared__ int warp_totals[16];
   __shared__ int block_base;
+  __shared__ int block_slot_s;
   const int tid = threadIdx.x;
   const int vx = tid & 7, vy = (tid >> 3) & 7, vz = tid >> 6;
   const int chunks = (p.total_entries + p.chunk - 1) / p.chunk;
@@ -148,9 +158,19 @@ __global__ void __launch_bounds__(512, 3) vk_extract_points_kernel(ExtractParams
         }
         if (tid < 16) warp_totals[tid] = wi - wt;  // exclusive offset of the warp
         if (tid == 15) block_base = wi ? atomicAdd(p.count, wi) : 0;
+        if (tid == 0 && p.edge_index) {
+          block_slot_s = atomicAdd(p.slot_counter, 1);
+          p.block_slot[e.z] = block_slot_s;
+        }
       }
       __syncthreads();
       int at = block_base + warp_totals[tid >> 5] + incl - mine;
+      if (p.edge_index) {   // vertex index of each of the voxel's three lattice edges, for the faces
+        int* row = p.edge_index + ((size_t)block_slot_s * VK_BLOCK_VOXELS + tid) * 3;
+        int k = at;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) row[a] = ((mask >> a) & 1u) ? k++ : -1;
+      }
 #pragma unroll
       for (int a = 0; a < 3; ++a) {
         if (!((mask >> a) & 1u)) continue;
@@ -166,6 +186,124 @@ __global__ void __launch_bounds__(512, 3) vk_extract_points_kernel(ExtractParams
           }
         }
         ++at;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- triangles (what the reference's empty ExtractVertexIndicesKernel / ExtractFacesKernel,
+// src/extractor.cu:392-413, leave open) ----------------------------------------------------------------------
+// One marching-cubes cube per voxel: the cube spanned by the voxel and its +x / +y / +z neighbours (corner c at
+// offset (c & 1, (c >> 1) & 1, c >> 2)), across block faces.  A cube is meshed when all eight corners are
+// observed (distance_weight > 0); its case index has bit c set where !(distance > 0) - the sign test of the
+// vertices - and kMcTriTable (generated, tools/gen_mc_tables.py) lists its triangles as cube-edge triples.
+// Every cube edge is the lattice edge some voxel owns, so a triangle corner is just the vertex index
+// vk_extract_points_kernel left in edge_index for (owner voxel, axis): vertices are shared between cubes and
+// blocks by construction, and the mesh is watertight wherever the surface is surrounded by observed voxels.
+__constant__ signed char c_tri_table[256][16];
+__constant__ signed char c_edge_corner[12];
+__constant__ signed char c_edge_axis[12];
+
+__global__ void __launch_bounds__(512, 3) vk_extract_faces_kernel(ExtractParams p) {
+  __shared__ float s_dist[VK_BLOCK_VOXELS];
+  __shared__ short s_weight[VK_BLOCK_VOXELS];
+  __shared__ int list[kExtractChunkMax];
+  __shared__ int list_count;
+  __shared__ int nb_data[8], nb_slot[8];   // the block (index 0) and its seven +x / +y / +z neighbours
+  __shared__ int warp_totals[16];
+  __shared__ int block_base;
+  const int tid = threadIdx.x;
+  const int vx = tid & 7, vy = (tid >> 3) & 7, vz = tid >> 6;
+  const int chunks = (p.total_entries + p.chunk - 1) / p.chunk;
+  for (int chunk = blockIdx.x; chunk < chunks; chunk += gridDim.x) {
+    if (tid == 0) list_count = 0;
+    __syncthreads();
+    const int ei = chunk * p.chunk + tid;
+    if (tid < p.chunk && ei < p.total_entries && __ldg(&p.entries[ei].data) != -1) list[atomicAdd(&list_count, 1)] = ei;
+    __syncthreads();
+    const int n = list_count;
+    for (int li = 0; li < n; ++li) {
+      const int4 e = ld_entry(p.entries + list[li]);
+      int bx, by, bz;
+      entry_origin(e, bx, by, bz);
+      __syncthreads();  // the previous block's tile is no longer read
+      {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(p.voxels + (size_t)e.z * VK_BLOCK_VOXELS) + 5 * tid;
+        s_dist[tid] = __uint_as_float(__ldg(src));
+        s_weight[tid] = (short)(__ldg(src + 4) & 0xffffu);
+      }
+      if (tid < 8) {
+        const int d = (tid == 0) ? e.z : extract_lookup(p, bx + (tid & 1), by + ((tid >> 1) & 1), bz + (tid >> 2));
+        nb_data[tid] = d;
+        nb_slot[tid] = (d >= 0) ? p.block_slot[d] : -1;
+      }
+      __syncthreads();
+      // the eight corners
+      unsigned cube = 0;
+      bool ok = true;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const int x = vx + (c & 1), y = vy + ((c >> 1) & 1), z = vz + (c >> 2);
+        float d;
+        int w;
+        if (x < 8 && y < 8 && z < 8) {
+          const int j = (z << 6) | (y << 3) | x;
+          d = s_dist[j];
+          w = s_weight[j];
+        } else {
+          const int nb = nb_data[(x >> 3) | ((y >> 3) << 1) | ((z >> 3) << 2)];
+          if (nb < 0) { ok = false; d = 1.f; w = 0; }
+          else {
+            const vkVoxel* q = p.voxels + (size_t)nb * VK_BLOCK_VOXELS + (((z & 7) << 6) | ((y & 7) << 3) | (x & 7));
+            d = __ldg(&q->distance);
+            w = (int)__ldg(&q->distance_weight);
+          }
+        }
+        if (w <= 0) ok = false;
+        if (!(d > 0)) cube |= 1u << c;
+      }
+      if (!ok) cube = 0;
+      int mine = 0;
+      while (mine < 5 && c_tri_table[cube][3 * mine] >= 0) ++mine;
+      // one atomicAdd per block: exclusive scan of the per-thread triangle counts over the CTA
+      int incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += up;
+      }
+      if ((tid & 31) == 31) warp_totals[tid >> 5] = incl;
+      __syncthreads();
+      if (tid < 32) {
+        int wt = tid < 16 ? warp_totals[tid] : 0;
+        int wi = wt;
+#pragma unroll
+        for (int o = 1; o < 16; o <<= 1) {
+          const int up = __shfl_up_sync(0xffffffffu, wi, o);
+          if (tid >= o) wi += up;
+        }
+        if (tid < 16) warp_totals[tid] = wi - wt;
+        if (tid == 15) block_base = wi ? atomicAdd(p.face_count, wi) : 0;
+      }
+      __syncthreads();
+      int at = block_base + warp_totals[tid >> 5] + incl - mine;
+      for (int k = 0; k < mine; ++k, ++at) {
+        int ids[3];
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const int edge = c_tri_table[cube][3 * k + j];
+          const int corner = c_edge_corner[edge], axis = c_edge_axis[edge];
+          const int x = vx + (corner & 1), y = vy + ((corner >> 1) & 1), z = vz + (corner >> 2);
+          const int slot = nb_slot[(x >> 3) | ((y >> 3) << 1) | ((z >> 3) << 2)];
+          const int voxel = ((z & 7) << 6) | ((y & 7) << 3) | (x & 7);
+          ids[j] = __ldg(p.edge_index + ((size_t)slot * VK_BLOCK_VOXELS + voxel) * 3 + axis);
+        }
+        if (at < p.face_capacity) {
+          p.faces[3 * (size_t)at] = ids[0];
+          p.faces[3 * (size_t)at + 1] = ids[1];
+          p.faces[3 * (size_t)at + 2] = ids[2];
+        }
       }
     }
     __syncthreads();
@@ -196,10 +334,75 @@ extern "C" int vk_extract_points(const vkVolume* v, float* points, float* colors
   p.colors = colors;
   p.capacity = capacity;
   p.count = count;
+  p.block_slot = nullptr; p.slot_counter = nullptr; p.edge_index = nullptr;
+  p.faces = nullptr; p.face_capacity = 0; p.face_count = nullptr;
   p.chunk = 16;  // measured on config 1 (33.6 k blocks): 128 -> 0.77 ms, 64 -> 0.58, 32 -> 0.49, 16 -> 0.47, 8 -> 0.50
   const int chunks = (p.total_entries + p.chunk - 1) / p.chunk;
   const int cap = 3 * sm_count();  // three 512-thread CTAs per SM are resident
   vk_extract_points_kernel<<<chunks < cap ? chunks : cap, 512, 0, s>>>(p);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
+}
+
+extern "C" int vk_extract_mesh(const vkVolume* v, float* points, float* colors, int point_capacity, int* point_count,
+                               int* faces, int face_capacity, int* face_count, void* stream) {
+  if (!v || !v->voxels || !points || !point_count || !faces || !face_count || point_capacity < 0 || face_capacity < 0)
+    return VK_E_INVALID;
+  if (v->shard_count > 1) return VK_E_INVALID;   // see vk_extract_points
+  cudaStream_t s = (cudaStream_t)stream;
+  static bool tables_loaded = false;   // per process; the tables are generated (tools/gen_mc_tables.py)
+  if (!tables_loaded) {
+    cudaError_t te = cudaMemcpyToSymbol(c_tri_table, kMcTriTable, sizeof(kMcTriTable));
+    if (te == cudaSuccess) te = cudaMemcpyToSymbol(c_edge_corner, kMcEdgeCorner, sizeof(kMcEdgeCorner));
+    if (te == cudaSuccess) te = cudaMemcpyToSymbol(c_edge_axis, kMcEdgeAxis, sizeof(kMcEdgeAxis));
+    if (te != cudaSuccess) return (int)te;
+    tables_loaded = true;
+  }
+  // blocks in use -> size of the per-edge vertex index table (6 KB per block)
+  int allocated = 0;
+  cudaError_t err = cudaMemcpyAsync(&allocated, v->counters + VK_CNT_ALLOCATED, sizeof(int), cudaMemcpyDeviceToHost, s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return (int)err;
+  const size_t B = (size_t)v->main_blocks + (size_t)v->excess_blocks;
+  int *block_slot = nullptr, *slot_counter = nullptr, *edge_index = nullptr;
+  err = cudaMalloc((void**)&block_slot, (B + 1) * sizeof(int));
+  if (err == cudaSuccess) err = cudaMalloc((void**)&edge_index, ((size_t)allocated + 1) * VK_BLOCK_VOXELS * 3 * sizeof(int));
+  int rc = 0;
+  if (err == cudaSuccess) {
+    slot_counter = block_slot + B;
+    err = cudaMemsetAsync(slot_counter, 0, sizeof(int), s);
+    if (err == cudaSuccess) err = cudaMemsetAsync(point_count, 0, sizeof(int), s);
+    if (err == cudaSuccess) err = cudaMemsetAsync(face_count, 0, sizeof(int), s);
+  }
+  if (err == cudaSuccess) {
+    ExtractParams p;
+    p.entries = (const vkHashEntry*)v->entries;
+    p.voxels = (const vkVoxel*)v->voxels;
+    p.total_entries = v->main_blocks + v->excess_blocks;
+    p.K = make_mod((uint32_t)v->main_blocks);
+    p.voxel_length = v->voxel_length;
+    p.block_length = VK_BLOCK_RES * v->voxel_length;
+    p.points = points;
+    p.colors = colors;
+    p.capacity = point_capacity;
+    p.count = point_count;
+    p.block_slot = block_slot;
+    p.slot_counter = slot_counter;
+    p.edge_index = edge_index;
+    p.faces = faces;
+    p.face_capacity = face_capacity;
+    p.face_count = face_count;
+    p.chunk = 16;
+    const int chunks = (p.total_entries + p.chunk - 1) / p.chunk;
+    const int cap = 3 * sm_count();
+    vk_extract_points_kernel<<<chunks < cap ? chunks : cap, 512, 0, s>>>(p);
+    VK_COUNT_LAUNCH();
+    vk_extract_faces_kernel<<<chunks < cap ? chunks : cap, 512, 0, s>>>(p);
+    VK_COUNT_LAUNCH();
+    err = cudaGetLastError();
+    if (err == cudaSuccess) err = cudaStreamSynchronize(s);   // the workspace is freed below
+  }
+  cudaFree(block_slot);
+  cudaFree(edge_index);
+  return rc ? rc : (int)err;
 }

@@ -223,26 +223,32 @@ Extractor::Extractor(std::shared_ptr<const Volume> volume) : volume_(volume)
 
 void Extractor::Extract(DeviceMesh& mesh) const
 {
-  Buffer<int> count(1);
+  // vertices (zero crossings on the lattice edges) and marching-cubes faces over them; the kernels count on
+  // past the capacities, so a second round with room for all follows when the first guess was too small
+  Buffer<int> count(2);
   size_t capacity = mesh.points.GetSize() > 0 ? mesh.points.GetSize() : (size_t)1 << 20;
+  size_t face_capacity = mesh.faces.GetSize() > 0 ? mesh.faces.GetSize() : 2 * capacity;
   for (;;)
   {
     mesh.points.Resize(capacity);
     mesh.colors.Resize(capacity);
-    VK_ASSERT(vk_extract_points(volume_->GetHandle(), reinterpret_cast<float*>(mesh.points.GetData()),
-                                reinterpret_cast<float*>(mesh.colors.GetData()), (int)capacity, count.GetData(),
-                                nullptr));
-    int found = 0;
-    count.CopyToHost(&found);
-    if ((size_t)found <= capacity)
+    mesh.faces.Resize(face_capacity);
+    VK_ASSERT(vk_extract_mesh(volume_->GetHandle(), reinterpret_cast<float*>(mesh.points.GetData()),
+                              reinterpret_cast<float*>(mesh.colors.GetData()), (int)capacity, count.GetData(),
+                              reinterpret_cast<int*>(mesh.faces.GetData()), (int)face_capacity, count.GetData() + 1,
+                              volume_->GetStream()));
+    int found[2] = {0, 0};
+    count.CopyToHost(found);
+    if ((size_t)found[0] <= capacity && (size_t)found[1] <= face_capacity)
     {
-      mesh.points.Resize(found);
-      mesh.colors.Resize(found);
+      mesh.points.Resize(found[0]);
+      mesh.colors.Resize(found[0]);
+      mesh.faces.Resize(found[1]);
       break;
     }
-    capacity = found;  // the kernel counted on: run again with room for all
+    if ((size_t)found[0] > capacity) capacity = found[0];
+    if ((size_t)found[1] > face_capacity) face_capacity = found[1];
   }
-  mesh.faces.Resize(0);
 }
 
 void Extractor::Extract(Mesh& mesh) const
@@ -251,12 +257,13 @@ void Extractor::Extract(Mesh& mesh) const
   Extract(device);
   mesh.points.resize(device.points.GetSize());
   mesh.colors.resize(device.colors.GetSize());
-  mesh.faces.clear();
+  mesh.faces.resize(device.faces.GetSize());
   if (!mesh.points.empty())
   {
     device.points.CopyToHost(mesh.points.data());
     device.colors.CopyToHost(mesh.colors.data());
   }
+  if (!mesh.faces.empty()) device.faces.CopyToHost(mesh.faces.data());
 }
 
 Exporter::Exporter(const std::string& file) : file_(file) {}
