@@ -75,7 +75,8 @@ def test_mesh_of_a_closed_surface_is_watertight():
     vol = _ours_volume(scn)
     entries = vol.GetHashEntries().cpu().numpy()
     alloc = np.nonzero(entries[:, 2] != -1)[0]
-    bx, by, bz = (a.astype(np.float64) for a in __import__("vulcan_b200").sharding.entry_coords(entries[alloc]))
+    from vulcan_b200 import sharding
+    bx, by, bz = (a.astype(np.float64) for a in sharding.entry_coords(entries[alloc]))
     data = entries[alloc, 2].astype(np.int64)
     l, L, tau = scn["voxel"], 8 * scn["voxel"], scn["trunc"]
     t = np.arange(512)
