@@ -314,41 +314,6 @@ int vk_ipc_export(const vkVolume* v, vkIpcHandles* out);
 int vk_ipc_open(const vkIpcHandles* handles, const vkHashEntry** entries, const vkVoxel** voxels, const float** sdf);
 int vk_ipc_close(const vkHashEntry* entries, const vkVoxel* voxels, const float* sdf);
 
-/* Exchange of the rendered bands without a library collective.  Every rank owns one "exchange
- * buffer" (vk_exchange_alloc: room for the full-size depth + colour + normal images of a view and
- * VK_MAX_SHARDS arrival flags), maps the buffers of its peers (vk_exchange_export / _open, CUDA
- * IPC) and renders its band INTO ITS OWN buffer (pass vk_exchange_depth/_color/_normal of it to
- * vk_trace_rows).  vk_exchange_bands then (1) stores `epoch` into this rank's flag in every
- * peer's buffer (release, system scope), (2) waits until all peers' flags in the local buffer
- * have reached `epoch`, (3) copies every peer's band out of that peer's buffer into the caller's
- * images over NVLink.  `epoch` must grow by one per call on all ranks.  A band may be overwritten
- * by its owner only after all ranks have passed a later collective (the bounds all-reduce of the
- * next view does that). */
-typedef struct vkExchange {
-  int32_t count, rank;                 /* ranks, this rank                                  */
-  int32_t width, height;               /* image size the buffers were allocated for         */
-  void*   buffers[VK_MAX_SHARDS];      /* exchange buffer of every rank (own one included)  */
-  int32_t row_begin[VK_MAX_SHARDS];    /* band of rank r: rows [row_begin[r], row_end[r])   */
-  int32_t row_end[VK_MAX_SHARDS];
-} vkExchange;
-
-int vk_exchange_alloc(int width, int height, void** buffer);
-int vk_exchange_free(void* buffer);
-int vk_exchange_export(const void* buffer, unsigned char handle[64]);
-int vk_exchange_open(const unsigned char handle[64], void** buffer);
-int vk_exchange_close(void* buffer);
-float* vk_exchange_depth(void* buffer, int width, int height);
-float* vk_exchange_color(void* buffer, int width, int height);
-float* vk_exchange_normal(void* buffer, int width, int height);
-int vk_exchange_bands(const vkExchange* x, int epoch, float* out_depth, float* out_color, float* out_normal,
-                      void* stream);
-/* The ray-bounds grids of vk_trace_bounds combined the same way (instead of a MIN all-reduce):
- * every rank stores its 80 x 60 x 2 grid into its slot of every rank's exchange buffer, announces
- * it, waits for the others and leaves the element-wise minimum of all grids in `bounds`.  It is
- * also the barrier that orders every rank's integration before any rank's peer reads.  `epoch`
- * as for vk_exchange_bands (the two calls keep separate flags; use the same counter for both). */
-int vk_exchange_bounds(const vkExchange* x, int epoch, float* bounds, void* stream);
-
 /* ---- block-sharded volume with replicated lookup structures (the multi-GPU mode of bench.py) --------
  *
  * A rank stores, allocates and integrates exactly the blocks it owns (10 KB of voxels each).  What the

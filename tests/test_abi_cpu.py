@@ -45,7 +45,7 @@ def test_struct_layouts_match_header(tmp_path):
                  "int main(void) { printf(\"%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n\", sizeof(vkVoxel), sizeof(vkHashEntry),"
                  " sizeof(vkPatch), sizeof(vkTransform), sizeof(vkProjection), sizeof(vkLight), sizeof(vkVolume),"
                  " sizeof(vkFrame), offsetof(vkVolume, math_mode), offsetof(vkFrame, depth_to_color),"
-                 " sizeof(vkPeerTable), sizeof(vkExchange), offsetof(vkExchange, row_begin), sizeof(vkIpcHandles));"
+                 " sizeof(vkPeerTable), sizeof(vkShard), offsetof(vkShard, push_entries), sizeof(vkIpcHandles));"
                  " return 0; }\n")
     exe = tmp_path / "layout"
     subprocess.check_call(["gcc", "-I", os.path.join(H.ROOT, "include"), "-o", str(exe), str(c)])
@@ -54,8 +54,8 @@ def test_struct_layouts_match_header(tmp_path):
     assert got[:6] == [20, 16, 16, 128, 16, 16]   # Appendix B of SURVEY.md: the reference's value types
     assert got[6] == C.sizeof(L.vkVolume) and got[7] == C.sizeof(L.vkFrame)
     assert got[8] == L.vkVolume.math_mode.offset and got[9] == L.vkFrame.depth_to_color.offset
-    assert got[10] == C.sizeof(L.vkPeerTable) and got[11] == C.sizeof(L.vkExchange)
-    assert got[12] == L.vkExchange.row_begin.offset and got[13] == C.sizeof(L.vkIpcHandles) == 192
+    assert got[10] == C.sizeof(L.vkPeerTable) and got[11] == C.sizeof(L.vkShard)
+    assert got[12] == L.vkShard.push_entries.offset and got[13] == C.sizeof(L.vkIpcHandles) == 192
 
 
 def test_no_device_is_an_error_not_a_fallback():

@@ -72,11 +72,6 @@ class vkIpcHandles(C.Structure):
     _fields_ = [("entries", C.c_ubyte * 64), ("voxels", C.c_ubyte * 64), ("sdf", C.c_ubyte * 64)]
 
 
-class vkExchange(C.Structure):
-    _fields_ = [("count", C.c_int32), ("rank", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
-                ("buffers", C.c_void_p * 8), ("row_begin", C.c_int32 * 8), ("row_end", C.c_int32 * 8)]
-
-
 class vkFrame(C.Structure):
     _fields_ = [
         ("depth", C.c_void_p), ("color", C.c_void_p), ("normal", C.c_void_p),
@@ -119,16 +114,6 @@ SYMBOLS = {
     "vk_ipc_export": [C.POINTER(vkVolume), C.POINTER(vkIpcHandles)],
     "vk_ipc_open": [C.POINTER(vkIpcHandles), C.POINTER(_P), C.POINTER(_P), C.POINTER(_P)],
     "vk_ipc_close": [_P, _P, _P],
-    "vk_exchange_alloc": [_I, _I, C.POINTER(_P)],
-    "vk_exchange_free": [_P],
-    "vk_exchange_export": [_P, C.c_char_p],
-    "vk_exchange_open": [C.c_char_p, C.POINTER(_P)],
-    "vk_exchange_close": [_P],
-    "vk_exchange_depth": [_P, _I, _I],
-    "vk_exchange_color": [_P, _I, _I],
-    "vk_exchange_normal": [_P, _I, _I],
-    "vk_exchange_bands": [C.POINTER(vkExchange), _I, _P, _P, _P, _P],
-    "vk_exchange_bounds": [C.POINTER(vkExchange), _I, _P, _P],
     "vk_shard_create": [C.POINTER(vkShard), C.POINTER(vkVolume), _I, _I, _I, _I, _I, _P],
     "vk_shard_export": [C.POINTER(vkShard), C.POINTER(vkVolume), C.POINTER(vkShardHandles)],
     "vk_shard_connect": [C.POINTER(vkShard), C.POINTER(vkShardHandles)],
@@ -165,7 +150,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the library does not export it
         fn.argtypes = argtypes
         fn.restype = (C.c_ulonglong if name == "vk_launch_count" else
-                      C.c_void_p if name in ("vk_exchange_depth", "vk_exchange_color", "vk_exchange_normal") else C.c_int)
+                      C.c_int)
     return lib
 
 

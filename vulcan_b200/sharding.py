@@ -2,15 +2,19 @@
 SURVEY.md 5.8 / 8e).
 
 Partition: a rank owns the blocks whose brick (block coordinates >> shift) hashes to it
-(vk_shard_owner in include/vulcan_b200.h) and stores exactly those, so allocation and integration
-need no exchange and each rank does 1/N of the work.  Ray casting is where the ranks meet:
+(vk_shard_owner in include/vulcan_b200.h) and stores, allocates and integrates exactly those, so
+allocation and integration need no exchange and each rank does 1/N of that work.  Ray casting is where
+the ranks meet:
 
-  ShardedTracer (exact)   every rank renders a band of image rows; a block outside the local shard is
-      read from its owner's hash table and voxel pool through peer memory (CUDA IPC mappings over
-      NVLink / NVSwitch), so each ray takes exactly the steps of the unsharded march.  Collectives per
-      view: one NCCL MIN all-reduce of the 80 x 60 ray-bounds grid (38 KB; also the barrier between
-      every rank's integration and any rank's peer reads); the image bands are then swapped by one
-      kernel per rank over peer memory (vk_exchange_bands: flag handshake + NVLink copies).
+  Shard (exact, the mode of bench.py)   the owner's allocation / integration kernels store every hash entry
+      and every changed 16-byte piece of block distances into all ranks' copies as they write their own
+      (plain stores into peer memory over NVLink / NVSwitch); every rank then ray-casts a band of image
+      rows from LOCAL memory only - each ray takes exactly the steps of the unsharded march - and stores
+      its band into its peers' images.  Two flag handshakes over peer memory per view, no library
+      collective (vk_trace_sharded, include/vulcan_b200.h).
+  peer table (exact, no replication)   Tracer.TraceRows with a vkPeerTable: a block outside the local shard
+      is read from its owner's tables through peer memory (vk_trace_rows); the long rays' chains of
+      dependent look-ups then cross NVLink, which is why the replicated mode replaced it.
   key merge (approximate)  every rank ray-casts its own shard into 64-bit keys (depth bits << 32 |
       rgb8 << 8 | rank, +inf for "no owned hit") and a MIN all-reduce leaves the nearest hit per
       pixel.  No peer mappings needed, but rays step differently where their blocks live on another
@@ -214,120 +218,3 @@ class Shard:
         if getattr(self, "_alive", False):
             _lib.lib.vk_shard_destroy(C.byref(self._s), C.byref(self.volume._v))
             self._alive = False
-
-
-class ShardedTracer:
-    """Tracer of a block-sharded volume, one instance per rank (process)."""
-
-    def __init__(self, volume, group=None):
-        import ctypes as C
-        import torch.distributed as dist
-        from . import _lib, api
-        self.volume, self.group = volume, group
-        self.use_nccl_bounds = False   # True: combine the ray-bounds grids with an NCCL all-reduce instead
-        self.tracer = api.Tracer(volume)
-        self.rank, self.count = dist.get_rank(group), dist.get_world_size(group)
-        assert volume._v.shard_rank == self.rank and volume._v.shard_count == self.count, "call Volume.SetSharding first"
-        mine = _lib.vkIpcHandles()
-        api.check(_lib.lib.vk_ipc_export(C.byref(volume._v), C.byref(mine)), "vk_ipc_export")
-        blobs = [None] * self.count
-        dist.all_gather_object(blobs, bytes(mine), group=group)
-        entries, voxels, sdf = [], [], []
-        self._opened = []
-        for r, blob in enumerate(blobs):
-            if r == self.rank:
-                entries.append(volume._v.entries)
-                voxels.append(volume._v.voxels)
-                sdf.append(volume._v.sdf)
-                continue
-            h = _lib.vkIpcHandles.from_buffer_copy(blob)
-            e, v, d = C.c_void_p(), C.c_void_p(), C.c_void_p()
-            api.check(_lib.lib.vk_ipc_open(C.byref(h), C.byref(e), C.byref(v), C.byref(d)), "vk_ipc_open")
-            self._opened.append((e.value, v.value, d.value))
-            entries.append(e.value)
-            voxels.append(v.value)
-            sdf.append(d.value)
-        self.peers = peer_table(self.rank, entries, voxels, sdf)
-
-    def close(self):
-        from . import _lib
-        for e, v, d in self._opened:
-            _lib.lib.vk_ipc_close(e, v, d)
-        self._opened = []
-        self._drop_exchange()
-
-    def _drop_exchange(self):
-        from . import _lib
-        x = getattr(self, "_exchange", None)
-        if x is None:
-            return
-        for r in range(self.count):
-            if r != self.rank and x["buffers"][r]:
-                _lib.lib.vk_exchange_close(x["buffers"][r])
-        _lib.lib.vk_exchange_free(x["buffers"][self.rank])
-        self._exchange = None
-
-    def _ensure_exchange(self, h, w):
-        """Exchange buffers for h x w images (collective: every rank calls it with the same size)."""
-        import ctypes as C
-        import torch.distributed as dist
-        from . import _lib, api
-        x = getattr(self, "_exchange", None)
-        if x is not None and x["size"] == (h, w):
-            return x
-        self._drop_exchange()
-        mine = C.c_void_p()
-        api.check(_lib.lib.vk_exchange_alloc(w, h, C.byref(mine)), "vk_exchange_alloc")
-        handle = C.create_string_buffer(64)
-        api.check(_lib.lib.vk_exchange_export(mine, handle), "vk_exchange_export")
-        blobs = [None] * self.count
-        dist.all_gather_object(blobs, handle.raw, group=self.group)
-        buffers = []
-        for r, blob in enumerate(blobs):
-            if r == self.rank:
-                buffers.append(mine.value)
-                continue
-            p = C.c_void_p()
-            api.check(_lib.lib.vk_exchange_open(C.create_string_buffer(blob, 64), C.byref(p)), "vk_exchange_open")
-            buffers.append(p.value)
-        desc = _lib.vkExchange()
-        desc.count, desc.rank, desc.width, desc.height = self.count, self.rank, w, h
-        for r in range(self.count):
-            desc.buffers[r] = buffers[r]
-            desc.row_begin[r], desc.row_end[r] = row_band(h, r, self.count)
-        lib = _lib.lib
-        x = dict(size=(h, w), buffers=buffers, desc=desc, epoch=0,
-                 depth=lib.vk_exchange_depth(mine, w, h), color=lib.vk_exchange_color(mine, w, h),
-                 normal=lib.vk_exchange_normal(mine, w, h))
-        self._exchange = x
-        return x
-
-    def Trace(self, frame):
-        """Fills frame.depth_image / color_image / normal_image on every rank (all bands gathered).
-        Per view: the ray-bounds grids (38 KB) combined over peer memory (vk_exchange_bounds; also the
-        barrier between every rank's integration and any rank's peer reads), the band of this rank
-        rendered into its exchange buffer, and one kernel that swaps the bands over peer memory.
-        No library collective on the per-frame path."""
-        import ctypes as C
-        import torch.distributed as dist
-        from . import _lib, api
-        t = self.tracer
-        t._ensure_outputs(frame)
-        h, w = frame.depth_image.shape
-        x = self._ensure_exchange(h, w)
-        t.TraceBounds(frame)
-        x["epoch"] += 1
-        # cells are (min depth, -max depth): ONE element-wise minimum over the ranks combines both
-        if self.use_nccl_bounds:
-            dist.all_reduce(t.bounds_, op=dist.ReduceOp.MIN, group=self.group)
-        else:
-            api.check(_lib.lib.vk_exchange_bounds(C.byref(x["desc"]), x["epoch"], t.bounds_.data_ptr(), api._stream()),
-                      "vk_exchange_bounds")
-        y0, y1 = row_band(h, self.rank, self.count)
-        f = frame.to_c()
-        v = self.volume
-        api.check(_lib.lib.vk_trace_rows(C.byref(v._v), C.byref(self.peers), C.byref(f), t.bounds_.data_ptr(), y0, y1,
-                                         x["depth"], x["color"], x["normal"], api._stream()), "TraceRows")
-        api.check(_lib.lib.vk_exchange_bands(C.byref(x["desc"]), x["epoch"], frame.depth_image.data_ptr(),
-                                             frame.color_image.data_ptr(), frame.normal_image.data_ptr(),
-                                             api._stream()), "vk_exchange_bands")
