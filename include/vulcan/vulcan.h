@@ -23,6 +23,7 @@
 #include <vulcan/mesh.h>
 #include <vulcan/projection.h>
 #include <vulcan/pyramid_tracker.h>
+#include <vulcan/sharded_tracer.h>
 #include <vulcan/tracer.h>
 #include <vulcan/tracer.cuh>
 #include <vulcan/tracker.h>

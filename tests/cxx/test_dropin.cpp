@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -526,6 +527,88 @@ static void TestFramePipeline()
   for (float* p : depths) FramePipeline::FreeHost(p);
 }
 
+// ShardedTracer (addition): two ranks of a block-sharded volume in this process (one GPU plays both, so the
+// collective runs in its three parts) must trace exactly the images of an unsharded volume.
+static void TestShardedTracer()
+{
+  const int w = 160, h = 120, frames = 3;
+  Projection projection;
+  projection.SetFocalLength(80, 80);
+  projection.SetCenterPoint(80, 60);
+  auto depth_of = [&](int k)
+  {
+    std::vector<float> host((size_t)w * h);
+    for (size_t i = 0; i < host.size(); ++i) host[i] = 1.4f + 0.02f * k + 0.001f * (float)(i % w) + 0.0007f * (float)(i / w);
+    auto image = std::make_shared<Image>(w, h);
+    image->CopyFromHost(host.data());
+    return image;
+  };
+  auto configure = [](std::shared_ptr<Volume> v)
+  {
+    v->SetVoxelLength(0.008f);
+    v->SetTruncationLength(0.04f);
+  };
+  auto whole = std::make_shared<Volume>(8192, 2048);
+  configure(whole);
+  DepthIntegrator whole_integrator(whole);
+  Tracer whole_tracer(whole);
+  std::vector<std::shared_ptr<Volume>> volumes;
+  std::vector<std::unique_ptr<DepthIntegrator>> integrators;
+  std::vector<std::unique_ptr<ShardedTracer>> tracers;
+  for (int r = 0; r < 2; ++r)
+  {
+    volumes.push_back(std::make_shared<Volume>(8192, 2048));
+    configure(volumes[r]);
+    tracers.emplace_back(new ShardedTracer(volumes[r], r, 2, w, h, 1));
+    integrators.emplace_back(new DepthIntegrator(volumes[r]));
+  }
+  ShardedTracer::ConnectLocal({tracers[0].get(), tracers[1].get()});
+  const size_t n = (size_t)w * h;
+  for (int k = 0; k < frames; ++k)
+  {
+    Frame f;
+    f.depth_projection = projection;
+    f.depth_to_world_transform = Transform::Translate(0.31f + 0.01f * k, 0.27f, 0.19f);
+    f.depth_image = depth_of(k);
+    whole->SetView(f);
+    whole_integrator.Integrate(f);
+    Frame traced;
+    traced.depth_projection = projection;
+    traced.depth_to_world_transform = f.depth_to_world_transform;
+    traced.depth_image = std::make_shared<Image>(w, h);
+    whole_tracer.Trace(traced);
+    std::vector<float> want_d(n), want_n(3 * n);
+    traced.depth_image->CopyToHost(want_d.data());
+    traced.normal_image->CopyToHost(want_n.data());
+    for (int r = 0; r < 2; ++r)
+    {
+      volumes[r]->SetView(f);
+      integrators[r]->Integrate(f);
+    }
+    ShardedTracer::Images images[2];
+    for (int stage = 1; stage <= 3; ++stage)
+      for (int r = 0; r < 2; ++r) tracers[r]->TraceStage(f, images[r], stage);
+    int b0, e0, b1, e1;
+    tracers[0]->GetBand(b0, e0);
+    tracers[1]->GetBand(b1, e1);
+    CHECK(b0 == 0 && e0 == b1 && e1 == h && e0 > 0 && e0 < h);
+    for (int r = 0; r < 2; ++r)
+    {
+      std::vector<float> got_d(n), got_n(3 * n);
+      CUDA_ASSERT(cudaMemcpy(got_d.data(), images[r].depth, n * sizeof(float), cudaMemcpyDeviceToHost));
+      CUDA_ASSERT(cudaMemcpy(got_n.data(), images[r].normal, 3 * n * sizeof(float), cudaMemcpyDeviceToHost));
+      CHECK(std::memcmp(got_d.data(), want_d.data(), n * sizeof(float)) == 0);
+      CHECK(std::memcmp(got_n.data(), want_n.data(), 3 * n * sizeof(float)) == 0);
+    }
+    size_t hits = 0;
+    for (float d : want_d) hits += d > 0;
+    CHECK(hits > n / 2);
+  }
+  // each rank holds only the blocks it owns; together they hold the unsharded set
+  CHECK(volumes[0]->GetAllocatedBlockCount() > 0 && volumes[1]->GetAllocatedBlockCount() > 0);
+  CHECK(volumes[0]->GetAllocatedBlockCount() + volumes[1]->GetAllocatedBlockCount() == whole->GetAllocatedBlockCount());
+}
+
 int main()
 {
   struct { const char* name; void (*fn)(); } tests[] = {
@@ -533,6 +616,7 @@ int main()
     {"Tracer.TraceWall", TestTraceWall}, {"Volume.TwoVolumes", TestTwoVolumes},
     {"Frame.Downsample", TestDownsample}, {"DepthTracker.Wall", TestDepthTrackerWall},
     {"Extractor.Wall", TestExtractWall}, {"FramePipeline", TestFramePipeline},
+    {"ShardedTracer", TestShardedTracer},
   };
   for (auto& t : tests)
   {

@@ -37,6 +37,7 @@ def test_cxx_library_builds_and_exports_reference_classes():
                    "vulcan::ComputePatches(", "vulcan::ComputeBounds(", "vulcan::ComputePoints(",
                    "vulcan::ComputeNormals(", "vulcan::ResetBoundsBuffer(",
                    "vulcan::FramePipeline::Submit(", "vulcan::FramePipeline::Result(int)",
+                   "vulcan::ShardedTracer::Trace(", "vulcan::ShardedTracer::ConnectLocal(",
                    "vulcan_pipeline_create", "vulcan_pipeline_run", "vulcan_pipeline_submit", "vulcan_pipeline_result"):
         assert needle in syms, "libvulcan.so does not define " + needle
     assert os.path.exists(BIN)
