@@ -65,17 +65,18 @@ def test_points_match_oracle(name, frames, mode, step, tmp_path):
     assert lines[12 + len(pts)].split() == ["3"] + [str(i) for i in mesh.faces[0]]
 
 
-def test_mesh_of_a_closed_surface_is_watertight():
-    """A sphere written into the voxels of a volume fused from eight sensors around it (every voxel observed):
-    the extracted mesh is CLOSED - every directed edge exactly once, its opposite present - oriented outwards,
-    and encloses the sphere's volume."""
+def test_mesh_of_closed_surfaces_is_watertight():
+    """Small spheres written into the voxels of a fused volume, centred ON the scene's surface (so that they
+    lie inside the allocated band, every voxel around them observed) and placed so that they straddle block
+    faces, edges and corners: the extracted mesh is CLOSED - every directed edge exactly once, its opposite
+    present - oriented outwards, and encloses the spheres' volume."""
     import torch
     import vulcan_b200 as vb
+    from vulcan_b200 import sharding
     scn = H.make_scenario("small", tuple(range(8)), "depth", 45.0)
     vol = _ours_volume(scn)
     entries = vol.GetHashEntries().cpu().numpy()
     alloc = np.nonzero(entries[:, 2] != -1)[0]
-    from vulcan_b200 import sharding
     bx, by, bz = (a.astype(np.float64) for a in sharding.entry_coords(entries[alloc]))
     data = entries[alloc, 2].astype(np.int64)
     l, L, tau = scn["voxel"], 8 * scn["voxel"], scn["trunc"]
@@ -84,8 +85,22 @@ def test_mesh_of_a_closed_surface_is_watertight():
     X = bx[:, None] * L + ox[None, :] * l
     Y = by[:, None] * L + oy[None, :] * l
     Z = bz[:, None] * L + oz[None, :] * l
-    r = 0.5
-    sdf = np.clip((np.sqrt(X ** 2 + Y ** 2 + (Z - 2.0) ** 2) - r) / tau, -1.0, 1.0).astype(np.float32)
+    # centres on the scene sphere (centre (0, 0, 2), radius 0.5), snapped to block corners / faces nearby
+    r = 0.022
+    centres = []
+    for az in range(0, 360, 45):
+        for el in (-20.0, 10.0):
+            d = np.array([np.sin(np.radians(az)) * np.cos(np.radians(el)), np.sin(np.radians(el)),
+                          -np.cos(np.radians(az)) * np.cos(np.radians(el))])
+            c = np.array([0.0, 0.0, 2.0]) + 0.5 * d
+            snapped = np.round(c / L) * L          # a block corner ...
+            if np.linalg.norm(snapped - c) < 0.012:  # ... if one is close enough to stay inside the band
+                c = snapped
+            centres.append(c)
+    sdf = np.full(X.shape, 1.0)
+    for c in centres:
+        sdf = np.minimum(sdf, (np.sqrt((X - c[0]) ** 2 + (Y - c[1]) ** 2 + (Z - c[2]) ** 2) - r) / tau)
+    sdf = np.clip(sdf, -1.0, 1.0).astype(np.float32)
     vox = vol.GetVoxelsMutable().view(-1, 512, 5)
     idx = torch.as_tensor(data, device="cuda")
     words = vox[idx]
@@ -94,12 +109,13 @@ def test_mesh_of_a_closed_surface_is_watertight():
     vox[idx] = words
     vol.SyncDistances()
     mesh = vb.Extractor(vol).Extract()
-    assert len(mesh.faces) > 10000
+    assert len(mesh.faces) > 100 * len(centres)
     rep = H.mesh_edge_report(mesh.faces)
     assert rep == dict(edges=3 * len(mesh.faces), repeated_directed=0, boundary=0, degenerate=0), rep
-    p = mesh.points[mesh.faces].astype(np.float64) - np.array([0.0, 0.0, 2.0])
+    p = mesh.points[mesh.faces].astype(np.float64)
     volume = np.einsum("ij,ij->i", p[:, 0], np.cross(p[:, 1], p[:, 2])).sum() / 6.0
-    assert abs(volume - 4.0 / 3.0 * np.pi * r ** 3) < 0.01 * volume, volume
+    want = len(centres) * 4.0 / 3.0 * np.pi * r ** 3
+    assert 0.8 * want < volume < 1.05 * want, (volume, want)
 
 
 def test_extract_empty_volume():

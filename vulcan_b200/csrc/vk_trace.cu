@@ -335,7 +335,7 @@ struct TraceParams {
   int free_run;                 // max free-space steps per lane per trip (0 = filter off)
   bool negated_hi;              // bounds cells hold (min, -max) (vk_trace_bounds / vk_trace_rows)
   int coop_lanes, coop_rounds;  // cooperative free-space runs when at most coop_lanes lanes are in free space
-  int ahead_lanes;              // look-ahead prefetch for the rays of a warp with at most this many live lanes (0 = off)
+  int pair_after;               // trips after which a warp takes its free-space steps two at a time (0 = never)
   Mod K;
   Div block_length, voxel_length;
   float trunc;
@@ -607,6 +607,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   if (timeline) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
   const long long c_start = DIAG ? clock64() : 0;
   int dbg_trips = 0;
+  int trips = 0;   // loop trips of this warp (warp-uniform)
   long long c_free = 0, c_a = 0, c_b = 0, c_t = 0, c_la = 0;
   int dbg_alive_sum = 0;
   int dbg_steps = 0, dbg_rounds = 0;
@@ -653,9 +654,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   }
 
   // parked lane: waits for phase B with the block / voxel coordinates of its point
-  // Look-ahead (see below): distance along the ray that is still covered by the last prefetch round.
-  // Bookkeeping only - it decides when to prefetch, never what a ray computes.
-  float ahead = 0.f;
   bool parked = false;
   int kbx = 0, kby = 0, kbz = 0, kdata = -1;
   float kwx = 0.f, kwy = 0.f, kwz = 0.f;
@@ -678,7 +676,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       pt.x = FP<F>::mad(dir.x, s, pt.x);
       pt.y = FP<F>::mad(dir.y, s, pt.y);
       pt.z = FP<F>::mad(dir.z, s, pt.z);
-      ahead -= s;
       return true;  // stepped: depth / iteration test follows
     }
     // ST_REFINE, block found: second refinement step, then the final depth
@@ -706,6 +703,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
 
   while (__any_sync(0xffffffffu, state != ST_DONE)) {
     ++dbg_trips;
+    ++trips;
     if (timeline) c_t = clock64();
     // ---- phase A: block under p, nearest voxel ---------------------------------------------
     int bx = 0, by = 0, bz = 0;
@@ -760,7 +758,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
           const int rflags = __shfl_sync(0xffffffffu, (cap ? 1 : 0) | (out ? 2 : 0) | (occ ? 4 : 0), w);
           if (lane == f) {
             dbg_steps += w + 1;
-            ahead = 0.f;
             pt.x = rx; pt.y = ry; pt.z = rz;
             bx = rbx; by = rby; bz = rbz;
             iters = fit + w + 1;
@@ -775,13 +772,51 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       // (Measured and rejected on B200, see profiles/r01_raycast_tail.md: 4 positions per lane and
       // trip, a brick-level map for 4-step jumps, one lane group per ray in the cooperative runs,
       // several sampling steps per trip, a second pass for the rays that outlive their tile.)
+      // A warp that is still marching after pair_after trips is one of the few long ones (the average warp is
+      // done after four): the machine is emptying, its own instruction stream is what the kernel waits for, and
+      // that stream is a chain of dependent operations per step.  Such a warp takes its free-space steps in
+      // PAIRS: the position, depth, block and filter bit of the step after next are evaluated alongside the
+      // next one's (independent work for the same pipeline latency) and used only if the first step leaves the
+      // ray in free space - the same operations in the same order per ray, hence the same result.
+      if (p.pair_after > 0 && trips > p.pair_after) {
+        for (int n = 0; n < p.free_run && __any_sync(0xffffffffu, freeing); n += 2) {
+          if (freeing) {
+            Vec3 p1, p2;
+            p1.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
+            p1.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
+            p1.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
+            p2.x = FP<F>::mad(dir.x, p.block_length.d, p1.x);
+            p2.y = FP<F>::mad(dir.y, p.block_length.d, p1.y);
+            p2.z = FP<F>::mad(dir.z, p.block_length.d, p1.z);
+            const float d1 = xform1_z<F>(Tcw, p1.x, p1.y, p1.z), d2 = xform1_z<F>(Tcw, p2.x, p2.y, p2.z);
+            int b1x, b1y, b1z, b2x, b2y, b2z;
+            block_of(p1, b1x, b1y, b1z);
+            block_of(p2, b2x, b2y, b2z);
+            const bool occ1 = space_bit(p, b1x, b1y, b1z), occ2 = space_bit(p, b2x, b2y, b2z);
+            // first step (after_step of the reference's trip)
+            pt = p1;
+            bx = b1x; by = b1y; bz = b1z;
+            freeing = false;
+            if (++iters >= 500) { red = true; state = ST_DONE; }
+            else if (!(d1 < hi)) state = ST_DONE;
+            else freeing = !occ1;
+            if (freeing) {   // second step
+              pt = p2;
+              bx = b2x; by = b2y; bz = b2z;
+              freeing = false;
+              if (++iters >= 500) { red = true; state = ST_DONE; }
+              else if (!(d2 < hi)) state = ST_DONE;
+              else freeing = !occ2;
+            }
+          }
+        }
+      }
       for (int n = 0; n < p.free_run && __any_sync(0xffffffffu, freeing); ++n) {
         if (freeing) {
           ++dbg_steps;
           pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
           pt.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
           pt.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
-          ahead -= p.block_length.d;
           after_step();
           freeing = false;
           if (state == ST_MARCH) {
@@ -792,56 +827,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       }
     }
     if (timeline) { const long long c = clock64(); c_free += c - c_t; c_t = c; }
-    // Look-ahead.  The duration of the kernel is its longest rays: a few silhouette-grazing rays that
-    // run alone in their warp through ~30 dependent trips (hash entry -> sample -> neighbour entries
-    // -> taps), every one a chain of cold misses.  When a warp is down to a few live lanes, its 32
-    // lanes walk AHEAD of one such ray - lane j takes the position (j + 1) voxel lengths further along
-    // it - resolve the blocks there (into the ray's own block cache) and pull the distance lines those
-    // positions sample into L1 with plain loads that nobody waits for.  The ray then finds its next
-    // ~32 voxels of path in shared memory / L1 instead of DRAM (or a peer GPU).  Positions are only
-    // approximate and nothing read here reaches a result: the ray still runs its own exact steps.
-    if (timeline) dbg_alive_sum += __popc(__ballot_sync(0xffffffffu, state != ST_DONE));
-    if (SOA && p.ahead_lanes > 0) {
-      const unsigned alive = __ballot_sync(0xffffffffu, state != ST_DONE);
-      if (__popc(alive) <= p.ahead_lanes) {
-        unsigned need = __ballot_sync(0xffffffffu, state != ST_DONE && !parked && ahead <= 0.f);
-        while (need) {
-          const int f = __ffs(need) - 1;
-          need &= need - 1;
-          const float step = p.voxel_length.d * (float)(lane + 1);
-          Vec3 c;
-          c.x = fmaf(__shfl_sync(0xffffffffu, dir.x, f), step, __shfl_sync(0xffffffffu, pt.x, f));
-          c.y = fmaf(__shfl_sync(0xffffffffu, dir.y, f), step, __shfl_sync(0xffffffffu, pt.y, f));
-          c.z = fmaf(__shfl_sync(0xffffffffu, dir.z, f), step, __shfl_sync(0xffffffffu, pt.z, f));
-          const float qx = c.x * p.block_length.r, qy = c.y * p.block_length.r, qz = c.z * p.block_length.r;
-          const int cbx = (int)floorf(qx), cby = (int)floorf(qy), cbz = (int)floorf(qz);
-          BlockCache fc;
-          fc.keys = s_keys + ((threadIdx.x & ~31) | f);
-          fc.data = s_data + ((threadIdx.x & ~31) | f);
-          fc.stride = cache.stride;
-          int d = -1;
-          const bool known = fc.peek(cbx, cby, cbz, d);
-          if (!known && space_bit(p, cbx, cby, cbz)) d = lookup_block<PEERS>(p, cbx, cby, cbz);
-          // one writer per slot of the ray's cache (a key and its id are two words)
-          const int slot = BlockCache::slot(cbx, cby, cbz);
-          const unsigned same = __match_any_sync(0xffffffffu, slot);
-          if (!known && lane == __ffs(same) - 1) fc.put(cbx, cby, cbz, d);
-          if (d != -1) {
-            const int vx = min(7, max(0, (int)((qx - (float)cbx) * 8.0f)));
-            const int vy = min(7, max(0, (int)((qy - (float)cby) * 8.0f)));
-            const int vz = min(7, max(0, (int)((qz - (float)cbz) * 8.0f)));
-            const float* base = PEERS ? p.peer_sdf[d >> kPeerShift] : p.sdf;
-            const float* line = base + (size_t)(d & ((1 << kPeerShift) - 1)) * VK_BLOCK_VOXELS + vz * 64 + vy * 8 + vx;
-            float sink;
-            asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(sink) : "l"(line));
-          }
-          __syncwarp();
-          if (lane == f) ahead = p.voxel_length.d * 30.0f;
-          ++dbg_rounds;
-        }
-      }
-    }
-    if (timeline) { const long long c = clock64(); c_la += c - c_t; c_t = c; }
     if (state != ST_DONE && !parked) {
       const int data = find_data<PEERS>(p, cache, bx, by, bz);
       if (data != -1) {
@@ -866,7 +851,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
         pt.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
         pt.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
-        ahead -= p.block_length.d;
         after_step();
       } else {
         // REFINE without a block under the backed-up point: no second interpolation
@@ -1210,7 +1194,7 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.free_run = 0;
   t.coop_lanes = g_tune[VK_TUNE_RAY_COOP_LANES].load();
   t.coop_rounds = g_tune[VK_TUNE_RAY_COOP_ROUNDS].load();
-  t.ahead_lanes = g_tune[VK_TUNE_RAY_AHEAD_LANES].load();
+  t.pair_after = g_tune[VK_TUNE_RAY_PAIR_AFTER].load();
   t.negated_hi = false;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
