@@ -3,7 +3,8 @@
 (the bench line is config 2; these are the secondary numbers quoted in DESIGN.md):
 
   c1  640x480 depth        c3  1280x720 depth + colour (ColorIntegrator)       light  640x480 LightIntegrator
-  c4  1920x1080 depth, 2 mm voxels, 4 194 303-block volume
+  c4  1920x1080 depth, 2 mm voxels, 4 194 303-block volume (orbit scene)
+  room  BASELINE config 4's scene: the 8 x 8 x 3 m room, 1920x1080, 2 mm, depth range 0.1-8 m, 4 of the 24 poses
 
 Each phase is timed with CUDA events, L2 flushed (256 MiB memset) before it, on frames 4..7 of an orbit
 after 4 warm-up frames (median).  The reference's SetView is repeated until the visible count is stable.
@@ -23,7 +24,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import harness as H  # noqa: E402
 import vulcan_b200 as vb  # noqa: E402
 
-CONFIGS = {"c1": ("c1", "depth"), "c3": ("c3", "color"), "light": ("c1", "light"), "c4": ("c4", "depth")}
+CONFIGS = {"c1": ("c1", "depth"), "c3": ("c3", "color"), "light": ("c1", "light"), "c4": ("c4", "depth"),
+           "room": ("room", "depth")}
 
 
 def timed(fn, flush):
@@ -39,7 +41,8 @@ def timed(fn, flush):
 def run(name):
     size, mode = CONFIGS[name]
     frames = tuple(range(8))
-    scn = H.make_scenario(size, frames, mode)
+    scn = H.make_scenario(size, frames, mode, 15.0) if size == "room" else H.make_scenario(size, frames, mode)
+    dmin, dmax = scn.get("depth_range", (0.1, 5.0))
     K = scn["K"]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     rep = {"config": name, "image": [scn["w"], scn["h"]], "mode": mode}
@@ -48,10 +51,13 @@ def run(name):
     vol = vb.Volume(scn["M"], scn["E"])
     vol.SetVoxelLength(scn["voxel"])
     vol.SetTruncationLength(scn["trunc"])
+    vol.SetDepthRange(dmin, dmax)
     integ = {"depth": vb.DepthIntegrator, "color": vb.ColorIntegrator, "light": vb.LightIntegrator}[mode](vol)
     if mode == "light":
         integ.SetLight(*scn["light"])
+    integ.SetDepthRange(dmin, dmax)
     tracer = vb.Tracer(vol)
+    tracer.SetDepthRange(dmin, dmax)
     t = {"setview": [], "integrate": [], "trace": []}
     for i, fr in enumerate(scn["frames"]):
         f = vb.Frame()
@@ -85,6 +91,7 @@ def run(name):
         try:
             kind = {"depth": 0, "color": 1, "light": 2}[mode]
             rv.set_light(*scn["light"])
+            rv.set_ranges(dmin, dmax, 16.0, 16.0, dmin, dmax)
             t = {"setview": [], "integrate": [], "trace": []}
             passes = []
             for i, fr in enumerate(scn["frames"]):
@@ -105,7 +112,7 @@ def run(name):
 
 
 def main():
-    names = sys.argv[1:] or ["c1", "c3", "light", "c4"]
+    names = sys.argv[1:] or ["c1", "c3", "light", "c4", "room"]
     out = [run(n) for n in names]
     for r in out:
         print(json.dumps(r))

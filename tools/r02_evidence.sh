@@ -2,7 +2,8 @@
 # Round-2 evidence in ONE GPU call (everything lands under gpurun_out/):
 #   1 the GPU test suite                       4 ncu --set full of the REFERENCE's kernels K1-K14
 #   2 both bench arms                          5 the reference's as-shipped build (no NDEBUG), timed once
-#   3 launch list + ncu --set full of ours     6 compute-sanitizer memcheck / racecheck / synccheck logs
+#   3 launch list + ncu --set full of ours     6 bulk-copy integrator capture, knob A/Bs, config / extract / track benches
+# (compute-sanitizer is closed on this pool: bounds are checked by the stress tests' own asserts instead)
 # Usage: gpurun --timeout 2400 -- 'bash tools/r02_evidence.sh [skip-tests]'
 mkdir -p gpurun_out
 if [ "$1" != "skip-tests" ]; then
@@ -26,7 +27,7 @@ PY
 python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"vk_(raycast|integrate|alloc|bounds|carry|normals|setview)" \
+ncu --set full --clock-control none --import-source on -k regex:"vk_(raycast|integrate|alloc|bounds|carry|normals)_kernel" \
     -s 18 -c 6 -o gpurun_out/prof_full -f python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
 ncu -i gpurun_out/prof_full.ncu-rep --page raw --csv > gpurun_out/prof_full_raw.csv 2>/dev/null
 python tools/ncu_summary.py gpurun_out/prof_full_raw.csv > gpurun_out/ncu_full_summary.csv
@@ -38,12 +39,16 @@ ncu --set full --clock-control none \
 ncu -i gpurun_out/prof_ref.ncu-rep --page raw --csv > gpurun_out/prof_ref_raw.csv 2>/dev/null
 python tools/ncu_summary.py gpurun_out/prof_ref_raw.csv > gpurun_out/ncu_ref_summary.csv
 rm -f gpurun_out/prof_ref.ncu-rep
-# sanitizers on config-1 frames (lock-free insert of the allocation kernel, shared-memory staging of the
-# integrator and the ray marcher); the colliding-table variant forces every insert through the lock path
-timeout 600 compute-sanitizer --tool memcheck python tools/one_frame.py --frames 2 > gpurun_out/sanitizer_memcheck_c1.log 2>&1
-timeout 600 compute-sanitizer --tool memcheck python tools/one_frame.py --small --collide --frames 3 > gpurun_out/sanitizer_memcheck_collide.log 2>&1
-timeout 900 compute-sanitizer --tool racecheck python tools/one_frame.py --small --frames 2 > gpurun_out/sanitizer_racecheck.log 2>&1
-timeout 600 compute-sanitizer --tool synccheck python tools/one_frame.py --small --frames 2 > gpurun_out/sanitizer_synccheck.log 2>&1
-tail -3 gpurun_out/sanitizer_*.log
-# ray marcher A/B on the bench workload: distance mirror (knob 10) and look-ahead (knob 11)
-timeout 300 python tools/ray_ab.py --sets "10=0,11=0;10=1,11=0;10=1,11=4;10=1,11=8;10=1,11=16;10=1,11=32" --out ray_ab_c2.json 2>&1 | tail -8
+# the bulk-copy (cp.async.bulk + mbarrier) integrator variant, for the record of the A/B (knob 14)
+VK_TUNE="14=1" ncu --set full --clock-control none -k regex:"vk_integrate_bulk" -s 3 -c 2 -o gpurun_out/prof_bulk -f \
+    python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_bulk.log 2>&1
+ncu -i gpurun_out/prof_bulk.ncu-rep --page raw --csv > gpurun_out/prof_bulk_raw.csv 2>/dev/null
+python tools/ncu_summary.py gpurun_out/prof_bulk_raw.csv > gpurun_out/ncu_bulk_summary.csv
+rm -f gpurun_out/prof_bulk.ncu-rep gpurun_out/prof_bulk_raw.csv
+# knob A/Bs on the bench workload: distance mirror (10), paired free-space steps (11), L2 warm-up (12), bulk integrator (14)
+timeout 300 python tools/ray_ab.py --sets "10=1;10=0;11=0;12=0" --out ray_ab_c2.json 2>&1 | tail -6
+timeout 300 python tools/ray_ab.py --phase integrate --sets "14=0;14=1" --out integrate_ab_c2.json 2>&1 | tail -4
+# the other BASELINE configurations per phase against the reference, surface extraction, tracker
+timeout 900 python tools/config_bench.py > gpurun_out/config_bench.log 2> gpurun_out/config_bench.err; tail -c 2500 gpurun_out/config_bench.log
+timeout 300 python tools/extract_bench.py > gpurun_out/extract_bench.json 2> gpurun_out/extract_bench.err; tail -c 800 gpurun_out/extract_bench.json
+timeout 300 python tools/track_bench.py > gpurun_out/track_bench.json 2> gpurun_out/track_bench.err; tail -c 800 gpurun_out/track_bench.json
