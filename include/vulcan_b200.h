@@ -32,6 +32,7 @@ extern "C" {
                              /* src/volume.cu:338-356)                              */
 #define VK_E_IO        (-4)  /* snapshot file missing, truncated or of another version */
 #define VK_E_TIMEOUT   (-5)  /* sharded volume: a peer did not arrive at a handshake within ~2 s */
+#define VK_E_TOO_LARGE (-6)  /* vk_extract_mesh_static: the volume exceeds VK_MESH_STATIC_MAX_* */
 
 /* vkVolume::math_mode: where float multiply-adds round.                               */
 #define VK_MATH_REFERENCE 0  /* fused exactly where nvcc's default -fmad=true fuses them  */
@@ -451,6 +452,22 @@ int vk_extract_points(const vkVolume* v, float* points, float* colors, int capac
  * with larger buffers).  Synchronises the stream (sizes its workspace from the allocated-block counter). */
 int vk_extract_mesh(const vkVolume* v, float* points, float* colors, int point_capacity, int* point_count,
                     int* faces, int face_capacity, int* face_count, void* stream);
+
+/* vk_extract_mesh without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments, same result as vk_extract_mesh (the same two kernels);
+ * the workspace vk_extract_mesh allocates per call lives in one file-scope `static __device__` array
+ * instead (vk_extract.cu: g_mesh_static, 64 + VK_MESH_STATIC_MAX_POOL + 1536 * VK_MESH_STATIC_MAX_BLOCKS
+ * ints = 12.5 MiB, held by every GPU that loads the library until the process exits).  Limits: main_blocks +
+ * excess_blocks <= VK_MESH_STATIC_MAX_POOL and at most VK_MESH_STATIC_MAX_BLOCKS allocated blocks; beyond
+ * either the call writes nothing and returns VK_E_TOO_LARGE (use vk_extract_mesh).  Calls no cudaMalloc /
+ * cudaFree / allocating library routine.  Synchronises the stream once (reads the allocated-block counter)
+ * and returns with the kernels enqueued.  Every call shares the array: calls that overlap on the GPU
+ * (different streams or host threads of one device) race - serialise them. */
+#define VK_MESH_STATIC_MAX_POOL   131072  /* main_blocks + excess_blocks */
+#define VK_MESH_STATIC_MAX_BLOCKS 2048    /* allocated blocks            */
+int vk_extract_mesh_static(const vkVolume* v, float* points, float* colors, int point_capacity, int* point_count,
+                           int* faces, int face_capacity, int* face_count, void* stream);
 
 /* ---- misc -------------------------------------------------------------------- */
 

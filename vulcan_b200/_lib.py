@@ -16,6 +16,8 @@ VK_CNT_OVERFLOW = 4
 VK_CNT_ALLOCATED = 6
 VK_CNT_COUNT = 16
 VK_E_OVERFLOW = -3
+VK_E_TOO_LARGE = -6
+VK_MESH_STATIC_MAX_POOL, VK_MESH_STATIC_MAX_BLOCKS = 131072, 2048
 VK_MATH_REFERENCE, VK_MATH_STRICT = 0, 1
 BOUNDS_W, BOUNDS_H = 80, 60
 
@@ -132,6 +134,7 @@ SYMBOLS = {
     "vk_track_depth": [C.POINTER(vkFrame), C.POINTER(vkFrame), _I, _I, _P, C.POINTER(_I), C.POINTER(_F), _P],
     "vk_extract_points": [C.POINTER(vkVolume), _P, _P, _I, _P, _P],
     "vk_extract_mesh": [C.POINTER(vkVolume), _P, _P, _I, _P, _P, _I, _P, _P],
+    "vk_extract_mesh_static": [C.POINTER(vkVolume), _P, _P, _I, _P, _P, _I, _P, _P],
     "vk_version": [],
     "vk_set_default_math_mode": [_I],
     "vk_get_default_math_mode": [],

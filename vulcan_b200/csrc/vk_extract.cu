@@ -406,3 +406,100 @@ extern "C" int vk_extract_mesh(const vkVolume* v, float* points, float* colors, 
   cudaFree(edge_index);
   return rc ? rc : (int)err;
 }
+
+// ---- vk_extract_mesh_static: the same mesh without any allocation (include/vulcan_b200.h) ------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it): the workspace vk_extract_mesh allocates per call - block -> slot table, slot counter and
+// the per-edge vertex index table - lives in ONE file-scope device array of fixed size instead, held by
+// every GPU that loads the library until the process exits.  Layout (ints):
+//   [0, 64)                                   header; [0] = slot counter (cleared by every call)
+//   [64, 64 + VK_MESH_STATIC_MAX_POOL)        block_slot: slot of voxel block `data`
+//   then VK_MESH_STATIC_MAX_BLOCKS * 1536     edge_index rows of the allocated blocks, by slot
+// block_slot and edge_index keep the previous call's contents; both kernels only read the rows the points
+// kernel of the SAME call wrote (every allocated block gets a slot and a full row), so only the counter must
+// start at zero.  All calls share the array: calls that overlap on the GPU (two streams, two host threads)
+// race - serialise them.
+namespace vk {
+
+constexpr size_t kMeshStaticInts = 64 + (size_t)VK_MESH_STATIC_MAX_POOL +
+                                   (size_t)VK_MESH_STATIC_MAX_BLOCKS * VK_BLOCK_VOXELS * 3;
+static __device__ __align__(256) int g_mesh_static[kMeshStaticInts];
+
+constexpr int kMaxDevices = 64;
+static int* g_mesh_static_addr[kMaxDevices];      // device address of g_mesh_static, per device (set-up below)
+static bool g_mesh_static_tables[kMaxDevices];    // marching-cubes tables copied to this device's constant memory
+
+// Once per device, with that device current: in host code `g_mesh_static` is only the host-side stand-in
+// of the symbol, NOT a device address - the address the kernels get comes from cudaGetSymbolAddress.
+static int mesh_static_setup(int** scratch) {
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  if (dev < 0 || dev >= kMaxDevices) return VK_E_NODEVICE;
+  if (!g_mesh_static_addr[dev]) {
+    int* ptr = nullptr;
+    err = cudaGetSymbolAddress((void**)&ptr, g_mesh_static);
+    if (err != cudaSuccess) return (int)err;
+    if (!ptr) return VK_E_NODEVICE;
+    g_mesh_static_addr[dev] = ptr;
+  }
+  if (!g_mesh_static_tables[dev]) {
+    err = cudaMemcpyToSymbol(c_tri_table, kMcTriTable, sizeof(kMcTriTable));
+    if (err == cudaSuccess) err = cudaMemcpyToSymbol(c_edge_corner, kMcEdgeCorner, sizeof(kMcEdgeCorner));
+    if (err == cudaSuccess) err = cudaMemcpyToSymbol(c_edge_axis, kMcEdgeAxis, sizeof(kMcEdgeAxis));
+    if (err != cudaSuccess) return (int)err;
+    g_mesh_static_tables[dev] = true;
+  }
+  *scratch = g_mesh_static_addr[dev];
+  return 0;
+}
+
+}  // namespace vk
+
+extern "C" int vk_extract_mesh_static(const vkVolume* v, float* points, float* colors, int point_capacity,
+                                      int* point_count, int* faces, int face_capacity, int* face_count, void* stream) {
+  if (!v || !v->voxels || !points || !point_count || !faces || !face_count || point_capacity < 0 || face_capacity < 0)
+    return VK_E_INVALID;
+  if (v->shard_count > 1) return VK_E_INVALID;   // see vk_extract_points
+  const size_t B = (size_t)v->main_blocks + (size_t)v->excess_blocks;
+  if (B > (size_t)VK_MESH_STATIC_MAX_POOL) return VK_E_TOO_LARGE;
+  cudaStream_t s = (cudaStream_t)stream;
+  int* scratch = nullptr;
+  int rc = mesh_static_setup(&scratch);
+  if (rc) return rc;
+  // blocks in use: each takes one 6 KB row of the static vertex index table
+  int allocated = 0;
+  cudaError_t err = cudaMemcpyAsync(&allocated, v->counters + VK_CNT_ALLOCATED, sizeof(int), cudaMemcpyDeviceToHost, s);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return (int)err;
+  if (allocated < 0 || allocated > VK_MESH_STATIC_MAX_BLOCKS) return VK_E_TOO_LARGE;
+  err = cudaMemsetAsync(scratch, 0, 64 * sizeof(int), s);   // the slot counter starts at zero
+  if (err == cudaSuccess) err = cudaMemsetAsync(point_count, 0, sizeof(int), s);
+  if (err == cudaSuccess) err = cudaMemsetAsync(face_count, 0, sizeof(int), s);
+  if (err != cudaSuccess) return (int)err;
+  ExtractParams p;
+  p.entries = (const vkHashEntry*)v->entries;
+  p.voxels = (const vkVoxel*)v->voxels;
+  p.total_entries = v->main_blocks + v->excess_blocks;
+  p.K = make_mod((uint32_t)v->main_blocks);
+  p.voxel_length = v->voxel_length;
+  p.block_length = VK_BLOCK_RES * v->voxel_length;
+  p.points = points;
+  p.colors = colors;
+  p.capacity = point_capacity;
+  p.count = point_count;
+  p.slot_counter = scratch;
+  p.block_slot = scratch + 64;
+  p.edge_index = scratch + 64 + VK_MESH_STATIC_MAX_POOL;
+  p.faces = faces;
+  p.face_capacity = face_capacity;
+  p.face_count = face_count;
+  p.chunk = 16;
+  const int chunks = (p.total_entries + p.chunk - 1) / p.chunk;
+  const int cap = 3 * sm_count();
+  vk_extract_points_kernel<<<chunks < cap ? chunks : cap, 512, 0, s>>>(p);
+  VK_COUNT_LAUNCH();
+  vk_extract_faces_kernel<<<chunks < cap ? chunks : cap, 512, 0, s>>>(p);
+  VK_COUNT_LAUNCH();
+  return (int)cudaGetLastError();
+}
