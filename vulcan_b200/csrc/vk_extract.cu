@@ -310,6 +310,24 @@ __global__ void __launch_bounds__(512, 3) vk_extract_faces_kernel(ExtractParams 
   }
 }
 
+// the generated tables (tools/gen_mc_tables.py) go to constant memory once per DEVICE, with that device current
+constexpr int kMaxDevices = 64;
+static bool g_mc_tables_loaded[kMaxDevices];
+
+static int load_mc_tables() {
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  if (dev < 0 || dev >= kMaxDevices) return VK_E_NODEVICE;
+  if (g_mc_tables_loaded[dev]) return 0;
+  err = cudaMemcpyToSymbol(c_tri_table, kMcTriTable, sizeof(kMcTriTable));
+  if (err == cudaSuccess) err = cudaMemcpyToSymbol(c_edge_corner, kMcEdgeCorner, sizeof(kMcEdgeCorner));
+  if (err == cudaSuccess) err = cudaMemcpyToSymbol(c_edge_axis, kMcEdgeAxis, sizeof(kMcEdgeAxis));
+  if (err != cudaSuccess) return (int)err;
+  g_mc_tables_loaded[dev] = true;
+  return 0;
+}
+
 }  // namespace vk
 
 using namespace vk;
@@ -350,13 +368,9 @@ extern "C" int vk_extract_mesh(const vkVolume* v, float* points, float* colors, 
     return VK_E_INVALID;
   if (v->shard_count > 1) return VK_E_INVALID;   // see vk_extract_points
   cudaStream_t s = (cudaStream_t)stream;
-  static bool tables_loaded = false;   // per process; the tables are generated (tools/gen_mc_tables.py)
-  if (!tables_loaded) {
-    cudaError_t te = cudaMemcpyToSymbol(c_tri_table, kMcTriTable, sizeof(kMcTriTable));
-    if (te == cudaSuccess) te = cudaMemcpyToSymbol(c_edge_corner, kMcEdgeCorner, sizeof(kMcEdgeCorner));
-    if (te == cudaSuccess) te = cudaMemcpyToSymbol(c_edge_axis, kMcEdgeAxis, sizeof(kMcEdgeAxis));
-    if (te != cudaSuccess) return (int)te;
-    tables_loaded = true;
+  {
+    const int trc = load_mc_tables();   // constant memory is per device
+    if (trc) return trc;
   }
   // blocks in use -> size of the per-edge vertex index table (6 KB per block)
   int allocated = 0;
@@ -425,9 +439,7 @@ constexpr size_t kMeshStaticInts = 64 + (size_t)VK_MESH_STATIC_MAX_POOL +
                                    (size_t)VK_MESH_STATIC_MAX_BLOCKS * VK_BLOCK_VOXELS * 3;
 static __device__ __align__(256) int g_mesh_static[kMeshStaticInts];
 
-constexpr int kMaxDevices = 64;
 static int* g_mesh_static_addr[kMaxDevices];      // device address of g_mesh_static, per device (set-up below)
-static bool g_mesh_static_tables[kMaxDevices];    // marching-cubes tables copied to this device's constant memory
 
 // Once per device, with that device current: in host code `g_mesh_static` is only the host-side stand-in
 // of the symbol, NOT a device address - the address the kernels get comes from cudaGetSymbolAddress.
@@ -443,13 +455,8 @@ static int mesh_static_setup(int** scratch) {
     if (!ptr) return VK_E_NODEVICE;
     g_mesh_static_addr[dev] = ptr;
   }
-  if (!g_mesh_static_tables[dev]) {
-    err = cudaMemcpyToSymbol(c_tri_table, kMcTriTable, sizeof(kMcTriTable));
-    if (err == cudaSuccess) err = cudaMemcpyToSymbol(c_edge_corner, kMcEdgeCorner, sizeof(kMcEdgeCorner));
-    if (err == cudaSuccess) err = cudaMemcpyToSymbol(c_edge_axis, kMcEdgeAxis, sizeof(kMcEdgeAxis));
-    if (err != cudaSuccess) return (int)err;
-    g_mesh_static_tables[dev] = true;
-  }
+  const int trc = load_mc_tables();
+  if (trc) return trc;
   *scratch = g_mesh_static_addr[dev];
   return 0;
 }
