@@ -228,3 +228,50 @@ def test_reference_block_set_is_not_deterministic_q24():
     _dump("q24_repro", rep)
     common_extra = frozenset.intersection(*sets) if sets else frozenset()
     assert len(common_extra) == 0, "blocks every reference run has and ours lacks: %s" % sorted(common_extra)[:8]
+
+
+@pytest.mark.parametrize("mode", ["depth", "color"])
+def test_bulk_copy_integrator_variant_is_bit_identical(mode):
+    """The cp.async.bulk + mbarrier integration kernel (tuning knob 14, kept for the A/B in DESIGN.md 4.2)
+    writes the same voxels and the same distance mirror as the default kernel, bit for bit."""
+    import torch
+    import vulcan_b200 as vb
+    scn = H.make_scenario("small", (0, 3, 6), mode, 5.0)
+
+    def fuse(bulk):
+        old = vb.lib.vk_tune(14, bulk)
+        try:
+            vol = vb.Volume(scn["M"], scn["E"])
+            vol.SetVoxelLength(scn["voxel"])
+            vol.SetTruncationLength(scn["trunc"])
+            integ = (vb.ColorIntegrator if mode == "color" else vb.DepthIntegrator)(vol)
+            for fr in scn["frames"]:
+                f = vb.Frame()
+                f.depth_projection = vb.Projection(*scn["K"])
+                f.color_projection = vb.Projection(*scn["K"])
+                f.depth_to_world_transform = vb.Transform(fr["T"][:16].reshape(4, 4).T.copy(), fr["T"][16:].reshape(4, 4).T.copy())
+                f.depth_to_color_transform = vb.Transform(scn["Tcd"][:16].reshape(4, 4).T.copy(),
+                                                          scn["Tcd"][16:].reshape(4, 4).T.copy())
+                f.depth_image = torch.from_numpy(fr["depth"]).cuda()
+                if fr["color"] is not None:
+                    f.color_image = torch.from_numpy(fr["color"]).cuda()
+                vol.SetView(f)
+                integ.Integrate(f)
+            torch.cuda.synchronize()
+            # the block a hash entry points to depends on the order of the allocation atomics: compare by entry
+            entries = vol.GetHashEntries().cpu().numpy()
+            voxels = vol.GetVoxels().cpu().numpy().reshape(-1, 512, 5)
+            sdf = vol.GetDistances().cpu().numpy().view(np.int32).reshape(-1, 512)
+            live = entries[entries[:, 2] != -1]
+            order = np.lexsort((live[:, 1], live[:, 0]))
+            live = live[order]
+            return live[:, :2].copy(), voxels[live[:, 2]], sdf[live[:, 2]]
+        finally:
+            vb.lib.vk_tune(14, old)
+
+    k0, v0, s0 = fuse(0)
+    k1, v1, s1 = fuse(1)
+    assert len(k0) > 500 and np.array_equal(k0, k1)
+    assert np.array_equal(v0, v1)
+    assert np.array_equal(s0, s1)
+    assert (v0[:, :, 4] & 0xffff).max() > 1   # blocks were integrated more than once

@@ -111,7 +111,8 @@ def main():
         med, mn = timed()
         d = digest()
         ref = ref or d
-        results.append(dict(phase=args.phase, scene=args.scene, knobs=spec, med_us=med, min_us=mn, same_images=(d == ref),
+        results.append(dict(phase=args.phase, scene=args.scene, knobs=spec, med_us=med, min_us=mn, same_images=((d == ref) if args.phase == "trace" else None),  # other phases change the model between sets
+                           
                             visible=vol.GetVisibleCount()))
         print(json.dumps(results[-1]), flush=True)
         for k, v in defaults.items():
