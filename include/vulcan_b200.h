@@ -126,7 +126,9 @@ typedef struct vkVolume {
                               /* step by the integrators, vk_volume_reset and vk_volume_load; after  */
                               /* writing `voxels` directly call vk_volume_sync_sdf.                  */
   int32_t*     counters;      /* [VK_CNT_COUNT] device                              */
-  int32_t*     host_counters; /* [VK_CNT_COUNT] pinned host mirror                  */
+  int32_t*     host_counters; /* [VK_CNT_COUNT] pinned host mirror, filled by vk_volume_sync_counters only: no   */
+                              /* kernel stores to host memory (such a store queues behind the PCIe traffic of   */
+                              /* concurrent downloads and delayed the kernel's completion by ~14 us per frame)   */
   int32_t      main_blocks;   /* M (also the hash modulus K)                        */
   int32_t      excess_blocks; /* E                                                  */
   float        voxel_length;
@@ -145,6 +147,15 @@ typedef struct vkVolume {
                               /* while 0 every Voxel::color_weight is 0, so the ray marcher writes the colour  */
                               /* that implies - (0,0,0) - without gathering the 8 colour taps per ray          */
   struct vkShard* shard;      /* replicated lookup structures of a block-sharded volume (vk_shard_create), or NULL */
+  /* Library-owned side stream + events (created by vk_volume_create): vk_trace computes the ray bounds of a view -  */
+  /* which depend on the visible list of vk_set_view only, not on the voxels - on aux_stream while the caller's      */
+  /* stream is still integrating, and joins before the ray march.  Results and stream-order semantics are unchanged. */
+  void*        aux_stream;
+  void*        ev_view;       /* recorded on the caller's stream at the end of vk_set_view                     */
+  void*        ev_bounds;     /* recorded on aux_stream after the bounds kernel                                 */
+  void*        ev_trace;      /* recorded on the caller's stream at the end of every ray cast (bounds scratch free) */
+  int32_t      aux_valid;     /* ev_view belongs to the current view                                            */
+  int32_t      reserved0;
 } vkVolume;
 
 /* One RGB-D frame on the device.  Replaces vulcan::Frame

@@ -108,7 +108,7 @@ def main():
             print("  long warp tile (x=%d,y=%d): start %.1f dur %.1f  sm %d trips %d cycles %d (%.0f cyc/trip)" % (
                 (w_ % (W // 8)) * 8, (w_ // (W // 8)) * 4, start[w_], dur[w_], t[w_, 2] >> 32, t[w_, 2] & 0xffffffff,
                 t[w_, 3], t[w_, 3] / max(1, t[w_, 2] & 0xffffffff)))
-            print("      cycles: free-run %d  look-ahead %d  phase A %d  phase B %d  max-lane free steps %d look-ahead rounds %d  mean live lanes %.1f" % (
+            print("      cycles: free-run %d  of which cooperative runs %d  phase A %d  phase B %d  max-lane free steps %d cooperative ray-runs %d  mean live lanes %.1f" % (
                 t[w_, 4], c_la[w_], t[w_, 5], t[w_, 6], t[w_, 7] & 0xffffffff, t[w_, 7] >> 32, alive_sum[w_] / max(1, t[w_, 2] & 0xffffffff)))
         trips = (t[:, 2] & 0xffffffff).astype(np.float64)
         print("  all warps: trips total %d, cycles/trip mean %.0f" % (trips.sum(), t[:, 3].sum() / trips.sum()))

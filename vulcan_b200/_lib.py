@@ -46,6 +46,8 @@ class vkVolume(C.Structure):
         ("shard_rank", C.c_int32), ("shard_count", C.c_int32), ("shard_shift", C.c_int32), ("shard_halo", C.c_int32),
         ("visible_slot", C.c_int32), ("view_id", C.c_int32), ("math_mode", C.c_int32), ("has_color", C.c_int32),
         ("shard", C.c_void_p),
+        ("aux_stream", C.c_void_p), ("ev_view", C.c_void_p), ("ev_bounds", C.c_void_p), ("ev_trace", C.c_void_p),
+        ("aux_valid", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 

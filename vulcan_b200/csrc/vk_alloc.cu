@@ -268,7 +268,6 @@ struct CarryParams {
   uint8_t* visibility;
   const int32_t* stamps;
   int32_t* counters;
-  int32_t* host_counters;
   const int32_t* prev_list;
   int32_t* visible_out;
   int prev_slot, cnt_slot;
@@ -341,11 +340,6 @@ __global__ void __launch_bounds__(256) vk_carry_kernel(const CarryParams p) {
     if (threadIdx.x == 0) {
       p.counters[p.prev_slot] = 0;
       *p.ticket = 0;
-    }
-    if (threadIdx.x < VK_CNT_COUNT && p.host_counters) {
-      int val = __ldcg(p.counters + threadIdx.x);
-      if (threadIdx.x == p.prev_slot) val = 0;
-      p.host_counters[threadIdx.x] = val;
     }
   }
 }
@@ -443,6 +437,7 @@ extern "C" int vk_volume_reset(vkVolume* v, void* stream) {
   v->visible_slot = 0;
   v->view_id = 0;
   v->has_color = 0;
+  v->aux_valid = 0;
   return 0;
 }
 
@@ -481,6 +476,14 @@ extern "C" int vk_volume_create(vkVolume* v, int main_blocks, int excess_blocks,
   VK_TRY(cudaMalloc((void**)&v->sdf, B * VK_BLOCK_VOXELS * sizeof(float)));
   VK_TRY(cudaMalloc((void**)&v->counters, (VK_CNT_COUNT + 4) * sizeof(int32_t)));
   VK_TRY(cudaHostAlloc((void**)&v->host_counters, VK_CNT_COUNT * sizeof(int32_t), cudaHostAllocMapped));
+  {
+    cudaStream_t aux = nullptr;
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    VK_TRY(cudaStreamCreateWithFlags(&aux, cudaStreamNonBlocking));
+    v->aux_stream = aux;
+    for (int i = 0; i < 3; ++i) VK_TRY(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+    v->ev_view = ev[0]; v->ev_bounds = ev[1]; v->ev_trace = ev[2];
+  }
 #undef VK_TRY
   return vk_volume_reset(v, stream);
 }
@@ -501,6 +504,13 @@ extern "C" int vk_volume_destroy(vkVolume* v) {
   cudaFree(v->sdf);
   cudaFree(v->counters);
   if (v->host_counters) cudaFreeHost(v->host_counters);
+  if (v->aux_stream) {
+    cudaStreamSynchronize((cudaStream_t)v->aux_stream);
+    cudaStreamDestroy((cudaStream_t)v->aux_stream);
+  }
+  if (v->ev_view) cudaEventDestroy((cudaEvent_t)v->ev_view);
+  if (v->ev_bounds) cudaEventDestroy((cudaEvent_t)v->ev_bounds);
+  if (v->ev_trace) cudaEventDestroy((cudaEvent_t)v->ev_trace);
   const int m = v->main_blocks, e = v->excess_blocks;
   memset(v, 0, sizeof(*v));
   v->main_blocks = m;
@@ -565,7 +575,6 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   c.visibility = v->visibility;
   c.stamps = v->stamps;
   c.counters = v->counters;
-  c.host_counters = v->host_counters;
   c.prev_list = v->visible[prev];
   c.visible_out = v->visible[cur];
   c.prev_slot = VK_CNT_VISIBLE0 + prev;
@@ -581,6 +590,10 @@ extern "C" int vk_set_view(vkVolume* v, const vkFrame* f, void* stream) {
   else launch_chained(vk_carry_kernel<true>, dim3(sm_count()), dim3(256), 0, s, c);
   VK_COUNT_LAUNCH();
   v->visible_slot = cur;
+  // vk_trace may compute this view's ray bounds on the side stream as soon as the list above exists
+  v->aux_valid = 0;
+  if (v->aux_stream && v->ev_view && !stream_capturing(s) && cudaEventRecord((cudaEvent_t)v->ev_view, s) == cudaSuccess)
+    v->aux_valid = 1;
   return (int)cudaGetLastError();
 }
 

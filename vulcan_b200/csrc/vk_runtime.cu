@@ -11,7 +11,8 @@ namespace vk {
 
 std::atomic<unsigned long long> g_launches{0};
 std::atomic<int> g_default_math_mode{VK_MATH_REFERENCE};
-std::atomic<int> g_tune[VK_TUNE_COUNT] = {{64}, {12}, {3}, {0}, {0}, {4}, {0}, {8}, {4}, {1}, {1}, {8}, {1}, {0}, {0}, {0}};
+std::atomic<int> g_tune[VK_TUNE_COUNT] = {{64}, {12}, {3}, {0}, {0}, {4}, {0}, {8}, {4}, {1}, {1}, {8}, {1}, {0}, {0}, {1}};
+std::atomic<int> g_capture_seen{0};
 
 // Compares the one-step FMA division against the IEEE division.
 //

@@ -299,6 +299,7 @@ extern "C" int vk_volume_load(vkVolume* v, const char* path, void* stream) {
   v->voxel_length = h.voxel_length; v->trunc_length = h.trunc_length;
   v->min_depth = h.min_depth; v->max_depth = h.max_depth;
   v->visible_slot = h.visible_slot; v->view_id = h.view_id;
+  v->aux_valid = 0;   // the visible list was replaced: no side-stream bounds until the next vk_set_view
   memcpy(v->host_counters, h.counters, VK_CNT_COUNT * sizeof(int32_t));
   return 0;
 }

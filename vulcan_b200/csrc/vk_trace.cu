@@ -336,6 +336,7 @@ struct TraceParams {
   bool negated_hi;              // bounds cells hold (min, -max) (vk_trace_bounds / vk_trace_rows)
   int coop_lanes, coop_rounds;  // cooperative free-space runs when at most coop_lanes lanes are in free space
   int pair_after;               // trips after which a warp takes its free-space steps two at a time (0 = never)
+  int pair_first;               // such a warp takes up to this many paired steps BEFORE its cooperative runs
   Mod K;
   Div block_length, voxel_length;
   float trunc;
@@ -701,6 +702,43 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     iz = (int)floorf(fz);
   };
 
+  // up to max_steps free-space steps of every lane that is in free space, two per pass (see the long-warp
+  // comment in the loop below): the second step's position, depth, block and filter bit are evaluated
+  // alongside the first one's and used only if the first step leaves the ray in free space
+  auto pair_steps = [&](bool& freeing, int& bx, int& by, int& bz, int max_steps) {
+    for (int n = 0; n < max_steps && __any_sync(0xffffffffu, freeing); n += 2) {
+      if (freeing) {
+        Vec3 p1, p2;
+        p1.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
+        p1.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
+        p1.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
+        p2.x = FP<F>::mad(dir.x, p.block_length.d, p1.x);
+        p2.y = FP<F>::mad(dir.y, p.block_length.d, p1.y);
+        p2.z = FP<F>::mad(dir.z, p.block_length.d, p1.z);
+        const float d1 = xform1_z<F>(Tcw, p1.x, p1.y, p1.z), d2 = xform1_z<F>(Tcw, p2.x, p2.y, p2.z);
+        int b1x, b1y, b1z, b2x, b2y, b2z;
+        block_of(p1, b1x, b1y, b1z);
+        block_of(p2, b2x, b2y, b2z);
+        const bool occ1 = space_bit(p, b1x, b1y, b1z), occ2 = space_bit(p, b2x, b2y, b2z);
+        // first step (after_step of the reference's trip)
+        pt = p1;
+        bx = b1x; by = b1y; bz = b1z;
+        freeing = false;
+        if (++iters >= 500) { red = true; state = ST_DONE; }
+        else if (!(d1 < hi)) state = ST_DONE;
+        else freeing = !occ1;
+        if (freeing) {   // second step
+          pt = p2;
+          bx = b2x; by = b2y; bz = b2z;
+          freeing = false;
+          if (++iters >= 500) { red = true; state = ST_DONE; }
+          else if (!(d2 < hi)) state = ST_DONE;
+          else freeing = !occ2;
+        }
+      }
+    }
+  };
+
   while (__any_sync(0xffffffffu, state != ST_DONE)) {
     ++dbg_trips;
     ++trips;
@@ -718,15 +756,22 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     // waiting in other states are not starved.
     if (p.free_run > 0) {
       bool freeing = (state == ST_MARCH && !parked && !space_bit(p, bx, by, bz));
+      // Long warps, first: a few paired steps for ALL lanes in free space at once.  Near the surface a grazing
+      // ray leaves and re-enters the allocated band every few blocks; such short runs cost one pass here for
+      // every lane together, where a cooperative run (below) spends a 32-position evaluation per ray on them.
+      if (p.pair_first > 0 && trips > p.pair_after) pair_steps(freeing, bx, by, bz, p.pair_first);
       unsigned fmask = __ballot_sync(0xffffffffu, freeing);
       // Few lanes in free space (the tail of the kernel: a handful of rays that graze the
       // surface and then cross metres of empty space): all 32 lanes evaluate the next 32
       // positions of ONE such ray at a time - lane j takes the position after j+1 steps, computed
       // by the same chain of FMAs the ray itself would run - and the ray jumps to the first
       // position that is occupied, out of range or at the iteration cap.
+      const long long c_coop0 = timeline ? clock64() : 0;
+      if (timeline) dbg_alive_sum += __popc(__ballot_sync(0xffffffffu, state != ST_DONE));
       for (int round = 0; round < p.coop_rounds && fmask != 0 && __popc(fmask) <= p.coop_lanes; ++round) {
         unsigned todo = fmask;
         while (todo) {
+          ++dbg_rounds;
           const int f = __ffs(todo) - 1;
           todo &= todo - 1;
           Vec3 c = {__shfl_sync(0xffffffffu, pt.x, f), __shfl_sync(0xffffffffu, pt.y, f),
@@ -768,6 +813,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
         }
         fmask = __ballot_sync(0xffffffffu, freeing);
       }
+      if (timeline) c_la += clock64() - c_coop0;
       // Many lanes in free space: they take the steps together, one step per loop trip.
       // (Measured and rejected on B200, see profiles/r01_raycast_tail.md: 4 positions per lane and
       // trip, a brick-level map for 4-step jumps, one lane group per ray in the cooperative runs,
@@ -778,39 +824,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       // PAIRS: the position, depth, block and filter bit of the step after next are evaluated alongside the
       // next one's (independent work for the same pipeline latency) and used only if the first step leaves the
       // ray in free space - the same operations in the same order per ray, hence the same result.
-      if (p.pair_after > 0 && trips > p.pair_after) {
-        for (int n = 0; n < p.free_run && __any_sync(0xffffffffu, freeing); n += 2) {
-          if (freeing) {
-            Vec3 p1, p2;
-            p1.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
-            p1.y = FP<F>::mad(dir.y, p.block_length.d, pt.y);
-            p1.z = FP<F>::mad(dir.z, p.block_length.d, pt.z);
-            p2.x = FP<F>::mad(dir.x, p.block_length.d, p1.x);
-            p2.y = FP<F>::mad(dir.y, p.block_length.d, p1.y);
-            p2.z = FP<F>::mad(dir.z, p.block_length.d, p1.z);
-            const float d1 = xform1_z<F>(Tcw, p1.x, p1.y, p1.z), d2 = xform1_z<F>(Tcw, p2.x, p2.y, p2.z);
-            int b1x, b1y, b1z, b2x, b2y, b2z;
-            block_of(p1, b1x, b1y, b1z);
-            block_of(p2, b2x, b2y, b2z);
-            const bool occ1 = space_bit(p, b1x, b1y, b1z), occ2 = space_bit(p, b2x, b2y, b2z);
-            // first step (after_step of the reference's trip)
-            pt = p1;
-            bx = b1x; by = b1y; bz = b1z;
-            freeing = false;
-            if (++iters >= 500) { red = true; state = ST_DONE; }
-            else if (!(d1 < hi)) state = ST_DONE;
-            else freeing = !occ1;
-            if (freeing) {   // second step
-              pt = p2;
-              bx = b2x; by = b2y; bz = b2z;
-              freeing = false;
-              if (++iters >= 500) { red = true; state = ST_DONE; }
-              else if (!(d2 < hi)) state = ST_DONE;
-              else freeing = !occ2;
-            }
-          }
-        }
-      }
+      if (p.pair_after > 0 && trips > p.pair_after) pair_steps(freeing, bx, by, bz, p.free_run);
       for (int n = 0; n < p.free_run && __any_sync(0xffffffffu, freeing); ++n) {
         if (freeing) {
           ++dbg_steps;
@@ -1195,6 +1209,7 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.coop_lanes = g_tune[VK_TUNE_RAY_COOP_LANES].load();
   t.coop_rounds = g_tune[VK_TUNE_RAY_COOP_ROUNDS].load();
   t.pair_after = g_tune[VK_TUNE_RAY_PAIR_AFTER].load();
+  t.pair_first = t.pair_after > 0 ? g_tune[VK_TUNE_RAY_PAIR_FIRST].load() : 0;
   t.negated_hi = false;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
@@ -1349,12 +1364,36 @@ static int trace_bounds(const vkVolume* v, const vkFrame* view, float min_depth,
   return (int)cudaGetLastError();
 }
 
+// end of a ray cast on stream s: from here on the bounds scratch may be rewritten (see vk_trace)
+static int trace_done(const vkVolume* v, cudaStream_t s) {
+  if (!v->ev_trace || stream_capturing(s)) return 0;
+  return (int)cudaEventRecord((cudaEvent_t)v->ev_trace, s);
+}
+
 extern "C" int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, float* bounds,
                         float* out_depth, float* out_color, float* out_normal, void* stream) {
   if (!v || !view || !v->voxels || !bounds || !out_depth || !out_color) return VK_E_INVALID;
   cudaStream_t s = (cudaStream_t)stream;
-  int rc = trace_bounds(v, view, min_depth, max_depth, bounds, s);
+  // The ray bounds depend on the view's visible list (vk_set_view) and the pose only, not on the voxels: they are
+  // computed on the volume's side stream, where they overlap whatever the caller's stream is still doing
+  // (normally this frame's integration), and the ray march joins them.  ev_trace keeps the bounds scratch of the
+  // previous ray cast safe.
+  const bool capturing = stream_capturing(s);
+  const bool fork = !capturing && v->aux_valid && v->aux_stream && g_tune[VK_TUNE_TRACE_FORK].load() != 0;
+  cudaStream_t bs = s;
+  if (fork) {
+    bs = (cudaStream_t)v->aux_stream;
+    cudaError_t e = cudaStreamWaitEvent(bs, (cudaEvent_t)v->ev_view, 0);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(bs, (cudaEvent_t)v->ev_trace, 0);
+    if (e != cudaSuccess) return (int)e;
+  }
+  int rc = trace_bounds(v, view, min_depth, max_depth, bounds, bs);
   if (rc) return rc;
+  if (fork) {
+    cudaError_t e = cudaEventRecord((cudaEvent_t)v->ev_bounds, bs);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s, (cudaEvent_t)v->ev_bounds, 0);
+    if (e != cudaSuccess) return (int)e;
+  }
   rc = compute_points_mode(v->entries, v->voxels, v->sdf, bounds, v->bucket_bits, v->space_bits, v->main_blocks, VK_BLOCK_RES * v->voxel_length,
                            v->voxel_length, v->trunc_length, &view->depth_to_world, &view->depth_proj, out_depth,
                            out_color, view->depth_w, view->depth_h, VK_BOUNDS_W, VK_BOUNDS_H, v->math_mode, s,
@@ -1362,7 +1401,8 @@ extern "C" int vk_trace(const vkVolume* v, const vkFrame* view, float min_depth,
   if (rc) return rc;
   if (out_normal)
     rc = normals_mode(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, v->math_mode, s);
-  return rc;
+  if (rc) return rc;
+  return trace_done(v, s);
 }
 
 extern "C" int vk_trace_keys(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth,
@@ -1382,7 +1422,9 @@ extern "C" int vk_trace_keys(const vkVolume* v, const vkFrame* view, float min_d
   t.shard_rank = v->shard_rank;
   t.shard_count = v->shard_count;
   t.shard_shift = v->shard_shift;
-  return launch_raycast<true>(t, v->math_mode, s);
+  rc = launch_raycast<true>(t, v->math_mode, s);
+  if (rc) return rc;
+  return trace_done(v, s);
 }
 
 extern "C" int vk_resolve_keys(const unsigned long long* keys, const vkFrame* view, float* out_depth,
@@ -1447,7 +1489,8 @@ extern "C" int vk_trace_rows(const vkVolume* v, const vkPeerTable* peers, const 
   if (out_normal)
     rc = normals_mode(out_depth, &view->depth_proj, out_normal, view->depth_w, view->depth_h, v->math_mode, s,
                       row_begin, row_end);
-  return rc;
+  if (rc) return rc;
+  return trace_done(v, s);
 }
 
 // ---- block-sharded volume with replicated lookup structures (vk_shard.cu) --------------------------

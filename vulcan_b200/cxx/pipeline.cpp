@@ -5,6 +5,7 @@
 #include <vulcan/frame_pipeline.h>
 
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 
 namespace vulcan
@@ -95,12 +96,15 @@ int FramePipeline::Submit(const float* host_depth, const Frame& frame, const flo
   VULCAN_ASSERT_MSG(host_depth != nullptr, "missing depth image");
   VULCAN_ASSERT_MSG(!with_color_ || host_color != nullptr, "missing color image");
   const int k = next_;
+  // diagnostics only (VULCAN_PIPELINE_DEBUG): bit 0 = skip the downloads, bit 1 = skip the uploads
+  static const int debug = std::getenv("VULCAN_PIPELINE_DEBUG") ? std::atoi(std::getenv("VULCAN_PIPELINE_DEBUG")) : 0;
   Slot& s = *slots_[k % slots_.size()];
   if (s.frame >= 0) CUDA_ASSERT(cudaEventSynchronize(s.downloaded));  // the slot's previous frame has left the device
   s.frame = k;
   const size_t n = (size_t)width_ * height_;
   // upload
-  CUDA_ASSERT(cudaMemcpyAsync(s.in.depth_image->GetData(), host_depth, n * sizeof(float), cudaMemcpyHostToDevice, upload_));
+  if (!(debug & 2) || k < (int)slots_.size())
+    CUDA_ASSERT(cudaMemcpyAsync(s.in.depth_image->GetData(), host_depth, n * sizeof(float), cudaMemcpyHostToDevice, upload_));
   if (with_color_)
     CUDA_ASSERT(cudaMemcpyAsync(s.in.color_image->GetData(), host_color, 3 * n * sizeof(float), cudaMemcpyHostToDevice, upload_));
   CUDA_ASSERT(cudaEventRecord(s.uploaded, upload_));
@@ -118,9 +122,12 @@ int FramePipeline::Submit(const float* host_depth, const Frame& frame, const flo
   CUDA_ASSERT(cudaEventRecord(s.computed, compute_));
   // download
   CUDA_ASSERT(cudaStreamWaitEvent(download_, s.computed, 0));
-  CUDA_ASSERT(cudaMemcpyAsync(s.h_depth, s.out.depth_image->GetData(), n * sizeof(float), cudaMemcpyDeviceToHost, download_));
-  CUDA_ASSERT(cudaMemcpyAsync(s.h_color, s.out.color_image->GetData(), 3 * n * sizeof(float), cudaMemcpyDeviceToHost, download_));
-  CUDA_ASSERT(cudaMemcpyAsync(s.h_normal, s.out.normal_image->GetData(), 3 * n * sizeof(float), cudaMemcpyDeviceToHost, download_));
+  if (!(debug & 1))
+  {
+    CUDA_ASSERT(cudaMemcpyAsync(s.h_depth, s.out.depth_image->GetData(), n * sizeof(float), cudaMemcpyDeviceToHost, download_));
+    CUDA_ASSERT(cudaMemcpyAsync(s.h_color, s.out.color_image->GetData(), 3 * n * sizeof(float), cudaMemcpyDeviceToHost, download_));
+    CUDA_ASSERT(cudaMemcpyAsync(s.h_normal, s.out.normal_image->GetData(), 3 * n * sizeof(float), cudaMemcpyDeviceToHost, download_));
+  }
   CUDA_ASSERT(cudaEventRecord(s.downloaded, download_));
   next_ = k + 1;
   return k;
