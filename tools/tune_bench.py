@@ -95,6 +95,10 @@ def main():
         t[:, 3] &= (1 << 40) - 1
         c_la = t[:, 4] >> 40
         t[:, 4] &= (1 << 40) - 1
+        single_alu = (t[:, 5] >> 40) << 4     # single-step passes: cycles up to the filter load (max over lanes), and whole pass
+        single_all = (t[:, 6] >> 40) << 4
+        t[:, 5] &= (1 << 40) - 1
+        t[:, 6] &= (1 << 40) - 1
         t0 = t[:, 0].min()
         dur = (t[:, 1] - t[:, 0]) / 1e3
         end = (t[:, 1] - t0) / 1e3
@@ -109,7 +113,8 @@ def main():
                 (w_ % (W // 8)) * 8, (w_ // (W // 8)) * 4, start[w_], dur[w_], t[w_, 2] >> 32, t[w_, 2] & 0xffffffff,
                 t[w_, 3], t[w_, 3] / max(1, t[w_, 2] & 0xffffffff)))
             print("      cycles: free-run %d  of which cooperative runs %d  phase A %d  phase B %d  max-lane free steps %d cooperative ray-runs %d  mean live lanes %.1f" % (
-                t[w_, 4], c_la[w_], t[w_, 5], t[w_, 6], t[w_, 7] & 0xffffffff, t[w_, 7] >> 32, alive_sum[w_] / max(1, t[w_, 2] & 0xffffffff)))
+                t[w_, 4], c_la[w_], t[w_, 5], t[w_, 6], t[w_, 7] & 0xffff, (t[w_, 7] >> 16) & 0xffff, alive_sum[w_] / max(1, t[w_, 2] & 0xffffffff)))
+            print("      paired passes %d  single-step passes %d (cycles: %d up to the filter load, %d in all)" % ((t[w_, 7] >> 48) & 0xffff, (t[w_, 7] >> 32) & 0xffff, single_alu[w_], single_all[w_]))
         trips = (t[:, 2] & 0xffffffff).astype(np.float64)
         print("  all warps: trips total %d, cycles/trip mean %.0f" % (trips.sum(), t[:, 3].sum() / trips.sum()))
         np.save(os.path.join(ROOT, "gpurun_out", "trace_timeline.npy"), t)

@@ -16,7 +16,7 @@ extern std::atomic<int> g_default_math_mode;
 // Tuning knobs (vk_tune): launch shapes and batching thresholds, never results.
 enum { VK_TUNE_RAY_CTA_THREADS = 0, VK_TUNE_RAY_BATCH_LANES = 1, VK_TUNE_RAY_BATCH_WAIT = 2,
        VK_TUNE_INTEGRATE_CTAS_PER_SM = 3, VK_TUNE_ALLOC_MODE = 4, VK_TUNE_RAY_COOP_LANES = 5, VK_TUNE_DEBUG_X = 6, VK_TUNE_RAY_FREE_RUN = 7,
-       VK_TUNE_RAY_COOP_ROUNDS = 8, VK_TUNE_PDL = 9, VK_TUNE_RAY_SOA = 10, VK_TUNE_RAY_PAIR_AFTER = 11, VK_TUNE_RAY_WARM_SDF = 12, VK_TUNE_RAY_PAIR_FIRST = 13, VK_TUNE_INTEGRATE_BULK = 14, VK_TUNE_TRACE_FORK = 15, VK_TUNE_COUNT = 16 };
+       VK_TUNE_RAY_COOP_ROUNDS = 8, VK_TUNE_PDL = 9, VK_TUNE_RAY_SOA = 10, VK_TUNE_RAY_PAIR_AFTER = 11, VK_TUNE_RAY_WARM_SDF = 12, VK_TUNE_INTEGRATE_BULK = 14, VK_TUNE_TRACE_FORK = 15, VK_TUNE_COUNT = 16 };
 extern std::atomic<int> g_tune[VK_TUNE_COUNT];
 
 // rows 0..2 of a column-major 4x4 (vulcan::Matrix4f) as row-major 3x4

@@ -336,7 +336,6 @@ struct TraceParams {
   bool negated_hi;              // bounds cells hold (min, -max) (vk_trace_bounds / vk_trace_rows)
   int coop_lanes, coop_rounds;  // cooperative free-space runs when at most coop_lanes lanes are in free space
   int pair_after;               // trips after which a warp takes its free-space steps two at a time (0 = never)
-  int pair_first;               // such a warp takes up to this many paired steps BEFORE its cooperative runs
   Mod K;
   Div block_length, voxel_length;
   float trunc;
@@ -611,7 +610,8 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   int trips = 0;   // loop trips of this warp (warp-uniform)
   long long c_free = 0, c_a = 0, c_b = 0, c_t = 0, c_la = 0;
   int dbg_alive_sum = 0;
-  int dbg_steps = 0, dbg_rounds = 0;
+  int dbg_steps = 0, dbg_rounds = 0, dbg_pair = 0, dbg_single = 0;
+  long long dbg_c1 = 0, dbg_c2 = 0;
 
   float lo = 0.f, hi = 0.f;
   if (inside) {
@@ -707,6 +707,7 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
   // alongside the first one's and used only if the first step leaves the ray in free space
   auto pair_steps = [&](bool& freeing, int& bx, int& by, int& bz, int max_steps) {
     for (int n = 0; n < max_steps && __any_sync(0xffffffffu, freeing); n += 2) {
+      if (DIAG) ++dbg_pair;
       if (freeing) {
         Vec3 p1, p2;
         p1.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
@@ -756,10 +757,6 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     // waiting in other states are not starved.
     if (p.free_run > 0) {
       bool freeing = (state == ST_MARCH && !parked && !space_bit(p, bx, by, bz));
-      // Long warps, first: a few paired steps for ALL lanes in free space at once.  Near the surface a grazing
-      // ray leaves and re-enters the allocated band every few blocks; such short runs cost one pass here for
-      // every lane together, where a cooperative run (below) spends a 32-position evaluation per ray on them.
-      if (p.pair_first > 0 && trips > p.pair_after) pair_steps(freeing, bx, by, bz, p.pair_first);
       unsigned fmask = __ballot_sync(0xffffffffu, freeing);
       // Few lanes in free space (the tail of the kernel: a handful of rays that graze the
       // surface and then cross metres of empty space): all 32 lanes evaluate the next 32
@@ -815,9 +812,11 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       }
       if (timeline) c_la += clock64() - c_coop0;
       // Many lanes in free space: they take the steps together, one step per loop trip.
-      // (Measured and rejected on B200, see profiles/r01_raycast_tail.md: 4 positions per lane and
-      // trip, a brick-level map for 4-step jumps, one lane group per ray in the cooperative runs,
-      // several sampling steps per trip, a second pass for the rays that outlive their tile.)
+      // (Measured and rejected on B200, see profiles/r01_raycast_tail.md and profiles/r02_raycast_tail.md:
+      // 4 positions per lane and trip, a brick-level map for 4-step jumps, one lane group per ray in the
+      // cooperative runs, several sampling steps per trip, a second pass for the rays that outlive their
+      // tile, paired steps before the cooperative runs, deferring long free flights until no lane is near
+      // the surface.)
       // A warp that is still marching after pair_after trips is one of the few long ones (the average warp is
       // done after four): the machine is emptying, its own instruction stream is what the kernel waits for, and
       // that stream is a chain of dependent operations per step.  Such a warp takes its free-space steps in
@@ -826,6 +825,9 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
       // ray in free space - the same operations in the same order per ray, hence the same result.
       if (p.pair_after > 0 && trips > p.pair_after) pair_steps(freeing, bx, by, bz, p.free_run);
       for (int n = 0; n < p.free_run && __any_sync(0xffffffffu, freeing); ++n) {
+        if (DIAG) ++dbg_single;
+        const long long d0 = (DIAG && timeline) ? clock64() : 0;
+        long long d1 = d0;
         if (freeing) {
           ++dbg_steps;
           pt.x = FP<F>::mad(dir.x, p.block_length.d, pt.x);
@@ -835,8 +837,14 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
           freeing = false;
           if (state == ST_MARCH) {
             block_of(pt, bx, by, bz);
+            if (DIAG && timeline) d1 = clock64() + (bx & 0);
             freeing = !space_bit(p, bx, by, bz);
           }
+        }
+        if (DIAG && timeline) {
+          const long long d2 = clock64() + (freeing ? 0 : 0);
+          dbg_c1 += __reduce_max_sync(0xffffffffu, (int)(d1 - d0));
+          dbg_c2 += (int)(d2 - d0);
         }
       }
     }
@@ -910,9 +918,10 @@ __global__ void __launch_bounds__(kMaxRayThreads, 16) vk_raycast_kernel(const Tr
     timeline[8 * wid + 2] = ((unsigned long long)smid << 32) | (unsigned)dbg_trips;
     timeline[8 * wid + 3] = (unsigned long long)(clock64() - c_start) | ((unsigned long long)dbg_alive_sum << 40);
     timeline[8 * wid + 4] = (unsigned long long)c_free | ((unsigned long long)c_la << 40) ;
-    timeline[8 * wid + 5] = (unsigned long long)c_a;
-    timeline[8 * wid + 6] = (unsigned long long)c_b;
-    timeline[8 * wid + 7] = ((unsigned long long)dbg_rounds << 32) | (unsigned)dbg_steps;
+    timeline[8 * wid + 5] = (unsigned long long)c_a | ((unsigned long long)(dbg_c1 >> 4) << 40);
+    timeline[8 * wid + 6] = (unsigned long long)c_b | ((unsigned long long)(dbg_c2 >> 4) << 40);
+    timeline[8 * wid + 7] = ((unsigned long long)(dbg_pair & 0xffff) << 48) | ((unsigned long long)(dbg_single & 0xffff) << 32) |
+                            ((unsigned long long)(dbg_rounds & 0xffff) << 16) | (unsigned)(dbg_steps & 0xffff);
   }
   if (!inside) return;
   // colour of the last interpolation (Q13: kept even on a miss), evaluated once per ray
@@ -1209,7 +1218,6 @@ static void fill_trace_params(TraceParams& t, const vkHashEntry* entries, const 
   t.coop_lanes = g_tune[VK_TUNE_RAY_COOP_LANES].load();
   t.coop_rounds = g_tune[VK_TUNE_RAY_COOP_ROUNDS].load();
   t.pair_after = g_tune[VK_TUNE_RAY_PAIR_AFTER].load();
-  t.pair_first = t.pair_after > 0 ? g_tune[VK_TUNE_RAY_PAIR_FIRST].load() : 0;
   t.negated_hi = false;
   t.K = make_mod((uint32_t)K);
   t.block_length = make_div(block_length, s);
