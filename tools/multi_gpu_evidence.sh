@@ -11,7 +11,7 @@ for c in $CONFIGS; do
   grep -E "rror|Traceback" gpurun_out/sharded_check_${N}gpu_${c}.log | head -5
   port=$((port+1))
 done
-timeout 300 $RUN --master-port 29531 bench.py --gpus $N --steps 40 --warmup 5 > gpurun_out/bench_ours_${N}gpu.json 2> gpurun_out/bench_ours_${N}gpu.err
+timeout 300 $RUN --master-port 29531 bench.py --gpus $N --steps 20 --warmup 5 > gpurun_out/bench_ours_${N}gpu.json 2> gpurun_out/bench_ours_${N}gpu.err
 python - $N <<'PY'
 import json, sys
 n = sys.argv[1]

@@ -9,9 +9,9 @@ mkdir -p gpurun_out
 if [ "$1" != "skip-tests" ]; then
   (timeout 1800 python -m pytest tests -m gpu -q -x 2>&1 | tail -15) > gpurun_out/pytest_gpu.log; cat gpurun_out/pytest_gpu.log
 fi
-timeout 300 python bench.py --impl reference --steps 40 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
-timeout 300 python bench.py --steps 40 --warmup 5 > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err
-timeout 300 python bench.py --impl reference --ref-variant asshipped --steps 40 --warmup 5 --no-cpu-baseline \
+timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
+timeout 300 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_ours.json 2> gpurun_out/bench_ours.err
+timeout 300 python bench.py --impl reference --ref-variant asshipped --steps 20 --warmup 5 --no-cpu-baseline \
     > gpurun_out/bench_ref_asshipped.json 2> gpurun_out/bench_ref_asshipped.err
 python - <<'PY'
 import json
