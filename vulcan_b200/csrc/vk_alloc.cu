@@ -67,13 +67,23 @@ __device__ __forceinline__ int find_block(const vkHashEntry* entries, uint32_t h
   }
 }
 
-__device__ __forceinline__ void touch_entry(const AllocParams& p, int idx) {
+// New entries of the visible list are collected per CTA in shared memory and appended with ONE atomicAdd on the
+// list's counter when the CTA retires (~16 k same-address atomics with a dependent store each
+// were serialising in L2).  A CTA that finds more than kNewCap falls back to direct appends for the rest.
+constexpr int kNewCap = 384;
+
+__device__ __forceinline__ void touch_entry(const AllocParams& p, int idx, int* s_new, int* s_count) {
   if (__ldcg(p.stamps + idx) != p.view_id) {
     const int old = atomicExch(p.stamps + idx, p.view_id);
     if (old != p.view_id) {
       p.visibility[idx] = VK_VIS_TRUE;
-      const int pos = atomicAdd(p.counters + p.cnt_slot, 1);
-      p.visible_out[pos] = idx;
+      const int at = atomicAdd(s_count, 1);
+      if (at < kNewCap) {
+        s_new[at] = idx;
+      } else {
+        const int pos = atomicAdd(p.counters + p.cnt_slot, 1);
+        p.visible_out[pos] = idx;
+      }
     }
   }
 }
@@ -172,11 +182,14 @@ __device__ __noinline__ int insert_block(const AllocParams& p, uint32_t h, int b
 //   tmax  = (L*(b + max(0,step)) - begin) / dir     FFMA bf*L - begin ; IEEE div
 template <bool F>
 __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
+  __shared__ int s_new[kNewCap];
+  __shared__ int s_count, s_base;
+  if (threadIdx.x == 0) s_count = 0;
+  __syncthreads();
   pdl_wait();     // the previous kernel of the chain has completed (no-op for a plain launch)
   pdl_trigger();  // the next one may be scheduled as this grid drains
   const int lane = threadIdx.x & 31;
-  // warp tile 8x4 pixels; the warps of the grid take the tiles row by row (the kernel has no
-  // CTA-level state, so the CTA size only sets the granularity of the waves)
+  // warp tile 8x4 pixels; the warps of the grid take the tiles row by row
   const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int tiles_x = (p.w + 7) >> 3;
   const int x = (tile % tiles_x) * 8 + (lane & 7);
@@ -248,7 +261,7 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
         if (shard_stores(bx, by, bz, p.shard_shift, p.shard_count, p.shard_rank, p.shard_halo)) idx = insert_block(p, h, bx, by, bz, key);
         else mark_space(p, bx, by, bz);  // exists on another rank: the filter is global
       }
-      if (idx >= 0 && !(idx == (int)h && head_stamp == p.view_id)) touch_entry(p, idx);
+      if (idx >= 0 && !(idx == (int)h && head_stamp == p.view_id)) touch_entry(p, idx, s_new, &s_count);
     }
     if (active) {
       // Amanatides-Woo step with the reference's comparison tree (src/volume.cu:241-295)
@@ -261,6 +274,12 @@ __global__ void __launch_bounds__(256) vk_alloc_kernel(const AllocParams p) {
       }
     }
   }
+  // the CTA's new entries: one append
+  __syncthreads();
+  const int n_new = min(s_count, kNewCap);
+  if (threadIdx.x == 0 && n_new > 0) s_base = atomicAdd(p.counters + p.cnt_slot, n_new);
+  __syncthreads();
+  for (int i = threadIdx.x; i < n_new; i += blockDim.x) p.visible_out[s_base + i] = s_new[i];
 }
 
 struct CarryParams {
