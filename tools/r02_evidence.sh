@@ -52,3 +52,9 @@ timeout 300 python tools/ray_ab.py --phase integrate --sets "14=0;14=1" --out in
 timeout 900 python tools/config_bench.py > gpurun_out/config_bench.log 2> gpurun_out/config_bench.err; tail -c 2500 gpurun_out/config_bench.log
 timeout 300 python tools/extract_bench.py > gpurun_out/extract_bench.json 2> gpurun_out/extract_bench.err; tail -c 800 gpurun_out/extract_bench.json
 timeout 300 python tools/track_bench.py > gpurun_out/track_bench.json 2> gpurun_out/track_bench.err; tail -c 800 gpurun_out/track_bench.json
+# the extraction kernels (points + faces) of the final tree, one full capture each
+ncu --set full --clock-control none -k regex:"vk_extract" -s 2 -c 3 -o gpurun_out/prof_extract -f \
+    python tools/extract_bench.py > gpurun_out/ncu_extract.log 2>&1
+ncu -i gpurun_out/prof_extract.ncu-rep --page raw --csv > gpurun_out/prof_extract_raw.csv 2>/dev/null
+python tools/ncu_summary.py gpurun_out/prof_extract_raw.csv > gpurun_out/ncu_extract_summary.csv
+rm -f gpurun_out/prof_extract.ncu-rep gpurun_out/prof_extract_raw.csv
