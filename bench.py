@@ -390,18 +390,83 @@ def run_ours(args, rank, world):
         cxx.vulcan_pipeline_destroy(h)
         return t, acc.value
 
+    def e2e_streamed_sharded():
+        """vulcan::ShardedPipeline (include/vulcan/sharded_pipeline.h, C++ host) on every rank through ONE C entry
+        point, vulcan_sharded_pipeline_run: upload of frame k+1, SetView + Integrate + sharded Trace of frame k and the
+        download of this rank's band of frame k-1 overlap; the host takes frame k-2's band (and reads a pixel of each
+        image in it) after submitting frame k.  No image is exchanged between the GPUs; torch.distributed only
+        carries the CUDA IPC handles once."""
+        cxx = C.CDLL(os.path.join(ROOT, "vulcan_b200", "libvulcan.so"))
+        cxx.vulcan_sharded_pipeline_create.restype = C.c_void_p
+        cxx.vulcan_sharded_pipeline_create.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, C.c_int,
+                                                       C.c_int, C.c_int]
+        cxx.vulcan_sharded_pipeline_export.argtypes = [C.c_void_p, C.c_void_p]
+        cxx.vulcan_sharded_pipeline_connect.argtypes = [C.c_void_p, C.c_void_p]
+        cxx.vulcan_sharded_pipeline_run.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_int,
+                                                    C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int)]
+        cxx.vulcan_sharded_pipeline_destroy.argtypes = [C.c_void_p]
+        cxx.vulcan_sharded_pipeline_error.restype = C.c_char_p
+        cxx.vulcan_sharded_pipeline_error.argtypes = [C.c_void_p]
+        depth = max(3, args.pipeline_depth)
+        h = cxx.vulcan_sharded_pipeline_create(MAIN, EXCESS, VOXEL, TRUNC, W, H, depth, rank, world)
+        assert h, "vulcan_sharded_pipeline_create failed"
+        nb = cxx.vulcan_shard_handles_bytes()
+        mine = C.create_string_buffer(nb)
+        assert cxx.vulcan_sharded_pipeline_export(h, mine) == 0, cxx.vulcan_sharded_pipeline_error(h)
+        blobs = [mine.raw]
+        if world > 1:
+            blobs = [None] * world
+            dist.all_gather_object(blobs, mine.raw)
+        everyone = C.create_string_buffer(b"".join(blobs), nb * world)
+        assert cxx.vulcan_sharded_pipeline_connect(h, everyone) == 0, cxx.vulcan_sharded_pipeline_error(h)
+        barrier()
+        ptrs = (C.c_void_p * nfr)(*[t.data_ptr() for t in pinned_in])   # page-locked host images
+        all_poses = np.ascontiguousarray(np.stack([T for _, T in frames]), dtype=np.float32)
+        proj = np.ascontiguousarray(K, dtype=np.float32)
+        acc = C.c_double(0)
+        sub = (C.c_double * nfr)()
+        rows = (C.c_int * nfr)()
+
+        def run(first, count):
+            sub_at = C.cast(C.addressof(sub) + 8 * first, C.POINTER(C.c_double))
+            rows_at = C.cast(C.addressof(rows) + 4 * first, C.POINTER(C.c_int))
+            rc = cxx.vulcan_sharded_pipeline_run(h, count, C.cast(C.addressof(ptrs) + 8 * first, C.POINTER(C.c_void_p)),
+                                                 proj.ctypes.data, all_poses[first:].ctypes.data, 2, C.byref(acc), sub_at, rows_at)
+            assert rc == 0, cxx.vulcan_sharded_pipeline_error(h)
+
+        run(0, args.warmup)
+        barrier()
+        t0 = time.perf_counter()
+        run(args.warmup, args.steps)
+        barrier()
+        t = time.perf_counter() - t0
+        band_rows.clear()
+        band_rows.extend(int(rows[i]) for i in range(args.warmup, nfr))
+        host_submit.clear()
+        host_submit.extend([0.0] * args.warmup + [sub[i] * 1e-6 for i in range(args.warmup, nfr)])
+        barrier()
+        cxx.vulcan_sharded_pipeline_destroy(h)
+        barrier()
+        return t, acc.value
+
     barrier()
     t_sync = e2e_sync()
-    e2e_mode = "sync"
-    t_e2e = t_sync
-    if world == 1:
+    if world == 1 and os.environ.get("BENCH_FORCE_SHARDED_E2E"):   # diagnostics: a single-rank sharded pipeline
+        del vol
+        torch.cuda.empty_cache()
+        t_e2e, _ = e2e_streamed_sharded()
+    elif world == 1:
         del vol
         torch.cuda.empty_cache()
         barrier()
         t_e2e, _ = e2e_streamed()   # the C++ pipeline owns its volume
-        e2e_mode = "streamed"
     else:
         drop_volume(vol)
+        del vol
+        torch.cuda.empty_cache()
+        barrier()
+        t_e2e, _ = e2e_streamed_sharded()
+    e2e_mode = "streamed"
     t_e2e_t = torch.tensor([t_e2e, t_sync], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_e2e_t, op=dist.ReduceOp.MAX)
@@ -437,6 +502,12 @@ def run_ours(args, rank, world):
                          "SetView+Integrate+Trace, traced depth+colour+normal -> pinned host; copies of neighbouring "
                          "frames overlap the kernels; the host takes (and reads a pixel of) frame k-%d's images after "
                          "submitting frame k" % (args.pipeline_depth, args.pipeline_depth - 1))
+                if (e2e_mode == "streamed" and world == 1) else
+                ("vulcan::ShardedPipeline (C++ host, include/vulcan/sharded_pipeline.h) on every rank through the C entry point "
+                 "vulcan_sharded_pipeline_run (%d frames in flight): every frame's pinned host depth -> device on "
+                 "every rank, SetView+Integrate+sharded Trace (each rank renders its band of rows, no image exchange), the "
+                 "rank's band of depth+colour+normal -> pinned host; copies of neighbouring frames overlap the kernels; the "
+                 "host takes (and reads a pixel of) frame k-2's band after submitting frame k" % max(3, args.pipeline_depth))
                 if e2e_mode == "streamed" else
                 ("pinned host depth -> device on every rank, SetView+Integrate+Trace (each rank renders its band of rows), "
                  "each rank's band of depth+colour+normal -> pinned host, sync every step" if world > 1 else

@@ -24,6 +24,7 @@
 #include <vulcan/projection.h>
 #include <vulcan/pyramid_tracker.h>
 #include <vulcan/sharded_tracer.h>
+#include <vulcan/sharded_pipeline.h>
 #include <vulcan/tracer.h>
 #include <vulcan/tracer.cuh>
 #include <vulcan/tracker.h>

@@ -397,6 +397,11 @@ int vk_trace_sharded_staged(vkVolume* v, const vkFrame* view, float min_depth, f
  * computed on the device from the merged ray bounds).  VK_E_TIMEOUT if a handshake of this rank was ever
  * given up (a peer did not arrive within ~2 s; the images of that view are incomplete). */
 int vk_shard_band(const vkVolume* v, int* band_begin, int* band_end, void* stream);
+/* The same without synchronising, for streaming hosts: enqueues on `stream` the copy of the LAST traced view's band
+ * table into host_bands[0..16) (page-locked; rank r renders rows [host_bands[r], host_bands[r+1])) and of the count of
+ * handshakes given up into host_bands[16] (non-zero = VK_E_TIMEOUT).  The table of a view stays valid until the
+ * second-next vk_trace_sharded of the volume. */
+int vk_shard_band_async(const vkVolume* v, int* host_bands /* [17] */, void* stream);
 
 /* Rank that owns block (bx, by, bz) when a volume is split over `count` ranks: a pure function
  * of the brick (bx >> shift, by >> shift, bz >> shift).  Host function; the kernels use the

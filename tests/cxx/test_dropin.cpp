@@ -609,6 +609,81 @@ static void TestShardedTracer()
   CHECK(volumes[0]->GetAllocatedBlockCount() + volumes[1]->GetAllocatedBlockCount() == whole->GetAllocatedBlockCount());
 }
 
+// vulcan::ShardedPipeline with ONE rank (its band is the whole image, the handshakes are trivial): the streamed bands
+// equal the synchronous unsharded images, results taken two frames late.  (Several ranks need a GPU each:
+// bench.py --gpus N drives the same class through vulcan_sharded_pipeline_run.)
+static void TestShardedPipeline()
+{
+  const int w = 160, h = 120, frames = 8;
+  const size_t n = (size_t)w * h;
+  Projection projection;
+  projection.SetFocalLength(80, 80);
+  projection.SetCenterPoint(80, 60);
+  std::vector<float*> depths;
+  std::vector<Frame> metas;
+  for (int k = 0; k < frames; ++k)
+  {
+    float* d = FramePipeline::AllocHost(n);
+    for (size_t i = 0; i < n; ++i) d[i] = 1.5f - 0.01f * k + 0.0005f * (float)(i % w);
+    depths.push_back(d);
+    Frame f;
+    f.depth_projection = projection;
+    f.depth_to_world_transform = Transform::Translate(0.31f + 0.004f * k, 0.27f, 0.19f);
+    metas.push_back(f);
+  }
+  auto make = [&](std::shared_ptr<Volume>& volume, std::shared_ptr<DepthIntegrator>& integrator)
+  {
+    volume = std::make_shared<Volume>(8192, 2048);
+    volume->SetVoxelLength(0.008f);
+    volume->SetTruncationLength(0.04f);
+    integrator = std::make_shared<DepthIntegrator>(volume);
+  };
+  std::shared_ptr<Volume> volume;
+  std::shared_ptr<DepthIntegrator> integrator;
+  make(volume, integrator);
+  Tracer tracer(volume);
+  std::vector<std::vector<float>> want_d(frames, std::vector<float>(n)), want_n(frames, std::vector<float>(3 * n));
+  for (int k = 0; k < frames; ++k)
+  {
+    Frame f = metas[k];
+    f.depth_image = std::make_shared<Image>(w, h);
+    f.depth_image->CopyFromHost(depths[k]);
+    volume->SetView(f);
+    integrator->Integrate(f);
+    Frame traced;
+    traced.depth_projection = projection;
+    traced.depth_to_world_transform = f.depth_to_world_transform;
+    traced.depth_image = std::make_shared<Image>(w, h);
+    tracer.Trace(traced);
+    traced.depth_image->CopyToHost(want_d[k].data());
+    traced.normal_image->CopyToHost(want_n[k].data());
+  }
+  make(volume, integrator);
+  {
+    auto sharded = std::make_shared<ShardedTracer>(volume, 0, 1, w, h);
+    ShardedPipeline pipeline(volume, integrator, sharded, w, h, 3);
+    auto check = [&](int k)
+    {
+      const ShardedPipeline::Band b = pipeline.Result(k);
+      CHECK(b.begin == 0 && b.end == h);
+      CHECK(std::memcmp(b.depth, want_d[k].data(), n * sizeof(float)) == 0);
+      CHECK(std::memcmp(b.normal, want_n[k].data(), 3 * n * sizeof(float)) == 0);
+    };
+    for (int k = 0; k < frames; ++k)
+    {
+      CHECK(pipeline.Submit(depths[k], metas[k]) == k);
+      if (k >= 2) check(k - 2);
+    }
+    check(frames - 2);
+    check(frames - 1);
+    pipeline.Drain();
+    bool threw = false;
+    try { pipeline.Result(0); } catch (const Exception&) { threw = true; }
+    CHECK(threw);
+  }
+  for (float* d : depths) FramePipeline::FreeHost(d);
+}
+
 int main()
 {
   struct { const char* name; void (*fn)(); } tests[] = {
@@ -616,7 +691,7 @@ int main()
     {"Tracer.TraceWall", TestTraceWall}, {"Volume.TwoVolumes", TestTwoVolumes},
     {"Frame.Downsample", TestDownsample}, {"DepthTracker.Wall", TestDepthTrackerWall},
     {"Extractor.Wall", TestExtractWall}, {"FramePipeline", TestFramePipeline},
-    {"ShardedTracer", TestShardedTracer},
+    {"ShardedTracer", TestShardedTracer}, {"ShardedPipeline", TestShardedPipeline},
   };
   for (auto& t : tests)
   {

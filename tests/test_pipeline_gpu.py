@@ -73,3 +73,61 @@ def test_pipeline_matches_synchronous_calls(depth):
     assert want[-1][0].max() > 0  # something was hit
     with pytest.raises(vb.VulcanError):
         pipe.result(0 if depth < len(frames) else 10_000)
+
+
+def test_sharded_pipeline_single_rank_matches_synchronous_calls():
+    """sharding.ShardedPipeline with ONE rank (its band is the whole image, the handshakes are trivial): the
+    streamed bands equal the synchronous unsharded images bit for bit, frame by frame, with results taken two
+    frames late.  (Several ranks need one GPU each: tools/sharded_check.py and bench.py --gpus N.)"""
+    import torch
+    import vulcan_b200 as vb
+    from vulcan_b200 import sharding
+
+    K, frames = _frames(8)
+
+    def volume():
+        vol = vb.Volume(32768, 8192)
+        vol.SetVoxelLength(0.008)
+        vol.SetTruncationLength(0.04)
+        return vol
+
+    vol = volume()
+    integ, tracer = vb.DepthIntegrator(vol), vb.Tracer(vol)
+    want = []
+    for d, T in frames:
+        f = _meta(vb, K, T)
+        f.depth_image = torch.from_numpy(d).cuda()
+        vol.SetView(f)
+        integ.Integrate(f)
+        o = _meta(vb, K, T)
+        o.depth_image = torch.zeros((Hh, W), dtype=torch.float32, device="cuda")
+        tracer.Trace(o)
+        want.append((o.depth_image.cpu().numpy(), o.color_image.cpu().numpy(), o.normal_image.cpu().numpy()))
+    torch.cuda.synchronize()
+
+    vol2 = volume()
+    shard = sharding.Shard(vol2, 0, 1, W, Hh)
+    pipe = sharding.ShardedPipeline(shard, vb.DepthIntegrator(vol2), W, Hh, depth=3)
+    pinned = [torch.from_numpy(d).pin_memory() for d, _ in frames]
+    got = {}
+
+    def take(j):
+        b0, b1, hd, hc, hn = pipe.result(j)
+        assert (b0, b1) == (0, Hh)
+        got[j] = (hd.numpy().copy(), hc.numpy().copy(), hn.numpy().copy())
+
+    for k, (d, T) in enumerate(frames):
+        pipe.submit(pinned[k], _meta(vb, K, T))
+        if k >= 2:
+            take(k - 2)
+    take(len(frames) - 2)
+    take(len(frames) - 1)
+    pipe.drain()
+    for k in range(len(frames)):
+        for a, b, name in zip(want[k], got[k], ("depth", "color", "normal")):
+            assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), (k, name)
+    with pytest.raises(vb.VulcanError):
+        pipe.result(0)
+    shard.close()
+    with pytest.raises(vb.VulcanError):
+        sharding.ShardedPipeline(shard, vb.DepthIntegrator(vol2), W, Hh, depth=2)

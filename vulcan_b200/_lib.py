@@ -127,6 +127,7 @@ SYMBOLS = {
     "vk_trace_sharded_staged": [C.POINTER(vkVolume), C.POINTER(vkFrame), _F, _F, _I, _I, C.POINTER(_P), C.POINTER(_P),
                                 C.POINTER(_P), _P],
     "vk_shard_band": [C.POINTER(vkVolume), C.POINTER(_I), C.POINTER(_I), _P],
+    "vk_shard_band_async": [C.POINTER(vkVolume), _P, _P],
     "vk_downsample_frame": [C.POINTER(vkFrame), C.POINTER(vkFrame), _P],
     "vk_downsample_image": [_P, _I, _I, _I, _I, _P, _P],
     "vk_track_residuals": [C.POINTER(vkFrame), C.POINTER(vkFrame), _P, _P],

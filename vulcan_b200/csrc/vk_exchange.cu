@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(256) vk_push_bands_kernel(const Xchg x, int w,
   const size_t seg_off[3] = {row0, plane + 3 * row0, 4 * plane + 3 * row0};
   const size_t seg_n[3] = {rows, 3 * rows, 3 * rows};
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nthr = (size_t)gridDim.x * blockDim.x;
-  for (int r = 0; r < x.count && (x.stages & 1); ++r) {
+  for (int r = 0; r < x.count && xchg_stores(x.stages); ++r) {
     if (r == x.rank) continue;
     float* dst = xchg_images(x.buf[r], x.parity, w, h);
     for (int sgm = 0; sgm < 3; ++sgm) {
@@ -42,8 +42,9 @@ __global__ void __launch_bounds__(256) vk_push_bands_kernel(const Xchg x, int w,
       }
     }
   }
+  if (x.stages == 4) return;   // store-only launch: the handshake follows in the next one (kernel boundary = fence)
   __shared__ bool last;
-  __threadfence_system();
+  if (!(x.stages & 8)) __threadfence_system();
   __syncthreads();
   int* ticket = xchg_ticket(mine) + 1;
   if (threadIdx.x == 0) last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
@@ -55,7 +56,8 @@ __global__ void __launch_bounds__(256) vk_push_bands_kernel(const Xchg x, int w,
 
 int exchange_push_bands(const Xchg& x, int w, int h, cudaStream_t s) {
   // (wait-only stage of ranks that share a GPU: one CTA, the peers have all announced by then)
-  launch_chained(vk_push_bands_kernel, dim3((x.stages & 1) ? sm_count() * 2 : 1), dim3(256), 0, s, x, w, h);
+  if (x.stages & 8) vk_push_bands_kernel<<<1, 256, 0, s>>>(x, w, h);   // plain launch: see trace_sharded_bounds
+  else launch_chained(vk_push_bands_kernel, dim3(xchg_stores(x.stages) ? sm_count() * 2 : 1), dim3(256), 0, s, x, w, h);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }

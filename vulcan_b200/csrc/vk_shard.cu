@@ -195,25 +195,30 @@ static int trace_sharded(vkVolume* v, const vkFrame* view, float min_depth, floa
   int rc = 0;
   // 1. ray bounds of the local visible blocks, combined over the ranks; row bands (also the barrier that
   //    orders every rank's replica stores before any rank's ray cast)
+  //    One rank per GPU: the grid is stored into the peers by one launch and announced by the next - the kernel
+  //    boundary orders the stores before the flags without a system-scope fence (vk_shard.cuh).
   if (stage == 0 || stage == 1) {
-    x.stages = (stage == 0) ? 3 : 1;
+    x.stages = (stage == 0) ? 4 : 1;
     rc = trace_sharded_bounds(v, view, min_depth, max_depth, x, st);
     if (rc) return rc;
   }
   if (stage == 0 || stage == 2) {
-    if (stage == 2) {
-      x.stages = 2;
-      rc = trace_sharded_bounds(v, view, min_depth, max_depth, x, st);
-      if (rc) return rc;
-    }
+    x.stages = (stage == 0) ? (1 | 2 | 8) : 2;
+    rc = trace_sharded_bounds(v, view, min_depth, max_depth, x, st);
+    if (rc) return rc;
     // 2. this rank's band: ray march (+2 rows either side) and normals, all reads local
     rc = trace_sharded_band(v, view, x, depth, color, normal, st);
     if (rc) return rc;
     // 3. the band into the peers' images, handshake
     if (gather) {   // (a single rank: nothing to store, the handshake is trivial)
-      x.stages = (stage == 0) ? 3 : 1;
+      x.stages = (stage == 0) ? 4 : 1;
       rc = exchange_push_bands(x, s->width, s->height, st);
       if (rc) return rc;
+      if (stage == 0) {
+        x.stages = 1 | 2 | 8;
+        rc = exchange_push_bands(x, s->width, s->height, st);
+        if (rc) return rc;
+      }
     }
   }
   if (stage == 3 && gather) {
@@ -252,3 +257,16 @@ extern "C" int vk_shard_band(const vkVolume* v, int* band_begin, int* band_end, 
   *band_end = bands[s->rank + 1];
   return timeouts ? VK_E_TIMEOUT : 0;
 }
+
+extern "C" int vk_shard_band_async(const vkVolume* v, int* host_bands, void* stream) {
+  if (!v || !v->shard || !host_bands) return VK_E_INVALID;
+  const vkShard* s = v->shard;
+  if (s->epoch <= 0) return VK_E_INVALID;
+  cudaError_t err = cudaMemcpyAsync(host_bands, xchg_bands(s->exchange[s->rank], s->epoch & 1), 16 * sizeof(int),
+                                    cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (err == cudaSuccess)
+    err = cudaMemcpyAsync(host_bands + 16, xchg_timeouts(s->exchange[s->rank]), sizeof(int), cudaMemcpyDeviceToHost,
+                          (cudaStream_t)stream);
+  return (int)err;
+}
+

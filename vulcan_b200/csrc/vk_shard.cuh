@@ -49,9 +49,14 @@ __host__ __device__ inline float* xchg_normal(void* buf, int parity, int w, int 
 // kernel-parameter view of the ranks' buffers for one collective
 struct Xchg {
   int count, rank, epoch, parity;
-  int stages;   // bit 0: store + announce, bit 1: wait + consume.  3 = both in one kernel (one rank per GPU);
-                // ranks that SHARE a GPU run the two halves as separate launches, all announcements first
-                // (vk_trace_sharded_staged): kernels of one device must never wait for one another
+  int stages;   // bit 0: store + announce, bit 1: wait + consume.  Ranks that SHARE a GPU run the two halves as
+                // separate launches, all announcements first (vk_trace_sharded_staged): kernels of one device must
+                // never wait for one another.  One rank per GPU (vk_trace_sharded) uses two launches as well, for
+                // another reason: bit 2 (alone) = store only, then a second launch with bits 0 | 1 | 3 =
+                // announce + wait + consume, where bit 3 says "what is announced was stored by an EARLIER launch":
+                // the kernel boundary orders those stores before the flags, so no system-scope fence is needed.
+                // (A system-scope fence waits for the GPU's outstanding PCIe traffic too: with a download of the
+                // previous frame in flight it cost the streamed pipeline 30-70 us per view.)
   void* buf[VK_MAX_SHARDS];
 };
 
@@ -64,6 +69,11 @@ __device__ __forceinline__ int ld_acquire_sys(const int* p) {
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys(int* p, int v) {
+  asm volatile("st.relaxed.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// what a launch with these stage bits stores into the peers itself
+__host__ __device__ inline bool xchg_stores(int stages) { return (stages & 4) || ((stages & 1) && !(stages & 8)); }
 
 // One CTA: "what this rank stored into its peers' buffers for `epoch` is complete" -> every peer, then
 // wait until every peer has said the same to this rank.  The stores being announced were issued by
@@ -71,12 +81,17 @@ __device__ __forceinline__ void st_release_sys(int* p, int v) {
 // the flags for observers on other GPUs.  Announcing never waits and precedes the wait, so ranks
 // cannot wait for each other in a cycle.
 __device__ __forceinline__ void xchg_handshake(const Xchg& x, bool bands) {
-  __threadfence_system();
+  const bool ordered = (x.stages & 8) != 0;   // the announced stores belong to an earlier launch
+  if (!ordered) {
+    if (x.count > 1) __threadfence_system();   // (a lone rank has nobody to publish to)
+    else __threadfence();
+  }
   __syncthreads();
   const int t = threadIdx.x;
   if ((x.stages & 1) && t < x.count && t != x.rank) {
     int* theirs = (bands ? xchg_bands_flags(x.buf[t], x.parity) : xchg_bounds_flags(x.buf[t], x.parity)) + x.rank;
-    st_release_sys(theirs, x.epoch);
+    if (ordered) st_relaxed_sys(theirs, x.epoch);
+    else st_release_sys(theirs, x.epoch);
   }
   if ((x.stages & 2) && t < x.count && t != x.rank) {
     const int* mine = (bands ? xchg_bands_flags(x.buf[x.rank], x.parity) : xchg_bounds_flags(x.buf[x.rank], x.parity)) + t;

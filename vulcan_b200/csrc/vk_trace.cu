@@ -129,12 +129,13 @@ __device__ __forceinline__ BlockBox block_box(const int4& ent, const Mat34& Tcw,
 // rank's ray cast.
 __device__ __forceinline__ void bounds_exchange(const BoundsParams& p, float* s_cells) {
   const int ncell = p.bw * p.bh, nf = 2 * ncell;
-  if (p.x.stages & 1)
+  if (xchg_stores(p.x.stages))
     for (int r = 0; r < p.x.count; ++r) {
       if (r == p.x.rank) continue;
       float* slot = xchg_bounds_slot(p.x.buf[r], p.x.parity, p.x.rank);
       for (int i = threadIdx.x; i < nf; i += blockDim.x) slot[i] = __ldcg(p.bounds + i);
     }
+  if (p.x.stages == 4) return;   // store-only launch: the announcement follows in the next one
   xchg_handshake(p.x, false);
   if (!(p.x.stages & 2)) return;
   // the same grid on every rank
@@ -1508,7 +1509,7 @@ namespace vk {
 int trace_sharded_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, const Xchg& x,
                          cudaStream_t s) {
   // the working grid lives in this rank's exchange buffer, cells as (min depth, -max depth)
-  if (x.stages & 1) return trace_bounds(v, view, min_depth, max_depth, xchg_grid(x.buf[x.rank]), s, true, &x);
+  if (xchg_stores(x.stages)) return trace_bounds(v, view, min_depth, max_depth, xchg_grid(x.buf[x.rank]), s, true, &x);
   // second half only (the first half ran in an earlier launch)
   BoundsParams b;
   fill_bounds_params(b, view->depth_to_world.inv, &view->depth_proj, VK_BLOCK_RES * v->voxel_length, min_depth, max_depth,
@@ -1517,7 +1518,10 @@ int trace_sharded_bounds(const vkVolume* v, const vkFrame* view, float min_depth
   b.has_x = 1;
   b.x = x;
   const size_t smem = (size_t)VK_BOUNDS_W * VK_BOUNDS_H * 2 * sizeof(float) + 64 * sizeof(int);
-  launch_chained(vk_bounds_merge_kernel, dim3(1), dim3(512), smem, s, b);
+  // "ordered" second launch (bit 3): a plain launch - the full kernel boundary is what orders the first launch's
+  // peer stores before the flags; a programmatic dependent launch only promises visibility to this grid
+  if (x.stages & 8) vk_bounds_merge_kernel<<<1, 512, smem, s>>>(b);
+  else launch_chained(vk_bounds_merge_kernel, dim3(1), dim3(512), smem, s, b);
   VK_COUNT_LAUNCH();
   return (int)cudaGetLastError();
 }

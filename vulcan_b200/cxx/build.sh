@@ -4,10 +4,10 @@ set -e
 ROOT="$(cd "$(dirname "$0")/../.." && pwd)"
 CUDA="${CUDA_HOME:-/usr/local/cuda}"
 OUT="$ROOT/vulcan_b200"
-SRC="$ROOT/vulcan_b200/cxx/vulcan.cpp $ROOT/vulcan_b200/cxx/pipeline.cpp $ROOT/vulcan_b200/cxx/sharded.cpp"
+SRC="$ROOT/vulcan_b200/cxx/vulcan.cpp $ROOT/vulcan_b200/cxx/pipeline.cpp $ROOT/vulcan_b200/cxx/sharded.cpp $ROOT/vulcan_b200/cxx/sharded_pipeline.cpp"
 LIB="$OUT/libvulcan.so"
 FLAGS="-std=c++14 -O2 -fPIC -Wall -DNDEBUG -I$ROOT/include -I$CUDA/include"
-if [ ! -f "$LIB" ] || [ "$ROOT/vulcan_b200/cxx/vulcan.cpp" -nt "$LIB" ] || [ "$ROOT/vulcan_b200/cxx/pipeline.cpp" -nt "$LIB" ] || [ "$ROOT/vulcan_b200/cxx/sharded.cpp" -nt "$LIB" ] || [ -n "$(find "$ROOT/include" -newer "$LIB" -name '*.h*' | head -1)" ]; then
+if [ ! -f "$LIB" ] || [ "$ROOT/vulcan_b200/cxx/vulcan.cpp" -nt "$LIB" ] || [ "$ROOT/vulcan_b200/cxx/pipeline.cpp" -nt "$LIB" ] || [ "$ROOT/vulcan_b200/cxx/sharded.cpp" -nt "$LIB" ] || [ "$ROOT/vulcan_b200/cxx/sharded_pipeline.cpp" -nt "$LIB" ] || [ -n "$(find "$ROOT/include" -newer "$LIB" -name '*.h*' | head -1)" ]; then
   g++ $FLAGS -shared -o "$LIB" $SRC -L"$OUT" -lvulcan_b200 -L"$CUDA/lib64" -lcudart \
       -Wl,-rpath,'$ORIGIN' -Wl,-rpath,"$CUDA/lib64"
 fi

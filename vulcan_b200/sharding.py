@@ -218,3 +218,145 @@ class Shard:
         if getattr(self, "_alive", False):
             _lib.lib.vk_shard_destroy(C.byref(self._s), C.byref(self.volume._v))
             self._alive = False
+
+
+class ShardedPipeline:
+    """Host frames in, host image BANDS out, for one rank of a block-sharded volume (the streamed counterpart of
+    FramePipeline; the consumer is the host, so no image is exchanged between the GPUs: every rank uploads the depth
+    image, ray-casts its band of rows and downloads that band only - the ranks' bands together are one image set).
+
+    Three streams per rank - upload of frame k+1, SetView + Integrate + sharded Trace of frame k, download of the band
+    of frame k-1 - over `depth` >= 3 slots.  Which rows a rank renders is decided on the device (the bands are balanced
+    from the merged ray bounds), so a frame's band table is fetched asynchronously (vk_shard_band_async) and its band is
+    copied one submit later, while the next frame computes; the shard's output images of a view stay valid until the
+    second-next Trace, which therefore waits for that copy.
+
+        pipe = ShardedPipeline(shard, integrator, 640, 480)
+        k = pipe.submit(pinned_depth, frame)            # every rank, same frames, same order (Trace is collective)
+        b0, b1, depth, color, normal = pipe.result(k)   # pinned host images; rows [b0, b1) are this rank's
+    """
+
+    class _Slot:
+        pass
+
+    def __init__(self, shard, integrator, width, height, depth=3, device=None):
+        import torch
+        from . import _lib, api
+        if depth < 3:
+            raise api.VulcanError("a sharded pipeline needs at least 3 slots")
+        self.shard_, self.volume_, self.integrator_ = shard, shard.volume, integrator
+        self.w_, self.h_ = int(width), int(height)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+        f32 = torch.float32
+        self.slots_ = []
+        for _ in range(depth):
+            s = ShardedPipeline._Slot()
+            s.d_depth = torch.empty((self.h_, self.w_), dtype=f32, device=dev)
+            s.h_depth = torch.zeros((self.h_, self.w_), dtype=f32).pin_memory()
+            s.h_color = torch.zeros((self.h_, self.w_, 3), dtype=f32).pin_memory()
+            s.h_normal = torch.zeros((self.h_, self.w_, 3), dtype=f32).pin_memory()
+            s.h_bands = torch.zeros(17, dtype=torch.int32).pin_memory()
+            s.uploaded, s.computed, s.integrated = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+            s.bandinfo, s.downloaded = torch.cuda.Event(), torch.cuda.Event()
+            s.frame, s.issued, s.out, s.band = -1, True, None, (0, 0)
+            s.cin = _lib.vkFrame()
+            s.cin.depth = s.d_depth.data_ptr()
+            s.cin.depth_w, s.cin.depth_h = self.w_, self.h_
+            self.slots_.append(s)
+        self.upload_, self.compute_, self.download_ = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        self.info_ = torch.cuda.Stream(dev)   # band tables: on the download stream they would queue a band behind the next frame's kernels
+        ready = torch.cuda.Event()
+        ready.record()
+        for st in (self.upload_, self.compute_, self.download_, self.info_):
+            st.wait_event(ready)
+        self.next_ = 0
+
+    def _slot(self, k):
+        return self.slots_[k % len(self.slots_)]
+
+    def _issue_download(self, k):
+        """Enqueue the copy of frame k's band (needs its band table on the host: waits for that 68-byte copy)."""
+        import torch
+        from . import api
+        s = self._slot(k)
+        if s.frame != k or s.issued:
+            return
+        s.bandinfo.synchronize()
+        bands = s.h_bands.tolist()
+        if bands[16] != 0:
+            raise api.VulcanError("sharded volume: a peer did not arrive at a handshake (VK_E_TIMEOUT)")
+        b0, b1 = bands[self.shard_.rank], bands[self.shard_.rank + 1]
+        s.band = (b0, b1)
+        with torch.cuda.stream(self.download_):
+            # the copy starts when the NEXT frame (if submitted) has finished integrating: allocation and integration
+            # store into the peers' replicas, and those stores queue behind download traffic on their way out of the GPU
+            if k + 1 < self.next_:
+                self.download_.wait_event(self._slot(k + 1).integrated)
+            if b1 > b0:
+                h, w = self.h_, self.w_
+                for host, ptr, shape in ((s.h_depth, s.out[0], (h, w)), (s.h_color, s.out[1], (h, w, 3)),
+                                         (s.h_normal, s.out[2], (h, w, 3))):
+                    src = api.device_view(ptr, shape, "<f4")
+                    host[b0:b1].copy_(src[b0:b1], non_blocking=True)
+            s.downloaded.record()
+        s.issued = True
+
+    def submit(self, host_depth, frame):
+        import ctypes as C
+        import torch
+        from . import _lib, api
+        k = self.next_
+        s = self._slot(k)
+        if s.frame >= 0:
+            self._issue_download(s.frame)
+            s.downloaded.synchronize()          # the slot's previous frame has left the device
+        # the band of frame k-2 must be on its way before Trace(k) reuses that view's output images
+        if k >= 2:
+            self._issue_download(k - 2)
+        s.frame, s.issued = k, False
+        with torch.cuda.stream(self.upload_):
+            s.d_depth.copy_(host_depth, non_blocking=True)
+            s.uploaded.record()
+        cin = s.cin
+        cin.depth_proj = frame.depth_projection.to_c()
+        cin.depth_to_world = frame.depth_to_world_transform.to_c()
+        v = C.byref(self.volume_._v)
+        integ, sh = self.integrator_, self.shard_
+        d, c, n = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        with torch.cuda.stream(self.compute_):
+            st = C.c_void_p(self.compute_.cuda_stream)
+            self.compute_.wait_event(s.uploaded)
+            if k >= 2:
+                self.compute_.wait_event(self._slot(k - 2).downloaded)
+            self.volume_.SyncDistances()
+            api.check(_lib.lib.vk_set_view(v, C.byref(cin), st), "SetView")
+            api.check(_lib.lib.vk_integrate_depth(v, C.byref(cin), integ.depth_range_[0], integ.depth_range_[1],
+                                                  integ.max_distance_weight_, st), "Integrate")
+            s.integrated.record()
+            api.check(_lib.lib.vk_trace_sharded(v, C.byref(cin), sh.depth_range_[0], sh.depth_range_[1], 0, C.byref(d),
+                                                C.byref(c), C.byref(n), st), "vk_trace_sharded")
+            s.computed.record()
+        s.out = (d.value, c.value, n.value)
+        with torch.cuda.stream(self.info_):
+            self.info_.wait_event(s.computed)
+            api.check(_lib.lib.vk_shard_band_async(v, s.h_bands.data_ptr(), C.c_void_p(self.info_.cuda_stream)),
+                      "vk_shard_band_async")
+            s.bandinfo.record()
+        self.next_ = k + 1
+        return k
+
+    def result(self, k):
+        """Block until frame k's band is in host memory: (row_begin, row_end, depth, color, normal)."""
+        from . import api
+        s = self._slot(k)
+        if s.frame != k:
+            raise api.VulcanError("frame %d is no longer (or not yet) in the pipeline" % k)
+        self._issue_download(k)
+        s.downloaded.synchronize()
+        return s.band[0], s.band[1], s.h_depth, s.h_color, s.h_normal
+
+    def drain(self):
+        for j in range(max(0, self.next_ - len(self.slots_)), self.next_):
+            self._issue_download(j)
+        for st in (self.upload_, self.compute_, self.download_, self.info_):
+            st.synchronize()
