@@ -1509,6 +1509,24 @@ namespace vk {
 int trace_sharded_bounds(const vkVolume* v, const vkFrame* view, float min_depth, float max_depth, const Xchg& x,
                          cudaStream_t s) {
   // the working grid lives in this rank's exchange buffer, cells as (min depth, -max depth)
+  if (x.stages == 4) {
+    // One rank per GPU, store-only launch: like vk_trace, the rank's own bounds (and their stores into the peers'
+    // slots) depend on vk_set_view only and run on the volume's side stream, beside the integration; the announce +
+    // wait + merge launch that follows on `s` is ordered after both.
+    const bool fork = !stream_capturing(s) && v->aux_valid && v->aux_stream && g_tune[VK_TUNE_TRACE_FORK].load() != 0;
+    cudaStream_t bs = s;
+    if (fork) {
+      bs = (cudaStream_t)v->aux_stream;
+      cudaError_t e = cudaStreamWaitEvent(bs, (cudaEvent_t)v->ev_view, 0);
+      if (e == cudaSuccess) e = cudaStreamWaitEvent(bs, (cudaEvent_t)v->ev_trace, 0);
+      if (e != cudaSuccess) return (int)e;
+    }
+    const int rc = trace_bounds(v, view, min_depth, max_depth, xchg_grid(x.buf[x.rank]), bs, true, &x);
+    if (rc || !fork) return rc;
+    cudaError_t e = cudaEventRecord((cudaEvent_t)v->ev_bounds, bs);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s, (cudaEvent_t)v->ev_bounds, 0);
+    return (int)e;
+  }
   if (xchg_stores(x.stages)) return trace_bounds(v, view, min_depth, max_depth, xchg_grid(x.buf[x.rank]), s, true, &x);
   // second half only (the first half ran in an earlier launch)
   BoundsParams b;
@@ -1554,8 +1572,10 @@ int trace_sharded_band(const vkVolume* v, const vkFrame* view, const Xchg& x, fl
   t.band_rank = x.rank;
   int rc = launch_raycast<false>(t, v->math_mode, s, true);
   if (rc) return rc;
-  return normals_mode(depth, &view->depth_proj, normal, view->depth_w, view->depth_h, v->math_mode, s, 0, -1, t.bands,
-                      t.band_rank);
+  rc = normals_mode(depth, &view->depth_proj, normal, view->depth_w, view->depth_h, v->math_mode, s, 0, -1, t.bands,
+                    t.band_rank);
+  if (rc) return rc;
+  return trace_done(v, s);   // the working grid may be rewritten from here on
 }
 
 }  // namespace vk
