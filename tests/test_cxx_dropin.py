@@ -38,7 +38,10 @@ def test_cxx_library_builds_and_exports_reference_classes():
                    "vulcan::ComputeNormals(", "vulcan::ResetBoundsBuffer(",
                    "vulcan::FramePipeline::Submit(", "vulcan::FramePipeline::Result(int)",
                    "vulcan::ShardedTracer::Trace(", "vulcan::ShardedTracer::ConnectLocal(",
-                   "vulcan_pipeline_create", "vulcan_pipeline_run", "vulcan_pipeline_submit", "vulcan_pipeline_result"):
+                   "vulcan::ShardedPipeline::Submit(", "vulcan::ShardedPipeline::Result(int)",
+                   "vulcan_pipeline_create", "vulcan_pipeline_run", "vulcan_pipeline_submit", "vulcan_pipeline_result",
+                   "vulcan_shard_handles_bytes", "vulcan_sharded_pipeline_create", "vulcan_sharded_pipeline_export",
+                   "vulcan_sharded_pipeline_connect", "vulcan_sharded_pipeline_run", "vulcan_sharded_pipeline_destroy"):
         assert needle in syms, "libvulcan.so does not define " + needle
     assert os.path.exists(BIN)
 
